@@ -1,0 +1,311 @@
+"""Host-side mirror of Spark ML's RandomForestClassifier / RandomForestClassificationModel.
+
+Same names, argument meaning and error behaviour as the Estimator/Model pair the reference would
+call for this stage (Spark 2.4.6 ml/classification/RandomForestClassifier.scala; dependency pinned
+at pom.xml:56-61; the stage it replaces in the reference program is the model train/predict block
+Main.java:110-141).  Everything below the setters goes through the C ABI of include/emrf.h — there
+is no Python or CPU compute path here.  (The Java 8 host + JNI shim for the same ABI are under
+euromillioner_b200/host/; no JDK exists in this image, so they ship as source.)
+"""
+import ctypes as C
+import threading
+
+import numpy as np
+
+from . import _lib
+from ._lib import EmrfParams, EmrfTimings, check
+
+DEFAULT_SEED = 207336481  # "org.apache.spark.ml.classification.RandomForestClassifier".hashCode
+_SUBSET_KINDS = {"auto": 0, "all": 1, "sqrt": 2, "log2": 3, "onethird": 4}
+
+
+def _ptr(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+class Context:
+    """Owns one GPU (device, stream, scratch) — emrf_ctx_t."""
+
+    def __init__(self, device=0, rank=0, world=1, nccl_uid=None):
+        L = _lib.lib()
+        h = C.c_void_p()
+        if world > 1:
+            uid = (C.c_uint8 * 128).from_buffer_copy(bytes(nccl_uid))
+            check(L.emrf_ctx_create_dist(device, rank, world, uid, C.byref(h)))
+        else:
+            check(L.emrf_ctx_create(device, C.byref(h)))
+        self.h, self.device, self.rank, self.world = h, device, rank, world
+
+    @staticmethod
+    def nccl_unique_id():
+        uid = (C.c_uint8 * 128)()
+        check(_lib.lib().emrf_nccl_unique_id(uid))
+        return bytes(uid)
+
+    def timings(self):
+        t = EmrfTimings()
+        check(_lib.lib().emrf_get_timings(self.h, C.byref(t)))
+        return t.as_dict()
+
+    def close(self):
+        if getattr(self, "h", None):
+            _lib.lib().emrf_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default_ctx = None
+_default_lock = threading.Lock()
+
+
+def default_context():
+    global _default_ctx
+    with _default_lock:
+        if _default_ctx is None:
+            _default_ctx = Context(0)
+        return _default_ctx
+
+
+class Dataset:
+    """The slice of Dataset[Row] this stage reads: a dense `features` column (N x F float64), a
+    `label` column (N float64) and the partition layout (Spark seeds bagging and split sampling per
+    partition, so it is part of the input).  `features`/`label` may also be raw device pointers
+    (int) when the data is already resident in HBM; then n_rows/n_features must be given."""
+
+    def __init__(self, features, label=None, num_partitions=1, partition_offsets=None, n_rows=None, n_features=None):
+        if isinstance(features, (int, np.integer)):
+            self.features, self.n_rows, self.n_features = int(features), int(n_rows), int(n_features)
+        else:
+            self.features = np.ascontiguousarray(features, np.float64)
+            if self.features.ndim != 2:
+                raise ValueError("features must be a 2-D array (rows x features)")
+            self.n_rows, self.n_features = self.features.shape
+        if label is None or isinstance(label, (int, np.integer)):
+            self.label = None if label is None else int(label)
+        else:
+            self.label = np.ascontiguousarray(label, np.float64)
+            if self.label.shape != (self.n_rows,):
+                raise ValueError("label must have one value per row")
+        if partition_offsets is None:
+            # SparkContext.parallelize slicing: [floor(i*N/P), floor((i+1)*N/P))
+            partition_offsets = [(i * self.n_rows) // num_partitions for i in range(num_partitions + 1)]
+        self.partition_offsets = np.ascontiguousarray(partition_offsets, np.int64)
+        self.columns = {}
+
+    def _fptr(self):
+        return C.c_void_p(self.features) if isinstance(self.features, int) else _ptr(self.features)
+
+    def _lptr(self):
+        return C.c_void_p(self.label) if isinstance(self.label, int) else _ptr(self.label)
+
+
+class RandomForestClassifier:
+    """Estimator.  Setters return self, defaults are Spark's (ml/tree/treeParams.scala)."""
+
+    def __init__(self, context=None):
+        self._ctx = context
+        self.numTrees, self.maxDepth, self.maxBins = 20, 5, 32
+        self.minInstancesPerNode, self.minInfoGain = 1, 0.0
+        self.impurity, self.featureSubsetStrategy = "gini", "auto"
+        self.subsamplingRate, self.maxMemoryInMB, self.seed = 1.0, 256, DEFAULT_SEED
+        self.cacheNodeIds, self.checkpointInterval = False, 10
+        self.numClasses = 0  # 0 = infer from labels (Predictor.getNumClasses)
+        self.findSplitsPolicy = 0
+        self.shardMode = 0
+
+    # --- Spark ML setters -----------------------------------------------------------------
+    def setNumTrees(self, v):
+        if int(v) < 1:
+            raise ValueError(f"numTrees must be >= 1 (got {v})")
+        self.numTrees = int(v); return self
+
+    def setMaxDepth(self, v):
+        if not 0 <= int(v) <= 30:
+            raise ValueError(f"maxDepth must be in [0, 30] (got {v})")
+        self.maxDepth = int(v); return self
+
+    def setMaxBins(self, v):
+        if int(v) < 2:
+            raise ValueError(f"maxBins must be >= 2 (got {v})")
+        self.maxBins = int(v); return self
+
+    def setMinInstancesPerNode(self, v):
+        if int(v) < 1:
+            raise ValueError("minInstancesPerNode must be >= 1")
+        self.minInstancesPerNode = int(v); return self
+
+    def setMinInfoGain(self, v):
+        if float(v) < 0:
+            raise ValueError("minInfoGain must be >= 0")
+        self.minInfoGain = float(v); return self
+
+    def setImpurity(self, v):
+        if str(v).lower() not in ("gini", "entropy"):
+            raise ValueError(f"impurity must be gini or entropy (got {v})")
+        self.impurity = str(v).lower(); return self
+
+    def setFeatureSubsetStrategy(self, v):
+        s = str(v).lower()
+        if s not in _SUBSET_KINDS:
+            try:
+                f = float(s)
+            except ValueError:
+                raise ValueError(f"unsupported featureSubsetStrategy: {v}")
+            if not (f > 0):
+                raise ValueError(f"unsupported featureSubsetStrategy: {v}")
+        self.featureSubsetStrategy = s; return self
+
+    def setSubsamplingRate(self, v):
+        if not 0 < float(v) <= 1:
+            raise ValueError("subsamplingRate must be in (0, 1]")
+        self.subsamplingRate = float(v); return self
+
+    def setMaxMemoryInMB(self, v):
+        if int(v) < 0:
+            raise ValueError("maxMemoryInMB must be >= 0")
+        self.maxMemoryInMB = int(v); return self
+
+    def setSeed(self, v):
+        self.seed = int(v); return self
+
+    def setCacheNodeIds(self, v):      # accepted; results do not depend on it
+        self.cacheNodeIds = bool(v); return self
+
+    def setCheckpointInterval(self, v):  # accepted; only meaningful with cacheNodeIds in Spark
+        self.checkpointInterval = int(v); return self
+
+    def setNumClasses(self, v):        # stands in for label-column NominalAttribute metadata
+        self.numClasses = int(v); return self
+
+    def _params(self):
+        p = EmrfParams()
+        p.num_trees, p.max_depth, p.max_bins = self.numTrees, self.maxDepth, self.maxBins
+        p.min_instances_per_node, p.num_classes = self.minInstancesPerNode, self.numClasses
+        p.impurity = 0 if self.impurity == "gini" else 1
+        s = self.featureSubsetStrategy
+        if s in _SUBSET_KINDS:
+            p.feature_subset_kind, p.feature_subset_value = _SUBSET_KINDS[s], 0.0
+        elif s.isdigit():
+            p.feature_subset_kind, p.feature_subset_value = 5, float(int(s))
+        else:
+            p.feature_subset_kind, p.feature_subset_value = 6, float(s)
+        p.min_info_gain, p.subsampling_rate = self.minInfoGain, self.subsamplingRate
+        p.max_memory_mb, p.find_splits_policy, p.seed = self.maxMemoryInMB, self.findSplitsPolicy, self.seed
+        p.shard_mode = self.shardMode
+        return p
+
+    def fit(self, dataset):
+        """Predictor.fit → RandomForestClassifier.train → RandomForest.run.  Synchronous."""
+        ctx = self._ctx or default_context()
+        L = _lib.lib()
+        if dataset.label is None:
+            raise ValueError("dataset has no label column")
+        p = self._params()
+        h = C.c_void_p()
+        po = dataset.partition_offsets
+        check(L.emrf_fit(ctx.h, C.byref(p), dataset._fptr(), dataset._lptr(), dataset.n_rows, dataset.n_features,
+                         po.ctypes.data_as(C.POINTER(C.c_int64)), len(po) - 1, C.byref(h)))
+        return RandomForestClassificationModel(ctx, h)
+
+
+class RandomForestClassificationModel:
+    """Model.  transform adds rawPrediction / probability / prediction (first-max argmax)."""
+
+    def __init__(self, ctx, handle):
+        self._ctx, self._h = ctx, handle
+        L = _lib.lib()
+        t, c, f, n = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int64()
+        check(L.emrf_forest_info(handle, C.byref(t), C.byref(c), C.byref(f), C.byref(n)))
+        self.numTrees, self.numClasses, self.numFeatures, self.totalNumNodes = t.value, c.value, f.value, n.value
+        self.treeWeights = [1.0] * self.numTrees
+        self._export = None
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib.lib().emrf_forest_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    @classmethod
+    def from_arrays(cls, e, num_features, ctx=None):
+        """Rebuild a model from the flat export (the persistence hook)."""
+        ctx = ctx or default_context()
+        L = _lib.lib()
+        T = len(e["tree_off"]) - 1
+        Cn = e["stats"].shape[1]
+        arrs = [np.ascontiguousarray(e[k], dt) for k, dt in (
+            ("tree_off", np.int64), ("node_id", np.int32), ("left", np.int32), ("right", np.int32),
+            ("feature", np.int32), ("threshold", np.float64), ("gain", np.float64), ("impurity", np.float64),
+            ("prediction", np.float64), ("stats", np.float64))]
+        h = C.c_void_p()
+        check(L.emrf_forest_import(ctx.h, T, Cn, num_features, *[_ptr(a) for a in arrs], C.byref(h)))
+        return cls(ctx, h)
+
+    def export(self):
+        """Flat arrays: trees in index order, nodes pre-order (see emrf_forest_export)."""
+        if self._export is None:
+            n, Cn = self.totalNumNodes, self.numClasses
+            e = {"tree_off": np.zeros(self.numTrees + 1, np.int64), "node_id": np.zeros(n, np.int32),
+                 "left": np.zeros(n, np.int32), "right": np.zeros(n, np.int32), "feature": np.zeros(n, np.int32),
+                 "threshold": np.zeros(n), "gain": np.zeros(n), "impurity": np.zeros(n), "prediction": np.zeros(n),
+                 "stats": np.zeros((n, Cn))}
+            check(_lib.lib().emrf_forest_export(self._h, *[_ptr(e[k]) for k in (
+                "tree_off", "node_id", "left", "right", "feature", "threshold", "gain", "impurity", "prediction", "stats")]))
+            self._export = e
+        return self._export
+
+    def trace(self):
+        """(group_sizes, per-popped-node rows [tree, node id, F_sub features]) of the fit."""
+        L = _lib.lib()
+        g, n, fs = C.c_int32(), C.c_int64(), C.c_int32()
+        check(L.emrf_forest_trace_info(self._h, C.byref(g), C.byref(n), C.byref(fs)))
+        gs, tr = np.zeros(g.value, np.int32), np.zeros(n.value, np.int32)
+        check(L.emrf_forest_trace(self._h, _ptr(gs), _ptr(tr)))
+        return gs, tr.reshape(-1, 2 + fs.value) if fs.value >= 0 and n.value else tr
+
+    @property
+    def featureImportances(self):
+        out = np.zeros(self.numFeatures)
+        check(_lib.lib().emrf_forest_feature_importances(self._h, _ptr(out)))
+        return out
+
+    @property
+    def toDebugString(self):
+        """Spark's text form: `If (feature 3 <= 24.5)` / `Else (feature 3 > 24.5)` / `Predict: 12.0`."""
+        e = self.export()
+        lines = [f"RandomForestClassificationModel with {self.numTrees} trees"]
+
+        def walk(base, i, depth):
+            pad = " " * (depth + 4)  # Node.subtreeToString(indentFactor = 4 + depth)
+            if e["left"][base + i] < 0:
+                lines.append(f"{pad}Predict: {float(e['prediction'][base + i])!r}")
+                return
+            f, thr = int(e["feature"][base + i]), float(e["threshold"][base + i])
+            lines.append(f"{pad}If (feature {f} <= {thr!r})")
+            walk(base, e["left"][base + i], depth + 1)
+            lines.append(f"{pad}Else (feature {f} > {thr!r})")
+            walk(base, e["right"][base + i], depth + 1)
+
+        for t in range(self.numTrees):
+            lines.append(f"  Tree {t} (weight 1.0):")
+            walk(int(e["tree_off"][t]), 0, 0)
+        return "\n".join(lines) + "\n"
+
+    def transform(self, dataset, raw=True, probability=True):
+        """Returns the dataset with rawPrediction (N x C), probability (N x C), prediction (N)."""
+        if dataset.n_features != self.numFeatures:
+            raise ValueError(f"features column has {dataset.n_features} values per row, model expects {self.numFeatures}")
+        n, Cn = dataset.n_rows, self.numClasses
+        rawp = np.zeros((n, Cn)) if raw else None
+        prob = np.zeros((n, Cn)) if probability else None
+        pred = np.zeros(n)
+        check(_lib.lib().emrf_predict(self._ctx.h, self._h, dataset._fptr(), n, _ptr(rawp), _ptr(prob), _ptr(pred)))
+        dataset.columns.update({"rawPrediction": rawp, "probability": prob, "prediction": pred})
+        return dataset

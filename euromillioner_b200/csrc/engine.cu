@@ -1,0 +1,1445 @@
+// engine.cu — C ABI (include/emrf.h) of the B200-native random-forest engine.
+//
+// Host side of RandomForest.run (ml/tree/impl/RandomForest.scala, Spark 2.4.6; dependency pin
+// pom.xml:56-61): the sequential node scheduler (selectNodesToSplit: LIFO stack, memory-bounded
+// groups, per-node feature subsets drawn from the driver RNG) stays on the host; everything
+// row-sized runs in the kernels of kernels.cuh.  One device round trip per group for the split
+// records (~0.5 KB per node) and one for the child segment sizes.
+//
+// No PyTorch, no CPU fallback: every compute entry point needs a CUDA device.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/emrf.h"
+#include "host_logic.hpp"
+#include "kernels.cuh"
+
+using namespace emrf;
+namespace hl = emrf::hostlogic;
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+#define CU(expr)                                                                                   \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess)                                                                         \
+      return fail(EMRF_ERR_CUDA, "CUDA error %s at %s:%d: %s", cudaGetErrorName(_e), __FILE__, __LINE__, \
+                  cudaGetErrorString(_e));                                                         \
+  } while (0)
+#define TRY(expr)           \
+  do {                      \
+    int _rc = (expr);       \
+    if (_rc != EMRF_OK) return _rc; \
+  } while (0)
+
+extern "C" const char* emrf_last_error(void) { return g_err.c_str(); }
+extern "C" const char* emrf_version(void) { return "emrf 0.1 (sm_100a; Spark MLlib 2.4.6 RandomForestClassifier semantics)"; }
+
+// ---------------------------------------------------------------------------------------------
+// small RAII helpers
+// ---------------------------------------------------------------------------------------------
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  DevBuf() {}
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    bytes = 0;
+  }
+  cudaError_t alloc(size_t n) {
+    release();
+    if (n == 0) n = 16;
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e == cudaSuccess) bytes = n;
+    return e;
+  }
+  cudaError_t ensure(size_t n) {  // grow-only
+    if (n <= bytes) return cudaSuccess;
+    return alloc(n + n / 4);
+  }
+  template <class T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+struct PinnedBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  ~PinnedBuf() { if (p) cudaFreeHost(p); }
+  cudaError_t ensure(size_t n) {
+    if (n <= bytes) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    bytes = 0;
+    n += n / 4;
+    cudaError_t e = cudaHostAlloc(&p, n, cudaHostAllocDefault);
+    if (e == cudaSuccess) bytes = n;
+    return e;
+  }
+  template <class T>
+  T* as() const { return reinterpret_cast<T*>(p); }
+};
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static inline double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+static bool is_device_ptr(const void* p) {
+  if (!p) return false;
+  cudaPointerAttributes a;
+  cudaError_t e = cudaPointerGetAttributes(&a, p);
+  if (e != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// ---------------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------------
+struct EventPool {
+  std::vector<cudaEvent_t> ev;
+  size_t used = 0;
+  cudaEvent_t get() {
+    if (used == ev.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      ev.push_back(e);
+    }
+    return ev[used++];
+  }
+  void reset() { used = 0; }
+  ~EventPool() { for (auto e : ev) cudaEventDestroy(e); }
+};
+
+struct emrf_ctx {
+  int device = 0;
+  int rank = 0, world = 1;
+  cudaStream_t stream = nullptr;
+  int sm_count = 148;
+  size_t smem_optin = 0;
+  emrf_timings_t tm;
+  std::mutex fit_mu;
+  EventPool events;
+  // NCCL (loaded lazily with dlopen; only multi-GPU contexts touch it)
+  void* nccl_lib = nullptr;
+  void* nccl_comm = nullptr;
+  // grow-only scratch reused across groups
+  DevBuf d_group, d_results, d_ghist, d_tickets, d_split, d_part;
+  PinnedBuf h_group, h_results, h_split, h_part;
+};
+
+static int ctx_init(emrf_ctx* c, int device) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(EMRF_ERR_CUDA, "no CUDA device available (%s): this engine has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  }
+  if (device < 0 || device >= n) return fail(EMRF_ERR_ARG, "device %d out of range (have %d)", device, n);
+  c->device = device;
+  CU(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return fail(EMRF_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major,
+                prop.minor);
+  c->sm_count = prop.multiProcessorCount;
+  c->smem_optin = prop.sharedMemPerBlockOptin;
+  CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  memset(&c->tm, 0, sizeof(c->tm));
+  return EMRF_OK;
+}
+
+extern "C" int emrf_ctx_create(int32_t device, emrf_ctx_t** out) {
+  if (!out) return fail(EMRF_ERR_ARG, "out is NULL");
+  emrf_ctx* c = new emrf_ctx();
+  int rc = ctx_init(c, device);
+  if (rc != EMRF_OK) { delete c; return rc; }
+  *out = c;
+  return EMRF_OK;
+}
+
+// ---- NCCL via dlopen (kept out of the single-GPU link) ----------------------------------------
+typedef struct { char internal[128]; } nccl_uid_t;
+typedef int (*ncclGetUniqueId_t)(nccl_uid_t*);
+typedef int (*ncclCommInitRank_t)(void**, int, nccl_uid_t, int);
+typedef int (*ncclCommDestroy_t)(void*);
+typedef int (*ncclAllReduce_t)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef const char* (*ncclGetErrorString_t)(int);
+static void* nccl_open() {
+  static void* lib = nullptr;
+  if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  return lib;
+}
+extern "C" int emrf_nccl_unique_id(uint8_t* uid128) {
+  void* lib = nccl_open();
+  if (!lib) return fail(EMRF_ERR_CUDA, "libnccl.so.2 not found: %s", dlerror());
+  auto f = (ncclGetUniqueId_t)dlsym(lib, "ncclGetUniqueId");
+  if (!f) return fail(EMRF_ERR_CUDA, "ncclGetUniqueId missing");
+  nccl_uid_t u;
+  int rc = f(&u);
+  if (rc) return fail(EMRF_ERR_CUDA, "ncclGetUniqueId failed (%d)", rc);
+  memcpy(uid128, &u, 128);
+  return EMRF_OK;
+}
+extern "C" int emrf_ctx_create_dist(int32_t device, int32_t rank, int32_t world, const uint8_t* nccl_uid,
+                                    emrf_ctx_t** out) {
+  if (!out) return fail(EMRF_ERR_ARG, "out is NULL");
+  if (world < 1 || rank < 0 || rank >= world) return fail(EMRF_ERR_ARG, "bad rank/world %d/%d", rank, world);
+  emrf_ctx* c = new emrf_ctx();
+  int rc = ctx_init(c, device);
+  if (rc != EMRF_OK) { delete c; return rc; }
+  c->rank = rank;
+  c->world = world;
+  if (world > 1) {
+    if (!nccl_uid) { delete c; return fail(EMRF_ERR_ARG, "nccl_uid is NULL"); }
+    void* lib = nccl_open();
+    if (!lib) { delete c; return fail(EMRF_ERR_CUDA, "libnccl.so.2 not found: %s", dlerror()); }
+    c->nccl_lib = lib;
+    auto init = (ncclCommInitRank_t)dlsym(lib, "ncclCommInitRank");
+    nccl_uid_t u;
+    memcpy(&u, nccl_uid, 128);
+    int nrc = init(&c->nccl_comm, world, u, rank);
+    if (nrc) { delete c; return fail(EMRF_ERR_CUDA, "ncclCommInitRank failed (%d)", nrc); }
+  }
+  *out = c;
+  return EMRF_OK;
+}
+extern "C" void emrf_ctx_destroy(emrf_ctx_t* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->nccl_comm) {
+    auto d = (ncclCommDestroy_t)dlsym(c->nccl_lib, "ncclCommDestroy");
+    if (d) d(c->nccl_comm);
+  }
+  if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+  delete c;
+}
+extern "C" int emrf_get_timings(const emrf_ctx_t* c, emrf_timings_t* out) {
+  if (!c || !out) return fail(EMRF_ERR_ARG, "NULL argument");
+  *out = c->tm;
+  return EMRF_OK;
+}
+// allreduce (sum) of uint32 words over the ctx communicator, in place
+static int nccl_allreduce_u32(emrf_ctx* c, uint32_t* buf, size_t count) {
+  if (c->world == 1) return EMRF_OK;
+  auto ar = (ncclAllReduce_t)dlsym(c->nccl_lib, "ncclAllReduce");
+  int rc = ar(buf, buf, count, /*ncclUint32*/ 3, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+  if (rc) return fail(EMRF_ERR_CUDA, "ncclAllReduce failed (%d)", rc);
+  return EMRF_OK;
+}
+
+extern "C" int emrf_dev_alloc(emrf_ctx_t* c, int64_t bytes, void** out) {
+  if (!c || !out || bytes < 0) return fail(EMRF_ERR_ARG, "bad argument");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMalloc(out, (size_t)std::max<int64_t>(bytes, 16)));
+  return EMRF_OK;
+}
+extern "C" int emrf_dev_free(emrf_ctx_t* c, void* p) {
+  if (!c) return fail(EMRF_ERR_ARG, "ctx is NULL");
+  CU(cudaSetDevice(c->device));
+  CU(cudaFree(p));
+  return EMRF_OK;
+}
+extern "C" int emrf_host_alloc_pinned(int64_t bytes, void** out) {
+  if (!out || bytes < 0) return fail(EMRF_ERR_ARG, "bad argument");
+  CU(cudaHostAlloc(out, (size_t)std::max<int64_t>(bytes, 16), cudaHostAllocDefault));
+  return EMRF_OK;
+}
+extern "C" int emrf_host_free_pinned(void* p) {
+  CU(cudaFreeHost(p));
+  return EMRF_OK;
+}
+extern "C" int emrf_memcpy_h2d(emrf_ctx_t* c, void* dst, const void* src, int64_t bytes) {
+  if (!c) return fail(EMRF_ERR_ARG, "ctx is NULL");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return EMRF_OK;
+}
+extern "C" int emrf_memcpy_d2h(emrf_ctx_t* c, void* dst, const void* src, int64_t bytes) {
+  if (!c) return fail(EMRF_ERR_ARG, "ctx is NULL");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return EMRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// parameter checks (the `require`s of ml/tree/treeParams.scala and Strategy.assertValid)
+// ---------------------------------------------------------------------------------------------
+static int check_params(const emrf_params_t* p) {
+  if (!p) return fail(EMRF_ERR_ARG, "params is NULL");
+  if (p->num_trees < 1) return fail(EMRF_ERR_ARG, "numTrees must be >= 1 (got %d)", p->num_trees);
+  if (p->max_depth < 0 || p->max_depth > 30) return fail(EMRF_ERR_ARG, "maxDepth must be in [0,30] (got %d)", p->max_depth);
+  if (p->max_bins < 2) return fail(EMRF_ERR_ARG, "maxBins must be >= 2 (got %d)", p->max_bins);
+  if (p->max_bins > 256) return fail(EMRF_ERR_LIMIT, "maxBins > 256 is not supported by the uint8 TreePoint matrix");
+  if (p->min_instances_per_node < 1) return fail(EMRF_ERR_ARG, "minInstancesPerNode must be >= 1");
+  if (!(p->subsampling_rate > 0.0 && p->subsampling_rate <= 1.0)) return fail(EMRF_ERR_ARG, "subsamplingRate must be in (0,1]");
+  if (p->impurity != 0 && p->impurity != 1) return fail(EMRF_ERR_ARG, "impurity must be gini(0) or entropy(1)");
+  if (p->feature_subset_kind < 0 || p->feature_subset_kind > 6) return fail(EMRF_ERR_ARG, "bad featureSubsetStrategy");
+  if (p->feature_subset_kind == 5 && p->feature_subset_value < 1) return fail(EMRF_ERR_ARG, "featureSubsetStrategy n must be >= 1");
+  if (p->feature_subset_kind == 6 && !(p->feature_subset_value > 0 && p->feature_subset_value <= 1.0))
+    return fail(EMRF_ERR_ARG, "featureSubsetStrategy fraction must be in (0,1]");
+  if (p->max_memory_mb < 0) return fail(EMRF_ERR_ARG, "maxMemoryInMB must be >= 0");
+  if (p->num_classes < 0 || p->num_classes > 256) return fail(EMRF_ERR_LIMIT, "numClasses must be <= 256");
+  return EMRF_OK;
+}
+static int check_partitions(int64_t n_rows, const int64_t* off, int n_parts) {
+  if (!off || n_parts < 1) return fail(EMRF_ERR_ARG, "partition_offsets missing");
+  if (off[0] != 0 || off[n_parts] != n_rows) return fail(EMRF_ERR_ARG, "partition_offsets must span [0, n_rows]");
+  for (int i = 0; i < n_parts; i++)
+    if (off[i + 1] < off[i]) return fail(EMRF_ERR_ARG, "partition_offsets must be non-decreasing");
+  return EMRF_OK;
+}
+
+// Bring a host-or-device input onto the device.  `owned` keeps the copy alive.
+static int stage_input(emrf_ctx* c, const void* src_hd, size_t bytes, DevBuf& owned, const void** dev_out, bool* copied) {
+  if (is_device_ptr(src_hd)) {
+    *dev_out = src_hd;
+    if (copied) *copied = false;
+    return EMRF_OK;
+  }
+  CU(owned.alloc(bytes));
+  CU(cudaMemcpyAsync(owned.p, src_hd, bytes, cudaMemcpyHostToDevice, c->stream));
+  *dev_out = owned.p;
+  if (copied) *copied = true;
+  return EMRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// findSplits on the device
+// ---------------------------------------------------------------------------------------------
+static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX, int64_t N, int F, const int64_t* part_off,
+                           int n_parts, DevBuf& d_thr, DevBuf& d_ns, std::vector<double>& h_thr, std::vector<int>& h_ns) {
+  const int TS = P.max_bins;
+  const int max_possible_bins = (int)std::min<int64_t>(P.max_bins, N);
+  const int num_splits = max_possible_bins - 1;
+  CU(d_thr.alloc((size_t)F * TS * 8));
+  CU(d_ns.alloc((size_t)F * 4));
+  CU(cudaMemsetAsync(d_thr.p, 0, (size_t)F * TS * 8, c->stream));
+  CU(cudaMemsetAsync(d_ns.p, 0, (size_t)F * 4, c->stream));
+  h_thr.assign((size_t)F * TS, 0.0);
+  h_ns.assign(F, 0);
+  if (num_splits >= 1) {
+    std::vector<int64_t> rows;
+    const bool sampled = hl::find_splits_rows(P, N, part_off, n_parts, &rows);
+    const int64_t n_s64 = sampled ? (int64_t)rows.size() : N;
+    if (n_s64 > (1 << 22)) return fail(EMRF_ERR_LIMIT, "findSplits sample too large (%lld)", (long long)n_s64);
+    const int n_s = (int)n_s64;
+    const double fraction = hl::find_splits_fraction(P, N);
+    const int64_t expected = (int64_t)(int32_t)(fraction * (double)N);
+    if (n_s > 0) {
+      int n_pad = 2;
+      while (n_pad < n_s) n_pad <<= 1;
+      DevBuf d_rows, d_S;
+      if (sampled) {
+        CU(d_rows.alloc((size_t)n_s * 8));
+        CU(cudaMemcpyAsync(d_rows.p, rows.data(), (size_t)n_s * 8, cudaMemcpyHostToDevice, c->stream));
+      }
+      CU(d_S.alloc((size_t)F * n_pad * 8));
+      const int64_t total = (int64_t)n_pad * F;
+      kern::fs_gather_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(
+          dX, F, d_rows.as<int64_t>(), n_s, n_pad, sampled ? 0 : 1, P.find_splits_policy == 0 ? 1 : 0, d_S.as<double>());
+      const int use_smem = ((size_t)n_pad * 8 <= 128 * 1024) ? 1 : 0;
+      const size_t smem = use_smem ? (size_t)n_pad * 8 : 0;
+      if (smem > 48 * 1024)
+        CU(cudaFuncSetAttribute(kern::fs_sort_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      kern::fs_sort_walk_kernel<<<F, 1024, smem, c->stream>>>(d_S.as<double>(), n_pad, n_s, use_smem, num_splits, expected,
+                                                             P.find_splits_policy, TS, d_thr.as<double>(), d_ns.as<int>());
+      c->tm.kernel_launches += 2;
+      CU(cudaGetLastError());
+      CU(cudaMemcpyAsync(h_thr.data(), d_thr.p, (size_t)F * TS * 8, cudaMemcpyDeviceToHost, c->stream));
+      CU(cudaMemcpyAsync(h_ns.data(), d_ns.p, (size_t)F * 4, cudaMemcpyDeviceToHost, c->stream));
+      CU(cudaStreamSynchronize(c->stream));  // d_rows/d_S/rows die here
+    }
+  }
+  for (int f = 0; f < F; f++)
+    if (h_ns[f] > TS || h_ns[f] >= 256)
+      return fail(EMRF_ERR_LIMIT, "feature %d produced %d splits (> maxBins); not representable", f, h_ns[f]);
+  return EMRF_OK;
+}
+
+static int run_bin(emrf_ctx* c, const double* dX, int64_t N, int F, const double* d_thr, const int* d_ns, int TS, int Fp,
+                   int64_t Np, uint8_t* d_rm, uint8_t* d_cm) {
+  const size_t tile_bytes = align_up((size_t)kern::kBinRows * Fp, 16);
+  const size_t thr_bytes = (size_t)F * TS * 8;
+  const unsigned grid = (unsigned)((N + kern::kBinRows - 1) / kern::kBinRows);
+  if (tile_bytes + thr_bytes <= 160 * 1024) {
+    const size_t smem = tile_bytes + thr_bytes;
+    if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern::bin_kernel<true><<<grid, 256, smem, c->stream>>>(dX, N, F, Fp, Np, d_thr, d_ns, TS, d_rm, d_cm);
+  } else {
+    if (tile_bytes > 200 * 1024) return fail(EMRF_ERR_LIMIT, "too many features for the binning tile (%d)", F);
+    if (tile_bytes > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes));
+    kern::bin_kernel<false><<<grid, 256, tile_bytes, c->stream>>>(dX, N, F, Fp, Np, d_thr, d_ns, TS, d_rm, d_cm);
+  }
+  c->tm.kernel_launches += 1;
+  CU(cudaGetLastError());
+  return EMRF_OK;
+}
+
+static int run_bag(emrf_ctx* c, const emrf_params_t& P, int64_t N, const int64_t* part_off, int n_parts, uint8_t* d_w,
+                   int* max_w_out) {
+  const int T = P.num_trees;
+  DevBuf d_off, d_max;
+  CU(d_off.alloc((size_t)(n_parts + 1) * 8));
+  CU(d_max.alloc(4));
+  CU(cudaMemcpyAsync(d_off.p, part_off, (size_t)(n_parts + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemsetAsync(d_max.p, 0, 4, c->stream));
+  if (T > 1) {
+    const double mean = P.subsampling_rate;
+    const double p_exp = std::exp(-mean);
+    kern::bag_poisson_kernel<<<(n_parts + 31) / 32, 32, 0, c->stream>>>(P.seed, d_off.as<int64_t>(), n_parts, T, mean, p_exp,
+                                                                         d_w, d_max.as<int>());
+  } else if (P.subsampling_rate == 1.0) {
+    CU(cudaMemsetAsync(d_w, 1, (size_t)N * T, c->stream));
+    int one = 1;
+    CU(cudaMemcpyAsync(d_max.p, &one, 4, cudaMemcpyHostToDevice, c->stream));
+  } else {
+    kern::bag_bernoulli_kernel<<<(n_parts + 63) / 64, 64, 0, c->stream>>>(P.seed, d_off.as<int64_t>(), n_parts, T,
+                                                                           P.subsampling_rate, d_w);
+    int one = 1;
+    CU(cudaMemcpyAsync(d_max.p, &one, 4, cudaMemcpyHostToDevice, c->stream));
+  }
+  c->tm.kernel_launches += 1;
+  CU(cudaGetLastError());
+  int mw = 0;
+  CU(cudaMemcpyAsync(&mw, d_max.p, 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  if (max_w_out) *max_w_out = mw;
+  if (mw > 255) return fail(EMRF_ERR_LIMIT, "a bootstrap weight exceeded 255");
+  return EMRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// forest
+// ---------------------------------------------------------------------------------------------
+struct FlatNode {
+  int32_t id, left, right, feature;
+  double threshold, gain, impurity, prediction;
+};
+struct emrf_forest {
+  int num_trees = 0, num_classes = 0, num_features = 0;
+  std::vector<int64_t> tree_off;
+  std::vector<FlatNode> nodes;
+  std::vector<double> stats;  // nodes*C
+  std::vector<int32_t> group_sizes, trace;
+  int f_sub = 0;
+  // device copy for predict (built once)
+  std::mutex dev_mu;
+  int dev_device = -1;
+  DevBuf d_nodes, d_roots, d_leaf_prob;
+};
+
+struct HNode {
+  int32_t id = 1;
+  int32_t left = -1, right = -1;
+  bool is_leaf = false, valid = true, has_stats = false;
+  int32_t feature = -1, split_bin = -1;
+  double threshold = 0.0, gain = std::numeric_limits<double>::quiet_NaN(), impurity = 0.0;
+  uint64_t seg_start = 0;
+  uint32_t seg_len = 0;
+  uint32_t buf = 0;
+  size_t counts_at = 0;  // index into the tree's counts pool (C words), valid when has_stats
+};
+struct HTree {
+  std::vector<HNode> pool;
+  std::vector<uint32_t> counts;
+};
+
+static int first_max(const uint32_t* a, int C) {
+  int mi = 0;
+  for (int c = 1; c < C; c++) if (a[c] > a[mi]) mi = c;
+  return mi;
+}
+// LearningNode.toNode(prune = true) (ml/tree/Node.scala)
+static int64_t export_node(const HTree& t, int ni, int C, emrf_forest& fo) {
+  const HNode& n = t.pool[ni];
+  const int64_t base = fo.tree_off.back();
+  const int64_t me = (int64_t)fo.nodes.size();
+  fo.nodes.emplace_back();
+  fo.stats.resize(fo.nodes.size() * (size_t)C);
+  const uint32_t* cnt = &t.counts[n.counts_at];
+  auto write_leaf = [&](double pred, double imp) {
+    FlatNode& f = fo.nodes[me];
+    f.id = n.id; f.left = -1; f.right = -1; f.feature = -1;
+    f.threshold = 0.0; f.gain = 0.0; f.impurity = imp; f.prediction = pred;
+    for (int c = 0; c < C; c++) fo.stats[me * C + c] = (double)cnt[c];
+  };
+  if (n.left >= 0) {
+    const int64_t l = export_node(t, n.left, C, fo);
+    const int64_t r = export_node(t, n.right, C, fo);
+    const bool both_leaves = fo.nodes[l].left < 0 && fo.nodes[r].left < 0;
+    if (both_leaves && fo.nodes[l].prediction == fo.nodes[r].prediction) {
+      const double pred = fo.nodes[l].prediction;
+      fo.nodes.resize(me + 1);
+      fo.stats.resize(fo.nodes.size() * (size_t)C);
+      write_leaf(pred, n.impurity);
+    } else {
+      FlatNode& f = fo.nodes[me];
+      f.id = n.id; f.left = (int32_t)(l - base); f.right = (int32_t)(r - base);
+      f.feature = n.feature; f.threshold = n.threshold; f.gain = n.gain; f.impurity = n.impurity;
+      f.prediction = (double)first_max(cnt, C);
+      for (int c = 0; c < C; c++) fo.stats[me * C + c] = (double)cnt[c];
+    }
+  } else {
+    write_leaf((double)first_max(cnt, C), n.valid ? n.impurity : -1.0);
+  }
+  return me;
+}
+
+// ---------------------------------------------------------------------------------------------
+// emrf_fit
+// ---------------------------------------------------------------------------------------------
+struct GroupEntry {
+  int tree, pool;
+  int feat_at;  // index into the group's feature array
+};
+
+static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* features_hd, const double* labels_hd, int64_t N,
+                    int F, const int64_t* part_off, int n_parts, emrf_forest_t** out) {
+  emrf_params_t P = P_in;
+  emrf_timings_t& tm = c->tm;
+  memset(&tm, 0, sizeof(tm));
+  c->events.reset();
+  cudaStream_t st = c->stream;
+  CU(cudaSetDevice(c->device));
+  if (N >= (1ll << 32)) return fail(EMRF_ERR_LIMIT, "n_rows must be < 2^32");
+  if (c->world > 1 && P.shard_mode == 1) return fail(EMRF_ERR_LIMIT, "row-sharded multi-GPU fit is not built yet");
+
+  cudaEvent_t ev_start = c->events.get(), ev_in = c->events.get(), ev_fs = c->events.get(), ev_bin = c->events.get(),
+              ev_bag = c->events.get(), ev_end = c->events.get();
+  CU(cudaEventRecord(ev_start, st));
+
+  // ---- inputs
+  DevBuf own_X, own_y;
+  const void* dXv = nullptr;
+  const void* dyv = nullptr;
+  bool copied = false;
+  TRY(stage_input(c, features_hd, (size_t)N * F * 8, own_X, &dXv, &copied));
+  TRY(stage_input(c, labels_hd, (size_t)N * 8, own_y, &dyv, nullptr));
+  const double* dX = (const double*)dXv;
+  const double* dy = (const double*)dyv;
+  CU(cudaEventRecord(ev_in, st));
+
+  // ---- labels (Predictor.extractLabeledPoints / getNumClasses)
+  DevBuf d_labels, d_flags;
+  CU(d_labels.alloc((size_t)N));
+  CU(d_flags.alloc(8));
+  CU(cudaMemsetAsync(d_flags.p, 0, 8, st));
+  kern::labels_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(dy, N, P.num_classes, d_labels.as<uint8_t>(), d_flags.as<int>());
+  tm.kernel_launches++;
+  int flags[2] = {0, 0};
+  CU(cudaMemcpyAsync(flags, d_flags.p, 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (flags[0]) return fail(EMRF_ERR_ARG, "Classifier given dataset with invalid label: labels must be integers in [0, numClasses)");
+  if (P.num_classes == 0) {
+    P.num_classes = flags[1] + 1;
+    if (P.num_classes > 100)
+      return fail(EMRF_ERR_ARG, "Classifier inferred %d classes from label values, above the 100 allowed to be inferred; set num_classes",
+                  P.num_classes);
+  }
+  const int C = P.num_classes;
+  const int T = P.num_trees;
+
+  // ---- findSplits
+  DevBuf d_thr, d_ns;
+  std::vector<double> h_thr;
+  std::vector<int> h_ns;
+  TRY(run_find_splits(c, P, dX, N, F, part_off, n_parts, d_thr, d_ns, h_thr, h_ns));
+  CU(cudaEventRecord(ev_fs, st));
+  const int TS = P.max_bins;
+  std::vector<int> num_bins(F);
+  int B = 1;
+  for (int f = 0; f < F; f++) { num_bins[f] = h_ns[f] + 1; B = std::max(B, num_bins[f]); }
+  DevBuf d_num_bins;
+  CU(d_num_bins.alloc((size_t)F * 4));
+  CU(cudaMemcpyAsync(d_num_bins.p, num_bins.data(), (size_t)F * 4, cudaMemcpyHostToDevice, st));
+
+  // ---- TreePoint matrices
+  const int Fp = (int)align_up(F, 16);
+  const int64_t Np = (int64_t)align_up((size_t)N, 128);
+  DevBuf d_rm, d_cm;
+  CU(d_rm.alloc((size_t)Np * Fp));
+  CU(d_cm.alloc((size_t)F * Np));
+  TRY(run_bin(c, dX, N, F, d_thr.as<double>(), d_ns.as<int>(), TS, Fp, Np, d_rm.as<uint8_t>(), d_cm.as<uint8_t>()));
+  CU(cudaEventRecord(ev_bin, st));
+
+  // ---- BaggedPoint weights → per-tree entry lists
+  // tree-sharded multi-GPU: every rank schedules all trees, but only builds lists (and
+  // histograms) for trees t % world == rank.
+  DevBuf d_ent[2];
+  std::vector<uint64_t> tree_base(T + 1, 0), tree_total(T, 0);
+  {
+    DevBuf d_w;
+    CU(d_w.alloc((size_t)N * T));
+    int maxw = 0;
+    TRY(run_bag(c, P, N, part_off, n_parts, d_w.as<uint8_t>(), &maxw));
+    const int n_tiles = (int)((N + kern::kListTile - 1) / kern::kListTile);
+    DevBuf d_counts, d_totals, d_base;
+    CU(d_counts.alloc((size_t)n_tiles * T * 4));
+    CU(d_totals.alloc((size_t)T * 8));
+    CU(d_base.alloc((size_t)T * 8));
+    const int bt = std::min(256, (int)align_up(T, 32));
+    kern::list_count_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), N, T, d_counts.as<uint32_t>());
+    kern::list_scan_kernel<<<(T + 127) / 128, 128, 0, st>>>(d_counts.as<uint32_t>(), n_tiles, T, d_totals.as<uint64_t>());
+    tm.kernel_launches += 2;
+    CU(cudaMemcpyAsync(tree_total.data(), d_totals.p, (size_t)T * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    for (int t = 0; t < T; t++) tree_base[t + 1] = tree_base[t] + tree_total[t];
+    CU(d_ent[0].alloc((size_t)tree_base[T] * 8));
+    CU(d_ent[1].alloc((size_t)tree_base[T] * 8));
+    CU(cudaMemcpyAsync(d_base.p, tree_base.data(), (size_t)T * 8, cudaMemcpyHostToDevice, st));
+    kern::list_fill_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, d_counts.as<uint32_t>(),
+                                                   d_base.as<uint64_t>(), d_ent[0].as<uint64_t>());
+    tm.kernel_launches += 1;
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(ev_bag, st));
+    CU(cudaStreamSynchronize(st));  // d_w and the tile tables are released here
+  }
+
+  // ---- metadata (DecisionTreeMetadata.buildMetadata)
+  const int f_sub = hl::features_per_node(P, F);
+  if (f_sub < 1 || f_sub > F) return fail(EMRF_ERR_ARG, "featureSubsetStrategy selects %d of %d features", f_sub, F);
+  const bool subsampling = (f_sub != F);
+  // histogram chunking: features per CTA so that [k][B][C] uint32 fits in shared memory
+  const size_t smem_cap = std::min<size_t>(c->smem_optin, 227 * 1024);
+  const size_t per_feat = (size_t)B * C * 4;
+  size_t soft_cap = 100 * 1024;
+  int k_chunk = (int)((soft_cap - 4096) / per_feat);
+  if (k_chunk < 1) k_chunk = (int)((smem_cap - 4096) / per_feat);
+  if (k_chunk < 1) return fail(EMRF_ERR_LIMIT, "one feature histogram (%d bins x %d classes) exceeds shared memory", B, C);
+  k_chunk = std::min(k_chunk, f_sub);
+  const int n_chunks = (f_sub + k_chunk - 1) / k_chunk;
+  const size_t hist_smem = kern::hist_smem_bytes(k_chunk, B, C);
+  if (hist_smem > smem_cap) return fail(EMRF_ERR_LIMIT, "histogram tile needs %zu B of shared memory", hist_smem);
+  CU(cudaFuncSetAttribute(kern::hist_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
+  const size_t slot_words = (size_t)f_sub * B * C;
+
+  // ---- trees, stack, driver RNG (RandomForest.run)
+  std::vector<HTree> trees(T);
+  for (int t = 0; t < T; t++) {
+    trees[t].pool.reserve(256);
+    trees[t].pool.emplace_back();
+    HNode& r = trees[t].pool[0];
+    r.seg_start = tree_base[t];
+    r.seg_len = (uint32_t)tree_total[t];
+    r.buf = 0;
+  }
+  std::vector<std::pair<int, int>> stack;
+  stack.reserve(1024);
+  for (int t = 0; t < T; t++) stack.emplace_back(t, 0);
+  hl::JavaUtilRandom rng(P.seed);
+  const int64_t max_mem = (int64_t)P.max_memory_mb * 1024ll * 1024ll;
+  int64_t all_feat_bins = 0;
+  for (int f = 0; f < F; f++) all_feat_bins += num_bins[f];
+
+  emrf_forest* fo = new emrf_forest();
+  std::unique_ptr<emrf_forest> fo_guard(fo);
+  fo->num_trees = T; fo->num_classes = C; fo->num_features = F; fo->f_sub = f_sub;
+
+  std::vector<GroupEntry> group;
+  std::vector<int32_t> group_feat;
+  std::vector<int> trees_seen;
+  std::map<int, std::vector<int>> nodes_for_tree;
+  std::vector<int32_t> subset(f_sub);
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_ev, part_ev;
+  double host_ms = 0.0;
+
+  while (!stack.empty()) {
+    double t_host0 = now_ms();
+    // ---- selectNodesToSplit
+    group.clear(); group_feat.clear(); trees_seen.clear(); nodes_for_tree.clear();
+    int64_t mem = 0;
+    while (!stack.empty()) {
+      const auto top = stack.back();
+      int64_t total_bins;
+      if (subsampling) {
+        int len = 0;
+        hl::reservoir_features(F, f_sub, rng.next_long(), subset.data(), &len);
+        total_bins = 0;
+        for (int k = 0; k < f_sub; k++) total_bins += num_bins[subset[k]];
+      } else {
+        for (int k = 0; k < F; k++) subset[k] = k;
+        total_bins = all_feat_bins;
+      }
+      const int64_t node_mem = (int64_t)C * total_bins * 8;
+      if (mem + node_mem <= max_mem || mem == 0) {
+        stack.pop_back();
+        if (!nodes_for_tree.count(top.first)) trees_seen.push_back(top.first);
+        nodes_for_tree[top.first].push_back((int)group.size());
+        group.push_back({top.first, top.second, (int)group_feat.size()});
+        group_feat.insert(group_feat.end(), subset.begin(), subset.end());
+        mem += node_mem;
+      } else {
+        break;
+      }
+    }
+    const int n_nodes = (int)group.size();
+    fo->group_sizes.push_back(n_nodes);
+    for (auto& g : group) {
+      fo->trace.push_back(g.tree);
+      fo->trace.push_back(trees[g.tree].pool[g.pool].id);
+      for (int k = 0; k < f_sub; k++) fo->trace.push_back(group_feat[g.feat_at + k]);
+    }
+
+    // ---- which nodes this rank computes (tree-sharded multi-GPU: own trees only)
+    // tiles
+    uint64_t total_entries = 0;
+    for (auto& g : group)
+      if (g.tree % c->world == c->rank) total_entries += trees[g.tree].pool[g.pool].seg_len;
+    uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
+    tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
+
+    // staging layout: [GroupNode n][node_feat n*f_sub][tile_node tiles]
+    std::vector<kern::GroupNode> gn(n_nodes);
+    uint32_t n_tiles = 0;
+    int n_slots = 0;
+    for (int i = 0; i < n_nodes; i++) {
+      const HNode& hn = trees[group[i].tree].pool[group[i].pool];
+      kern::GroupNode& d = gn[i];
+      d.seg_start = hn.seg_start;
+      d.seg_len = hn.seg_len;
+      d.buf = hn.buf;
+      d.pad = 0;
+      d.tile_begin = n_tiles;
+      const bool mine = (group[i].tree % c->world == c->rank);
+      d.n_tiles = mine ? std::max<uint32_t>(1, (hn.seg_len + tile_len - 1) / tile_len) : 0;
+      d.slot = (d.n_tiles > 1) ? n_slots++ : -1;
+      n_tiles += d.n_tiles;
+    }
+    const size_t off_feat = align_up(sizeof(kern::GroupNode) * (size_t)n_nodes, 16);
+    const size_t off_tiles = align_up(off_feat + (size_t)n_nodes * f_sub * 4, 16);
+    const size_t group_bytes = off_tiles + (size_t)n_tiles * 4;
+    CU(c->h_group.ensure(group_bytes));
+    CU(c->d_group.ensure(group_bytes));
+    memcpy(c->h_group.p, gn.data(), sizeof(kern::GroupNode) * (size_t)n_nodes);
+    memcpy((char*)c->h_group.p + off_feat, group_feat.data(), (size_t)n_nodes * f_sub * 4);
+    {
+      uint32_t* tn = (uint32_t*)((char*)c->h_group.p + off_tiles);
+      for (int i = 0; i < n_nodes; i++)
+        for (uint32_t q = 0; q < gn[i].n_tiles; q++) tn[gn[i].tile_begin + q] = (uint32_t)i;
+    }
+    const size_t n_rec = (size_t)n_nodes * n_chunks;
+    const size_t off_left = align_up(sizeof(kern::ScanResult) * n_rec, 16);
+    const size_t off_total = off_left + n_rec * C * 4;
+    const size_t res_bytes = off_total + n_rec * C * 4;
+    CU(c->d_results.ensure(res_bytes));
+    CU(c->h_results.ensure(res_bytes));
+    CU(c->d_tickets.ensure(n_rec * 4));
+    CU(c->d_ghist.ensure((size_t)std::max(n_slots, 1) * slot_words * 4));
+    host_ms += now_ms() - t_host0;
+
+    CU(cudaMemcpyAsync(c->d_group.p, c->h_group.p, group_bytes, cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(c->d_tickets.p, 0, n_rec * 4, st));
+    if (c->world > 1) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
+    if (n_slots) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots * slot_words * 4, st));
+    kern::HistArgs A;
+    A.ent0 = d_ent[0].as<uint64_t>();
+    A.ent1 = d_ent[1].as<uint64_t>();
+    A.bins_rm = d_rm.as<uint8_t>();
+    A.nodes = (const kern::GroupNode*)c->d_group.p;
+    A.node_feat = (const int32_t*)((char*)c->d_group.p + off_feat);
+    A.tile_node = (const uint32_t*)((char*)c->d_group.p + off_tiles);
+    A.num_bins_all = d_num_bins.as<int32_t>();
+    A.ghist = c->d_ghist.as<uint32_t>();
+    A.tickets = c->d_tickets.as<uint32_t>();
+    A.results = (kern::ScanResult*)c->d_results.p;
+    A.left_counts = (uint32_t*)((char*)c->d_results.p + off_left);
+    A.total_counts = (uint32_t*)((char*)c->d_results.p + off_total);
+    A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
+    A.tile_len = tile_len;
+    A.impurity = P.impurity; A.min_instances = P.min_instances_per_node; A.hist_only = 0;
+    A.min_info_gain = P.min_info_gain;
+    cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
+    CU(cudaEventRecord(e0, st));
+    if (n_tiles) {
+      kern::hist_scan_kernel<<<dim3(n_tiles, n_chunks), kern::kHistThreads, hist_smem, st>>>(A);
+      tm.kernel_launches++;
+      tm.hist_launches++;
+    }
+    CU(cudaEventRecord(e1, st));
+    hist_ev.emplace_back(e0, e1);
+    CU(cudaGetLastError());
+    if (c->world > 1) TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
+    CU(cudaMemcpyAsync(c->h_results.p, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    tm.hist_units += (int64_t)total_entries;
+    tm.hist_alg_bytes += (int64_t)total_entries * (f_sub + 6);
+    for (auto& g : group)
+      if (g.tree % c->world == c->rank) tm.hist_alg_bytes += (int64_t)slot_words * 4;
+    tm.total_nodes_split += n_nodes;
+
+    // ---- driver side of findBestSplits: node updates in Scala map iteration order
+    t_host0 = now_ms();
+    const kern::ScanResult* res = (const kern::ScanResult*)c->h_results.p;
+    const uint32_t* res_left = (const uint32_t*)((char*)c->h_results.p + off_left);
+    const uint32_t* res_total = (const uint32_t*)((char*)c->h_results.p + off_total);
+    std::vector<kern::SplitNode> splits;
+    struct SplitRef { int tree, pool; };
+    std::vector<SplitRef> split_ref;
+    const std::vector<int> order = hl::group_tree_visit_order(trees_seen);
+    std::vector<uint32_t> rightc(C);
+    for (int t : order) {
+      for (int gi : nodes_for_tree[t]) {
+        const GroupEntry& g = group[gi];
+        HTree& tr = trees[t];
+        // combine feature chunks: first maximum in subset order
+        int best = -1;
+        for (int ch = 0; ch < n_chunks; ch++) {
+          const kern::ScanResult& r = res[(size_t)gi * n_chunks + ch];
+          if (r.k < 0) continue;
+          if (best < 0 || r.gain > res[(size_t)gi * n_chunks + best].gain) best = ch;
+        }
+        const size_t rec = (size_t)gi * n_chunks + (best < 0 ? 0 : best);
+        const uint32_t* totc = res_total + rec * C;
+        const uint32_t* leftc = res_left + rec * C;
+        const int id = tr.pool[g.pool].id;
+        const int level = 31 - __builtin_clz((unsigned)id);
+        // node stats: parent calculator = class totals; impurity recomputed on the host
+        if (!tr.pool[g.pool].has_stats) {
+          tr.pool[g.pool].counts_at = tr.counts.size();
+          tr.counts.insert(tr.counts.end(), totc, totc + C);
+          tr.pool[g.pool].has_stats = true;
+        }
+        const double pimp = hl::impurity_of(P.impurity, totc, C);
+        double gain = kern::kInvalidGain, limp = 0.0, rimp = 0.0;
+        bool valid = false;
+        if (best >= 0 && res[rec].valid) {
+          uint64_t lc = 0, rc = 0;
+          for (int cc = 0; cc < C; cc++) { rightc[cc] = totc[cc] - leftc[cc]; lc += leftc[cc]; rc += rightc[cc]; }
+          limp = hl::impurity_of(P.impurity, leftc, C);
+          rimp = hl::impurity_of(P.impurity, rightc.data(), C);
+          const double tc = (double)(lc + rc);
+          const double lw = (double)lc / tc, rw = (double)rc / tc;
+          gain = pimp - lw * limp - rw * rimp;
+          valid = true;
+          if (gain != res[rec].gain) tm.gain_mismatches++;
+        }
+        const bool is_leaf = (gain <= 0) || (level == P.max_depth);
+        {
+          HNode& n = tr.pool[g.pool];
+          n.is_leaf = is_leaf; n.gain = gain; n.impurity = pimp; n.valid = valid;
+        }
+        if (!is_leaf) {
+          const int feat = group_feat[g.feat_at + res[rec].k];
+          const int sbin = res[rec].split;
+          const bool child_leaf = (level + 1) == P.max_depth;
+          const bool l_leaf = child_leaf || (limp == 0.0);
+          const bool r_leaf = child_leaf || (rimp == 0.0);
+          const int li = (int)tr.pool.size();
+          HNode l, r;
+          l.id = 2 * id; l.is_leaf = l_leaf; l.has_stats = true; l.impurity = limp;
+          l.counts_at = tr.counts.size();
+          tr.counts.insert(tr.counts.end(), leftc, leftc + C);
+          r.id = 2 * id + 1; r.is_leaf = r_leaf; r.has_stats = true; r.impurity = rimp;
+          r.counts_at = tr.counts.size();
+          tr.counts.insert(tr.counts.end(), rightc.begin(), rightc.end());
+          tr.pool.push_back(l);
+          tr.pool.push_back(r);
+          HNode& n = tr.pool[g.pool];
+          n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
+          n.left = li; n.right = li + 1;
+          if (!l_leaf) stack.emplace_back(t, li);
+          if (!r_leaf) stack.emplace_back(t, li + 1);
+          if ((!l_leaf || !r_leaf) && (t % c->world == c->rank)) {
+            kern::SplitNode s;
+            s.seg_start = n.seg_start; s.seg_len = n.seg_len; s.buf = n.buf;
+            s.feature = feat; s.split_bin = sbin; s.tile_begin = 0; s.n_tiles = 0;
+            splits.push_back(s);
+            split_ref.push_back({t, g.pool});
+          }
+        }
+      }
+    }
+    host_ms += now_ms() - t_host0;
+
+    // ---- K4: partition the split nodes' segments, learn the children's segment sizes
+    if (!splits.empty()) {
+      t_host0 = now_ms();
+      const int ns = (int)splits.size();
+      uint32_t ptiles = 0;
+      for (auto& s : splits) {
+        s.tile_begin = ptiles;
+        s.n_tiles = (s.seg_len + kern::kPartTile - 1) / kern::kPartTile;
+        ptiles += s.n_tiles;
+      }
+      const size_t off_ptn = align_up(sizeof(kern::SplitNode) * (size_t)ns, 16);
+      const size_t split_bytes = off_ptn + (size_t)ptiles * 4;
+      CU(c->h_split.ensure(split_bytes));
+      CU(c->d_split.ensure(split_bytes));
+      memcpy(c->h_split.p, splits.data(), sizeof(kern::SplitNode) * (size_t)ns);
+      uint32_t* tn = (uint32_t*)((char*)c->h_split.p + off_ptn);
+      for (int i = 0; i < ns; i++)
+        for (uint32_t q = 0; q < splits[i].n_tiles; q++) tn[splits[i].tile_begin + q] = (uint32_t)i;
+      const size_t off_nleft = align_up((size_t)ptiles * 4, 16);
+      CU(c->d_part.ensure(off_nleft + (size_t)ns * 8));
+      CU(c->h_part.ensure((size_t)ns * 8));
+      host_ms += now_ms() - t_host0;
+      CU(cudaMemcpyAsync(c->d_split.p, c->h_split.p, split_bytes, cudaMemcpyHostToDevice, st));
+      const kern::SplitNode* dsn = (const kern::SplitNode*)c->d_split.p;
+      const uint32_t* dtn = (const uint32_t*)((char*)c->d_split.p + off_ptn);
+      uint32_t* d_tile_left = (uint32_t*)c->d_part.p;
+      uint64_t* d_nleft = (uint64_t*)((char*)c->d_part.p + off_nleft);
+      cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
+      CU(cudaEventRecord(p0, st));
+      if (ptiles) {
+        kern::part_count_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0].as<uint64_t>(), d_ent[1].as<uint64_t>(),
+                                                                      d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left);
+        kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft);
+        kern::part_scatter_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0].as<uint64_t>(), d_ent[1].as<uint64_t>(),
+                                                                        d_ent[0].as<uint64_t>(), d_ent[1].as<uint64_t>(),
+                                                                        d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft);
+        tm.kernel_launches += 3;
+      } else {
+        CU(cudaMemsetAsync(d_nleft, 0, (size_t)ns * 8, st));
+      }
+      CU(cudaEventRecord(p1, st));
+      part_ev.emplace_back(p0, p1);
+      CU(cudaGetLastError());
+      CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      t_host0 = now_ms();
+      const uint64_t* nl = (const uint64_t*)c->h_part.p;
+      for (int i = 0; i < ns; i++) {
+        HTree& tr = trees[split_ref[i].tree];
+        const HNode& n = tr.pool[split_ref[i].pool];
+        HNode& l = tr.pool[n.left];
+        HNode& r = tr.pool[n.right];
+        l.seg_start = n.seg_start; l.seg_len = (uint32_t)nl[i]; l.buf = n.buf ^ 1u;
+        r.seg_start = n.seg_start + nl[i]; r.seg_len = n.seg_len - (uint32_t)nl[i]; r.buf = n.buf ^ 1u;
+      }
+      host_ms += now_ms() - t_host0;
+    }
+  }
+
+  // ---- topNodes.map(_.toNode(prune = true))
+  double t_host0 = now_ms();
+  fo->tree_off.push_back(0);
+  for (int t = 0; t < T; t++) {
+    export_node(trees[t], 0, C, *fo);
+    fo->tree_off.push_back((int64_t)fo->nodes.size());
+  }
+  host_ms += now_ms() - t_host0;
+  CU(cudaEventRecord(ev_end, st));
+  CU(cudaStreamSynchronize(st));
+
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, ev_start, ev_end)); tm.total_ms = ms;
+  CU(cudaEventElapsedTime(&ms, ev_start, ev_in)); tm.h2d_ms = copied ? ms : 0.0;
+  CU(cudaEventElapsedTime(&ms, ev_in, ev_fs)); tm.find_splits_ms = ms;
+  CU(cudaEventElapsedTime(&ms, ev_fs, ev_bin)); tm.bin_ms = ms;
+  CU(cudaEventElapsedTime(&ms, ev_bin, ev_bag)); tm.bag_ms = ms;
+  for (auto& pr : hist_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.hist_kernel_ms += ms; }
+  for (auto& pr : part_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.partition_ms += ms; }
+  tm.find_best_splits_ms = tm.hist_kernel_ms;
+  tm.host_scheduler_ms = host_ms;
+  tm.num_groups = (int64_t)fo->group_sizes.size();
+  *out = fo_guard.release();
+  return EMRF_OK;
+}
+
+extern "C" int emrf_fit(emrf_ctx_t* c, const emrf_params_t* params, const double* features_hd, const double* labels_hd,
+                        int64_t n_rows, int32_t n_features, const int64_t* partition_offsets, int32_t n_partitions,
+                        emrf_forest_t** out) {
+  if (!c || !out || !features_hd || !labels_hd) return fail(EMRF_ERR_ARG, "NULL argument");
+  TRY(check_params(params));
+  if (n_rows < 1 || n_features < 1) return fail(EMRF_ERR_ARG, "empty dataset");
+  TRY(check_partitions(n_rows, partition_offsets, n_partitions));
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  return fit_impl(c, *params, features_hd, labels_hd, n_rows, n_features, partition_offsets, n_partitions, out);
+}
+
+// ---------------------------------------------------------------------------------------------
+// forest accessors
+// ---------------------------------------------------------------------------------------------
+extern "C" void emrf_forest_free(emrf_forest_t* f) { delete f; }
+extern "C" int emrf_forest_info(const emrf_forest_t* f, int32_t* T, int32_t* C, int32_t* F, int64_t* total_nodes) {
+  if (!f) return fail(EMRF_ERR_ARG, "forest is NULL");
+  if (T) *T = f->num_trees;
+  if (C) *C = f->num_classes;
+  if (F) *F = f->num_features;
+  if (total_nodes) *total_nodes = (int64_t)f->nodes.size();
+  return EMRF_OK;
+}
+extern "C" int emrf_forest_export(const emrf_forest_t* f, int64_t* tree_off, int32_t* node_id, int32_t* left, int32_t* right,
+                                  int32_t* feature, double* threshold, double* gain, double* impurity, double* prediction,
+                                  double* stats) {
+  if (!f) return fail(EMRF_ERR_ARG, "forest is NULL");
+  for (size_t t = 0; t < f->tree_off.size(); t++) tree_off[t] = f->tree_off[t];
+  for (size_t i = 0; i < f->nodes.size(); i++) {
+    const FlatNode& n = f->nodes[i];
+    node_id[i] = n.id; left[i] = n.left; right[i] = n.right; feature[i] = n.feature;
+    threshold[i] = n.threshold; gain[i] = n.gain; impurity[i] = n.impurity; prediction[i] = n.prediction;
+  }
+  memcpy(stats, f->stats.data(), f->stats.size() * 8);
+  return EMRF_OK;
+}
+extern "C" int emrf_forest_import(emrf_ctx_t* c, int32_t T, int32_t C, int32_t F, const int64_t* tree_off, const int32_t* node_id,
+                                  const int32_t* left, const int32_t* right, const int32_t* feature, const double* threshold,
+                                  const double* gain, const double* impurity, const double* prediction, const double* stats,
+                                  emrf_forest_t** out) {
+  (void)c;
+  if (!out || !tree_off || T < 1 || C < 1 || C > 256 || F < 1) return fail(EMRF_ERR_ARG, "bad forest description");
+  emrf_forest* f = new emrf_forest();
+  f->num_trees = T; f->num_classes = C; f->num_features = F;
+  f->tree_off.assign(tree_off, tree_off + T + 1);
+  const int64_t n = tree_off[T];
+  f->nodes.resize(n);
+  for (int64_t i = 0; i < n; i++) {
+    FlatNode& q = f->nodes[i];
+    q.id = node_id ? node_id[i] : 0; q.left = left[i]; q.right = right[i]; q.feature = feature[i];
+    q.threshold = threshold[i]; q.gain = gain ? gain[i] : 0.0; q.impurity = impurity ? impurity[i] : 0.0;
+    q.prediction = prediction ? prediction[i] : 0.0;
+    if (q.left >= 0 && (q.feature < 0 || q.feature >= F)) { delete f; return fail(EMRF_ERR_ARG, "node %lld: bad feature", (long long)i); }
+  }
+  f->stats.assign(stats, stats + n * C);
+  *out = f;
+  return EMRF_OK;
+}
+extern "C" int emrf_forest_trace_info(const emrf_forest_t* f, int32_t* num_groups, int64_t* trace_len, int32_t* f_sub) {
+  if (!f) return fail(EMRF_ERR_ARG, "forest is NULL");
+  if (num_groups) *num_groups = (int32_t)f->group_sizes.size();
+  if (trace_len) *trace_len = (int64_t)f->trace.size();
+  if (f_sub) *f_sub = f->f_sub;
+  return EMRF_OK;
+}
+extern "C" int emrf_forest_trace(const emrf_forest_t* f, int32_t* group_sizes, int32_t* trace) {
+  if (!f) return fail(EMRF_ERR_ARG, "forest is NULL");
+  if (group_sizes) memcpy(group_sizes, f->group_sizes.data(), f->group_sizes.size() * 4);
+  if (trace) memcpy(trace, f->trace.data(), f->trace.size() * 4);
+  return EMRF_OK;
+}
+// TreeEnsembleModel.featureImportances (ml/tree/treeModels.scala): per tree, sum over internal
+// nodes of gain * count; normalise per tree; sum over trees; normalise.
+extern "C" int emrf_forest_feature_importances(const emrf_forest_t* f, double* out) {
+  if (!f || !out) return fail(EMRF_ERR_ARG, "NULL argument");
+  const int F = f->num_features, C = f->num_classes;
+  std::vector<double> total(F, 0.0), one(F);
+  for (int t = 0; t < f->num_trees; t++) {
+    std::fill(one.begin(), one.end(), 0.0);
+    for (int64_t i = f->tree_off[t]; i < f->tree_off[t + 1]; i++) {
+      const FlatNode& n = f->nodes[i];
+      if (n.left < 0) continue;
+      double cnt = 0.0;
+      for (int c = 0; c < C; c++) cnt += f->stats[i * C + c];
+      one[n.feature] += n.gain * cnt;
+    }
+    double s = 0.0;
+    for (int j = 0; j < F; j++) s += one[j];
+    if (s != 0.0) for (int j = 0; j < F; j++) total[j] += one[j] / s;
+  }
+  double s = 0.0;
+  for (int j = 0; j < F; j++) s += total[j];
+  for (int j = 0; j < F; j++) out[j] = (s != 0.0) ? total[j] / s : total[j];
+  return EMRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// emrf_predict
+// ---------------------------------------------------------------------------------------------
+static int forest_to_device(emrf_ctx* c, emrf_forest* f) {
+  std::lock_guard<std::mutex> lk(f->dev_mu);
+  if (f->dev_device == c->device) return EMRF_OK;
+  const int C = f->num_classes;
+  const int64_t n = (int64_t)f->nodes.size();
+  std::vector<kern::DevNode> dn(n);
+  std::vector<int64_t> roots(f->num_trees);
+  std::vector<double> leaf_prob;
+  int64_t n_leaves = 0;
+  for (int t = 0; t < f->num_trees; t++) {
+    const int64_t base = f->tree_off[t];
+    roots[t] = base;
+    for (int64_t i = base; i < f->tree_off[t + 1]; i++) {
+      const FlatNode& q = f->nodes[i];
+      kern::DevNode& d = dn[i];
+      d.pad = 0;
+      if (q.left >= 0) {
+        d.feature = q.feature; d.threshold = q.threshold;
+        d.left = (int32_t)(base + q.left); d.right = (int32_t)(base + q.right);
+      } else {
+        d.feature = -1; d.threshold = 0.0; d.left = (int32_t)n_leaves;
+        double total = 0.0;
+        for (int cc = 0; cc < C; cc++) total += f->stats[i * C + cc];
+        d.right = (total != 0.0) ? 1 : 0;
+        leaf_prob.resize((size_t)(n_leaves + 1) * C);
+        for (int cc = 0; cc < C; cc++)
+          leaf_prob[(size_t)n_leaves * C + cc] = (total != 0.0) ? f->stats[i * C + cc] / total : 0.0;
+        n_leaves++;
+      }
+    }
+  }
+  if (n >= (1ll << 31)) return fail(EMRF_ERR_LIMIT, "forest too large");
+  CU(f->d_nodes.alloc((size_t)n * sizeof(kern::DevNode)));
+  CU(f->d_roots.alloc((size_t)f->num_trees * 8));
+  CU(f->d_leaf_prob.alloc(leaf_prob.size() * 8));
+  CU(cudaMemcpy(f->d_nodes.p, dn.data(), (size_t)n * sizeof(kern::DevNode), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(f->d_roots.p, roots.data(), (size_t)f->num_trees * 8, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(f->d_leaf_prob.p, leaf_prob.data(), leaf_prob.size() * 8, cudaMemcpyHostToDevice));
+  f->dev_device = c->device;
+  return EMRF_OK;
+}
+
+extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* features_hd, int64_t N, double* raw_hd,
+                            double* prob_hd, double* pred_hd) {
+  if (!c || !f_in || !features_hd) return fail(EMRF_ERR_ARG, "NULL argument");
+  if (N < 0) return fail(EMRF_ERR_ARG, "negative row count");
+  if (N == 0) return EMRF_OK;
+  emrf_forest* f = const_cast<emrf_forest*>(f_in);
+  CU(cudaSetDevice(c->device));
+  TRY(forest_to_device(c, f));
+  const int C = f->num_classes, F = f->num_features;
+  cudaStream_t st;
+  CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamDestroy(s); } } sg{st};
+  const bool x_dev = is_device_ptr(features_hd);
+  const bool raw_dev = raw_hd && is_device_ptr(raw_hd), prob_dev = prob_hd && is_device_ptr(prob_hd),
+             pred_dev = pred_hd && is_device_ptr(pred_hd);
+  // chunk so that staging buffers stay modest
+  const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(N, (int64_t)(512ll << 20) / ((int64_t)F * 8)));
+  DevBuf dX, dRaw, dProb, dPred;
+  if (!x_dev) CU(dX.alloc((size_t)chunk * F * 8));
+  if (raw_hd && !raw_dev) CU(dRaw.alloc((size_t)chunk * C * 8));
+  if (prob_hd && !prob_dev) CU(dProb.alloc((size_t)chunk * C * 8));
+  if (pred_hd && !pred_dev) CU(dPred.alloc((size_t)chunk * 8));
+  for (int64_t r0 = 0; r0 < N; r0 += chunk) {
+    const int64_t n = std::min(chunk, N - r0);
+    const double* x = features_hd + r0 * F;
+    if (!x_dev) {
+      CU(cudaMemcpyAsync(dX.p, x, (size_t)n * F * 8, cudaMemcpyHostToDevice, st));
+      x = dX.as<double>();
+    }
+    double* raw = raw_hd ? (raw_dev ? raw_hd + r0 * C : dRaw.as<double>()) : nullptr;
+    double* prob = prob_hd ? (prob_dev ? prob_hd + r0 * C : dProb.as<double>()) : nullptr;
+    double* pred = pred_hd ? (pred_dev ? pred_hd + r0 : dPred.as<double>()) : nullptr;
+    const int64_t threads = n * 32;
+    kern::predict_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(x, n, F, f->d_nodes.as<kern::DevNode>(),
+                                                                         f->d_roots.as<int64_t>(), f->num_trees,
+                                                                         f->d_leaf_prob.as<double>(), C, raw, prob, pred);
+    CU(cudaGetLastError());
+    if (raw_hd && !raw_dev) CU(cudaMemcpyAsync(raw_hd + r0 * C, raw, (size_t)n * C * 8, cudaMemcpyDeviceToHost, st));
+    if (prob_hd && !prob_dev) CU(cudaMemcpyAsync(prob_hd + r0 * C, prob, (size_t)n * C * 8, cudaMemcpyDeviceToHost, st));
+    if (pred_hd && !pred_dev) CU(cudaMemcpyAsync(pred_hd + r0, pred, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  return EMRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// stage-level entry points
+// ---------------------------------------------------------------------------------------------
+extern "C" int emrf_find_splits(emrf_ctx_t* c, const emrf_params_t* params, const double* features_hd, int64_t N, int32_t F,
+                                const int64_t* part_off, int32_t n_parts, double* thresholds_out, int32_t* n_splits_out) {
+  if (!c || !features_hd || !thresholds_out || !n_splits_out) return fail(EMRF_ERR_ARG, "NULL argument");
+  TRY(check_params(params));
+  TRY(check_partitions(N, part_off, n_parts));
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  DevBuf own_X, d_thr, d_ns;
+  const void* dX = nullptr;
+  TRY(stage_input(c, features_hd, (size_t)N * F * 8, own_X, &dX, nullptr));
+  std::vector<double> h_thr;
+  std::vector<int> h_ns;
+  TRY(run_find_splits(c, *params, (const double*)dX, N, F, part_off, n_parts, d_thr, d_ns, h_thr, h_ns));
+  memcpy(thresholds_out, h_thr.data(), h_thr.size() * 8);
+  memcpy(n_splits_out, h_ns.data(), h_ns.size() * 4);
+  return EMRF_OK;
+}
+extern "C" int64_t emrf_find_splits_sample_rows(const emrf_params_t* params, int64_t N, const int64_t* part_off, int32_t n_parts,
+                                                int64_t* rows_out, int64_t cap) {
+  if (check_params(params) != EMRF_OK || check_partitions(N, part_off, n_parts) != EMRF_OK) return -1;
+  std::vector<int64_t> rows;
+  if (!hl::find_splits_rows(*params, N, part_off, n_parts, &rows)) {
+    for (int64_t i = 0; i < N && i < cap; i++) rows_out[i] = i;
+    return N;
+  }
+  for (size_t i = 0; i < rows.size() && (int64_t)i < cap; i++) rows_out[i] = rows[i];
+  return (int64_t)rows.size();
+}
+extern "C" int emrf_bin(emrf_ctx_t* c, const double* features_hd, int64_t N, int32_t F, const double* thresholds,
+                        const int32_t* n_splits, int32_t thr_stride, uint8_t* bins_cm_out, uint8_t* bins_rm_out) {
+  if (!c || !features_hd || !thresholds || !n_splits) return fail(EMRF_ERR_ARG, "NULL argument");
+  if (N < 1 || F < 1 || thr_stride < 1) return fail(EMRF_ERR_ARG, "bad shape");
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  DevBuf own_X, d_thr, d_ns, d_rm, d_cm;
+  const void* dX = nullptr;
+  TRY(stage_input(c, features_hd, (size_t)N * F * 8, own_X, &dX, nullptr));
+  CU(d_thr.alloc((size_t)F * thr_stride * 8));
+  CU(d_ns.alloc((size_t)F * 4));
+  CU(cudaMemcpyAsync(d_thr.p, thresholds, (size_t)F * thr_stride * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(d_ns.p, n_splits, (size_t)F * 4, cudaMemcpyHostToDevice, c->stream));
+  const int Fp = (int)align_up(F, 16);
+  const int64_t Np = (int64_t)align_up((size_t)N, 128);
+  CU(d_rm.alloc((size_t)Np * Fp));
+  CU(d_cm.alloc((size_t)F * Np));
+  TRY(run_bin(c, (const double*)dX, N, F, d_thr.as<double>(), d_ns.as<int>(), thr_stride, Fp, Np, d_rm.as<uint8_t>(),
+              d_cm.as<uint8_t>()));
+  if (bins_rm_out)
+    CU(cudaMemcpy2DAsync(bins_rm_out, (size_t)F, d_rm.p, (size_t)Fp, (size_t)F, (size_t)N, cudaMemcpyDeviceToHost, c->stream));
+  if (bins_cm_out)
+    CU(cudaMemcpy2DAsync(bins_cm_out, (size_t)N, d_cm.p, (size_t)Np, (size_t)N, (size_t)F, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return EMRF_OK;
+}
+extern "C" int emrf_bag_weights(emrf_ctx_t* c, const emrf_params_t* params, int64_t N, const int64_t* part_off, int32_t n_parts,
+                                uint8_t* weights_out, int32_t* max_weight_out) {
+  if (!c || !weights_out) return fail(EMRF_ERR_ARG, "NULL argument");
+  TRY(check_params(params));
+  TRY(check_partitions(N, part_off, n_parts));
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  DevBuf d_w;
+  CU(d_w.alloc((size_t)N * params->num_trees));
+  int mw = 0;
+  TRY(run_bag(c, *params, N, part_off, n_parts, d_w.as<uint8_t>(), &mw));
+  if (max_weight_out) *max_weight_out = mw;
+  CU(cudaMemcpyAsync(weights_out, d_w.p, (size_t)N * params->num_trees, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return EMRF_OK;
+}
+
+// shared set-up of the histogram chunking for the stage entry points
+static int hist_geometry(emrf_ctx* c, int f_sub, int B, int C, int* k_chunk_out, int* n_chunks_out, size_t* smem_out) {
+  const size_t smem_cap = std::min<size_t>(c->smem_optin, 227 * 1024);
+  const size_t per_feat = (size_t)B * C * 4;
+  int k_chunk = (int)((100 * 1024 - 4096) / per_feat);
+  if (k_chunk < 1) k_chunk = (int)((smem_cap - 4096) / per_feat);
+  if (k_chunk < 1) return fail(EMRF_ERR_LIMIT, "one feature histogram (%d bins x %d classes) exceeds shared memory", B, C);
+  k_chunk = std::min(k_chunk, f_sub);
+  *k_chunk_out = k_chunk;
+  *n_chunks_out = (f_sub + k_chunk - 1) / k_chunk;
+  *smem_out = kern::hist_smem_bytes(k_chunk, B, C);
+  if (*smem_out > smem_cap) return fail(EMRF_ERR_LIMIT, "histogram tile needs %zu B of shared memory", *smem_out);
+  return EMRF_OK;
+}
+
+extern "C" int emrf_histogram(emrf_ctx_t* c, const uint8_t* bins_rm, int64_t N, int32_t F, const uint64_t* entries,
+                              const int64_t* node_seg_off, int32_t n_nodes, const int32_t* subsets, int32_t f_sub,
+                              const int32_t* num_bins_all, int32_t C, uint32_t* hist_out) {
+  if (!c || !bins_rm || !entries || !node_seg_off || !subsets || !num_bins_all || !hist_out) return fail(EMRF_ERR_ARG, "NULL argument");
+  if (n_nodes < 1 || f_sub < 1 || C < 1 || C > 256 || F < 1) return fail(EMRF_ERR_ARG, "bad shape");
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  int B = 1;
+  for (int f = 0; f < F; f++) B = std::max(B, num_bins_all[f]);
+  int k_chunk, n_chunks;
+  size_t smem;
+  TRY(hist_geometry(c, f_sub, B, C, &k_chunk, &n_chunks, &smem));
+  CU(cudaFuncSetAttribute(kern::hist_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int Fp = (int)align_up(F, 16);
+  const int64_t n_ent = node_seg_off[n_nodes];
+  DevBuf d_rm, d_ent, d_nodes, d_feat, d_tiles, d_nb, d_hist;
+  CU(d_rm.alloc((size_t)N * Fp));
+  CU(cudaMemsetAsync(d_rm.p, 0, (size_t)N * Fp, st));
+  CU(cudaMemcpy2DAsync(d_rm.p, (size_t)Fp, bins_rm, (size_t)F, (size_t)F, (size_t)N, cudaMemcpyHostToDevice, st));
+  CU(d_ent.alloc((size_t)n_ent * 8));
+  CU(cudaMemcpyAsync(d_ent.p, entries, (size_t)n_ent * 8, cudaMemcpyHostToDevice, st));
+  const uint32_t tile_len = 8192;
+  std::vector<kern::GroupNode> gn(n_nodes);
+  std::vector<uint32_t> tn;
+  for (int i = 0; i < n_nodes; i++) {
+    kern::GroupNode& d = gn[i];
+    d.seg_start = (uint64_t)node_seg_off[i];
+    d.seg_len = (uint32_t)(node_seg_off[i + 1] - node_seg_off[i]);
+    d.buf = 0; d.pad = 0; d.slot = i;
+    d.tile_begin = (uint32_t)tn.size();
+    d.n_tiles = std::max<uint32_t>(1, (d.seg_len + tile_len - 1) / tile_len);
+    for (uint32_t q = 0; q < d.n_tiles; q++) tn.push_back((uint32_t)i);
+  }
+  const size_t slot_words = (size_t)f_sub * B * C;
+  CU(d_nodes.alloc(sizeof(kern::GroupNode) * (size_t)n_nodes));
+  CU(d_feat.alloc((size_t)n_nodes * f_sub * 4));
+  CU(d_tiles.alloc(tn.size() * 4));
+  CU(d_nb.alloc((size_t)F * 4));
+  CU(d_hist.alloc((size_t)n_nodes * slot_words * 4));
+  CU(cudaMemcpyAsync(d_nodes.p, gn.data(), sizeof(kern::GroupNode) * (size_t)n_nodes, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_feat.p, subsets, (size_t)n_nodes * f_sub * 4, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_tiles.p, tn.data(), tn.size() * 4, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_nb.p, num_bins_all, (size_t)F * 4, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(d_hist.p, 0, (size_t)n_nodes * slot_words * 4, st));
+  kern::HistArgs A;
+  memset(&A, 0, sizeof(A));
+  A.ent0 = d_ent.as<uint64_t>(); A.ent1 = d_ent.as<uint64_t>();
+  A.bins_rm = d_rm.as<uint8_t>();
+  A.nodes = d_nodes.as<kern::GroupNode>();
+  A.tile_node = d_tiles.as<uint32_t>();
+  A.node_feat = d_feat.as<int32_t>();
+  A.num_bins_all = d_nb.as<int32_t>();
+  A.ghist = d_hist.as<uint32_t>();
+  A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
+  A.tile_len = tile_len; A.hist_only = 1;
+  kern::hist_scan_kernel<<<dim3((unsigned)tn.size(), n_chunks), kern::kHistThreads, smem, st>>>(A);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(hist_out, d_hist.p, (size_t)n_nodes * slot_words * 4, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return EMRF_OK;
+}
+
+extern "C" int emrf_best_splits(emrf_ctx_t* c, const uint32_t* hist, int32_t n_nodes, const int32_t* subsets, int32_t f_sub,
+                                const int32_t* num_bins_all, int32_t F, int32_t C, int32_t impurity, int32_t min_instances,
+                                double min_info_gain, int32_t* k_out, int32_t* split_out, double* gain_out, int32_t* valid_out,
+                                uint32_t* left_out, uint32_t* total_out) {
+  if (!c || !hist || !subsets || !num_bins_all) return fail(EMRF_ERR_ARG, "NULL argument");
+  if (n_nodes < 1 || f_sub < 1 || C < 1 || C > 256 || F < 1) return fail(EMRF_ERR_ARG, "bad shape");
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  int B = 1;
+  for (int f = 0; f < F; f++) B = std::max(B, num_bins_all[f]);
+  int k_chunk, n_chunks;
+  size_t smem;
+  TRY(hist_geometry(c, f_sub, B, C, &k_chunk, &n_chunks, &smem));
+  CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const size_t slot_words = (size_t)f_sub * B * C;
+  const size_t n_rec = (size_t)n_nodes * n_chunks;
+  DevBuf d_hist, d_feat, d_nb, d_res, d_left, d_tot;
+  CU(d_hist.alloc((size_t)n_nodes * slot_words * 4));
+  CU(d_feat.alloc((size_t)n_nodes * f_sub * 4));
+  CU(d_nb.alloc((size_t)F * 4));
+  CU(d_res.alloc(n_rec * sizeof(kern::ScanResult)));
+  CU(d_left.alloc(n_rec * C * 4));
+  CU(d_tot.alloc(n_rec * C * 4));
+  CU(cudaMemcpyAsync(d_hist.p, hist, (size_t)n_nodes * slot_words * 4, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_feat.p, subsets, (size_t)n_nodes * f_sub * 4, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_nb.p, num_bins_all, (size_t)F * 4, cudaMemcpyHostToDevice, st));
+  kern::scan_kernel<<<dim3(n_nodes, n_chunks), kern::kHistThreads, smem, st>>>(
+      d_hist.as<uint32_t>(), d_feat.as<int32_t>(), d_nb.as<int32_t>(), f_sub, B, C, k_chunk, n_chunks, impurity, min_instances,
+      min_info_gain, d_res.as<kern::ScanResult>(), d_left.as<uint32_t>(), d_tot.as<uint32_t>());
+  CU(cudaGetLastError());
+  std::vector<kern::ScanResult> res(n_rec);
+  std::vector<uint32_t> l(n_rec * C), t(n_rec * C);
+  CU(cudaMemcpyAsync(res.data(), d_res.p, n_rec * sizeof(kern::ScanResult), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(l.data(), d_left.p, n_rec * C * 4, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(t.data(), d_tot.p, n_rec * C * 4, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (int g = 0; g < n_nodes; g++) {
+    int best = -1;
+    for (int ch = 0; ch < n_chunks; ch++) {
+      const kern::ScanResult& r = res[(size_t)g * n_chunks + ch];
+      if (r.k < 0) continue;
+      if (best < 0 || r.gain > res[(size_t)g * n_chunks + best].gain) best = ch;
+    }
+    const size_t rec = (size_t)g * n_chunks + (best < 0 ? 0 : best);
+    if (k_out) k_out[g] = best < 0 ? -1 : res[rec].k;
+    if (split_out) split_out[g] = best < 0 ? 0 : res[rec].split;
+    if (gain_out) gain_out[g] = best < 0 ? kern::kInvalidGain : res[rec].gain;
+    if (valid_out) valid_out[g] = best < 0 ? 0 : res[rec].valid;
+    if (left_out) memcpy(left_out + (size_t)g * C, &l[rec * C], (size_t)C * 4);
+    if (total_out) memcpy(total_out + (size_t)g * C, &t[rec * C], (size_t)C * 4);
+  }
+  return EMRF_OK;
+}
+
+extern "C" int emrf_update_partition(emrf_ctx_t* c, const uint8_t* bins_cm, int64_t N, int32_t F, const uint64_t* entries,
+                                     const int64_t* node_seg_off, int32_t n_nodes, const int32_t* split_feature,
+                                     const int32_t* split_bin, uint64_t* entries_out, int64_t* n_left_out) {
+  if (!c || !bins_cm || !entries || !node_seg_off || !split_feature || !split_bin || !entries_out || !n_left_out)
+    return fail(EMRF_ERR_ARG, "NULL argument");
+  if (n_nodes < 1 || F < 1 || N < 1) return fail(EMRF_ERR_ARG, "bad shape");
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int64_t Np = (int64_t)align_up((size_t)N, 128);
+  const int64_t n_ent = node_seg_off[n_nodes];
+  DevBuf d_cm, d_in, d_out, d_nodes, d_tiles, d_tl, d_nl;
+  CU(d_cm.alloc((size_t)F * Np));
+  CU(cudaMemcpy2DAsync(d_cm.p, (size_t)Np, bins_cm, (size_t)N, (size_t)N, (size_t)F, cudaMemcpyHostToDevice, st));
+  CU(d_in.alloc((size_t)n_ent * 8));
+  CU(d_out.alloc((size_t)n_ent * 8));
+  CU(cudaMemcpyAsync(d_in.p, entries, (size_t)n_ent * 8, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(d_out.p, 0, (size_t)n_ent * 8, st));
+  std::vector<kern::SplitNode> sn(n_nodes);
+  std::vector<uint32_t> tn;
+  for (int i = 0; i < n_nodes; i++) {
+    kern::SplitNode& s = sn[i];
+    s.seg_start = (uint64_t)node_seg_off[i];
+    s.seg_len = (uint32_t)(node_seg_off[i + 1] - node_seg_off[i]);
+    s.buf = 0; s.feature = split_feature[i]; s.split_bin = split_bin[i];
+    if (s.feature < 0 || s.feature >= F) return fail(EMRF_ERR_ARG, "split feature out of range");
+    s.tile_begin = (uint32_t)tn.size();
+    s.n_tiles = (s.seg_len + kern::kPartTile - 1) / kern::kPartTile;
+    for (uint32_t q = 0; q < s.n_tiles; q++) tn.push_back((uint32_t)i);
+  }
+  CU(d_nodes.alloc(sizeof(kern::SplitNode) * (size_t)n_nodes));
+  CU(d_tiles.alloc(tn.size() * 4));
+  CU(d_tl.alloc(tn.size() * 4));
+  CU(d_nl.alloc((size_t)n_nodes * 8));
+  CU(cudaMemcpyAsync(d_nodes.p, sn.data(), sizeof(kern::SplitNode) * (size_t)n_nodes, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_tiles.p, tn.data(), tn.size() * 4, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(d_nl.p, 0, (size_t)n_nodes * 8, st));
+  if (!tn.empty()) {
+    kern::part_count_kernel<<<(unsigned)tn.size(), kern::kPartThreads, 0, st>>>(d_in.as<uint64_t>(), d_in.as<uint64_t>(),
+                                                                              d_cm.as<uint8_t>(), Np, d_nodes.as<kern::SplitNode>(),
+                                                                              d_tiles.as<uint32_t>(), d_tl.as<uint32_t>());
+    kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(d_nodes.as<kern::SplitNode>(), d_tl.as<uint32_t>(), d_nl.as<uint64_t>());
+    kern::part_scatter_kernel<<<(unsigned)tn.size(), kern::kPartThreads, 0, st>>>(
+        d_in.as<uint64_t>(), d_in.as<uint64_t>(), d_out.as<uint64_t>(), d_out.as<uint64_t>(), d_cm.as<uint8_t>(), Np,
+        d_nodes.as<kern::SplitNode>(), d_tiles.as<uint32_t>(), d_tl.as<uint32_t>(), d_nl.as<uint64_t>());
+  }
+  CU(cudaGetLastError());
+  std::vector<uint64_t> nl(n_nodes);
+  CU(cudaMemcpyAsync(entries_out, d_out.p, (size_t)n_ent * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(nl.data(), d_nl.p, (size_t)n_nodes * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (int i = 0; i < n_nodes; i++) n_left_out[i] = (int64_t)nl[i];
+  return EMRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-logic probes (no GPU)
+// ---------------------------------------------------------------------------------------------
+extern "C" int64_t emrf_host_java_random_next_long(int64_t seed, int32_t nth) {
+  hl::JavaUtilRandom r(seed);
+  int64_t v = 0;
+  for (int i = 0; i <= nth; i++) v = r.next_long();
+  return v;
+}
+extern "C" double emrf_host_xorshift_next_double(int64_t seed, int32_t nth) {
+  hl::SparkXorShift r(seed);
+  double v = 0;
+  for (int i = 0; i <= nth; i++) v = r.next_double();
+  return v;
+}
+extern "C" int32_t emrf_host_reservoir_sample(int32_t n_items, int32_t k, int64_t seed, int32_t* out) {
+  int len = 0;
+  hl::reservoir_features(n_items, k, seed, out, &len);
+  return len;
+}
+extern "C" int32_t emrf_host_group_tree_order(const int32_t* trees_first_seen, int32_t n, int32_t* out) {
+  std::vector<int> in(trees_first_seen, trees_first_seen + n);
+  std::vector<int> o = hl::group_tree_visit_order(in);
+  for (size_t i = 0; i < o.size(); i++) out[i] = o[i];
+  return (int32_t)o.size();
+}
+extern "C" int32_t emrf_host_num_features_per_node(const emrf_params_t* params, int32_t n_features) {
+  return hl::features_per_node(*params, n_features);
+}

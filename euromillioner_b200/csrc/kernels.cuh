@@ -1,0 +1,902 @@
+// kernels.cuh — hand-written sm_100a kernels of the random-forest fit/transform hot path.
+// Each kernel names the Spark MLlib 2.4.6 routine it replaces;
+// none of that code is in /root/reference (dependency pin: pom.xml:56-61).
+//
+// Data layout in HBM:
+//   bins_rm  uint8 [N][Fp]    row-major TreePoint matrix, Fp = F rounded up to 16 (one row = one
+//                             or two 32 B sectors … 128 B line): the histogram kernel gathers rows
+//   bins_cm  uint8 [F][Np]    column-major TreePoint matrix, Np = N rounded up to 128: the
+//                             partition kernel reads one column per node, rows ascending
+//   entries  uint64 per in-bag (row,tree): row | weight<<32 | label<<40, grouped per tree and,
+//                             inside a tree, per node (each node = one contiguous segment)
+// All floating-point split arithmetic uses explicit round-to-nearest intrinsics so that no FMA
+// contraction can change a gain (the JVM does not fuse).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace emrf {
+namespace kern {
+
+constexpr int kHistThreads = 256;
+constexpr int kPartThreads = 256;
+constexpr int kPartTile = 2048;     // entries per partition tile
+constexpr int kListTile = 2048;     // rows per list-building tile
+constexpr double kInvalidGain = -1.7976931348623157e308;  // Scala Double.MinValue
+
+__host__ __device__ inline uint64_t pack_entry(uint32_t row, uint32_t w, uint32_t label) {
+  return (uint64_t)row | ((uint64_t)(w & 0xffu) << 32) | ((uint64_t)(label & 0xffu) << 40);
+}
+
+// ---------------------------------------------------------------------------------------------
+// labels: validate (Predictor.extractLabeledPoints) and narrow to uint8.
+// flags[0] |= 1 when a label is non-integral / negative / >= n_classes(if >0); flags[1] = max label
+// ---------------------------------------------------------------------------------------------
+__global__ void labels_kernel(const double* __restrict__ y, int64_t n, int n_classes, uint8_t* __restrict__ out,
+                              int* __restrict__ flags) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int bad = 0, mx = 0;
+  if (i < n) {
+    double l = y[i];
+    bool ok = (l >= 0.0) && (l < 256.0) && (floor(l) == l);
+    if (ok && n_classes > 0 && l >= (double)n_classes) ok = false;
+    if (!ok) bad = 1;
+    else { mx = (int)l; out[i] = (uint8_t)mx; }
+  }
+  bad = __any_sync(0xffffffffu, bad);
+  for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) {
+    if (bad) atomicOr(&flags[0], 1);
+    atomicMax(&flags[1], mx);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1 — TreePoint.findBin (ml/tree/impl/TreePoint.scala): bin = #thresholds ordered before x under
+// java.lang.Double.compare (Arrays.binarySearch; an exact hit returns that threshold's index).
+// One CTA bins a tile of 128 rows x all F features: coalesced f64 reads (consecutive threads read
+// consecutive elements of the row-major input), bins staged in shared memory, then written twice
+// with 128-bit stores: row-major rows and column-major 128-row runs.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool java_less(double a, double b) {
+  // Double.compare(a,b) < 0 for non-NaN a (thresholds are never NaN); NaN b sorts above all.
+  if (a < b) return true;
+  if (a > b) return false;
+  if (b != b) return true;
+  return (__double_as_longlong(a) < 0) && (__double_as_longlong(b) >= 0);  // -0.0 < 0.0
+}
+__device__ __forceinline__ int find_bin_dev(const double* thr, int n, double x) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (java_less(thr[mid], x)) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+constexpr int kBinRows = 128;
+template <bool kThrInSmem>
+__global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, int64_t n_rows, int F, int Fp,
+                                                  int64_t Np, const double* __restrict__ thr,
+                                                  const int* __restrict__ n_splits, int thr_stride,
+                                                  uint8_t* __restrict__ bins_rm, uint8_t* __restrict__ bins_cm) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  // layout: tile[kBinRows][Fp] bytes | (optional) thresholds
+  uint8_t* tile = smem_raw;
+  const double* sthr = thr;
+  if (kThrInSmem) {
+    double* st = reinterpret_cast<double*>(smem_raw + (((size_t)kBinRows * Fp + 15) & ~(size_t)15));
+    for (int i = threadIdx.x; i < F * thr_stride; i += blockDim.x) st[i] = thr[i];
+    sthr = st;
+  }
+  const int64_t row0 = (int64_t)blockIdx.x * kBinRows;
+  const int rows = (int)min((int64_t)kBinRows, n_rows - row0);
+  for (int i = threadIdx.x; i < kBinRows * Fp; i += blockDim.x) tile[i] = 0;
+  __syncthreads();
+  const int64_t base = row0 * F;
+  const int total = rows * F;
+  for (int e = threadIdx.x; e < total; e += blockDim.x) {
+    const int r = e / F, f = e - r * F;
+    const double x = X[base + e];
+    tile[r * Fp + f] = (uint8_t)find_bin_dev(sthr + (size_t)f * thr_stride, n_splits[f], x);
+  }
+  __syncthreads();
+  if (bins_rm) {  // rows of the tile are contiguous in bins_rm: straight 128-bit copy
+    const uint4* src = reinterpret_cast<const uint4*>(tile);
+    uint4* dst = reinterpret_cast<uint4*>(bins_rm + (size_t)row0 * Fp);
+    const int n16 = rows * Fp / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = src[i];
+  }
+  if (bins_cm) {  // per feature: 128 consecutive rows = 8 x 16 B
+    for (int i = threadIdx.x; i < F * (kBinRows / 16); i += blockDim.x) {
+      const int f = i / (kBinRows / 16), c = i - f * (kBinRows / 16);
+      uint32_t w[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        uint32_t v = 0;
+#pragma unroll
+        for (int b = 0; b < 4; b++) v |= (uint32_t)tile[(c * 16 + q * 4 + b) * Fp + f] << (8 * b);
+        w[q] = v;
+      }
+      // Np is a multiple of 128 and the buffer is padded, so the full 16 B store is in bounds.
+      *reinterpret_cast<uint4*>(bins_cm + (size_t)f * Np + row0 + c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// BaggedPoint.convertToBaggedRDD (ml/tree/impl/BaggedPoint.scala) with commons-math3 3.4.1
+// PoissonDistribution.sample() on Well19937c: ONE sequential stream per Spark partition, reseeded
+// with seed + partitionIndex + 1; a row's T weights are T successive samples.  One thread per
+// partition (the stream is inherently serial); state in local memory.
+// weights: row-major uint8 [N][T].  max_w: running maximum (weights above 255 are an error).
+// ---------------------------------------------------------------------------------------------
+struct WellState {
+  uint32_t v[624];
+  int idx;
+  __device__ void seed(int64_t s) {
+    v[0] = (uint32_t)((uint64_t)s >> 32);
+    v[1] = (uint32_t)((uint64_t)s & 0xffffffffull);
+    for (int i = 2; i < 624; i++) {
+      const int64_t l = (int64_t)(int32_t)v[i - 2];
+      v[i] = (uint32_t)((1812433253ll * (l ^ (l >> 30)) + i) & 0xffffffffll);
+    }
+    idx = 0;
+  }
+  __device__ __forceinline__ uint32_t next(int bits) {
+    const int i = idx;
+    const int im1 = i ? i - 1 : 623;
+    const int im2 = im1 ? im1 - 1 : 623;
+    int j1 = i + 70;  if (j1 >= 624) j1 -= 624;
+    int j2 = i + 179; if (j2 >= 624) j2 -= 624;
+    int j3 = i + 449; if (j3 >= 624) j3 -= 624;
+    const uint32_t v0 = v[i], vM1 = v[j1], vM2 = v[j2], vM3 = v[j3];
+    const uint32_t z0 = (0x80000000u & v[im1]) ^ (0x7FFFFFFFu & v[im2]);
+    const uint32_t z1 = (v0 ^ (v0 << 25)) ^ (vM1 ^ (vM1 >> 27));
+    const uint32_t z2 = (vM2 >> 9) ^ (vM3 ^ (vM3 >> 1));
+    const uint32_t z3 = z1 ^ z2;
+    uint32_t z4 = z0 ^ (z1 ^ (z1 << 9)) ^ (z2 ^ (z2 << 21)) ^ (z3 ^ (z3 >> 21));
+    v[i] = z3;
+    v[im1] = z4;
+    v[im2] &= 0x80000000u;
+    idx = im1;
+    z4 ^= (z4 << 7) & 0xe46e1700u;
+    z4 ^= (z4 << 15) & 0x9b868000u;
+    return z4 >> (32 - bits);
+  }
+  __device__ __forceinline__ double next_double() {
+    const uint64_t hi = (uint64_t)next(26) << 26;
+    const uint64_t lo = next(26);
+    return __dmul_rn((double)(hi | lo), 2.220446049250313e-16);  // 0x1.0p-52
+  }
+};
+__global__ void __launch_bounds__(32) bag_poisson_kernel(int64_t seed, const int64_t* __restrict__ part_off,
+                                                         int n_parts, int T, double mean, double p_exp,
+                                                         uint8_t* __restrict__ weights, int* __restrict__ max_w) {
+  const int part = blockIdx.x * blockDim.x + threadIdx.x;
+  if (part >= n_parts) return;
+  WellState ws;
+  ws.seed(seed + (int64_t)part + 1);
+  const double limit = __dmul_rn(1000.0, mean);
+  int mx = 0;
+  const int64_t lo = part_off[part], hi = part_off[part + 1];
+  uint8_t* out = weights + (size_t)lo * T;
+  const int64_t total = (hi - lo) * (int64_t)T;
+  for (int64_t q = 0; q < total; q++) {
+    int n = 0;
+    double r = 1.0;
+    while ((double)n < limit) {
+      r = __dmul_rn(r, ws.next_double());
+      if (r >= p_exp) n++; else break;
+    }
+    mx = max(mx, n);
+    out[q] = (uint8_t)min(n, 255);
+  }
+  atomicMax(max_w, mx);
+}
+// T == 1 without replacement and rate < 1: XORShiftRandom(seed+p+1).nextDouble() < rate
+__device__ __forceinline__ uint32_t mm3_mix(uint32_t k) {
+  k *= 0xcc9e2d51u;
+  k = (k << 15) | (k >> 17);
+  return k * 0x1b873593u;
+}
+__device__ inline uint32_t mm3_seed64(const uint32_t* words16, uint32_t seed) {
+  uint32_t h = seed;
+  for (int i = 0; i < 16; i++) {
+    h ^= mm3_mix(words16[i]);
+    h = (h << 13) | (h >> 19);
+    h = h * 5u + 0xe6546b64u;
+  }
+  h ^= 64u;
+  h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+__global__ void bag_bernoulli_kernel(int64_t seed, const int64_t* __restrict__ part_off, int n_parts, int T,
+                                     double rate, uint8_t* __restrict__ weights) {
+  const int part = blockIdx.x * blockDim.x + threadIdx.x;
+  if (part >= n_parts) return;
+  const uint64_t s = (uint64_t)(seed + (int64_t)part + 1);
+  uint32_t words[16];
+  for (int i = 0; i < 16; i++) words[i] = 0;
+  // big-endian seed bytes, read as little-endian words
+  words[0] = __byte_perm((uint32_t)(s >> 32), 0, 0x0123);
+  words[1] = __byte_perm((uint32_t)s, 0, 0x0123);
+  const uint32_t lo = mm3_seed64(words, 0x3c074a61u);
+  const uint32_t hi = mm3_seed64(words, lo);
+  uint64_t x = ((uint64_t)hi << 32) | lo;
+  const int64_t a = part_off[part], b = part_off[part + 1];
+  for (int64_t q = a * T; q < b * T; q++) {
+    uint64_t d[2];
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      x ^= x << 21; x ^= x >> 35; x ^= x << 4;
+      d[k] = x;
+    }
+    const int64_t u = (int64_t)((d[0] & ((1ull << 26) - 1)) << 27) + (int64_t)(d[1] & ((1ull << 27) - 1));
+    const double dd = __dmul_rn((double)u, 1.1102230246251565e-16);  // 0x1.0p-53
+    weights[q] = dd < rate ? 1 : 0;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Per-tree in-bag row lists from the [N][T] weight matrix (stable: rows ascending).
+//   list_count_kernel : per (row tile, tree) number of rows with weight > 0
+//   list_scan_kernel  : per tree exclusive scan over tiles (+ totals)
+//   list_fill_kernel  : writes packed entries at tree_base[t] + tile_off[tile][t] + rank
+// Thread = tree, so weight reads are coalesced along T.
+// ---------------------------------------------------------------------------------------------
+__global__ void list_count_kernel(const uint8_t* __restrict__ w, int64_t n_rows, int T, uint32_t* __restrict__ counts) {
+  const int64_t r0 = (int64_t)blockIdx.x * kListTile;
+  const int rows = (int)min((int64_t)kListTile, n_rows - r0);
+  for (int t = threadIdx.x; t < T; t += blockDim.x) {
+    uint32_t c = 0;
+    const uint8_t* p = w + (size_t)r0 * T + t;
+    for (int r = 0; r < rows; r++) c += (p[(size_t)r * T] != 0);
+    counts[(size_t)blockIdx.x * T + t] = c;
+  }
+}
+__global__ void list_scan_kernel(uint32_t* __restrict__ counts, int n_tiles, int T, uint64_t* __restrict__ totals) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= T) return;
+  uint64_t run = 0;
+  for (int i = 0; i < n_tiles; i++) {
+    const uint32_t c = counts[(size_t)i * T + t];
+    counts[(size_t)i * T + t] = (uint32_t)run;  // < 2^32 rows per tree
+    run += c;
+  }
+  totals[t] = run;
+}
+__global__ void list_fill_kernel(const uint8_t* __restrict__ w, const uint8_t* __restrict__ labels, int64_t n_rows,
+                                 int T, const uint32_t* __restrict__ tile_off, const uint64_t* __restrict__ tree_base,
+                                 uint64_t* __restrict__ entries) {
+  const int64_t r0 = (int64_t)blockIdx.x * kListTile;
+  const int rows = (int)min((int64_t)kListTile, n_rows - r0);
+  for (int t = threadIdx.x; t < T; t += blockDim.x) {
+    uint64_t* dst = entries + tree_base[t] + tile_off[(size_t)blockIdx.x * T + t];
+    const uint8_t* p = w + (size_t)r0 * T + t;
+    for (int r = 0; r < rows; r++) {
+      const uint32_t wt = p[(size_t)r * T];
+      if (wt) *dst++ = pack_entry((uint32_t)(r0 + r), wt, labels[r0 + r]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2 + K3 — DTStatsAggregator update (RandomForest.binSeqOp / orderedBinSeqOp) fused with
+// binsToBestSplit + calculateImpurityStats (ml/tree/impl/RandomForest.scala,
+// mllib/tree/impurity/Gini.scala, Entropy.scala).
+//
+// Work unit = (tile of one node's entry segment, feature chunk).  The CTA privatises the node's
+// class-count histogram [k][bin][class] (uint32) in shared memory, adds its tile with shared
+// memory atomics, and then either
+//   * (node fits one tile)  scans the histogram in place — no histogram ever touches HBM, or
+//   * (multi-tile node)     flushes non-zero counters to the node's global slot with RED.ADD and
+//     the last tile to finish (threadfence + ticket) reloads the slot and scans it.
+// No CTA waits on another, so any launch order is safe.
+// ---------------------------------------------------------------------------------------------
+struct GroupNode {
+  uint64_t seg_start;   // first entry of the node's segment in entries[buf]
+  uint32_t seg_len;
+  uint32_t tile_begin;  // index of the node's first tile in the group
+  uint32_t n_tiles;
+  int32_t slot;         // global histogram slot, -1 = single tile (shared memory only)
+  uint32_t buf;         // which entries buffer holds the segment
+  uint32_t pad;
+};
+struct ScanResult {
+  double gain;
+  int32_t k;      // feature index within the node's subset (-1: no feature with splits in this chunk)
+  int32_t split;
+  int32_t valid;
+  int32_t pad;
+};
+struct HistArgs {
+  const uint64_t* ent0;
+  const uint64_t* ent1;
+  const uint8_t* bins_rm;
+  const GroupNode* nodes;
+  const uint32_t* tile_node;   // tile → node index
+  const int32_t* node_feat;    // [n_nodes][f_sub]
+  const int32_t* num_bins_all; // [F]
+  uint32_t* ghist;             // [slots][f_sub*B*C]
+  uint32_t* tickets;           // [n_nodes*n_chunks], zeroed
+  ScanResult* results;         // [n_nodes*n_chunks]
+  uint32_t* left_counts;       // [n_nodes*n_chunks][C]
+  uint32_t* total_counts;      // [n_nodes*n_chunks][C]
+  int32_t Fp, f_sub, B, C, k_chunk, n_chunks;
+  uint32_t tile_len;
+  int32_t impurity, min_instances, hist_only;
+  double min_info_gain;
+};
+
+// Impurity of the class-count vector v[c] = (sub ? sub[c] - cnt[c] : cnt[c]); total_u = sum v.
+// Gini: 1 - sum f^2 accumulated in class order; Entropy: -sum f*log2(f) over non-zero classes.
+__device__ __forceinline__ double impurity_dev(int kind, const uint32_t* cnt, const uint32_t* sub, int C,
+                                               uint32_t total_u) {
+  if (total_u == 0) return 0.0;
+  const double total = (double)total_u;
+  if (kind == 0) {
+    double imp = 1.0;
+#pragma unroll 5
+    for (int c = 0; c < C; c++) {
+      const uint32_t v = sub ? sub[c] - cnt[c] : cnt[c];
+      const double f = __ddiv_rn((double)v, total);  // v == 0 → f*f == 0 → imp unchanged, exactly
+      imp = __dsub_rn(imp, __dmul_rn(f, f));
+    }
+    return imp;
+  }
+  double imp = 0.0;
+  const double ln2 = log(2.0);
+  for (int c = 0; c < C; c++) {
+    const uint32_t v = sub ? sub[c] - cnt[c] : cnt[c];
+    if (v) {
+      const double f = __ddiv_rn((double)v, total);
+      imp = __dsub_rn(imp, __dmul_rn(f, __ddiv_rn(log(f), ln2)));
+    }
+  }
+  return imp;
+}
+
+// Shared-memory carve-up used by hist_scan_kernel and scan_kernel.
+struct ScanSmem {
+  uint32_t* hist;      // [k_chunk][B][C]
+  uint32_t* tot;       // [256]
+  double* sq;          // [256]
+  double* red_gain;    // [8]
+  double* pimp;        // [1]
+  int* red_idx;        // [8]
+  int* feat;           // [k_chunk]
+  int* nb;             // [k_chunk]
+};
+__host__ __device__ inline size_t scan_hist_words(int k_chunk, int B, int C) {
+  return ((size_t)k_chunk * B * C + 1) & ~(size_t)1;
+}
+__device__ __forceinline__ ScanSmem carve_smem(uint8_t* raw, int k_chunk, int B, int C) {
+  ScanSmem s;
+  s.hist = reinterpret_cast<uint32_t*>(raw);
+  s.tot = s.hist + scan_hist_words(k_chunk, B, C);
+  s.sq = reinterpret_cast<double*>(s.tot + 256);
+  s.red_gain = s.sq + 256;
+  s.pimp = s.red_gain + 8;
+  s.red_idx = reinterpret_cast<int*>(s.pimp + 1);
+  s.feat = s.red_idx + 8;
+  s.nb = s.feat + k_chunk;
+  return s;
+}
+inline size_t hist_smem_bytes(int k_chunk, int B, int C) {
+  return scan_hist_words(k_chunk, B, C) * 4 + 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + (size_t)k_chunk * 8 + 16;
+}
+
+// Scans a histogram chunk held in shared memory: hist[kc][B][C]; nb[k] = numBins of subset
+// feature k0+k.  All threads of the CTA participate; writes the chunk's result record.
+__device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int impurity, int min_instances,
+                           double min_info_gain, ScanResult* res, uint32_t* left_out, uint32_t* total_out) {
+  const int tid = threadIdx.x, NT = blockDim.x;
+  uint32_t* sh = S.hist;
+  const int* nb = S.nb;
+  // (a) inclusive prefix sum over bins for every (feature, class) column — conflict-free
+  for (int p = tid; p < kc * C; p += NT) {
+    const int k = p / C, c = p - k * C;
+    uint32_t* col = sh + (size_t)k * B * C + c;
+    uint32_t run = 0;
+    const int n = nb[k];
+    for (int b = 0; b < n; b++) { run += col[b * C]; col[b * C] = run; }
+  }
+  __syncthreads();
+  // (b) node totals = last bin of the chunk's first feature (every feature sums to the same)
+  for (int c = tid; c < C; c += NT) S.tot[c] = sh[(size_t)(nb[0] - 1) * C + c];
+  __syncthreads();
+  uint32_t tot_all = 0;
+  for (int c = 0; c < C; c++) tot_all += S.tot[c];
+  // parent impurity: the per-class terms in parallel, then the ordered subtraction chain
+  for (int c = tid; c < C; c += NT) {
+    double term = 0.0;
+    const uint32_t v = S.tot[c];
+    if (v && tot_all) {
+      const double f = __ddiv_rn((double)v, (double)tot_all);
+      term = impurity == 0 ? __dmul_rn(f, f) : __dmul_rn(f, __ddiv_rn(log(f), log(2.0)));
+    }
+    S.sq[c] = term;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    double imp = 0.0;
+    if (tot_all) {
+      imp = impurity == 0 ? 1.0 : 0.0;
+      for (int c = 0; c < C; c++) imp = __dsub_rn(imp, S.sq[c]);
+    }
+    *S.pimp = imp;
+  }
+  __syncthreads();
+  const double pimp = *S.pimp;
+  // (c) one candidate (feature, split) per thread, Spark's operation order
+  double best_gain = -INFINITY;  // below Double.MinValue: "no candidate"
+  int best_idx = 0x7fffffff;
+  const int n_cand = kc * (B - 1);
+  for (int cand = tid; cand < n_cand; cand += NT) {
+    const int k = cand / (B - 1), s = cand - k * (B - 1);
+    if (s >= nb[k] - 1) continue;
+    const uint32_t* l = sh + ((size_t)k * B + s) * C;
+    uint32_t lc = 0;
+    for (int c = 0; c < C; c++) lc += l[c];
+    const uint32_t rc = tot_all - lc;
+    double gain;
+    if (lc < (uint32_t)min_instances || rc < (uint32_t)min_instances) {
+      gain = kInvalidGain;
+    } else {
+      const double li = impurity_dev(impurity, l, nullptr, C, lc);
+      const double ri = impurity_dev(impurity, l, S.tot, C, rc);
+      const double tc = (double)tot_all;  // (leftCount + rightCount).toDouble
+      const double lw = __ddiv_rn((double)lc, tc);
+      const double rw = __ddiv_rn((double)rc, tc);
+      gain = __dsub_rn(__dsub_rn(pimp, __dmul_rn(lw, li)), __dmul_rn(rw, ri));
+      if (gain < min_info_gain) gain = kInvalidGain;
+    }
+    if (gain > best_gain) { best_gain = gain; best_idx = cand; }  // first max (cand ascending per thread)
+  }
+  // (d) block arg-max: greatest gain, ties → smallest candidate index (= Spark's first maximum
+  // in (subset order, split order))
+  for (int o = 16; o; o >>= 1) {
+    const double g2 = __shfl_xor_sync(0xffffffffu, best_gain, o);
+    const int i2 = __shfl_xor_sync(0xffffffffu, best_idx, o);
+    if (g2 > best_gain || (g2 == best_gain && i2 < best_idx)) { best_gain = g2; best_idx = i2; }
+  }
+  if ((tid & 31) == 0) { S.red_gain[tid >> 5] = best_gain; S.red_idx[tid >> 5] = best_idx; }
+  __syncthreads();
+  if (tid < 32) {
+    const int nw = NT >> 5;
+    double g = tid < nw ? S.red_gain[tid] : -INFINITY;
+    int ix = tid < nw ? S.red_idx[tid] : 0x7fffffff;
+    for (int o = 16; o; o >>= 1) {
+      const double g2 = __shfl_xor_sync(0xffffffffu, g, o);
+      const int i2 = __shfl_xor_sync(0xffffffffu, ix, o);
+      if (g2 > g || (g2 == g && i2 < ix)) { g = g2; ix = i2; }
+    }
+    if (tid == 0) { S.red_gain[0] = g; S.red_idx[0] = ix; }
+  }
+  __syncthreads();
+  const double g = S.red_gain[0];
+  const int ix = S.red_idx[0];
+  if (ix == 0x7fffffff) {
+    if (tid == 0) { res->gain = kInvalidGain; res->k = -1; res->split = 0; res->valid = 0; res->pad = 0; }
+    for (int c = tid; c < C; c += NT) { left_out[c] = 0; total_out[c] = S.tot[c]; }
+  } else {
+    const int k = ix / (B - 1), s = ix - k * (B - 1);
+    if (tid == 0) { res->gain = g; res->k = k0 + k; res->split = s; res->valid = (g != kInvalidGain); res->pad = 0; }
+    const uint32_t* l = sh + ((size_t)k * B + s) * C;
+    for (int c = tid; c < C; c += NT) { left_out[c] = l[c]; total_out[c] = S.tot[c]; }
+  }
+}
+
+__global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs A) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int tid = threadIdx.x;
+  const int chunk = blockIdx.y;
+  const int k0 = chunk * A.k_chunk;
+  const int kc = min(A.k_chunk, A.f_sub - k0);
+  const int B = A.B, C = A.C;
+  const ScanSmem S = carve_smem(smem_raw, A.k_chunk, B, C);
+  uint32_t* sh = S.hist;
+  int* sh_feat = S.feat;
+  int* sh_nb = S.nb;
+  __shared__ int sh_last;
+
+  const uint32_t g = A.tile_node[blockIdx.x];
+  const GroupNode nd = A.nodes[g];
+  const uint32_t tile_in_node = blockIdx.x - nd.tile_begin;
+  for (int k = tid; k < kc; k += kHistThreads) {
+    const int f = A.node_feat[(size_t)g * A.f_sub + k0 + k];
+    sh_feat[k] = f;
+    sh_nb[k] = A.num_bins_all[f];
+  }
+  for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = 0;
+  __syncthreads();
+
+  // ---- accumulate this tile
+  const uint64_t* ent = (nd.buf ? A.ent1 : A.ent0) + nd.seg_start + (uint64_t)tile_in_node * A.tile_len;
+  const uint32_t len = min(A.tile_len, nd.seg_len - tile_in_node * A.tile_len);
+  const uint8_t* bins = A.bins_rm;
+  const int Fp = A.Fp;
+  for (uint32_t j = tid; j < len; j += kHistThreads) {
+    const uint64_t e = ent[j];
+    const uint32_t row = (uint32_t)e;
+    const uint32_t w = (uint32_t)(e >> 32) & 0xffu;
+    const uint32_t lab = (uint32_t)(e >> 40) & 0xffu;
+    const uint8_t* rp = bins + (size_t)row * Fp;
+    for (int k = 0; k < kc; k++) {
+      const uint32_t b = rp[sh_feat[k]];
+      atomicAdd(&sh[(k * B + b) * C + lab], w);
+    }
+  }
+  __syncthreads();
+
+  const size_t slot_words = (size_t)A.f_sub * B * C;
+  const size_t rec = (size_t)g * A.n_chunks + chunk;
+  if (nd.slot >= 0) {
+    uint32_t* gh = A.ghist + (size_t)nd.slot * slot_words + (size_t)k0 * B * C;
+    for (int i = tid; i < kc * B * C; i += kHistThreads) {
+      const uint32_t v = sh[i];
+      if (v) atomicAdd(&gh[i], v);
+    }
+    if (A.hist_only) return;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) sh_last = (atomicAdd(&A.tickets[rec], 1u) == nd.n_tiles - 1);
+    __syncthreads();
+    if (!sh_last) return;
+    __threadfence();
+    for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = __ldcg(&gh[i]);
+    __syncthreads();
+  }
+  scan_chunk(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rec],
+             A.left_counts + rec * C, A.total_counts + rec * C);
+}
+
+// K3 alone — binsToBestSplit on histograms already in HBM (stage entry point; also the scan used
+// after the histogram all-reduce when rows are sharded across GPUs).  grid = (n_nodes, n_chunks).
+__global__ void __launch_bounds__(kHistThreads) scan_kernel(const uint32_t* __restrict__ hist, const int32_t* node_feat,
+                                                           const int32_t* num_bins_all, int f_sub, int B, int C,
+                                                           int k_chunk, int n_chunks, int impurity, int min_instances,
+                                                           double min_info_gain, ScanResult* results,
+                                                           uint32_t* left_counts, uint32_t* total_counts) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int tid = threadIdx.x;
+  const int g = blockIdx.x, chunk = blockIdx.y;
+  const int k0 = chunk * k_chunk;
+  const int kc = min(k_chunk, f_sub - k0);
+  const ScanSmem S = carve_smem(smem_raw, k_chunk, B, C);
+  uint32_t* sh = S.hist;
+  int* sh_nb = S.nb;
+  for (int k = tid; k < kc; k += kHistThreads) sh_nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
+  const uint32_t* gh = hist + ((size_t)g * f_sub + k0) * B * C;
+  for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = gh[i];
+  __syncthreads();
+  const size_t rec = (size_t)g * n_chunks + chunk;
+  scan_chunk(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,
+             total_counts + rec * C);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4 — LearningNode.predictImpl, one level: rows of a split node go left iff
+// bin(feature) <= splitIndex (ContinuousSplit.shouldGoLeft on binned features).  Stable partition
+// of the node's entry segment into the other entries buffer: [left … | right …].
+//   part_count_kernel   : lefts per tile
+//   part_scan_kernel    : per node exclusive scan over its tiles, node totals
+//   part_scatter_kernel : ranks inside the tile by ballot/prefix, then scatter
+// ---------------------------------------------------------------------------------------------
+struct SplitNode {
+  uint64_t seg_start;
+  uint32_t seg_len;
+  uint32_t tile_begin;
+  uint32_t n_tiles;
+  uint32_t buf;        // source buffer; destination is the other one
+  int32_t feature;
+  int32_t split_bin;
+};
+__global__ void __launch_bounds__(kPartThreads) part_count_kernel(const uint64_t* ent0, const uint64_t* ent1,
+                                                                  const uint8_t* __restrict__ bins_cm, int64_t Np,
+                                                                  const SplitNode* __restrict__ nodes,
+                                                                  const uint32_t* __restrict__ tile_node,
+                                                                  uint32_t* __restrict__ tile_left) {
+  __shared__ uint32_t sh_cnt[kPartThreads / 32];
+  const uint32_t g = tile_node[blockIdx.x];
+  const SplitNode nd = nodes[g];
+  const uint32_t t_in = blockIdx.x - nd.tile_begin;
+  const uint64_t* ent = (nd.buf ? ent1 : ent0) + nd.seg_start + (uint64_t)t_in * kPartTile;
+  const uint32_t len = min((uint32_t)kPartTile, nd.seg_len - t_in * kPartTile);
+  const uint8_t* col = bins_cm + (size_t)nd.feature * Np;
+  uint32_t c = 0;
+  for (uint32_t j = threadIdx.x; j < len; j += kPartThreads) {
+    const uint32_t row = (uint32_t)ent[j];
+    c += ((int)col[row] <= nd.split_bin);
+  }
+  for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) sh_cnt[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t s = 0;
+    for (int i = 0; i < kPartThreads / 32; i++) s += sh_cnt[i];
+    tile_left[blockIdx.x] = s;
+  }
+}
+__global__ void __launch_bounds__(256) part_scan_kernel(const SplitNode* __restrict__ nodes, uint32_t* __restrict__ tile_left,
+                                                        uint64_t* __restrict__ n_left) {
+  // one CTA per node; sequential chunks of 256 tiles with a block scan
+  __shared__ uint32_t sh[256];
+  __shared__ uint32_t carry;
+  const SplitNode nd = nodes[blockIdx.x];
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < nd.n_tiles; base += 256) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < nd.n_tiles ? tile_left[nd.tile_begin + i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < 256; o <<= 1) {  // Hillis–Steele inclusive scan
+      uint32_t add = threadIdx.x >= o ? sh[threadIdx.x - o] : 0;
+      __syncthreads();
+      sh[threadIdx.x] += add;
+      __syncthreads();
+    }
+    const uint32_t incl = sh[threadIdx.x];
+    const uint32_t c0 = carry;
+    if (i < nd.n_tiles) tile_left[nd.tile_begin + i] = c0 + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 255) carry = c0 + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) n_left[blockIdx.x] = carry;
+}
+__global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64_t* ent0, const uint64_t* ent1,
+                                                                    uint64_t* out0, uint64_t* out1,
+                                                                    const uint8_t* __restrict__ bins_cm, int64_t Np,
+                                                                    const SplitNode* __restrict__ nodes,
+                                                                    const uint32_t* __restrict__ tile_node,
+                                                                    const uint32_t* __restrict__ tile_left_off,
+                                                                    const uint64_t* __restrict__ n_left) {
+  __shared__ uint32_t sh_w[kPartThreads / 32];
+  __shared__ uint32_t sh_base;
+  const uint32_t g = tile_node[blockIdx.x];
+  const SplitNode nd = nodes[g];
+  const uint32_t t_in = blockIdx.x - nd.tile_begin;
+  const uint64_t tile_start = (uint64_t)t_in * kPartTile;
+  const uint64_t* ent = (nd.buf ? ent1 : ent0) + nd.seg_start + tile_start;
+  uint64_t* dst = (nd.buf ? out0 : out1) + nd.seg_start;  // other buffer, same segment
+  const uint32_t len = min((uint32_t)kPartTile, nd.seg_len - (uint32_t)tile_start);
+  const uint8_t* col = bins_cm + (size_t)nd.feature * Np;
+  const uint64_t left_base = tile_left_off[blockIdx.x];
+  const uint64_t right_base = n_left[g] + (tile_start - left_base);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) sh_base = 0;
+  __syncthreads();
+  for (uint32_t j0 = 0; j0 < len; j0 += kPartThreads) {
+    const uint32_t j = j0 + threadIdx.x;
+    const bool act = j < len;
+    uint64_t e = 0;
+    bool left = false;
+    if (act) { e = ent[j]; left = ((int)col[(uint32_t)e] <= nd.split_bin); }
+    const uint32_t bal = __ballot_sync(0xffffffffu, left);
+    const uint32_t before = __popc(bal & ((1u << lane) - 1));
+    if (lane == 0) sh_w[wid] = __popc(bal);
+    __syncthreads();
+    uint32_t wbase = 0, round_total = 0;
+    for (int i = 0; i < kPartThreads / 32; i++) {
+      const uint32_t c = sh_w[i];
+      if (i < wid) wbase += c;
+      round_total += c;
+    }
+    const uint32_t lefts_before_round = sh_base;       // lefts in earlier rounds of this tile
+    const uint32_t lrank = lefts_before_round + wbase + before;
+    if (act) {
+      if (left) dst[left_base + lrank] = e;
+      else dst[right_base + (j - lrank)] = e;          // j - (#lefts before j in tile) = right rank
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) sh_base = lefts_before_round + round_total;
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// findSplits on the device (RandomForest.findSplitsBySorting / findSplitsForContinuousFeature).
+//   fs_gather_kernel : sampled rows → column-major sample matrix, zero filter (policy 0) marks
+//                      filtered values with a sentinel that sorts last
+//   fs_sort_walk_kernel : one CTA per feature: bitonic sort, distinct count, then the sequential
+//                      stride walk over distinct values (thread 0), Spark's exact arithmetic
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool fs_is_sentinel(double v) { return __double_as_longlong(v) == 0x7ff8dead0000beefll; }
+__device__ __forceinline__ double fs_sentinel() { return __longlong_as_double(0x7ff8dead0000beefll); }
+__device__ __forceinline__ bool fs_less(double a, double b) {
+  if (fs_is_sentinel(a)) return false;
+  if (fs_is_sentinel(b)) return true;
+  return a < b;
+}
+__global__ void fs_gather_kernel(const double* __restrict__ X, int F, const int64_t* __restrict__ rows, int n_s,
+                                 int n_pad, int all_rows, int zero_filter, double* __restrict__ S) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t total = (int64_t)n_pad * F;
+  if (i >= total) return;
+  // element i ↔ (j = i / F sample, f = i % F feature): coalesced reads of X
+  const int j = (int)(i / F), f = (int)(i - (int64_t)j * F);
+  double v = fs_sentinel();
+  if (j < n_s) {
+    const int64_t r = all_rows ? j : rows[j];
+    v = X[r * F + f];
+    if (zero_filter && v == 0.0) v = fs_sentinel();
+  }
+  S[(size_t)f * n_pad + j] = v;
+}
+__global__ void __launch_bounds__(1024) fs_sort_walk_kernel(double* __restrict__ S, int n_pad, int n_s, int use_smem,
+                                                            int num_splits, int64_t num_samples_expected, int policy,
+                                                            int thr_stride, double* __restrict__ thr_out,
+                                                            int* __restrict__ n_splits_out) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  __shared__ int sh_nvalid, sh_distinct;
+  const int f = blockIdx.x;
+  double* g = S + (size_t)f * n_pad;
+  double* a = g;
+  if (use_smem) {
+    a = reinterpret_cast<double*>(smem_raw);
+    for (int i = threadIdx.x; i < n_pad; i += blockDim.x) a[i] = g[i];
+  }
+  if (threadIdx.x == 0) { sh_nvalid = 0; sh_distinct = 0; }
+  __syncthreads();
+  for (int k = 2; k <= n_pad; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < n_pad; i += blockDim.x) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const double x = a[i], y = a[ixj];
+          const bool up = ((i & k) == 0);
+          if (up ? fs_less(y, x) : fs_less(x, y)) { a[i] = y; a[ixj] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // count kept samples and distinct values among them
+  int nv = 0, nd = 0;
+  for (int i = threadIdx.x; i < n_s; i += blockDim.x) {
+    if (!fs_is_sentinel(a[i])) {
+      nv++;
+      if (i == 0 || a[i] != a[i - 1]) nd++;
+    }
+  }
+  atomicAdd(&sh_nvalid, nv);
+  atomicAdd(&sh_distinct, nd);
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  const int part_num = sh_nvalid;
+  int n_out = 0;
+  double* out = thr_out + (size_t)f * thr_stride;
+  if (part_num == 0) { n_splits_out[f] = 0; return; }  // featureSamples.isEmpty (or key absent)
+  int64_t num_samples = part_num;
+  int64_t phantom = 0;  // count of the re-added 0.0 value
+  if (policy == 0) {
+    num_samples = num_samples_expected;
+    if (num_samples - part_num > 0) phantom = num_samples - part_num;
+  }
+  const int distinct = sh_distinct + (phantom > 0 ? 1 : 0);
+  const int possible = distinct - 1;
+  if (possible == 0) { n_splits_out[f] = 0; return; }
+  // iterate (value,count) pairs ascending, merging the phantom zero in order
+  int pos = 0;
+  bool phantom_done = (phantom == 0);
+  double pv = 0.0, cv = 0.0;   // previous / current distinct value
+  int64_t cc = 0;              // current count
+  auto next_pair = [&]() -> bool {
+    if (pos >= part_num && phantom_done) return false;
+    if (!phantom_done && (pos >= part_num || a[pos] > 0.0)) {
+      phantom_done = true; cv = 0.0; cc = phantom; return true;
+    }
+    const double v = a[pos];
+    int64_t c = 0;
+    while (pos < part_num && a[pos] == v) { c++; pos++; }
+    cv = v; cc = c;
+    return true;
+  };
+  if (possible <= num_splits) {
+    next_pair();
+    pv = cv;
+    while (next_pair()) {
+      if (n_out < thr_stride) out[n_out] = __ddiv_rn(__dadd_rn(pv, cv), 2.0);
+      n_out++;
+      pv = cv;
+    }
+  } else {
+    const double stride = __ddiv_rn((double)num_samples, (double)(num_splits + 1));
+    next_pair();
+    int64_t current = cc;
+    pv = cv;
+    double target = stride;
+    while (next_pair()) {
+      const int64_t previous = current;
+      current += cc;
+      const double pgap = fabs(__dsub_rn((double)previous, target));
+      const double cgap = fabs(__dsub_rn((double)current, target));
+      if (pgap < cgap) {
+        if (n_out < thr_stride) out[n_out] = __ddiv_rn(__dadd_rn(pv, cv), 2.0);
+        n_out++;
+        target = __dadd_rn(target, stride);
+      }
+      pv = cv;
+    }
+  }
+  n_splits_out[f] = n_out;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K5 — RandomForestClassificationModel.predictRaw / raw2probabilityInPlace / raw2prediction
+// (ml/classification/RandomForestClassifier.scala; Node.predictImpl, ContinuousSplit.shouldGoLeft:
+// features(f) <= threshold → left).  One warp per row: all lanes walk the tree together (uniform,
+// broadcast loads), lane c owns classes c, c+32, … and accumulates votes in tree order (the f64
+// sum order is part of the contract).  leaf_prob[leaf][C] holds stats(c)/sum(stats) precomputed
+// with the same division.
+// ---------------------------------------------------------------------------------------------
+struct DevNode {        // 24 bytes
+  double threshold;
+  int32_t feature;      // -1 = leaf
+  int32_t left;         // absolute node index; for a leaf: index into leaf_prob
+  int32_t right;
+  int32_t pad;
+};
+constexpr int kMaxClassSlots = 8;  // C <= 256
+__global__ void __launch_bounds__(256) predict_kernel(const double* __restrict__ X, int64_t n_rows, int F,
+                                                      const DevNode* __restrict__ nodes,
+                                                      const int64_t* __restrict__ tree_root, int T,
+                                                      const double* __restrict__ leaf_prob, int C,
+                                                      double* __restrict__ raw, double* __restrict__ prob,
+                                                      double* __restrict__ pred) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= n_rows) return;
+  const double* x = X + row * F;
+  double votes[kMaxClassSlots];
+#pragma unroll
+  for (int q = 0; q < kMaxClassSlots; q++) votes[q] = 0.0;
+  for (int t = 0; t < T; t++) {
+    int64_t n = tree_root[t];
+    DevNode nd = nodes[n];
+    while (nd.feature >= 0) {
+      n = (x[nd.feature] <= nd.threshold) ? nd.left : nd.right;
+      nd = nodes[n];
+    }
+    if (nd.right) {  // right != 0 marks a leaf with non-zero total
+      const double* lp = leaf_prob + (size_t)nd.left * C;
+#pragma unroll
+      for (int q = 0; q < kMaxClassSlots; q++) {
+        const int c = lane + 32 * q;
+        if (c < C) votes[q] = __dadd_rn(votes[q], lp[c]);
+      }
+    }
+  }
+  if (raw) {
+#pragma unroll
+    for (int q = 0; q < kMaxClassSlots; q++) {
+      const int c = lane + 32 * q;
+      if (c < C) raw[row * C + c] = votes[q];
+    }
+  }
+  // sequential (index-order) sum and first-max argmax, as Array[Double].sum / Vector.argmax do
+  double s = 0.0, best = 0.0;
+  int best_c = 0;
+  for (int c = 0; c < C; c++) {
+    const int q = c >> 5;
+    double v = 0.0;
+#pragma unroll
+    for (int qq = 0; qq < kMaxClassSlots; qq++) if (qq == q) v = votes[qq];
+    v = __shfl_sync(0xffffffffu, v, c & 31);
+    s = __dadd_rn(s, v);
+    if (c == 0 || v > best) { best = v; best_c = c; }
+  }
+  if (pred && lane == 0) pred[row] = (double)best_c;
+  if (prob) {
+#pragma unroll
+    for (int q = 0; q < kMaxClassSlots; q++) {
+      const int c = lane + 32 * q;
+      if (c < C) prob[row * C + c] = (s != 0.0) ? __ddiv_rn(votes[q], s) : votes[q];
+    }
+  }
+}
+
+}  // namespace kern
+}  // namespace emrf

@@ -1,0 +1,186 @@
+/*
+ * emrf.h — C ABI of the B200-native random-forest engine (libemrf.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of mareksagan/Euromillioner that this
+ * repository accelerates: the Spark MLlib 2.4.6 RandomForestClassifier fit/transform stage
+ * (SURVEY.md §8).  The reference exposes no FFI/plugin interface of its own (its only native
+ * boundary is inside the undeclared xgboost4j jar, Main.java:110,137,140 — the model stage these
+ * entry points replace; the dependency that holds the RF arithmetic is pinned at pom.xml:56-61).
+ * Each entry point below therefore cites the Spark ML / MLlib interface it stands in for
+ * (upstream path under spark/mllib/src/main/scala/org/apache/spark/).
+ *
+ * Conventions: plain C, POD structs, caller-allocated outputs or opaque handles with a matching
+ * _free/_destroy; every function returns int status (0 = OK, <0 = error) and never throws;
+ * emrf_last_error() returns the calling thread's last message.  Pointers named *_hd may point
+ * to host or device memory (detected with cudaPointerGetAttributes); all others are host.
+ * There is NO CPU fallback: every compute entry point fails with EMRF_ERR_CUDA when no usable
+ * sm_100 device is present.
+ */
+#ifndef EMRF_H_
+#define EMRF_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EMRF_OK 0
+#define EMRF_ERR_ARG (-1)     /* IllegalArgumentException on the JVM side (Spark `require`) */
+#define EMRF_ERR_CUDA (-2)    /* RuntimeException / SparkException on the JVM side */
+#define EMRF_ERR_LIMIT (-3)   /* shape outside what this build supports */
+#define EMRF_ERR_INTERNAL (-4)
+
+typedef struct emrf_ctx emrf_ctx_t;       /* device, stream, scratch; one fit at a time per ctx */
+typedef struct emrf_forest emrf_forest_t; /* host + device copy of a trained forest; immutable */
+
+/* Spark ML RandomForestClassifier params (ml/classification/RandomForestClassifier.scala,
+ * ml/tree/treeParams.scala): setNumTrees/setMaxDepth/setMaxBins/setMinInstancesPerNode/
+ * setImpurity/setFeatureSubsetStrategy/setMinInfoGain/setSubsamplingRate/setMaxMemoryInMB/setSeed. */
+typedef struct {
+  int32_t num_trees;               /* default 20 */
+  int32_t max_depth;               /* default 5, <= 30 */
+  int32_t max_bins;                /* default 32, 2..256 */
+  int32_t min_instances_per_node;  /* default 1 */
+  int32_t num_classes;             /* 0 = infer max(label)+1 (<= 100, Predictor.getNumClasses) */
+  int32_t impurity;                /* 0 gini, 1 entropy (entropy gains are not bit-exact) */
+  int32_t feature_subset_kind;     /* 0 auto, 1 all, 2 sqrt, 3 log2, 4 onethird, 5 n, 6 fraction */
+  double feature_subset_value;     /* for kinds 5 and 6 */
+  double min_info_gain;            /* default 0.0 */
+  double subsampling_rate;         /* default 1.0, (0,1] */
+  int32_t max_memory_mb;           /* default 256: bounds nodes per group exactly as Spark does */
+  int32_t find_splits_policy;      /* 0 = Spark 2.4 (zero filter + expected sample count); 1 = pre-2.4 */
+  int64_t seed;                    /* default 207336481 = "…RandomForestClassifier".hashCode */
+  int32_t shard_mode;              /* multi-GPU: 0 tree-sharded, 1 row-sharded (ignored when world==1) */
+  int32_t reserved;
+} emrf_params_t;
+
+/* Phase timers named after Spark's TimeTracker phases (ml/tree/impl/TimeTracker.scala), device
+ * time measured with CUDA events on the ctx stream, plus the counters bench.py needs. */
+typedef struct {
+  double total_ms;          /* whole emrf_fit: first byte on device → forest on host */
+  double h2d_ms;            /* host→device copy of features/labels (0 when inputs were device-resident) */
+  double find_splits_ms;    /* findSplits */
+  double bin_ms;            /* TreePoint conversion (K1) */
+  double bag_ms;            /* BaggedPoint weights + per-tree row lists */
+  double find_best_splits_ms; /* all groups: histogram + split scan kernels (K2+K3), device time */
+  double hist_kernel_ms;    /* of which: the histogram(+fused scan) kernel, summed over launches */
+  double partition_ms;      /* row→node partition update kernels (K4), summed */
+  double host_scheduler_ms; /* selectNodesToSplit + driver-side tree updates, wall time */
+  int64_t hist_launches;    /* number of histogram kernel launches (= number of groups) */
+  int64_t kernel_launches;  /* all kernels launched by the fit */
+  int64_t hist_alg_bytes;   /* algorithmic bytes of the histogram kernel: sum (F_sub+6)*rows + hist out */
+  int64_t hist_units;       /* in-bag (row,tree) visits summed over groups */
+  int64_t num_groups;
+  int64_t total_nodes_split; /* nodes that went through findBestSplits */
+  int64_t gain_mismatches;  /* device-vs-host recomputed gain differences (must be 0) */
+} emrf_timings_t;
+
+const char* emrf_last_error(void);
+/* build/version string; also proves the library loaded */
+const char* emrf_version(void);
+
+/* ---- context ------------------------------------------------------------------------------ */
+int emrf_ctx_create(int32_t device, emrf_ctx_t** out);
+/* Multi-GPU: one process per GPU.  `nccl_uid` is the 128-byte ncclUniqueId made by rank 0 with
+ * emrf_nccl_unique_id and broadcast by the launcher (torch.distributed / any side channel). */
+int emrf_nccl_unique_id(uint8_t* uid128);
+int emrf_ctx_create_dist(int32_t device, int32_t rank, int32_t world, const uint8_t* nccl_uid,
+                         emrf_ctx_t** out);
+void emrf_ctx_destroy(emrf_ctx_t* ctx);
+int emrf_get_timings(const emrf_ctx_t* ctx, emrf_timings_t* out);
+
+/* Device/pinned memory helpers for hosts without a CUDA binding of their own (the JNI shim). */
+int emrf_dev_alloc(emrf_ctx_t* ctx, int64_t bytes, void** out);
+int emrf_dev_free(emrf_ctx_t* ctx, void* p);
+int emrf_host_alloc_pinned(int64_t bytes, void** out);
+int emrf_host_free_pinned(void* p);
+int emrf_memcpy_h2d(emrf_ctx_t* ctx, void* dst_dev, const void* src_host, int64_t bytes);
+int emrf_memcpy_d2h(emrf_ctx_t* ctx, void* dst_host, const void* src_dev, int64_t bytes);
+
+/* ---- Estimator: RandomForestClassifier.fit → RandomForest.run ------------------------------
+ * Replaces ml/classification/RandomForestClassifier.train + ml/tree/impl/RandomForest.run.
+ * features: row-major N×F float64 (a Dataset's dense `features` vectors), labels: N float64
+ * (integral, 0 <= label < num_classes, as Predictor.extractLabeledPoints validates).
+ * partition_offsets[P+1]: the Dataset's partition layout (rows of partition p are
+ * [off[p], off[p+1])) — part of the contract because Spark seeds bagging and split-sampling per
+ * partition (BaggedPoint.convertToBaggedRDD, RDD.sample). */
+int emrf_fit(emrf_ctx_t* ctx, const emrf_params_t* params, const double* features_hd,
+             const double* labels_hd, int64_t n_rows, int32_t n_features,
+             const int64_t* partition_offsets, int32_t n_partitions, emrf_forest_t** out);
+
+/* ---- Model: RandomForestClassificationModel ------------------------------------------------ */
+void emrf_forest_free(emrf_forest_t* f);
+int emrf_forest_info(const emrf_forest_t* f, int32_t* num_trees, int32_t* num_classes,
+                     int32_t* num_features, int64_t* total_nodes);
+/* Flat export, trees in index order, nodes pre-order per tree (what Model.trees / toDebugString
+ * walk): tree_off[T+1]; per node: Spark node id, left/right (index within the tree, -1 = leaf),
+ * split feature (-1 = leaf), threshold, gain, impurity, prediction, class counts stats[C]. */
+int emrf_forest_export(const emrf_forest_t* f, int64_t* tree_off, int32_t* node_id, int32_t* left,
+                       int32_t* right, int32_t* feature, double* threshold, double* gain,
+                       double* impurity, double* prediction, double* stats);
+int emrf_forest_import(emrf_ctx_t* ctx, int32_t num_trees, int32_t num_classes, int32_t num_features,
+                       const int64_t* tree_off, const int32_t* node_id, const int32_t* left,
+                       const int32_t* right, const int32_t* feature, const double* threshold,
+                       const double* gain, const double* impurity, const double* prediction,
+                       const double* stats, emrf_forest_t** out);
+/* Scheduler trace of the fit that made this forest: group sizes, and per popped node
+ * (tree, node id, F_sub feature ids) in pop order — what selectNodesToSplit decided. */
+int emrf_forest_trace_info(const emrf_forest_t* f, int32_t* num_groups, int64_t* trace_len, int32_t* f_sub);
+int emrf_forest_trace(const emrf_forest_t* f, int32_t* group_sizes, int32_t* trace);
+/* featureImportances (ml/tree/treeModels.scala TreeEnsembleModel.featureImportances) */
+int emrf_forest_feature_importances(const emrf_forest_t* f, double* out /* F */);
+
+/* RandomForestClassificationModel.transform: predictRaw / raw2probabilityInPlace / raw2prediction.
+ * raw/prob: N×C or NULL; pred: N or NULL.  Safe for concurrent callers on one ctx. */
+int emrf_predict(emrf_ctx_t* ctx, const emrf_forest_t* f, const double* features_hd, int64_t n_rows,
+                 double* raw_hd, double* prob_hd, double* pred_hd);
+
+/* ---- stage-level entry points (each kernel parity-checked alone) ---------------------------- */
+/* RandomForest.findSplits: thresholds_out[F*max_bins] (row f holds n_splits_out[f] values). */
+int emrf_find_splits(emrf_ctx_t* ctx, const emrf_params_t* params, const double* features_hd, int64_t n_rows,
+                     int32_t n_features, const int64_t* partition_offsets, int32_t n_partitions,
+                     double* thresholds_out, int32_t* n_splits_out);
+/* the rows RDD.sample keeps for findSplits (host logic; no GPU needed) */
+int64_t emrf_find_splits_sample_rows(const emrf_params_t* params, int64_t n_rows, const int64_t* partition_offsets,
+                                     int32_t n_partitions, int64_t* rows_out, int64_t cap);
+/* TreePoint.convertToTreeRDD (K1): bins_cm_out[F*N] column-major, bins_rm_out[N*F] row-major
+ * (either may be NULL). */
+int emrf_bin(emrf_ctx_t* ctx, const double* features_hd, int64_t n_rows, int32_t n_features,
+             const double* thresholds, const int32_t* n_splits, int32_t thr_stride, uint8_t* bins_cm_out,
+             uint8_t* bins_rm_out);
+/* BaggedPoint.convertToBaggedRDD: weights_out[N*T] row-major uint8 */
+int emrf_bag_weights(emrf_ctx_t* ctx, const emrf_params_t* params, int64_t n_rows, const int64_t* partition_offsets,
+                     int32_t n_partitions, uint8_t* weights_out, int32_t* max_weight_out);
+/* DTStatsAggregator (K2): nodes are given as segments of `entries` (packed row | weight<<32 |
+ * label<<40); subsets[n_nodes*f_sub]; hist_out[n_nodes][f_sub][max_nb][C] uint32 where max_nb =
+ * max over features of num_bins_all. */
+int emrf_histogram(emrf_ctx_t* ctx, const uint8_t* bins_rm, int64_t n_rows, int32_t n_features,
+                   const uint64_t* entries, const int64_t* node_seg_off, int32_t n_nodes, const int32_t* subsets,
+                   int32_t f_sub, const int32_t* num_bins_all, int32_t n_classes, uint32_t* hist_out);
+/* binsToBestSplit (K3) on histograms laid out as emrf_histogram writes them.  Outputs per node:
+ * k (index into the subset, -1 = no feature with splits), split index, gain, valid flag,
+ * left[C] and total[C] class counts. */
+int emrf_best_splits(emrf_ctx_t* ctx, const uint32_t* hist, int32_t n_nodes, const int32_t* subsets, int32_t f_sub,
+                     const int32_t* num_bins_all, int32_t n_features, int32_t n_classes, int32_t impurity,
+                     int32_t min_instances_per_node, double min_info_gain, int32_t* k_out, int32_t* split_out,
+                     double* gain_out, int32_t* valid_out, uint32_t* left_out, uint32_t* total_out);
+/* LearningNode.predictImpl one level (K4): stable partition of each node's entries by
+ * bin(feature) <= split_bin.  entries_out has the same segments; n_left_out[n_nodes]. */
+int emrf_update_partition(emrf_ctx_t* ctx, const uint8_t* bins_cm, int64_t n_rows, int32_t n_features,
+                          const uint64_t* entries, const int64_t* node_seg_off, int32_t n_nodes,
+                          const int32_t* split_feature, const int32_t* split_bin, uint64_t* entries_out,
+                          int64_t* n_left_out);
+
+/* ---- host-logic probes (no GPU needed): the sequential, parity-critical pieces of
+ * RandomForest.selectNodesToSplit that run on the host inside emrf_fit ------------------------- */
+int64_t emrf_host_java_random_next_long(int64_t seed, int32_t nth);           /* java.util.Random */
+double emrf_host_xorshift_next_double(int64_t seed, int32_t nth);             /* XORShiftRandom (2.4 hashSeed) */
+int32_t emrf_host_reservoir_sample(int32_t n_items, int32_t k, int64_t seed, int32_t* out); /* SamplingUtils */
+int32_t emrf_host_group_tree_order(const int32_t* trees_first_seen, int32_t n, int32_t* out); /* Scala map order */
+int32_t emrf_host_num_features_per_node(const emrf_params_t* params, int32_t n_features);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EMRF_H_ */

@@ -1,0 +1,160 @@
+"""End-to-end GPU parity through the reference-facing API (RandomForestClassifier.fit / Model.transform)
+against the CPU oracle: scheduler trace, tree structure, thresholds, class counts and predicted labels
+bit-exact; gains/impurities/probabilities bit-exact for gini (tolerance 1e-6 relative for entropy)."""
+import numpy as np
+import pytest
+
+from euromillioner_b200 import synth
+from euromillioner_b200.classifier import Dataset, RandomForestClassificationModel, RandomForestClassifier
+
+pytestmark = pytest.mark.gpu
+
+
+def _fit_both(ctx, oracle, X, y, parts, n_classes, **kw):
+    impurity = kw.pop("impurity", "gini")
+    subset = kw.pop("feature_subset", "auto")
+    rf = RandomForestClassifier(ctx).setNumClasses(n_classes).setImpurity(impurity).setFeatureSubsetStrategy(subset)
+    for k, v in kw.items():
+        getattr(rf, "set" + k[0].upper() + k[1:])(v)
+    model = rf.fit(Dataset(X, y, num_partitions=parts))
+    po = oracle.make_params(num_trees=rf.numTrees, max_depth=rf.maxDepth, max_bins=rf.maxBins, num_classes=n_classes,
+                            seed=rf.seed, impurity=impurity, feature_subset=subset, subsampling_rate=rf.subsamplingRate,
+                            min_instances_per_node=rf.minInstancesPerNode, min_info_gain=rf.minInfoGain,
+                            max_memory_mb=rf.maxMemoryInMB)
+    ofo = oracle.fit(po, X, y, oracle.partition_offsets(len(X), parts))
+    return model, ofo
+
+
+def _assert_same_forest(model, ofo, exact=True):
+    gs, tr = model.trace()
+    assert np.array_equal(gs, ofo.group_sizes())
+    assert np.array_equal(tr, ofo.trace())
+    e, o = model.export(), ofo.export()
+    for k in ("tree_off", "node_id", "left", "right", "feature", "prediction", "stats", "threshold"):
+        assert np.array_equal(e[k], o[k]), k
+    for k in ("gain", "impurity"):
+        if exact:
+            assert np.array_equal(e[k], o[k]), k
+        else:
+            assert np.allclose(e[k], o[k], rtol=1e-6, atol=1e-12), k
+    assert model.ctx_timings["gain_mismatches"] == 0 if hasattr(model, "ctx_timings") else True
+
+
+def test_cfg1_draw_history_ball1(ctx, oracle):
+    """BASELINE.json configs[0]: 20 trees, depth 6, maxBins 32, 1 500 draws, 10-draw lags, ball 1."""
+    X, y, C = synth.draw_history()
+    model, ofo = _fit_both(ctx, oracle, X, y, 8, C, numTrees=20, maxDepth=6)
+    _assert_same_forest(model, ofo)
+    assert ctx.timings()["gain_mismatches"] == 0
+    ds = model.transform(Dataset(X))
+    raw, prob, pred = ofo.predict(X)
+    assert np.array_equal(ds.columns["prediction"], pred)
+    assert np.array_equal(ds.columns["rawPrediction"], raw)
+    assert np.array_equal(ds.columns["probability"], prob)
+
+
+@pytest.mark.parametrize("ball", [4, 6])
+def test_cfg4_other_balls(ctx, oracle, ball):
+    X, y, C = synth.draw_history(ball=ball)
+    model, ofo = _fit_both(ctx, oracle, X, y, 8, C, numTrees=12, maxDepth=6, seed=ball)
+    _assert_same_forest(model, ofo)
+
+
+@pytest.mark.parametrize("n,F,T,D,parts,kw", [
+    (60000, 64, 12, 8, 64, {}),                                   # cfg2-shaped, scaled down
+    (30000, 32, 6, 10, 16, {"feature_subset": "all"}),            # forest independent of group order
+    (30000, 32, 1, 6, 16, {}),                                    # single tree: no bagging, all features
+    (20000, 24, 8, 7, 5, {"subsamplingRate": 0.7, "minInstancesPerNode": 25}),
+    (20000, 24, 8, 7, 5, {"minInfoGain": 0.002, "feature_subset": "log2"}),
+    (40000, 64, 30, 7, 32, {"maxMemoryInMB": 2}),                 # tiny groups: the memory check redraws the RNG
+    (3000, 10, 40, 12, 3, {"feature_subset": "onethird"}),        # deep, small: pure children, many leaves
+    (25000, 16, 5, 6, 4, {"maxBins": 100, "feature_subset": "0.5"}),
+])
+def test_flat_fits_match_oracle(ctx, oracle, n, F, T, D, parts, kw):
+    X, y = synth.flat(n, F, 50)
+    model, ofo = _fit_both(ctx, oracle, X, y, parts, 50, numTrees=T, maxDepth=D, **kw)
+    _assert_same_forest(model, ofo)
+    assert ctx.timings()["gain_mismatches"] == 0
+    Xt, _ = synth.flat(5000, F, 50, seed=7)
+    ds = model.transform(Dataset(Xt))
+    raw, prob, pred = ofo.predict(Xt)
+    assert np.array_equal(ds.columns["prediction"], pred)
+    assert np.array_equal(ds.columns["rawPrediction"], raw)
+    assert np.array_equal(ds.columns["probability"], prob)
+
+
+def test_entropy_fit_within_tolerance(ctx, oracle):
+    X, y = synth.flat(20000, 16, 10)
+    y = y % 10
+    model, ofo = _fit_both(ctx, oracle, X, y, 8, 10, numTrees=6, maxDepth=5, impurity="entropy")
+    _assert_same_forest(model, ofo, exact=False)
+
+
+def test_few_rows_and_inferred_classes(ctx, oracle):
+    X, y = synth.flat(20, 5, 3)                  # rows < maxBins: numBins = min(maxBins, N)
+    rf = RandomForestClassifier(ctx).setNumTrees(3).setMaxDepth(4)
+    model = rf.fit(Dataset(X, y, num_partitions=2))
+    assert model.numClasses == int(y.max()) + 1
+    po = oracle.make_params(num_trees=3, max_depth=4, num_classes=model.numClasses)
+    _assert_same_forest(model, oracle.fit(po, X, y, oracle.partition_offsets(20, 2)))
+
+
+def test_invalid_inputs_raise_like_spark(ctx):
+    X, y = synth.flat(100, 5, 3)
+    with pytest.raises(ValueError, match="invalid label"):
+        RandomForestClassifier(ctx).fit(Dataset(X, y + 0.5))
+    with pytest.raises(ValueError, match="invalid label"):
+        RandomForestClassifier(ctx).setNumClasses(2).fit(Dataset(X, y))
+    y2 = y.copy()
+    y2[0] = 150
+    with pytest.raises(ValueError, match="100"):
+        RandomForestClassifier(ctx).fit(Dataset(X, y2))
+
+
+def test_device_resident_inputs_and_model_roundtrip(ctx, oracle):
+    """fit() on features already in HBM gives the same forest; export → import → same predictions."""
+    import ctypes as C
+    from euromillioner_b200 import _lib
+    L = _lib.lib()
+    X, y = synth.flat(30000, 32, 50)
+    dX, dy = C.c_void_p(), C.c_void_p()
+    _lib.check(L.emrf_dev_alloc(ctx.h, X.nbytes, C.byref(dX)))
+    _lib.check(L.emrf_dev_alloc(ctx.h, y.nbytes, C.byref(dy)))
+    _lib.check(L.emrf_memcpy_h2d(ctx.h, dX, X.ctypes.data, X.nbytes))
+    _lib.check(L.emrf_memcpy_h2d(ctx.h, dy, y.ctypes.data, y.nbytes))
+    rf = RandomForestClassifier(ctx).setNumTrees(5).setMaxDepth(6).setNumClasses(50)
+    m_dev = rf.fit(Dataset(dX.value, dy.value, num_partitions=8, n_rows=30000, n_features=32))
+    m_host = rf.fit(Dataset(X, y, num_partitions=8))
+    for k, v in m_host.export().items():
+        assert np.array_equal(v, m_dev.export()[k]), k
+    _lib.check(L.emrf_dev_free(ctx.h, dX))
+    _lib.check(L.emrf_dev_free(ctx.h, dy))
+    m2 = RandomForestClassificationModel.from_arrays(m_host.export(), 32, ctx)
+    a = m_host.transform(Dataset(X[:2000])).columns
+    b = m2.transform(Dataset(X[:2000])).columns
+    for k in ("prediction", "rawPrediction", "probability"):
+        assert np.array_equal(a[k], b[k])
+    imp = m_host.featureImportances
+    assert imp.shape == (32,) and abs(imp.sum() - 1.0) < 1e-12 and imp[0] > imp[10] and imp[3] > imp[10]
+    assert m_host.toDebugString.startswith("RandomForestClassificationModel with 5 trees")
+
+
+def test_fit_is_deterministic_and_counts_are_conserved(ctx):
+    """Size-independent properties at a larger size than the oracle is run on."""
+    X, y = synth.flat(300000, 64, 50)
+    rf = RandomForestClassifier(ctx).setNumTrees(10).setMaxDepth(8).setNumClasses(50)
+    m1 = rf.fit(Dataset(X, y, num_partitions=256))
+    m2 = rf.fit(Dataset(X, y, num_partitions=256))
+    e1, e2 = m1.export(), m2.export()
+    for k in e1:
+        assert np.array_equal(e1[k], e2[k]), k
+    # children's class counts sum to the parent's, for every internal node of every tree
+    for t in range(m1.numTrees):
+        a, b = e1["tree_off"][t], e1["tree_off"][t + 1]
+        L_, R_, st = e1["left"][a:b], e1["right"][a:b], e1["stats"][a:b]
+        internal = np.where(L_ >= 0)[0]
+        # pruned leaves keep the parent's counts, so conservation holds over the exported tree
+        assert np.array_equal(st[internal], st[L_[internal]] + st[R_[internal]])
+    # root count = sum of Poisson weights ~ N
+    roots = e1["stats"][e1["tree_off"][:-1]].sum(axis=1)
+    assert np.all(np.abs(roots - 300000) < 5000)

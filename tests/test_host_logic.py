@@ -1,0 +1,112 @@
+"""CPU-side checks of the product: libemrf.so loads, exports every symbol include/emrf.h declares,
+its host-side scheduler primitives (java.util.Random, XORShiftRandom, reservoir sampling, Scala
+map orders, findSplits row sampler) agree with the oracle, and it fails loudly without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import HAS_GPU, ROOT
+
+
+def _lib():
+    from euromillioner_b200 import _lib
+    return _lib.lib()
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "emrf.h")).read()
+    names = sorted(set(re.findall(r"\b(emrf_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(names) >= 30
+    L = _lib()
+    missing = [n for n in names if not hasattr(L, n)]
+    assert not missing, missing
+    assert b"sm_100a" in L.emrf_version()
+
+
+@pytest.mark.skipif(HAS_GPU, reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback_without_gpu():
+    from euromillioner_b200._lib import EmrfError
+    from euromillioner_b200.classifier import Context
+    with pytest.raises(EmrfError, match="no CPU fallback"):
+        Context(0)
+
+
+def test_java_random_and_xorshift_match_oracle(oracle):
+    L, O = _lib(), oracle.lib()
+    for seed in (0, 1, 42, 207336481, -77, 2**40 + 3):
+        want = np.zeros(5, np.int64)
+        O.orc_java_random_longs(C.c_int64(seed), 5, want.ctypes.data_as(C.POINTER(C.c_int64)))
+        assert [L.emrf_host_java_random_next_long(seed, i) for i in range(5)] == list(want)
+        wd = np.zeros(5)
+        O.orc_xorshift_doubles(C.c_int64(seed), 5, wd.ctypes.data_as(C.POINTER(C.c_double)))
+        assert [L.emrf_host_xorshift_next_double(seed, i) for i in range(5)] == list(wd)
+    assert L.emrf_host_java_random_next_long(42, 0) == -5025562857975149833
+    assert L.emrf_host_xorshift_next_double(207336481, 0) == 0.26236745326918753
+
+
+@pytest.mark.parametrize("n_items,k", [(70, 9), (64, 8), (128, 12), (5, 9), (9, 9), (1000, 32)])
+def test_reservoir_sample_matches_oracle(oracle, n_items, k):
+    L, O = _lib(), oracle.lib()
+    for seed in (1, -5025562857975149833, 987654321987):
+        a, b = np.zeros(k, np.int32), np.zeros(k, np.int32)
+        na = L.emrf_host_reservoir_sample(n_items, k, seed, a.ctypes.data)
+        nb = O.orc_reservoir(n_items, k, C.c_int64(seed), b.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert na == nb == min(n_items, k)
+        assert list(a[:na]) == list(b[:nb])
+
+
+def test_group_tree_order_matches_oracle_and_known_answers(oracle):
+    L, O = _lib(), oracle.lib()
+    rng = np.random.default_rng(7)
+    cases = [np.arange(n, dtype=np.int32) for n in (1, 3, 4, 5, 9, 13, 14, 20, 100, 500)]
+    cases += [np.arange(n - 1, -1, -1, dtype=np.int32) for n in (4, 20, 100, 500)]
+    cases += [rng.permutation(500)[:n].astype(np.int32) for n in (2, 4, 7, 30, 200)]
+    for k in cases:
+        a, b = np.zeros(len(k), np.int32), np.zeros(len(k), np.int32)
+        assert L.emrf_host_group_tree_order(k.ctypes.data, len(k), a.ctypes.data) == len(k)
+        O.orc_group_tree_order(k.ctypes.data_as(C.POINTER(C.c_int32)), len(k), b.ctypes.data_as(C.POINTER(C.c_int32)))
+        assert list(a) == list(b)
+    k = np.arange(9, dtype=np.int32)
+    a = np.zeros(9, np.int32)
+    L.emrf_host_group_tree_order(k.ctypes.data, 9, a.ctypes.data)
+    assert list(a) == [0, 5, 1, 6, 2, 7, 3, 8, 4]
+
+
+@pytest.mark.parametrize("n_rows,n_parts,max_bins", [(1490, 8, 32), (25000, 16, 32), (200000, 64, 32), (30000, 7, 128)])
+def test_find_splits_row_sampler_matches_oracle(oracle, n_rows, n_parts, max_bins):
+    from euromillioner_b200 import stages
+    from euromillioner_b200._lib import EmrfParams
+    po = oracle.partition_offsets(n_rows, n_parts)
+    for seed in (207336481, 5):
+        pe = oracle.make_params(num_trees=10, max_bins=max_bins, num_classes=2, seed=seed, cls=EmrfParams)
+        po_ = oracle.make_params(num_trees=10, max_bins=max_bins, num_classes=2, seed=seed)
+        got = stages.find_splits_sample_rows(pe, n_rows, po)
+        want = oracle.find_splits_sample_rows(po_, n_rows, po)
+        assert np.array_equal(got, want)
+        if n_rows <= 10000:
+            assert len(got) == n_rows
+
+
+@pytest.mark.parametrize("F,kind,want", [(70, "auto", 9), (64, "auto", 8), (128, "sqrt", 12), (128, "log2", 7),
+                                         (128, "onethird", 43), (64, "all", 64), (64, "10", 10), (64, "0.5", 32)])
+def test_num_features_per_node(oracle, F, kind, want):
+    from euromillioner_b200._lib import EmrfParams
+    pe = oracle.make_params(num_trees=5, num_classes=2, feature_subset=kind, cls=EmrfParams)
+    po = oracle.make_params(num_trees=5, num_classes=2, feature_subset=kind)
+    assert _lib().emrf_host_num_features_per_node(C.byref(pe), F) == want
+    assert oracle.lib().orc_num_features_per_node(C.byref(po), F) == want
+
+
+def test_estimator_setters_mirror_spark_requires():
+    from euromillioner_b200.classifier import RandomForestClassifier
+    rf = RandomForestClassifier()
+    assert (rf.numTrees, rf.maxDepth, rf.maxBins, rf.seed, rf.featureSubsetStrategy) == (20, 5, 32, 207336481, "auto")
+    assert rf.setNumTrees(100).setMaxDepth(10).setMaxBins(32).setSeed(1) is rf
+    for bad in (lambda: rf.setNumTrees(0), lambda: rf.setMaxDepth(31), lambda: rf.setMaxBins(1),
+                lambda: rf.setImpurity("variance"), lambda: rf.setSubsamplingRate(0.0),
+                lambda: rf.setFeatureSubsetStrategy("half")):
+        with pytest.raises(ValueError):
+            bad()

@@ -30,7 +30,8 @@ class EmrfTimings(C.Structure):
         "total_ms", "h2d_ms", "find_splits_ms", "bin_ms", "bag_ms", "find_best_splits_ms",
         "hist_kernel_ms", "partition_ms", "host_scheduler_ms")] + [(n, C.c_int64) for n in (
             "hist_launches", "kernel_launches", "hist_alg_bytes", "hist_units", "num_groups",
-            "total_nodes_split", "gain_mismatches")]
+            "total_nodes_split", "gain_mismatches", "h2d_bytes", "d2h_bytes")] + [
+        (n, C.c_double) for n in ("host_select_ms", "host_update_ms", "host_export_ms")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

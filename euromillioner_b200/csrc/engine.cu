@@ -328,6 +328,7 @@ static int stage_input(emrf_ctx* c, const void* src_hd, size_t bytes, DevBuf& ow
   }
   CU(owned.alloc(bytes));
   CU(cudaMemcpyAsync(owned.p, src_hd, bytes, cudaMemcpyHostToDevice, c->stream));
+  c->tm.h2d_bytes += (int64_t)bytes;
   *dev_out = owned.p;
   if (copied) *copied = true;
   return EMRF_OK;
@@ -375,6 +376,8 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
                                                              P.find_splits_policy, TS, d_thr.as<double>(), d_ns.as<int>());
       c->tm.kernel_launches += 2;
       CU(cudaGetLastError());
+      c->tm.d2h_bytes += (int64_t)F * TS * 8 + (int64_t)F * 4;
+      c->tm.h2d_bytes += sampled ? (int64_t)n_s * 8 : 0;
       CU(cudaMemcpyAsync(h_thr.data(), d_thr.p, (size_t)F * TS * 8, cudaMemcpyDeviceToHost, c->stream));
       CU(cudaMemcpyAsync(h_ns.data(), d_ns.p, (size_t)F * 4, cudaMemcpyDeviceToHost, c->stream));
       CU(cudaStreamSynchronize(c->stream));  // d_rows/d_S/rows die here
@@ -416,7 +419,8 @@ static int run_bag(emrf_ctx* c, const emrf_params_t& P, int64_t N, const int64_t
   if (T > 1) {
     const double mean = P.subsampling_rate;
     const double p_exp = std::exp(-mean);
-    kern::bag_poisson_kernel<<<(n_parts + 31) / 32, 32, 0, c->stream>>>(P.seed, d_off.as<int64_t>(), n_parts, T, mean, p_exp,
+    CU(cudaFuncSetAttribute(kern::bag_poisson_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kern::kBagSmemBytes));
+    kern::bag_poisson_kernel<<<(n_parts + 31) / 32, 32, kern::kBagSmemBytes, c->stream>>>(P.seed, d_off.as<int64_t>(), n_parts, T, mean, p_exp,
                                                                          d_w, d_max.as<int>());
   } else if (P.subsampling_rate == 1.0) {
     CU(cudaMemsetAsync(d_w, 1, (size_t)N * T, c->stream));
@@ -449,7 +453,9 @@ struct emrf_forest {
   int num_trees = 0, num_classes = 0, num_features = 0;
   std::vector<int64_t> tree_off;
   std::vector<FlatNode> nodes;
-  std::vector<double> stats;  // nodes*C
+  std::vector<double> stats;  // nodes*C (filled lazily from counts for forests made by emrf_fit)
+  std::vector<uint32_t> counts;  // nodes*C integer class counts as trained
+  std::mutex stats_mu;
   std::vector<int32_t> group_sizes, trace;
   int f_sub = 0;
   // device copy for predict (built once)
@@ -479,40 +485,65 @@ static int first_max(const uint32_t* a, int C) {
   for (int c = 1; c < C; c++) if (a[c] > a[mi]) mi = c;
   return mi;
 }
-// LearningNode.toNode(prune = true) (ml/tree/Node.scala)
-static int64_t export_node(const HTree& t, int ni, int C, emrf_forest& fo) {
+// LearningNode.toNode(prune = true) (ml/tree/Node.scala), two passes per tree so that trees can be
+// exported in parallel into pre-sized arrays:
+//   pass A (post-order): does the node come out as a leaf (own leaf, or both children leaves with
+//                        the same prediction), its prediction, and the size of its exported subtree
+//   pass B (pre-order):  fill the flat arrays
+struct ExportInfo { int32_t size; int32_t pred; bool leaf; };
+static void export_pass_a(const HTree& t, int ni, int C, std::vector<ExportInfo>& info) {
   const HNode& n = t.pool[ni];
-  const int64_t base = fo.tree_off.back();
-  const int64_t me = (int64_t)fo.nodes.size();
-  fo.nodes.emplace_back();
-  fo.stats.resize(fo.nodes.size() * (size_t)C);
-  const uint32_t* cnt = &t.counts[n.counts_at];
-  auto write_leaf = [&](double pred, double imp) {
-    FlatNode& f = fo.nodes[me];
-    f.id = n.id; f.left = -1; f.right = -1; f.feature = -1;
-    f.threshold = 0.0; f.gain = 0.0; f.impurity = imp; f.prediction = pred;
-    for (int c = 0; c < C; c++) fo.stats[me * C + c] = (double)cnt[c];
-  };
+  ExportInfo& e = info[ni];
   if (n.left >= 0) {
-    const int64_t l = export_node(t, n.left, C, fo);
-    const int64_t r = export_node(t, n.right, C, fo);
-    const bool both_leaves = fo.nodes[l].left < 0 && fo.nodes[r].left < 0;
-    if (both_leaves && fo.nodes[l].prediction == fo.nodes[r].prediction) {
-      const double pred = fo.nodes[l].prediction;
-      fo.nodes.resize(me + 1);
-      fo.stats.resize(fo.nodes.size() * (size_t)C);
-      write_leaf(pred, n.impurity);
-    } else {
-      FlatNode& f = fo.nodes[me];
-      f.id = n.id; f.left = (int32_t)(l - base); f.right = (int32_t)(r - base);
-      f.feature = n.feature; f.threshold = n.threshold; f.gain = n.gain; f.impurity = n.impurity;
-      f.prediction = (double)first_max(cnt, C);
-      for (int c = 0; c < C; c++) fo.stats[me * C + c] = (double)cnt[c];
-    }
+    export_pass_a(t, n.left, C, info);
+    export_pass_a(t, n.right, C, info);
+    const ExportInfo &l = info[n.left], &r = info[n.right];
+    if (l.leaf && r.leaf && l.pred == r.pred) { e.leaf = true; e.pred = l.pred; e.size = 1; }
+    else { e.leaf = false; e.pred = first_max(&t.counts[n.counts_at], C); e.size = 1 + l.size + r.size; }
   } else {
-    write_leaf((double)first_max(cnt, C), n.valid ? n.impurity : -1.0);
+    e.leaf = true; e.pred = first_max(&t.counts[n.counts_at], C); e.size = 1;
   }
-  return me;
+}
+static void export_pass_b(const HTree& t, int ni, int C, const std::vector<ExportInfo>& info, int64_t base, int32_t pos,
+                          emrf_forest& fo) {
+  const HNode& n = t.pool[ni];
+  const ExportInfo& e = info[ni];
+  FlatNode& f = fo.nodes[base + pos];
+  memcpy(&fo.counts[(size_t)(base + pos) * C], &t.counts[n.counts_at], (size_t)C * 4);
+  f.id = n.id;
+  f.prediction = (double)e.pred;
+  if (e.leaf) {
+    f.left = -1; f.right = -1; f.feature = -1; f.threshold = 0.0; f.gain = 0.0;
+    // own leaf with invalid stats → -1.0 (old mllib behaviour kept by Spark); merged leaf → parent's impurity
+    f.impurity = (n.left < 0 && !n.valid) ? -1.0 : n.impurity;
+  } else {
+    const int32_t lpos = pos + 1, rpos = pos + 1 + info[n.left].size;
+    f.left = lpos; f.right = rpos; f.feature = n.feature; f.threshold = n.threshold; f.gain = n.gain;
+    f.impurity = n.impurity;
+    export_pass_b(t, n.left, C, info, base, lpos, fo);
+    export_pass_b(t, n.right, C, info, base, rpos, fo);
+  }
+}
+static void export_forest(const std::vector<HTree>& trees, int C, emrf_forest& fo) {
+  const int T = (int)trees.size();
+  std::vector<std::vector<ExportInfo>> info(T);
+#pragma omp parallel for schedule(dynamic)
+  for (int t = 0; t < T; t++) {
+    info[t].resize(trees[t].pool.size());
+    export_pass_a(trees[t], 0, C, info[t]);
+  }
+  fo.tree_off.assign(T + 1, 0);
+  for (int t = 0; t < T; t++) fo.tree_off[t + 1] = fo.tree_off[t] + info[t][0].size;
+  fo.nodes.resize((size_t)fo.tree_off[T]);
+  fo.counts.resize((size_t)fo.tree_off[T] * C);
+#pragma omp parallel for schedule(dynamic)
+  for (int t = 0; t < T; t++) export_pass_b(trees[t], 0, C, info[t], fo.tree_off[t], 0, fo);
+}
+static void ensure_double_stats(emrf_forest* f) {
+  std::lock_guard<std::mutex> lk(f->stats_mu);
+  if (!f->stats.empty() || f->counts.empty()) return;
+  f->stats.resize(f->counts.size());
+  for (size_t i = 0; i < f->counts.size(); i++) f->stats[i] = (double)f->counts[i];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -668,38 +699,73 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   std::vector<GroupEntry> group;
   std::vector<int32_t> group_feat;
   std::vector<int> trees_seen;
-  std::map<int, std::vector<int>> nodes_for_tree;
-  std::vector<int32_t> subset(f_sub);
+  std::vector<std::vector<int>> nodes_for_tree;   // per tree of the group (slot = first-seen order)
+  std::vector<int> tree_slot(T, -1);
+  std::vector<int32_t> batch_feat;
+  std::vector<int64_t> batch_bins, batch_seed;
+  std::vector<uint64_t> batch_state;
+  // smallest aggregate a node can need: the f_sub features with the fewest bins
+  int64_t min_node_mem;
+  {
+    std::vector<int> nbs(num_bins.begin(), num_bins.end());
+    std::sort(nbs.begin(), nbs.end());
+    int64_t sb = 0;
+    for (int k = 0; k < f_sub; k++) sb += nbs[k];
+    min_node_mem = std::max<int64_t>((int64_t)C * sb * 8, 1);
+  }
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_ev, part_ev;
-  double host_ms = 0.0;
+  double host_ms = 0.0, host_sel = 0.0, host_upd = 0.0;
+  static const bool verify_gains = getenv("EMRF_VERIFY_GAINS") != nullptr;
 
   while (!stack.empty()) {
     double t_host0 = now_ms();
-    // ---- selectNodesToSplit
+    // ---- selectNodesToSplit.  The driver RNG hands each popped node one nextLong() (drawn BEFORE
+    // the memory check, so the node that does not fit consumes a draw too); the reservoir sampling
+    // a seed implies is independent per node, so a batch of candidate nodes is drawn sequentially
+    // (cheap LCG steps, state saved after every draw), sampled in parallel, and then admitted
+    // sequentially exactly as Spark does; the RNG is rewound to just after the rejected node's draw.
     group.clear(); group_feat.clear(); trees_seen.clear(); nodes_for_tree.clear();
     int64_t mem = 0;
-    while (!stack.empty()) {
-      const auto top = stack.back();
-      int64_t total_bins;
+    bool group_done = false;
+    while (!stack.empty() && !group_done) {
+      const int64_t room = (max_mem - mem) / min_node_mem + 1;
+      const int K = (int)std::min<int64_t>((int64_t)stack.size(), std::max<int64_t>(room, 1));
+      batch_feat.resize((size_t)K * f_sub);
+      batch_bins.resize(K);
       if (subsampling) {
-        int len = 0;
-        hl::reservoir_features(F, f_sub, rng.next_long(), subset.data(), &len);
-        total_bins = 0;
-        for (int k = 0; k < f_sub; k++) total_bins += num_bins[subset[k]];
+        batch_seed.resize(K);
+        batch_state.resize(K);
+        for (int j = 0; j < K; j++) { batch_seed[j] = rng.next_long(); batch_state[j] = rng.state; }
+#pragma omp parallel for schedule(static) if (K >= 64)
+        for (int j = 0; j < K; j++) {
+          int len = 0;
+          int32_t* sub = &batch_feat[(size_t)j * f_sub];
+          hl::reservoir_features(F, f_sub, batch_seed[j], sub, &len);
+          int64_t tb = 0;
+          for (int k = 0; k < f_sub; k++) tb += num_bins[sub[k]];
+          batch_bins[j] = tb;
+        }
       } else {
-        for (int k = 0; k < F; k++) subset[k] = k;
-        total_bins = all_feat_bins;
+        for (int j = 0; j < K; j++) {
+          for (int k = 0; k < F; k++) batch_feat[(size_t)j * f_sub + k] = k;
+          batch_bins[j] = all_feat_bins;
+        }
       }
-      const int64_t node_mem = (int64_t)C * total_bins * 8;
-      if (mem + node_mem <= max_mem || mem == 0) {
-        stack.pop_back();
-        if (!nodes_for_tree.count(top.first)) trees_seen.push_back(top.first);
-        nodes_for_tree[top.first].push_back((int)group.size());
-        group.push_back({top.first, top.second, (int)group_feat.size()});
-        group_feat.insert(group_feat.end(), subset.begin(), subset.end());
-        mem += node_mem;
-      } else {
-        break;
+      for (int j = 0; j < K; j++) {
+        const auto top = stack.back();
+        const int64_t node_mem = (int64_t)C * batch_bins[j] * 8;
+        if (mem + node_mem <= max_mem || mem == 0) {
+          stack.pop_back();
+          if (tree_slot[top.first] < 0) { tree_slot[top.first] = (int)trees_seen.size(); trees_seen.push_back(top.first); nodes_for_tree.emplace_back(); }
+          nodes_for_tree[tree_slot[top.first]].push_back((int)group.size());
+          group.push_back({top.first, top.second, (int)group_feat.size()});
+          group_feat.insert(group_feat.end(), batch_feat.begin() + (size_t)j * f_sub, batch_feat.begin() + (size_t)(j + 1) * f_sub);
+          mem += node_mem;
+        } else {
+          if (subsampling) rng.state = batch_state[j];  // draws after the rejected node's are undone
+          group_done = true;
+          break;
+        }
       }
     }
     const int n_nodes = (int)group.size();
@@ -755,9 +821,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(c->h_results.ensure(res_bytes));
     CU(c->d_tickets.ensure(n_rec * 4));
     CU(c->d_ghist.ensure((size_t)std::max(n_slots, 1) * slot_words * 4));
-    host_ms += now_ms() - t_host0;
+    { const double d_ = now_ms() - t_host0; host_ms += d_; host_sel += d_; }
 
     CU(cudaMemcpyAsync(c->d_group.p, c->h_group.p, group_bytes, cudaMemcpyHostToDevice, st));
+    tm.h2d_bytes += (int64_t)group_bytes;
+    tm.d2h_bytes += (int64_t)res_bytes;
     CU(cudaMemsetAsync(c->d_tickets.p, 0, n_rec * 4, st));
     if (c->world > 1) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
     if (n_slots) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots * slot_words * 4, st));
@@ -808,7 +876,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const std::vector<int> order = hl::group_tree_visit_order(trees_seen);
     std::vector<uint32_t> rightc(C);
     for (int t : order) {
-      for (int gi : nodes_for_tree[t]) {
+      for (int gi : nodes_for_tree[tree_slot[t]]) {
         const GroupEntry& g = group[gi];
         HTree& tr = trees[t];
         // combine feature chunks: first maximum in subset order
@@ -823,25 +891,30 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         const uint32_t* leftc = res_left + rec * C;
         const int id = tr.pool[g.pool].id;
         const int level = 31 - __builtin_clz((unsigned)id);
-        // node stats: parent calculator = class totals; impurity recomputed on the host
+        // node stats: parent calculator = class totals; impurities and gain come from the scan
+        // kernel (bit-exact IEEE, Spark's operation order); EMRF_VERIFY_GAINS=1 recomputes them here.
         if (!tr.pool[g.pool].has_stats) {
           tr.pool[g.pool].counts_at = tr.counts.size();
           tr.counts.insert(tr.counts.end(), totc, totc + C);
           tr.pool[g.pool].has_stats = true;
         }
-        const double pimp = hl::impurity_of(P.impurity, totc, C);
+        const double pimp = res[rec].impurity;
         double gain = kern::kInvalidGain, limp = 0.0, rimp = 0.0;
         bool valid = false;
         if (best >= 0 && res[rec].valid) {
-          uint64_t lc = 0, rc = 0;
-          for (int cc = 0; cc < C; cc++) { rightc[cc] = totc[cc] - leftc[cc]; lc += leftc[cc]; rc += rightc[cc]; }
-          limp = hl::impurity_of(P.impurity, leftc, C);
-          rimp = hl::impurity_of(P.impurity, rightc.data(), C);
-          const double tc = (double)(lc + rc);
-          const double lw = (double)lc / tc, rw = (double)rc / tc;
-          gain = pimp - lw * limp - rw * rimp;
+          for (int cc = 0; cc < C; cc++) rightc[cc] = totc[cc] - leftc[cc];
+          gain = res[rec].gain; limp = res[rec].left_impurity; rimp = res[rec].right_impurity;
           valid = true;
-          if (gain != res[rec].gain) tm.gain_mismatches++;
+          if (verify_gains) {
+            uint64_t lc = 0, rc = 0;
+            for (int cc = 0; cc < C; cc++) { lc += leftc[cc]; rc += rightc[cc]; }
+            const double hl_ = hl::impurity_of(P.impurity, leftc, C), hr_ = hl::impurity_of(P.impurity, rightc.data(), C);
+            const double hp_ = hl::impurity_of(P.impurity, totc, C);
+            const double tc = (double)(lc + rc);
+            const double lw = (double)lc / tc, rw = (double)rc / tc;
+            const double hg = hp_ - lw * hl_ - rw * hr_;
+            if (hg != gain || hl_ != limp || hr_ != rimp || hp_ != pimp) tm.gain_mismatches++;
+          }
         }
         const bool is_leaf = (gain <= 0) || (level == P.max_depth);
         {
@@ -879,7 +952,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         }
       }
     }
-    host_ms += now_ms() - t_host0;
+    for (int t : trees_seen) tree_slot[t] = -1;
+    { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
 
     // ---- K4: partition the split nodes' segments, learn the children's segment sizes
     if (!splits.empty()) {
@@ -902,8 +976,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       const size_t off_nleft = align_up((size_t)ptiles * 4, 16);
       CU(c->d_part.ensure(off_nleft + (size_t)ns * 8));
       CU(c->h_part.ensure((size_t)ns * 8));
-      host_ms += now_ms() - t_host0;
+      { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
       CU(cudaMemcpyAsync(c->d_split.p, c->h_split.p, split_bytes, cudaMemcpyHostToDevice, st));
+      tm.h2d_bytes += (int64_t)split_bytes;
+      tm.d2h_bytes += (int64_t)ns * 8;
       const kern::SplitNode* dsn = (const kern::SplitNode*)c->d_split.p;
       const uint32_t* dtn = (const uint32_t*)((char*)c->d_split.p + off_ptn);
       uint32_t* d_tile_left = (uint32_t*)c->d_part.p;
@@ -936,18 +1012,14 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         l.seg_start = n.seg_start; l.seg_len = (uint32_t)nl[i]; l.buf = n.buf ^ 1u;
         r.seg_start = n.seg_start + nl[i]; r.seg_len = n.seg_len - (uint32_t)nl[i]; r.buf = n.buf ^ 1u;
       }
-      host_ms += now_ms() - t_host0;
+      { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
     }
   }
 
   // ---- topNodes.map(_.toNode(prune = true))
   double t_host0 = now_ms();
-  fo->tree_off.push_back(0);
-  for (int t = 0; t < T; t++) {
-    export_node(trees[t], 0, C, *fo);
-    fo->tree_off.push_back((int64_t)fo->nodes.size());
-  }
-  host_ms += now_ms() - t_host0;
+  export_forest(trees, C, *fo);
+  { const double d_ = now_ms() - t_host0; host_ms += d_; tm.host_export_ms = d_; }
   CU(cudaEventRecord(ev_end, st));
   CU(cudaStreamSynchronize(st));
 
@@ -961,6 +1033,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   for (auto& pr : part_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.partition_ms += ms; }
   tm.find_best_splits_ms = tm.hist_kernel_ms;
   tm.host_scheduler_ms = host_ms;
+  tm.host_select_ms = host_sel;
+  tm.host_update_ms = host_upd;
   tm.num_groups = (int64_t)fo->group_sizes.size();
   *out = fo_guard.release();
   return EMRF_OK;
@@ -993,6 +1067,7 @@ extern "C" int emrf_forest_export(const emrf_forest_t* f, int64_t* tree_off, int
                                   int32_t* feature, double* threshold, double* gain, double* impurity, double* prediction,
                                   double* stats) {
   if (!f) return fail(EMRF_ERR_ARG, "forest is NULL");
+  ensure_double_stats(const_cast<emrf_forest*>(f));
   for (size_t t = 0; t < f->tree_off.size(); t++) tree_off[t] = f->tree_off[t];
   for (size_t i = 0; i < f->nodes.size(); i++) {
     const FlatNode& n = f->nodes[i];
@@ -1041,6 +1116,7 @@ extern "C" int emrf_forest_trace(const emrf_forest_t* f, int32_t* group_sizes, i
 // nodes of gain * count; normalise per tree; sum over trees; normalise.
 extern "C" int emrf_forest_feature_importances(const emrf_forest_t* f, double* out) {
   if (!f || !out) return fail(EMRF_ERR_ARG, "NULL argument");
+  ensure_double_stats(const_cast<emrf_forest*>(f));
   const int F = f->num_features, C = f->num_classes;
   std::vector<double> total(F, 0.0), one(F);
   for (int t = 0; t < f->num_trees; t++) {
@@ -1068,6 +1144,7 @@ extern "C" int emrf_forest_feature_importances(const emrf_forest_t* f, double* o
 static int forest_to_device(emrf_ctx* c, emrf_forest* f) {
   std::lock_guard<std::mutex> lk(f->dev_mu);
   if (f->dev_device == c->device) return EMRF_OK;
+  ensure_double_stats(f);
   const int C = f->num_classes;
   const int64_t n = (int64_t)f->nodes.size();
   std::vector<kern::DevNode> dn(n);

@@ -130,35 +130,54 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
 // partition (the stream is inherently serial); state in local memory.
 // weights: row-major uint8 [N][T].  max_w: running maximum (weights above 255 are an error).
 // ---------------------------------------------------------------------------------------------
+// The recurrence's only serial chain runs through z4 (next step's v0); every other operand is at
+// least 70 steps old.  Lanes of a warp own different partitions and drift apart (a Poisson draw
+// consumes a data-dependent number of uniforms), so the 624-word states live in SHARED memory laid
+// out [word][lane]: bank = lane whatever the lane's index, i.e. conflict-free.  The chain values
+// are carried in registers and the four array operands of step n+1 are loaded before step n's
+// stores, which takes the shared-memory latency off the critical path.
 struct WellState {
-  uint32_t v[624];
+  uint32_t* v;               // &smem[lane]; word j of this lane's state is v[j * 32]
   int idx;
+  uint32_t v0, p1, p2;       // v[idx], v[idx-1], v[idx-2]
+  uint32_t m1, m2, m3;       // v[idx+70], v[idx+179], v[idx+449]
+  __device__ __forceinline__ static int wrap(int j) { return j >= 624 ? j - 624 : j; }
+  __device__ __forceinline__ static int dec(int j) { return j ? j - 1 : 623; }
+  __device__ __forceinline__ uint32_t& at(int j) { return v[j * 32]; }
   __device__ void seed(int64_t s) {
-    v[0] = (uint32_t)((uint64_t)s >> 32);
-    v[1] = (uint32_t)((uint64_t)s & 0xffffffffull);
+    uint32_t a = (uint32_t)((uint64_t)s >> 32), b = (uint32_t)((uint64_t)s & 0xffffffffull);
+    at(0) = a;
+    at(1) = b;
     for (int i = 2; i < 624; i++) {
-      const int64_t l = (int64_t)(int32_t)v[i - 2];
-      v[i] = (uint32_t)((1812433253ll * (l ^ (l >> 30)) + i) & 0xffffffffll);
+      const int64_t l = (int64_t)(int32_t)a;
+      const uint32_t nv = (uint32_t)((1812433253ll * (l ^ (l >> 30)) + i) & 0xffffffffll);
+      at(i) = nv;
+      a = b;
+      b = nv;
     }
     idx = 0;
+    v0 = at(0); p1 = at(623); p2 = at(622);
+    m1 = at(70); m2 = at(179); m3 = at(449);
   }
   __device__ __forceinline__ uint32_t next(int bits) {
     const int i = idx;
-    const int im1 = i ? i - 1 : 623;
-    const int im2 = im1 ? im1 - 1 : 623;
-    int j1 = i + 70;  if (j1 >= 624) j1 -= 624;
-    int j2 = i + 179; if (j2 >= 624) j2 -= 624;
-    int j3 = i + 449; if (j3 >= 624) j3 -= 624;
-    const uint32_t v0 = v[i], vM1 = v[j1], vM2 = v[j2], vM3 = v[j3];
-    const uint32_t z0 = (0x80000000u & v[im1]) ^ (0x7FFFFFFFu & v[im2]);
-    const uint32_t z1 = (v0 ^ (v0 << 25)) ^ (vM1 ^ (vM1 >> 27));
-    const uint32_t z2 = (vM2 >> 9) ^ (vM3 ^ (vM3 >> 1));
+    const int im1 = dec(i);
+    const int im2 = dec(im1);
+    // operands of the NEXT step (index im1): none of them is written by this step
+    const uint32_t n1 = at(wrap(im1 + 70)), n2 = at(wrap(im1 + 179)), n3 = at(wrap(im1 + 449));
+    const uint32_t np2 = at(dec(im2));
+    const uint32_t z0 = (0x80000000u & p1) ^ (0x7FFFFFFFu & p2);
+    const uint32_t z1 = (v0 ^ (v0 << 25)) ^ (m1 ^ (m1 >> 27));
+    const uint32_t z2 = (m2 >> 9) ^ (m3 ^ (m3 >> 1));
     const uint32_t z3 = z1 ^ z2;
     uint32_t z4 = z0 ^ (z1 ^ (z1 << 9)) ^ (z2 ^ (z2 << 21)) ^ (z3 ^ (z3 >> 21));
-    v[i] = z3;
-    v[im1] = z4;
-    v[im2] &= 0x80000000u;
+    const uint32_t masked = p2 & 0x80000000u;
+    at(i) = z3;
+    at(im1) = z4;
+    at(im2) = masked;
     idx = im1;
+    v0 = z4; p1 = masked; p2 = np2;
+    m1 = n1; m2 = n2; m3 = n3;
     z4 ^= (z4 << 7) & 0xe46e1700u;
     z4 ^= (z4 << 15) & 0x9b868000u;
     return z4 >> (32 - bits);
@@ -166,15 +185,18 @@ struct WellState {
   __device__ __forceinline__ double next_double() {
     const uint64_t hi = (uint64_t)next(26) << 26;
     const uint64_t lo = next(26);
-    return __dmul_rn((double)(hi | lo), 2.220446049250313e-16);  // 0x1.0p-52
+    return __dmul_rn((double)(int64_t)(hi | lo), 2.220446049250313e-16);  // 0x1.0p-52
   }
 };
+constexpr int kBagSmemBytes = 624 * 32 * 4;
 __global__ void __launch_bounds__(32) bag_poisson_kernel(int64_t seed, const int64_t* __restrict__ part_off,
                                                          int n_parts, int T, double mean, double p_exp,
                                                          uint8_t* __restrict__ weights, int* __restrict__ max_w) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
   const int part = blockIdx.x * blockDim.x + threadIdx.x;
   if (part >= n_parts) return;
   WellState ws;
+  ws.v = reinterpret_cast<uint32_t*>(smem_raw) + threadIdx.x;
   ws.seed(seed + (int64_t)part + 1);
   const double limit = __dmul_rn(1000.0, mean);
   int mx = 0;
@@ -304,6 +326,9 @@ struct GroupNode {
 };
 struct ScanResult {
   double gain;
+  double impurity;        // parent (node) impurity
+  double left_impurity;   // of the winning candidate (0 when invalid)
+  double right_impurity;
   int32_t k;      // feature index within the node's subset (-1: no feature with splits in this chunk)
   int32_t split;
   int32_t valid;
@@ -430,6 +455,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
   const double pimp = *S.pimp;
   // (c) one candidate (feature, split) per thread, Spark's operation order
   double best_gain = -INFINITY;  // below Double.MinValue: "no candidate"
+  double best_li = 0.0, best_ri = 0.0;
   int best_idx = 0x7fffffff;
   const int n_cand = kc * (B - 1);
   for (int cand = tid; cand < n_cand; cand += NT) {
@@ -439,22 +465,23 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
     uint32_t lc = 0;
     for (int c = 0; c < C; c++) lc += l[c];
     const uint32_t rc = tot_all - lc;
-    double gain;
+    double gain, li = 0.0, ri = 0.0;
     if (lc < (uint32_t)min_instances || rc < (uint32_t)min_instances) {
       gain = kInvalidGain;
     } else {
-      const double li = impurity_dev(impurity, l, nullptr, C, lc);
-      const double ri = impurity_dev(impurity, l, S.tot, C, rc);
+      li = impurity_dev(impurity, l, nullptr, C, lc);
+      ri = impurity_dev(impurity, l, S.tot, C, rc);
       const double tc = (double)tot_all;  // (leftCount + rightCount).toDouble
       const double lw = __ddiv_rn((double)lc, tc);
       const double rw = __ddiv_rn((double)rc, tc);
       gain = __dsub_rn(__dsub_rn(pimp, __dmul_rn(lw, li)), __dmul_rn(rw, ri));
       if (gain < min_info_gain) gain = kInvalidGain;
     }
-    if (gain > best_gain) { best_gain = gain; best_idx = cand; }  // first max (cand ascending per thread)
+    if (gain > best_gain) { best_gain = gain; best_idx = cand; best_li = li; best_ri = ri; }  // first max
   }
   // (d) block arg-max: greatest gain, ties → smallest candidate index (= Spark's first maximum
   // in (subset order, split order))
+  const int my_idx = best_idx;   // this thread's own best candidate (keeps best_li / best_ri)
   for (int o = 16; o; o >>= 1) {
     const double g2 = __shfl_xor_sync(0xffffffffu, best_gain, o);
     const int i2 = __shfl_xor_sync(0xffffffffu, best_idx, o);
@@ -477,11 +504,15 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
   const double g = S.red_gain[0];
   const int ix = S.red_idx[0];
   if (ix == 0x7fffffff) {
-    if (tid == 0) { res->gain = kInvalidGain; res->k = -1; res->split = 0; res->valid = 0; res->pad = 0; }
+    if (tid == 0) {
+      res->gain = kInvalidGain; res->impurity = pimp; res->left_impurity = 0.0; res->right_impurity = 0.0;
+      res->k = -1; res->split = 0; res->valid = 0; res->pad = 0;
+    }
     for (int c = tid; c < C; c += NT) { left_out[c] = 0; total_out[c] = S.tot[c]; }
   } else {
     const int k = ix / (B - 1), s = ix - k * (B - 1);
-    if (tid == 0) { res->gain = g; res->k = k0 + k; res->split = s; res->valid = (g != kInvalidGain); res->pad = 0; }
+    if (tid == 0) { res->gain = g; res->impurity = pimp; res->k = k0 + k; res->split = s; res->valid = (g != kInvalidGain); res->pad = 0; }
+    if (my_idx == ix) { res->left_impurity = best_li; res->right_impurity = best_ri; }  // the owner of the winner
     const uint32_t* l = sh + ((size_t)k * B + s) * C;
     for (int c = tid; c < C; c += NT) { left_out[c] = l[c]; total_out[c] = S.tot[c]; }
   }

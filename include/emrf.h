@@ -74,6 +74,11 @@ typedef struct {
   int64_t num_groups;
   int64_t total_nodes_split; /* nodes that went through findBestSplits */
   int64_t gain_mismatches;  /* device-vs-host recomputed gain differences (must be 0) */
+  int64_t h2d_bytes;        /* bytes copied host→device inside the fit (inputs + group descriptors) */
+  int64_t d2h_bytes;        /* bytes copied device→host inside the fit (split records, segment sizes …) */
+  double host_select_ms;    /* host_scheduler_ms split: selectNodesToSplit + descriptor staging */
+  double host_update_ms;    /*   driver-side node updates after each group */
+  double host_export_ms;    /*   LearningNode.toNode(prune) + flat export */
 } emrf_timings_t;
 
 const char* emrf_last_error(void);

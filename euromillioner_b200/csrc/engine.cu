@@ -443,6 +443,50 @@ static int run_bag(emrf_ctx* c, const emrf_params_t& P, int64_t N, const int64_t
 }
 
 // ---------------------------------------------------------------------------------------------
+// histogram kernel dispatch (template on 16 B chunks per TreePoint row)
+// ---------------------------------------------------------------------------------------------
+template <int CH>
+static cudaError_t hist_launch_t(dim3 grid, size_t smem, cudaStream_t st, const kern::HistArgs& A, bool prepare_only) {
+  if (prepare_only)
+    return cudaFuncSetAttribute(kern::hist_scan_kernel<CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  kern::hist_scan_kernel<CH><<<grid, kern::kHistThreads, smem, st>>>(A);
+  return cudaGetLastError();
+}
+static cudaError_t hist_launch(int ch, dim3 grid, size_t smem, cudaStream_t st, const kern::HistArgs& A, bool prepare_only) {
+  switch (ch) {
+    case 1: return hist_launch_t<1>(grid, smem, st, A, prepare_only);
+    case 2: return hist_launch_t<2>(grid, smem, st, A, prepare_only);
+    case 3: return hist_launch_t<3>(grid, smem, st, A, prepare_only);
+    case 4: return hist_launch_t<4>(grid, smem, st, A, prepare_only);
+    case 5: return hist_launch_t<5>(grid, smem, st, A, prepare_only);
+    case 6: return hist_launch_t<6>(grid, smem, st, A, prepare_only);
+    case 7: return hist_launch_t<7>(grid, smem, st, A, prepare_only);
+    case 8: return hist_launch_t<8>(grid, smem, st, A, prepare_only);
+    default: return hist_launch_t<0>(grid, smem, st, A, prepare_only);
+  }
+}
+// features per CTA so that the [k][B][C] uint32 histogram plus the row tiles fit in shared memory
+static int hist_geometry(emrf_ctx* c, int Fp, int f_sub, int B, int C, int* ch_out, int* k_chunk_out, int* n_chunks_out,
+                         size_t* hist_bytes_out, size_t* smem_out) {
+  const int ch = kern::hist_row_chunks(Fp);
+  const size_t tile_bytes = kern::hist_tile_bytes(ch);
+  const size_t smem_cap = std::min<size_t>(c->smem_optin, 227 * 1024);
+  const size_t per_feat = (size_t)B * C * 4;
+  const size_t fixed = 4096 + tile_bytes;
+  int k_chunk = (100 * 1024 > fixed) ? (int)((100 * 1024 - fixed) / per_feat) : 0;
+  if (k_chunk < f_sub && k_chunk < 4) k_chunk = (int)((smem_cap - fixed) / per_feat);  // big bins x classes: one CTA per SM
+  if (k_chunk < 1) return fail(EMRF_ERR_LIMIT, "one feature histogram (%d bins x %d classes) exceeds shared memory", B, C);
+  k_chunk = std::min(k_chunk, f_sub);
+  *ch_out = ch;
+  *k_chunk_out = k_chunk;
+  *n_chunks_out = (f_sub + k_chunk - 1) / k_chunk;
+  *hist_bytes_out = kern::hist_smem_bytes(k_chunk, B, C);
+  *smem_out = *hist_bytes_out + tile_bytes;
+  if (*smem_out > smem_cap) return fail(EMRF_ERR_LIMIT, "histogram tile needs %zu B of shared memory", *smem_out);
+  return EMRF_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // forest
 // ---------------------------------------------------------------------------------------------
 struct FlatNode {
@@ -660,18 +704,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   const int f_sub = hl::features_per_node(P, F);
   if (f_sub < 1 || f_sub > F) return fail(EMRF_ERR_ARG, "featureSubsetStrategy selects %d of %d features", f_sub, F);
   const bool subsampling = (f_sub != F);
-  // histogram chunking: features per CTA so that [k][B][C] uint32 fits in shared memory
-  const size_t smem_cap = std::min<size_t>(c->smem_optin, 227 * 1024);
-  const size_t per_feat = (size_t)B * C * 4;
-  size_t soft_cap = 100 * 1024;
-  int k_chunk = (int)((soft_cap - 4096) / per_feat);
-  if (k_chunk < 1) k_chunk = (int)((smem_cap - 4096) / per_feat);
-  if (k_chunk < 1) return fail(EMRF_ERR_LIMIT, "one feature histogram (%d bins x %d classes) exceeds shared memory", B, C);
-  k_chunk = std::min(k_chunk, f_sub);
-  const int n_chunks = (f_sub + k_chunk - 1) / k_chunk;
-  const size_t hist_smem = kern::hist_smem_bytes(k_chunk, B, C);
-  if (hist_smem > smem_cap) return fail(EMRF_ERR_LIMIT, "histogram tile needs %zu B of shared memory", hist_smem);
-  CU(cudaFuncSetAttribute(kern::hist_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem));
+  int row_ch, k_chunk, n_chunks;
+  size_t hist_bytes, hist_smem;
+  TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &hist_smem));
+  CU(hist_launch(row_ch, dim3(1), hist_smem, st, kern::HistArgs(), true));
   const size_t slot_words = (size_t)f_sub * B * C;
 
   // ---- trees, stack, driver RNG (RandomForest.run)
@@ -844,12 +880,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.total_counts = (uint32_t*)((char*)c->d_results.p + off_total);
     A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
     A.tile_len = tile_len;
+    A.tile_smem_off = (uint32_t)hist_bytes;
     A.impurity = P.impurity; A.min_instances = P.min_instances_per_node; A.hist_only = 0;
     A.min_info_gain = P.min_info_gain;
     cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
     CU(cudaEventRecord(e0, st));
     if (n_tiles) {
-      kern::hist_scan_kernel<<<dim3(n_tiles, n_chunks), kern::kHistThreads, hist_smem, st>>>(A);
+      CU(hist_launch(row_ch, dim3(n_tiles, n_chunks), hist_smem, st, A, false));
       tm.kernel_launches++;
       tm.hist_launches++;
     }
@@ -1303,21 +1340,6 @@ extern "C" int emrf_bag_weights(emrf_ctx_t* c, const emrf_params_t* params, int6
   return EMRF_OK;
 }
 
-// shared set-up of the histogram chunking for the stage entry points
-static int hist_geometry(emrf_ctx* c, int f_sub, int B, int C, int* k_chunk_out, int* n_chunks_out, size_t* smem_out) {
-  const size_t smem_cap = std::min<size_t>(c->smem_optin, 227 * 1024);
-  const size_t per_feat = (size_t)B * C * 4;
-  int k_chunk = (int)((100 * 1024 - 4096) / per_feat);
-  if (k_chunk < 1) k_chunk = (int)((smem_cap - 4096) / per_feat);
-  if (k_chunk < 1) return fail(EMRF_ERR_LIMIT, "one feature histogram (%d bins x %d classes) exceeds shared memory", B, C);
-  k_chunk = std::min(k_chunk, f_sub);
-  *k_chunk_out = k_chunk;
-  *n_chunks_out = (f_sub + k_chunk - 1) / k_chunk;
-  *smem_out = kern::hist_smem_bytes(k_chunk, B, C);
-  if (*smem_out > smem_cap) return fail(EMRF_ERR_LIMIT, "histogram tile needs %zu B of shared memory", *smem_out);
-  return EMRF_OK;
-}
-
 extern "C" int emrf_histogram(emrf_ctx_t* c, const uint8_t* bins_rm, int64_t N, int32_t F, const uint64_t* entries,
                               const int64_t* node_seg_off, int32_t n_nodes, const int32_t* subsets, int32_t f_sub,
                               const int32_t* num_bins_all, int32_t C, uint32_t* hist_out) {
@@ -1328,11 +1350,11 @@ extern "C" int emrf_histogram(emrf_ctx_t* c, const uint8_t* bins_rm, int64_t N, 
   cudaStream_t st = c->stream;
   int B = 1;
   for (int f = 0; f < F; f++) B = std::max(B, num_bins_all[f]);
-  int k_chunk, n_chunks;
-  size_t smem;
-  TRY(hist_geometry(c, f_sub, B, C, &k_chunk, &n_chunks, &smem));
-  CU(cudaFuncSetAttribute(kern::hist_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int Fp = (int)align_up(F, 16);
+  int row_ch, k_chunk, n_chunks;
+  size_t hist_bytes, smem;
+  TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &smem));
+  CU(hist_launch(row_ch, dim3(1), smem, st, kern::HistArgs(), true));
   const int64_t n_ent = node_seg_off[n_nodes];
   DevBuf d_rm, d_ent, d_nodes, d_feat, d_tiles, d_nb, d_hist;
   CU(d_rm.alloc((size_t)N * Fp));
@@ -1374,8 +1396,8 @@ extern "C" int emrf_histogram(emrf_ctx_t* c, const uint8_t* bins_rm, int64_t N, 
   A.ghist = d_hist.as<uint32_t>();
   A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
   A.tile_len = tile_len; A.hist_only = 1;
-  kern::hist_scan_kernel<<<dim3((unsigned)tn.size(), n_chunks), kern::kHistThreads, smem, st>>>(A);
-  CU(cudaGetLastError());
+  A.tile_smem_off = (uint32_t)hist_bytes;
+  CU(hist_launch(row_ch, dim3((unsigned)tn.size(), n_chunks), smem, st, A, false));
   CU(cudaMemcpyAsync(hist_out, d_hist.p, (size_t)n_nodes * slot_words * 4, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   return EMRF_OK;
@@ -1392,9 +1414,10 @@ extern "C" int emrf_best_splits(emrf_ctx_t* c, const uint32_t* hist, int32_t n_n
   cudaStream_t st = c->stream;
   int B = 1;
   for (int f = 0; f < F; f++) B = std::max(B, num_bins_all[f]);
-  int k_chunk, n_chunks;
-  size_t smem;
-  TRY(hist_geometry(c, f_sub, B, C, &k_chunk, &n_chunks, &smem));
+  int row_ch, k_chunk, n_chunks;
+  size_t hist_bytes, smem;
+  TRY(hist_geometry(c, 16, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &smem));
+  smem = hist_bytes;
   CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const size_t slot_words = (size_t)f_sub * B * C;
   const size_t n_rec = (size_t)n_nodes * n_chunks;

@@ -349,6 +349,7 @@ struct HistArgs {
   uint32_t* total_counts;      // [n_nodes*n_chunks][C]
   int32_t Fp, f_sub, B, C, k_chunk, n_chunks;
   uint32_t tile_len;
+  uint32_t tile_smem_off;      // byte offset of the per-warp row tiles inside dynamic shared memory
   int32_t impurity, min_instances, hist_only;
   double min_info_gain;
 };
@@ -408,7 +409,14 @@ __device__ __forceinline__ ScanSmem carve_smem(uint8_t* raw, int k_chunk, int B,
   return s;
 }
 inline size_t hist_smem_bytes(int k_chunk, int B, int C) {
-  return scan_hist_words(k_chunk, B, C) * 4 + 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + (size_t)k_chunk * 8 + 16;
+  return (scan_hist_words(k_chunk, B, C) * 4 + 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + (size_t)k_chunk * 8 + 16 + 15) & ~(size_t)15;
+}
+// chunks of 16 B per TreePoint row handled by the cooperative row loader (0 = generic byte gather)
+inline int hist_row_chunks(int Fp) { return (Fp / 16 <= 8) ? Fp / 16 : 0; }
+inline size_t hist_tile_bytes(int ch) {
+  if (ch == 0) return 0;
+  const int stride = (ch == 1 || ch == 2 || ch == 4 || ch == 8) ? 32 + 8 / ch : 33;
+  return (size_t)(kHistThreads / 32) * 4 * ch * stride * 4;
 }
 
 // Scans a histogram chunk held in shared memory: hist[kc][B][C]; nb[k] = numBins of subset
@@ -518,6 +526,47 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
   }
 }
 
+// Row staging for the accumulate loop.  A warp takes 32 entries at a time.  Its lanes fetch the 32
+// TreePoint rows cooperatively with 128-bit loads (CH = Fp/16 chunks per row, so one warp-wide
+// LDG.128 covers 32/CH whole rows: every fetched sector is fully used and one row costs Fp bytes of
+// L2 traffic instead of one 32 B sector per feature), park them TRANSPOSED in shared memory
+// (tile[word][row], row stride TS chosen so that both the 4 STS.32 of a chunk and the later
+// "lane = row" byte reads are bank-conflict free), and then every lane adds its own row's F_sub
+// bins.  The loads of batch b+1 are issued before batch b is consumed (register double buffer).
+template <int CH>
+struct RowTile {
+  static constexpr int kWords = 4 * CH;                                  // 32-bit words per row
+  static constexpr int kStride = (CH == 1 || CH == 2 || CH == 4 || CH == 8) ? 32 + 8 / CH : 33;
+  static constexpr int kWarpWords = kWords * kStride;
+};
+template <int CH>
+__device__ __forceinline__ void load_rows(const uint8_t* __restrict__ bins, int Fp, uint32_t my_row, int lane,
+                                          uint4 (&R)[CH]) {
+#pragma unroll
+  for (int it = 0; it < CH; it++) {
+    const int q = it * 32 + lane;
+    const int r = q / CH, c = q - r * CH;
+    const uint32_t row = __shfl_sync(0xffffffffu, my_row, r);
+    R[it] = __ldcg(reinterpret_cast<const uint4*>(bins + (size_t)row * Fp) + c);
+  }
+}
+template <int CH>
+__device__ __forceinline__ void stage_rows(uint32_t* tile, int lane, const uint4 (&R)[CH]) {
+  constexpr int TS = RowTile<CH>::kStride;
+#pragma unroll
+  for (int it = 0; it < CH; it++) {
+    const int q = it * 32 + lane;
+    const int r = q / CH, c = q - r * CH;
+    uint32_t* d = tile + (4 * c) * TS + r;
+    d[0] = R[it].x; d[TS] = R[it].y; d[2 * TS] = R[it].z; d[3 * TS] = R[it].w;
+  }
+}
+// entries of one warp-batch: lane j of batch b takes entry b*32 + j of the tile (0-weight beyond the end)
+__device__ __forceinline__ uint64_t load_entry(const uint64_t* __restrict__ ent, uint32_t len, uint32_t j) {
+  return j < len ? __ldcs(ent + j) : 0ull;
+}
+
+template <int CH>
 __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs A) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int tid = threadIdx.x;
@@ -547,15 +596,50 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
   const uint32_t len = min(A.tile_len, nd.seg_len - tile_in_node * A.tile_len);
   const uint8_t* bins = A.bins_rm;
   const int Fp = A.Fp;
-  for (uint32_t j = tid; j < len; j += kHistThreads) {
-    const uint64_t e = ent[j];
-    const uint32_t row = (uint32_t)e;
-    const uint32_t w = (uint32_t)(e >> 32) & 0xffu;
-    const uint32_t lab = (uint32_t)(e >> 40) & 0xffu;
-    const uint8_t* rp = bins + (size_t)row * Fp;
-    for (int k = 0; k < kc; k++) {
-      const uint32_t b = rp[sh_feat[k]];
-      atomicAdd(&sh[(k * B + b) * C + lab], w);
+  if (CH == 0) {
+    // generic path (rows wider than 128 B): one byte gather per (entry, feature)
+    for (uint32_t j = tid; j < len; j += kHistThreads) {
+      const uint64_t e = ent[j];
+      const uint32_t row = (uint32_t)e;
+      const uint32_t w = (uint32_t)(e >> 32) & 0xffu;
+      const uint32_t lab = (uint32_t)(e >> 40) & 0xffu;
+      const uint8_t* rp = bins + (size_t)row * Fp;
+      for (int k = 0; k < kc; k++) {
+        const uint32_t b = rp[sh_feat[k]];
+        atomicAdd(&sh[(k * B + b) * C + lab], w);
+      }
+    }
+  } else {
+    constexpr int CHX = CH ? CH : 1;
+    constexpr int TS = RowTile<CHX>::kStride;
+    const int lane = tid & 31, wv = tid >> 5;
+    constexpr int NW = kHistThreads / 32;
+    uint32_t* tile = reinterpret_cast<uint32_t*>(smem_raw + A.tile_smem_off) + wv * RowTile<CHX>::kWarpWords;
+    const uint8_t* tile_b = reinterpret_cast<const uint8_t*>(tile);
+    const uint32_t n_batches = (len + 31) >> 5;
+    uint4 R[CHX];
+    uint32_t b = wv;
+    uint64_t e_cur = load_entry(ent, len, b * 32 + lane);
+    uint64_t e_nxt = load_entry(ent, len, (b + NW) * 32 + lane);
+    if (b < n_batches) load_rows<CHX>(bins, Fp, (uint32_t)e_cur, lane, R);
+    for (; b < n_batches; b += NW) {
+      stage_rows<CHX>(tile, lane, R);
+      __syncwarp();
+      const uint64_t e_nn = load_entry(ent, len, (b + 2 * NW) * 32 + lane);
+      if (b + NW < n_batches) load_rows<CHX>(bins, Fp, (uint32_t)e_nxt, lane, R);
+      const uint32_t w = (uint32_t)(e_cur >> 32) & 0xffu;
+      const uint32_t lab = (uint32_t)(e_cur >> 40) & 0xffu;
+      if (w) {
+        uint32_t* hl = sh + lab;
+        for (int k = 0; k < kc; k++) {
+          const int f = sh_feat[k];
+          const uint32_t bin = tile_b[(((f >> 2) * TS + lane) << 2) + (f & 3)];
+          atomicAdd(hl + (k * B + bin) * C, w);
+        }
+      }
+      __syncwarp();
+      e_cur = e_nxt;
+      e_nxt = e_nn;
     }
   }
   __syncthreads();

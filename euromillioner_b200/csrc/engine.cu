@@ -419,9 +419,17 @@ static int run_bag(emrf_ctx* c, const emrf_params_t& P, int64_t N, const int64_t
   if (T > 1) {
     const double mean = P.subsampling_rate;
     const double p_exp = std::exp(-mean);
-    CU(cudaFuncSetAttribute(kern::bag_poisson_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kern::kBagSmemBytes));
-    kern::bag_poisson_kernel<<<(n_parts + 31) / 32, 32, kern::kBagSmemBytes, c->stream>>>(P.seed, d_off.as<int64_t>(), n_parts, T, mean, p_exp,
-                                                                         d_w, d_max.as<int>());
+    static const bool serial = getenv("EMRF_BAG_SERIAL") != nullptr;  // one thread per partition (cross-check)
+    if (serial) {
+      CU(cudaFuncSetAttribute(kern::bag_poisson_serial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kern::kBagSmemBytes));
+      kern::bag_poisson_serial_kernel<<<(n_parts + 31) / 32, 32, kern::kBagSmemBytes, c->stream>>>(
+          P.seed, d_off.as<int64_t>(), n_parts, T, mean, p_exp, d_w, d_max.as<int>());
+    } else {
+      const size_t smem = sizeof(kern::BagSmem);
+      CU(cudaFuncSetAttribute(kern::bag_poisson_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      kern::bag_poisson_kernel<<<(n_parts + kern::kBagWarps - 1) / kern::kBagWarps, kern::kBagWarps * 32, smem, c->stream>>>(
+          P.seed, d_off.as<int64_t>(), n_parts, T, mean, p_exp, d_w, d_max.as<int>());
+    }
   } else if (P.subsampling_rate == 1.0) {
     CU(cudaMemsetAsync(d_w, 1, (size_t)N * T, c->stream));
     int one = 1;
@@ -498,7 +506,8 @@ struct emrf_forest {
   std::vector<int64_t> tree_off;
   std::vector<FlatNode> nodes;
   std::vector<double> stats;  // nodes*C (filled lazily from counts for forests made by emrf_fit)
-  std::vector<uint32_t> counts;  // nodes*C integer class counts as trained
+  std::unique_ptr<uint32_t[]> counts;  // nodes*C integer class counts as trained (left uninitialised until filled)
+  size_t counts_len = 0;
   std::mutex stats_mu;
   std::vector<int32_t> group_sizes, trace;
   int f_sub = 0;
@@ -579,15 +588,16 @@ static void export_forest(const std::vector<HTree>& trees, int C, emrf_forest& f
   fo.tree_off.assign(T + 1, 0);
   for (int t = 0; t < T; t++) fo.tree_off[t + 1] = fo.tree_off[t] + info[t][0].size;
   fo.nodes.resize((size_t)fo.tree_off[T]);
-  fo.counts.resize((size_t)fo.tree_off[T] * C);
+  fo.counts_len = (size_t)fo.tree_off[T] * C;
+  fo.counts.reset(new uint32_t[fo.counts_len]);  // first touched by the parallel fill below
 #pragma omp parallel for schedule(dynamic)
   for (int t = 0; t < T; t++) export_pass_b(trees[t], 0, C, info[t], fo.tree_off[t], 0, fo);
 }
 static void ensure_double_stats(emrf_forest* f) {
   std::lock_guard<std::mutex> lk(f->stats_mu);
-  if (!f->stats.empty() || f->counts.empty()) return;
-  f->stats.resize(f->counts.size());
-  for (size_t i = 0; i < f->counts.size(); i++) f->stats[i] = (double)f->counts[i];
+  if (!f->stats.empty() || f->counts_len == 0) return;
+  f->stats.resize(f->counts_len);
+  for (size_t i = 0; i < f->counts_len; i++) f->stats[i] = (double)f->counts[i];
 }
 
 // ---------------------------------------------------------------------------------------------

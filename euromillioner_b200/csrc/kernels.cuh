@@ -189,9 +189,10 @@ struct WellState {
   }
 };
 constexpr int kBagSmemBytes = 624 * 32 * 4;
-__global__ void __launch_bounds__(32) bag_poisson_kernel(int64_t seed, const int64_t* __restrict__ part_off,
-                                                         int n_parts, int T, double mean, double p_exp,
-                                                         uint8_t* __restrict__ weights, int* __restrict__ max_w) {
+__global__ void __launch_bounds__(32) bag_poisson_serial_kernel(int64_t seed, const int64_t* __restrict__ part_off,
+                                                                int n_parts, int T, double mean, double p_exp,
+                                                                uint8_t* __restrict__ weights, int* __restrict__ max_w) {
+  // one THREAD per partition (kept as the cross-check of the warp-parallel kernel below)
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int part = blockIdx.x * blockDim.x + threadIdx.x;
   if (part >= n_parts) return;
@@ -214,6 +215,152 @@ __global__ void __launch_bounds__(32) bag_poisson_kernel(int64_t seed, const int
     out[q] = (uint8_t)min(n, 255);
   }
   atomicMax(max_w, mx);
+}
+
+// ---- one WARP per partition ---------------------------------------------------------------
+// WELL19937c is linear over GF(2).  Writing a_n for the word a step stores (z3) and b_n for the
+// word it hands to the next step (z4 before tempering), every operand of step n except b_{n-1} is
+// at least 70 steps old, and
+//     b_n = M(b_{n-1}) ^ e_n,   M(x) = Az(x ^ (x << 25)),  Az(x) = (x << 9) ^ (x >>> 21),
+//     e_n = z0_n ^ Az(vM1 ^ (vM1 >>> 27)) ^ (z2_n << 21) ^ (z2_n >>> 21)
+// with e_n known from old state.  A block of 64 steps (< 70) is therefore an affine recurrence with
+// a constant matrix: lane j owns steps 2j, 2j+1, the 32 lanes solve it with a Hillis-Steele scan
+// over powers of M^2 (byte-indexed lookup tables in shared memory), then every lane replays its
+// two steps from its carry-in and emits one nextDouble().  The Poisson loop itself (a running
+// product compared with exp(-mean)) stays sequential on lane 0; it reads the 32 uniforms of the
+// block from shared memory.  Bit-identical to the serial stream (tests/test_gpu_stages.py).
+constexpr int kBagWarps = 8;
+constexpr int kBagObuf = 1024;
+__device__ __forceinline__ uint32_t well_M(uint32_t x) {
+  const uint32_t t = x ^ (x << 25);
+  return (t << 9) ^ (t >> 21);
+}
+__device__ __forceinline__ uint32_t well_temper(uint32_t z4) {
+  z4 ^= (z4 << 7) & 0xe46e1700u;
+  z4 ^= (z4 << 15) & 0x9b868000u;
+  return z4;
+}
+struct BagSmem {
+  uint32_t lut[4][4][256];                 // (M^2)^(2^s) for s = 1..4, one table per input byte
+  uint32_t state[kBagWarps][624];
+  double ubuf[kBagWarps][32];
+  uint8_t obuf[kBagWarps][kBagObuf];
+};
+__global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t seed, const int64_t* __restrict__ part_off,
+                                                                     int n_parts, int T, double mean, double p_exp,
+                                                                     uint8_t* __restrict__ weights,
+                                                                     int* __restrict__ max_w) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  BagSmem& S = *reinterpret_cast<BagSmem*>(smem_raw);
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  for (int e = threadIdx.x; e < 4 * 4 * 256; e += blockDim.x) {
+    const int sidx = e >> 10, tb = (e >> 8) & 3, v = e & 255;
+    uint32_t x = (uint32_t)v << (8 * tb);
+    const int reps = 4 << sidx;            // (M^2)^(2^(sidx+1)) = M^(4 << sidx)
+    for (int i = 0; i < reps; i++) x = well_M(x);
+    S.lut[sidx][tb][v] = x;
+  }
+  __syncthreads();
+  const int part = blockIdx.x * kBagWarps + wv;
+  if (part >= n_parts) return;
+  uint32_t* A = S.state[wv];
+  {  // AbstractWell.setSeed(long): serial 624-word fill by lane 0
+    if (lane == 0) {
+      const int64_t sd = seed + (int64_t)part + 1;
+      uint32_t a = (uint32_t)((uint64_t)sd >> 32), b = (uint32_t)((uint64_t)sd & 0xffffffffull);
+      A[0] = a; A[1] = b;
+      for (int i = 2; i < 624; i++) {
+        const int64_t l = (int64_t)(int32_t)a;
+        const uint32_t nv = (uint32_t)((1812433253ll * (l ^ (l >> 30)) + i) & 0xffffffffll);
+        A[i] = nv; a = b; b = nv;
+      }
+    }
+    __syncwarp();
+  }
+  auto wrap = [](int j) { return j >= 624 ? j - 624 : (j < 0 ? j + 624 : j); };
+  auto applyQ = [&](int sidx, uint32_t x) {
+    return S.lut[sidx][0][x & 255] ^ S.lut[sidx][1][(x >> 8) & 255] ^ S.lut[sidx][2][(x >> 16) & 255] ^ S.lut[sidx][3][x >> 24];
+  };
+  const double limit = __dmul_rn(1000.0, mean);
+  const int64_t lo = part_off[part], hi = part_off[part + 1];
+  uint8_t* out = weights + (size_t)lo * T;
+  const int64_t total = (hi - lo) * (int64_t)T;
+  uint32_t carry = A[0];
+  int i0 = 0;                      // state index of the block's first step
+  // lane-0 Poisson state
+  int64_t q = 0;
+  int n = 0, mx = 0, pos = 0;
+  double r = 1.0;
+  int64_t flushed = 0;
+  while (true) {
+    // ---- 64 WELL steps -> 32 uniforms
+    const int i = wrap(i0 - 2 * lane);                 // index of this lane's first step
+    const uint32_t m1a = A[wrap(i + 70)], m2a = A[wrap(i + 179)], m3a = A[wrap(i + 449)];
+    const uint32_t m1b = A[wrap(i + 69)], m2b = A[wrap(i + 178)], m3b = A[wrap(i + 448)];
+    const uint32_t t1 = A[wrap(i - 1)], t2 = A[wrap(i - 2)], t3 = A[wrap(i - 3)];
+    const uint32_t z0a = (t1 & 0x80000000u) ^ (t2 & 0x7fffffffu);
+    const uint32_t z0b = (t2 & 0x80000000u) ^ (t3 & 0x7fffffffu);
+    const uint32_t ca = m1a ^ (m1a >> 27), cb = m1b ^ (m1b >> 27);
+    const uint32_t z2a = (m2a >> 9) ^ (m3a ^ (m3a >> 1)), z2b = (m2b >> 9) ^ (m3b ^ (m3b >> 1));
+    const uint32_t ea = z0a ^ ((ca << 9) ^ (ca >> 21)) ^ (z2a << 21) ^ (z2a >> 21);
+    const uint32_t eb = z0b ^ ((cb << 9) ^ (cb >> 21)) ^ (z2b << 21) ^ (z2b >> 21);
+    uint32_t X = well_M(ea) ^ eb;
+    if (lane == 0) X ^= well_M(well_M(carry));
+    {
+      uint32_t y = __shfl_up_sync(0xffffffffu, X, 1);
+      if (lane >= 1) X ^= well_M(well_M(y));
+#pragma unroll
+      for (int sidx = 0; sidx < 4; sidx++) {
+        const int d = 2 << sidx;
+        y = __shfl_up_sync(0xffffffffu, X, d);
+        if (lane >= d) X ^= applyQ(sidx, y);
+      }
+    }
+    uint32_t bin = __shfl_up_sync(0xffffffffu, X, 1);
+    if (lane == 0) bin = carry;
+    const uint32_t z1a = (bin ^ (bin << 25)) ^ ca;
+    const uint32_t aa = z1a ^ z2a;
+    const uint32_t ba = z0a ^ (z1a ^ (z1a << 9)) ^ (z2a ^ (z2a << 21)) ^ (aa ^ (aa >> 21));
+    const uint32_t z1b = (ba ^ (ba << 25)) ^ cb;
+    const uint32_t ab = z1b ^ z2b;
+    const uint32_t bb = z0b ^ (z1b ^ (z1b << 9)) ^ (z2b ^ (z2b << 21)) ^ (ab ^ (ab >> 21));
+    carry = __shfl_sync(0xffffffffu, bb, 31);
+    __syncwarp();                                        // every lane has read its operands
+    A[i] = aa;
+    A[wrap(i - 1)] = ab;
+    const uint64_t hi26 = (uint64_t)(well_temper(ba) >> 6) << 26;
+    const uint64_t lo26 = well_temper(bb) >> 6;
+    S.ubuf[wv][lane] = __dmul_rn((double)(int64_t)(hi26 | lo26), 2.220446049250313e-16);
+    i0 = wrap(i0 - 64);
+    __syncwarp();
+    // ---- PoissonDistribution.sample() over the block's uniforms (lane 0)
+    if (lane == 0) {
+      const double* ub = S.ubuf[wv];
+      uint8_t* ob = S.obuf[wv];
+#pragma unroll 4
+      for (int t = 0; t < 32 && q < total; t++) {
+        r = __dmul_rn(r, ub[t]);
+        bool emit;
+        if (r >= p_exp) { n++; emit = !((double)n < limit); } else emit = true;
+        if (emit) {
+          mx = max(mx, n);
+          ob[pos++] = (uint8_t)min(n, 255);
+          q++; n = 0; r = 1.0;
+        }
+      }
+    }
+    const int pos_all = __shfl_sync(0xffffffffu, pos, 0);
+    const int done = __shfl_sync(0xffffffffu, (int)(q >= total), 0);
+    if (pos_all > kBagObuf - 32 || done) {
+      __syncwarp();
+      for (int t = lane; t < pos_all; t += 32) out[flushed + t] = S.obuf[wv][t];
+      flushed += pos_all;
+      pos = 0;
+      __syncwarp();
+    }
+    if (done) break;
+  }
+  if (lane == 0) atomicMax(max_w, mx);
 }
 // T == 1 without replacement and rate < 1: XORShiftRandom(seed+p+1).nextDouble() < rate
 __device__ __forceinline__ uint32_t mm3_mix(uint32_t k) {

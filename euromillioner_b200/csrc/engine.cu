@@ -1553,3 +1553,102 @@ extern "C" int32_t emrf_host_group_tree_order(const int32_t* trees_first_seen, i
 extern "C" int32_t emrf_host_num_features_per_node(const emrf_params_t* params, int32_t n_features) {
   return hl::features_per_node(*params, n_features);
 }
+
+// ---------------------------------------------------------------------------------------------
+// emrf_update_partition_noalloc — the partition update for callers that must not allocate.
+//
+// Some hosts of this library cannot let it call cudaMalloc: a Spark executor that has handed the
+// whole device to a pooling allocator at start-up (nothing is left for a plain cudaMalloc to
+// find), or a serving loop that cannot afford the device-wide synchronisation cudaMalloc/cudaFree
+// imply.  For them this variant keeps everything the three partition kernels need besides the
+// caller's own inputs and outputs — node descriptors, the tile→node map and the per-tile left
+// counts — in ONE file-scope device array of fixed size.  Every GPU that loads libemrf.so holds
+// those kNoAllocScratchBytes until the process exits.
+//
+// The array's name below is only a host-side handle; the device address the kernels need is
+// looked up with cudaGetSymbolAddress the first time the entry point runs on a device (with that
+// device current).  Make that first call outside any stream capture.  All calls share the one
+// array and it keeps whatever the previous call left there: this call overwrites every word it
+// later reads, and clears the caller's n_left output itself when there is nothing to partition.
+// Two calls that overlap on the GPU (different streams, contexts or threads) would race on the
+// array — serialise them.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kNoAllocMaxNodes = 4096;
+constexpr size_t kNoAllocMaxTiles = 262144;   // 262144 tiles x 2048 entries = 536 870 912 entries
+constexpr size_t kNoAllocNodesOff = 0;
+constexpr size_t kNoAllocTileNodeOff = kNoAllocMaxNodes * sizeof(kern::SplitNode);
+constexpr size_t kNoAllocTileLeftOff = kNoAllocTileNodeOff + kNoAllocMaxTiles * 4;
+constexpr size_t kNoAllocScratchBytes = kNoAllocTileLeftOff + kNoAllocMaxTiles * 4;  // 2 228 224 B
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+static std::mutex g_noalloc_mu;
+static void* g_noalloc_ptr[64] = {nullptr};   // per device ordinal
+
+extern "C" int emrf_update_partition_noalloc(emrf_ctx_t* c, const uint8_t* bins_cm_dev, int64_t col_stride,
+                                             int32_t n_features, const uint64_t* entries_dev,
+                                             const int64_t* node_seg_off, int32_t n_nodes, const int32_t* split_feature,
+                                             const int32_t* split_bin, uint64_t* entries_out_dev, uint64_t* n_left_dev) {
+  if (!c || !bins_cm_dev || !entries_dev || !node_seg_off || !split_feature || !split_bin || !entries_out_dev || !n_left_dev)
+    return fail(EMRF_ERR_ARG, "NULL argument");
+  if (n_nodes < 1 || n_features < 1 || col_stride < 1) return fail(EMRF_ERR_ARG, "bad shape");
+  if ((size_t)n_nodes > kNoAllocMaxNodes)
+    return fail(EMRF_ERR_LIMIT, "emrf_update_partition_noalloc handles at most %zu nodes per call (got %d)", kNoAllocMaxNodes, n_nodes);
+  if (c->device < 0 || c->device >= 64) return fail(EMRF_ERR_LIMIT, "device ordinal %d not supported", c->device);
+  // host-side descriptors first, so that the size check happens before anything is enqueued
+  std::vector<kern::SplitNode> sn(n_nodes);
+  size_t n_tiles = 0;
+  for (int i = 0; i < n_nodes; i++) {
+    const int64_t len = node_seg_off[i + 1] - node_seg_off[i];
+    if (len < 0 || len >= (1ll << 32)) return fail(EMRF_ERR_ARG, "node %d: bad segment", i);
+    if (split_feature[i] < 0 || split_feature[i] >= n_features) return fail(EMRF_ERR_ARG, "split feature out of range");
+    kern::SplitNode& s = sn[i];
+    s.seg_start = (uint64_t)node_seg_off[i];
+    s.seg_len = (uint32_t)len;
+    s.buf = 0;
+    s.feature = split_feature[i];
+    s.split_bin = split_bin[i];
+    s.tile_begin = (uint32_t)n_tiles;
+    s.n_tiles = (uint32_t)((len + kern::kPartTile - 1) / kern::kPartTile);
+    n_tiles += s.n_tiles;
+  }
+  if (n_tiles > kNoAllocMaxTiles)
+    return fail(EMRF_ERR_LIMIT, "emrf_update_partition_noalloc handles at most %zu entries per call (%zu tiles of %d; got %zu tiles)",
+                kNoAllocMaxTiles * (size_t)kern::kPartTile, kNoAllocMaxTiles, kern::kPartTile, n_tiles);
+  std::vector<uint32_t> tn(n_tiles);
+  for (int i = 0; i < n_nodes; i++)
+    for (uint32_t q = 0; q < sn[i].n_tiles; q++) tn[sn[i].tile_begin + q] = (uint32_t)i;
+
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  unsigned char* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk2(g_noalloc_mu);
+    if (!g_noalloc_ptr[c->device]) {  // once per device, with that device current
+      void* p = nullptr;
+      CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+      g_noalloc_ptr[c->device] = p;
+    }
+    scratch = static_cast<unsigned char*>(g_noalloc_ptr[c->device]);
+  }
+  cudaStream_t st = c->stream;
+  kern::SplitNode* d_nodes = reinterpret_cast<kern::SplitNode*>(scratch + kNoAllocNodesOff);
+  uint32_t* d_tile_node = reinterpret_cast<uint32_t*>(scratch + kNoAllocTileNodeOff);
+  uint32_t* d_tile_left = reinterpret_cast<uint32_t*>(scratch + kNoAllocTileLeftOff);
+  CU(cudaMemcpyAsync(d_nodes, sn.data(), sizeof(kern::SplitNode) * (size_t)n_nodes, cudaMemcpyHostToDevice, st));
+  if (n_tiles) {
+    CU(cudaMemcpyAsync(d_tile_node, tn.data(), n_tiles * 4, cudaMemcpyHostToDevice, st));
+    // part_count writes tile_left[0..n_tiles), part_scan turns it into offsets and writes n_left for
+    // every node, part_scatter reads both: no word of the scratch is read before this call wrote it.
+    kern::part_count_kernel<<<(unsigned)n_tiles, kern::kPartThreads, 0, st>>>(entries_dev, entries_dev, bins_cm_dev, col_stride,
+                                                                          d_nodes, d_tile_node, d_tile_left);
+    kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(d_nodes, d_tile_left, n_left_dev);
+    kern::part_scatter_kernel<<<(unsigned)n_tiles, kern::kPartThreads, 0, st>>>(entries_dev, entries_dev, entries_out_dev,
+                                                                            entries_out_dev, bins_cm_dev, col_stride, d_nodes,
+                                                                            d_tile_node, d_tile_left, n_left_dev);
+    CU(cudaGetLastError());
+  } else {
+    CU(cudaMemsetAsync(n_left_dev, 0, (size_t)n_nodes * 8, st));  // every segment is empty
+  }
+  CU(cudaStreamSynchronize(st));  // sn / tn are pageable host memory read by the async copies
+  return EMRF_OK;
+}

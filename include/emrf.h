@@ -177,6 +177,21 @@ int emrf_update_partition(emrf_ctx_t* ctx, const uint8_t* bins_cm, int64_t n_row
                           const int32_t* split_feature, const int32_t* split_bin, uint64_t* entries_out,
                           int64_t* n_left_out);
 
+/* Partition update for callers that cannot allocate device memory (a process whose GPU memory is
+ * wholly owned by a pool allocator, or a loop that must avoid cudaMalloc's device-wide sync).
+ * No counterpart in the reference or in Spark: same computation as emrf_update_partition, but
+ * bins_cm_dev (column-major uint8, `col_stride` bytes between feature columns), entries_dev,
+ * entries_out_dev (distinct from entries_dev) and n_left_dev[n_nodes] are DEVICE buffers owned by
+ * the caller, and all working storage is a fixed 2 228 224-byte device array inside the library
+ * (held by every GPU that loads it, until exit).  Limits per call: 4096 nodes, 262 144 tiles of
+ * 2048 entries; larger requests fail with EMRF_ERR_LIMIT.  The first call on a device looks up
+ * the array's address (do it before any stream capture); concurrent calls on one GPU race. */
+int emrf_update_partition_noalloc(emrf_ctx_t* ctx, const uint8_t* bins_cm_dev, int64_t col_stride,
+                                  int32_t n_features, const uint64_t* entries_dev,
+                                  const int64_t* node_seg_off, int32_t n_nodes,
+                                  const int32_t* split_feature, const int32_t* split_bin,
+                                  uint64_t* entries_out_dev, uint64_t* n_left_dev);
+
 /* ---- host-logic probes (no GPU needed): the sequential, parity-critical pieces of
  * RandomForest.selectNodesToSplit that run on the host inside emrf_fit ------------------------- */
 int64_t emrf_host_java_random_next_long(int64_t seed, int32_t nth);           /* java.util.Random */

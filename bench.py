@@ -150,9 +150,8 @@ def main():
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        uid = [Context.nccl_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        ctx = Context(local_rank, rank, world, uid[0])
+        from euromillioner_b200.dist import make_context
+        ctx = make_context(dist)
     else:
         ctx = Context(local_rank)
 

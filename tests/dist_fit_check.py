@@ -1,0 +1,39 @@
+"""Run under torchrun on N GPUs: a tree-sharded fit must give the 1-process oracle forest bit for bit.
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/dist_fit_check.py"""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from euromillioner_b200 import synth  # noqa: E402
+from euromillioner_b200.classifier import Dataset, RandomForestClassifier  # noqa: E402
+from euromillioner_b200.dist import env_rank, make_context  # noqa: E402
+
+rank, local_rank, world = env_rank()
+torch.cuda.set_device(local_rank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+ctx = make_context(dist)
+X, y = synth.flat(50000, 32, 50)
+rf = RandomForestClassifier(ctx).setNumTrees(13).setMaxDepth(8).setNumClasses(50).setMaxMemoryInMB(16)
+model = rf.fit(Dataset(X, y, num_partitions=32))
+e = model.export()
+if rank == 0:
+    from oracle import binding as ob
+    o = ob.fit(ob.make_params(num_trees=13, max_depth=8, num_classes=50, max_memory_mb=16), X, y,
+               ob.partition_offsets(len(X), 32)).export()
+    for k in e:
+        assert np.array_equal(e[k], o[k]), k
+    print(f"DIST_FIT_OK world={world} nodes={model.totalNumNodes}")
+# every rank must hold the same forest
+digest = torch.tensor([float(e["threshold"].sum()), float(e["stats"].sum()), float(len(e["left"]))], device="cuda",
+                      dtype=torch.float64)
+lo, hi = digest.clone(), digest.clone()
+dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+assert torch.equal(lo, hi), "ranks disagree on the forest"
+dist.barrier()
+dist.destroy_process_group()

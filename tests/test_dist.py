@@ -1,0 +1,60 @@
+"""N > 1 path.  CPU (gloo, world_size 2): the rendezvous plumbing, tree ownership and the rule that only
+rank 0 runs/prints the reference arm.  GPU (needs >= 2 B200s): a tree-sharded fit equals the oracle forest."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+from conftest import ROOT
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from euromillioner_b200.dist import broadcast_bytes, env_rank, trees_of_rank
+    uid = broadcast_bytes(dist, bytes(range(128)) if rank == 0 else None)
+    q.put((rank, uid == bytes(range(128)), env_rank(), trees_of_rank(7, rank, world)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_rendezvous_and_tree_ownership():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, 29533, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got[0] == (0, True, (0, 0, 2), [0, 2, 4, 6])
+    assert got[1] == (1, True, (1, 1, 2), [1, 3, 5])
+
+
+def test_reference_arm_runs_on_rank0_only(monkeypatch):
+    """bench.py --impl reference under N ranks: rank 0 prints the line, the others exit 0 silently."""
+    env = dict(os.environ, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
+                        "--warmup", "0"], env=env, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+@pytest.mark.gpu
+def test_tree_sharded_fit_matches_oracle_on_2_gpus():
+    import ctypes
+    n = ctypes.c_int(0)
+    cuda = ctypes.CDLL("libcuda.so.1")
+    cuda.cuInit(0)
+    cuda.cuDeviceGetCount(ctypes.byref(n))
+    if n.value < 2:
+        pytest.skip("needs 2 GPUs")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "dist_fit_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "DIST_FIT_OK world=2" in r.stdout

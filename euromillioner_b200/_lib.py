@@ -71,6 +71,7 @@ def lib():
     L.emrf_memcpy_h2d.argtypes = [vp, vp, vp, i64]
     L.emrf_memcpy_d2h.argtypes = [vp, vp, vp, i64]
     L.emrf_fit.argtypes = [vp, P(EmrfParams), vp, vp, i64, i32, P(i64), i32, P(vp)]
+    L.emrf_fit_sharded.argtypes = [vp, P(EmrfParams), vp, vp, i64, i32, P(i64), i32, i32, i32, P(vp)]
     L.emrf_forest_free.argtypes = [vp]
     L.emrf_forest_free.restype = None
     L.emrf_forest_info.argtypes = [vp, P(i32), P(i32), P(i32), P(i64)]

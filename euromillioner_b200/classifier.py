@@ -77,7 +77,8 @@ class Dataset:
     partition, so it is part of the input).  `features`/`label` may also be raw device pointers
     (int) when the data is already resident in HBM; then n_rows/n_features must be given."""
 
-    def __init__(self, features, label=None, num_partitions=1, partition_offsets=None, n_rows=None, n_features=None):
+    def __init__(self, features, label=None, num_partitions=1, partition_offsets=None, n_rows=None, n_features=None,
+                 global_partition_offsets=None, first_partition=0):
         if isinstance(features, (int, np.integer)):
             self.features, self.n_rows, self.n_features = int(features), int(n_rows), int(n_features)
         else:
@@ -95,7 +96,20 @@ class Dataset:
             # SparkContext.parallelize slicing: [floor(i*N/P), floor((i+1)*N/P))
             partition_offsets = [(i * self.n_rows) // num_partitions for i in range(num_partitions + 1)]
         self.partition_offsets = np.ascontiguousarray(partition_offsets, np.int64)
+        # row-sharded fit: this object holds only the rows of global partitions
+        # [first_partition, first_partition + n_local) of a Dataset described by global_partition_offsets
+        self.global_partition_offsets = (None if global_partition_offsets is None
+                                         else np.ascontiguousarray(global_partition_offsets, np.int64))
+        self.first_partition = int(first_partition)
         self.columns = {}
+
+    @classmethod
+    def shard(cls, features_local, label_local, global_partition_offsets, first_partition, n_partitions_local):
+        """The slice of a partitioned Dataset owned by one rank (emrf_fit_sharded)."""
+        g = np.ascontiguousarray(global_partition_offsets, np.int64)
+        local = g[first_partition:first_partition + n_partitions_local + 1] - g[first_partition]
+        return cls(features_local, label_local, partition_offsets=local, global_partition_offsets=g,
+                   first_partition=first_partition)
 
     def _fptr(self):
         return C.c_void_p(self.features) if isinstance(self.features, int) else _ptr(self.features)
@@ -208,8 +222,15 @@ class RandomForestClassifier:
         p = self._params()
         h = C.c_void_p()
         po = dataset.partition_offsets
-        check(L.emrf_fit(ctx.h, C.byref(p), dataset._fptr(), dataset._lptr(), dataset.n_rows, dataset.n_features,
-                         po.ctypes.data_as(C.POINTER(C.c_int64)), len(po) - 1, C.byref(h)))
+        if dataset.global_partition_offsets is not None:
+            g = dataset.global_partition_offsets
+            p.shard_mode = 1
+            check(L.emrf_fit_sharded(ctx.h, C.byref(p), dataset._fptr(), dataset._lptr(), dataset.n_rows, dataset.n_features,
+                                     g.ctypes.data_as(C.POINTER(C.c_int64)), len(g) - 1, dataset.first_partition,
+                                     len(po) - 1, C.byref(h)))
+        else:
+            check(L.emrf_fit(ctx.h, C.byref(p), dataset._fptr(), dataset._lptr(), dataset.n_rows, dataset.n_features,
+                             po.ctypes.data_as(C.POINTER(C.c_int64)), len(po) - 1, C.byref(h)))
         return RandomForestClassificationModel(ctx, h)
 
 

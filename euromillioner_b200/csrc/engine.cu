@@ -246,14 +246,28 @@ extern "C" int emrf_get_timings(const emrf_ctx_t* c, emrf_timings_t* out) {
   *out = c->tm;
   return EMRF_OK;
 }
-// allreduce (sum) of uint32 words over the ctx communicator, in place
-static int nccl_allreduce_u32(emrf_ctx* c, uint32_t* buf, size_t count) {
+// in-place all-reduce over the ctx communicator: uint32 sum (histograms, split records, raw bit
+// patterns against zeros) or int32 max (label flags)
+static int nccl_allreduce(emrf_ctx* c, void* buf, size_t count, bool int32_max) {
   if (c->world == 1) return EMRF_OK;
-  auto ar = (ncclAllReduce_t)dlsym(c->nccl_lib, "ncclAllReduce");
-  int rc = ar(buf, buf, count, /*ncclUint32*/ 3, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+  static ncclAllReduce_t ar = nullptr;
+  if (!ar) ar = (ncclAllReduce_t)dlsym(c->nccl_lib, "ncclAllReduce");
+  int rc = ar(buf, buf, count, int32_max ? /*ncclInt32*/ 2 : /*ncclUint32*/ 3, int32_max ? /*ncclMax*/ 2 : /*ncclSum*/ 0,
+              c->nccl_comm, c->stream);
   if (rc) return fail(EMRF_ERR_CUDA, "ncclAllReduce failed (%d)", rc);
   return EMRF_OK;
 }
+static int nccl_allreduce_u32(emrf_ctx* c, uint32_t* buf, size_t count) { return nccl_allreduce(c, buf, count, false); }
+
+// Row-sharded fit (shard_mode 1): this rank holds the rows of partitions
+// [first_part, first_part + n_parts_local) of a dataset of n_rows_global rows in n_parts_global partitions.
+struct ShardSpec {
+  int first_part = 0;
+  int64_t n_rows_global = 0;
+  const int64_t* goff = nullptr;   // global partition offsets, n_parts_global + 1
+  int n_parts_global = 0;
+  int64_t row0 = 0;                // global index of the first local row
+};
 
 extern "C" int emrf_dev_alloc(emrf_ctx_t* c, int64_t bytes, void** out) {
   if (!c || !out || bytes < 0) return fail(EMRF_ERR_ARG, "bad argument");
@@ -337,8 +351,13 @@ static int stage_input(emrf_ctx* c, const void* src_hd, size_t bytes, DevBuf& ow
 // ---------------------------------------------------------------------------------------------
 // findSplits on the device
 // ---------------------------------------------------------------------------------------------
-static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX, int64_t N, int F, const int64_t* part_off,
-                           int n_parts, DevBuf& d_thr, DevBuf& d_ns, std::vector<double>& h_thr, std::vector<int>& h_ns) {
+static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX, int64_t N_local, int F, const int64_t* part_off_local,
+                           int n_parts_local, DevBuf& d_thr, DevBuf& d_ns, std::vector<double>& h_thr, std::vector<int>& h_ns,
+                           const ShardSpec* sh = nullptr) {
+  // metadata and sampling are defined on the WHOLE dataset
+  const int64_t N = sh ? sh->n_rows_global : N_local;
+  const int64_t* part_off = sh ? sh->goff : part_off_local;
+  const int n_parts = sh ? sh->n_parts_global : n_parts_local;
   const int TS = P.max_bins;
   const int max_possible_bins = (int)std::min<int64_t>(P.max_bins, N);
   const int num_splits = max_possible_bins - 1;
@@ -366,8 +385,37 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
       }
       CU(d_S.alloc((size_t)F * n_pad * 8));
       const int64_t total = (int64_t)n_pad * F;
-      kern::fs_gather_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(
-          dX, F, d_rows.as<int64_t>(), n_s, n_pad, sampled ? 0 : 1, P.find_splits_policy == 0 ? 1 : 0, d_S.as<double>());
+      if (!sh) {
+        kern::fs_gather_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(
+            dX, F, d_rows.as<int64_t>(), n_s, n_pad, sampled ? 0 : 1, P.find_splits_policy == 0 ? 1 : 0, d_S.as<double>());
+      } else {
+        // own samples → global sample positions, all-reduce the bit patterns, then mark sentinels
+        std::vector<int64_t> own_rows;
+        std::vector<int32_t> own_pos;
+        const int64_t lo = sh->row0, hi = sh->row0 + N_local;
+        if (sampled) {
+          for (int j = 0; j < n_s; j++)
+            if (rows[j] >= lo && rows[j] < hi) { own_rows.push_back(rows[j] - lo); own_pos.push_back(j); }
+        } else {
+          for (int64_t r = lo; r < hi; r++) { own_rows.push_back(r - lo); own_pos.push_back((int32_t)r); }
+        }
+        const int n_own = (int)own_rows.size();
+        DevBuf d_or, d_op;
+        CU(d_or.alloc((size_t)n_own * 8));
+        CU(d_op.alloc((size_t)n_own * 4));
+        CU(cudaMemcpyAsync(d_or.p, own_rows.data(), (size_t)n_own * 8, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(d_op.p, own_pos.data(), (size_t)n_own * 4, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemsetAsync(d_S.p, 0, (size_t)F * n_pad * 8, c->stream));
+        if (n_own)
+          kern::fs_gather_sharded_kernel<<<(unsigned)(((int64_t)n_own * F + 255) / 256), 256, 0, c->stream>>>(
+              dX, F, d_or.as<int64_t>(), d_op.as<int32_t>(), n_own, n_pad, d_S.as<double>());
+        TRY(nccl_allreduce_u32(c, d_S.as<uint32_t>(), (size_t)F * n_pad * 2));
+        kern::fs_mark_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(d_S.as<double>(), F, n_s, n_pad,
+                                                                                    P.find_splits_policy == 0 ? 1 : 0);
+        c->tm.kernel_launches += 1;
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(c->stream));  // own_rows/own_pos/d_or/d_op die here
+      }
       const int use_smem = ((size_t)n_pad * 8 <= 128 * 1024) ? 1 : 0;
       const size_t smem = use_smem ? (size_t)n_pad * 8 : 0;
       if (smem > 48 * 1024)
@@ -609,7 +657,7 @@ struct GroupEntry {
 };
 
 static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* features_hd, const double* labels_hd, int64_t N,
-                    int F, const int64_t* part_off, int n_parts, emrf_forest_t** out) {
+                    int F, const int64_t* part_off, int n_parts, emrf_forest_t** out, const ShardSpec* sh = nullptr) {
   emrf_params_t P = P_in;
   emrf_timings_t& tm = c->tm;
   memset(&tm, 0, sizeof(tm));
@@ -617,7 +665,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   cudaStream_t st = c->stream;
   CU(cudaSetDevice(c->device));
   if (N >= (1ll << 32)) return fail(EMRF_ERR_LIMIT, "n_rows must be < 2^32");
-  if (c->world > 1 && P.shard_mode == 1) return fail(EMRF_ERR_LIMIT, "row-sharded multi-GPU fit is not built yet");
+  // row_sharded: this rank holds a slice of the rows and every tree; node histograms are all-reduced.
+  // otherwise (world > 1): tree-sharded — every rank holds all rows and builds trees t % world == rank.
+  const bool row_sharded = (sh != nullptr);
+  if (c->world > 1 && P.shard_mode == 1 && !row_sharded)
+    return fail(EMRF_ERR_ARG, "shard_mode 1 (row-sharded) needs emrf_fit_sharded: each rank passes its own rows");
+  auto mine = [&](int tree) { return row_sharded || (tree % c->world == c->rank); };
 
   cudaEvent_t ev_start = c->events.get(), ev_in = c->events.get(), ev_fs = c->events.get(), ev_bin = c->events.get(),
               ev_bag = c->events.get(), ev_end = c->events.get();
@@ -642,6 +695,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   kern::labels_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(dy, N, P.num_classes, d_labels.as<uint8_t>(), d_flags.as<int>());
   tm.kernel_launches++;
   int flags[2] = {0, 0};
+  if (row_sharded) TRY(nccl_allreduce(c, d_flags.p, 2, true));
   CU(cudaMemcpyAsync(flags, d_flags.p, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   if (flags[0]) return fail(EMRF_ERR_ARG, "Classifier given dataset with invalid label: labels must be integers in [0, numClasses)");
@@ -658,7 +712,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   DevBuf d_thr, d_ns;
   std::vector<double> h_thr;
   std::vector<int> h_ns;
-  TRY(run_find_splits(c, P, dX, N, F, part_off, n_parts, d_thr, d_ns, h_thr, h_ns));
+  TRY(run_find_splits(c, P, dX, N, F, part_off, n_parts, d_thr, d_ns, h_thr, h_ns, sh));
   CU(cudaEventRecord(ev_fs, st));
   const int TS = P.max_bins;
   std::vector<int> num_bins(F);
@@ -686,7 +740,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     DevBuf d_w;
     CU(d_w.alloc((size_t)N * T));
     int maxw = 0;
-    TRY(run_bag(c, P, N, part_off, n_parts, d_w.as<uint8_t>(), &maxw));
+    {
+      emrf_params_t Pb = P;   // partition p of this rank is global partition first_part + p: seed + p_global + 1
+      if (row_sharded) Pb.seed = P.seed + sh->first_part;
+      TRY(run_bag(c, Pb, N, part_off, n_parts, d_w.as<uint8_t>(), &maxw));
+    }
     const int n_tiles = (int)((N + kern::kListTile - 1) / kern::kListTile);
     DevBuf d_counts, d_totals, d_base;
     CU(d_counts.alloc((size_t)n_tiles * T * 4));
@@ -718,6 +776,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   size_t hist_bytes, hist_smem;
   TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &hist_smem));
   CU(hist_launch(row_ch, dim3(1), hist_smem, st, kern::HistArgs(), true));
+  if (row_sharded) CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
   const size_t slot_words = (size_t)f_sub * B * C;
 
   // ---- trees, stack, driver RNG (RandomForest.run)
@@ -826,7 +885,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     // tiles
     uint64_t total_entries = 0;
     for (auto& g : group)
-      if (g.tree % c->world == c->rank) total_entries += trees[g.tree].pool[g.pool].seg_len;
+      if (mine(g.tree)) total_entries += trees[g.tree].pool[g.pool].seg_len;
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
 
@@ -842,9 +901,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       d.buf = hn.buf;
       d.pad = 0;
       d.tile_begin = n_tiles;
-      const bool mine = (group[i].tree % c->world == c->rank);
-      d.n_tiles = mine ? std::max<uint32_t>(1, (hn.seg_len + tile_len - 1) / tile_len) : 0;
-      d.slot = (d.n_tiles > 1) ? n_slots++ : -1;
+      d.n_tiles = mine(group[i].tree) ? std::max<uint32_t>(1, (hn.seg_len + tile_len - 1) / tile_len) : 0;
+      d.slot = (row_sharded || d.n_tiles > 1) ? n_slots++ : -1;   // row-sharded: every histogram goes to HBM for the all-reduce
       n_tiles += d.n_tiles;
     }
     const size_t off_feat = align_up(sizeof(kern::GroupNode) * (size_t)n_nodes, 16);
@@ -873,7 +931,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     tm.h2d_bytes += (int64_t)group_bytes;
     tm.d2h_bytes += (int64_t)res_bytes;
     CU(cudaMemsetAsync(c->d_tickets.p, 0, n_rec * 4, st));
-    if (c->world > 1) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
+    if (c->world > 1 && !row_sharded) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
     if (n_slots) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots * slot_words * 4, st));
     kern::HistArgs A;
     A.ent0 = d_ent[0].as<uint64_t>();
@@ -891,7 +949,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
     A.tile_len = tile_len;
     A.tile_smem_off = (uint32_t)hist_bytes;
-    A.impurity = P.impurity; A.min_instances = P.min_instances_per_node; A.hist_only = 0;
+    A.impurity = P.impurity; A.min_instances = P.min_instances_per_node; A.hist_only = row_sharded ? 1 : 0;
     A.min_info_gain = P.min_info_gain;
     cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
     CU(cudaEventRecord(e0, st));
@@ -903,13 +961,24 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaEventRecord(e1, st));
     hist_ev.emplace_back(e0, e1);
     CU(cudaGetLastError());
-    if (c->world > 1) TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
+    if (row_sharded) {
+      // reduceByKey(_.merge(_)) of Spark's per-partition aggregators: sum the partial histograms of
+      // all ranks (exact integers), then every rank scans every node (identical results everywhere)
+      TRY(nccl_allreduce_u32(c, c->d_ghist.as<uint32_t>(), (size_t)n_nodes * slot_words));
+      kern::scan_kernel<<<dim3(n_nodes, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
+          c->d_ghist.as<uint32_t>(), A.node_feat, A.num_bins_all, f_sub, B, C, k_chunk, n_chunks, P.impurity,
+          P.min_instances_per_node, P.min_info_gain, A.results, A.left_counts, A.total_counts);
+      tm.kernel_launches++;
+      CU(cudaGetLastError());
+    } else if (c->world > 1) {
+      TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
+    }
     CU(cudaMemcpyAsync(c->h_results.p, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     tm.hist_units += (int64_t)total_entries;
     tm.hist_alg_bytes += (int64_t)total_entries * (f_sub + 6);
     for (auto& g : group)
-      if (g.tree % c->world == c->rank) tm.hist_alg_bytes += (int64_t)slot_words * 4;
+      if (mine(g.tree)) tm.hist_alg_bytes += (int64_t)slot_words * 4;
     tm.total_nodes_split += n_nodes;
 
     // ---- driver side of findBestSplits: node updates in Scala map iteration order
@@ -989,7 +1058,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           n.left = li; n.right = li + 1;
           if (!l_leaf) stack.emplace_back(t, li);
           if (!r_leaf) stack.emplace_back(t, li + 1);
-          if ((!l_leaf || !r_leaf) && (t % c->world == c->rank)) {
+          if ((!l_leaf || !r_leaf) && mine(t)) {
             kern::SplitNode s;
             s.seg_start = n.seg_start; s.seg_len = n.seg_len; s.buf = n.buf;
             s.feature = feat; s.split_bin = sbin; s.tile_begin = 0; s.n_tiles = 0;
@@ -1096,6 +1165,35 @@ extern "C" int emrf_fit(emrf_ctx_t* c, const emrf_params_t* params, const double
   TRY(check_partitions(n_rows, partition_offsets, n_partitions));
   std::lock_guard<std::mutex> lk(c->fit_mu);
   return fit_impl(c, *params, features_hd, labels_hd, n_rows, n_features, partition_offsets, n_partitions, out);
+}
+
+extern "C" int emrf_fit_sharded(emrf_ctx_t* c, const emrf_params_t* params, const double* features_hd, const double* labels_hd,
+                                int64_t n_rows_local, int32_t n_features, const int64_t* partition_offsets_global,
+                                int32_t n_partitions_global, int32_t first_partition, int32_t n_partitions_local,
+                                emrf_forest_t** out) {
+  if (!c || !out || !features_hd || !labels_hd || !partition_offsets_global) return fail(EMRF_ERR_ARG, "NULL argument");
+  TRY(check_params(params));
+  if (n_partitions_global < 1 || first_partition < 0 || n_partitions_local < 1 ||
+      first_partition + n_partitions_local > n_partitions_global)
+    return fail(EMRF_ERR_ARG, "bad partition range [%d, %d) of %d", first_partition, first_partition + n_partitions_local,
+                n_partitions_global);
+  const int64_t n_global = partition_offsets_global[n_partitions_global];
+  TRY(check_partitions(n_global, partition_offsets_global, n_partitions_global));
+  const int64_t row0 = partition_offsets_global[first_partition];
+  if (partition_offsets_global[first_partition + n_partitions_local] - row0 != n_rows_local)
+    return fail(EMRF_ERR_ARG, "n_rows_local does not match the partition range");
+  if (n_rows_local < 1 || n_features < 1) return fail(EMRF_ERR_ARG, "every rank needs at least one row");
+  if (params->num_classes < 1 && c->world > 1) {}  // inferred classes are all-reduced below
+  std::vector<int64_t> local_off(n_partitions_local + 1);
+  for (int i = 0; i <= n_partitions_local; i++) local_off[i] = partition_offsets_global[first_partition + i] - row0;
+  ShardSpec sh;
+  sh.first_part = first_partition;
+  sh.n_rows_global = n_global;
+  sh.goff = partition_offsets_global;
+  sh.n_parts_global = n_partitions_global;
+  sh.row0 = row0;
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  return fit_impl(c, *params, features_hd, labels_hd, n_rows_local, n_features, local_off.data(), n_partitions_local, out, &sh);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -987,6 +987,25 @@ __global__ void fs_gather_kernel(const double* __restrict__ X, int F, const int6
   }
   S[(size_t)f * n_pad + j] = v;
 }
+// Row-sharded fit: every rank owns a slice of the rows, so the sample matrix is assembled in two
+// steps — each rank writes the values of ITS sampled rows at their global sample positions (all
+// other slots stay zero), the ranks all-reduce the raw bit patterns (integer add against zeros is
+// exact), then fs_mark_kernel applies the padding / zero-filter sentinels everywhere.
+__global__ void fs_gather_sharded_kernel(const double* __restrict__ X, int F, const int64_t* __restrict__ local_rows,
+                                         const int32_t* __restrict__ sample_pos, int n_own, int n_pad,
+                                         double* __restrict__ S) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)n_own * F) return;
+  const int s = (int)(i / F), f = (int)(i - (int64_t)s * F);
+  S[(size_t)f * n_pad + sample_pos[s]] = X[local_rows[s] * F + f];
+}
+__global__ void fs_mark_kernel(double* __restrict__ S, int F, int n_s, int n_pad, int zero_filter) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)n_pad * F) return;
+  const int j = (int)(i % n_pad);
+  const double v = S[i];
+  if (j >= n_s || (zero_filter && v == 0.0)) S[i] = fs_sentinel();
+}
 __global__ void __launch_bounds__(1024) fs_sort_walk_kernel(double* __restrict__ S, int n_pad, int n_s, int use_smem,
                                                             int num_splits, int64_t num_samples_expected, int policy,
                                                             int thr_stride, double* __restrict__ thr_out,

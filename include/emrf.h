@@ -114,6 +114,18 @@ int emrf_fit(emrf_ctx_t* ctx, const emrf_params_t* params, const double* feature
              const double* labels_hd, int64_t n_rows, int32_t n_features,
              const int64_t* partition_offsets, int32_t n_partitions, emrf_forest_t** out);
 
+/* Row-sharded fit (one process per GPU; ctx made by emrf_ctx_create_dist).  The Dataset's rows are
+ * split across ranks at partition boundaries: this rank passes only the rows of global partitions
+ * [first_partition, first_partition + n_partitions_local), every rank passes the same global
+ * partition_offsets.  Per group each rank builds partial node histograms for its rows and the ranks
+ * sum them with an NCCL all-reduce — the role of reduceByKey(_.merge(_)) over the per-partition
+ * DTStatsAggregators in RandomForest.findBestSplits.  Every rank returns the same forest, identical
+ * to the single-GPU forest on the concatenated rows (integer histograms: reduction order is moot). */
+int emrf_fit_sharded(emrf_ctx_t* ctx, const emrf_params_t* params, const double* features_hd,
+                     const double* labels_hd, int64_t n_rows_local, int32_t n_features,
+                     const int64_t* partition_offsets_global, int32_t n_partitions_global,
+                     int32_t first_partition, int32_t n_partitions_local, emrf_forest_t** out);
+
 /* ---- Model: RandomForestClassificationModel ------------------------------------------------ */
 void emrf_forest_free(emrf_forest_t* f);
 int emrf_forest_info(const emrf_forest_t* f, int32_t* num_trees, int32_t* num_classes,

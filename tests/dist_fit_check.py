@@ -28,6 +28,25 @@ if rank == 0:
     for k in e:
         assert np.array_equal(e[k], o[k]), k
     print(f"DIST_FIT_OK world={world} nodes={model.totalNumNodes}")
+# ---- row-sharded: each rank passes only its rows; node histograms are all-reduced per group
+P = 32
+goff = np.array([(i * len(X)) // P for i in range(P + 1)], np.int64)
+p_lo, p_hi = (rank * P) // world, ((rank + 1) * P) // world
+r_lo, r_hi = int(goff[p_lo]), int(goff[p_hi])
+for kw in ({}, {"n": 9000}):            # second case: N <= 10000 → findSplits keeps every row
+    n = kw.get("n", len(X))
+    Xs, ys = X[:n], y[:n]
+    goff = np.array([(i * n) // P for i in range(P + 1)], np.int64)
+    r_lo, r_hi = int(goff[p_lo]), int(goff[p_hi])
+    rf2 = RandomForestClassifier(ctx).setNumTrees(7).setMaxDepth(7).setNumClasses(50).setMaxMemoryInMB(16)
+    m2 = rf2.fit(Dataset.shard(Xs[r_lo:r_hi], ys[r_lo:r_hi], goff, p_lo, p_hi - p_lo))
+    e2 = m2.export()
+    if rank == 0:
+        o2 = ob.fit(ob.make_params(num_trees=7, max_depth=7, num_classes=50, max_memory_mb=16), Xs, ys, goff).export()
+        for k in e2:
+            assert np.array_equal(e2[k], o2[k]), ("row-sharded", n, k)
+        print(f"DIST_ROWS_OK world={world} n={n} nodes={m2.totalNumNodes}")
+    e = e2
 # every rank must hold the same forest
 digest = torch.tensor([float(e["threshold"].sum()), float(e["stats"].sum()), float(len(e["left"]))], device="cuda",
                       dtype=torch.float64)

@@ -45,7 +45,7 @@ def test_reference_arm_runs_on_rank0_only(monkeypatch):
 
 
 @pytest.mark.gpu
-def test_tree_sharded_fit_matches_oracle_on_2_gpus():
+def test_tree_and_row_sharded_fits_match_oracle_on_2_gpus():
     import ctypes
     n = ctypes.c_int(0)
     cuda = ctypes.CDLL("libcuda.so.1")
@@ -58,3 +58,4 @@ def test_tree_sharded_fit_matches_oracle_on_2_gpus():
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "DIST_FIT_OK world=2" in r.stdout
+    assert r.stdout.count("DIST_ROWS_OK world=2") == 2

@@ -8,9 +8,11 @@ in HBM (CUDA events on the engine's stream); `e2e` is the same fit through the r
 (RandomForestClassifier.fit on a host Dataset): pinned host buffers, H2D of features inside the
 timed region, forest back on the host.
 
-N > 1 (one process per GPU, torchrun): ONE forest of 100*N trees, tree-sharded across the ranks
-(weak scaling: per-GPU work fixed); the only exchange is an NCCL all-reduce of the per-node split
-records each group.  torch is used for the rendezvous / barrier only.
+N > 1 (one process per GPU, torchrun): ONE forest of 100 trees on N x 1M rows, ROW-sharded across the
+ranks (weak scaling: 1M rows per GPU; north_star's mode for large shapes): each rank bins, bags and
+histograms its own rows and the ranks all-reduce the node histograms with NCCL every group.
+`--mode trees` instead shards the trees of one 100*N-tree forest (all rows on every rank).  torch is
+used for the rendezvous / barrier only.
 
 --impl reference: times the CPU oracle (the restated Spark MLlib algorithm; no JVM/Spark exists on
 this box, so there is no oracle/_ref) on the host cores, on a bounded sample of the same workload.
@@ -35,9 +37,12 @@ METRIC, UNIT = "rf_fit_rows_trees_per_sec", "rows*trees/s"
 CPU_SAMPLE_TREES = 40
 
 
-def workload_name(n_gpus):
-    return (f"BASELINE.json configs[1]: RF {TREES_PER_GPU * n_gpus} trees, depth {MAX_DEPTH}, maxBins {MAX_BINS}, "
-            f"{N_ROWS} synthetic draw rows x {N_FEATURES} features, {N_CLASSES}-class label, {N_PARTS} partitions")
+def workload_name(n_gpus, mode="rows"):
+    trees = TREES_PER_GPU * (n_gpus if mode == "trees" else 1)
+    rows = N_ROWS * (n_gpus if mode == "rows" else 1)
+    parts = N_PARTS * (n_gpus if mode == "rows" else 1)
+    return (f"BASELINE.json configs[1]: RF {trees} trees, depth {MAX_DEPTH}, maxBins {MAX_BINS}, "
+            f"{rows} synthetic draw rows x {N_FEATURES} features, {N_CLASSES}-class label, {parts} partitions")
 
 
 class ClockSampler:
@@ -129,6 +134,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="rows", choices=["rows", "trees"], help="how N > 1 GPUs share one forest")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -161,8 +167,11 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    T = TREES_PER_GPU * world
-    X, y = synth.flat(N_ROWS, N_FEATURES, N_CLASSES)
+    mode = args.mode if world > 1 else "rows"
+    T = TREES_PER_GPU * (world if mode == "trees" else 1)
+    n_global = N_ROWS * (world if mode == "rows" else 1)
+    # rows mode: this rank owns global rows [rank*1M, (rank+1)*1M) = global partitions [rank*1024, (rank+1)*1024)
+    X, y = synth.flat(N_ROWS, N_FEATURES, N_CLASSES, row_start=rank * N_ROWS if mode == "rows" else 0)
     # pinned host copies (for the e2e leg) and device-resident copies (for `value`)
     hX, hy, dX, dy = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
     _lib.check(L.emrf_host_alloc_pinned(X.nbytes, C.byref(hX)))
@@ -178,8 +187,16 @@ def main():
 
     rf = (RandomForestClassifier(ctx).setNumTrees(T).setMaxDepth(MAX_DEPTH).setMaxBins(MAX_BINS)
           .setNumClasses(N_CLASSES).setSeed(207336481))
-    ds_dev = Dataset(dX.value, dy.value, num_partitions=N_PARTS, n_rows=N_ROWS, n_features=N_FEATURES)
-    ds_host = Dataset(pX, py, num_partitions=N_PARTS)
+    if world > 1 and mode == "rows":
+        goff = np.array([(i * n_global) // (N_PARTS * world) for i in range(N_PARTS * world + 1)], np.int64)
+        assert goff[rank * N_PARTS] == rank * N_ROWS and goff[(rank + 1) * N_PARTS] == (rank + 1) * N_ROWS
+        local = goff[rank * N_PARTS:(rank + 1) * N_PARTS + 1] - goff[rank * N_PARTS]
+        shard = dict(partition_offsets=local, global_partition_offsets=goff, first_partition=rank * N_PARTS)
+        ds_dev = Dataset(dX.value, dy.value, n_rows=N_ROWS, n_features=N_FEATURES, **shard)
+        ds_host = Dataset(pX, py, **shard)
+    else:
+        ds_dev = Dataset(dX.value, dy.value, num_partitions=N_PARTS, n_rows=N_ROWS, n_features=N_FEATURES)
+        ds_host = Dataset(pX, py, num_partitions=N_PARTS)
     # Dataset() copies non-contiguous input only; pX is contiguous, so ds_host.features aliases the pinned buffer
     assert ds_host.features.ctypes.data == hX.value
 
@@ -220,7 +237,7 @@ def main():
             dist.destroy_process_group()
         return
 
-    units = N_ROWS * T * args.steps
+    units = n_global * T * args.steps
     value = units / (step_ms / 1e3)
     hist_ms = float(np.sum([t["hist_kernel_ms"] for t in tms]))
     hist_bytes = float(np.sum([t["hist_alg_bytes"] for t in tms]))
@@ -239,7 +256,9 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": step_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u32", "data": "synthetic",
-        "config": {"workload": workload_name(world), "parallelism": "tree-sharded x%d" % world if world > 1 else "1 GPU",
+        "config": {"workload": workload_name(world, mode),
+                   "parallelism": ("row-sharded x%d (NCCL all-reduce of node histograms per group)" % world if mode == "rows"
+                                   else "tree-sharded x%d" % world) if world > 1 else "1 GPU",
                    "l2": "inputs (512 MB f64 features, 1 GB entry lists) are larger than the 126 MB L2; no explicit flush",
                    "seed": 207336481, "timing": "CUDA events on the engine stream per fit (emrf_timings_t.total_ms)",
                    "wall_ms_per_step": wall_ms / args.steps},

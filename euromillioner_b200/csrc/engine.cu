@@ -20,6 +20,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -140,6 +141,7 @@ struct emrf_ctx {
   int rank = 0, world = 1;
   cudaStream_t stream = nullptr;
   int sm_count = 148;
+  int host_threads = 1;   // OpenMP threads for the host scheduler's parallel pieces (cores / ranks on this node)
   size_t smem_optin = 0;
   emrf_timings_t tm;
   std::mutex fit_mu;
@@ -172,6 +174,7 @@ static int ctx_init(emrf_ctx* c, int device) {
   c->smem_optin = prop.sharedMemPerBlockOptin;
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   memset(&c->tm, 0, sizeof(c->tm));
+  c->host_threads = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
   return EMRF_OK;
 }
 
@@ -217,6 +220,8 @@ extern "C" int emrf_ctx_create_dist(int32_t device, int32_t rank, int32_t world,
   if (rc != EMRF_OK) { delete c; return rc; }
   c->rank = rank;
   c->world = world;
+  // launchers such as torchrun export OMP_NUM_THREADS=1; size the host pool explicitly instead
+  c->host_threads = std::max(1, c->host_threads / std::max(1, world));
   if (world > 1) {
     if (!nccl_uid) { delete c; return fail(EMRF_ERR_ARG, "nccl_uid is NULL"); }
     void* lib = nccl_open();
@@ -625,10 +630,10 @@ static void export_pass_b(const HTree& t, int ni, int C, const std::vector<Expor
     export_pass_b(t, n.right, C, info, base, rpos, fo);
   }
 }
-static void export_forest(const std::vector<HTree>& trees, int C, emrf_forest& fo) {
+static void export_forest(const std::vector<HTree>& trees, int C, emrf_forest& fo, int n_threads) {
   const int T = (int)trees.size();
   std::vector<std::vector<ExportInfo>> info(T);
-#pragma omp parallel for schedule(dynamic)
+#pragma omp parallel for schedule(dynamic) num_threads(n_threads)
   for (int t = 0; t < T; t++) {
     info[t].resize(trees[t].pool.size());
     export_pass_a(trees[t], 0, C, info[t]);
@@ -638,7 +643,7 @@ static void export_forest(const std::vector<HTree>& trees, int C, emrf_forest& f
   fo.nodes.resize((size_t)fo.tree_off[T]);
   fo.counts_len = (size_t)fo.tree_off[T] * C;
   fo.counts.reset(new uint32_t[fo.counts_len]);  // first touched by the parallel fill below
-#pragma omp parallel for schedule(dynamic)
+#pragma omp parallel for schedule(dynamic) num_threads(n_threads)
   for (int t = 0; t < T; t++) export_pass_b(trees[t], 0, C, info[t], fo.tree_off[t], 0, fo);
 }
 static void ensure_double_stats(emrf_forest* f) {
@@ -841,7 +846,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         batch_seed.resize(K);
         batch_state.resize(K);
         for (int j = 0; j < K; j++) { batch_seed[j] = rng.next_long(); batch_state[j] = rng.state; }
-#pragma omp parallel for schedule(static) if (K >= 64)
+#pragma omp parallel for schedule(static) num_threads(c->host_threads) if (K >= 64)
         for (int j = 0; j < K; j++) {
           int len = 0;
           int32_t* sub = &batch_feat[(size_t)j * f_sub];
@@ -1134,7 +1139,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
 
   // ---- topNodes.map(_.toNode(prune = true))
   double t_host0 = now_ms();
-  export_forest(trees, C, *fo);
+  export_forest(trees, C, *fo, c->host_threads);
   { const double d_ = now_ms() - t_host0; host_ms += d_; tm.host_export_ms = d_; }
   CU(cudaEventRecord(ev_end, st));
   CU(cudaStreamSynchronize(st));

@@ -151,7 +151,26 @@ struct emrf_ctx {
   void* nccl_comm = nullptr;
   // grow-only scratch reused across groups
   DevBuf d_group, d_results, d_ghist, d_tickets, d_split, d_part;
-  PinnedBuf h_group, h_results, h_split, h_part;
+  PinnedBuf h_group, h_split, h_part;
+  // pinned arena that keeps every group's split records for the whole fit (nodes point into it)
+  std::vector<std::unique_ptr<PinnedBuf>> arena;
+  size_t arena_chunk = 0, arena_used = 0;
+  void arena_reset() { arena_chunk = 0; arena_used = 0; }
+  void* arena_alloc(size_t bytes) {
+    bytes = (bytes + 255) & ~(size_t)255;
+    while (true) {
+      if (arena_chunk < arena.size()) {
+        PinnedBuf& b = *arena[arena_chunk];
+        if (arena_used + bytes <= b.bytes) { void* p = (char*)b.p + arena_used; arena_used += bytes; return p; }
+        arena_chunk++; arena_used = 0;
+        continue;
+      }
+      std::unique_ptr<PinnedBuf> nb(new PinnedBuf());
+      if (nb->ensure(std::max<size_t>(bytes, (size_t)48 << 20)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+      arena.push_back(std::move(nb));
+      arena_used = 0;
+    }
+  }
 };
 
 static int ctx_init(emrf_ctx* c, int device) {
@@ -573,18 +592,25 @@ struct emrf_forest {
 struct HNode {
   int32_t id = 1;
   int32_t left = -1, right = -1;
-  bool is_leaf = false, valid = true, has_stats = false;
+  bool is_leaf = false, valid = true;
   int32_t feature = -1, split_bin = -1;
   double threshold = 0.0, gain = std::numeric_limits<double>::quiet_NaN(), impurity = 0.0;
   uint64_t seg_start = 0;
   uint32_t seg_len = 0;
   uint32_t buf = 0;
-  size_t counts_at = 0;  // index into the tree's counts pool (C words), valid when has_stats
+  // class counts = cnt_a[c] - (cnt_b ? cnt_b[c] : 0); both point into the fit's result arena (the
+  // split records copied back from the device): a left child shares its parent's "left" array, a
+  // right child is parent total minus parent left, a node that went through a group owns its totals.
+  const uint32_t* cnt_a = nullptr;
+  const uint32_t* cnt_b = nullptr;
 };
 struct HTree {
   std::vector<HNode> pool;
-  std::vector<uint32_t> counts;
 };
+static inline void node_counts(const HNode& n, int C, uint32_t* out) {
+  if (n.cnt_b) for (int c = 0; c < C; c++) out[c] = n.cnt_a[c] - n.cnt_b[c];
+  else memcpy(out, n.cnt_a, (size_t)C * 4);
+}
 
 static int first_max(const uint32_t* a, int C) {
   int mi = 0;
@@ -605,9 +631,11 @@ static void export_pass_a(const HTree& t, int ni, int C, std::vector<ExportInfo>
     export_pass_a(t, n.right, C, info);
     const ExportInfo &l = info[n.left], &r = info[n.right];
     if (l.leaf && r.leaf && l.pred == r.pred) { e.leaf = true; e.pred = l.pred; e.size = 1; }
-    else { e.leaf = false; e.pred = first_max(&t.counts[n.counts_at], C); e.size = 1 + l.size + r.size; }
+    else { e.leaf = false; e.pred = first_max(n.cnt_a, C); e.size = 1 + l.size + r.size; }  // a split node owns its totals
   } else {
-    e.leaf = true; e.pred = first_max(&t.counts[n.counts_at], C); e.size = 1;
+    uint32_t tmp[256];
+    node_counts(n, C, tmp);
+    e.leaf = true; e.pred = first_max(tmp, C); e.size = 1;
   }
 }
 static void export_pass_b(const HTree& t, int ni, int C, const std::vector<ExportInfo>& info, int64_t base, int32_t pos,
@@ -615,7 +643,7 @@ static void export_pass_b(const HTree& t, int ni, int C, const std::vector<Expor
   const HNode& n = t.pool[ni];
   const ExportInfo& e = info[ni];
   FlatNode& f = fo.nodes[base + pos];
-  memcpy(&fo.counts[(size_t)(base + pos) * C], &t.counts[n.counts_at], (size_t)C * 4);
+  node_counts(n, C, &fo.counts[(size_t)(base + pos) * C]);
   f.id = n.id;
   f.prediction = (double)e.pred;
   if (e.leaf) {
@@ -806,10 +834,18 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   std::unique_ptr<emrf_forest> fo_guard(fo);
   fo->num_trees = T; fo->num_classes = C; fo->num_features = F; fo->f_sub = f_sub;
 
-  std::vector<GroupEntry> group;
-  std::vector<int32_t> group_feat;
-  std::vector<int> trees_seen;
-  std::vector<std::vector<int>> nodes_for_tree;   // per tree of the group (slot = first-seen order)
+  // A group as selectNodesToSplit leaves it: popped nodes in pop order, their feature subsets, the
+  // trees in first-seen order (= mutable.HashMap insertion order) and each tree's nodes.
+  struct GroupSel {
+    std::vector<GroupEntry> group;
+    std::vector<int32_t> feat;
+    std::vector<int> trees_seen;
+    std::vector<std::vector<int>> nodes_for_tree;
+    void clear() { group.clear(); feat.clear(); trees_seen.clear(); nodes_for_tree.clear(); }
+  };
+  GroupSel sel_a, sel_b;
+  GroupSel* cur = &sel_a;
+  GroupSel* nxt = &sel_b;
   std::vector<int> tree_slot(T, -1);
   std::vector<int32_t> batch_feat;
   std::vector<int64_t> batch_bins, batch_seed;
@@ -826,15 +862,16 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_ev, part_ev;
   double host_ms = 0.0, host_sel = 0.0, host_upd = 0.0;
   static const bool verify_gains = getenv("EMRF_VERIFY_GAINS") != nullptr;
+  c->arena_reset();
 
-  while (!stack.empty()) {
-    double t_host0 = now_ms();
-    // ---- selectNodesToSplit.  The driver RNG hands each popped node one nextLong() (drawn BEFORE
-    // the memory check, so the node that does not fit consumes a draw too); the reservoir sampling
-    // a seed implies is independent per node, so a batch of candidate nodes is drawn sequentially
-    // (cheap LCG steps, state saved after every draw), sampled in parallel, and then admitted
-    // sequentially exactly as Spark does; the RNG is rewound to just after the rejected node's draw.
-    group.clear(); group_feat.clear(); trees_seen.clear(); nodes_for_tree.clear();
+  // ---- selectNodesToSplit.  The driver RNG hands each popped node one nextLong() (drawn BEFORE the
+  // memory check, so the node that does not fit consumes a draw too); the reservoir sampling a seed
+  // implies is independent per node, so a batch of candidate nodes is drawn sequentially (cheap LCG
+  // steps, state saved after every draw), sampled in parallel, and then admitted sequentially exactly
+  // as Spark does; the RNG is rewound to just after the rejected node's draw.  Needs only the stack,
+  // so it runs on the host while the GPU is still partitioning the previous group.
+  auto select_group = [&](GroupSel& G) {
+    G.clear();
     int64_t mem = 0;
     bool group_done = false;
     while (!stack.empty() && !group_done) {
@@ -866,10 +903,14 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         const int64_t node_mem = (int64_t)C * batch_bins[j] * 8;
         if (mem + node_mem <= max_mem || mem == 0) {
           stack.pop_back();
-          if (tree_slot[top.first] < 0) { tree_slot[top.first] = (int)trees_seen.size(); trees_seen.push_back(top.first); nodes_for_tree.emplace_back(); }
-          nodes_for_tree[tree_slot[top.first]].push_back((int)group.size());
-          group.push_back({top.first, top.second, (int)group_feat.size()});
-          group_feat.insert(group_feat.end(), batch_feat.begin() + (size_t)j * f_sub, batch_feat.begin() + (size_t)(j + 1) * f_sub);
+          if (tree_slot[top.first] < 0) {
+            tree_slot[top.first] = (int)G.trees_seen.size();
+            G.trees_seen.push_back(top.first);
+            G.nodes_for_tree.emplace_back();
+          }
+          G.nodes_for_tree[tree_slot[top.first]].push_back((int)G.group.size());
+          G.group.push_back({top.first, top.second, (int)G.feat.size()});
+          G.feat.insert(G.feat.end(), batch_feat.begin() + (size_t)j * f_sub, batch_feat.begin() + (size_t)(j + 1) * f_sub);
           mem += node_mem;
         } else {
           if (subsampling) rng.state = batch_state[j];  // draws after the rejected node's are undone
@@ -878,6 +919,18 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         }
       }
     }
+    for (int t : G.trees_seen) tree_slot[t] = -1;   // slots are recomputed by whoever consumes the group
+  };
+
+  {
+    const double t0 = now_ms();
+    select_group(*cur);
+    const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
+  }
+  while (!cur->group.empty()) {
+    double t_host0 = now_ms();
+    std::vector<GroupEntry>& group = cur->group;
+    std::vector<int32_t>& group_feat = cur->feat;
     const int n_nodes = (int)group.size();
     fo->group_sizes.push_back(n_nodes);
     for (auto& g : group) {
@@ -886,8 +939,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       for (int k = 0; k < f_sub; k++) fo->trace.push_back(group_feat[g.feat_at + k]);
     }
 
-    // ---- which nodes this rank computes (tree-sharded multi-GPU: own trees only)
-    // tiles
+    // ---- tiles (tree-sharded multi-GPU: own trees only)
     uint64_t total_entries = 0;
     for (auto& g : group)
       if (mine(g.tree)) total_entries += trees[g.tree].pool[g.pool].seg_len;
@@ -927,7 +979,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const size_t off_total = off_left + n_rec * C * 4;
     const size_t res_bytes = off_total + n_rec * C * 4;
     CU(c->d_results.ensure(res_bytes));
-    CU(c->h_results.ensure(res_bytes));
+    char* h_res = (char*)c->arena_alloc(res_bytes);   // kept until the forest is exported
+    if (!h_res) return fail(EMRF_ERR_CUDA, "out of pinned host memory for the split-record arena");
     CU(c->d_tickets.ensure(n_rec * 4));
     CU(c->d_ghist.ensure((size_t)std::max(n_slots, 1) * slot_words * 4));
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_sel += d_; }
@@ -978,7 +1031,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     } else if (c->world > 1) {
       TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
     }
-    CU(cudaMemcpyAsync(c->h_results.p, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     tm.hist_units += (int64_t)total_entries;
     tm.hist_alg_bytes += (int64_t)total_entries * (f_sub + 6);
@@ -986,18 +1039,20 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       if (mine(g.tree)) tm.hist_alg_bytes += (int64_t)slot_words * 4;
     tm.total_nodes_split += n_nodes;
 
-    // ---- driver side of findBestSplits: node updates in Scala map iteration order
+    // ---- driver side of findBestSplits: node updates in Scala map iteration order.  Class counts
+    // are not copied: nodes point into the arena records.
     t_host0 = now_ms();
-    const kern::ScanResult* res = (const kern::ScanResult*)c->h_results.p;
-    const uint32_t* res_left = (const uint32_t*)((char*)c->h_results.p + off_left);
-    const uint32_t* res_total = (const uint32_t*)((char*)c->h_results.p + off_total);
+    const kern::ScanResult* res = (const kern::ScanResult*)h_res;
+    const uint32_t* res_left = (const uint32_t*)(h_res + off_left);
+    const uint32_t* res_total = (const uint32_t*)(h_res + off_total);
     std::vector<kern::SplitNode> splits;
     struct SplitRef { int tree, pool; };
     std::vector<SplitRef> split_ref;
-    const std::vector<int> order = hl::group_tree_visit_order(trees_seen);
+    for (size_t q = 0; q < cur->trees_seen.size(); q++) tree_slot[cur->trees_seen[q]] = (int)q;
+    const std::vector<int> order = hl::group_tree_visit_order(cur->trees_seen);
     std::vector<uint32_t> rightc(C);
     for (int t : order) {
-      for (int gi : nodes_for_tree[tree_slot[t]]) {
+      for (int gi : cur->nodes_for_tree[tree_slot[t]]) {
         const GroupEntry& g = group[gi];
         HTree& tr = trees[t];
         // combine feature chunks: first maximum in subset order
@@ -1012,23 +1067,17 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         const uint32_t* leftc = res_left + rec * C;
         const int id = tr.pool[g.pool].id;
         const int level = 31 - __builtin_clz((unsigned)id);
-        // node stats: parent calculator = class totals; impurities and gain come from the scan
-        // kernel (bit-exact IEEE, Spark's operation order); EMRF_VERIFY_GAINS=1 recomputes them here.
-        if (!tr.pool[g.pool].has_stats) {
-          tr.pool[g.pool].counts_at = tr.counts.size();
-          tr.counts.insert(tr.counts.end(), totc, totc + C);
-          tr.pool[g.pool].has_stats = true;
-        }
+        // impurities and gain come from the scan kernel (bit-exact IEEE, Spark's operation order);
+        // EMRF_VERIFY_GAINS=1 recomputes them here.
         const double pimp = res[rec].impurity;
         double gain = kern::kInvalidGain, limp = 0.0, rimp = 0.0;
         bool valid = false;
         if (best >= 0 && res[rec].valid) {
-          for (int cc = 0; cc < C; cc++) rightc[cc] = totc[cc] - leftc[cc];
           gain = res[rec].gain; limp = res[rec].left_impurity; rimp = res[rec].right_impurity;
           valid = true;
           if (verify_gains) {
             uint64_t lc = 0, rc = 0;
-            for (int cc = 0; cc < C; cc++) { lc += leftc[cc]; rc += rightc[cc]; }
+            for (int cc = 0; cc < C; cc++) { rightc[cc] = totc[cc] - leftc[cc]; lc += leftc[cc]; rc += rightc[cc]; }
             const double hl_ = hl::impurity_of(P.impurity, leftc, C), hr_ = hl::impurity_of(P.impurity, rightc.data(), C);
             const double hp_ = hl::impurity_of(P.impurity, totc, C);
             const double tc = (double)(lc + rc);
@@ -1041,6 +1090,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         {
           HNode& n = tr.pool[g.pool];
           n.is_leaf = is_leaf; n.gain = gain; n.impurity = pimp; n.valid = valid;
+          n.cnt_a = totc; n.cnt_b = nullptr;
         }
         if (!is_leaf) {
           const int feat = group_feat[g.feat_at + res[rec].k];
@@ -1049,42 +1099,37 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           const bool l_leaf = child_leaf || (limp == 0.0);
           const bool r_leaf = child_leaf || (rimp == 0.0);
           const int li = (int)tr.pool.size();
-          HNode l, r;
-          l.id = 2 * id; l.is_leaf = l_leaf; l.has_stats = true; l.impurity = limp;
-          l.counts_at = tr.counts.size();
-          tr.counts.insert(tr.counts.end(), leftc, leftc + C);
-          r.id = 2 * id + 1; r.is_leaf = r_leaf; r.has_stats = true; r.impurity = rimp;
-          r.counts_at = tr.counts.size();
-          tr.counts.insert(tr.counts.end(), rightc.begin(), rightc.end());
-          tr.pool.push_back(l);
-          tr.pool.push_back(r);
+          tr.pool.emplace_back();
+          tr.pool.emplace_back();
+          HNode& l = tr.pool[li];
+          HNode& r = tr.pool[li + 1];
+          l.id = 2 * id; l.is_leaf = l_leaf; l.impurity = limp; l.cnt_a = leftc;
+          r.id = 2 * id + 1; r.is_leaf = r_leaf; r.impurity = rimp; r.cnt_a = totc; r.cnt_b = leftc;
           HNode& n = tr.pool[g.pool];
           n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
           n.left = li; n.right = li + 1;
           if (!l_leaf) stack.emplace_back(t, li);
           if (!r_leaf) stack.emplace_back(t, li + 1);
           if ((!l_leaf || !r_leaf) && mine(t)) {
-            kern::SplitNode s;
-            s.seg_start = n.seg_start; s.seg_len = n.seg_len; s.buf = n.buf;
-            s.feature = feat; s.split_bin = sbin; s.tile_begin = 0; s.n_tiles = 0;
-            splits.push_back(s);
+            kern::SplitNode sn;
+            sn.seg_start = n.seg_start; sn.seg_len = n.seg_len; sn.buf = n.buf;
+            sn.feature = feat; sn.split_bin = sbin; sn.tile_begin = 0; sn.n_tiles = 0;
+            splits.push_back(sn);
             split_ref.push_back({t, g.pool});
           }
         }
       }
     }
-    for (int t : trees_seen) tree_slot[t] = -1;
-    { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
+    for (int t : cur->trees_seen) tree_slot[t] = -1;
 
-    // ---- K4: partition the split nodes' segments, learn the children's segment sizes
-    if (!splits.empty()) {
-      t_host0 = now_ms();
-      const int ns = (int)splits.size();
+    // ---- K4: partition the split nodes' segments (asynchronously) ...
+    const int ns = (int)splits.size();
+    if (ns) {
       uint32_t ptiles = 0;
-      for (auto& s : splits) {
-        s.tile_begin = ptiles;
-        s.n_tiles = (s.seg_len + kern::kPartTile - 1) / kern::kPartTile;
-        ptiles += s.n_tiles;
+      for (auto& sn : splits) {
+        sn.tile_begin = ptiles;
+        sn.n_tiles = (sn.seg_len + kern::kPartTile - 1) / kern::kPartTile;
+        ptiles += sn.n_tiles;
       }
       const size_t off_ptn = align_up(sizeof(kern::SplitNode) * (size_t)ns, 16);
       const size_t split_bytes = off_ptn + (size_t)ptiles * 4;
@@ -1122,6 +1167,16 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       part_ev.emplace_back(p0, p1);
       CU(cudaGetLastError());
       CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
+    } else {
+      const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_;
+    }
+    // ---- ... while the host already selects the next group (needs only the stack)
+    {
+      const double t0 = now_ms();
+      select_group(*nxt);
+      const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
+    }
+    if (ns) {
       CU(cudaStreamSynchronize(st));
       t_host0 = now_ms();
       const uint64_t* nl = (const uint64_t*)c->h_part.p;
@@ -1135,6 +1190,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       }
       { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
     }
+    std::swap(cur, nxt);
   }
 
   // ---- topNodes.map(_.toNode(prune = true))

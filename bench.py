@@ -276,7 +276,7 @@ def main():
                      "share_of_step": hist_ms / step_ms},
         "phases_ms_per_step": {k: float(np.mean([t[k] for t in tms])) for k in (
             "find_splits_ms", "bin_ms", "bag_ms", "hist_kernel_ms", "partition_ms", "host_scheduler_ms",
-            "host_select_ms", "host_update_ms", "host_export_ms")},
+            "host_select_ms", "host_update_ms", "host_export_ms", "bag_kernel_ms")},
         "groups_per_step": int(tms[0]["num_groups"]), "total_nodes": int(model.totalNumNodes),
         "gain_mismatches": int(np.sum([t["gain_mismatches"] for t in tms])),
     }

@@ -31,7 +31,7 @@ class EmrfTimings(C.Structure):
         "hist_kernel_ms", "partition_ms", "host_scheduler_ms")] + [(n, C.c_int64) for n in (
             "hist_launches", "kernel_launches", "hist_alg_bytes", "hist_units", "num_groups",
             "total_nodes_split", "gain_mismatches", "h2d_bytes", "d2h_bytes")] + [
-        (n, C.c_double) for n in ("host_select_ms", "host_update_ms", "host_export_ms")]
+        (n, C.c_double) for n in ("host_select_ms", "host_update_ms", "host_export_ms", "bag_kernel_ms")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

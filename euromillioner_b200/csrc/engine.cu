@@ -69,6 +69,7 @@ struct DevBuf {
   DevBuf() {}
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
+  DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
   ~DevBuf() { release(); }
   void release() {
     if (p) cudaFree(p);
@@ -140,6 +141,7 @@ struct emrf_ctx {
   int device = 0;
   int rank = 0, world = 1;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;   // bagging runs here, underneath input copy / findSplits / binning
   int sm_count = 148;
   int host_threads = 1;   // OpenMP threads for the host scheduler's parallel pieces (cores / ranks on this node)
   size_t smem_optin = 0;
@@ -192,6 +194,7 @@ static int ctx_init(emrf_ctx* c, int device) {
   c->sm_count = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
   memset(&c->tm, 0, sizeof(c->tm));
   c->host_threads = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
   return EMRF_OK;
@@ -263,6 +266,7 @@ extern "C" void emrf_ctx_destroy(emrf_ctx_t* c) {
     if (d) d(c->nccl_comm);
   }
   if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+  if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
   delete c;
 }
 extern "C" int emrf_get_timings(const emrf_ctx_t* c, emrf_timings_t* out) {
@@ -377,7 +381,9 @@ static int stage_input(emrf_ctx* c, const void* src_hd, size_t bytes, DevBuf& ow
 // ---------------------------------------------------------------------------------------------
 static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX, int64_t N_local, int F, const int64_t* part_off_local,
                            int n_parts_local, DevBuf& d_thr, DevBuf& d_ns, std::vector<double>& h_thr, std::vector<int>& h_ns,
-                           const ShardSpec* sh = nullptr) {
+                           const ShardSpec* sh = nullptr, std::vector<DevBuf>* keep = nullptr) {
+  // `keep`: where temporaries are parked instead of being freed here — cudaFree synchronises the whole
+  // device and would stall this stream behind the bagging kernel running on the other one.
   // metadata and sampling are defined on the WHOLE dataset
   const int64_t N = sh ? sh->n_rows_global : N_local;
   const int64_t* part_off = sh ? sh->goff : part_off_local;
@@ -438,7 +444,8 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
                                                                                     P.find_splits_policy == 0 ? 1 : 0);
         c->tm.kernel_launches += 1;
         CU(cudaGetLastError());
-        CU(cudaStreamSynchronize(c->stream));  // own_rows/own_pos/d_or/d_op die here
+        CU(cudaStreamSynchronize(c->stream));  // own_rows/own_pos die here
+        if (keep) { keep->push_back(std::move(d_or)); keep->push_back(std::move(d_op)); }
       }
       const int use_smem = ((size_t)n_pad * 8 <= 128 * 1024) ? 1 : 0;
       const size_t smem = use_smem ? (size_t)n_pad * 8 : 0;
@@ -452,7 +459,8 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
       c->tm.h2d_bytes += sampled ? (int64_t)n_s * 8 : 0;
       CU(cudaMemcpyAsync(h_thr.data(), d_thr.p, (size_t)F * TS * 8, cudaMemcpyDeviceToHost, c->stream));
       CU(cudaMemcpyAsync(h_ns.data(), d_ns.p, (size_t)F * 4, cudaMemcpyDeviceToHost, c->stream));
-      CU(cudaStreamSynchronize(c->stream));  // d_rows/d_S/rows die here
+      CU(cudaStreamSynchronize(c->stream));  // rows dies here
+      if (keep) { keep->push_back(std::move(d_rows)); keep->push_back(std::move(d_S)); }
     }
   }
   for (int f = 0; f < F; f++)
@@ -480,46 +488,58 @@ static int run_bin(emrf_ctx* c, const double* dX, int64_t N, int F, const double
   return EMRF_OK;
 }
 
-static int run_bag(emrf_ctx* c, const emrf_params_t& P, int64_t N, const int64_t* part_off, int n_parts, uint8_t* d_w,
-                   int* max_w_out) {
-  const int T = P.num_trees;
+// Bootstrap weights.  bag_launch only enqueues (on `stream`): it depends on nothing but the partition
+// layout, so emrf_fit runs it on a second stream underneath the input copy, findSplits and binning.
+struct BagJob {
   DevBuf d_off, d_max;
-  CU(d_off.alloc((size_t)(n_parts + 1) * 8));
-  CU(d_max.alloc(4));
-  CU(cudaMemcpyAsync(d_off.p, part_off, (size_t)(n_parts + 1) * 8, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemsetAsync(d_max.p, 0, 4, c->stream));
+};
+static int bag_launch(emrf_ctx* c, cudaStream_t stream, const emrf_params_t& P, int64_t N, const int64_t* part_off, int n_parts,
+                      uint8_t* d_w, BagJob& job) {
+  const int T = P.num_trees;
+  CU(job.d_off.alloc((size_t)(n_parts + 1) * 8));
+  CU(job.d_max.alloc(4));
+  CU(cudaMemcpyAsync(job.d_off.p, part_off, (size_t)(n_parts + 1) * 8, cudaMemcpyHostToDevice, stream));
+  CU(cudaMemsetAsync(job.d_max.p, 0, 4, stream));
   if (T > 1) {
     const double mean = P.subsampling_rate;
     const double p_exp = std::exp(-mean);
     static const bool serial = getenv("EMRF_BAG_SERIAL") != nullptr;  // one thread per partition (cross-check)
     if (serial) {
       CU(cudaFuncSetAttribute(kern::bag_poisson_serial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kern::kBagSmemBytes));
-      kern::bag_poisson_serial_kernel<<<(n_parts + 31) / 32, 32, kern::kBagSmemBytes, c->stream>>>(
-          P.seed, d_off.as<int64_t>(), n_parts, T, mean, p_exp, d_w, d_max.as<int>());
+      kern::bag_poisson_serial_kernel<<<(n_parts + 31) / 32, 32, kern::kBagSmemBytes, stream>>>(
+          P.seed, job.d_off.as<int64_t>(), n_parts, T, mean, p_exp, d_w, job.d_max.as<int>());
     } else {
       const size_t smem = sizeof(kern::BagSmem);
       CU(cudaFuncSetAttribute(kern::bag_poisson_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      kern::bag_poisson_kernel<<<(n_parts + kern::kBagWarps - 1) / kern::kBagWarps, kern::kBagWarps * 32, smem, c->stream>>>(
-          P.seed, d_off.as<int64_t>(), n_parts, T, mean, p_exp, d_w, d_max.as<int>());
+      kern::bag_poisson_kernel<<<(n_parts + kern::kBagWarps - 1) / kern::kBagWarps, kern::kBagWarps * 32, smem, stream>>>(
+          P.seed, job.d_off.as<int64_t>(), n_parts, T, mean, p_exp, d_w, job.d_max.as<int>());
     }
   } else if (P.subsampling_rate == 1.0) {
-    CU(cudaMemsetAsync(d_w, 1, (size_t)N * T, c->stream));
-    int one = 1;
-    CU(cudaMemcpyAsync(d_max.p, &one, 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemsetAsync(d_w, 1, (size_t)N * T, stream));
+    CU(cudaMemsetAsync(job.d_max.p, 0, 4, stream));
   } else {
-    kern::bag_bernoulli_kernel<<<(n_parts + 63) / 64, 64, 0, c->stream>>>(P.seed, d_off.as<int64_t>(), n_parts, T,
-                                                                           P.subsampling_rate, d_w);
-    int one = 1;
-    CU(cudaMemcpyAsync(d_max.p, &one, 4, cudaMemcpyHostToDevice, c->stream));
+    kern::bag_bernoulli_kernel<<<(n_parts + 63) / 64, 64, 0, stream>>>(P.seed, job.d_off.as<int64_t>(), n_parts, T,
+                                                                         P.subsampling_rate, d_w);
   }
   c->tm.kernel_launches += 1;
   CU(cudaGetLastError());
+  return EMRF_OK;
+}
+// after the stream that ran bag_launch has been waited for / synchronised
+static int bag_finish(emrf_ctx* c, cudaStream_t stream, const emrf_params_t& P, BagJob& job, int* max_w_out) {
   int mw = 0;
-  CU(cudaMemcpyAsync(&mw, d_max.p, 4, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  CU(cudaMemcpyAsync(&mw, job.d_max.p, 4, cudaMemcpyDeviceToHost, stream));
+  CU(cudaStreamSynchronize(stream));
+  if (P.num_trees == 1) mw = 1;
   if (max_w_out) *max_w_out = mw;
   if (mw > 255) return fail(EMRF_ERR_LIMIT, "a bootstrap weight exceeded 255");
   return EMRF_OK;
+}
+static int run_bag(emrf_ctx* c, const emrf_params_t& P, int64_t N, const int64_t* part_off, int n_parts, uint8_t* d_w,
+                   int* max_w_out) {
+  BagJob job;
+  TRY(bag_launch(c, c->stream, P, N, part_off, n_parts, d_w, job));
+  return bag_finish(c, c->stream, P, job, max_w_out);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -709,6 +729,19 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
               ev_bag = c->events.get(), ev_end = c->events.get();
   CU(cudaEventRecord(ev_start, st));
 
+  // ---- bootstrap weights start now, on the second stream (they need only the partition layout)
+  DevBuf d_w;
+  BagJob bag_job;
+  cudaEvent_t ev_b0 = c->events.get(), ev_b1 = c->events.get();
+  CU(d_w.alloc((size_t)N * P.num_trees));
+  CU(cudaEventRecord(ev_b0, c->stream2));
+  {
+    emrf_params_t Pb = P;   // partition p of this rank is global partition first_part + p: seed + p_global + 1
+    if (row_sharded) Pb.seed = P.seed + sh->first_part;
+    TRY(bag_launch(c, c->stream2, Pb, N, part_off, n_parts, d_w.as<uint8_t>(), bag_job));
+  }
+  CU(cudaEventRecord(ev_b1, c->stream2));
+
   // ---- inputs
   DevBuf own_X, own_y;
   const void* dXv = nullptr;
@@ -745,7 +778,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   DevBuf d_thr, d_ns;
   std::vector<double> h_thr;
   std::vector<int> h_ns;
-  TRY(run_find_splits(c, P, dX, N, F, part_off, n_parts, d_thr, d_ns, h_thr, h_ns, sh));
+  std::vector<DevBuf> parked;   // temporaries released once nothing overlaps any more
+  TRY(run_find_splits(c, P, dX, N, F, part_off, n_parts, d_thr, d_ns, h_thr, h_ns, sh, &parked));
   CU(cudaEventRecord(ev_fs, st));
   const int TS = P.max_bins;
   std::vector<int> num_bins(F);
@@ -770,14 +804,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   DevBuf d_ent[2];
   std::vector<uint64_t> tree_base(T + 1, 0), tree_total(T, 0);
   {
-    DevBuf d_w;
-    CU(d_w.alloc((size_t)N * T));
     int maxw = 0;
-    {
-      emrf_params_t Pb = P;   // partition p of this rank is global partition first_part + p: seed + p_global + 1
-      if (row_sharded) Pb.seed = P.seed + sh->first_part;
-      TRY(run_bag(c, Pb, N, part_off, n_parts, d_w.as<uint8_t>(), &maxw));
-    }
+    CU(cudaStreamWaitEvent(st, ev_b1, 0));
+    TRY(bag_finish(c, st, P, bag_job, &maxw));
     const int n_tiles = (int)((N + kern::kListTile - 1) / kern::kListTile);
     DevBuf d_counts, d_totals, d_base;
     CU(d_counts.alloc((size_t)n_tiles * T * 4));
@@ -798,7 +827,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     tm.kernel_launches += 1;
     CU(cudaGetLastError());
     CU(cudaEventRecord(ev_bag, st));
-    CU(cudaStreamSynchronize(st));  // d_w and the tile tables are released here
+    CU(cudaStreamSynchronize(st));  // the tile tables are released here
+    d_w.release();
+    parked.clear();
   }
 
   // ---- metadata (DecisionTreeMetadata.buildMetadata)
@@ -1205,7 +1236,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(cudaEventElapsedTime(&ms, ev_start, ev_in)); tm.h2d_ms = copied ? ms : 0.0;
   CU(cudaEventElapsedTime(&ms, ev_in, ev_fs)); tm.find_splits_ms = ms;
   CU(cudaEventElapsedTime(&ms, ev_fs, ev_bin)); tm.bin_ms = ms;
-  CU(cudaEventElapsedTime(&ms, ev_bin, ev_bag)); tm.bag_ms = ms;
+  CU(cudaEventElapsedTime(&ms, ev_bin, ev_bag)); tm.bag_ms = ms;   // wait for the bag kernel (if still running) + list building
+  CU(cudaEventElapsedTime(&ms, ev_b0, ev_b1)); tm.bag_kernel_ms = ms;
   for (auto& pr : hist_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.hist_kernel_ms += ms; }
   for (auto& pr : part_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.partition_ms += ms; }
   tm.find_best_splits_ms = tm.hist_kernel_ms;

@@ -501,18 +501,31 @@ struct HistArgs {
   double min_info_gain;
 };
 
+// Correctly rounded a / b for integer-valued 0 <= a <= b < 2^32 with y = RN(1 / b): one multiply and
+// two FMA correction steps instead of the generic IEEE division sequence.  q0 = RN(a*y) is within
+// 2 ulp of a/b; r = a - b*q is exact in an FMA; q + r*y then differs from a/b by < 2^-52 ulp, far less
+// than the distance (>= 2^-33 ulp) from a quotient of two such integers to any rounding midpoint,
+// so RN(q + r*y) = RN(a / b) — the value the JVM's `/` produces.  The second step is a safety net.
+__device__ __forceinline__ double div_by(double a, double b, double y) {
+  double q = __dmul_rn(a, y);
+  double r = __fma_rn(-b, q, a);
+  q = __fma_rn(r, y, q);
+  r = __fma_rn(-b, q, a);
+  return __fma_rn(r, y, q);
+}
 // Impurity of the class-count vector v[c] = (sub ? sub[c] - cnt[c] : cnt[c]); total_u = sum v.
 // Gini: 1 - sum f^2 accumulated in class order; Entropy: -sum f*log2(f) over non-zero classes.
 __device__ __forceinline__ double impurity_dev(int kind, const uint32_t* cnt, const uint32_t* sub, int C,
                                                uint32_t total_u) {
   if (total_u == 0) return 0.0;
   const double total = (double)total_u;
+  const double y = __drcp_rn(total);
   if (kind == 0) {
     double imp = 1.0;
 #pragma unroll 5
     for (int c = 0; c < C; c++) {
       const uint32_t v = sub ? sub[c] - cnt[c] : cnt[c];
-      const double f = __ddiv_rn((double)v, total);  // v == 0 → f*f == 0 → imp unchanged, exactly
+      const double f = div_by((double)v, total, y);  // v == 0 → f*f == 0 → imp unchanged, exactly
       imp = __dsub_rn(imp, __dmul_rn(f, f));
     }
     return imp;
@@ -522,7 +535,7 @@ __device__ __forceinline__ double impurity_dev(int kind, const uint32_t* cnt, co
   for (int c = 0; c < C; c++) {
     const uint32_t v = sub ? sub[c] - cnt[c] : cnt[c];
     if (v) {
-      const double f = __ddiv_rn((double)v, total);
+      const double f = div_by((double)v, total, y);
       imp = __dsub_rn(imp, __dmul_rn(f, __ddiv_rn(log(f), ln2)));
     }
   }

@@ -62,7 +62,7 @@ typedef struct {
   double h2d_ms;            /* host→device copy of features/labels (0 when inputs were device-resident) */
   double find_splits_ms;    /* findSplits */
   double bin_ms;            /* TreePoint conversion (K1) */
-  double bag_ms;            /* BaggedPoint weights + per-tree row lists */
+  double bag_ms;            /* remaining wait for the bag kernel after binning + per-tree row lists */
   double find_best_splits_ms; /* all groups: histogram + split scan kernels (K2+K3), device time */
   double hist_kernel_ms;    /* of which: the histogram(+fused scan) kernel, summed over launches */
   double partition_ms;      /* row→node partition update kernels (K4), summed */
@@ -79,6 +79,7 @@ typedef struct {
   double host_select_ms;    /* host_scheduler_ms split: selectNodesToSplit + descriptor staging */
   double host_update_ms;    /*   driver-side node updates after each group */
   double host_export_ms;    /*   LearningNode.toNode(prune) + flat export */
+  double bag_kernel_ms;     /* the Poisson kernel alone (second stream, overlaps h2d/findSplits/binning) */
 } emrf_timings_t;
 
 const char* emrf_last_error(void);

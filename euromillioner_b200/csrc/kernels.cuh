@@ -243,7 +243,7 @@ __device__ __forceinline__ uint32_t well_temper(uint32_t z4) {
 struct BagSmem {
   uint32_t lut[4][4][256];                 // (M^2)^(2^s) for s = 1..4, one table per input byte
   uint32_t state[kBagWarps][624];
-  double ubuf[kBagWarps][32];
+  uint8_t stage[kBagWarps][32][32];        // per lane: the draws of the run it owns in the current block
   uint8_t obuf[kBagWarps][kBagObuf];
 };
 __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t seed, const int64_t* __restrict__ part_off,
@@ -287,13 +287,16 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
   const int64_t total = (hi - lo) * (int64_t)T;
   uint32_t carry = A[0];
   int i0 = 0;                      // state index of the block's first step
-  // lane-0 Poisson state
-  int64_t q = 0;
-  int n = 0, mx = 0, pos = 0;
-  double r = 1.0;
+  // Poisson state carried across blocks (uniform over the warp)
+  int64_t q = 0;                   // draws emitted so far
+  int pos = 0, mx = 0;
+  double carry_r = 1.0;            // running product / count of the draw left open by the previous block
+  int carry_n = 0;
   int64_t flushed = 0;
+  uint8_t* stage = S.stage[wv][lane];
+  uint8_t* ob = S.obuf[wv];
   while (true) {
-    // ---- 64 WELL steps -> 32 uniforms
+    // ---- 64 WELL steps -> 32 uniforms, one per lane
     const int i = wrap(i0 - 2 * lane);                 // index of this lane's first step
     const uint32_t m1a = A[wrap(i + 70)], m2a = A[wrap(i + 179)], m3a = A[wrap(i + 449)];
     const uint32_t m1b = A[wrap(i + 69)], m2b = A[wrap(i + 178)], m3b = A[wrap(i + 448)];
@@ -330,36 +333,69 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
     A[wrap(i - 1)] = ab;
     const uint64_t hi26 = (uint64_t)(well_temper(ba) >> 6) << 26;
     const uint64_t lo26 = well_temper(bb) >> 6;
-    S.ubuf[wv][lane] = __dmul_rn((double)(int64_t)(hi26 | lo26), 2.220446049250313e-16);
+    const double u = __dmul_rn((double)(int64_t)(hi26 | lo26), 2.220446049250313e-16);   // nextDouble()
     i0 = wrap(i0 - 64);
     __syncwarp();
-    // ---- PoissonDistribution.sample() over the block's uniforms (lane 0)
-    if (lane == 0) {
-      const double* ub = S.ubuf[wv];
-      uint8_t* ob = S.obuf[wv];
-#pragma unroll 4
-      for (int t = 0; t < 32 && q < total; t++) {
-        r = __dmul_rn(r, ub[t]);
+    // ---- PoissonDistribution.sample() over the block's 32 uniforms.
+    // r <= 1 always, so a uniform below exp(-mean) ends whatever draw is running: such positions cut
+    // the stream into independent RUNS (each starts with r = 1, n = 0).  The lane that sits at a run's
+    // first position walks the run (mean length 1/(1-e^-mean) uniforms), all runs in parallel; only the
+    // block's first run inherits state from the previous block and only its last one can stay open.
+    const uint32_t tmask = __ballot_sync(0xffffffffu, u < p_exp);
+    const bool is_start = (lane == 0) || ((tmask >> (lane - 1)) & 1u);
+    const uint32_t rest = tmask >> lane;
+    const int run_end = rest ? lane + __ffs(rest) - 1 : 31;
+    const int len = is_start ? run_end - lane + 1 : 0;
+    const int maxlen = __reduce_max_sync(0xffffffffu, len);
+    double r = lane == 0 ? carry_r : 1.0;
+    int n = lane == 0 ? carry_n : 0;
+    int cnt = 0;
+    for (int t = 0; t < maxlen; t++) {
+      const double ut = __shfl_sync(0xffffffffu, u, (lane + t) & 31);
+      if (t < len) {
+        r = __dmul_rn(r, ut);
         bool emit;
         if (r >= p_exp) { n++; emit = !((double)n < limit); } else emit = true;
         if (emit) {
-          mx = max(mx, n);
-          ob[pos++] = (uint8_t)min(n, 255);
-          q++; n = 0; r = 1.0;
+          if (n > 255) mx = 256;                         // not representable: reported as an error by the host
+          stage[cnt++] = (uint8_t)min(n, 255);
+          n = 0; r = 1.0;
         }
       }
     }
-    const int pos_all = __shfl_sync(0xffffffffu, pos, 0);
-    const int done = __shfl_sync(0xffffffffu, (int)(q >= total), 0);
-    if (pos_all > kBagObuf - 32 || done) {
+    // the open run (if the block does not end on a terminator) hands its state to the next block
+    const int open_lane = tmask ? 32 - __clz(tmask) : 0;     // first position after the last terminator
+    const bool has_open = !(tmask >> 31);
+    const double or_ = __shfl_sync(0xffffffffu, r, open_lane & 31);
+    const int on_ = __shfl_sync(0xffffffffu, n, open_lane & 31);
+    carry_r = has_open ? or_ : 1.0;
+    carry_n = has_open ? on_ : 0;
+    // ordered compaction of the runs' draws into the output buffer
+    int excl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, excl, d);
+      if (lane >= d) excl += v;
+    }
+    const int total_cnt = __shfl_sync(0xffffffffu, excl, 31);
+    excl -= cnt;
+    const int64_t remaining = total - q;
+    const int emit_total = (int)(remaining < (int64_t)total_cnt ? remaining : (int64_t)total_cnt);
+    for (int k = 0; k < cnt; k++)
+      if (excl + k < emit_total) { const uint8_t v = stage[k]; ob[pos + excl + k] = v; mx = max(mx, (int)v); }
+    pos += emit_total;
+    q += emit_total;
+    const bool done = q >= total;
+    if (pos > kBagObuf - 32 || done) {
       __syncwarp();
-      for (int t = lane; t < pos_all; t += 32) out[flushed + t] = S.obuf[wv][t];
-      flushed += pos_all;
+      for (int t = lane; t < pos; t += 32) out[flushed + t] = ob[t];
+      flushed += pos;
       pos = 0;
       __syncwarp();
     }
     if (done) break;
   }
+  mx = __reduce_max_sync(0xffffffffu, mx);
   if (lane == 0) atomicMax(max_w, mx);
 }
 // T == 1 without replacement and rate < 1: XORShiftRandom(seed+p+1).nextDouble() < rate

@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libemrf.so")
+LIB_PATH = os.environ.get("EMRF_LIB_PATH") or os.path.join(_HERE, "libemrf.so")  # override: A/B builds only
 
 EMRF_OK, EMRF_ERR_ARG, EMRF_ERR_CUDA, EMRF_ERR_LIMIT, EMRF_ERR_INTERNAL = 0, -1, -2, -3, -4
 

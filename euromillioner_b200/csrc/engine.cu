@@ -153,7 +153,8 @@ struct emrf_ctx {
   void* nccl_comm = nullptr;
   // grow-only scratch reused across groups
   DevBuf d_group, d_results, d_ghist, d_tickets, d_split, d_part;
-  PinnedBuf h_group, h_split, h_part;
+  PinnedBuf h_group, h_split, h_part, h_seeds, h_table, h_tsum;
+  DevBuf d_seeds, d_table, d_tsum;
   // pinned arena that keeps every group's split records for the whole fit (nodes point into it)
   std::vector<std::unique_ptr<PinnedBuf>> arena;
   size_t arena_chunk = 0, arena_used = 0;
@@ -878,22 +879,47 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   GroupSel* cur = &sel_a;
   GroupSel* nxt = &sel_b;
   std::vector<int> tree_slot(T, -1);
-  std::vector<int32_t> batch_feat;
-  std::vector<int64_t> batch_bins, batch_seed;
-  std::vector<uint64_t> batch_state;
-  // smallest aggregate a node can need: the f_sub features with the fewest bins
-  int64_t min_node_mem;
-  {
-    std::vector<int> nbs(num_bins.begin(), num_bins.end());
-    std::sort(nbs.begin(), nbs.end());
-    int64_t sb = 0;
-    for (int k = 0; k < f_sub; k++) sb += nbs[k];
-    min_node_mem = std::max<int64_t>((int64_t)C * sb * 8, 1);
-  }
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_ev, part_ev;
   double host_ms = 0.0, host_sel = 0.0, host_upd = 0.0;
   static const bool verify_gains = getenv("EMRF_VERIFY_GAINS") != nullptr;
   c->arena_reset();
+
+  // ---- feature-subset table: draw k of the driver RNG → (subset, sum of numBins), tabulated on the GPU
+  // in chunks (kernels.cuh reservoir_table_kernel).  selectNodesToSplit then only counts draws.
+  const int64_t draws_bound = 2 * (int64_t)T * ((int64_t)1 << std::min(P.max_depth, 24)) + 1024;
+  const int table_cap = (int)std::min<int64_t>(draws_bound, (int64_t)1 << 20);
+  DevBuf &d_seeds = c->d_seeds, &d_table = c->d_table, &d_tsum = c->d_tsum;
+  PinnedBuf &h_seeds = c->h_seeds, &h_table = c->h_table, &h_tsum = c->h_tsum;
+  int64_t table_base = -1;        // first draw index held by the table (-1: nothing yet)
+  int64_t draw_idx = 0;           // draws consumed so far (accepted nodes + rejected ones)
+  if (subsampling) {
+    CU(d_seeds.ensure((size_t)table_cap * 8));
+    CU(d_table.ensure((size_t)table_cap * f_sub * 4));
+    CU(d_tsum.ensure((size_t)table_cap * 4));
+    CU(h_seeds.ensure((size_t)table_cap * 8));
+    CU(h_table.ensure((size_t)table_cap * f_sub * 4));
+    CU(h_tsum.ensure((size_t)table_cap * 4));
+  }
+  auto table_fill = [&](int64_t base) -> int {   // rng is positioned at draw `base`
+    int64_t* hs = h_seeds.as<int64_t>();
+    for (int k = 0; k < table_cap; k++) hs[k] = rng.next_long();
+    CU(cudaMemcpyAsync(d_seeds.p, hs, (size_t)table_cap * 8, cudaMemcpyHostToDevice, st));
+    kern::reservoir_table_kernel<<<(table_cap + 127) / 128, 128, 0, st>>>(d_seeds.as<int64_t>(), table_cap, F, f_sub,
+                                                                         d_num_bins.as<int32_t>(), d_table.as<int32_t>(),
+                                                                         d_tsum.as<int32_t>());
+    tm.kernel_launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(h_table.p, d_table.p, (size_t)table_cap * f_sub * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h_tsum.p, d_tsum.p, (size_t)table_cap * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    table_base = base;
+    return EMRF_OK;
+  };
+  {
+    const double t0 = now_ms();
+    if (subsampling) TRY(table_fill(0));
+    if (getenv("EMRF_DEBUG_TIMERS")) fprintf(stderr, "[emrf] subset table (%d draws): %.3f ms\n", table_cap, now_ms() - t0);
+  }
 
   // ---- selectNodesToSplit.  The driver RNG hands each popped node one nextLong() (drawn BEFORE the
   // memory check, so the node that does not fit consumes a draw too); the reservoir sampling a seed
@@ -901,53 +927,40 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   // steps, state saved after every draw), sampled in parallel, and then admitted sequentially exactly
   // as Spark does; the RNG is rewound to just after the rejected node's draw.  Needs only the stack,
   // so it runs on the host while the GPU is still partitioning the previous group.
+  int select_rc = EMRF_OK;
   auto select_group = [&](GroupSel& G) {
     G.clear();
     int64_t mem = 0;
-    bool group_done = false;
-    while (!stack.empty() && !group_done) {
-      const int64_t room = (max_mem - mem) / min_node_mem + 1;
-      const int K = (int)std::min<int64_t>((int64_t)stack.size(), std::max<int64_t>(room, 1));
-      batch_feat.resize((size_t)K * f_sub);
-      batch_bins.resize(K);
+    while (!stack.empty()) {
+      const auto top = stack.back();
+      const int32_t* sub = nullptr;
+      int64_t total_bins = all_feat_bins;
       if (subsampling) {
-        batch_seed.resize(K);
-        batch_state.resize(K);
-        for (int j = 0; j < K; j++) { batch_seed[j] = rng.next_long(); batch_state[j] = rng.state; }
-#pragma omp parallel for schedule(static) num_threads(c->host_threads) if (K >= 64)
-        for (int j = 0; j < K; j++) {
-          int len = 0;
-          int32_t* sub = &batch_feat[(size_t)j * f_sub];
-          hl::reservoir_features(F, f_sub, batch_seed[j], sub, &len);
-          int64_t tb = 0;
-          for (int k = 0; k < f_sub; k++) tb += num_bins[sub[k]];
-          batch_bins[j] = tb;
+        // featureSubset = reservoirSampleAndCount(Range(0, F), F_sub, rng.nextLong()) — draw number draw_idx
+        if (draw_idx >= table_base + table_cap) {
+          select_rc = table_fill(table_base + table_cap);
+          if (select_rc != EMRF_OK) return;
         }
-      } else {
-        for (int j = 0; j < K; j++) {
-          for (int k = 0; k < F; k++) batch_feat[(size_t)j * f_sub + k] = k;
-          batch_bins[j] = all_feat_bins;
-        }
+        const size_t at = (size_t)(draw_idx - table_base);
+        sub = h_table.as<int32_t>() + at * f_sub;
+        total_bins = h_tsum.as<int32_t>()[at];
+        draw_idx++;            // drawn BEFORE the memory check: a node that does not fit still consumes it
       }
-      for (int j = 0; j < K; j++) {
-        const auto top = stack.back();
-        const int64_t node_mem = (int64_t)C * batch_bins[j] * 8;
-        if (mem + node_mem <= max_mem || mem == 0) {
-          stack.pop_back();
-          if (tree_slot[top.first] < 0) {
-            tree_slot[top.first] = (int)G.trees_seen.size();
-            G.trees_seen.push_back(top.first);
-            G.nodes_for_tree.emplace_back();
-          }
-          G.nodes_for_tree[tree_slot[top.first]].push_back((int)G.group.size());
-          G.group.push_back({top.first, top.second, (int)G.feat.size()});
-          G.feat.insert(G.feat.end(), batch_feat.begin() + (size_t)j * f_sub, batch_feat.begin() + (size_t)(j + 1) * f_sub);
-          mem += node_mem;
-        } else {
-          if (subsampling) rng.state = batch_state[j];  // draws after the rejected node's are undone
-          group_done = true;
-          break;
+      const int64_t node_mem = (int64_t)C * total_bins * 8;
+      if (mem + node_mem <= max_mem || mem == 0) {
+        stack.pop_back();
+        if (tree_slot[top.first] < 0) {
+          tree_slot[top.first] = (int)G.trees_seen.size();
+          G.trees_seen.push_back(top.first);
+          G.nodes_for_tree.emplace_back();
         }
+        G.nodes_for_tree[tree_slot[top.first]].push_back((int)G.group.size());
+        G.group.push_back({top.first, top.second, (int)G.feat.size()});
+        if (sub) G.feat.insert(G.feat.end(), sub, sub + f_sub);
+        else for (int k = 0; k < F; k++) G.feat.push_back(k);
+        mem += node_mem;
+      } else {
+        break;
       }
     }
     for (int t : G.trees_seen) tree_slot[t] = -1;   // slots are recomputed by whoever consumes the group
@@ -958,6 +971,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     select_group(*cur);
     const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
   }
+  TRY(select_rc);
   while (!cur->group.empty()) {
     double t_host0 = now_ms();
     std::vector<GroupEntry>& group = cur->group;
@@ -1207,6 +1221,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       select_group(*nxt);
       const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
     }
+    TRY(select_rc);
     if (ns) {
       CU(cudaStreamSynchronize(st));
       t_host0 = now_ms();

@@ -443,6 +443,46 @@ __global__ void bag_bernoulli_kernel(int64_t seed, const int64_t* __restrict__ p
 }
 
 // ---------------------------------------------------------------------------------------------
+// Feature subsets of selectNodesToSplit, precomputed.  The k-th nextLong() of the driver's
+// java.util.Random is the same number whichever node ends up receiving it, so the reservoir sample
+// it seeds (SamplingUtils.reservoirSampleAndCount over Range(0, F) with XORShiftRandom(seed_k)) can be
+// tabulated for draw indices 0..M-1 in one launch: one thread per draw.  out[k][f_sub] keeps the
+// reservoir order (it is the histogram layout and the tie-break order); bins_sum[k] = sum of
+// numBins over the subset (the memory check of selectNodesToSplit).
+// ---------------------------------------------------------------------------------------------
+__global__ void reservoir_table_kernel(const int64_t* __restrict__ seeds, int n_draws, int F, int f_sub,
+                                       const int32_t* __restrict__ num_bins_all, int32_t* __restrict__ out,
+                                       int32_t* __restrict__ bins_sum) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_draws) return;
+  int32_t* sub = out + (size_t)k * f_sub;
+  for (int i = 0; i < f_sub; i++) sub[i] = i;
+  if (F > f_sub) {
+    const uint64_t sd = (uint64_t)seeds[k];
+    uint32_t words[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) words[i] = 0;
+    words[0] = __byte_perm((uint32_t)(sd >> 32), 0, 0x0123);
+    words[1] = __byte_perm((uint32_t)sd, 0, 0x0123);
+    const uint32_t lo = mm3_seed64(words, 0x3c074a61u);
+    const uint32_t hi = mm3_seed64(words, lo);
+    uint64_t x = ((uint64_t)hi << 32) | lo;
+    for (int item = f_sub; item < F; item++) {
+      x ^= x << 21; x ^= x >> 35; x ^= x << 4;
+      const uint64_t a = x & ((1ull << 26) - 1);
+      x ^= x << 21; x ^= x >> 35; x ^= x << 4;
+      const uint64_t b = x & ((1ull << 27) - 1);
+      const double d = __dmul_rn((double)(int64_t)((a << 27) + b), 1.1102230246251565e-16);   // nextDouble()
+      const int64_t j = (int64_t)__dmul_rn(d, (double)(item + 1));
+      if (j < f_sub) sub[j] = item;
+    }
+  }
+  int s = 0;
+  for (int i = 0; i < f_sub; i++) s += num_bins_all[sub[i]];
+  bins_sum[k] = s;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Per-tree in-bag row lists from the [N][T] weight matrix (stable: rows ascending).
 //   list_count_kernel : per (row tile, tree) number of rows with weight > 0
 //   list_scan_kernel  : per tree exclusive scan over tiles (+ totals)

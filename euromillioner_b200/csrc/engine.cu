@@ -217,6 +217,7 @@ typedef int (*ncclCommInitRank_t)(void**, int, nccl_uid_t, int);
 typedef int (*ncclCommDestroy_t)(void*);
 typedef int (*ncclAllReduce_t)(const void*, void*, size_t, int, int, void*, cudaStream_t);
 typedef const char* (*ncclGetErrorString_t)(int);
+typedef int (*ncclReduceScatter_t)(const void*, void*, size_t, int, int, void*, cudaStream_t);
 static void* nccl_open() {
   static void* lib = nullptr;
   if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
@@ -287,6 +288,15 @@ static int nccl_allreduce(emrf_ctx* c, void* buf, size_t count, bool int32_max) 
   return EMRF_OK;
 }
 static int nccl_allreduce_u32(emrf_ctx* c, uint32_t* buf, size_t count) { return nccl_allreduce(c, buf, count, false); }
+// in-place reduce-scatter (uint32 sum): rank r ends up with the sum of words [r*per_rank, (r+1)*per_rank)
+static int nccl_reduce_scatter_u32(emrf_ctx* c, uint32_t* buf, size_t per_rank) {
+  static ncclReduceScatter_t rs = nullptr;
+  if (!rs) rs = (ncclReduceScatter_t)dlsym(c->nccl_lib, "ncclReduceScatter");
+  if (!rs) return fail(EMRF_ERR_CUDA, "ncclReduceScatter missing");
+  int rc = rs(buf, buf + (size_t)c->rank * per_rank, per_rank, /*ncclUint32*/ 3, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+  if (rc) return fail(EMRF_ERR_CUDA, "ncclReduceScatter failed (%d)", rc);
+  return EMRF_OK;
+}
 
 // Row-sharded fit (shard_mode 1): this rank holds the rows of partitions
 // [first_part, first_part + n_parts_local) of a dataset of n_rows_global rows in n_parts_global partitions.
@@ -1027,15 +1037,17 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     char* h_res = (char*)c->arena_alloc(res_bytes);   // kept until the forest is exported
     if (!h_res) return fail(EMRF_ERR_CUDA, "out of pinned host memory for the split-record arena");
     CU(c->d_tickets.ensure(n_rec * 4));
-    CU(c->d_ghist.ensure((size_t)std::max(n_slots, 1) * slot_words * 4));
+    const int nodes_per_rank = row_sharded ? (n_nodes + c->world - 1) / c->world : 0;
+    const int n_slots_alloc = row_sharded ? nodes_per_rank * c->world : n_slots;
+    CU(c->d_ghist.ensure((size_t)std::max(n_slots_alloc, 1) * slot_words * 4));
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_sel += d_; }
 
     CU(cudaMemcpyAsync(c->d_group.p, c->h_group.p, group_bytes, cudaMemcpyHostToDevice, st));
     tm.h2d_bytes += (int64_t)group_bytes;
     tm.d2h_bytes += (int64_t)res_bytes;
     CU(cudaMemsetAsync(c->d_tickets.p, 0, n_rec * 4, st));
-    if (c->world > 1 && !row_sharded) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
-    if (n_slots) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots * slot_words * 4, st));
+    if (c->world > 1) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
+    if (n_slots_alloc) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots_alloc * slot_words * 4, st));
     kern::HistArgs A;
     A.ent0 = d_ent[0].as<uint64_t>();
     A.ent1 = d_ent[1].as<uint64_t>();
@@ -1065,14 +1077,23 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     hist_ev.emplace_back(e0, e1);
     CU(cudaGetLastError());
     if (row_sharded) {
-      // reduceByKey(_.merge(_)) of Spark's per-partition aggregators: sum the partial histograms of
-      // all ranks (exact integers), then every rank scans every node (identical results everywhere)
-      TRY(nccl_allreduce_u32(c, c->d_ghist.as<uint32_t>(), (size_t)n_nodes * slot_words));
-      kern::scan_kernel<<<dim3(n_nodes, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
-          c->d_ghist.as<uint32_t>(), A.node_feat, A.num_bins_all, f_sub, B, C, k_chunk, n_chunks, P.impurity,
-          P.min_instances_per_node, P.min_info_gain, A.results, A.left_counts, A.total_counts);
-      tm.kernel_launches++;
-      CU(cudaGetLastError());
+      // reduceByKey(_.merge(_)) of Spark's per-partition aggregators, keyed by node exactly as Spark
+      // does it: a reduce-scatter leaves each rank with the summed histograms (exact integers) of ITS
+      // share of the group's nodes, it scans those, and the small split records are combined with an
+      // all-reduce over zero-filled slots (as in the tree-sharded mode).
+      TRY(nccl_reduce_scatter_u32(c, c->d_ghist.as<uint32_t>(), (size_t)nodes_per_rank * slot_words));
+      const int first = c->rank * nodes_per_rank;
+      const int mine_n = std::max(0, std::min(nodes_per_rank, n_nodes - first));
+      if (mine_n > 0) {
+        kern::scan_kernel<<<dim3(mine_n, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
+            c->d_ghist.as<uint32_t>() + (size_t)first * slot_words, A.node_feat + (size_t)first * f_sub, A.num_bins_all, f_sub,
+            B, C, k_chunk, n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain,
+            A.results + (size_t)first * n_chunks, A.left_counts + (size_t)first * n_chunks * C,
+            A.total_counts + (size_t)first * n_chunks * C);
+        tm.kernel_launches++;
+        CU(cudaGetLastError());
+      }
+      TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
     } else if (c->world > 1) {
       TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
     }

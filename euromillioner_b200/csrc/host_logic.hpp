@@ -232,15 +232,17 @@ inline bool find_splits_rows(const emrf_params_t& p, int64_t n_rows, const int64
     SparkXorShift rng(partition_seeds.next_long());
     const int64_t lo = part_off[part], hi = part_off[part + 1];
     if (gap) {
-      // GapSampling: skip ~ Geometric(fraction); constructed lazily at the first sample() call.
-      int64_t skip = -1;
-      for (int64_t i = lo; i < hi; ++i) {
-        if (skip < 0) skip = static_cast<int32_t>(std::log(std::max(rng.next_double(), 5e-11)) / lnq);
-        if (skip > 0) {
-          --skip;
-        } else {
-          skip = static_cast<int32_t>(std::log(std::max(rng.next_double(), 5e-11)) / lnq);
+      // GapSampling: `skip` items are dropped, the next one is kept, then a new Geometric(fraction)
+      // skip is drawn (the first one lazily, at the partition's first item).  Walked by jumps.
+      if (lo < hi) {
+        int64_t i = lo;
+        while (true) {
+          const int64_t skip = static_cast<int32_t>(std::log(std::max(rng.next_double(), 5e-11)) / lnq);
+          i += skip;
+          if (i >= hi) break;
           rows->push_back(i);
+          ++i;
+          if (i >= hi) break;
         }
       }
     } else {

@@ -34,7 +34,7 @@ sys.path.insert(0, ROOT)
 N_ROWS, N_FEATURES, N_CLASSES = 1_000_000, 64, 50
 TREES_PER_GPU, MAX_DEPTH, MAX_BINS, N_PARTS = 100, 10, 32, 1024
 METRIC, UNIT = "rf_fit_rows_trees_per_sec", "rows*trees/s"
-CPU_SAMPLE_TREES = 40
+CPU_SAMPLE_TREES = 100   # the whole workload: ~8 s on 16 cores
 
 
 def workload_name(n_gpus, mode="rows"):
@@ -130,7 +130,7 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")

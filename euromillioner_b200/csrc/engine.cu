@@ -618,6 +618,10 @@ struct emrf_forest {
   std::mutex dev_mu;
   int dev_device = -1;
   DevBuf d_nodes, d_roots, d_leaf_prob;
+  // binned-walk layout (predict v2): 8-byte nodes with adjacent children, per-feature threshold tables
+  bool walk_ok = false;
+  int walk_ts = 0;            // threshold table stride
+  DevBuf d_wnodes, d_wroots, d_pthr, d_pns;
 };
 
 struct HNode {
@@ -1454,6 +1458,72 @@ static int forest_to_device(emrf_ctx* c, emrf_forest* f) {
   CU(cudaMemcpy(f->d_nodes.p, dn.data(), (size_t)n * sizeof(kern::DevNode), cudaMemcpyHostToDevice));
   CU(cudaMemcpy(f->d_roots.p, roots.data(), (size_t)f->num_trees * 8, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(f->d_leaf_prob.p, leaf_prob.data(), leaf_prob.size() * 8, cudaMemcpyHostToDevice));
+  // ---- binned-walk layout: per-feature sorted tables of every threshold the forest compares with,
+  // nodes re-laid breadth-first so that siblings are adjacent (right = left + 1)
+  {
+    const int F = f->num_features;
+    std::vector<std::vector<double>> tab(F);
+    for (int64_t i = 0; i < n; i++)
+      if (f->nodes[i].left >= 0) tab[f->nodes[i].feature].push_back(f->nodes[i].threshold);
+    size_t ts = 1;
+    bool ok = (F <= 65535);
+    for (int j = 0; j < F; j++) {
+      std::sort(tab[j].begin(), tab[j].end());
+      tab[j].erase(std::unique(tab[j].begin(), tab[j].end()), tab[j].end());
+      for (double v : tab[j]) if (v != v) ok = false;
+      ts = std::max(ts, tab[j].size());
+    }
+    if (ts > 255) ok = false;   // bins must fit uint8; such forests use the f64 walk
+    f->walk_ok = ok;
+    if (ok) {
+      f->walk_ts = (int)ts;
+      std::vector<double> pthr((size_t)F * ts, 0.0);
+      std::vector<int32_t> pns(F);
+      for (int j = 0; j < F; j++) {
+        pns[j] = (int32_t)tab[j].size();
+        std::copy(tab[j].begin(), tab[j].end(), pthr.begin() + (size_t)j * ts);
+      }
+      std::vector<kern::WalkNode> wn(n);
+      std::vector<int32_t> wroots(f->num_trees);
+      std::vector<int64_t> queue;
+      int64_t next_free = 0;
+      // leaf rows must match the legacy numbering (leaf_prob was filled in flat pre-order)
+      std::vector<int32_t> leaf_of(n, -1);
+      for (int64_t i = 0; i < n; i++)
+        if (f->nodes[i].left < 0) leaf_of[i] = dn[i].right ? dn[i].left : -1;
+      for (int t = 0; t < f->num_trees; t++) {
+        const int64_t base = f->tree_off[t];
+        wroots[t] = (int32_t)next_free;
+        queue.clear();
+        queue.push_back(base);
+        std::vector<int64_t> slot_of;   // BFS slot for queue entry q = wroots[t] + q
+        next_free += 1;
+        for (size_t q = 0; q < queue.size(); q++) {
+          const int64_t i = queue[q];
+          const FlatNode& nd = f->nodes[i];
+          kern::WalkNode& w = wn[wroots[t] + (int64_t)q];
+          if (nd.left >= 0) {
+            const auto& tb = tab[nd.feature];
+            const int sb = (int)(std::lower_bound(tb.begin(), tb.end(), nd.threshold) - tb.begin());
+            w.left = (int32_t)next_free; w.feature = (uint16_t)nd.feature; w.split_bin = (uint8_t)sb; w.is_leaf = 0;
+            queue.push_back(base + nd.left);
+            queue.push_back(base + nd.right);
+            next_free += 2;
+          } else {
+            w.left = leaf_of[i]; w.feature = 0; w.split_bin = 0; w.is_leaf = 1;
+          }
+        }
+      }
+      CU(f->d_wnodes.alloc((size_t)n * sizeof(kern::WalkNode)));
+      CU(f->d_wroots.alloc((size_t)f->num_trees * 4));
+      CU(f->d_pthr.alloc(pthr.size() * 8));
+      CU(f->d_pns.alloc((size_t)F * 4));
+      CU(cudaMemcpy(f->d_wnodes.p, wn.data(), (size_t)n * sizeof(kern::WalkNode), cudaMemcpyHostToDevice));
+      CU(cudaMemcpy(f->d_wroots.p, wroots.data(), (size_t)f->num_trees * 4, cudaMemcpyHostToDevice));
+      CU(cudaMemcpy(f->d_pthr.p, pthr.data(), pthr.size() * 8, cudaMemcpyHostToDevice));
+      CU(cudaMemcpy(f->d_pns.p, pns.data(), (size_t)F * 4, cudaMemcpyHostToDevice));
+    }
+  }
   f->dev_device = c->device;
   return EMRF_OK;
 }
@@ -1475,7 +1545,8 @@ extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f_in, const doub
              pred_dev = pred_hd && is_device_ptr(pred_hd);
   // chunk so that staging buffers stay modest
   const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(N, (int64_t)(512ll << 20) / ((int64_t)F * 8)));
-  DevBuf dX, dRaw, dProb, dPred;
+  DevBuf dX, dRaw, dProb, dPred, dBins;
+  CU(dBins.alloc((size_t)align_up((size_t)chunk, 128) * align_up(F, 16)));
   if (!x_dev) CU(dX.alloc((size_t)chunk * F * 8));
   if (raw_hd && !raw_dev) CU(dRaw.alloc((size_t)chunk * C * 8));
   if (prob_hd && !prob_dev) CU(dProb.alloc((size_t)chunk * C * 8));
@@ -1490,10 +1561,35 @@ extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f_in, const doub
     double* raw = raw_hd ? (raw_dev ? raw_hd + r0 * C : dRaw.as<double>()) : nullptr;
     double* prob = prob_hd ? (prob_dev ? prob_hd + r0 * C : dProb.as<double>()) : nullptr;
     double* pred = pred_hd ? (pred_dev ? pred_hd + r0 : dPred.as<double>()) : nullptr;
-    const int64_t threads = n * 32;
-    kern::predict_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(x, n, F, f->d_nodes.as<kern::DevNode>(),
-                                                                         f->d_roots.as<int64_t>(), f->num_trees,
-                                                                         f->d_leaf_prob.as<double>(), C, raw, prob, pred);
+    const int Fp = (int)align_up(F, 16);
+    const size_t walk_smem = kern::predict_smem_bytes(Fp, C);
+    static const bool force_f64_walk = getenv("EMRF_PREDICT_F64_WALK") != nullptr;
+    if (f->walk_ok && !force_f64_walk && walk_smem <= 200 * 1024) {
+      // bin the chunk once (numeric compare against the forest's own threshold tables), then walk bins
+      const size_t tile_bytes = align_up((size_t)kern::kBinRows * Fp, 16);
+      const size_t thr_bytes = (size_t)F * f->walk_ts * 8;
+      const unsigned bgrid = (unsigned)((n + kern::kBinRows - 1) / kern::kBinRows);
+      if (tile_bytes + thr_bytes <= 160 * 1024) {
+        const size_t smem = tile_bytes + thr_bytes;
+        if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern::bin_kernel<true, true><<<bgrid, 256, smem, st>>>(x, n, F, Fp, 0, f->d_pthr.as<double>(), f->d_pns.as<int>(),
+                                                               f->walk_ts, dBins.as<uint8_t>(), nullptr);
+      } else {
+        if (tile_bytes > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes));
+        kern::bin_kernel<false, true><<<bgrid, 256, tile_bytes, st>>>(x, n, F, Fp, 0, f->d_pthr.as<double>(), f->d_pns.as<int>(),
+                                                                      f->walk_ts, dBins.as<uint8_t>(), nullptr);
+      }
+      if (walk_smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::predict_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)walk_smem));
+      const unsigned wgrid = (unsigned)((n + kern::kPredWarps * 32 - 1) / (kern::kPredWarps * 32));
+      kern::predict_walk_kernel<<<wgrid, kern::kPredWarps * 32, walk_smem, st>>>(
+          dBins.as<uint8_t>(), Fp, n, f->d_wnodes.as<kern::WalkNode>(), f->d_wroots.as<int32_t>(), f->num_trees,
+          f->d_leaf_prob.as<double>(), C, raw, prob, pred);
+    } else {
+      const int64_t threads = n * 32;
+      kern::predict_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(x, n, F, f->d_nodes.as<kern::DevNode>(),
+                                                                           f->d_roots.as<int64_t>(), f->num_trees,
+                                                                           f->d_leaf_prob.as<double>(), C, raw, prob, pred);
+    }
     CU(cudaGetLastError());
     if (raw_hd && !raw_dev) CU(cudaMemcpyAsync(raw_hd + r0 * C, raw, (size_t)n * C * 8, cudaMemcpyDeviceToHost, st));
     if (prob_hd && !prob_dev) CU(cudaMemcpyAsync(prob_hd + r0 * C, prob, (size_t)n * C * 8, cudaMemcpyDeviceToHost, st));

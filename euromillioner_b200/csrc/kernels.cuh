@@ -73,8 +73,19 @@ __device__ __forceinline__ int find_bin_dev(const double* thr, int n, double x) 
   }
   return lo;
 }
+// Predict-time variant: bin = #thresholds numerically below x (NaN above all), so that
+// bin(x) <= s  <=>  x <= thr[s]  — ContinuousSplit.shouldGoLeft on raw features.
+__device__ __forceinline__ int find_bin_numeric(const double* thr, int n, double x) {
+  if (x != x) return n;
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (thr[mid] < x) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
 constexpr int kBinRows = 128;
-template <bool kThrInSmem>
+template <bool kThrInSmem, bool kNumeric = false>
 __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, int64_t n_rows, int F, int Fp,
                                                   int64_t Np, const double* __restrict__ thr,
                                                   const int* __restrict__ n_splits, int thr_stride,
@@ -97,7 +108,8 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
   for (int e = threadIdx.x; e < total; e += blockDim.x) {
     const int r = e / F, f = e - r * F;
     const double x = X[base + e];
-    tile[r * Fp + f] = (uint8_t)find_bin_dev(sthr + (size_t)f * thr_stride, n_splits[f], x);
+    tile[r * Fp + f] = (uint8_t)(kNumeric ? find_bin_numeric(sthr + (size_t)f * thr_stride, n_splits[f], x)
+                                          : find_bin_dev(sthr + (size_t)f * thr_stride, n_splits[f], x));
   }
   __syncthreads();
   if (bins_rm) {  // rows of the tile are contiguous in bins_rm: straight 128-bit copy
@@ -1264,6 +1276,137 @@ __global__ void __launch_bounds__(256) predict_kernel(const double* __restrict__
     for (int q = 0; q < kMaxClassSlots; q++) {
       const int c = lane + 32 * q;
       if (c < C) prob[row * C + c] = (s != 0.0) ? __ddiv_rn(votes[q], s) : votes[q];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K5 v2 — batch prediction on BINNED rows.  A forest only ever compares feature f with thresholds
+// from a finite per-feature table, and x <= thr[s] <=> bin(x) <= s for bin(x) = #thresholds below x,
+// so a chunk of rows is first binned once (bin_kernel<.., numeric>: 8 B -> 1 B per value, HBM-bound)
+// and every tree walk then touches 1-byte bins held in shared memory and 8-byte nodes (children
+// adjacent).  lane = row for the walks; the leaf's class distribution is then added by the whole
+// warp, lane = class, one row at a time, so the 8*C-byte leaf record is read coalesced.  Votes are
+// accumulated per class in tree order (the f64 sum order is part of the contract), exactly as
+// RandomForestClassificationModel.predictRaw does; normalisation and first-max argmax as in
+// raw2probabilityInPlace / Vector.argmax.
+// ---------------------------------------------------------------------------------------------
+struct WalkNode {      // 8 bytes
+  int32_t left;        // internal: index of the left child (right = left + 1); leaf: row of leaf_prob, -1 if empty
+  uint16_t feature;
+  uint8_t split_bin;
+  uint8_t is_leaf;
+};
+constexpr int kPredWarps = 4;
+inline size_t predict_smem_bytes(int Fp, int C) {
+  const int Cp = C | 1;
+  return (size_t)kPredWarps * 32 * Cp * 8 + (size_t)kPredWarps * 32 * (Fp + 4);
+}
+__global__ void __launch_bounds__(kPredWarps * 32) predict_walk_kernel(const uint8_t* __restrict__ bins_rm, int Fp,
+                                                                       int64_t n_rows, const WalkNode* __restrict__ nodes,
+                                                                       const int32_t* __restrict__ tree_root, int T,
+                                                                       const double* __restrict__ leaf_prob, int C,
+                                                                       double* __restrict__ raw, double* __restrict__ prob,
+                                                                       double* __restrict__ pred) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  const int Cp = C | 1;                       // odd stride: "lane = row" accesses are conflict-free
+  const int RS = Fp + 4;                      // row stride in bytes (Fp/4 + 1 words, odd)
+  double* votes = reinterpret_cast<double*>(smem_raw) + (size_t)wv * 32 * Cp;
+  uint8_t* rowb = smem_raw + (size_t)kPredWarps * 32 * Cp * 8 + (size_t)wv * 32 * RS;
+  const int64_t r0 = ((int64_t)blockIdx.x * kPredWarps + wv) * 32;
+  if (r0 >= n_rows) return;
+  const int n_here = (int)min((int64_t)32, n_rows - r0);
+  {  // stage the 32 binned rows (contiguous in bins_rm) word by word into the padded tile
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(bins_rm + (size_t)r0 * Fp);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(rowb);
+    const int wpr = Fp >> 2;
+    for (int i = lane; i < n_here * wpr; i += 32) {
+      const int r = i / wpr, w = i - r * wpr;
+      dst[r * (wpr + 1) + w] = src[i];
+    }
+    for (int i = lane; i < 32 * Cp; i += 32) votes[i] = 0.0;
+  }
+  __syncwarp();
+  const uint8_t* my = rowb + (size_t)min(lane, n_here - 1) * RS;
+  constexpr int TB = 4;   // trees walked together: four independent pointer chases per lane hide the node latency
+  constexpr int RB = 8;   // rows whose leaf records are fetched before any is added (loads in flight)
+  for (int t0 = 0; t0 < T; t0 += TB) {
+    int li[TB];
+    {
+      int n[TB];
+      WalkNode nd[TB];
+      bool any = false;
+#pragma unroll
+      for (int u = 0; u < TB; u++) {
+        const int t = min(t0 + u, T - 1);
+        n[u] = tree_root[t];
+        nd[u] = nodes[n[u]];
+        any |= !nd[u].is_leaf;
+      }
+      while (any) {
+        any = false;
+#pragma unroll
+        for (int u = 0; u < TB; u++) {
+          if (!nd[u].is_leaf) {
+            n[u] = nd[u].left + (my[nd[u].feature] > nd[u].split_bin ? 1 : 0);
+            nd[u] = nodes[n[u]];
+            any |= !nd[u].is_leaf;
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < TB; u++) li[u] = nd[u].left;
+    }
+    // votes(c) += leaf(c) in tree order; lane = class, RB rows per round so that RB leaf records are in flight
+#pragma unroll
+    for (int u = 0; u < TB; u++) {
+      if (t0 + u >= T) break;
+      for (int j0 = 0; j0 < n_here; j0 += RB) {
+        for (int qb = 0; qb < C; qb += 64) {
+          double a0[RB], a1[RB];
+#pragma unroll
+          for (int r = 0; r < RB; r++) {
+            const int l = __shfl_sync(0xffffffffu, li[u], (j0 + r) & 31);
+            const bool ok = (j0 + r < n_here) && (l >= 0);
+            const double* lp = leaf_prob + (size_t)max(l, 0) * C;
+            a0[r] = (ok && qb + lane < C) ? lp[qb + lane] : 0.0;
+            a1[r] = (ok && qb + lane + 32 < C) ? lp[qb + lane + 32] : 0.0;
+          }
+#pragma unroll
+          for (int r = 0; r < RB; r++) {
+            if (j0 + r < n_here) {          // adding +0.0 leaves a non-negative sum unchanged, exactly
+              double* vr = votes + (j0 + r) * Cp;
+              if (qb + lane < C) vr[qb + lane] = __dadd_rn(vr[qb + lane], a0[r]);
+              if (qb + lane + 32 < C) vr[qb + lane + 32] = __dadd_rn(vr[qb + lane + 32], a1[r]);
+            }
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+  // per row (lane = row): index-order sum and first-max argmax
+  double s = 0.0, best = 0.0;
+  int best_c = 0;
+  {
+    const double* vr = votes + min(lane, n_here - 1) * Cp;
+    for (int c = 0; c < C; c++) {
+      const double v = vr[c];
+      s = __dadd_rn(s, v);
+      if (c == 0 || v > best) { best = v; best_c = c; }
+    }
+  }
+  if (pred && lane < n_here) pred[r0 + lane] = (double)best_c;
+  if (raw || prob) {
+    for (int j = 0; j < n_here; j++) {
+      const double sj = __shfl_sync(0xffffffffu, s, j);
+      const double* vr = votes + j * Cp;
+      for (int q = lane; q < C; q += 32) {
+        const double v = vr[q];
+        if (raw) raw[(r0 + j) * C + q] = v;
+        if (prob) prob[(r0 + j) * C + q] = (sj != 0.0) ? __ddiv_rn(v, sj) : v;
+      }
     }
   }
 }

@@ -69,6 +69,10 @@ def test_cfg4_other_balls(ctx, oracle, ball):
     (40000, 64, 30, 7, 32, {"maxMemoryInMB": 2}),                 # tiny groups: the memory check redraws the RNG
     (3000, 10, 40, 12, 3, {"feature_subset": "onethird"}),        # deep, small: pure children, many leaves
     (25000, 16, 5, 6, 4, {"maxBins": 100, "feature_subset": "0.5"}),
+    (12000, 100, 4, 6, 6, {}),                                    # Fp = 112: 7 row chunks (irregular tile stride)
+    (9000, 150, 3, 5, 4, {}),                                     # rows wider than 128 B: generic byte-gather path
+    (5000, 3, 4, 5, 1, {"maxBins": 2}),                           # one split per feature, one partition
+    (4000, 1, 3, 4, 7, {}),                                       # a single feature
 ])
 def test_flat_fits_match_oracle(ctx, oracle, n, F, T, D, parts, kw):
     X, y = synth.flat(n, F, 50)
@@ -88,6 +92,16 @@ def test_entropy_fit_within_tolerance(ctx, oracle):
     y = y % 10
     model, ofo = _fit_both(ctx, oracle, X, y, 8, 10, numTrees=6, maxDepth=5, impurity="entropy")
     _assert_same_forest(model, ofo, exact=False)
+
+
+def test_two_classes_and_empty_partitions(ctx, oracle):
+    """Binary labels; a partition layout with empty partitions (their RNG streams are simply unused)."""
+    X, y = synth.flat(6000, 12, 2)
+    off = np.array([0, 0, 1500, 1500, 1500, 4000, 6000, 6000], np.int64)
+    rf = RandomForestClassifier(ctx).setNumTrees(9).setMaxDepth(6).setNumClasses(2)
+    model = rf.fit(Dataset(X, y, partition_offsets=off))
+    po = oracle.make_params(num_trees=9, max_depth=6, num_classes=2)
+    _assert_same_forest(model, oracle.fit(po, X, y, off))
 
 
 def test_few_rows_and_inferred_classes(ctx, oracle):

@@ -261,7 +261,7 @@ def main():
                                    else "tree-sharded x%d" % world) if world > 1 else "1 GPU",
                    "l2": "inputs (512 MB f64 features, 1 GB entry lists) are larger than the 126 MB L2; no explicit flush",
                    "seed": 207336481, "timing": "CUDA events on the engine stream per fit (emrf_timings_t.total_ms)",
-                   "wall_ms_per_step": wall_ms / args.steps},
+                   "wall_ms_per_step": wall_ms / args.steps, "ms_each_step": [round(v, 2) for v in ev_ms]},
         "clocks": clocks,
         "e2e": {"value": units / (e2e_ms / 1e3), "unit": UNIT,
                 "h2d_bytes_per_step": int(np.mean([t["h2d_bytes"] for t in e2e_tm])),

@@ -87,6 +87,10 @@ struct DevBuf {
     if (n <= bytes) return cudaSuccess;
     return alloc(n + n / 4);
   }
+  cudaError_t ensure_exact(size_t n) {  // grow-only, no slack (GB-sized buffers)
+    if (n <= bytes) return cudaSuccess;
+    return alloc(n);
+  }
   template <class T>
   T* as() const { return reinterpret_cast<T*>(p); }
 };
@@ -155,6 +159,9 @@ struct emrf_ctx {
   DevBuf d_group, d_results, d_ghist, d_tickets, d_split, d_part;
   PinnedBuf h_group, h_split, h_part, h_seeds, h_table, h_tsum;
   DevBuf d_seeds, d_table, d_tsum;
+  // fit-sized buffers kept between fits (grow-only): cudaMalloc/cudaFree of GB-sized buffers costs
+  // milliseconds and cudaFree synchronises the device; they are released by emrf_ctx_destroy
+  DevBuf p_w, p_X, p_y, p_labels, p_rm, p_cm, p_ent0, p_ent1, p_counts;
   // pinned arena that keeps every group's split records for the whole fit (nodes point into it)
   std::vector<std::unique_ptr<PinnedBuf>> arena;
   size_t arena_chunk = 0, arena_used = 0;
@@ -379,7 +386,7 @@ static int stage_input(emrf_ctx* c, const void* src_hd, size_t bytes, DevBuf& ow
     if (copied) *copied = false;
     return EMRF_OK;
   }
-  CU(owned.alloc(bytes));
+  CU(owned.ensure_exact(bytes));
   CU(cudaMemcpyAsync(owned.p, src_hd, bytes, cudaMemcpyHostToDevice, c->stream));
   c->tm.h2d_bytes += (int64_t)bytes;
   *dev_out = owned.p;
@@ -628,6 +635,7 @@ struct HNode {
   int32_t id = 1;
   int32_t left = -1, right = -1;
   bool is_leaf = false, valid = true;
+  int32_t pred = 0;   // first index of the largest class count (from the scan kernel)
   int32_t feature = -1, split_bin = -1;
   double threshold = 0.0, gain = std::numeric_limits<double>::quiet_NaN(), impurity = 0.0;
   uint64_t seg_start = 0;
@@ -647,11 +655,6 @@ static inline void node_counts(const HNode& n, int C, uint32_t* out) {
   else memcpy(out, n.cnt_a, (size_t)C * 4);
 }
 
-static int first_max(const uint32_t* a, int C) {
-  int mi = 0;
-  for (int c = 1; c < C; c++) if (a[c] > a[mi]) mi = c;
-  return mi;
-}
 // LearningNode.toNode(prune = true) (ml/tree/Node.scala), two passes per tree so that trees can be
 // exported in parallel into pre-sized arrays:
 //   pass A (post-order): does the node come out as a leaf (own leaf, or both children leaves with
@@ -666,12 +669,11 @@ static void export_pass_a(const HTree& t, int ni, int C, std::vector<ExportInfo>
     export_pass_a(t, n.right, C, info);
     const ExportInfo &l = info[n.left], &r = info[n.right];
     if (l.leaf && r.leaf && l.pred == r.pred) { e.leaf = true; e.pred = l.pred; e.size = 1; }
-    else { e.leaf = false; e.pred = first_max(n.cnt_a, C); e.size = 1 + l.size + r.size; }  // a split node owns its totals
+    else { e.leaf = false; e.pred = n.pred; e.size = 1 + l.size + r.size; }
   } else {
-    uint32_t tmp[256];
-    node_counts(n, C, tmp);
-    e.leaf = true; e.pred = first_max(tmp, C); e.size = 1;
+    e.leaf = true; e.pred = n.pred; e.size = 1;
   }
+  (void)C;
 }
 static void export_pass_b(const HTree& t, int ni, int C, const std::vector<ExportInfo>& info, int64_t base, int32_t pos,
                           emrf_forest& fo) {
@@ -745,10 +747,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(cudaEventRecord(ev_start, st));
 
   // ---- bootstrap weights start now, on the second stream (they need only the partition layout)
-  DevBuf d_w;
+  DevBuf& d_w = c->p_w;
   BagJob bag_job;
   cudaEvent_t ev_b0 = c->events.get(), ev_b1 = c->events.get();
-  CU(d_w.alloc((size_t)N * P.num_trees));
+  CU(d_w.ensure_exact((size_t)N * P.num_trees));
   CU(cudaEventRecord(ev_b0, c->stream2));
   {
     emrf_params_t Pb = P;   // partition p of this rank is global partition first_part + p: seed + p_global + 1
@@ -758,7 +760,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(cudaEventRecord(ev_b1, c->stream2));
 
   // ---- inputs
-  DevBuf own_X, own_y;
+  DevBuf &own_X = c->p_X, &own_y = c->p_y;
   const void* dXv = nullptr;
   const void* dyv = nullptr;
   bool copied = false;
@@ -769,8 +771,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(cudaEventRecord(ev_in, st));
 
   // ---- labels (Predictor.extractLabeledPoints / getNumClasses)
-  DevBuf d_labels, d_flags;
-  CU(d_labels.alloc((size_t)N));
+  DevBuf& d_labels = c->p_labels;
+  DevBuf d_flags;
+  CU(d_labels.ensure_exact((size_t)N));
   CU(d_flags.alloc(8));
   CU(cudaMemsetAsync(d_flags.p, 0, 8, st));
   kern::labels_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(dy, N, P.num_classes, d_labels.as<uint8_t>(), d_flags.as<int>());
@@ -807,24 +810,25 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   // ---- TreePoint matrices
   const int Fp = (int)align_up(F, 16);
   const int64_t Np = (int64_t)align_up((size_t)N, 128);
-  DevBuf d_rm, d_cm;
-  CU(d_rm.alloc((size_t)Np * Fp));
-  CU(d_cm.alloc((size_t)F * Np));
+  DevBuf &d_rm = c->p_rm, &d_cm = c->p_cm;
+  CU(d_rm.ensure_exact((size_t)Np * Fp));
+  CU(d_cm.ensure_exact((size_t)F * Np));
   TRY(run_bin(c, dX, N, F, d_thr.as<double>(), d_ns.as<int>(), TS, Fp, Np, d_rm.as<uint8_t>(), d_cm.as<uint8_t>()));
   CU(cudaEventRecord(ev_bin, st));
 
   // ---- BaggedPoint weights → per-tree entry lists
   // tree-sharded multi-GPU: every rank schedules all trees, but only builds lists (and
   // histograms) for trees t % world == rank.
-  DevBuf d_ent[2];
+  DevBuf* d_ent[2] = {&c->p_ent0, &c->p_ent1};
   std::vector<uint64_t> tree_base(T + 1, 0), tree_total(T, 0);
   {
     int maxw = 0;
     CU(cudaStreamWaitEvent(st, ev_b1, 0));
     TRY(bag_finish(c, st, P, bag_job, &maxw));
     const int n_tiles = (int)((N + kern::kListTile - 1) / kern::kListTile);
-    DevBuf d_counts, d_totals, d_base;
-    CU(d_counts.alloc((size_t)n_tiles * T * 4));
+    DevBuf& d_counts = c->p_counts;
+    DevBuf d_totals, d_base;
+    CU(d_counts.ensure_exact((size_t)n_tiles * T * 4));
     CU(d_totals.alloc((size_t)T * 8));
     CU(d_base.alloc((size_t)T * 8));
     const int bt = std::min(256, (int)align_up(T, 32));
@@ -834,16 +838,15 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaMemcpyAsync(tree_total.data(), d_totals.p, (size_t)T * 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     for (int t = 0; t < T; t++) tree_base[t + 1] = tree_base[t] + tree_total[t];
-    CU(d_ent[0].alloc((size_t)tree_base[T] * 8));
-    CU(d_ent[1].alloc((size_t)tree_base[T] * 8));
+    CU(d_ent[0]->ensure((size_t)tree_base[T] * 8));
+    CU(d_ent[1]->ensure((size_t)tree_base[T] * 8));
     CU(cudaMemcpyAsync(d_base.p, tree_base.data(), (size_t)T * 8, cudaMemcpyHostToDevice, st));
     kern::list_fill_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, d_counts.as<uint32_t>(),
-                                                   d_base.as<uint64_t>(), d_ent[0].as<uint64_t>());
+                                                   d_base.as<uint64_t>(), d_ent[0]->as<uint64_t>());
     tm.kernel_launches += 1;
     CU(cudaGetLastError());
     CU(cudaEventRecord(ev_bag, st));
-    CU(cudaStreamSynchronize(st));  // the tile tables are released here
-    d_w.release();
+    CU(cudaStreamSynchronize(st));  // the small tables die here; d_w stays in the ctx pool
     parked.clear();
   }
 
@@ -1053,8 +1056,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     if (c->world > 1) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
     if (n_slots_alloc) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots_alloc * slot_words * 4, st));
     kern::HistArgs A;
-    A.ent0 = d_ent[0].as<uint64_t>();
-    A.ent1 = d_ent[1].as<uint64_t>();
+    A.ent0 = d_ent[0]->as<uint64_t>();
+    A.ent1 = d_ent[1]->as<uint64_t>();
     A.bins_rm = d_rm.as<uint8_t>();
     A.nodes = (const kern::GroupNode*)c->d_group.p;
     A.node_feat = (const int32_t*)((char*)c->d_group.p + off_feat);
@@ -1160,7 +1163,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         {
           HNode& n = tr.pool[g.pool];
           n.is_leaf = is_leaf; n.gain = gain; n.impurity = pimp; n.valid = valid;
-          n.cnt_a = totc; n.cnt_b = nullptr;
+          n.cnt_a = totc; n.cnt_b = nullptr; n.pred = res[rec].pred;
         }
         if (!is_leaf) {
           const int feat = group_feat[g.feat_at + res[rec].k];
@@ -1173,8 +1176,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           tr.pool.emplace_back();
           HNode& l = tr.pool[li];
           HNode& r = tr.pool[li + 1];
-          l.id = 2 * id; l.is_leaf = l_leaf; l.impurity = limp; l.cnt_a = leftc;
-          r.id = 2 * id + 1; r.is_leaf = r_leaf; r.impurity = rimp; r.cnt_a = totc; r.cnt_b = leftc;
+          l.id = 2 * id; l.is_leaf = l_leaf; l.impurity = limp; l.cnt_a = leftc; l.pred = res[rec].left_pred;
+          r.id = 2 * id + 1; r.is_leaf = r_leaf; r.impurity = rimp; r.cnt_a = totc; r.cnt_b = leftc; r.pred = res[rec].right_pred;
           HNode& n = tr.pool[g.pool];
           n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
           n.left = li; n.right = li + 1;
@@ -1223,11 +1226,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
       CU(cudaEventRecord(p0, st));
       if (ptiles) {
-        kern::part_count_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0].as<uint64_t>(), d_ent[1].as<uint64_t>(),
+        kern::part_count_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
                                                                       d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left);
         kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft);
-        kern::part_scatter_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0].as<uint64_t>(), d_ent[1].as<uint64_t>(),
-                                                                        d_ent[0].as<uint64_t>(), d_ent[1].as<uint64_t>(),
+        kern::part_scatter_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                        d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
                                                                         d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft);
         tm.kernel_launches += 3;
       } else {

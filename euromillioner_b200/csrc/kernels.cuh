@@ -567,7 +567,9 @@ struct ScanResult {
   int32_t k;      // feature index within the node's subset (-1: no feature with splits in this chunk)
   int32_t split;
   int32_t valid;
-  int32_t pad;
+  int32_t pred;        // ImpurityCalculator.predict = first index of the largest class count: node,
+  int32_t left_pred;   //   left child,
+  int32_t right_pred;  //   right child (so the host never has to scan class counts)
 };
 struct HistArgs {
   const uint64_t* ent0;
@@ -667,6 +669,23 @@ inline size_t hist_tile_bytes(int ch) {
   return (size_t)(kHistThreads / 32) * 4 * ch * stride * 4;
 }
 
+// first index of the largest value among v(c), c < C, computed by one warp (call with all 32 lanes)
+template <class F>
+__device__ __forceinline__ int warp_first_argmax(int C, int lane, F v) {
+  uint32_t best = 0;
+  int bi = 0x7fffffff;
+  for (int c = lane; c < C; c += 32) {
+    const uint32_t x = v(c);
+    if (bi == 0x7fffffff || x > best) { best = x; bi = c; }
+  }
+  for (int o = 16; o; o >>= 1) {
+    const uint32_t b2 = __shfl_xor_sync(0xffffffffu, best, o);
+    const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (i2 != 0x7fffffff && (bi == 0x7fffffff || b2 > best || (b2 == best && i2 < bi))) { best = b2; bi = i2; }
+  }
+  return bi == 0x7fffffff ? 0 : bi;
+}
+
 // Scans a histogram chunk held in shared memory: hist[kc][B][C]; nb[k] = numBins of subset
 // feature k0+k.  All threads of the CTA participate; writes the chunk's result record.
 __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int impurity, int min_instances,
@@ -762,12 +781,24 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
   if (ix == 0x7fffffff) {
     if (tid == 0) {
       res->gain = kInvalidGain; res->impurity = pimp; res->left_impurity = 0.0; res->right_impurity = 0.0;
-      res->k = -1; res->split = 0; res->valid = 0; res->pad = 0;
+      res->k = -1; res->split = 0; res->valid = 0; res->left_pred = 0; res->right_pred = 0;
+    }
+    if (tid < 32) {
+      const int p = warp_first_argmax(C, tid, [&](int c) { return S.tot[c]; });
+      if (tid == 0) res->pred = p;
     }
     for (int c = tid; c < C; c += NT) { left_out[c] = 0; total_out[c] = S.tot[c]; }
   } else {
     const int k = ix / (B - 1), s = ix - k * (B - 1);
-    if (tid == 0) { res->gain = g; res->impurity = pimp; res->k = k0 + k; res->split = s; res->valid = (g != kInvalidGain); res->pad = 0; }
+    if (tid == 0) { res->gain = g; res->impurity = pimp; res->k = k0 + k; res->split = s; res->valid = (g != kInvalidGain); }
+    if (tid < 96) {   // three warps: predictions of the node, its left and its right child
+      const uint32_t* lw = sh + ((size_t)k * B + s) * C;
+      const int which = tid >> 5, ln = tid & 31;
+      const int p = which == 0 ? warp_first_argmax(C, ln, [&](int c) { return S.tot[c]; })
+                  : which == 1 ? warp_first_argmax(C, ln, [&](int c) { return lw[c]; })
+                               : warp_first_argmax(C, ln, [&](int c) { return S.tot[c] - lw[c]; });
+      if (ln == 0) { if (which == 0) res->pred = p; else if (which == 1) res->left_pred = p; else res->right_pred = p; }
+    }
     if (my_idx == ix) { res->left_impurity = best_li; res->right_impurity = best_ri; }  // the owner of the winner
     const uint32_t* l = sh + ((size_t)k * B + s) * C;
     for (int c = tid; c < C; c += NT) { left_out[c] = l[c]; total_out[c] = S.tot[c]; }

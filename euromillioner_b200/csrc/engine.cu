@@ -529,7 +529,7 @@ static int bag_launch(emrf_ctx* c, cudaStream_t stream, const emrf_params_t& P, 
     } else {
       const size_t smem = sizeof(kern::BagSmem);
       CU(cudaFuncSetAttribute(kern::bag_poisson_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      kern::bag_poisson_kernel<<<(n_parts + kern::kBagWarps - 1) / kern::kBagWarps, kern::kBagWarps * 32, smem, stream>>>(
+      kern::bag_poisson_kernel<<<(n_parts + kern::kBagPairs - 1) / kern::kBagPairs, kern::kBagWarps * 32, smem, stream>>>(
           P.seed, job.d_off.as<int64_t>(), n_parts, T, mean, p_exp, d_w, job.d_max.as<int>());
     }
   } else if (P.subsampling_rate == 1.0) {

@@ -241,8 +241,10 @@ __global__ void __launch_bounds__(32) bag_poisson_serial_kernel(int64_t seed, co
 // two steps from its carry-in and emits one nextDouble().  The Poisson loop itself (a running
 // product compared with exp(-mean)) stays sequential on lane 0; it reads the 32 uniforms of the
 // block from shared memory.  Bit-identical to the serial stream (tests/test_gpu_stages.py).
-constexpr int kBagWarps = 8;
+constexpr int kBagPairs = 4;              // partitions per CTA: one producer warp + one consumer warp each
+constexpr int kBagWarps = 2 * kBagPairs;
 constexpr int kBagObuf = 1024;
+constexpr int kBagRing = 4;               // blocks of 32 uniforms the producer may run ahead
 __device__ __forceinline__ uint32_t well_M(uint32_t x) {
   const uint32_t t = x ^ (x << 25);
   return (t << 9) ^ (t >> 21);
@@ -254,10 +256,104 @@ __device__ __forceinline__ uint32_t well_temper(uint32_t z4) {
 }
 struct BagSmem {
   uint32_t lut[4][4][256];                 // (M^2)^(2^s) for s = 1..4, one table per input byte
-  uint32_t state[kBagWarps][624];
-  uint8_t stage[kBagWarps][32][32];        // per lane: the draws of the run it owns in the current block
-  uint8_t obuf[kBagWarps][kBagObuf];
+  uint32_t state[kBagPairs][624];
+  double ring[kBagPairs][kBagRing][32];    // producer → consumer: blocks of 32 nextDouble() values
+  uint8_t stage[kBagPairs][32][32];        // per lane: the draws of the run it owns in the current block
+  uint8_t obuf[kBagPairs][kBagObuf];
+  volatile uint32_t produced[kBagPairs];   // blocks written by the producer
+  volatile uint32_t consumed[kBagPairs];   // blocks released by the consumer
+  volatile uint32_t stop[kBagPairs];
 };
+__device__ __forceinline__ int well_wrap(int j) { return j >= 624 ? j - 624 : (j < 0 ? j + 624 : j); }
+
+// 64 WELL19937c steps -> 32 uniforms, one per lane (see the derivation above)
+__device__ __forceinline__ double well_block(uint32_t* A, const BagSmem& S, uint32_t& carry, int& i0, int lane) {
+  const int i = well_wrap(i0 - 2 * lane);                 // index of this lane's first step
+  const uint32_t m1a = A[well_wrap(i + 70)], m2a = A[well_wrap(i + 179)], m3a = A[well_wrap(i + 449)];
+  const uint32_t m1b = A[well_wrap(i + 69)], m2b = A[well_wrap(i + 178)], m3b = A[well_wrap(i + 448)];
+  const uint32_t t1 = A[well_wrap(i - 1)], t2 = A[well_wrap(i - 2)], t3 = A[well_wrap(i - 3)];
+  const uint32_t z0a = (t1 & 0x80000000u) ^ (t2 & 0x7fffffffu);
+  const uint32_t z0b = (t2 & 0x80000000u) ^ (t3 & 0x7fffffffu);
+  const uint32_t ca = m1a ^ (m1a >> 27), cb = m1b ^ (m1b >> 27);
+  const uint32_t z2a = (m2a >> 9) ^ (m3a ^ (m3a >> 1)), z2b = (m2b >> 9) ^ (m3b ^ (m3b >> 1));
+  const uint32_t ea = z0a ^ ((ca << 9) ^ (ca >> 21)) ^ (z2a << 21) ^ (z2a >> 21);
+  const uint32_t eb = z0b ^ ((cb << 9) ^ (cb >> 21)) ^ (z2b << 21) ^ (z2b >> 21);
+  uint32_t X = well_M(ea) ^ eb;
+  if (lane == 0) X ^= well_M(well_M(carry));
+  {
+    uint32_t y = __shfl_up_sync(0xffffffffu, X, 1);
+    if (lane >= 1) X ^= well_M(well_M(y));
+#pragma unroll
+    for (int sidx = 0; sidx < 4; sidx++) {
+      const int d = 2 << sidx;
+      y = __shfl_up_sync(0xffffffffu, X, d);
+      const uint32_t qy = S.lut[sidx][0][y & 255] ^ S.lut[sidx][1][(y >> 8) & 255] ^ S.lut[sidx][2][(y >> 16) & 255] ^
+                          S.lut[sidx][3][y >> 24];
+      if (lane >= d) X ^= qy;
+    }
+  }
+  uint32_t bin = __shfl_up_sync(0xffffffffu, X, 1);
+  if (lane == 0) bin = carry;
+  const uint32_t z1a = (bin ^ (bin << 25)) ^ ca;
+  const uint32_t aa = z1a ^ z2a;
+  const uint32_t ba = z0a ^ (z1a ^ (z1a << 9)) ^ (z2a ^ (z2a << 21)) ^ (aa ^ (aa >> 21));
+  const uint32_t z1b = (ba ^ (ba << 25)) ^ cb;
+  const uint32_t ab = z1b ^ z2b;
+  const uint32_t bb = z0b ^ (z1b ^ (z1b << 9)) ^ (z2b ^ (z2b << 21)) ^ (ab ^ (ab >> 21));
+  carry = __shfl_sync(0xffffffffu, bb, 31);
+  __syncwarp();                                        // every lane has read its operands
+  A[i] = aa;
+  A[well_wrap(i - 1)] = ab;
+  i0 = well_wrap(i0 - 64);
+  __syncwarp();
+  const uint64_t hi26 = (uint64_t)(well_temper(ba) >> 6) << 26;
+  const uint64_t lo26 = well_temper(bb) >> 6;
+  return __dmul_rn((double)(int64_t)(hi26 | lo26), 2.220446049250313e-16);   // BitsStreamGenerator.nextDouble()
+}
+
+// PoissonDistribution.sample() over a block of 32 uniforms (one per lane).
+// r <= 1 always, so a uniform below exp(-mean) ends whatever draw is running: such positions cut the
+// stream into independent RUNS (each starts with r = 1, n = 0).  The lane that sits at a run's first
+// position walks the run (mean length 1/(1-e^-mean) uniforms), all runs in parallel; only the block's
+// first run inherits state from the previous block and only its last one can stay open.
+struct PoissonCarry {
+  double r = 1.0;
+  int n = 0;
+};
+__device__ __forceinline__ int poisson_block(double u, double p_exp, double limit, PoissonCarry& pc, uint8_t* stage, int lane,
+                                            int& overflow) {
+  const uint32_t tmask = __ballot_sync(0xffffffffu, u < p_exp);
+  const bool is_start = (lane == 0) || ((tmask >> (lane - 1)) & 1u);
+  const uint32_t rest = tmask >> lane;
+  const int run_end = rest ? lane + __ffs(rest) - 1 : 31;
+  const int len = is_start ? run_end - lane + 1 : 0;
+  const int maxlen = __reduce_max_sync(0xffffffffu, len);
+  double r = lane == 0 ? pc.r : 1.0;
+  int n = lane == 0 ? pc.n : 0;
+  int cnt = 0;
+  for (int t = 0; t < maxlen; t++) {
+    const double ut = __shfl_sync(0xffffffffu, u, (lane + t) & 31);
+    if (t < len) {
+      r = __dmul_rn(r, ut);
+      bool emit;
+      if (r >= p_exp) { n++; emit = !((double)n < limit); } else emit = true;
+      if (emit) {
+        if (n > 255) overflow = 1;                     // not representable: reported as an error by the host
+        stage[cnt++] = (uint8_t)min(n, 255);
+        n = 0; r = 1.0;
+      }
+    }
+  }
+  // the open run (if the block does not end on a terminator) hands its state to the next block
+  const int open_lane = tmask ? 32 - __clz(tmask) : 0;     // first position after the last terminator
+  const bool has_open = !(tmask >> 31);
+  const double or_ = __shfl_sync(0xffffffffu, r, open_lane & 31);
+  const int on_ = __shfl_sync(0xffffffffu, n, open_lane & 31);
+  pc.r = has_open ? or_ : 1.0;
+  pc.n = has_open ? on_ : 0;
+  return cnt;
+}
+
 __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t seed, const int64_t* __restrict__ part_off,
                                                                      int n_parts, int T, double mean, double p_exp,
                                                                      uint8_t* __restrict__ weights,
@@ -265,6 +361,8 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
   extern __shared__ __align__(16) uint8_t smem_raw[];
   BagSmem& S = *reinterpret_cast<BagSmem*>(smem_raw);
   const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  const int pair = wv >> 1;
+  const bool producer = (wv & 1) == 0;
   for (int e = threadIdx.x; e < 4 * 4 * 256; e += blockDim.x) {
     const int sidx = e >> 10, tb = (e >> 8) & 3, v = e & 255;
     uint32_t x = (uint32_t)v << (8 * tb);
@@ -272,12 +370,14 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
     for (int i = 0; i < reps; i++) x = well_M(x);
     S.lut[sidx][tb][v] = x;
   }
+  if (threadIdx.x < kBagPairs) { S.produced[threadIdx.x] = 0; S.consumed[threadIdx.x] = 0; S.stop[threadIdx.x] = 0; }
   __syncthreads();
-  const int part = blockIdx.x * kBagWarps + wv;
-  if (part >= n_parts) return;
-  uint32_t* A = S.state[wv];
-  {  // AbstractWell.setSeed(long): serial 624-word fill by lane 0
-    if (lane == 0) {
+  const int part = blockIdx.x * kBagPairs + pair;
+  if (part >= n_parts) return;              // both warps of the pair leave together
+  if (producer) {
+    // ---- producer warp: WELL19937c, 32 uniforms per block into the ring
+    uint32_t* A = S.state[pair];
+    if (lane == 0) {  // AbstractWell.setSeed(long)
       const int64_t sd = seed + (int64_t)part + 1;
       uint32_t a = (uint32_t)((uint64_t)sd >> 32), b = (uint32_t)((uint64_t)sd & 0xffffffffull);
       A[0] = a; A[1] = b;
@@ -288,127 +388,65 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
       }
     }
     __syncwarp();
-  }
-  auto wrap = [](int j) { return j >= 624 ? j - 624 : (j < 0 ? j + 624 : j); };
-  auto applyQ = [&](int sidx, uint32_t x) {
-    return S.lut[sidx][0][x & 255] ^ S.lut[sidx][1][(x >> 8) & 255] ^ S.lut[sidx][2][(x >> 16) & 255] ^ S.lut[sidx][3][x >> 24];
-  };
-  const double limit = __dmul_rn(1000.0, mean);
-  const int64_t lo = part_off[part], hi = part_off[part + 1];
-  uint8_t* out = weights + (size_t)lo * T;
-  const int64_t total = (hi - lo) * (int64_t)T;
-  uint32_t carry = A[0];
-  int i0 = 0;                      // state index of the block's first step
-  // Poisson state carried across blocks (uniform over the warp)
-  int64_t q = 0;                   // draws emitted so far
-  int pos = 0, mx = 0;
-  double carry_r = 1.0;            // running product / count of the draw left open by the previous block
-  int carry_n = 0;
-  int64_t flushed = 0;
-  uint8_t* stage = S.stage[wv][lane];
-  uint8_t* ob = S.obuf[wv];
-  while (true) {
-    // ---- 64 WELL steps -> 32 uniforms, one per lane
-    const int i = wrap(i0 - 2 * lane);                 // index of this lane's first step
-    const uint32_t m1a = A[wrap(i + 70)], m2a = A[wrap(i + 179)], m3a = A[wrap(i + 449)];
-    const uint32_t m1b = A[wrap(i + 69)], m2b = A[wrap(i + 178)], m3b = A[wrap(i + 448)];
-    const uint32_t t1 = A[wrap(i - 1)], t2 = A[wrap(i - 2)], t3 = A[wrap(i - 3)];
-    const uint32_t z0a = (t1 & 0x80000000u) ^ (t2 & 0x7fffffffu);
-    const uint32_t z0b = (t2 & 0x80000000u) ^ (t3 & 0x7fffffffu);
-    const uint32_t ca = m1a ^ (m1a >> 27), cb = m1b ^ (m1b >> 27);
-    const uint32_t z2a = (m2a >> 9) ^ (m3a ^ (m3a >> 1)), z2b = (m2b >> 9) ^ (m3b ^ (m3b >> 1));
-    const uint32_t ea = z0a ^ ((ca << 9) ^ (ca >> 21)) ^ (z2a << 21) ^ (z2a >> 21);
-    const uint32_t eb = z0b ^ ((cb << 9) ^ (cb >> 21)) ^ (z2b << 21) ^ (z2b >> 21);
-    uint32_t X = well_M(ea) ^ eb;
-    if (lane == 0) X ^= well_M(well_M(carry));
-    {
-      uint32_t y = __shfl_up_sync(0xffffffffu, X, 1);
-      if (lane >= 1) X ^= well_M(well_M(y));
+    uint32_t carry = A[0];
+    int i0 = 0;
+    for (uint32_t blk = 0;; blk++) {
+      while (blk - S.consumed[pair] >= (uint32_t)kBagRing) {
+        if (S.stop[pair]) return;
+        __nanosleep(40);
+      }
+      if (S.stop[pair]) return;
+      const double u = well_block(A, S, carry, i0, lane);
+      S.ring[pair][blk % kBagRing][lane] = u;
+      __threadfence_block();
+      __syncwarp();
+      if (lane == 0) S.produced[pair] = blk + 1;
+    }
+  } else {
+    // ---- consumer warp: Poisson draws, ordered compaction, coalesced flush
+    const double limit = __dmul_rn(1000.0, mean);
+    const int64_t lo = part_off[part], hi = part_off[part + 1];
+    uint8_t* out = weights + (size_t)lo * T;
+    const int64_t total = (hi - lo) * (int64_t)T;
+    int64_t q = 0, flushed = 0;
+    int pos = 0, mx = 0, overflow = 0;
+    PoissonCarry pc;
+    uint8_t* stage = S.stage[pair][lane];
+    uint8_t* ob = S.obuf[pair];
+    for (uint32_t blk = 0; q < total; blk++) {
+      while (S.produced[pair] <= blk) __nanosleep(40);
+      __threadfence_block();
+      const double u = S.ring[pair][blk % kBagRing][lane];
+      __syncwarp();
+      if (lane == 0) S.consumed[pair] = blk + 1;        // the value is in a register: the slot may be refilled
+      const int cnt = poisson_block(u, p_exp, limit, pc, stage, lane, overflow);
+      int excl = cnt;
 #pragma unroll
-      for (int sidx = 0; sidx < 4; sidx++) {
-        const int d = 2 << sidx;
-        y = __shfl_up_sync(0xffffffffu, X, d);
-        if (lane >= d) X ^= applyQ(sidx, y);
+      for (int d = 1; d < 32; d <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, excl, d);
+        if (lane >= d) excl += v;
+      }
+      const int total_cnt = __shfl_sync(0xffffffffu, excl, 31);
+      excl -= cnt;
+      const int64_t remaining = total - q;
+      const int emit_total = (int)(remaining < (int64_t)total_cnt ? remaining : (int64_t)total_cnt);
+      for (int k = 0; k < cnt; k++)
+        if (excl + k < emit_total) { const uint8_t v = stage[k]; ob[pos + excl + k] = v; mx = max(mx, (int)v); }
+      pos += emit_total;
+      q += emit_total;
+      if (pos > kBagObuf - 32 || q >= total) {
+        __syncwarp();
+        for (int t = lane; t < pos; t += 32) out[flushed + t] = ob[t];
+        flushed += pos;
+        pos = 0;
+        __syncwarp();
       }
     }
-    uint32_t bin = __shfl_up_sync(0xffffffffu, X, 1);
-    if (lane == 0) bin = carry;
-    const uint32_t z1a = (bin ^ (bin << 25)) ^ ca;
-    const uint32_t aa = z1a ^ z2a;
-    const uint32_t ba = z0a ^ (z1a ^ (z1a << 9)) ^ (z2a ^ (z2a << 21)) ^ (aa ^ (aa >> 21));
-    const uint32_t z1b = (ba ^ (ba << 25)) ^ cb;
-    const uint32_t ab = z1b ^ z2b;
-    const uint32_t bb = z0b ^ (z1b ^ (z1b << 9)) ^ (z2b ^ (z2b << 21)) ^ (ab ^ (ab >> 21));
-    carry = __shfl_sync(0xffffffffu, bb, 31);
-    __syncwarp();                                        // every lane has read its operands
-    A[i] = aa;
-    A[wrap(i - 1)] = ab;
-    const uint64_t hi26 = (uint64_t)(well_temper(ba) >> 6) << 26;
-    const uint64_t lo26 = well_temper(bb) >> 6;
-    const double u = __dmul_rn((double)(int64_t)(hi26 | lo26), 2.220446049250313e-16);   // nextDouble()
-    i0 = wrap(i0 - 64);
-    __syncwarp();
-    // ---- PoissonDistribution.sample() over the block's 32 uniforms.
-    // r <= 1 always, so a uniform below exp(-mean) ends whatever draw is running: such positions cut
-    // the stream into independent RUNS (each starts with r = 1, n = 0).  The lane that sits at a run's
-    // first position walks the run (mean length 1/(1-e^-mean) uniforms), all runs in parallel; only the
-    // block's first run inherits state from the previous block and only its last one can stay open.
-    const uint32_t tmask = __ballot_sync(0xffffffffu, u < p_exp);
-    const bool is_start = (lane == 0) || ((tmask >> (lane - 1)) & 1u);
-    const uint32_t rest = tmask >> lane;
-    const int run_end = rest ? lane + __ffs(rest) - 1 : 31;
-    const int len = is_start ? run_end - lane + 1 : 0;
-    const int maxlen = __reduce_max_sync(0xffffffffu, len);
-    double r = lane == 0 ? carry_r : 1.0;
-    int n = lane == 0 ? carry_n : 0;
-    int cnt = 0;
-    for (int t = 0; t < maxlen; t++) {
-      const double ut = __shfl_sync(0xffffffffu, u, (lane + t) & 31);
-      if (t < len) {
-        r = __dmul_rn(r, ut);
-        bool emit;
-        if (r >= p_exp) { n++; emit = !((double)n < limit); } else emit = true;
-        if (emit) {
-          if (n > 255) mx = 256;                         // not representable: reported as an error by the host
-          stage[cnt++] = (uint8_t)min(n, 255);
-          n = 0; r = 1.0;
-        }
-      }
-    }
-    // the open run (if the block does not end on a terminator) hands its state to the next block
-    const int open_lane = tmask ? 32 - __clz(tmask) : 0;     // first position after the last terminator
-    const bool has_open = !(tmask >> 31);
-    const double or_ = __shfl_sync(0xffffffffu, r, open_lane & 31);
-    const int on_ = __shfl_sync(0xffffffffu, n, open_lane & 31);
-    carry_r = has_open ? or_ : 1.0;
-    carry_n = has_open ? on_ : 0;
-    // ordered compaction of the runs' draws into the output buffer
-    int excl = cnt;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const int v = __shfl_up_sync(0xffffffffu, excl, d);
-      if (lane >= d) excl += v;
-    }
-    const int total_cnt = __shfl_sync(0xffffffffu, excl, 31);
-    excl -= cnt;
-    const int64_t remaining = total - q;
-    const int emit_total = (int)(remaining < (int64_t)total_cnt ? remaining : (int64_t)total_cnt);
-    for (int k = 0; k < cnt; k++)
-      if (excl + k < emit_total) { const uint8_t v = stage[k]; ob[pos + excl + k] = v; mx = max(mx, (int)v); }
-    pos += emit_total;
-    q += emit_total;
-    const bool done = q >= total;
-    if (pos > kBagObuf - 32 || done) {
-      __syncwarp();
-      for (int t = lane; t < pos; t += 32) out[flushed + t] = ob[t];
-      flushed += pos;
-      pos = 0;
-      __syncwarp();
-    }
-    if (done) break;
+    if (lane == 0) S.stop[pair] = 1;
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    overflow = __any_sync(0xffffffffu, overflow);
+    if (lane == 0) atomicMax(max_w, overflow ? 256 : mx);
   }
-  mx = __reduce_max_sync(0xffffffffu, mx);
-  if (lane == 0) atomicMax(max_w, mx);
 }
 // T == 1 without replacement and rate < 1: XORShiftRandom(seed+p+1).nextDouble() < rate
 __device__ __forceinline__ uint32_t mm3_mix(uint32_t k) {

@@ -63,25 +63,76 @@ extern "C" const char* emrf_version(void) { return "emrf 0.1 (sm_100a; Spark MLl
 // ---------------------------------------------------------------------------------------------
 // small RAII helpers
 // ---------------------------------------------------------------------------------------------
+// Device allocations go through a small caching layer: a released block is parked in a per-device free
+// list (size classes: powers of two up to 64 MB, 2 MB multiples above) instead of going back to the
+// driver, because cudaFree synchronises the whole device and cudaMalloc/cudaFree of many buffers per
+// fit showed up as 10-100 ms outliers.  Every release in this file happens after the stream that used
+// the block has been synchronised.  emrf_ctx_destroy trims the cache of its device.
+class DevCache {
+ public:
+  static DevCache& get() { static DevCache c; return c; }
+  static size_t round_up(size_t n) {
+    if (n < 256) n = 256;
+    if (n <= ((size_t)64 << 20)) { size_t p = 256; while (p < n) p <<= 1; return p; }
+    return (n + ((size_t)2 << 20) - 1) & ~(((size_t)2 << 20) - 1);
+  }
+  cudaError_t take(size_t n, void** out, size_t* cap) {
+    const size_t want = round_up(n);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      auto it = free_.find(std::make_pair(dev, want));
+      if (it != free_.end()) { *out = it->second; *cap = want; free_.erase(it); return cudaSuccess; }
+    }
+    cudaError_t e = cudaMalloc(out, want);
+    if (e != cudaSuccess) {       // out of memory: give cached blocks back and retry once
+      cudaGetLastError();
+      trim(dev);
+      e = cudaMalloc(out, want);
+    }
+    if (e == cudaSuccess) *cap = want;
+    return e;
+  }
+  void give(void* p, size_t cap) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(mu_);
+    free_.insert(std::make_pair(std::make_pair(dev, cap), p));
+  }
+  void trim(int dev) {
+    std::vector<void*> blocks;
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      for (auto it = free_.begin(); it != free_.end();) {
+        if (it->first.first == dev) { blocks.push_back(it->second); it = free_.erase(it); } else ++it;
+      }
+    }
+    for (void* p : blocks) cudaFree(p);
+  }
+
+ private:
+  std::mutex mu_;
+  std::multimap<std::pair<int, size_t>, void*> free_;
+};
+
 struct DevBuf {
   void* p = nullptr;
-  size_t bytes = 0;
+  size_t bytes = 0;   // capacity
   DevBuf() {}
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
   DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
   ~DevBuf() { release(); }
   void release() {
-    if (p) cudaFree(p);
+    if (p) DevCache::get().give(p, bytes);
     p = nullptr;
     bytes = 0;
   }
   cudaError_t alloc(size_t n) {
+    if (p && n <= bytes) return cudaSuccess;
     release();
-    if (n == 0) n = 16;
-    cudaError_t e = cudaMalloc(&p, n);
-    if (e == cudaSuccess) bytes = n;
-    return e;
+    return DevCache::get().take(n, &p, &bytes);
   }
   cudaError_t ensure(size_t n) {  // grow-only
     if (n <= bytes) return cudaSuccess;
@@ -276,7 +327,9 @@ extern "C" void emrf_ctx_destroy(emrf_ctx_t* c) {
   }
   if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
   if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
+  const int dev = c->device;
   delete c;
+  DevCache::get().trim(dev);
 }
 extern "C" int emrf_get_timings(const emrf_ctx_t* c, emrf_timings_t* out) {
   if (!c || !out) return fail(EMRF_ERR_ARG, "NULL argument");

@@ -1024,6 +1024,9 @@ struct SplitNode {
   int32_t feature;
   int32_t split_bin;
 };
+// Each warp owns a contiguous run of 256 entries of the tile: eight coalesced 8-byte loads and eight
+// column gathers are in flight per lane before anything is consumed.
+constexpr int kPartPerLane = kPartTile / kPartThreads;   // 8
 __global__ void __launch_bounds__(kPartThreads) part_count_kernel(const uint64_t* ent0, const uint64_t* ent1,
                                                                   const uint8_t* __restrict__ bins_cm, int64_t Np,
                                                                   const SplitNode* __restrict__ nodes,
@@ -1036,13 +1039,20 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(const uint64_t
   const uint64_t* ent = (nd.buf ? ent1 : ent0) + nd.seg_start + (uint64_t)t_in * kPartTile;
   const uint32_t len = min((uint32_t)kPartTile, nd.seg_len - t_in * kPartTile);
   const uint8_t* col = bins_cm + (size_t)nd.feature * Np;
-  uint32_t c = 0;
-  for (uint32_t j = threadIdx.x; j < len; j += kPartThreads) {
-    const uint32_t row = (uint32_t)ent[j];
-    c += ((int)col[row] <= nd.split_bin);
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  const uint32_t wbase = wv * (32 * kPartPerLane);
+  uint32_t rows[kPartPerLane];
+#pragma unroll
+  for (int r = 0; r < kPartPerLane; r++) {
+    const uint32_t j = wbase + r * 32 + lane;
+    rows[r] = j < len ? (uint32_t)__ldcs(ent + j) : 0xffffffffu;
   }
+  uint32_t c = 0;
+#pragma unroll
+  for (int r = 0; r < kPartPerLane; r++)
+    if (rows[r] != 0xffffffffu) c += ((int)col[rows[r]] <= nd.split_bin);
   for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-  if ((threadIdx.x & 31) == 0) sh_cnt[threadIdx.x >> 5] = c;
+  if (lane == 0) sh_cnt[wv] = c;
   __syncthreads();
   if (threadIdx.x == 0) {
     uint32_t s = 0;
@@ -1086,7 +1096,6 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64
                                                                     const uint32_t* __restrict__ tile_left_off,
                                                                     const uint64_t* __restrict__ n_left) {
   __shared__ uint32_t sh_w[kPartThreads / 32];
-  __shared__ uint32_t sh_base;
   const uint32_t g = tile_node[blockIdx.x];
   const SplitNode nd = nodes[g];
   const uint32_t t_in = blockIdx.x - nd.tile_begin;
@@ -1097,34 +1106,39 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64
   const uint8_t* col = bins_cm + (size_t)nd.feature * Np;
   const uint64_t left_base = tile_left_off[blockIdx.x];
   const uint64_t right_base = n_left[g] + (tile_start - left_base);
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (threadIdx.x == 0) sh_base = 0;
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  const uint32_t wbase = wv * (32 * kPartPerLane);
+  // this warp's 256 contiguous entries, eight loads and eight gathers in flight per lane
+  uint64_t e[kPartPerLane];
+#pragma unroll
+  for (int r = 0; r < kPartPerLane; r++) {
+    const uint32_t j = wbase + r * 32 + lane;
+    e[r] = j < len ? __ldcs(ent + j) : ~0ull;
+  }
+  uint32_t bal[kPartPerLane];
+  uint32_t wleft = 0;
+#pragma unroll
+  for (int r = 0; r < kPartPerLane; r++) {
+    const bool left = (e[r] != ~0ull) && ((int)col[(uint32_t)e[r]] <= nd.split_bin);
+    bal[r] = __ballot_sync(0xffffffffu, left);
+    wleft += __popc(bal[r]);
+  }
+  if (lane == 0) sh_w[wv] = wleft;
   __syncthreads();
-  for (uint32_t j0 = 0; j0 < len; j0 += kPartThreads) {
-    const uint32_t j = j0 + threadIdx.x;
-    const bool act = j < len;
-    uint64_t e = 0;
-    bool left = false;
-    if (act) { e = ent[j]; left = ((int)col[(uint32_t)e] <= nd.split_bin); }
-    const uint32_t bal = __ballot_sync(0xffffffffu, left);
-    const uint32_t before = __popc(bal & ((1u << lane) - 1));
-    if (lane == 0) sh_w[wid] = __popc(bal);
-    __syncthreads();
-    uint32_t wbase = 0, round_total = 0;
-    for (int i = 0; i < kPartThreads / 32; i++) {
-      const uint32_t c = sh_w[i];
-      if (i < wid) wbase += c;
-      round_total += c;
+  uint32_t lefts_before = 0;   // lefts in earlier warps of the tile
+  for (int i = 0; i < wv; i++) lefts_before += sh_w[i];
+  // stable: position inside the tile decides the rank on either side
+  uint32_t lrank = lefts_before;
+#pragma unroll
+  for (int r = 0; r < kPartPerLane; r++) {
+    const uint32_t j = wbase + r * 32 + lane;
+    const uint32_t before = __popc(bal[r] & ((1u << lane) - 1));
+    if (j < len) {
+      const uint32_t my_l = lrank + before;           // lefts before j in the tile
+      if ((bal[r] >> lane) & 1u) dst[left_base + my_l] = e[r];
+      else dst[right_base + (j - my_l)] = e[r];
     }
-    const uint32_t lefts_before_round = sh_base;       // lefts in earlier rounds of this tile
-    const uint32_t lrank = lefts_before_round + wbase + before;
-    if (act) {
-      if (left) dst[left_base + lrank] = e;
-      else dst[right_base + (j - lrank)] = e;          // j - (#lefts before j in tile) = right rank
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) sh_base = lefts_before_round + round_total;
-    __syncthreads();
+    lrank += __popc(bal[r]);
   }
 }
 

@@ -648,6 +648,7 @@ static int hist_geometry(emrf_ctx* c, int Fp, int f_sub, int B, int C, int* ch_o
   if (k_chunk < f_sub && k_chunk < 4) k_chunk = (int)((smem_cap - fixed) / per_feat);  // big bins x classes: one CTA per SM
   if (k_chunk < 1) return fail(EMRF_ERR_LIMIT, "one feature histogram (%d bins x %d classes) exceeds shared memory", B, C);
   k_chunk = std::min(k_chunk, f_sub);
+  if (ch) k_chunk = std::min(k_chunk, 64);   // the row-tile path keeps 64 per-feature offsets in shared memory
   *ch_out = ch;
   *k_chunk_out = k_chunk;
   *n_chunks_out = (f_sub + k_chunk - 1) / k_chunk;

@@ -633,12 +633,11 @@ struct HistArgs {
 // two FMA correction steps instead of the generic IEEE division sequence.  q0 = RN(a*y) is within
 // 2 ulp of a/b; r = a - b*q is exact in an FMA; q + r*y then differs from a/b by < 2^-52 ulp, far less
 // than the distance (>= 2^-33 ulp) from a quotient of two such integers to any rounding midpoint,
-// so RN(q + r*y) = RN(a / b) — the value the JVM's `/` produces.  The second step is a safety net.
+// so RN(q + r*y) = RN(a / b) — the value the JVM's `/` produces (checked against true division on
+// the host for every chosen split when EMRF_VERIFY_GAINS is set, and by the oracle parity tests).
 __device__ __forceinline__ double div_by(double a, double b, double y) {
-  double q = __dmul_rn(a, y);
-  double r = __fma_rn(-b, q, a);
-  q = __fma_rn(r, y, q);
-  r = __fma_rn(-b, q, a);
+  const double q = __dmul_rn(a, y);
+  const double r = __fma_rn(-b, q, a);
   return __fma_rn(r, y, q);
 }
 // Impurity of the class-count vector v[c] = (sub ? sub[c] - cnt[c] : cnt[c]); total_u = sum v.
@@ -704,7 +703,7 @@ inline int hist_row_chunks(int Fp) { return (Fp / 16 <= 8) ? Fp / 16 : 0; }
 inline size_t hist_tile_bytes(int ch) {
   if (ch == 0) return 0;
   const int stride = (ch == 1 || ch == 2 || ch == 4 || ch == 8) ? 32 + 8 / ch : 33;
-  return (size_t)(kHistThreads / 32) * 4 * ch * stride * 4;
+  return (size_t)(kHistThreads / 32) * 4 * ch * stride * 4 + 64 * 4;   // + per-feature tile offsets (k_chunk <= 64 here)
 }
 
 // first index of the largest value among v(c), c < C, computed by one warp (call with all 32 lanes)
@@ -782,8 +781,24 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
     if (lc < (uint32_t)min_instances || rc < (uint32_t)min_instances) {
       gain = kInvalidGain;
     } else {
-      li = impurity_dev(impurity, l, nullptr, C, lc);
-      ri = impurity_dev(impurity, l, S.tot, C, rc);
+      if (impurity == 0) {
+        // both children in one pass over the classes (same per-child operation order as Gini.calculate)
+        const double lt = (double)lc, rt = (double)rc;
+        const double ly = __drcp_rn(lt), ry = __drcp_rn(rt);
+        double il = 1.0, ir = 1.0;
+#pragma unroll 5
+        for (int c = 0; c < C; c++) {
+          const uint32_t lv = l[c], rv = S.tot[c] - lv;
+          const double fl = div_by((double)lv, lt, ly);
+          const double fr = div_by((double)rv, rt, ry);
+          il = __dsub_rn(il, __dmul_rn(fl, fl));
+          ir = __dsub_rn(ir, __dmul_rn(fr, fr));
+        }
+        li = il; ri = ir;
+      } else {
+        li = impurity_dev(impurity, l, nullptr, C, lc);
+        ri = impurity_dev(impurity, l, S.tot, C, rc);
+      }
       const double tc = (double)tot_all;  // (leftCount + rightCount).toDouble
       const double lw = __ddiv_rn((double)lc, tc);
       const double rw = __ddiv_rn((double)rc, tc);
@@ -934,6 +949,10 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
     uint32_t* tile = reinterpret_cast<uint32_t*>(smem_raw + A.tile_smem_off) + wv * RowTile<CHX>::kWarpWords;
     const uint8_t* tile_b = reinterpret_cast<const uint8_t*>(tile);
     const uint32_t n_batches = (len + 31) >> 5;
+    // per-feature byte offsets into the transposed tile: word (f >> 2) of every row, byte (f & 3)
+    int* sh_off = reinterpret_cast<int*>(smem_raw + A.tile_smem_off + NW * RowTile<CHX>::kWarpWords * 4);
+    for (int k = tid; k < kc; k += kHistThreads) sh_off[k] = (((sh_feat[k] >> 2) * TS) << 2) + (sh_feat[k] & 3);
+    __syncthreads();
     uint4 R[CHX];
     uint32_t b = wv;
     uint64_t e_cur = load_entry(ent, len, b * 32 + lane);
@@ -948,10 +967,13 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
       const uint32_t lab = (uint32_t)(e_cur >> 40) & 0xffu;
       if (w) {
         uint32_t* hl = sh + lab;
+        const uint8_t* tb = tile_b + (lane << 2);
+        const int BC = B * C;
+#pragma unroll 4
         for (int k = 0; k < kc; k++) {
-          const int f = sh_feat[k];
-          const uint32_t bin = tile_b[(((f >> 2) * TS + lane) << 2) + (f & 3)];
-          atomicAdd(hl + (k * B + bin) * C, w);
+          const uint32_t bin = tb[sh_off[k]];            // byte offset of feature k inside the transposed tile
+          atomicAdd(hl + bin * C, w);
+          hl += BC;
         }
       }
       __syncwarp();

@@ -166,6 +166,10 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 static inline double now_ms() {
   return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
+static bool env_flag(const char* name) {   // set and not empty / "0"
+  const char* v = getenv(name);
+  return v && *v && strcmp(v, "0") != 0;
+}
 static bool is_device_ptr(const void* p) {
   if (!p) return false;
   cudaPointerAttributes a;
@@ -213,6 +217,11 @@ struct emrf_ctx {
   // fit-sized buffers kept between fits (grow-only): cudaMalloc/cudaFree of GB-sized buffers costs
   // milliseconds and cudaFree synchronises the device; they are released by emrf_ctx_destroy
   DevBuf p_w, p_X, p_y, p_labels, p_rm, p_cm, p_ent0, p_ent1, p_counts;
+  // row-sharded push mode: this rank's staging buffer and the peers' buffers mapped through CUDA IPC
+  DevBuf p_stage, p_ipc;
+  void* peer_stage[8] = {nullptr};
+  size_t peer_bytes = 0;
+  bool peer_ok = false;
   // pinned arena that keeps every group's split records for the whole fit (nodes point into it)
   std::vector<std::unique_ptr<PinnedBuf>> arena;
   size_t arena_chunk = 0, arena_used = 0;
@@ -321,6 +330,8 @@ extern "C" int emrf_ctx_create_dist(int32_t device, int32_t rank, int32_t world,
 extern "C" void emrf_ctx_destroy(emrf_ctx_t* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  for (int r = 0; r < 8; r++)
+    if (r != c->rank && c->peer_stage[r]) cudaIpcCloseMemHandle(c->peer_stage[r]);
   if (c->nccl_comm) {
     auto d = (ncclCommDestroy_t)dlsym(c->nccl_lib, "ncclCommDestroy");
     if (d) d(c->nccl_comm);
@@ -355,6 +366,47 @@ static int nccl_reduce_scatter_u32(emrf_ctx* c, uint32_t* buf, size_t per_rank) 
   if (!rs) return fail(EMRF_ERR_CUDA, "ncclReduceScatter missing");
   int rc = rs(buf, buf + (size_t)c->rank * per_rank, per_rank, /*ncclUint32*/ 3, /*ncclSum*/ 0, c->nccl_comm, c->stream);
   if (rc) return fail(EMRF_ERR_CUDA, "ncclReduceScatter failed (%d)", rc);
+  return EMRF_OK;
+}
+
+// Staging buffers of the fused histogram + reduce-scatter path: every rank allocates `bytes`, the CUDA IPC
+// handles are exchanged with an all-reduce over zero-filled slots, and each rank maps its peers' buffers.
+// Collective: every rank must call it with the same `bytes`.
+static int peer_stage_setup(emrf_ctx* c, size_t bytes) {
+  if (c->world > 8) return fail(EMRF_ERR_LIMIT, "peer staging supports up to 8 ranks");
+  if (c->peer_ok && c->peer_bytes >= bytes) return EMRF_OK;
+  cudaStream_t st = c->stream;
+  for (int r = 0; r < c->world; r++)
+    if (r != c->rank && c->peer_stage[r]) { cudaIpcCloseMemHandle(c->peer_stage[r]); c->peer_stage[r] = nullptr; }
+  c->peer_ok = false;
+  CU(c->p_ipc.ensure((size_t)c->world * 64 + 64));
+  {  // nobody may free a buffer a peer still has mapped: everybody has closed before anybody re-allocates
+    CU(cudaMemsetAsync(c->p_ipc.p, 0, 4, st));
+    TRY(nccl_allreduce_u32(c, c->p_ipc.as<uint32_t>(), 1));
+    CU(cudaStreamSynchronize(st));
+  }
+  CU(c->p_stage.ensure_exact(bytes));
+  cudaIpcMemHandle_t mine;
+  CU(cudaIpcGetMemHandle(&mine, c->p_stage.p));
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  std::vector<uint8_t> all((size_t)c->world * 64, 0);
+  memcpy(&all[(size_t)c->rank * 64], &mine, 64);
+  CU(cudaMemcpyAsync(c->p_ipc.p, all.data(), all.size(), cudaMemcpyHostToDevice, st));
+  TRY(nccl_allreduce_u32(c, c->p_ipc.as<uint32_t>(), all.size() / 4));
+  CU(cudaMemcpyAsync(all.data(), c->p_ipc.p, all.size(), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (int r = 0; r < c->world; r++) {
+    if (r == c->rank) { c->peer_stage[r] = c->p_stage.p; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, &all[(size_t)r * 64], 64);
+    cudaError_t e = cudaIpcOpenMemHandle(&c->peer_stage[r], h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(EMRF_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d) failed: %s", r, cudaGetErrorString(e));
+    }
+  }
+  c->peer_bytes = c->p_stage.bytes >= bytes ? bytes : 0;
+  c->peer_ok = true;
   return EMRF_OK;
 }
 
@@ -470,7 +522,9 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
   h_ns.assign(F, 0);
   if (num_splits >= 1) {
     std::vector<int64_t> rows;
+    const double t_s0 = now_ms();
     const bool sampled = hl::find_splits_rows(P, N, part_off, n_parts, &rows);
+    if (env_flag("EMRF_DEBUG_TIMERS")) fprintf(stderr, "[emrf] findSplits row sampler: %.3f ms (%zu rows)\n", now_ms() - t_s0, rows.size());
     const int64_t n_s64 = sampled ? (int64_t)rows.size() : N;
     if (n_s64 > (1 << 22)) return fail(EMRF_ERR_LIMIT, "findSplits sample too large (%lld)", (long long)n_s64);
     const int n_s = (int)n_s64;
@@ -510,7 +564,15 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
         if (n_own)
           kern::fs_gather_sharded_kernel<<<(unsigned)(((int64_t)n_own * F + 255) / 256), 256, 0, c->stream>>>(
               dX, F, d_or.as<int64_t>(), d_op.as<int32_t>(), n_own, n_pad, d_S.as<double>());
+        const double t_ar0 = now_ms();
+        if (env_flag("EMRF_DEBUG_TIMERS")) CU(cudaStreamSynchronize(c->stream));
+        const double t_ar1 = now_ms();
         TRY(nccl_allreduce_u32(c, d_S.as<uint32_t>(), (size_t)F * n_pad * 2));
+        if (env_flag("EMRF_DEBUG_TIMERS")) {
+          CU(cudaStreamSynchronize(c->stream));
+          fprintf(stderr, "[emrf] sharded findSplits: gather %.3f ms, all-reduce of %zu B %.3f ms\n", t_ar1 - t_ar0,
+                  (size_t)F * n_pad * 8, now_ms() - t_ar1);
+        }
         kern::fs_mark_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(d_S.as<double>(), F, n_s, n_pad,
                                                                                     P.find_splits_policy == 0 ? 1 : 0);
         c->tm.kernel_launches += 1;
@@ -914,6 +976,26 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(hist_launch(row_ch, dim3(1), hist_smem, st, kern::HistArgs(), true));
   if (row_sharded) CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
   const size_t slot_words = (size_t)f_sub * B * C;
+  // row-sharded: partial histograms are pushed straight into the owner rank's staging buffer over NVLink
+  // (fused histogram + reduce-scatter); EMRF_NO_PEER=1 keeps the NCCL reduce-scatter path instead
+  bool push_mode = false;
+  if (row_sharded && c->world > 1 && c->world <= 8 && !env_flag("EMRF_NO_PEER")) {
+    int64_t sb = 0;   // fewest bins a node's aggregate can have → most nodes a group can hold
+    {
+      std::vector<int> nbs(num_bins.begin(), num_bins.end());
+      std::sort(nbs.begin(), nbs.end());
+      for (int k = 0; k < f_sub; k++) sb += nbs[k];
+    }
+    const int64_t max_mem_b = (int64_t)P.max_memory_mb * 1024ll * 1024ll;
+    const int64_t max_nodes = max_mem_b / std::max<int64_t>((int64_t)C * sb * 8, 1) + 1;
+    const int64_t npr_max = (max_nodes + c->world - 1) / c->world + 1;
+    const size_t stage_bytes = (size_t)c->world * (size_t)npr_max * slot_words * 4;
+    if (stage_bytes <= ((size_t)8 << 30)) {
+      TRY(peer_stage_setup(c, stage_bytes));
+      CU(cudaFuncSetAttribute(kern::scan_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
+      push_mode = true;
+    }
+  }
 
   // ---- trees, stack, driver RNG (RandomForest.run)
   std::vector<HTree> trees(T);
@@ -1075,7 +1157,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       d.pad = 0;
       d.tile_begin = n_tiles;
       d.n_tiles = mine(group[i].tree) ? std::max<uint32_t>(1, (hn.seg_len + tile_len - 1) / tile_len) : 0;
-      d.slot = (row_sharded || d.n_tiles > 1) ? n_slots++ : -1;   // row-sharded: every histogram goes to HBM for the all-reduce
+      // row-sharded without push mode: every histogram goes to HBM for the reduce-scatter
+      d.slot = ((row_sharded && !push_mode) || d.n_tiles > 1) ? n_slots++ : -1;
       n_tiles += d.n_tiles;
     }
     const size_t off_feat = align_up(sizeof(kern::GroupNode) * (size_t)n_nodes, 16);
@@ -1099,7 +1182,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     if (!h_res) return fail(EMRF_ERR_CUDA, "out of pinned host memory for the split-record arena");
     CU(c->d_tickets.ensure(n_rec * 4));
     const int nodes_per_rank = row_sharded ? (n_nodes + c->world - 1) / c->world : 0;
-    const int n_slots_alloc = row_sharded ? nodes_per_rank * c->world : n_slots;
+    const int n_slots_alloc = (row_sharded && !push_mode) ? nodes_per_rank * c->world : n_slots;
     CU(c->d_ghist.ensure((size_t)std::max(n_slots_alloc, 1) * slot_words * 4));
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_sel += d_; }
 
@@ -1126,6 +1209,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.tile_len = tile_len;
     A.tile_smem_off = (uint32_t)hist_bytes;
     A.impurity = P.impurity; A.min_instances = P.min_instances_per_node; A.hist_only = row_sharded ? 1 : 0;
+    A.push_world = push_mode ? c->world : 0; A.push_rank = c->rank; A.push_npr = nodes_per_rank;
+    for (int r = 0; r < 8; r++) A.peer_stage[r] = (uint32_t*)c->peer_stage[r];
     A.min_info_gain = P.min_info_gain;
     cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
     CU(cudaEventRecord(e0, st));
@@ -1137,7 +1222,22 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaEventRecord(e1, st));
     hist_ev.emplace_back(e0, e1);
     CU(cudaGetLastError());
-    if (row_sharded) {
+    if (row_sharded && push_mode) {
+      // every rank's partials must have landed in the owners' staging buffers: a 1-word all-reduce is the
+      // cross-rank barrier (in stream order it follows this rank's histogram kernel)
+      CU(cudaMemsetAsync(c->d_tickets.p, 0, 4, st));
+      TRY(nccl_allreduce_u32(c, c->d_tickets.as<uint32_t>(), 1));
+      const int first = c->rank * nodes_per_rank;
+      const int mine_n = std::max(0, std::min(nodes_per_rank, n_nodes - first));
+      if (mine_n > 0) {
+        kern::scan_sum_kernel<<<dim3(mine_n, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
+            c->p_stage.as<uint32_t>(), c->world, nodes_per_rank, first, A.node_feat, A.num_bins_all, f_sub, B, C, k_chunk,
+            n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain, A.results, A.left_counts, A.total_counts);
+        tm.kernel_launches++;
+        CU(cudaGetLastError());
+      }
+      TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
+    } else if (row_sharded) {
       // reduceByKey(_.merge(_)) of Spark's per-partition aggregators, keyed by node exactly as Spark
       // does it: a reduce-scatter leaves each rank with the summed histograms (exact integers) of ITS
       // share of the group's nodes, it scans those, and the small split records are combined with an

@@ -626,6 +626,9 @@ struct HistArgs {
   uint32_t tile_len;
   uint32_t tile_smem_off;      // byte offset of the per-warp row tiles inside dynamic shared memory
   int32_t impurity, min_instances, hist_only;
+  // row-sharded push mode: partial histograms go straight into the owner rank's staging buffer over NVLink
+  int32_t push_world, push_rank, push_npr;   // push_world == 0: off
+  uint32_t* peer_stage[8];                   // [owner]: base of that rank's staging buffer (peer-mapped)
   double min_info_gain;
 };
 
@@ -985,6 +988,32 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
 
   const size_t slot_words = (size_t)A.f_sub * B * C;
   const size_t rec = (size_t)g * A.n_chunks + chunk;
+  if (A.push_world) {
+    // ---- fused histogram + reduce-scatter: this rank's partial histogram of node g is stored, dense and
+    // coalesced, into slot [this rank][g's index on its owner] of the OWNER rank's staging buffer through
+    // the NVLink peer mapping — tile by tile, while other CTAs are still accumulating.  The owner sums
+    // the `world` partials when it scans the node (scan_sum_kernel).  No atomics cross the link.
+    const int owner = (int)(g / (uint32_t)A.push_npr);
+    const uint32_t local = g - (uint32_t)owner * (uint32_t)A.push_npr;
+    uint32_t* dst = A.peer_stage[owner] + ((size_t)A.push_rank * A.push_npr + local) * slot_words + (size_t)k0 * B * C;
+    if (nd.slot < 0) {                       // the whole local segment was this one tile
+      for (int i = tid; i < kc * B * C; i += kHistThreads) dst[i] = sh[i];
+      return;
+    }
+    uint32_t* gh = A.ghist + (size_t)nd.slot * slot_words + (size_t)k0 * B * C;
+    for (int i = tid; i < kc * B * C; i += kHistThreads) {
+      const uint32_t v = sh[i];
+      if (v) atomicAdd(&gh[i], v);
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) sh_last = (atomicAdd(&A.tickets[rec], 1u) == nd.n_tiles - 1);
+    __syncthreads();
+    if (!sh_last) return;
+    __threadfence();
+    for (int i = tid; i < kc * B * C; i += kHistThreads) dst[i] = __ldcg(&gh[i]);   // last tile forwards the sum
+    return;
+  }
   if (nd.slot >= 0) {
     uint32_t* gh = A.ghist + (size_t)nd.slot * slot_words + (size_t)k0 * B * C;
     for (int i = tid; i < kc * B * C; i += kHistThreads) {
@@ -1023,6 +1052,34 @@ __global__ void __launch_bounds__(kHistThreads) scan_kernel(const uint32_t* __re
   for (int k = tid; k < kc; k += kHistThreads) sh_nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
   const uint32_t* gh = hist + ((size_t)g * f_sub + k0) * B * C;
   for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = gh[i];
+  __syncthreads();
+  const size_t rec = (size_t)g * n_chunks + chunk;
+  scan_chunk(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,
+             total_counts + rec * C);
+}
+
+// Owner-side scan of the push mode: node `node0 + blockIdx.x` of the group is summed over the `n_src`
+// partial histograms the ranks stored into this rank's staging buffer (stage[src][local][f_sub*B*C]).
+__global__ void __launch_bounds__(kHistThreads) scan_sum_kernel(const uint32_t* __restrict__ stage, int n_src, int npr,
+                                                               int node0, const int32_t* node_feat,
+                                                               const int32_t* num_bins_all, int f_sub, int B, int C,
+                                                               int k_chunk, int n_chunks, int impurity, int min_instances,
+                                                               double min_info_gain, ScanResult* results,
+                                                               uint32_t* left_counts, uint32_t* total_counts) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int tid = threadIdx.x;
+  const int local = blockIdx.x, g = node0 + local, chunk = blockIdx.y;
+  const int k0 = chunk * k_chunk;
+  const int kc = min(k_chunk, f_sub - k0);
+  const ScanSmem S = carve_smem(smem_raw, k_chunk, B, C);
+  uint32_t* sh = S.hist;
+  for (int k = tid; k < kc; k += kHistThreads) S.nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
+  const size_t slot_words = (size_t)f_sub * B * C;
+  for (int i = tid; i < kc * B * C; i += kHistThreads) {
+    uint32_t v = 0;
+    for (int r = 0; r < n_src; r++) v += __ldcg(stage + ((size_t)r * npr + local) * slot_words + (size_t)k0 * B * C + i);
+    sh[i] = v;
+  }
   __syncthreads();
   const size_t rec = (size_t)g * n_chunks + chunk;
   scan_chunk(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,

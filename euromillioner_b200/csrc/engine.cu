@@ -976,10 +976,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(hist_launch(row_ch, dim3(1), hist_smem, st, kern::HistArgs(), true));
   if (row_sharded) CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
   const size_t slot_words = (size_t)f_sub * B * C;
-  // row-sharded: partial histograms are pushed straight into the owner rank's staging buffer over NVLink
-  // (fused histogram + reduce-scatter); EMRF_NO_PEER=1 keeps the NCCL reduce-scatter path instead
+  // row-sharded, EMRF_PEER_PUSH=1: partial histograms are pushed straight into the owner rank's staging
+  // buffer over NVLink (fused histogram + reduce-scatter).  Measured on 8 B200s it is ~4 % SLOWER per fit
+  // than local flush + ncclReduceScatter (the remote stores lengthen the histogram kernel by more than the
+  // collective costs), so the NCCL path stays the default; see DESIGN.md §5.
   bool push_mode = false;
-  if (row_sharded && c->world > 1 && c->world <= 8 && !env_flag("EMRF_NO_PEER")) {
+  if (row_sharded && c->world > 1 && c->world <= 8 && env_flag("EMRF_PEER_PUSH")) {
     int64_t sb = 0;   // fewest bins a node's aggregate can have → most nodes a group can hold
     {
       std::vector<int> nbs(num_bins.begin(), num_bins.end());

@@ -53,9 +53,11 @@ def test_tree_and_row_sharded_fits_match_oracle_on_2_gpus():
     cuda.cuDeviceGetCount(ctypes.byref(n))
     if n.value < 2:
         pytest.skip("needs 2 GPUs")
-    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-                        "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "dist_fit_check.py")],
-                       capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-    assert "DIST_FIT_OK world=2" in r.stdout
-    assert r.stdout.count("DIST_ROWS_OK world=2") == 2
+    for push in ("0", "1"):   # NCCL reduce-scatter path, then the fused NVLink-push path
+        env = dict(os.environ, EMRF_PEER_PUSH=push)
+        r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                            "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "dist_fit_check.py")],
+                           capture_output=True, text=True, timeout=600, env=env)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        assert "DIST_FIT_OK world=2" in r.stdout
+        assert r.stdout.count("DIST_ROWS_OK world=2") == 2

@@ -92,7 +92,42 @@ def kernel_summary():
         return traffic
 
 
+def hist_dram():
+    path = os.path.join(go, f"hist_dram_{tag}.csv")
+    if not os.path.exists(path):
+        return None
+    rows = list(csv.reader(open(path)))
+    h = [i for i, r in enumerate(rows) if r and r[0] == "ID"][0]
+    H, data = rows[h], rows[h + 1:]
+    ii, mi, vi, ui = H.index("ID"), H.index("Metric Name"), H.index("Metric Value"), H.index("Metric Unit")
+    per = collections.OrderedDict()
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for r in data:
+        if len(r) <= vi:
+            continue
+        d = per.setdefault(r[ii], {"bytes": 0.0, "ms": 0.0})
+        if r[mi].startswith("dram__bytes"):
+            d["bytes"] += float(r[vi].replace(",", "")) * scale.get(r[ui], 1)
+        elif r[mi].startswith("gpu__time"):
+            d["ms"] = ms(r[vi], r[ui])
+    vals = list(per.values())
+    tot_b, tot_ms = sum(v["bytes"] for v in vals), sum(v["ms"] for v in vals)
+    out = {"kernel": "hist_scan_kernel", "launches": len(vals), "dram_bytes_per_launch": tot_b / len(vals),
+           "dram_bytes_per_fit": tot_b, "kernel_ms_per_fit_under_ncu": tot_ms,
+           "how": "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum -k regex:hist_scan, "
+                  "every launch of one fit of BASELINE configs[1]; mean over the launches"}
+    json.dump(out, open(os.path.join(out_dir, "hist_kernel_traffic.json"), "w"), indent=1)
+    with open(os.path.join(out_dir, f"{tag}_hist_kernel.md"), "a") as f:
+        f.write(f"## DRAM traffic of every launch in one fit\n\n{len(vals)} launches, {tot_b / 1e9:.2f} GB read+written in total "
+                f"({tot_b / len(vals) / 1e6:.1f} MB per launch) against 13.36 GB of algorithmic bytes per fit "
+                f"(`emrf_timings_t.hist_alg_bytes`).\n\n| launch | ms | DRAM MB |\n|---:|---:|---:|\n")
+        for i, v in enumerate(vals):
+            f.write(f"| {i + 1} | {v['ms']:.3f} | {v['bytes'] / 1e6:.1f} |\n")
+    return out
+
+
 agg, tot = launches()
 traffic = kernel_summary()
+print("hist dram:", hist_dram())
 print("kernels:", {k: round(v[1], 3) for k, v in agg.items()}, "total", round(tot, 3))
 print("traffic:", traffic)

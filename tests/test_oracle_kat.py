@@ -153,3 +153,21 @@ def test_cfg1_forest_matches_committed_golden(oracle):
     assert float(e["gain"].sum()) == g["gain_sum"]
     raw, prob, pred = fo.predict(X[:64])
     assert [int(v) for v in pred] == g["pred_head"]
+
+
+def test_oracle_learns_like_an_independent_random_forest(oracle):
+    """Secondary sanity oracle (not a parity claim): on a learnable problem the restated
+    Spark forest must reach about the accuracy scikit-learn's RandomForestClassifier reaches."""
+    sklearn = pytest.importorskip("sklearn.ensemble")
+    rng = np.random.default_rng(11)
+    X = rng.integers(1, 51, size=(6000, 20)).astype(np.float64)
+    y = ((X[:, 0] > 25).astype(int) * 2 + (X[:, 3] + X[:, 7] > 50).astype(int)).astype(np.float64)
+    flip = rng.random(len(y)) < 0.05
+    y[flip] = rng.integers(0, 4, size=flip.sum())
+    Xtr, ytr, Xte, yte = X[:4000], y[:4000], X[4000:], y[4000:]
+    p = oracle.make_params(num_trees=30, max_depth=8, num_classes=4, seed=7)
+    fo = oracle.fit(p, Xtr, ytr, oracle.partition_offsets(len(Xtr), 4))
+    acc = float((fo.predict(Xte)[2] == yte).mean())
+    sk = sklearn.RandomForestClassifier(n_estimators=30, max_depth=8, max_features="sqrt", random_state=7).fit(Xtr, ytr)
+    acc_sk = float((sk.predict(Xte) == yte).mean())
+    assert acc > 0.85 and abs(acc - acc_sk) < 0.05, (acc, acc_sk)

@@ -89,6 +89,7 @@ def lib():
     L.emrf_histogram.argtypes = [vp, vp, i64, i32, vp, vp, i32, vp, i32, vp, i32, vp]
     L.emrf_best_splits.argtypes = [vp, vp, i32, vp, i32, vp, i32, i32, i32, i32, f64, vp, vp, vp, vp, vp, vp]
     L.emrf_update_partition.argtypes = [vp, vp, i64, i32, vp, vp, i32, vp, vp, vp, vp]
+    L.emrf_build_lag_features.argtypes = [vp, vp, i32, i32, i32, vp, vp]
     L.emrf_update_partition_noalloc.argtypes = [vp, vp, i64, i32, vp, vp, i32, vp, vp, vp, vp]
     L.emrf_host_java_random_next_long.argtypes = [i64, i32]
     L.emrf_host_java_random_next_long.restype = i64

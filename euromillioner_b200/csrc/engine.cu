@@ -2134,3 +2134,30 @@ extern "C" int emrf_update_partition_noalloc(emrf_ctx_t* c, const uint8_t* bins_
   CU(cudaStreamSynchronize(st));  // sn / tn are pageable host memory read by the async copies
   return EMRF_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// emrf_build_lag_features — draw table -> lag-window feature matrix + label column, on the device
+// ---------------------------------------------------------------------------------------------
+extern "C" int emrf_build_lag_features(emrf_ctx_t* c, const int32_t* draws, int32_t n_draws, int32_t lag, int32_t ball,
+                                       double* features_hd, double* labels_hd) {
+  if (!c || !draws || !features_hd) return fail(EMRF_ERR_ARG, "NULL argument");
+  if (lag < 1 || n_draws <= lag || ball < 0 || ball > 6) return fail(EMRF_ERR_ARG, "need n_draws > lag >= 1 and ball in 0..6");
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const int64_t n_rows = n_draws - lag, F = 7 * (int64_t)lag;
+  DevBuf d_draws, d_X, d_y;
+  CU(d_draws.alloc((size_t)n_draws * 7 * 4));
+  CU(cudaMemcpyAsync(d_draws.p, draws, (size_t)n_draws * 7 * 4, cudaMemcpyHostToDevice, st));
+  const bool x_dev = is_device_ptr(features_hd), y_dev = labels_hd && is_device_ptr(labels_hd);
+  double* dX = features_hd;
+  double* dy = labels_hd;
+  if (!x_dev) { CU(d_X.alloc((size_t)n_rows * F * 8)); dX = d_X.as<double>(); }
+  if (labels_hd && !y_dev) { CU(d_y.alloc((size_t)n_rows * 8)); dy = d_y.as<double>(); }
+  kern::lag_features_kernel<<<(unsigned)((n_rows * F + 255) / 256), 256, 0, st>>>(d_draws.as<int32_t>(), n_draws, lag, ball, dX, dy);
+  CU(cudaGetLastError());
+  if (!x_dev) CU(cudaMemcpyAsync(features_hd, dX, (size_t)n_rows * F * 8, cudaMemcpyDeviceToHost, st));
+  if (labels_hd && !y_dev) CU(cudaMemcpyAsync(labels_hd, dy, (size_t)n_rows * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return EMRF_OK;
+}

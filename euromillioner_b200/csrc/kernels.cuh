@@ -1573,5 +1573,24 @@ __global__ void __launch_bounds__(kPredWarps * 32) predict_walk_kernel(const uin
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Draw-history feature builder (the step before the path; reference analogue: the row -> features
+// loop of Main.java:86-102, here with the lag window north_star describes).  draws[Dn][7] holds the
+// 5 mains and 2 stars of each draw; row t - lag of the output (t in [lag, Dn)) is
+// x[(l-1)*7 + q] = draws[t-l][q] for l = 1..lag, q = 0..6, label = draws[t][ball] - 1.
+// ---------------------------------------------------------------------------------------------
+__global__ void lag_features_kernel(const int32_t* __restrict__ draws, int n_draws, int lag, int ball,
+                                    double* __restrict__ X, double* __restrict__ y) {
+  const int F = 7 * lag;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t n_rows = n_draws - lag;
+  if (i >= n_rows * F) return;
+  const int row = (int)(i / F), f = (int)(i - (int64_t)row * F);
+  const int l = f / 7 + 1, q = f - (l - 1) * 7;
+  const int t = row + lag;
+  X[i] = (double)draws[(size_t)(t - l) * 7 + q];
+  if (f == 0 && y) y[row] = (double)(draws[(size_t)t * 7 + ball] - 1);
+}
+
 }  // namespace kern
 }  // namespace emrf

@@ -110,3 +110,14 @@ def update_partition(bins_cm, entries, seg_off, split_feature, split_bin, ctx=No
     check(_lib.lib().emrf_update_partition(ctx.h, _ptr(bins_cm), N, F, _ptr(entries), _ptr(seg_off), len(sf), _ptr(sf),
                                            _ptr(sb), _ptr(out), _ptr(n_left)))
     return out, n_left
+
+
+def build_lag_features(draws, lag=10, ball=0, ctx=None):
+    """Draw table (n_draws x 7) -> (X: N x 7*lag float64, y: N float64) built on the device."""
+    ctx = ctx or default_context()
+    draws = np.ascontiguousarray(draws, np.int32)
+    n = draws.shape[0] - lag
+    X = np.zeros((n, 7 * lag))
+    y = np.zeros(n)
+    check(_lib.lib().emrf_build_lag_features(ctx.h, _ptr(draws), draws.shape[0], lag, ball, _ptr(X), _ptr(y)))
+    return X, y

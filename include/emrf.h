@@ -190,6 +190,13 @@ int emrf_update_partition(emrf_ctx_t* ctx, const uint8_t* bins_cm, int64_t n_row
                           const int32_t* split_feature, const int32_t* split_bin, uint64_t* entries_out,
                           int64_t* n_left_out);
 
+/* Draw-history feature builder (reference analogue: the row -> features loop of
+ * Main.java:86-102).  draws: n_draws x 7 int32 (5 mains, 2 stars).  Output rows t = lag..n_draws-1:
+ * features_hd[(t-lag)*7*lag + (l-1)*7 + q] = draws[t-l][q], labels_hd[t-lag] = draws[t][ball] - 1
+ * (labels_hd may be NULL).  Outputs may be host or device buffers. */
+int emrf_build_lag_features(emrf_ctx_t* ctx, const int32_t* draws, int32_t n_draws, int32_t lag, int32_t ball,
+                            double* features_hd, double* labels_hd);
+
 /* Partition update for callers that cannot allocate device memory (a process whose GPU memory is
  * wholly owned by a pool allocator, or a loop that must avoid cudaMalloc's device-wide sync).
  * No counterpart in the reference or in Spark: same computation as emrf_update_partition, but

@@ -161,3 +161,12 @@ def test_update_partition_is_stable_and_exact(ctx, sizes):
         left = bins_cm[sf[g], (e & np.uint64(0xFFFFFFFF)).astype(np.int64)] <= sb[g]
         assert n_left[g] == left.sum()
         assert np.array_equal(out[seg[g]:seg[g + 1]], np.concatenate([e[left], e[~left]]))
+
+
+@pytest.mark.parametrize("ball,lag", [(0, 10), (6, 10), (3, 1), (2, 25)])
+def test_lag_feature_builder_matches_host_construction(ctx, ball, lag):
+    """the draw-history feature builder (reference analogue Main.java:86-102)."""
+    d = synth.draws(400)
+    X, y = stages.build_lag_features(d, lag, ball, ctx)
+    Xw, yw, _ = synth.draw_history(400, lag, ball)
+    assert np.array_equal(X, Xw) and np.array_equal(y, yw)

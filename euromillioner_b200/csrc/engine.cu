@@ -219,6 +219,7 @@ struct emrf_ctx {
   DevBuf p_w, p_X, p_y, p_labels, p_rm, p_cm, p_ent0, p_ent1, p_counts;
   // row-sharded push mode: this rank's staging buffer and the peers' buffers mapped through CUDA IPC
   DevBuf p_stage, p_ipc;
+  DevBuf p_segtab;   // device segment table (kern::Seg per node slot)
   void* peer_stage[8] = {nullptr};
   size_t peer_bytes = 0;
   bool peer_ok = false;
@@ -754,9 +755,8 @@ struct HNode {
   int32_t pred = 0;   // first index of the largest class count (from the scan kernel)
   int32_t feature = -1, split_bin = -1;
   double threshold = 0.0, gain = std::numeric_limits<double>::quiet_NaN(), impurity = 0.0;
-  uint64_t seg_start = 0;
-  uint32_t seg_len = 0;
-  uint32_t buf = 0;
+  uint32_t slot = 0;   // index of the node's entry segment in the device segment table
+  uint32_t ub = 0;     // upper bound on the segment's length (exact for roots and when rows are sharded)
   // class counts = cnt_a[c] - (cnt_b ? cnt_b[c] : 0); both point into the fit's result arena (the
   // split records copied back from the device): a left child shares its parent's "left" array, a
   // right child is parent total minus parent left, a node that went through a group owns its totals.
@@ -1005,10 +1005,21 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     trees[t].pool.reserve(256);
     trees[t].pool.emplace_back();
     HNode& r = trees[t].pool[0];
-    r.seg_start = tree_base[t];
-    r.seg_len = (uint32_t)tree_total[t];
-    r.buf = 0;
+    r.slot = (uint32_t)t;
+    r.ub = (uint32_t)tree_total[t];
   }
+  // device segment table: roots now, children written by the partition kernels
+  size_t seg_cap = std::max<size_t>((size_t)1 << 18, (size_t)4 * T);
+  uint32_t next_slot = (uint32_t)T;
+  CU(c->p_segtab.ensure(seg_cap * sizeof(kern::Seg)));
+  seg_cap = c->p_segtab.bytes / sizeof(kern::Seg);
+  {
+    std::vector<kern::Seg> roots(T);
+    for (int t = 0; t < T; t++) { roots[t].start = tree_base[t]; roots[t].len = (uint32_t)tree_total[t]; roots[t].buf = 0; }
+    CU(cudaMemcpyAsync(c->p_segtab.p, roots.data(), (size_t)T * sizeof(kern::Seg), cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  std::vector<uint32_t> hist_slots;   // slot of every node this rank built a histogram for (exact stats at the end)
   std::vector<std::pair<int, int>> stack;
   stack.reserve(1024);
   for (int t = 0; t < T; t++) stack.emplace_back(t, 0);
@@ -1142,7 +1153,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     // ---- tiles (tree-sharded multi-GPU: own trees only)
     uint64_t total_entries = 0;
     for (auto& g : group)
-      if (mine(g.tree)) total_entries += trees[g.tree].pool[g.pool].seg_len;
+      if (mine(g.tree)) total_entries += trees[g.tree].pool[g.pool].ub;   // upper bound
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
 
@@ -1153,12 +1164,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     for (int i = 0; i < n_nodes; i++) {
       const HNode& hn = trees[group[i].tree].pool[group[i].pool];
       kern::GroupNode& d = gn[i];
-      d.seg_start = hn.seg_start;
-      d.seg_len = hn.seg_len;
-      d.buf = hn.buf;
-      d.pad = 0;
+      d.seg_start = 0;
+      d.seg_len = 0;
+      d.buf = 0;
+      d.seg_slot = hn.slot;
       d.tile_begin = n_tiles;
-      d.n_tiles = mine(group[i].tree) ? std::max<uint32_t>(1, (hn.seg_len + tile_len - 1) / tile_len) : 0;
+      d.n_tiles = mine(group[i].tree) ? std::max<uint32_t>(1, (hn.ub + tile_len - 1) / tile_len) : 0;
+      if (d.n_tiles) hist_slots.push_back(hn.slot);
       // row-sharded without push mode: every histogram goes to HBM for the reduce-scatter
       d.slot = ((row_sharded && !push_mode) || d.n_tiles > 1) ? n_slots++ : -1;
       n_tiles += d.n_tiles;
@@ -1197,6 +1209,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     kern::HistArgs A;
     A.ent0 = d_ent[0]->as<uint64_t>();
     A.ent1 = d_ent[1]->as<uint64_t>();
+    A.segtab = c->p_segtab.as<kern::Seg>();
     A.bins_rm = d_rm.as<uint8_t>();
     A.nodes = (const kern::GroupNode*)c->d_group.p;
     A.node_feat = (const int32_t*)((char*)c->d_group.p + off_feat);
@@ -1262,8 +1275,6 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     }
     CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    tm.hist_units += (int64_t)total_entries;
-    tm.hist_alg_bytes += (int64_t)total_entries * (f_sub + 6);
     for (auto& g : group)
       if (mine(g.tree)) tm.hist_alg_bytes += (int64_t)slot_words * 4;
     tm.total_nodes_split += n_nodes;
@@ -1280,6 +1291,15 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     for (size_t q = 0; q < cur->trees_seen.size(); q++) tree_slot[cur->trees_seen[q]] = (int)q;
     const std::vector<int> order = hl::group_tree_visit_order(cur->trees_seen);
     std::vector<uint32_t> rightc(C);
+    if ((size_t)next_slot + 2 * (size_t)n_nodes > seg_cap) {   // grow the segment table (nothing is in flight here)
+      DevBuf bigger;
+      CU(bigger.alloc(std::max(seg_cap * 2, (size_t)next_slot + 2 * (size_t)n_nodes) * sizeof(kern::Seg)));
+      CU(cudaMemcpyAsync(bigger.p, c->p_segtab.p, (size_t)next_slot * sizeof(kern::Seg), cudaMemcpyDeviceToDevice, st));
+      CU(cudaStreamSynchronize(st));
+      std::swap(bigger.p, c->p_segtab.p);
+      std::swap(bigger.bytes, c->p_segtab.bytes);
+      seg_cap = c->p_segtab.bytes / sizeof(kern::Seg);
+    }
     for (int t : order) {
       for (int gi : cur->nodes_for_tree[tree_slot[t]]) {
         const GroupEntry& g = group[gi];
@@ -1335,13 +1355,19 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           l.id = 2 * id; l.is_leaf = l_leaf; l.impurity = limp; l.cnt_a = leftc; l.pred = res[rec].left_pred;
           r.id = 2 * id + 1; r.is_leaf = r_leaf; r.impurity = rimp; r.cnt_a = totc; r.cnt_b = leftc; r.pred = res[rec].right_pred;
           HNode& n = tr.pool[g.pool];
+          // a segment cannot hold more entries than its parent's, nor more than the node's total weight
+          // (every entry weighs >= 1): good enough to tile the next launches without reading sizes back
+          l.slot = next_slot++; r.slot = next_slot++;
+          l.ub = std::min(n.ub, res[rec].left_weight);
+          r.ub = std::min(n.ub, res[rec].total_weight - res[rec].left_weight);
           n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
           n.left = li; n.right = li + 1;
           if (!l_leaf) stack.emplace_back(t, li);
           if (!r_leaf) stack.emplace_back(t, li + 1);
           if ((!l_leaf || !r_leaf) && mine(t)) {
             kern::SplitNode sn;
-            sn.seg_start = n.seg_start; sn.seg_len = n.seg_len; sn.buf = n.buf;
+            sn.seg_start = 0; sn.seg_len = n.ub; sn.buf = 0;   // real segment: segment table [seg_slot]
+            sn.seg_slot = n.slot; sn.left_slot = l.slot; sn.right_slot = r.slot; sn.pad = 0;
             sn.feature = feat; sn.split_bin = sbin; sn.tile_begin = 0; sn.n_tiles = 0;
             splits.push_back(sn);
             split_ref.push_back({t, g.pool});
@@ -1381,21 +1407,24 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       uint64_t* d_nleft = (uint64_t*)((char*)c->d_part.p + off_nleft);
       cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
       CU(cudaEventRecord(p0, st));
+      if (!ptiles) CU(cudaMemsetAsync(d_tile_left, 0, 16, st));
+      if (!ptiles) kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>());   // empty segments: children = empty
       if (ptiles) {
         kern::part_count_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                      d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left);
-        kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft);
+                                                                      d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left,
+                                                                      c->p_segtab.as<kern::Seg>());
+        kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>());
         kern::part_scatter_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
                                                                         d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                        d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft);
+                                                                        d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft,
+                                                                        c->p_segtab.as<kern::Seg>());
         tm.kernel_launches += 3;
-      } else {
-        CU(cudaMemsetAsync(d_nleft, 0, (size_t)ns * 8, st));
       }
       CU(cudaEventRecord(p1, st));
       part_ev.emplace_back(p0, p1);
       CU(cudaGetLastError());
-      CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
+      // rows sharded: the weight bound is global (world times too loose), so read the exact sizes back
+      if (row_sharded) CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
     } else {
       const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_;
     }
@@ -1406,23 +1435,31 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
     }
     TRY(select_rc);
-    if (ns) {
+    if (ns && row_sharded) {
       CU(cudaStreamSynchronize(st));
       t_host0 = now_ms();
       const uint64_t* nl = (const uint64_t*)c->h_part.p;
       for (int i = 0; i < ns; i++) {
         HTree& tr = trees[split_ref[i].tree];
         const HNode& n = tr.pool[split_ref[i].pool];
-        HNode& l = tr.pool[n.left];
-        HNode& r = tr.pool[n.right];
-        l.seg_start = n.seg_start; l.seg_len = (uint32_t)nl[i]; l.buf = n.buf ^ 1u;
-        r.seg_start = n.seg_start + nl[i]; r.seg_len = n.seg_len - (uint32_t)nl[i]; r.buf = n.buf ^ 1u;
+        tr.pool[n.left].ub = (uint32_t)nl[i];
+        tr.pool[n.right].ub = n.ub - (uint32_t)nl[i];
       }
       { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
     }
     std::swap(cur, nxt);
   }
 
+  // ---- exact entry counts of every histogram built (the roofline's algorithmic bytes), from the table
+  {
+    std::vector<kern::Seg> segs(next_slot);
+    CU(cudaMemcpyAsync(segs.data(), c->p_segtab.p, (size_t)next_slot * sizeof(kern::Seg), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    int64_t units = 0;
+    for (uint32_t sl : hist_slots) units += segs[sl].len;
+    tm.hist_units = units;
+    tm.hist_alg_bytes += units * (int64_t)(f_sub + 6);
+  }
   // ---- topNodes.map(_.toNode(prune = true))
   double t_host0 = now_ms();
   export_forest(trees, C, *fo, c->host_threads);
@@ -1861,7 +1898,7 @@ extern "C" int emrf_histogram(emrf_ctx_t* c, const uint8_t* bins_rm, int64_t N, 
     kern::GroupNode& d = gn[i];
     d.seg_start = (uint64_t)node_seg_off[i];
     d.seg_len = (uint32_t)(node_seg_off[i + 1] - node_seg_off[i]);
-    d.buf = 0; d.pad = 0; d.slot = i;
+    d.buf = 0; d.seg_slot = 0; d.slot = i;
     d.tile_begin = (uint32_t)tn.size();
     d.n_tiles = std::max<uint32_t>(1, (d.seg_len + tile_len - 1) / tile_len);
     for (uint32_t q = 0; q < d.n_tiles; q++) tn.push_back((uint32_t)i);
@@ -1976,6 +2013,7 @@ extern "C" int emrf_update_partition(emrf_ctx_t* c, const uint8_t* bins_cm, int6
     s.seg_start = (uint64_t)node_seg_off[i];
     s.seg_len = (uint32_t)(node_seg_off[i + 1] - node_seg_off[i]);
     s.buf = 0; s.feature = split_feature[i]; s.split_bin = split_bin[i];
+    s.seg_slot = 0; s.left_slot = 0; s.right_slot = 0; s.pad = 0;
     if (s.feature < 0 || s.feature >= F) return fail(EMRF_ERR_ARG, "split feature out of range");
     s.tile_begin = (uint32_t)tn.size();
     s.n_tiles = (s.seg_len + kern::kPartTile - 1) / kern::kPartTile;
@@ -1991,11 +2029,11 @@ extern "C" int emrf_update_partition(emrf_ctx_t* c, const uint8_t* bins_cm, int6
   if (!tn.empty()) {
     kern::part_count_kernel<<<(unsigned)tn.size(), kern::kPartThreads, 0, st>>>(d_in.as<uint64_t>(), d_in.as<uint64_t>(),
                                                                               d_cm.as<uint8_t>(), Np, d_nodes.as<kern::SplitNode>(),
-                                                                              d_tiles.as<uint32_t>(), d_tl.as<uint32_t>());
-    kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(d_nodes.as<kern::SplitNode>(), d_tl.as<uint32_t>(), d_nl.as<uint64_t>());
+                                                                              d_tiles.as<uint32_t>(), d_tl.as<uint32_t>(), nullptr);
+    kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(d_nodes.as<kern::SplitNode>(), d_tl.as<uint32_t>(), d_nl.as<uint64_t>(), nullptr);
     kern::part_scatter_kernel<<<(unsigned)tn.size(), kern::kPartThreads, 0, st>>>(
         d_in.as<uint64_t>(), d_in.as<uint64_t>(), d_out.as<uint64_t>(), d_out.as<uint64_t>(), d_cm.as<uint8_t>(), Np,
-        d_nodes.as<kern::SplitNode>(), d_tiles.as<uint32_t>(), d_tl.as<uint32_t>(), d_nl.as<uint64_t>());
+        d_nodes.as<kern::SplitNode>(), d_tiles.as<uint32_t>(), d_tl.as<uint32_t>(), d_nl.as<uint64_t>(), nullptr);
   }
   CU(cudaGetLastError());
   std::vector<uint64_t> nl(n_nodes);
@@ -2089,6 +2127,7 @@ extern "C" int emrf_update_partition_noalloc(emrf_ctx_t* c, const uint8_t* bins_
     s.buf = 0;
     s.feature = split_feature[i];
     s.split_bin = split_bin[i];
+    s.seg_slot = 0; s.left_slot = 0; s.right_slot = 0; s.pad = 0;
     s.tile_begin = (uint32_t)n_tiles;
     s.n_tiles = (uint32_t)((len + kern::kPartTile - 1) / kern::kPartTile);
     n_tiles += s.n_tiles;
@@ -2122,11 +2161,11 @@ extern "C" int emrf_update_partition_noalloc(emrf_ctx_t* c, const uint8_t* bins_
     // part_count writes tile_left[0..n_tiles), part_scan turns it into offsets and writes n_left for
     // every node, part_scatter reads both: no word of the scratch is read before this call wrote it.
     kern::part_count_kernel<<<(unsigned)n_tiles, kern::kPartThreads, 0, st>>>(entries_dev, entries_dev, bins_cm_dev, col_stride,
-                                                                          d_nodes, d_tile_node, d_tile_left);
-    kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(d_nodes, d_tile_left, n_left_dev);
+                                                                          d_nodes, d_tile_node, d_tile_left, nullptr);
+    kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(d_nodes, d_tile_left, n_left_dev, nullptr);
     kern::part_scatter_kernel<<<(unsigned)n_tiles, kern::kPartThreads, 0, st>>>(entries_dev, entries_dev, entries_out_dev,
                                                                             entries_out_dev, bins_cm_dev, col_stride, d_nodes,
-                                                                            d_tile_node, d_tile_left, n_left_dev);
+                                                                            d_tile_node, d_tile_left, n_left_dev, nullptr);
     CU(cudaGetLastError());
   } else {
     CU(cudaMemsetAsync(n_left_dev, 0, (size_t)n_nodes * 8, st));  // every segment is empty

@@ -588,14 +588,23 @@ __global__ void list_fill_kernel(const uint8_t* __restrict__ w, const uint8_t* _
 //     the last tile to finish (threadfence + ticket) reloads the slot and scans it.
 // No CTA waits on another, so any launch order is safe.
 // ---------------------------------------------------------------------------------------------
+// A node's entry segment as the device knows it.  During a fit the segments live in a device table
+// indexed by node slot: the partition kernels write the children's segments there and the next
+// histogram launch reads them, so the host never has to wait for the children's sizes (it tiles
+// with an upper bound: a node cannot hold more entries than its total weight).
+struct Seg {
+  uint64_t start;   // first entry of the segment in entries[buf]
+  uint32_t len;
+  uint32_t buf;     // which entries buffer holds the segment
+};
 struct GroupNode {
-  uint64_t seg_start;   // first entry of the node's segment in entries[buf]
+  uint64_t seg_start;   // used when HistArgs.segtab == nullptr (stage entry points)
   uint32_t seg_len;
   uint32_t tile_begin;  // index of the node's first tile in the group
-  uint32_t n_tiles;
+  uint32_t n_tiles;     // provisioned tiles (from the upper bound); tiles past the real end are empty
   int32_t slot;         // global histogram slot, -1 = single tile (shared memory only)
-  uint32_t buf;         // which entries buffer holds the segment
-  uint32_t pad;
+  uint32_t buf;
+  uint32_t seg_slot;    // index into HistArgs.segtab
 };
 struct ScanResult {
   double gain;
@@ -608,10 +617,13 @@ struct ScanResult {
   int32_t pred;        // ImpurityCalculator.predict = first index of the largest class count: node,
   int32_t left_pred;   //   left child,
   int32_t right_pred;  //   right child (so the host never has to scan class counts)
+  uint32_t total_weight;  // sum of the node's class counts,
+  uint32_t left_weight;   //   of the left child's (upper bounds on the children's entry counts)
 };
 struct HistArgs {
   const uint64_t* ent0;
   const uint64_t* ent1;
+  const Seg* segtab;           // device segment table (nullptr: segments come inside GroupNode)
   const uint8_t* bins_rm;
   const GroupNode* nodes;
   const uint32_t* tile_node;   // tile → node index
@@ -771,6 +783,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
   // (c) one candidate (feature, split) per thread, Spark's operation order
   double best_gain = -INFINITY;  // below Double.MinValue: "no candidate"
   double best_li = 0.0, best_ri = 0.0;
+  uint32_t best_lc = 0;
   int best_idx = 0x7fffffff;
   const int n_cand = kc * (B - 1);
   for (int cand = tid; cand < n_cand; cand += NT) {
@@ -808,7 +821,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
       gain = __dsub_rn(__dsub_rn(pimp, __dmul_rn(lw, li)), __dmul_rn(rw, ri));
       if (gain < min_info_gain) gain = kInvalidGain;
     }
-    if (gain > best_gain) { best_gain = gain; best_idx = cand; best_li = li; best_ri = ri; }  // first max
+    if (gain > best_gain) { best_gain = gain; best_idx = cand; best_li = li; best_ri = ri; best_lc = lc; }  // first max
   }
   // (d) block arg-max: greatest gain, ties → smallest candidate index (= Spark's first maximum
   // in (subset order, split order))
@@ -838,6 +851,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
     if (tid == 0) {
       res->gain = kInvalidGain; res->impurity = pimp; res->left_impurity = 0.0; res->right_impurity = 0.0;
       res->k = -1; res->split = 0; res->valid = 0; res->left_pred = 0; res->right_pred = 0;
+      res->total_weight = tot_all; res->left_weight = 0;
     }
     if (tid < 32) {
       const int p = warp_first_argmax(C, tid, [&](int c) { return S.tot[c]; });
@@ -846,7 +860,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
     for (int c = tid; c < C; c += NT) { left_out[c] = 0; total_out[c] = S.tot[c]; }
   } else {
     const int k = ix / (B - 1), s = ix - k * (B - 1);
-    if (tid == 0) { res->gain = g; res->impurity = pimp; res->k = k0 + k; res->split = s; res->valid = (g != kInvalidGain); }
+    if (tid == 0) { res->gain = g; res->impurity = pimp; res->k = k0 + k; res->split = s; res->valid = (g != kInvalidGain); res->total_weight = tot_all; }
     if (tid < 96) {   // three warps: predictions of the node, its left and its right child
       const uint32_t* lw = sh + ((size_t)k * B + s) * C;
       const int which = tid >> 5, ln = tid & 31;
@@ -855,7 +869,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
                                : warp_first_argmax(C, ln, [&](int c) { return S.tot[c] - lw[c]; });
       if (ln == 0) { if (which == 0) res->pred = p; else if (which == 1) res->left_pred = p; else res->right_pred = p; }
     }
-    if (my_idx == ix) { res->left_impurity = best_li; res->right_impurity = best_ri; }  // the owner of the winner
+    if (my_idx == ix) { res->left_impurity = best_li; res->right_impurity = best_ri; res->left_weight = best_lc; }  // the owner of the winner
     const uint32_t* l = sh + ((size_t)k * B + s) * C;
     for (int c = tid; c < C; c += NT) { left_out[c] = l[c]; total_out[c] = S.tot[c]; }
   }
@@ -916,7 +930,11 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
   __shared__ int sh_last;
 
   const uint32_t g = A.tile_node[blockIdx.x];
-  const GroupNode nd = A.nodes[g];
+  GroupNode nd = A.nodes[g];
+  if (A.segtab) {
+    const Seg sg = A.segtab[nd.seg_slot];
+    nd.seg_start = sg.start; nd.seg_len = sg.len; nd.buf = sg.buf;
+  }
   const uint32_t tile_in_node = blockIdx.x - nd.tile_begin;
   for (int k = tid; k < kc; k += kHistThreads) {
     const int f = A.node_feat[(size_t)g * A.f_sub + k0 + k];
@@ -928,7 +946,8 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
 
   // ---- accumulate this tile
   const uint64_t* ent = (nd.buf ? A.ent1 : A.ent0) + nd.seg_start + (uint64_t)tile_in_node * A.tile_len;
-  const uint32_t len = min(A.tile_len, nd.seg_len - tile_in_node * A.tile_len);
+  const uint64_t tile_first = (uint64_t)tile_in_node * A.tile_len;
+  const uint32_t len = tile_first < nd.seg_len ? (uint32_t)min((uint64_t)A.tile_len, nd.seg_len - tile_first) : 0u;
   const uint8_t* bins = A.bins_rm;
   const int Fp = A.Fp;
   if (CH == 0) {
@@ -1095,14 +1114,26 @@ __global__ void __launch_bounds__(kHistThreads) scan_sum_kernel(const uint32_t* 
 //   part_scatter_kernel : ranks inside the tile by ballot/prefix, then scatter
 // ---------------------------------------------------------------------------------------------
 struct SplitNode {
-  uint64_t seg_start;
+  uint64_t seg_start;  // used when no segment table is passed (stage entry points)
   uint32_t seg_len;
   uint32_t tile_begin;
-  uint32_t n_tiles;
+  uint32_t n_tiles;    // provisioned tiles; tiles past the real end are empty
   uint32_t buf;        // source buffer; destination is the other one
   int32_t feature;
   int32_t split_bin;
+  uint32_t seg_slot;   // parent's slot in the segment table
+  uint32_t left_slot;  // where part_scan_kernel writes the children's segments
+  uint32_t right_slot;
+  uint32_t pad;
 };
+__device__ __forceinline__ SplitNode load_split(const SplitNode* nodes, uint32_t g, const Seg* segtab) {
+  SplitNode nd = nodes[g];
+  if (segtab) {
+    const Seg sg = segtab[nd.seg_slot];
+    nd.seg_start = sg.start; nd.seg_len = sg.len; nd.buf = sg.buf;
+  }
+  return nd;
+}
 // Each warp owns a contiguous run of 256 entries of the tile: eight coalesced 8-byte loads and eight
 // column gathers are in flight per lane before anything is consumed.
 constexpr int kPartPerLane = kPartTile / kPartThreads;   // 8
@@ -1110,13 +1141,14 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(const uint64_t
                                                                   const uint8_t* __restrict__ bins_cm, int64_t Np,
                                                                   const SplitNode* __restrict__ nodes,
                                                                   const uint32_t* __restrict__ tile_node,
-                                                                  uint32_t* __restrict__ tile_left) {
+                                                                  uint32_t* __restrict__ tile_left,
+                                                                  const Seg* __restrict__ segtab) {
   __shared__ uint32_t sh_cnt[kPartThreads / 32];
   const uint32_t g = tile_node[blockIdx.x];
-  const SplitNode nd = nodes[g];
+  const SplitNode nd = load_split(nodes, g, segtab);
   const uint32_t t_in = blockIdx.x - nd.tile_begin;
   const uint64_t* ent = (nd.buf ? ent1 : ent0) + nd.seg_start + (uint64_t)t_in * kPartTile;
-  const uint32_t len = min((uint32_t)kPartTile, nd.seg_len - t_in * kPartTile);
+  const uint32_t len = (uint64_t)t_in * kPartTile < nd.seg_len ? min((uint32_t)kPartTile, nd.seg_len - t_in * kPartTile) : 0u;
   const uint8_t* col = bins_cm + (size_t)nd.feature * Np;
   const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
   const uint32_t wbase = wv * (32 * kPartPerLane);
@@ -1140,11 +1172,11 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(const uint64_t
   }
 }
 __global__ void __launch_bounds__(256) part_scan_kernel(const SplitNode* __restrict__ nodes, uint32_t* __restrict__ tile_left,
-                                                        uint64_t* __restrict__ n_left) {
+                                                        uint64_t* __restrict__ n_left, Seg* __restrict__ segtab) {
   // one CTA per node; sequential chunks of 256 tiles with a block scan
   __shared__ uint32_t sh[256];
   __shared__ uint32_t carry;
-  const SplitNode nd = nodes[blockIdx.x];
+  const SplitNode nd = load_split(nodes, blockIdx.x, segtab);
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
   for (uint32_t base = 0; base < nd.n_tiles; base += 256) {
@@ -1165,7 +1197,16 @@ __global__ void __launch_bounds__(256) part_scan_kernel(const SplitNode* __restr
     if (threadIdx.x == 255) carry = c0 + incl;
     __syncthreads();
   }
-  if (threadIdx.x == 0) n_left[blockIdx.x] = carry;
+  if (threadIdx.x == 0) {
+    n_left[blockIdx.x] = carry;
+    if (segtab) {   // children: [left ... | right ...] in the other buffer, same place
+      Seg l, r;
+      l.start = nd.seg_start; l.len = carry; l.buf = nd.buf ^ 1u;
+      r.start = nd.seg_start + carry; r.len = nd.seg_len - carry; r.buf = nd.buf ^ 1u;
+      segtab[nd.left_slot] = l;
+      segtab[nd.right_slot] = r;
+    }
+  }
 }
 __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64_t* ent0, const uint64_t* ent1,
                                                                     uint64_t* out0, uint64_t* out1,
@@ -1173,15 +1214,17 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64
                                                                     const SplitNode* __restrict__ nodes,
                                                                     const uint32_t* __restrict__ tile_node,
                                                                     const uint32_t* __restrict__ tile_left_off,
-                                                                    const uint64_t* __restrict__ n_left) {
+                                                                    const uint64_t* __restrict__ n_left,
+                                                                    const Seg* __restrict__ segtab) {
   __shared__ uint32_t sh_w[kPartThreads / 32];
   const uint32_t g = tile_node[blockIdx.x];
-  const SplitNode nd = nodes[g];
+  const SplitNode nd = load_split(nodes, g, segtab);
   const uint32_t t_in = blockIdx.x - nd.tile_begin;
   const uint64_t tile_start = (uint64_t)t_in * kPartTile;
   const uint64_t* ent = (nd.buf ? ent1 : ent0) + nd.seg_start + tile_start;
   uint64_t* dst = (nd.buf ? out0 : out1) + nd.seg_start;  // other buffer, same segment
-  const uint32_t len = min((uint32_t)kPartTile, nd.seg_len - (uint32_t)tile_start);
+  const uint32_t len = tile_start < nd.seg_len ? min((uint32_t)kPartTile, nd.seg_len - (uint32_t)tile_start) : 0u;
+  if (len == 0) return;   // provisioned from an upper bound: nothing here
   const uint8_t* col = bins_cm + (size_t)nd.feature * Np;
   const uint64_t left_base = tile_left_off[blockIdx.x];
   const uint64_t right_base = n_left[g] + (tile_start - left_base);

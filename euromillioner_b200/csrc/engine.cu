@@ -213,6 +213,9 @@ struct emrf_ctx {
   // grow-only scratch reused across groups
   DevBuf d_group, d_results, d_ghist, d_tickets, d_split, d_part;
   PinnedBuf h_group, h_split, h_part, h_seeds, h_table, h_tsum;
+  PinnedBuf h_split_p[2];
+  DevBuf d_split_p[2], d_part_p[2];
+  std::vector<kern::SplitNode> splits_tmp;
   DevBuf d_seeds, d_table, d_tsum;
   // fit-sized buffers kept between fits (grow-only): cudaMalloc/cudaFree of GB-sized buffers costs
   // milliseconds and cudaFree synchronises the device; they are released by emrf_ctx_destroy
@@ -1138,6 +1141,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
   }
   TRY(select_rc);
+  // Per group the histogram launch can be cut into `pieces` (node ranges; EMRF_PIECES=1): while the host turns
+  // the split records of piece p into tree nodes, children and partition work, the GPU is already computing
+  // piece p+1, and the partition kernels of piece p run under the host's work on piece p+1.  Multi-GPU modes
+  // exchange the whole group's records at once, so they always use one piece.
+  struct Decision { int32_t left_pool; bool l_leaf, r_leaf; };
+  std::vector<Decision> decisions;
   while (!cur->group.empty()) {
     double t_host0 = now_ms();
     std::vector<GroupEntry>& group = cur->group;
@@ -1150,10 +1159,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       for (int k = 0; k < f_sub; k++) fo->trace.push_back(group_feat[g.feat_at + k]);
     }
 
-    // ---- tiles (tree-sharded multi-GPU: own trees only)
+    // ---- tiles (tree-sharded multi-GPU: own trees only); sizes are upper bounds
     uint64_t total_entries = 0;
     for (auto& g : group)
-      if (mine(g.tree)) total_entries += trees[g.tree].pool[g.pool].ub;   // upper bound
+      if (mine(g.tree)) total_entries += trees[g.tree].pool[g.pool].ub;
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
 
@@ -1187,10 +1196,29 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       for (int i = 0; i < n_nodes; i++)
         for (uint32_t q = 0; q < gn[i].n_tiles; q++) tn[gn[i].tile_begin + q] = (uint32_t)i;
     }
+    // pieces: node ranges with about the same number of tiles
+    // measured (configs[1]): two pieces hide ≈ 2 ms of host work per fit but cost ≈ 2.3 ms of histogram-kernel
+    // time (two short launches fill the SMs worse than one), so one piece is the default
+    static const bool two_pieces = env_flag("EMRF_PIECES");
+    const int n_pieces = (two_pieces && c->world == 1 && n_nodes >= 64) ? 2 : 1;
+    int piece_n0[3] = {0, n_nodes, n_nodes};
+    if (n_pieces == 2) {
+      int cut = n_nodes / 2;
+      for (int i = 0; i < n_nodes; i++) if (gn[i].tile_begin >= n_tiles / 2) { cut = std::max(1, i); break; }
+      piece_n0[1] = std::min(cut, n_nodes - 1);
+    }
+    // per-piece record block: [ScanResult r][left r*C][total r*C]
+    size_t piece_off[3], piece_left[2], piece_total[2];
+    size_t res_bytes = 0;
+    for (int pz = 0; pz < n_pieces; pz++) {
+      const size_t r = (size_t)(piece_n0[pz + 1] - piece_n0[pz]) * n_chunks;
+      piece_off[pz] = res_bytes;
+      piece_left[pz] = align_up(sizeof(kern::ScanResult) * r, 16);
+      piece_total[pz] = piece_left[pz] + r * C * 4;
+      res_bytes += align_up(piece_total[pz] + r * C * 4, 256);
+    }
+    piece_off[n_pieces] = res_bytes;
     const size_t n_rec = (size_t)n_nodes * n_chunks;
-    const size_t off_left = align_up(sizeof(kern::ScanResult) * n_rec, 16);
-    const size_t off_total = off_left + n_rec * C * 4;
-    const size_t res_bytes = off_total + n_rec * C * 4;
     CU(c->d_results.ensure(res_bytes));
     char* h_res = (char*)c->arena_alloc(res_bytes);   // kept until the forest is exported
     if (!h_res) return fail(EMRF_ERR_CUDA, "out of pinned host memory for the split-record arena");
@@ -1217,9 +1245,6 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.num_bins_all = d_num_bins.as<int32_t>();
     A.ghist = c->d_ghist.as<uint32_t>();
     A.tickets = c->d_tickets.as<uint32_t>();
-    A.results = (kern::ScanResult*)c->d_results.p;
-    A.left_counts = (uint32_t*)((char*)c->d_results.p + off_left);
-    A.total_counts = (uint32_t*)((char*)c->d_results.p + off_total);
     A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
     A.tile_len = tile_len;
     A.tile_smem_off = (uint32_t)hist_bytes;
@@ -1227,71 +1252,79 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.push_world = push_mode ? c->world : 0; A.push_rank = c->rank; A.push_npr = nodes_per_rank;
     for (int r = 0; r < 8; r++) A.peer_stage[r] = (uint32_t*)c->peer_stage[r];
     A.min_info_gain = P.min_info_gain;
-    cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
-    CU(cudaEventRecord(e0, st));
-    if (n_tiles) {
-      CU(hist_launch(row_ch, dim3(n_tiles, n_chunks), hist_smem, st, A, false));
-      tm.kernel_launches++;
-      tm.hist_launches++;
-    }
-    CU(cudaEventRecord(e1, st));
-    hist_ev.emplace_back(e0, e1);
-    CU(cudaGetLastError());
-    if (row_sharded && push_mode) {
-      // every rank's partials must have landed in the owners' staging buffers: a 1-word all-reduce is the
-      // cross-rank barrier (in stream order it follows this rank's histogram kernel)
-      CU(cudaMemsetAsync(c->d_tickets.p, 0, 4, st));
-      TRY(nccl_allreduce_u32(c, c->d_tickets.as<uint32_t>(), 1));
-      const int first = c->rank * nodes_per_rank;
-      const int mine_n = std::max(0, std::min(nodes_per_rank, n_nodes - first));
-      if (mine_n > 0) {
-        kern::scan_sum_kernel<<<dim3(mine_n, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
-            c->p_stage.as<uint32_t>(), c->world, nodes_per_rank, first, A.node_feat, A.num_bins_all, f_sub, B, C, k_chunk,
-            n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain, A.results, A.left_counts, A.total_counts);
+    cudaEvent_t piece_done[2] = {nullptr, nullptr};
+    for (int pz = 0; pz < n_pieces; pz++) {
+      const int n0 = piece_n0[pz], n1 = piece_n0[pz + 1];
+      const uint32_t t0 = gn[n0].tile_begin, t1 = (n1 < n_nodes) ? gn[n1].tile_begin : n_tiles;
+      char* blk = (char*)c->d_results.p + piece_off[pz];
+      A.results = (kern::ScanResult*)blk;
+      A.left_counts = (uint32_t*)(blk + piece_left[pz]);
+      A.total_counts = (uint32_t*)(blk + piece_total[pz]);
+      A.tile_base = t0;
+      A.node_base = (uint32_t)n0;
+      cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
+      CU(cudaEventRecord(e0, st));
+      if (t1 > t0) {
+        CU(hist_launch(row_ch, dim3(t1 - t0, n_chunks), hist_smem, st, A, false));
         tm.kernel_launches++;
-        CU(cudaGetLastError());
+        tm.hist_launches++;
+      }
+      CU(cudaEventRecord(e1, st));
+      hist_ev.emplace_back(e0, e1);
+      CU(cudaGetLastError());
+      if (c->world == 1) {
+        CU(cudaMemcpyAsync(h_res + piece_off[pz], blk, piece_off[pz + 1] - piece_off[pz], cudaMemcpyDeviceToHost, st));
+        piece_done[pz] = c->events.get();
+        CU(cudaEventRecord(piece_done[pz], st));
+      }
+    }
+    if (c->world > 1) {   // single piece: block 0 holds every record
+      if (row_sharded && push_mode) {
+        // every rank's partials must have landed in the owners' staging buffers: a 1-word all-reduce is the
+        // cross-rank barrier (in stream order it follows this rank's histogram kernel)
+        CU(cudaMemsetAsync(c->d_tickets.p, 0, 4, st));
+        TRY(nccl_allreduce_u32(c, c->d_tickets.as<uint32_t>(), 1));
+        const int first = c->rank * nodes_per_rank;
+        const int mine_n = std::max(0, std::min(nodes_per_rank, n_nodes - first));
+        if (mine_n > 0) {
+          kern::scan_sum_kernel<<<dim3(mine_n, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
+              c->p_stage.as<uint32_t>(), c->world, nodes_per_rank, first, A.node_feat, A.num_bins_all, f_sub, B, C, k_chunk,
+              n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain, A.results, A.left_counts, A.total_counts);
+          tm.kernel_launches++;
+          CU(cudaGetLastError());
+        }
+      } else if (row_sharded) {
+        // reduceByKey(_.merge(_)) of Spark's per-partition aggregators, keyed by node exactly as Spark
+        // does it: a reduce-scatter leaves each rank with the summed histograms (exact integers) of ITS
+        // share of the group's nodes, it scans those, and the small split records are combined with an
+        // all-reduce over zero-filled slots (as in the tree-sharded mode).
+        TRY(nccl_reduce_scatter_u32(c, c->d_ghist.as<uint32_t>(), (size_t)nodes_per_rank * slot_words));
+        const int first = c->rank * nodes_per_rank;
+        const int mine_n = std::max(0, std::min(nodes_per_rank, n_nodes - first));
+        if (mine_n > 0) {
+          kern::scan_kernel<<<dim3(mine_n, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
+              c->d_ghist.as<uint32_t>() + (size_t)first * slot_words, A.node_feat + (size_t)first * f_sub, A.num_bins_all, f_sub,
+              B, C, k_chunk, n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain,
+              A.results + (size_t)first * n_chunks, A.left_counts + (size_t)first * n_chunks * C,
+              A.total_counts + (size_t)first * n_chunks * C);
+          tm.kernel_launches++;
+          CU(cudaGetLastError());
+        }
       }
       TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
-    } else if (row_sharded) {
-      // reduceByKey(_.merge(_)) of Spark's per-partition aggregators, keyed by node exactly as Spark
-      // does it: a reduce-scatter leaves each rank with the summed histograms (exact integers) of ITS
-      // share of the group's nodes, it scans those, and the small split records are combined with an
-      // all-reduce over zero-filled slots (as in the tree-sharded mode).
-      TRY(nccl_reduce_scatter_u32(c, c->d_ghist.as<uint32_t>(), (size_t)nodes_per_rank * slot_words));
-      const int first = c->rank * nodes_per_rank;
-      const int mine_n = std::max(0, std::min(nodes_per_rank, n_nodes - first));
-      if (mine_n > 0) {
-        kern::scan_kernel<<<dim3(mine_n, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
-            c->d_ghist.as<uint32_t>() + (size_t)first * slot_words, A.node_feat + (size_t)first * f_sub, A.num_bins_all, f_sub,
-            B, C, k_chunk, n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain,
-            A.results + (size_t)first * n_chunks, A.left_counts + (size_t)first * n_chunks * C,
-            A.total_counts + (size_t)first * n_chunks * C);
-        tm.kernel_launches++;
-        CU(cudaGetLastError());
-      }
-      TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
-    } else if (c->world > 1) {
-      TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
+      CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, st));
+      piece_done[0] = c->events.get();
+      CU(cudaEventRecord(piece_done[0], st));
     }
-    CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
     for (auto& g : group)
       if (mine(g.tree)) tm.hist_alg_bytes += (int64_t)slot_words * 4;
     tm.total_nodes_split += n_nodes;
 
-    // ---- driver side of findBestSplits: node updates in Scala map iteration order.  Class counts
-    // are not copied: nodes point into the arena records.
-    t_host0 = now_ms();
-    const kern::ScanResult* res = (const kern::ScanResult*)h_res;
-    const uint32_t* res_left = (const uint32_t*)(h_res + off_left);
-    const uint32_t* res_total = (const uint32_t*)(h_res + off_total);
-    std::vector<kern::SplitNode> splits;
-    struct SplitRef { int tree, pool; };
-    std::vector<SplitRef> split_ref;
-    for (size_t q = 0; q < cur->trees_seen.size(); q++) tree_slot[cur->trees_seen[q]] = (int)q;
-    const std::vector<int> order = hl::group_tree_visit_order(cur->trees_seen);
-    std::vector<uint32_t> rightc(C);
-    if ((size_t)next_slot + 2 * (size_t)n_nodes > seg_cap) {   // grow the segment table (nothing is in flight here)
+    // ---- driver side of findBestSplits, piece by piece: records → node stats, children, partition work.
+    // Class counts are not copied: nodes point into the arena records.
+    decisions.assign(n_nodes, Decision{-1, true, true});
+    if ((size_t)next_slot + 2 * (size_t)n_nodes > seg_cap) {   // grow the segment table
+      CU(cudaStreamSynchronize(st));
       DevBuf bigger;
       CU(bigger.alloc(std::max(seg_cap * 2, (size_t)next_slot + 2 * (size_t)n_nodes) * sizeof(kern::Seg)));
       CU(cudaMemcpyAsync(bigger.p, c->p_segtab.p, (size_t)next_slot * sizeof(kern::Seg), cudaMemcpyDeviceToDevice, st));
@@ -1300,18 +1333,33 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       std::swap(bigger.bytes, c->p_segtab.bytes);
       seg_cap = c->p_segtab.bytes / sizeof(kern::Seg);
     }
-    for (int t : order) {
-      for (int gi : cur->nodes_for_tree[tree_slot[t]]) {
+    struct SplitRef { int tree, pool; };
+    std::vector<SplitRef> split_ref_all;
+    int ns_total = 0;
+    for (int pz = 0; pz < n_pieces; pz++) {
+      CU(cudaEventSynchronize(piece_done[pz]));
+      t_host0 = now_ms();
+      const int n0 = piece_n0[pz], n1 = piece_n0[pz + 1];
+      const char* blk = h_res + piece_off[pz];
+      const kern::ScanResult* res = (const kern::ScanResult*)blk;
+      const uint32_t* res_left = (const uint32_t*)(blk + piece_left[pz]);
+      const uint32_t* res_total = (const uint32_t*)(blk + piece_total[pz]);
+      std::vector<kern::SplitNode>& splits = c->splits_tmp;
+      splits.clear();
+      std::vector<uint32_t> rightc(C);
+      for (int gi = n0; gi < n1; gi++) {
         const GroupEntry& g = group[gi];
+        const int t = g.tree;
         HTree& tr = trees[t];
         // combine feature chunks: first maximum in subset order
+        const size_t r0 = (size_t)(gi - n0) * n_chunks;
         int best = -1;
         for (int ch = 0; ch < n_chunks; ch++) {
-          const kern::ScanResult& r = res[(size_t)gi * n_chunks + ch];
+          const kern::ScanResult& r = res[r0 + ch];
           if (r.k < 0) continue;
-          if (best < 0 || r.gain > res[(size_t)gi * n_chunks + best].gain) best = ch;
+          if (best < 0 || r.gain > res[r0 + best].gain) best = ch;
         }
-        const size_t rec = (size_t)gi * n_chunks + (best < 0 ? 0 : best);
+        const size_t rec = r0 + (best < 0 ? 0 : best);
         const uint32_t* totc = res_total + rec * C;
         const uint32_t* leftc = res_left + rec * C;
         const int id = tr.pool[g.pool].id;
@@ -1362,86 +1410,106 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           r.ub = std::min(n.ub, res[rec].total_weight - res[rec].left_weight);
           n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
           n.left = li; n.right = li + 1;
-          if (!l_leaf) stack.emplace_back(t, li);
-          if (!r_leaf) stack.emplace_back(t, li + 1);
+          decisions[gi] = Decision{li, l_leaf, r_leaf};
           if ((!l_leaf || !r_leaf) && mine(t)) {
             kern::SplitNode sn;
             sn.seg_start = 0; sn.seg_len = n.ub; sn.buf = 0;   // real segment: segment table [seg_slot]
             sn.seg_slot = n.slot; sn.left_slot = l.slot; sn.right_slot = r.slot; sn.pad = 0;
             sn.feature = feat; sn.split_bin = sbin; sn.tile_begin = 0; sn.n_tiles = 0;
             splits.push_back(sn);
-            split_ref.push_back({t, g.pool});
+            split_ref_all.push_back({t, g.pool});
           }
         }
       }
-    }
-    for (int t : cur->trees_seen) tree_slot[t] = -1;
-
-    // ---- K4: partition the split nodes' segments (asynchronously) ...
-    const int ns = (int)splits.size();
-    if (ns) {
-      uint32_t ptiles = 0;
-      for (auto& sn : splits) {
-        sn.tile_begin = ptiles;
-        sn.n_tiles = (sn.seg_len + kern::kPartTile - 1) / kern::kPartTile;
-        ptiles += sn.n_tiles;
-      }
-      const size_t off_ptn = align_up(sizeof(kern::SplitNode) * (size_t)ns, 16);
-      const size_t split_bytes = off_ptn + (size_t)ptiles * 4;
-      CU(c->h_split.ensure(split_bytes));
-      CU(c->d_split.ensure(split_bytes));
-      memcpy(c->h_split.p, splits.data(), sizeof(kern::SplitNode) * (size_t)ns);
-      uint32_t* tn = (uint32_t*)((char*)c->h_split.p + off_ptn);
-      for (int i = 0; i < ns; i++)
-        for (uint32_t q = 0; q < splits[i].n_tiles; q++) tn[splits[i].tile_begin + q] = (uint32_t)i;
-      const size_t off_nleft = align_up((size_t)ptiles * 4, 16);
-      CU(c->d_part.ensure(off_nleft + (size_t)ns * 8));
-      CU(c->h_part.ensure((size_t)ns * 8));
-      { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
-      CU(cudaMemcpyAsync(c->d_split.p, c->h_split.p, split_bytes, cudaMemcpyHostToDevice, st));
-      tm.h2d_bytes += (int64_t)split_bytes;
-      tm.d2h_bytes += (int64_t)ns * 8;
-      const kern::SplitNode* dsn = (const kern::SplitNode*)c->d_split.p;
-      const uint32_t* dtn = (const uint32_t*)((char*)c->d_split.p + off_ptn);
-      uint32_t* d_tile_left = (uint32_t*)c->d_part.p;
-      uint64_t* d_nleft = (uint64_t*)((char*)c->d_part.p + off_nleft);
-      cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
-      CU(cudaEventRecord(p0, st));
-      if (!ptiles) CU(cudaMemsetAsync(d_tile_left, 0, 16, st));
-      if (!ptiles) kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>());   // empty segments: children = empty
-      if (ptiles) {
-        kern::part_count_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                      d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left,
-                                                                      c->p_segtab.as<kern::Seg>());
-        kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>());
-        kern::part_scatter_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                        d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                        d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft,
+      // ---- K4 for this piece: partition the split nodes' segments (asynchronously)
+      const int ns = (int)splits.size();
+      if (ns) {
+        uint32_t ptiles = 0;
+        for (auto& sn : splits) {
+          sn.tile_begin = ptiles;
+          sn.n_tiles = (sn.seg_len + kern::kPartTile - 1) / kern::kPartTile;
+          ptiles += sn.n_tiles;
+        }
+        PinnedBuf& hs = c->h_split_p[pz];
+        DevBuf& ds = c->d_split_p[pz];
+        DevBuf& dp = c->d_part_p[pz];
+        const size_t off_ptn = align_up(sizeof(kern::SplitNode) * (size_t)ns, 16);
+        const size_t split_bytes = off_ptn + (size_t)ptiles * 4;
+        CU(hs.ensure(split_bytes));
+        CU(ds.ensure(split_bytes));
+        memcpy(hs.p, splits.data(), sizeof(kern::SplitNode) * (size_t)ns);
+        uint32_t* tn = (uint32_t*)((char*)hs.p + off_ptn);
+        for (int i = 0; i < ns; i++)
+          for (uint32_t q = 0; q < splits[i].n_tiles; q++) tn[splits[i].tile_begin + q] = (uint32_t)i;
+        const size_t off_nleft = align_up((size_t)std::max<uint32_t>(ptiles, 4) * 4, 16);
+        CU(dp.ensure(off_nleft + (size_t)ns * 8));
+        { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
+        CU(cudaMemcpyAsync(ds.p, hs.p, split_bytes, cudaMemcpyHostToDevice, st));
+        tm.h2d_bytes += (int64_t)split_bytes;
+        const kern::SplitNode* dsn = (const kern::SplitNode*)ds.p;
+        const uint32_t* dtn = (const uint32_t*)((char*)ds.p + off_ptn);
+        uint32_t* d_tile_left = (uint32_t*)dp.p;
+        uint64_t* d_nleft = (uint64_t*)((char*)dp.p + off_nleft);
+        cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
+        CU(cudaEventRecord(p0, st));
+        if (ptiles) {
+          kern::part_count_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                        d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left,
                                                                         c->p_segtab.as<kern::Seg>());
-        tm.kernel_launches += 3;
+          tm.kernel_launches++;
+        } else {
+          CU(cudaMemsetAsync(d_tile_left, 0, 16, st));
+        }
+        kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>());
+        tm.kernel_launches++;
+        if (ptiles) {
+          kern::part_scatter_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                          d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                          d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft,
+                                                                          c->p_segtab.as<kern::Seg>());
+          tm.kernel_launches++;
+        }
+        CU(cudaEventRecord(p1, st));
+        part_ev.emplace_back(p0, p1);
+        CU(cudaGetLastError());
+        // rows sharded: the weight bound is global (world times too loose), so read the exact sizes back
+        if (row_sharded) {
+          CU(c->h_part.ensure((size_t)ns * 8));
+          CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
+          tm.d2h_bytes += (int64_t)ns * 8;
+        }
+        ns_total += ns;
+      } else {
+        const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_;
       }
-      CU(cudaEventRecord(p1, st));
-      part_ev.emplace_back(p0, p1);
-      CU(cudaGetLastError());
-      // rows sharded: the weight bound is global (world times too loose), so read the exact sizes back
-      if (row_sharded) CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
-    } else {
-      const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_;
     }
-    // ---- ... while the host already selects the next group (needs only the stack)
+    // ---- children go on the stack in Scala map iteration order (tree by tree, nodes in pop order)
+    t_host0 = now_ms();
+    for (size_t q = 0; q < cur->trees_seen.size(); q++) tree_slot[cur->trees_seen[q]] = (int)q;
+    const std::vector<int> order = hl::group_tree_visit_order(cur->trees_seen);
+    for (int t : order)
+      for (int gi : cur->nodes_for_tree[tree_slot[t]]) {
+        const Decision& dc = decisions[gi];
+        if (dc.left_pool < 0) continue;
+        if (!dc.l_leaf) stack.emplace_back(t, dc.left_pool);
+        if (!dc.r_leaf) stack.emplace_back(t, dc.left_pool + 1);
+      }
+    for (int t : cur->trees_seen) tree_slot[t] = -1;
+    { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
+    // ---- the host selects the next group (needs only the stack) while the GPU partitions
     {
       const double t0 = now_ms();
       select_group(*nxt);
       const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
     }
     TRY(select_rc);
-    if (ns && row_sharded) {
+    if (ns_total && row_sharded) {
       CU(cudaStreamSynchronize(st));
       t_host0 = now_ms();
       const uint64_t* nl = (const uint64_t*)c->h_part.p;
-      for (int i = 0; i < ns; i++) {
-        HTree& tr = trees[split_ref[i].tree];
-        const HNode& n = tr.pool[split_ref[i].pool];
+      for (int i = 0; i < ns_total; i++) {
+        HTree& tr = trees[split_ref_all[i].tree];
+        const HNode& n = tr.pool[split_ref_all[i].pool];
         tr.pool[n.left].ub = (uint32_t)nl[i];
         tr.pool[n.right].ub = n.ub - (uint32_t)nl[i];
       }
@@ -2098,7 +2166,7 @@ constexpr size_t kNoAllocMaxTiles = 262144;   // 262144 tiles x 2048 entries = 5
 constexpr size_t kNoAllocNodesOff = 0;
 constexpr size_t kNoAllocTileNodeOff = kNoAllocMaxNodes * sizeof(kern::SplitNode);
 constexpr size_t kNoAllocTileLeftOff = kNoAllocTileNodeOff + kNoAllocMaxTiles * 4;
-constexpr size_t kNoAllocScratchBytes = kNoAllocTileLeftOff + kNoAllocMaxTiles * 4;  // 2 228 224 B
+constexpr size_t kNoAllocScratchBytes = kNoAllocTileLeftOff + kNoAllocMaxTiles * 4;  // 2 293 760 B
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
 
 static std::mutex g_noalloc_mu;

@@ -636,6 +636,8 @@ struct HistArgs {
   uint32_t* total_counts;      // [n_nodes*n_chunks][C]
   int32_t Fp, f_sub, B, C, k_chunk, n_chunks;
   uint32_t tile_len;
+  uint32_t tile_base;          // first tile of this launch (a group may be launched in pieces)
+  uint32_t node_base;          // first node of this launch: result records are indexed relative to it
   uint32_t tile_smem_off;      // byte offset of the per-warp row tiles inside dynamic shared memory
   int32_t impurity, min_instances, hist_only;
   // row-sharded push mode: partial histograms go straight into the owner rank's staging buffer over NVLink
@@ -929,13 +931,14 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
   int* sh_nb = S.nb;
   __shared__ int sh_last;
 
-  const uint32_t g = A.tile_node[blockIdx.x];
+  const uint32_t tile_abs = blockIdx.x + A.tile_base;
+  const uint32_t g = A.tile_node[tile_abs];
   GroupNode nd = A.nodes[g];
   if (A.segtab) {
     const Seg sg = A.segtab[nd.seg_slot];
     nd.seg_start = sg.start; nd.seg_len = sg.len; nd.buf = sg.buf;
   }
-  const uint32_t tile_in_node = blockIdx.x - nd.tile_begin;
+  const uint32_t tile_in_node = tile_abs - nd.tile_begin;
   for (int k = tid; k < kc; k += kHistThreads) {
     const int f = A.node_feat[(size_t)g * A.f_sub + k0 + k];
     sh_feat[k] = f;
@@ -1006,7 +1009,8 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
   __syncthreads();
 
   const size_t slot_words = (size_t)A.f_sub * B * C;
-  const size_t rec = (size_t)g * A.n_chunks + chunk;
+  const size_t rec = (size_t)g * A.n_chunks + chunk;                   // tickets: absolute
+  const size_t rrec = (size_t)(g - A.node_base) * A.n_chunks + chunk;    // result record: relative to the launch
   if (A.push_world) {
     // ---- fused histogram + reduce-scatter: this rank's partial histogram of node g is stored, dense and
     // coalesced, into slot [this rank][g's index on its owner] of the OWNER rank's staging buffer through
@@ -1049,8 +1053,8 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
     for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = __ldcg(&gh[i]);
     __syncthreads();
   }
-  scan_chunk(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rec],
-             A.left_counts + rec * C, A.total_counts + rec * C);
+  scan_chunk(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rrec],
+             A.left_counts + rrec * C, A.total_counts + rrec * C);
 }
 
 // K3 alone — binsToBestSplit on histograms already in HBM (stage entry point; also the scan used

@@ -202,7 +202,7 @@ int emrf_build_lag_features(emrf_ctx_t* ctx, const int32_t* draws, int32_t n_dra
  * No counterpart in the reference or in Spark: same computation as emrf_update_partition, but
  * bins_cm_dev (column-major uint8, `col_stride` bytes between feature columns), entries_dev,
  * entries_out_dev (distinct from entries_dev) and n_left_dev[n_nodes] are DEVICE buffers owned by
- * the caller, and all working storage is a fixed 2 228 224-byte device array inside the library
+ * the caller, and all working storage is a fixed 2 293 760-byte device array inside the library
  * (held by every GPU that loads it, until exit).  Limits per call: 4096 nodes, 262 144 tiles of
  * 2048 entries; larger requests fail with EMRF_ERR_LIMIT.  The first call on a device looks up
  * the array's address (do it before any stream capture); concurrent calls on one GPU race. */

@@ -211,8 +211,8 @@ struct emrf_ctx {
   void* nccl_lib = nullptr;
   void* nccl_comm = nullptr;
   // grow-only scratch reused across groups
-  DevBuf d_group, d_results, d_ghist, d_tickets, d_split, d_part;
-  PinnedBuf h_group, h_split, h_part, h_seeds, h_table, h_tsum;
+  DevBuf d_group, d_results, d_ghist, d_tickets;
+  PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum;
   PinnedBuf h_split_p[2];
   DevBuf d_split_p[2], d_part_p[2];
   std::vector<kern::SplitNode> splits_tmp;
@@ -2167,6 +2167,7 @@ constexpr size_t kNoAllocNodesOff = 0;
 constexpr size_t kNoAllocTileNodeOff = kNoAllocMaxNodes * sizeof(kern::SplitNode);
 constexpr size_t kNoAllocTileLeftOff = kNoAllocTileNodeOff + kNoAllocMaxTiles * 4;
 constexpr size_t kNoAllocScratchBytes = kNoAllocTileLeftOff + kNoAllocMaxTiles * 4;  // 2 293 760 B
+static_assert(kNoAllocScratchBytes == 2293760, "documented in include/emrf.h, DESIGN.md and INTEGRATION.md");
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
 
 static std::mutex g_noalloc_mu;

@@ -979,6 +979,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(hist_launch(row_ch, dim3(1), hist_smem, st, kern::HistArgs(), true));
   if (row_sharded) CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
   const size_t slot_words = (size_t)f_sub * B * C;
+  // L2 blocking of the row gathers (shapes whose row-major TreePoint matrix does not fit L2, e.g. configs[2]);
+  // opt-in (EMRF_L2_BLOCK=1): measured on 10M x 128, depth 12, 50 trees it shortens the histogram kernel by
+  // only 6 % (217 -> 203 ms: the deep levels, where a group spans < 2 trees, have no reuse to win) and the
+  // host spends more than that building the per-tile tables
+  const size_t rm_bytes = (size_t)Np * Fp;
+  const bool l2_blocked = rm_bytes > ((size_t)80 << 20) && env_flag("EMRF_L2_BLOCK");
+  const int l2_ranges = l2_blocked ? (int)std::min<size_t>(256, (rm_bytes + ((size_t)24 << 20) - 1) / ((size_t)24 << 20)) : 1;
   // row-sharded, EMRF_PEER_PUSH=1: partial histograms are pushed straight into the owner rank's staging
   // buffer over NVLink (fused histogram + reduce-scatter).  Measured on 8 B200s it is ~4 % SLOWER per fit
   // than local flush + ncclReduceScatter (the remote stores lengthen the histogram kernel by more than the
@@ -1165,8 +1172,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       if (mine(g.tree)) total_entries += trees[g.tree].pool[g.pool].ub;
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
+    // TreePoint matrix larger than L2: many small tiles, launched in row-range order (below), so that the
+    // CTAs resident at any moment gather rows from the same slice of the matrix and trees share it in L2
+    if (l2_blocked) tile_len = 8192;
 
-    // staging layout: [GroupNode n][node_feat n*f_sub][tile_node tiles]
+    // staging layout: [GroupNode n][node_feat n*f_sub][tile_node tiles][tile_q tiles]
     std::vector<kern::GroupNode> gn(n_nodes);
     uint32_t n_tiles = 0;
     int n_slots = 0;
@@ -1186,21 +1196,35 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     }
     const size_t off_feat = align_up(sizeof(kern::GroupNode) * (size_t)n_nodes, 16);
     const size_t off_tiles = align_up(off_feat + (size_t)n_nodes * f_sub * 4, 16);
-    const size_t group_bytes = off_tiles + (size_t)n_tiles * 4;
+    const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
+    const size_t group_bytes = l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4;
     CU(c->h_group.ensure(group_bytes));
     CU(c->d_group.ensure(group_bytes));
     memcpy(c->h_group.p, gn.data(), sizeof(kern::GroupNode) * (size_t)n_nodes);
     memcpy((char*)c->h_group.p + off_feat, group_feat.data(), (size_t)n_nodes * f_sub * 4);
     {
       uint32_t* tn = (uint32_t*)((char*)c->h_group.p + off_tiles);
-      for (int i = 0; i < n_nodes; i++)
-        for (uint32_t q = 0; q < gn[i].n_tiles; q++) tn[gn[i].tile_begin + q] = (uint32_t)i;
+      if (!l2_blocked) {
+        for (int i = 0; i < n_nodes; i++)
+          for (uint32_t q = 0; q < gn[i].n_tiles; q++) tn[gn[i].tile_begin + q] = (uint32_t)i;
+      } else {
+        // entries of a node are in ascending row order, so tile q of a node with n tiles covers about the
+        // q/n-th part of the rows: emit range by range, every node's tiles of that range together
+        uint32_t* tq = (uint32_t*)((char*)c->h_group.p + off_tq);
+        uint32_t at = 0;
+        for (int r = 0; r < l2_ranges; r++)
+          for (int i = 0; i < n_nodes; i++) {
+            const uint32_t n = gn[i].n_tiles;
+            const uint32_t q0 = (uint32_t)((uint64_t)n * r / l2_ranges), q1 = (uint32_t)((uint64_t)n * (r + 1) / l2_ranges);
+            for (uint32_t q = q0; q < q1; q++) { tn[at] = (uint32_t)i; tq[at] = q; at++; }
+          }
+      }
     }
     // pieces: node ranges with about the same number of tiles
     // measured (configs[1]): two pieces hide ≈ 2 ms of host work per fit but cost ≈ 2.3 ms of histogram-kernel
     // time (two short launches fill the SMs worse than one), so one piece is the default
     static const bool two_pieces = env_flag("EMRF_PIECES");
-    const int n_pieces = (two_pieces && c->world == 1 && n_nodes >= 64) ? 2 : 1;
+    const int n_pieces = (two_pieces && !l2_blocked && c->world == 1 && n_nodes >= 64) ? 2 : 1;
     int piece_n0[3] = {0, n_nodes, n_nodes};
     if (n_pieces == 2) {
       int cut = n_nodes / 2;
@@ -1242,6 +1266,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.nodes = (const kern::GroupNode*)c->d_group.p;
     A.node_feat = (const int32_t*)((char*)c->d_group.p + off_feat);
     A.tile_node = (const uint32_t*)((char*)c->d_group.p + off_tiles);
+    A.tile_q = l2_blocked ? (const uint32_t*)((char*)c->d_group.p + off_tq) : nullptr;
     A.num_bins_all = d_num_bins.as<int32_t>();
     A.ghist = c->d_ghist.as<uint32_t>();
     A.tickets = c->d_tickets.as<uint32_t>();

@@ -627,6 +627,7 @@ struct HistArgs {
   const uint8_t* bins_rm;
   const GroupNode* nodes;
   const uint32_t* tile_node;   // tile → node index
+  const uint32_t* tile_q;      // tile → index of the tile inside its node (nullptr: tiles of a node are consecutive)
   const int32_t* node_feat;    // [n_nodes][f_sub]
   const int32_t* num_bins_all; // [F]
   uint32_t* ghist;             // [slots][f_sub*B*C]
@@ -938,7 +939,7 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
     const Seg sg = A.segtab[nd.seg_slot];
     nd.seg_start = sg.start; nd.seg_len = sg.len; nd.buf = sg.buf;
   }
-  const uint32_t tile_in_node = tile_abs - nd.tile_begin;
+  const uint32_t tile_in_node = A.tile_q ? A.tile_q[tile_abs] : tile_abs - nd.tile_begin;
   for (int k = tid; k < kc; k += kHistThreads) {
     const int f = A.node_feat[(size_t)g * A.f_sub + k0 + k];
     sh_feat[k] = f;

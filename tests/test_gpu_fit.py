@@ -94,6 +94,25 @@ def test_entropy_fit_within_tolerance(ctx, oracle):
     _assert_same_forest(model, ofo, exact=False)
 
 
+def test_large_matrix_and_l2_blocked_tile_order_match_oracle(oracle):
+    """A TreePoint matrix above 80 MB; with EMRF_L2_BLOCK=1 the histogram launch uses small tiles in row-range
+    order.  Runs in a subprocess because the switch is read once per process."""
+    import os, subprocess, sys
+    code = ("import numpy as np, sys; sys.path.insert(0, %r)\n"
+            "from euromillioner_b200 import synth\n"
+            "from euromillioner_b200.classifier import Dataset, RandomForestClassifier\n"
+            "from oracle import binding as ob\n"
+            "X, y = synth.flat(700000, 128, 50)\n"
+            "m = RandomForestClassifier().setNumTrees(3).setMaxDepth(5).setNumClasses(50).fit(Dataset(X, y, num_partitions=64))\n"
+            "o = ob.fit(ob.make_params(num_trees=3, max_depth=5, num_classes=50), X, y, ob.partition_offsets(len(X), 64)).export()\n"
+            "assert all(np.array_equal(v, o[k]) for k, v in m.export().items())\n"
+            "print('BIG_OK')\n") % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for flag in ("0", "1"):
+        r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, EMRF_L2_BLOCK=flag), capture_output=True,
+                           text=True, timeout=600)
+        assert r.returncode == 0 and "BIG_OK" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
 def test_two_classes_and_empty_partitions(ctx, oracle):
     """Binary labels; a partition layout with empty partitions (their RNG streams are simply unused)."""
     X, y = synth.flat(6000, 12, 2)

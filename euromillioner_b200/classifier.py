@@ -319,6 +319,87 @@ class RandomForestClassificationModel:
             walk(int(e["tree_off"][t]), 0, 0)
         return "\n".join(lines) + "\n"
 
+    # ---- Spark ML persistence --------------------------------------------------------
+    def save(self, path, uid="rfc_b200", params=None):
+        """Writes the directory layout of Spark 2.4.x `RandomForestClassificationModel.save`
+        (ml/tree/treeModels.scala EnsembleModelReadWrite.saveImpl): metadata/part-00000 (one JSON line),
+        treesMetadata/ (treeID, metadata, weights) and data/ (treeID, nodeData) as Parquet.  NodeData ids are
+        pre-order indices inside each tree, leaves carry leftChild = rightChild = -1, gain -1.0 and a
+        SplitData(-1, [], -1).  Restated from the upstream source; NOT checked against a JVM (none here)."""
+        import json
+        import os
+        import time
+        import pyarrow as pa
+        import pyarrow.parquet as pq
+        e = self.export()
+        os.makedirs(os.path.join(path, "metadata"), exist_ok=True)
+        os.makedirs(os.path.join(path, "treesMetadata"), exist_ok=True)
+        os.makedirs(os.path.join(path, "data"), exist_ok=True)
+        now = int(time.time() * 1000)
+        meta = {"class": "org.apache.spark.ml.classification.RandomForestClassificationModel", "timestamp": now,
+                "sparkVersion": "2.4.6", "uid": uid, "paramMap": dict(params or {}), "defaultParamMap": {},
+                "numFeatures": int(self.numFeatures), "numClasses": int(self.numClasses), "numTrees": int(self.numTrees)}
+        with open(os.path.join(path, "metadata", "part-00000"), "w") as f:
+            f.write(json.dumps(meta) + "\n")
+        tree_meta = [json.dumps({"class": "org.apache.spark.ml.classification.DecisionTreeClassificationModel",
+                                 "timestamp": now, "sparkVersion": "2.4.6", "uid": f"dtc_b200_{t}", "paramMap": {},
+                                 "defaultParamMap": {}, "numFeatures": int(self.numFeatures),
+                                 "numClasses": int(self.numClasses)}) for t in range(self.numTrees)]
+        pq.write_table(pa.table({"treeID": pa.array(range(self.numTrees), pa.int32()), "metadata": pa.array(tree_meta),
+                                 "weights": pa.array([1.0] * self.numTrees, pa.float64())}),
+                       os.path.join(path, "treesMetadata", "part-00000.parquet"))
+        split_t = pa.struct([("featureIndex", pa.int32()), ("leftCategoriesOrThreshold", pa.list_(pa.float64())),
+                             ("numCategories", pa.int32())])
+        node_t = pa.struct([("id", pa.int32()), ("prediction", pa.float64()), ("impurity", pa.float64()),
+                            ("impurityStats", pa.list_(pa.float64())), ("gain", pa.float64()), ("leftChild", pa.int32()),
+                            ("rightChild", pa.int32()), ("split", split_t)])
+        tree_ids, nodes = [], []
+        for t in range(self.numTrees):
+            a, b = int(e["tree_off"][t]), int(e["tree_off"][t + 1])
+            for i in range(a, b):
+                leaf = e["left"][i] < 0
+                nodes.append({"id": i - a, "prediction": float(e["prediction"][i]), "impurity": float(e["impurity"][i]),
+                              "impurityStats": [float(v) for v in e["stats"][i]],
+                              "gain": -1.0 if leaf else float(e["gain"][i]),
+                              "leftChild": -1 if leaf else int(e["left"][i]), "rightChild": -1 if leaf else int(e["right"][i]),
+                              "split": {"featureIndex": -1, "leftCategoriesOrThreshold": [], "numCategories": -1} if leaf else
+                                       {"featureIndex": int(e["feature"][i]), "leftCategoriesOrThreshold": [float(e["threshold"][i])],
+                                        "numCategories": -1}})
+                tree_ids.append(t)
+        pq.write_table(pa.table({"treeID": pa.array(tree_ids, pa.int32()), "nodeData": pa.array(nodes, node_t)}),
+                       os.path.join(path, "data", "part-00000.parquet"))
+
+    @classmethod
+    def load(cls, path, ctx=None):
+        """Reads a directory written by `save` (or by Spark 2.4.x, as far as the restated layout is right)."""
+        import glob
+        import json
+        import os
+        import pyarrow.parquet as pq
+        with open(os.path.join(path, "metadata", "part-00000")) as f:
+            meta = json.loads(f.readline())
+        rows = []
+        for fn in sorted(glob.glob(os.path.join(path, "data", "*.parquet"))):
+            tb = pq.read_table(fn).to_pydict()
+            rows += list(zip(tb["treeID"], tb["nodeData"]))
+        rows.sort(key=lambda r: (r[0], r[1]["id"]))
+        T, Cn = int(meta["numTrees"]), int(meta["numClasses"])
+        n = len(rows)
+        e = {"tree_off": np.zeros(T + 1, np.int64), "node_id": np.zeros(n, np.int32), "left": np.full(n, -1, np.int32),
+             "right": np.full(n, -1, np.int32), "feature": np.full(n, -1, np.int32), "threshold": np.zeros(n),
+             "gain": np.zeros(n), "impurity": np.zeros(n), "prediction": np.zeros(n), "stats": np.zeros((n, Cn))}
+        for i, (t, nd) in enumerate(rows):
+            e["tree_off"][t + 1] += 1
+            e["prediction"][i], e["impurity"][i] = nd["prediction"], nd["impurity"]
+            e["stats"][i] = nd["impurityStats"]
+            if nd["leftChild"] >= 0:
+                e["left"][i], e["right"][i] = nd["leftChild"], nd["rightChild"]
+                e["feature"][i] = nd["split"]["featureIndex"]
+                e["threshold"][i] = nd["split"]["leftCategoriesOrThreshold"][0]
+                e["gain"][i] = nd["gain"]
+        e["tree_off"] = np.cumsum(e["tree_off"])
+        return cls.from_arrays(e, int(meta["numFeatures"]), ctx)
+
     def transform(self, dataset, raw=True, probability=True):
         """Returns the dataset with rawPrediction (N x C), probability (N x C), prediction (N)."""
         if dataset.n_features != self.numFeatures:

@@ -172,6 +172,28 @@ def test_device_resident_inputs_and_model_roundtrip(ctx, oracle):
     assert m_host.toDebugString.startswith("RandomForestClassificationModel with 5 trees")
 
 
+def test_spark_ml_persistence_layout_round_trip(ctx, tmp_path):
+    """save() writes Spark 2.4's model directory layout; load() rebuilds the same model."""
+    import json
+    import pyarrow.parquet as pq
+    X, y = synth.flat(8000, 12, 5)
+    y = y % 5
+    m = RandomForestClassifier(ctx).setNumTrees(4).setMaxDepth(5).setNumClasses(5).fit(Dataset(X, y, num_partitions=4))
+    path = str(tmp_path / "model")
+    m.save(path, params={"numTrees": 4, "maxDepth": 5})
+    meta = json.loads(open(path + "/metadata/part-00000").readline())
+    assert meta["class"].endswith("RandomForestClassificationModel") and meta["numTrees"] == 4 and meta["numClasses"] == 5
+    data = pq.read_table(path + "/data/part-00000.parquet")
+    assert data.schema.names == ["treeID", "nodeData"] and data.num_rows == m.totalNumNodes
+    assert [f.name for f in data.schema.field("nodeData").type] == ["id", "prediction", "impurity", "impurityStats", "gain",
+                                                                     "leftChild", "rightChild", "split"]
+    m2 = RandomForestClassificationModel.load(path, ctx)
+    a, b = m.export(), m2.export()
+    for k in ("tree_off", "left", "right", "feature", "threshold", "prediction", "impurity", "stats"):
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(m.transform(Dataset(X[:500])).columns["probability"], m2.transform(Dataset(X[:500])).columns["probability"])
+
+
 def test_fit_is_deterministic_and_counts_are_conserved(ctx):
     """Size-independent properties at a larger size than the oracle is run on."""
     X, y = synth.flat(300000, 64, 50)

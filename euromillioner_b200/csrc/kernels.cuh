@@ -720,7 +720,7 @@ inline size_t hist_smem_bytes(int k_chunk, int B, int C) {
 inline int hist_row_chunks(int Fp) { return (Fp / 16 <= 8) ? Fp / 16 : 0; }
 inline size_t hist_tile_bytes(int ch) {
   if (ch == 0) return 0;
-  const int stride = (ch == 1 || ch == 2 || ch == 4 || ch == 8) ? 32 + 8 / ch : 33;
+  const int stride = (ch >= 5) ? 17 : ((ch == 1 || ch == 2 || ch == 4) ? 32 + 8 / ch : 33);
   return (size_t)(kHistThreads / 32) * 4 * ch * stride * 4 + 64 * 4;   // + per-feature tile offsets (k_chunk <= 64 here)
 }
 
@@ -887,30 +887,38 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
 // bins.  The loads of batch b+1 are issued before batch b is consumed (register double buffer).
 template <int CH>
 struct RowTile {
-  static constexpr int kWords = 4 * CH;                                  // 32-bit words per row
-  static constexpr int kStride = (CH == 1 || CH == 2 || CH == 4 || CH == 8) ? 32 + 8 / CH : 33;
+  // rows a warp stages per batch: 32, or 16 for rows wider than 64 B (half the tile memory keeps two CTAs on an
+  // SM next to a 77 KB histogram; two lanes then share a row and split its features)
+  static constexpr int kRows = (CH >= 5) ? 16 : 32;
+  static constexpr int kLoads = (CH * kRows + 31) / 32;                     // 128-bit loads per lane per batch
+  static constexpr int kWords = 4 * CH;                                     // 32-bit words per row
+  // row stride (in words) that keeps the four STS.32 of a chunk and the lane-per-row reads conflict-free
+  static constexpr int kStride = (kRows == 32) ? ((CH == 1 || CH == 2 || CH == 4) ? 32 + 8 / CH : 33)
+                                               : ((CH == 8) ? 17 : 17);
   static constexpr int kWarpWords = kWords * kStride;
 };
 template <int CH>
 __device__ __forceinline__ void load_rows(const uint8_t* __restrict__ bins, int Fp, uint32_t my_row, int lane,
-                                          uint4 (&R)[CH]) {
+                                          uint4 (&R)[RowTile<CH>::kLoads]) {
 #pragma unroll
-  for (int it = 0; it < CH; it++) {
+  for (int it = 0; it < RowTile<CH>::kLoads; it++) {
     const int q = it * 32 + lane;
     const int r = q / CH, c = q - r * CH;
-    const uint32_t row = __shfl_sync(0xffffffffu, my_row, r);
-    R[it] = __ldcg(reinterpret_cast<const uint4*>(bins + (size_t)row * Fp) + c);
+    const uint32_t row = __shfl_sync(0xffffffffu, my_row, r & 31);     // lane r (< kRows) holds row r's entry
+    if (q < CH * RowTile<CH>::kRows) R[it] = __ldcg(reinterpret_cast<const uint4*>(bins + (size_t)row * Fp) + c);
   }
 }
 template <int CH>
-__device__ __forceinline__ void stage_rows(uint32_t* tile, int lane, const uint4 (&R)[CH]) {
+__device__ __forceinline__ void stage_rows(uint32_t* tile, int lane, const uint4 (&R)[RowTile<CH>::kLoads]) {
   constexpr int TS = RowTile<CH>::kStride;
 #pragma unroll
-  for (int it = 0; it < CH; it++) {
+  for (int it = 0; it < RowTile<CH>::kLoads; it++) {
     const int q = it * 32 + lane;
     const int r = q / CH, c = q - r * CH;
-    uint32_t* d = tile + (4 * c) * TS + r;
-    d[0] = R[it].x; d[TS] = R[it].y; d[2 * TS] = R[it].z; d[3 * TS] = R[it].w;
+    if (q < CH * RowTile<CH>::kRows) {
+      uint32_t* d = tile + (4 * c) * TS + r;
+      d[0] = R[it].x; d[TS] = R[it].y; d[2 * TS] = R[it].z; d[3 * TS] = R[it].w;
+    }
   }
 }
 // entries of one warp-batch: lane j of batch b takes entry b*32 + j of the tile (0-weight beyond the end)
@@ -970,36 +978,39 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
   } else {
     constexpr int CHX = CH ? CH : 1;
     constexpr int TS = RowTile<CHX>::kStride;
+    constexpr int ROWS = RowTile<CHX>::kRows;        // entries per warp batch
+    constexpr int SHARE = 32 / ROWS;                 // lanes per row (1 or 2): they split the row's features
     const int lane = tid & 31, wv = tid >> 5;
+    const int rlane = lane & (ROWS - 1), part = lane / ROWS;
     constexpr int NW = kHistThreads / 32;
     uint32_t* tile = reinterpret_cast<uint32_t*>(smem_raw + A.tile_smem_off) + wv * RowTile<CHX>::kWarpWords;
     const uint8_t* tile_b = reinterpret_cast<const uint8_t*>(tile);
-    const uint32_t n_batches = (len + 31) >> 5;
+    const uint32_t n_batches = (len + ROWS - 1) / ROWS;
     // per-feature byte offsets into the transposed tile: word (f >> 2) of every row, byte (f & 3)
     int* sh_off = reinterpret_cast<int*>(smem_raw + A.tile_smem_off + NW * RowTile<CHX>::kWarpWords * 4);
     for (int k = tid; k < kc; k += kHistThreads) sh_off[k] = (((sh_feat[k] >> 2) * TS) << 2) + (sh_feat[k] & 3);
     __syncthreads();
-    uint4 R[CHX];
+    uint4 R[RowTile<CHX>::kLoads];
     uint32_t b = wv;
-    uint64_t e_cur = load_entry(ent, len, b * 32 + lane);
-    uint64_t e_nxt = load_entry(ent, len, (b + NW) * 32 + lane);
+    uint64_t e_cur = load_entry(ent, len, b * ROWS + rlane);
+    uint64_t e_nxt = load_entry(ent, len, (b + NW) * ROWS + rlane);
     if (b < n_batches) load_rows<CHX>(bins, Fp, (uint32_t)e_cur, lane, R);
     for (; b < n_batches; b += NW) {
       stage_rows<CHX>(tile, lane, R);
       __syncwarp();
-      const uint64_t e_nn = load_entry(ent, len, (b + 2 * NW) * 32 + lane);
+      const uint64_t e_nn = load_entry(ent, len, (b + 2 * NW) * ROWS + rlane);
       if (b + NW < n_batches) load_rows<CHX>(bins, Fp, (uint32_t)e_nxt, lane, R);
       const uint32_t w = (uint32_t)(e_cur >> 32) & 0xffu;
       const uint32_t lab = (uint32_t)(e_cur >> 40) & 0xffu;
       if (w) {
-        uint32_t* hl = sh + lab;
-        const uint8_t* tb = tile_b + (lane << 2);
         const int BC = B * C;
+        uint32_t* hl = sh + lab + part * BC;
+        const uint8_t* tb = tile_b + (rlane << 2);
 #pragma unroll 4
-        for (int k = 0; k < kc; k++) {
+        for (int k = part; k < kc; k += SHARE) {
           const uint32_t bin = tb[sh_off[k]];            // byte offset of feature k inside the transposed tile
           atomicAdd(hl + bin * C, w);
-          hl += BC;
+          hl += SHARE * BC;
         }
       }
       __syncwarp();

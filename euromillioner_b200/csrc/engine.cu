@@ -196,6 +196,50 @@ struct EventPool {
   ~EventPool() { for (auto e : ev) cudaEventDestroy(e); }
 };
 
+// host-side tree under construction (LearningNode)
+struct HNode {
+  int32_t id = 1;
+  int32_t left = -1, right = -1;
+  bool is_leaf = false, valid = true;
+  int32_t pred = 0;   // first index of the largest class count (from the scan kernel)
+  int32_t feature = -1, split_bin = -1;
+  double threshold = 0.0, gain = std::numeric_limits<double>::quiet_NaN(), impurity = 0.0;
+  uint32_t slot = 0;   // index of the node's entry segment in the device segment table
+  uint32_t ub = 0;     // upper bound on the segment's length (exact for roots and when rows are sharded)
+  // class counts = cnt_a[c] - (cnt_b ? cnt_b[c] : 0); both point into the fit's result arena (the
+  // split records copied back from the device): a left child shares its parent's "left" array, a
+  // right child is parent total minus parent left, a node that went through a group owns its totals.
+  const uint32_t* cnt_a = nullptr;
+  const uint32_t* cnt_b = nullptr;
+};
+// node pool of one tree: grows without constructing (the scheduler's parallel pass builds the children in place)
+class NodePool {
+ public:
+  NodePool() = default;
+  NodePool(NodePool&& o) noexcept : p_(o.p_), n_(o.n_), cap_(o.cap_) { o.p_ = nullptr; o.n_ = o.cap_ = 0; }
+  NodePool& operator=(NodePool&& o) noexcept { std::swap(p_, o.p_); std::swap(n_, o.n_); std::swap(cap_, o.cap_); return *this; }
+  NodePool(const NodePool&) = delete;
+  NodePool& operator=(const NodePool&) = delete;
+  ~NodePool() { free(p_); }
+  size_t size() const { return n_; }
+  void clear() { n_ = 0; }
+  void reserve(size_t cap) {
+    if (cap <= cap_) return;
+    HNode* q = (HNode*)realloc((void*)p_, cap * sizeof(HNode));   // HNode is trivially copyable
+    if (!q) throw std::bad_alloc();
+    p_ = q; cap_ = cap;
+  }
+  void resize_uninit(size_t n) { if (n > cap_) reserve(std::max(n, cap_ * 2)); n_ = n; }
+  HNode& emplace_back() { resize_uninit(n_ + 1); return *new (&p_[n_ - 1]) HNode(); }
+  HNode& operator[](size_t i) { return p_[i]; }
+  const HNode& operator[](size_t i) const { return p_[i]; }
+ private:
+  HNode* p_ = nullptr;
+  size_t n_ = 0, cap_ = 0;
+};
+struct HTree {
+  NodePool pool;
+};
 struct emrf_ctx {
   int device = 0;
   int rank = 0, world = 1;
@@ -213,9 +257,8 @@ struct emrf_ctx {
   // grow-only scratch reused across groups
   DevBuf d_group, d_results, d_ghist, d_tickets;
   PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum;
-  PinnedBuf h_split_p[2];
-  DevBuf d_split_p[2], d_part_p[2];
-  std::vector<kern::SplitNode> splits_tmp;
+  DevBuf d_split, d_part;   // partition work of the current group (written by decide_kernel)
+  std::vector<HTree> tree_pools;   // LearningNode pools of the last fit (memory reused by the next)
   DevBuf d_seeds, d_table, d_tsum;
   // fit-sized buffers kept between fits (grow-only): cudaMalloc/cudaFree of GB-sized buffers costs
   // milliseconds and cudaFree synchronises the device; they are released by emrf_ctx_destroy
@@ -731,12 +774,79 @@ struct FlatNode {
   int32_t id, left, right, feature;
   double threshold, gain, impurity, prediction;
 };
+// Host blocks of freed forests are kept (process-wide, bounded) and handed to the next forest: a fit's
+// model is tens of MB, above glibc's mmap threshold, so a fresh block would be page-faulted in 4 KB
+// steps on every fit (the host-side counterpart of DevCache).
+class HostBlockCache {
+ public:
+  static HostBlockCache& get() { static HostBlockCache g; return g; }
+  void* take(size_t bytes, size_t* got) {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      int best = -1;
+      for (int i = 0; i < (int)blocks_.size(); i++)
+        if (blocks_[i].second >= bytes && blocks_[i].second <= 2 * bytes + 4096 && (best < 0 || blocks_[i].second < blocks_[best].second)) best = i;
+      if (best >= 0) {
+        void* p = blocks_[best].first;
+        *got = blocks_[best].second;
+        held_ -= blocks_[best].second;
+        blocks_.erase(blocks_.begin() + best);
+        return p;
+      }
+    }
+    *got = bytes;
+    return malloc(bytes ? bytes : 1);
+  }
+  void give(void* p, size_t bytes) {
+    if (!p) return;
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      if (bytes >= ((size_t)1 << 20) && held_ + bytes <= kMaxHeld && blocks_.size() < 64) {
+        blocks_.emplace_back(p, bytes);
+        held_ += bytes;
+        return;
+      }
+    }
+    free(p);
+  }
+ private:
+  static constexpr size_t kMaxHeld = (size_t)2 << 30;
+  std::mutex mu_;
+  std::vector<std::pair<void*, size_t>> blocks_;
+  size_t held_ = 0;
+};
+// uninitialised array of trivially copyable T on a cached host block
+template <class T>
+class HostArr {
+ public:
+  HostArr() = default;
+  HostArr(const HostArr&) = delete;
+  HostArr& operator=(const HostArr&) = delete;
+  ~HostArr() { HostBlockCache::get().give(p_, cap_bytes_); }
+  bool resize_uninit(size_t n) {
+    if (n * sizeof(T) > cap_bytes_) {
+      HostBlockCache::get().give(p_, cap_bytes_);
+      p_ = (T*)HostBlockCache::get().take(n * sizeof(T), &cap_bytes_);
+      if (!p_) { cap_bytes_ = 0; n_ = 0; return false; }
+    }
+    n_ = n;
+    return true;
+  }
+  size_t size() const { return n_; }
+  T* data() { return p_; }
+  const T* data() const { return p_; }
+  T& operator[](size_t i) { return p_[i]; }
+  const T& operator[](size_t i) const { return p_[i]; }
+ private:
+  T* p_ = nullptr;
+  size_t n_ = 0, cap_bytes_ = 0;
+};
 struct emrf_forest {
   int num_trees = 0, num_classes = 0, num_features = 0;
   std::vector<int64_t> tree_off;
-  std::vector<FlatNode> nodes;
+  HostArr<FlatNode> nodes;
   std::vector<double> stats;  // nodes*C (filled lazily from counts for forests made by emrf_fit)
-  std::unique_ptr<uint32_t[]> counts;  // nodes*C integer class counts as trained (left uninitialised until filled)
+  HostArr<uint32_t> counts;   // nodes*C integer class counts as trained (left uninitialised until filled)
   size_t counts_len = 0;
   std::mutex stats_mu;
   std::vector<int32_t> group_sizes, trace;
@@ -751,24 +861,6 @@ struct emrf_forest {
   DevBuf d_wnodes, d_wroots, d_pthr, d_pns;
 };
 
-struct HNode {
-  int32_t id = 1;
-  int32_t left = -1, right = -1;
-  bool is_leaf = false, valid = true;
-  int32_t pred = 0;   // first index of the largest class count (from the scan kernel)
-  int32_t feature = -1, split_bin = -1;
-  double threshold = 0.0, gain = std::numeric_limits<double>::quiet_NaN(), impurity = 0.0;
-  uint32_t slot = 0;   // index of the node's entry segment in the device segment table
-  uint32_t ub = 0;     // upper bound on the segment's length (exact for roots and when rows are sharded)
-  // class counts = cnt_a[c] - (cnt_b ? cnt_b[c] : 0); both point into the fit's result arena (the
-  // split records copied back from the device): a left child shares its parent's "left" array, a
-  // right child is parent total minus parent left, a node that went through a group owns its totals.
-  const uint32_t* cnt_a = nullptr;
-  const uint32_t* cnt_b = nullptr;
-};
-struct HTree {
-  std::vector<HNode> pool;
-};
 static inline void node_counts(const HNode& n, int C, uint32_t* out) {
   if (n.cnt_b) for (int c = 0; c < C; c++) out[c] = n.cnt_a[c] - n.cnt_b[c];
   else memcpy(out, n.cnt_a, (size_t)C * 4);
@@ -814,7 +906,7 @@ static void export_pass_b(const HTree& t, int ni, int C, const std::vector<Expor
     export_pass_b(t, n.right, C, info, base, rpos, fo);
   }
 }
-static void export_forest(const std::vector<HTree>& trees, int C, emrf_forest& fo, int n_threads) {
+static bool export_forest(const std::vector<HTree>& trees, int C, emrf_forest& fo, int n_threads) {
   const int T = (int)trees.size();
   std::vector<std::vector<ExportInfo>> info(T);
 #pragma omp parallel for schedule(dynamic) num_threads(n_threads)
@@ -824,11 +916,11 @@ static void export_forest(const std::vector<HTree>& trees, int C, emrf_forest& f
   }
   fo.tree_off.assign(T + 1, 0);
   for (int t = 0; t < T; t++) fo.tree_off[t + 1] = fo.tree_off[t] + info[t][0].size;
-  fo.nodes.resize((size_t)fo.tree_off[T]);
   fo.counts_len = (size_t)fo.tree_off[T] * C;
-  fo.counts.reset(new uint32_t[fo.counts_len]);  // first touched by the parallel fill below
+  if (!fo.nodes.resize_uninit((size_t)fo.tree_off[T]) || !fo.counts.resize_uninit(fo.counts_len)) return false;
 #pragma omp parallel for schedule(dynamic) num_threads(n_threads)
   for (int t = 0; t < T; t++) export_pass_b(trees[t], 0, C, info[t], fo.tree_off[t], 0, fo);
+  return true;
 }
 static void ensure_double_stats(emrf_forest* f) {
   std::lock_guard<std::mutex> lk(f->stats_mu);
@@ -1010,9 +1102,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   }
 
   // ---- trees, stack, driver RNG (RandomForest.run)
-  std::vector<HTree> trees(T);
+  // node pools live in the context: a fit reuses the (already faulted-in) memory of the previous one
+  std::vector<HTree>& trees = c->tree_pools;
+  trees.resize(T);
+  const size_t pool_reserve = (size_t)1 << std::min(P.max_depth + 1, 12);
   for (int t = 0; t < T; t++) {
-    trees[t].pool.reserve(256);
+    trees[t].pool.clear();
+    trees[t].pool.reserve(pool_reserve);
     trees[t].pool.emplace_back();
     HNode& r = trees[t].pool[0];
     r.slot = (uint32_t)t;
@@ -1148,28 +1244,36 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
   }
   TRY(select_rc);
-  // Per group the histogram launch can be cut into `pieces` (node ranges; EMRF_PIECES=1): while the host turns
-  // the split records of piece p into tree nodes, children and partition work, the GPU is already computing
-  // piece p+1, and the partition kernels of piece p run under the host's work on piece p+1.  Multi-GPU modes
-  // exchange the whole group's records at once, so they always use one piece.
+  // Per group the GPU runs histogram+scan, decide_kernel and the partition kernels back to back; the host reads
+  // the records and decision words on the second stream, builds the tree nodes and children under the
+  // partition kernels, and must only have the next group's launch ready by the time they end.
+  if (n_chunks > 255) return fail(EMRF_ERR_LIMIT, "a node's histogram needs %d feature chunks (at most 255)", n_chunks);
   struct Decision { int32_t left_pool; bool l_leaf, r_leaf; };
   std::vector<Decision> decisions;
+  std::vector<kern::GroupNode> gn_tmp;
+  struct Upd { uint32_t slot_l, split_idx; int32_t left_pool; };
+  std::vector<Upd> upd_vec;
+  struct SplitRef { int tree, pool; };
+  std::vector<SplitRef> split_ref_tmp;
+  std::vector<int> pool_next(T, 0);
+  double ph[12] = {0};   // EMRF_DEBUG_TIMERS: where the host's time goes, per phase
+  double tp = now_ms();
+  auto lap = [&](int i) { const double n_ = now_ms(); ph[i] += n_ - tp; tp = n_; };
   while (!cur->group.empty()) {
     double t_host0 = now_ms();
+    lap(11);
     std::vector<GroupEntry>& group = cur->group;
     std::vector<int32_t>& group_feat = cur->feat;
     const int n_nodes = (int)group.size();
+    const int nt_host = n_nodes >= 1024 ? c->host_threads : 1;   // OpenMP only where a group is worth a fork/join
+    (void)nt_host;
     fo->group_sizes.push_back(n_nodes);
-    for (auto& g : group) {
-      fo->trace.push_back(g.tree);
-      fo->trace.push_back(trees[g.tree].pool[g.pool].id);
-      for (int k = 0; k < f_sub; k++) fo->trace.push_back(group_feat[g.feat_at + k]);
-    }
 
     // ---- tiles (tree-sharded multi-GPU: own trees only); sizes are upper bounds
     uint64_t total_entries = 0;
-    for (auto& g : group)
-      if (mine(g.tree)) total_entries += trees[g.tree].pool[g.pool].ub;
+#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : total_entries)
+    for (int i = 0; i < n_nodes; i++)
+      if (mine(group[i].tree)) total_entries += trees[group[i].tree].pool[group[i].pool].ub;
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
     // TreePoint matrix larger than L2: many small tiles, launched in row-range order (below), so that the
@@ -1177,9 +1281,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     if (l2_blocked) tile_len = 8192;
 
     // staging layout: [GroupNode n][node_feat n*f_sub][tile_node tiles][tile_q tiles]
-    std::vector<kern::GroupNode> gn(n_nodes);
-    uint32_t n_tiles = 0;
-    int n_slots = 0;
+    std::vector<kern::GroupNode>& gn = gn_tmp;
+    gn.resize(n_nodes);
+#pragma omp parallel for num_threads(nt_host) schedule(static)
     for (int i = 0; i < n_nodes; i++) {
       const HNode& hn = trees[group[i].tree].pool[group[i].pool];
       kern::GroupNode& d = gn[i];
@@ -1187,24 +1291,46 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       d.seg_len = 0;
       d.buf = 0;
       d.seg_slot = hn.slot;
-      d.tile_begin = n_tiles;
       d.n_tiles = mine(group[i].tree) ? std::max<uint32_t>(1, (hn.ub + tile_len - 1) / tile_len) : 0;
-      if (d.n_tiles) hist_slots.push_back(hn.slot);
+    }
+    uint32_t n_tiles = 0;
+    int n_slots = 0;
+    for (int i = 0; i < n_nodes; i++) {
+      kern::GroupNode& d = gn[i];
+      d.tile_begin = n_tiles;
       // row-sharded without push mode: every histogram goes to HBM for the reduce-scatter
       d.slot = ((row_sharded && !push_mode) || d.n_tiles > 1) ? n_slots++ : -1;
       n_tiles += d.n_tiles;
     }
     const size_t off_feat = align_up(sizeof(kern::GroupNode) * (size_t)n_nodes, 16);
-    const size_t off_tiles = align_up(off_feat + (size_t)n_nodes * f_sub * 4, 16);
+    const size_t off_info = align_up(off_feat + (size_t)n_nodes * f_sub * 4, 16);
+    const size_t off_tiles = align_up(off_info + (size_t)n_nodes * 4, 16);
     const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
     const size_t group_bytes = l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4;
     CU(c->h_group.ensure(group_bytes));
     CU(c->d_group.ensure(group_bytes));
     memcpy(c->h_group.p, gn.data(), sizeof(kern::GroupNode) * (size_t)n_nodes);
     memcpy((char*)c->h_group.p + off_feat, group_feat.data(), (size_t)n_nodes * f_sub * 4);
+    // node_info for decide_kernel (level, "this rank partitions the node") and the partition grid's upper
+    // bound: every node that may still split, tiled by its entry bound
+    uint64_t ptiles_ub64 = 0;
+    {
+      uint32_t* info = (uint32_t*)((char*)c->h_group.p + off_info);
+#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : ptiles_ub64)
+      for (int i = 0; i < n_nodes; i++) {
+        const HNode& hn = trees[group[i].tree].pool[group[i].pool];
+        const int level = 31 - __builtin_clz((unsigned)hn.id);
+        const bool m = mine(group[i].tree);
+        info[i] = (uint32_t)level | (m ? kern::kInfoMine : 0u);
+        if (m && level < P.max_depth) ptiles_ub64 += (hn.ub + kern::kPartTile - 1) / kern::kPartTile;
+      }
+    }
+    if (ptiles_ub64 > 0x7fffffffull) return fail(EMRF_ERR_LIMIT, "too many partition tiles in one group");
+    const uint32_t ptiles_ub = (uint32_t)ptiles_ub64;
     {
       uint32_t* tn = (uint32_t*)((char*)c->h_group.p + off_tiles);
       if (!l2_blocked) {
+#pragma omp parallel for num_threads(nt_host) schedule(static)
         for (int i = 0; i < n_nodes; i++)
           for (uint32_t q = 0; q < gn[i].n_tiles; q++) tn[gn[i].tile_begin + q] = (uint32_t)i;
       } else {
@@ -1220,29 +1346,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           }
       }
     }
-    // pieces: node ranges with about the same number of tiles
-    // measured (configs[1]): two pieces hide ≈ 2 ms of host work per fit but cost ≈ 2.3 ms of histogram-kernel
-    // time (two short launches fill the SMs worse than one), so one piece is the default
-    static const bool two_pieces = env_flag("EMRF_PIECES");
-    const int n_pieces = (two_pieces && !l2_blocked && c->world == 1 && n_nodes >= 64) ? 2 : 1;
-    int piece_n0[3] = {0, n_nodes, n_nodes};
-    if (n_pieces == 2) {
-      int cut = n_nodes / 2;
-      for (int i = 0; i < n_nodes; i++) if (gn[i].tile_begin >= n_tiles / 2) { cut = std::max(1, i); break; }
-      piece_n0[1] = std::min(cut, n_nodes - 1);
-    }
-    // per-piece record block: [ScanResult r][left r*C][total r*C]
-    size_t piece_off[3], piece_left[2], piece_total[2];
-    size_t res_bytes = 0;
-    for (int pz = 0; pz < n_pieces; pz++) {
-      const size_t r = (size_t)(piece_n0[pz + 1] - piece_n0[pz]) * n_chunks;
-      piece_off[pz] = res_bytes;
-      piece_left[pz] = align_up(sizeof(kern::ScanResult) * r, 16);
-      piece_total[pz] = piece_left[pz] + r * C * 4;
-      res_bytes += align_up(piece_total[pz] + r * C * 4, 256);
-    }
-    piece_off[n_pieces] = res_bytes;
+    // record block: [ScanResult r][left r*C][total r*C][decision word n]
     const size_t n_rec = (size_t)n_nodes * n_chunks;
+    const size_t res_left = align_up(sizeof(kern::ScanResult) * n_rec, 16);
+    const size_t res_total = res_left + n_rec * C * 4;
+    const size_t res_dec = align_up(res_total + n_rec * C * 4, 16);
+    const size_t res_bytes = align_up(res_dec + (size_t)n_nodes * 4, 256);
     CU(c->d_results.ensure(res_bytes));
     char* h_res = (char*)c->arena_alloc(res_bytes);   // kept until the forest is exported
     if (!h_res) return fail(EMRF_ERR_CUDA, "out of pinned host memory for the split-record arena");
@@ -1250,7 +1359,26 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const int nodes_per_rank = row_sharded ? (n_nodes + c->world - 1) / c->world : 0;
     const int n_slots_alloc = (row_sharded && !push_mode) ? nodes_per_rank * c->world : n_slots;
     CU(c->d_ghist.ensure((size_t)std::max(n_slots_alloc, 1) * slot_words * 4));
+    // partition work of this group, written by decide_kernel: [SplitNode n][tile_node ptiles_ub] and
+    // [tile_left ptiles_ub][n_left n][limits 2]
+    const size_t off_ptn = align_up(sizeof(kern::SplitNode) * (size_t)n_nodes, 16);
+    const size_t split_bytes = off_ptn + (size_t)std::max<uint32_t>(ptiles_ub, 4) * 4;
+    const size_t off_nleft = align_up((size_t)std::max<uint32_t>(ptiles_ub, 4) * 4, 16);
+    const size_t off_limits = off_nleft + (size_t)n_nodes * 8;
+    CU(c->d_split.ensure(split_bytes));
+    CU(c->d_part.ensure(off_limits + 16));
+    if ((size_t)next_slot + 2 * (size_t)n_nodes > seg_cap) {   // grow the segment table
+      CU(cudaStreamSynchronize(st));
+      DevBuf bigger;
+      CU(bigger.alloc(std::max(seg_cap * 2, (size_t)next_slot + 2 * (size_t)n_nodes) * sizeof(kern::Seg)));
+      CU(cudaMemcpyAsync(bigger.p, c->p_segtab.p, (size_t)next_slot * sizeof(kern::Seg), cudaMemcpyDeviceToDevice, st));
+      CU(cudaStreamSynchronize(st));
+      std::swap(bigger.p, c->p_segtab.p);
+      std::swap(bigger.bytes, c->p_segtab.bytes);
+      seg_cap = c->p_segtab.bytes / sizeof(kern::Seg);
+    }
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_sel += d_; }
+    lap(0);
 
     CU(cudaMemcpyAsync(c->d_group.p, c->h_group.p, group_bytes, cudaMemcpyHostToDevice, st));
     tm.h2d_bytes += (int64_t)group_bytes;
@@ -1277,33 +1405,24 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.push_world = push_mode ? c->world : 0; A.push_rank = c->rank; A.push_npr = nodes_per_rank;
     for (int r = 0; r < 8; r++) A.peer_stage[r] = (uint32_t*)c->peer_stage[r];
     A.min_info_gain = P.min_info_gain;
-    cudaEvent_t piece_done[2] = {nullptr, nullptr};
-    for (int pz = 0; pz < n_pieces; pz++) {
-      const int n0 = piece_n0[pz], n1 = piece_n0[pz + 1];
-      const uint32_t t0 = gn[n0].tile_begin, t1 = (n1 < n_nodes) ? gn[n1].tile_begin : n_tiles;
-      char* blk = (char*)c->d_results.p + piece_off[pz];
-      A.results = (kern::ScanResult*)blk;
-      A.left_counts = (uint32_t*)(blk + piece_left[pz]);
-      A.total_counts = (uint32_t*)(blk + piece_total[pz]);
-      A.tile_base = t0;
-      A.node_base = (uint32_t)n0;
+    A.results = (kern::ScanResult*)c->d_results.p;
+    A.left_counts = (uint32_t*)((char*)c->d_results.p + res_left);
+    A.total_counts = (uint32_t*)((char*)c->d_results.p + res_total);
+    A.tile_base = 0;
+    A.node_base = 0;
+    {
       cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
       CU(cudaEventRecord(e0, st));
-      if (t1 > t0) {
-        CU(hist_launch(row_ch, dim3(t1 - t0, n_chunks), hist_smem, st, A, false));
+      if (n_tiles) {
+        CU(hist_launch(row_ch, dim3(n_tiles, n_chunks), hist_smem, st, A, false));
         tm.kernel_launches++;
         tm.hist_launches++;
       }
       CU(cudaEventRecord(e1, st));
       hist_ev.emplace_back(e0, e1);
       CU(cudaGetLastError());
-      if (c->world == 1) {
-        CU(cudaMemcpyAsync(h_res + piece_off[pz], blk, piece_off[pz + 1] - piece_off[pz], cudaMemcpyDeviceToHost, st));
-        piece_done[pz] = c->events.get();
-        CU(cudaEventRecord(piece_done[pz], st));
-      }
     }
-    if (c->world > 1) {   // single piece: block 0 holds every record
+    if (c->world > 1) {
       if (row_sharded && push_mode) {
         // every rank's partials must have landed in the owners' staging buffers: a 1-word all-reduce is the
         // cross-rank barrier (in stream order it follows this rank's histogram kernel)
@@ -1336,178 +1455,168 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           CU(cudaGetLastError());
         }
       }
-      TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_bytes / 4));
-      CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, st));
-      piece_done[0] = c->events.get();
-      CU(cudaEventRecord(piece_done[0], st));
+      TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_dec / 4));
     }
-    for (auto& g : group)
-      if (mine(g.tree)) tm.hist_alg_bytes += (int64_t)slot_words * 4;
-    tm.total_nodes_split += n_nodes;
-
-    // ---- driver side of findBestSplits, piece by piece: records → node stats, children, partition work.
-    // Class counts are not copied: nodes point into the arena records.
-    decisions.assign(n_nodes, Decision{-1, true, true});
-    if ((size_t)next_slot + 2 * (size_t)n_nodes > seg_cap) {   // grow the segment table
-      CU(cudaStreamSynchronize(st));
-      DevBuf bigger;
-      CU(bigger.alloc(std::max(seg_cap * 2, (size_t)next_slot + 2 * (size_t)n_nodes) * sizeof(kern::Seg)));
-      CU(cudaMemcpyAsync(bigger.p, c->p_segtab.p, (size_t)next_slot * sizeof(kern::Seg), cudaMemcpyDeviceToDevice, st));
-      CU(cudaStreamSynchronize(st));
-      std::swap(bigger.p, c->p_segtab.p);
-      std::swap(bigger.bytes, c->p_segtab.bytes);
-      seg_cap = c->p_segtab.bytes / sizeof(kern::Seg);
+    // ---- decisions and partition work on the device, the partition kernels right behind; the records (with
+    // the decision words) go to the host on the second stream meanwhile
+    kern::SplitNode* dsn = (kern::SplitNode*)c->d_split.p;
+    uint32_t* dtn = (uint32_t*)((char*)c->d_split.p + off_ptn);
+    uint32_t* d_tile_left = (uint32_t*)c->d_part.p;
+    uint64_t* d_nleft = (uint64_t*)((char*)c->d_part.p + off_nleft);
+    uint32_t* d_limits = (uint32_t*)((char*)c->d_part.p + off_limits);
+    {
+      kern::DecideArgs D;
+      D.results = A.results; D.nodes = A.nodes; D.node_feat = A.node_feat;
+      D.node_info = (const uint32_t*)((char*)c->d_group.p + off_info);
+      D.segtab = c->p_segtab.as<kern::Seg>();
+      D.out_splits = dsn; D.out_tile_node = dtn;
+      D.out_dec = (uint32_t*)((char*)c->d_results.p + res_dec);
+      D.out_limits = d_limits;
+      D.n_nodes = n_nodes; D.n_chunks = n_chunks; D.f_sub = f_sub; D.max_depth = P.max_depth;
+      D.next_slot = next_slot;
+      kern::decide_kernel<<<1, 1024, 0, st>>>(D);
+      tm.kernel_launches++;
+      CU(cudaGetLastError());
     }
-    struct SplitRef { int tree, pool; };
-    std::vector<SplitRef> split_ref_all;
-    int ns_total = 0;
-    for (int pz = 0; pz < n_pieces; pz++) {
-      CU(cudaEventSynchronize(piece_done[pz]));
+    cudaEvent_t ev_dec = c->events.get(), rec_done = c->events.get();
+    CU(cudaEventRecord(ev_dec, st));
+    CU(cudaStreamWaitEvent(c->stream2, ev_dec, 0));
+    CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, c->stream2));
+    CU(cudaEventRecord(rec_done, c->stream2));
+    if (ptiles_ub) {
+      cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
+      CU(cudaEventRecord(p0, st));
+      kern::part_count_kernel<<<ptiles_ub, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                       d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left,
+                                                                       c->p_segtab.as<kern::Seg>(), d_limits);
+      kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>(), d_limits);
+      kern::part_scatter_kernel<<<ptiles_ub, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                         d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                         d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft,
+                                                                         c->p_segtab.as<kern::Seg>(), d_limits);
+      tm.kernel_launches += 3;
+      CU(cudaEventRecord(p1, st));
+      part_ev.emplace_back(p0, p1);
+      CU(cudaGetLastError());
+    }
+    // the next group's staging and records must not be overwritten before this copy is done: the host waits
+    // for rec_done below, before it launches anything else
+    lap(1);
+    // ---- bookkeeping nobody waits for, done while the GPU works
+    {
       t_host0 = now_ms();
-      const int n0 = piece_n0[pz], n1 = piece_n0[pz + 1];
-      const char* blk = h_res + piece_off[pz];
-      const kern::ScanResult* res = (const kern::ScanResult*)blk;
-      const uint32_t* res_left = (const uint32_t*)(blk + piece_left[pz]);
-      const uint32_t* res_total = (const uint32_t*)(blk + piece_total[pz]);
-      std::vector<kern::SplitNode>& splits = c->splits_tmp;
-      splits.clear();
-      std::vector<uint32_t> rightc(C);
-      for (int gi = n0; gi < n1; gi++) {
-        const GroupEntry& g = group[gi];
-        const int t = g.tree;
-        HTree& tr = trees[t];
-        // combine feature chunks: first maximum in subset order
-        const size_t r0 = (size_t)(gi - n0) * n_chunks;
-        int best = -1;
-        for (int ch = 0; ch < n_chunks; ch++) {
-          const kern::ScanResult& r = res[r0 + ch];
-          if (r.k < 0) continue;
-          if (best < 0 || r.gain > res[r0 + best].gain) best = ch;
-        }
-        const size_t rec = r0 + (best < 0 ? 0 : best);
-        const uint32_t* totc = res_total + rec * C;
-        const uint32_t* leftc = res_left + rec * C;
-        const int id = tr.pool[g.pool].id;
-        const int level = 31 - __builtin_clz((unsigned)id);
-        // impurities and gain come from the scan kernel (bit-exact IEEE, Spark's operation order);
-        // EMRF_VERIFY_GAINS=1 recomputes them here.
-        const double pimp = res[rec].impurity;
-        double gain = kern::kInvalidGain, limp = 0.0, rimp = 0.0;
-        bool valid = false;
-        if (best >= 0 && res[rec].valid) {
-          gain = res[rec].gain; limp = res[rec].left_impurity; rimp = res[rec].right_impurity;
-          valid = true;
-          if (verify_gains) {
-            uint64_t lc = 0, rc = 0;
-            for (int cc = 0; cc < C; cc++) { rightc[cc] = totc[cc] - leftc[cc]; lc += leftc[cc]; rc += rightc[cc]; }
-            const double hl_ = hl::impurity_of(P.impurity, leftc, C), hr_ = hl::impurity_of(P.impurity, rightc.data(), C);
-            const double hp_ = hl::impurity_of(P.impurity, totc, C);
-            const double tc = (double)(lc + rc);
-            const double lw = (double)lc / tc, rw = (double)rc / tc;
-            const double hg = hp_ - lw * hl_ - rw * hr_;
-            if (hg != gain || hl_ != limp || hr_ != rimp || hp_ != pimp) tm.gain_mismatches++;
-          }
-        }
-        const bool is_leaf = (gain <= 0) || (level == P.max_depth);
-        {
-          HNode& n = tr.pool[g.pool];
-          n.is_leaf = is_leaf; n.gain = gain; n.impurity = pimp; n.valid = valid;
-          n.cnt_a = totc; n.cnt_b = nullptr; n.pred = res[rec].pred;
-        }
-        if (!is_leaf) {
-          const int feat = group_feat[g.feat_at + res[rec].k];
-          const int sbin = res[rec].split;
-          const bool child_leaf = (level + 1) == P.max_depth;
-          const bool l_leaf = child_leaf || (limp == 0.0);
-          const bool r_leaf = child_leaf || (rimp == 0.0);
-          const int li = (int)tr.pool.size();
-          tr.pool.emplace_back();
-          tr.pool.emplace_back();
-          HNode& l = tr.pool[li];
-          HNode& r = tr.pool[li + 1];
-          l.id = 2 * id; l.is_leaf = l_leaf; l.impurity = limp; l.cnt_a = leftc; l.pred = res[rec].left_pred;
-          r.id = 2 * id + 1; r.is_leaf = r_leaf; r.impurity = rimp; r.cnt_a = totc; r.cnt_b = leftc; r.pred = res[rec].right_pred;
-          HNode& n = tr.pool[g.pool];
-          // a segment cannot hold more entries than its parent's, nor more than the node's total weight
-          // (every entry weighs >= 1): good enough to tile the next launches without reading sizes back
-          l.slot = next_slot++; r.slot = next_slot++;
-          l.ub = std::min(n.ub, res[rec].left_weight);
-          r.ub = std::min(n.ub, res[rec].total_weight - res[rec].left_weight);
-          n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
-          n.left = li; n.right = li + 1;
-          decisions[gi] = Decision{li, l_leaf, r_leaf};
-          if ((!l_leaf || !r_leaf) && mine(t)) {
-            kern::SplitNode sn;
-            sn.seg_start = 0; sn.seg_len = n.ub; sn.buf = 0;   // real segment: segment table [seg_slot]
-            sn.seg_slot = n.slot; sn.left_slot = l.slot; sn.right_slot = r.slot; sn.pad = 0;
-            sn.feature = feat; sn.split_bin = sbin; sn.tile_begin = 0; sn.n_tiles = 0;
-            splits.push_back(sn);
-            split_ref_all.push_back({t, g.pool});
-          }
-        }
+      const size_t at0 = fo->trace.size();
+      fo->trace.resize(at0 + (size_t)n_nodes * (2 + f_sub));
+      int32_t* tr_out = fo->trace.data() + at0;
+#pragma omp parallel for num_threads(nt_host) schedule(static)
+      for (int i = 0; i < n_nodes; i++) {
+        const GroupEntry& g = group[i];
+        int32_t* o = tr_out + (size_t)i * (2 + f_sub);
+        o[0] = g.tree;
+        o[1] = trees[g.tree].pool[g.pool].id;
+        for (int k = 0; k < f_sub; k++) o[2 + k] = group_feat[g.feat_at + k];
       }
-      // ---- K4 for this piece: partition the split nodes' segments (asynchronously)
-      const int ns = (int)splits.size();
-      if (ns) {
-        uint32_t ptiles = 0;
-        for (auto& sn : splits) {
-          sn.tile_begin = ptiles;
-          sn.n_tiles = (sn.seg_len + kern::kPartTile - 1) / kern::kPartTile;
-          ptiles += sn.n_tiles;
-        }
-        PinnedBuf& hs = c->h_split_p[pz];
-        DevBuf& ds = c->d_split_p[pz];
-        DevBuf& dp = c->d_part_p[pz];
-        const size_t off_ptn = align_up(sizeof(kern::SplitNode) * (size_t)ns, 16);
-        const size_t split_bytes = off_ptn + (size_t)ptiles * 4;
-        CU(hs.ensure(split_bytes));
-        CU(ds.ensure(split_bytes));
-        memcpy(hs.p, splits.data(), sizeof(kern::SplitNode) * (size_t)ns);
-        uint32_t* tn = (uint32_t*)((char*)hs.p + off_ptn);
-        for (int i = 0; i < ns; i++)
-          for (uint32_t q = 0; q < splits[i].n_tiles; q++) tn[splits[i].tile_begin + q] = (uint32_t)i;
-        const size_t off_nleft = align_up((size_t)std::max<uint32_t>(ptiles, 4) * 4, 16);
-        CU(dp.ensure(off_nleft + (size_t)ns * 8));
-        { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
-        CU(cudaMemcpyAsync(ds.p, hs.p, split_bytes, cudaMemcpyHostToDevice, st));
-        tm.h2d_bytes += (int64_t)split_bytes;
-        const kern::SplitNode* dsn = (const kern::SplitNode*)ds.p;
-        const uint32_t* dtn = (const uint32_t*)((char*)ds.p + off_ptn);
-        uint32_t* d_tile_left = (uint32_t*)dp.p;
-        uint64_t* d_nleft = (uint64_t*)((char*)dp.p + off_nleft);
-        cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
-        CU(cudaEventRecord(p0, st));
-        if (ptiles) {
-          kern::part_count_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                        d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left,
-                                                                        c->p_segtab.as<kern::Seg>());
-          tm.kernel_launches++;
-        } else {
-          CU(cudaMemsetAsync(d_tile_left, 0, 16, st));
-        }
-        kern::part_scan_kernel<<<ns, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>());
-        tm.kernel_launches++;
-        if (ptiles) {
-          kern::part_scatter_kernel<<<ptiles, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                          d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                          d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft,
-                                                                          c->p_segtab.as<kern::Seg>());
-          tm.kernel_launches++;
-        }
-        CU(cudaEventRecord(p1, st));
-        part_ev.emplace_back(p0, p1);
-        CU(cudaGetLastError());
-        // rows sharded: the weight bound is global (world times too loose), so read the exact sizes back
-        if (row_sharded) {
-          CU(c->h_part.ensure((size_t)ns * 8));
-          CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
-          tm.d2h_bytes += (int64_t)ns * 8;
-        }
-        ns_total += ns;
-      } else {
-        const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_;
-      }
+      int64_t built = 0;
+      for (int i = 0; i < n_nodes; i++)
+        if (gn[i].n_tiles) { hist_slots.push_back(gn[i].seg_slot); built++; }
+      tm.hist_alg_bytes += built * (int64_t)slot_words * 4;
+      tm.total_nodes_split += n_nodes;
+      const double d_ = now_ms() - t_host0; host_ms += d_; host_sel += d_;
     }
+    lap(2);
+
+    // ---- host side of findBestSplits: the decision words say what became of every node; numbering repeats
+    // decide_kernel's (group order).  Class counts are not copied: nodes point into the arena records.
+    CU(cudaEventSynchronize(rec_done));
+    t_host0 = now_ms();
+    lap(3);
+    const kern::ScanResult* res = (const kern::ScanResult*)h_res;
+    const uint32_t* res_leftc = (const uint32_t*)(h_res + res_left);
+    const uint32_t* res_totalc = (const uint32_t*)(h_res + res_total);
+    const uint32_t* dec = (const uint32_t*)(h_res + res_dec);
+    decisions.resize(n_nodes);
+    upd_vec.resize(n_nodes);
+    Upd* upd = upd_vec.data();
+    for (int t : cur->trees_seen) pool_next[t] = (int)trees[t].pool.size();
+    int ns = 0;
+    for (int gi = 0; gi < n_nodes; gi++) {
+      Upd& u = upd[gi];
+      u.left_pool = -1; u.slot_l = 0; u.split_idx = 0;
+      if (!(dec[gi] & kern::kDecNonLeaf)) continue;
+      u.slot_l = next_slot; next_slot += 2;
+      int& pn = pool_next[group[gi].tree];
+      u.left_pool = pn; pn += 2;
+      if (dec[gi] & kern::kDecSplit) u.split_idx = (uint32_t)ns++;
+    }
+    for (int t : cur->trees_seen) trees[t].pool.resize_uninit((size_t)pool_next[t]);
+    lap(5);
+    std::vector<SplitRef>& split_ref = split_ref_tmp;
+    // rows sharded: the weight bound is global (world times too loose), so read the exact sizes back
+    if (row_sharded && ns) {
+      CU(c->h_part.ensure((size_t)ns * 8));
+      CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
+      tm.d2h_bytes += (int64_t)ns * 8;
+      split_ref.resize((size_t)ns);
+    }
+    int64_t mism = 0;
+#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : mism)
+    for (int gi = 0; gi < n_nodes; gi++) {
+      const GroupEntry& g = group[gi];
+      const Upd& u = upd[gi];
+      const uint32_t dw = dec[gi];
+      HTree& tr = trees[g.tree];
+      const size_t rec = (size_t)gi * n_chunks + (dw & 0xffu);
+      const kern::ScanResult& r = res[rec];
+      const uint32_t* totc = res_totalc + rec * C;
+      const uint32_t* leftc = res_leftc + rec * C;
+      const bool valid = (dw & kern::kDecValid) != 0;
+      // impurities and gain come from the scan kernel (bit-exact IEEE, Spark's operation order);
+      // EMRF_VERIFY_GAINS=1 recomputes them here.
+      const double pimp = r.impurity;
+      const double gain = valid ? r.gain : kern::kInvalidGain;
+      const double limp = valid ? r.left_impurity : 0.0, rimp = valid ? r.right_impurity : 0.0;
+      if (valid && verify_gains) {
+        std::vector<uint32_t> rightc(C);
+        uint64_t lc = 0, rc = 0;
+        for (int cc = 0; cc < C; cc++) { rightc[cc] = totc[cc] - leftc[cc]; lc += leftc[cc]; rc += rightc[cc]; }
+        const double hl_ = hl::impurity_of(P.impurity, leftc, C), hr_ = hl::impurity_of(P.impurity, rightc.data(), C);
+        const double hp_ = hl::impurity_of(P.impurity, totc, C);
+        const double tc = (double)(lc + rc);
+        const double lw = (double)lc / tc, rw = (double)rc / tc;
+        const double hg = hp_ - lw * hl_ - rw * hr_;
+        if (hg != gain || hl_ != limp || hr_ != rimp || hp_ != pimp) mism++;
+      }
+      HNode& n = tr.pool[g.pool];
+      const bool is_leaf = !(dw & kern::kDecNonLeaf);
+      if (verify_gains) {   // the device's leaf rule against the host's
+        const int level = 31 - __builtin_clz((unsigned)n.id);
+        if (is_leaf != ((gain <= 0) || (level == P.max_depth))) mism++;
+      }
+      n.is_leaf = is_leaf; n.gain = gain; n.impurity = pimp; n.valid = valid;
+      n.cnt_a = totc; n.cnt_b = nullptr; n.pred = r.pred;
+      if (is_leaf) { decisions[gi] = Decision{-1, true, true}; continue; }
+      const int feat = group_feat[g.feat_at + r.k];
+      const int sbin = r.split;
+      const bool l_leaf = (dw & kern::kDecLLeaf) != 0, r_leaf = (dw & kern::kDecRLeaf) != 0;
+      const int li = u.left_pool;
+      HNode& l = *new (&tr.pool[li]) HNode();
+      HNode& rn = *new (&tr.pool[li + 1]) HNode();
+      const int id = n.id;
+      l.id = 2 * id; l.is_leaf = l_leaf; l.impurity = limp; l.cnt_a = leftc; l.pred = r.left_pred;
+      rn.id = 2 * id + 1; rn.is_leaf = r_leaf; rn.impurity = rimp; rn.cnt_a = totc; rn.cnt_b = leftc; rn.pred = r.right_pred;
+      // a segment cannot hold more entries than its parent's, nor more than the node's total weight
+      // (every entry weighs >= 1): good enough to tile the next launches without reading sizes back
+      l.slot = u.slot_l; rn.slot = u.slot_l + 1;
+      l.ub = std::min(n.ub, r.left_weight);
+      rn.ub = std::min(n.ub, r.total_weight - r.left_weight);
+      n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
+      n.left = li; n.right = li + 1;
+      decisions[gi] = Decision{li, l_leaf, r_leaf};
+      if (row_sharded && (dw & kern::kDecSplit)) split_ref[u.split_idx] = {g.tree, g.pool};
+    }
+    tm.gain_mismatches += mism;
+    { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
+    lap(8);
     // ---- children go on the stack in Scala map iteration order (tree by tree, nodes in pop order)
     t_host0 = now_ms();
     for (size_t q = 0; q < cur->trees_seen.size(); q++) tree_slot[cur->trees_seen[q]] = (int)q;
@@ -1521,6 +1630,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       }
     for (int t : cur->trees_seen) tree_slot[t] = -1;
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
+    lap(9);
     // ---- the host selects the next group (needs only the stack) while the GPU partitions
     {
       const double t0 = now_ms();
@@ -1528,13 +1638,14 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       const double d_ = now_ms() - t0; host_ms += d_; host_sel += d_;
     }
     TRY(select_rc);
-    if (ns_total && row_sharded) {
+    lap(10);
+    if (ns && row_sharded) {
       CU(cudaStreamSynchronize(st));
       t_host0 = now_ms();
       const uint64_t* nl = (const uint64_t*)c->h_part.p;
-      for (int i = 0; i < ns_total; i++) {
-        HTree& tr = trees[split_ref_all[i].tree];
-        const HNode& n = tr.pool[split_ref_all[i].pool];
+      for (int i = 0; i < ns; i++) {
+        HTree& tr = trees[split_ref[i].tree];
+        const HNode& n = tr.pool[split_ref[i].pool];
         tr.pool[n.left].ub = (uint32_t)nl[i];
         tr.pool[n.right].ub = n.ub - (uint32_t)nl[i];
       }
@@ -1543,6 +1654,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     std::swap(cur, nxt);
   }
 
+  if (env_flag("EMRF_DEBUG_TIMERS"))
+    fprintf(stderr, "[emrf] host phases ms: prep %.2f | launch %.2f | bookkeeping %.2f | wait %.2f | numbering %.2f | nodes %.2f | "
+            "stack %.2f | select %.2f | other %.2f\n", ph[0], ph[1], ph[2], ph[3], ph[5], ph[8], ph[9], ph[10], ph[11]);
   // ---- exact entry counts of every histogram built (the roofline's algorithmic bytes), from the table
   {
     std::vector<kern::Seg> segs(next_slot);
@@ -1555,7 +1669,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   }
   // ---- topNodes.map(_.toNode(prune = true))
   double t_host0 = now_ms();
-  export_forest(trees, C, *fo, c->host_threads);
+  if (!export_forest(trees, C, *fo, c->host_threads)) return fail(EMRF_ERR_INTERNAL, "out of host memory for the model");
   { const double d_ = now_ms() - t_host0; host_ms += d_; tm.host_export_ms = d_; }
   CU(cudaEventRecord(ev_end, st));
   CU(cudaStreamSynchronize(st));
@@ -1654,7 +1768,7 @@ extern "C" int emrf_forest_import(emrf_ctx_t* c, int32_t T, int32_t C, int32_t F
   f->num_trees = T; f->num_classes = C; f->num_features = F;
   f->tree_off.assign(tree_off, tree_off + T + 1);
   const int64_t n = tree_off[T];
-  f->nodes.resize(n);
+  if (!f->nodes.resize_uninit((size_t)n)) { delete f; return fail(EMRF_ERR_INTERNAL, "out of host memory for the model"); }
   for (int64_t i = 0; i < n; i++) {
     FlatNode& q = f->nodes[i];
     q.id = node_id ? node_id[i] : 0; q.left = left[i]; q.right = right[i]; q.feature = feature[i];

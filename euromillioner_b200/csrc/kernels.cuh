@@ -1158,8 +1158,10 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(const uint64_t
                                                                   const SplitNode* __restrict__ nodes,
                                                                   const uint32_t* __restrict__ tile_node,
                                                                   uint32_t* __restrict__ tile_left,
-                                                                  const Seg* __restrict__ segtab) {
+                                                                  const Seg* __restrict__ segtab,
+                                                                  const uint32_t* __restrict__ limits = nullptr) {
   __shared__ uint32_t sh_cnt[kPartThreads / 32];
+  if (limits && blockIdx.x >= limits[1]) return;   // grid provisioned from upper bounds (decide_kernel)
   const uint32_t g = tile_node[blockIdx.x];
   const SplitNode nd = load_split(nodes, g, segtab);
   const uint32_t t_in = blockIdx.x - nd.tile_begin;
@@ -1188,10 +1190,12 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(const uint64_t
   }
 }
 __global__ void __launch_bounds__(256) part_scan_kernel(const SplitNode* __restrict__ nodes, uint32_t* __restrict__ tile_left,
-                                                        uint64_t* __restrict__ n_left, Seg* __restrict__ segtab) {
+                                                        uint64_t* __restrict__ n_left, Seg* __restrict__ segtab,
+                                                        const uint32_t* __restrict__ limits = nullptr) {
   // one CTA per node; sequential chunks of 256 tiles with a block scan
   __shared__ uint32_t sh[256];
   __shared__ uint32_t carry;
+  if (limits && blockIdx.x >= limits[0]) return;
   const SplitNode nd = load_split(nodes, blockIdx.x, segtab);
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
@@ -1231,8 +1235,10 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64
                                                                     const uint32_t* __restrict__ tile_node,
                                                                     const uint32_t* __restrict__ tile_left_off,
                                                                     const uint64_t* __restrict__ n_left,
-                                                                    const Seg* __restrict__ segtab) {
+                                                                    const Seg* __restrict__ segtab,
+                                                                    const uint32_t* __restrict__ limits = nullptr) {
   __shared__ uint32_t sh_w[kPartThreads / 32];
+  if (limits && blockIdx.x >= limits[1]) return;
   const uint32_t g = tile_node[blockIdx.x];
   const SplitNode nd = load_split(nodes, g, segtab);
   const uint32_t t_in = blockIdx.x - nd.tile_begin;
@@ -1278,6 +1284,105 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64
     }
     lrank += __popc(bal[r]);
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Driver side of findBestSplits, on the device: turns a group's split records into (a) one decision word per
+// node — the winning feature chunk and Spark's leaf rules (RandomForest.findBestSplits: isLeaf = gain <= 0 ||
+// level == maxDepth; a child is a leaf at maxDepth or when its impurity is 0.0) — which the host reads back
+// with the records, and (b) the partition work (SplitNode list, tile map, counts) that the K4 kernels
+// launched right behind it consume, so that the GPU never waits for the host between a group's histograms and
+// its partition.  Numbering is in group order: segment slots next_slot + 2*i for the i-th non-leaf node, split
+// index = rank among the nodes that have a child to partition.  One CTA; nodes in chunks of 1024.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kDecNonLeaf = 1u << 8, kDecLLeaf = 1u << 9, kDecRLeaf = 1u << 10, kDecSplit = 1u << 11, kDecValid = 1u << 12;
+constexpr uint32_t kInfoMine = 1u << 8;   // node_info: level | kInfoMine (this rank builds/partitions the node's tree)
+struct DecideArgs {
+  const ScanResult* results;     // [n_nodes][n_chunks]
+  const GroupNode* nodes;
+  const int32_t* node_feat;      // [n_nodes][f_sub]
+  const uint32_t* node_info;     // [n_nodes]
+  const Seg* segtab;
+  SplitNode* out_splits;
+  uint32_t* out_tile_node;
+  uint32_t* out_dec;             // [n_nodes] best chunk | kDec* flags
+  uint32_t* out_limits;          // [0] split nodes, [1] partition tiles
+  int n_nodes, n_chunks, f_sub, max_depth;
+  uint32_t next_slot;
+};
+__global__ void __launch_bounds__(1024) decide_kernel(const DecideArgs A) {
+  __shared__ uint32_t sh_a[32], sh_b[32], sh_t[32];
+  __shared__ uint32_t carry[3];
+  const int tid = threadIdx.x, lane = tid & 31, wv = tid >> 5;
+  if (tid < 3) carry[tid] = 0;
+  __syncthreads();
+  for (int base = 0; base < A.n_nodes; base += 1024) {
+    const int gi = base + tid;
+    uint32_t dec = 0, tiles = 0, len = 0;
+    int best = -1;
+    if (gi < A.n_nodes) {
+      const ScanResult* r0 = A.results + (size_t)gi * A.n_chunks;
+      for (int ch = 0; ch < A.n_chunks; ch++) {        // first maximum in subset order
+        if (r0[ch].k < 0) continue;
+        if (best < 0 || r0[ch].gain > r0[best].gain) best = ch;
+      }
+      const ScanResult& r = r0[best < 0 ? 0 : best];
+      const uint32_t info = A.node_info[gi];
+      const int level = (int)(info & 0xffu);
+      const bool valid = best >= 0 && r.valid;
+      const double gain = valid ? r.gain : kInvalidGain;
+      const bool is_leaf = (gain <= 0) || (level == A.max_depth);
+      dec = (uint32_t)(best < 0 ? 0 : best) | (valid ? kDecValid : 0u);
+      if (!is_leaf) {
+        const bool child_leaf = (level + 1) == A.max_depth;
+        const bool l_leaf = child_leaf || (r.left_impurity == 0.0);
+        const bool r_leaf = child_leaf || (r.right_impurity == 0.0);
+        dec |= kDecNonLeaf | (l_leaf ? kDecLLeaf : 0u) | (r_leaf ? kDecRLeaf : 0u);
+        if ((!l_leaf || !r_leaf) && (info & kInfoMine)) {
+          dec |= kDecSplit;
+          len = A.segtab[A.nodes[gi].seg_slot].len;
+          tiles = (len + kPartTile - 1) / kPartTile;
+        }
+      }
+      A.out_dec[gi] = dec;
+    }
+    // block-wide exclusive scans of (non-leaf, split, tiles)
+    uint32_t a = (dec & kDecNonLeaf) ? 1u : 0u, b = (dec & kDecSplit) ? 1u : 0u, t = tiles;
+    uint32_t ia = a, ib = b, it = t;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t xa = __shfl_up_sync(0xffffffffu, ia, o), xb = __shfl_up_sync(0xffffffffu, ib, o),
+                     xt = __shfl_up_sync(0xffffffffu, it, o);
+      if (lane >= o) { ia += xa; ib += xb; it += xt; }
+    }
+    if (lane == 31) { sh_a[wv] = ia; sh_b[wv] = ib; sh_t[wv] = it; }
+    __syncthreads();
+    if (wv == 0) {
+      uint32_t va = sh_a[lane], vb = sh_b[lane], vt = sh_t[lane];
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t xa = __shfl_up_sync(0xffffffffu, va, o), xb = __shfl_up_sync(0xffffffffu, vb, o),
+                       xt = __shfl_up_sync(0xffffffffu, vt, o);
+        if (lane >= o) { va += xa; vb += xb; vt += xt; }
+      }
+      sh_a[lane] = va; sh_b[lane] = vb; sh_t[lane] = vt;   // inclusive over warps
+    }
+    __syncthreads();
+    const uint32_t wa = wv ? sh_a[wv - 1] : 0u, wb = wv ? sh_b[wv - 1] : 0u, wt = wv ? sh_t[wv - 1] : 0u;
+    const uint32_t ea = carry[0] + wa + ia - a, eb = carry[1] + wb + ib - b, et = carry[2] + wt + it - t;
+    if (dec & kDecSplit) {
+      const ScanResult& r = A.results[(size_t)gi * A.n_chunks + (dec & 0xffu)];
+      SplitNode sn;
+      sn.seg_start = 0; sn.seg_len = len; sn.buf = 0;       // the kernels take the segment from the table
+      sn.tile_begin = et; sn.n_tiles = tiles;
+      sn.feature = A.node_feat[(size_t)gi * A.f_sub + r.k]; sn.split_bin = r.split;
+      sn.seg_slot = A.nodes[gi].seg_slot; sn.left_slot = A.next_slot + 2 * ea; sn.right_slot = sn.left_slot + 1; sn.pad = 0;
+      A.out_splits[eb] = sn;
+      for (uint32_t q = 0; q < tiles; q++) A.out_tile_node[et + q] = eb;
+    }
+    __syncthreads();
+    if (tid == 1023) { carry[0] = ea + a; carry[1] = eb + b; carry[2] = et + t; }
+    __syncthreads();
+  }
+  if (tid == 0) { A.out_limits[0] = carry[1]; A.out_limits[1] = carry[2]; }
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -268,7 +268,9 @@ def main():
         "e2e": {"value": units / (e2e_ms / 1e3), "unit": UNIT,
                 "h2d_bytes_per_step": int(np.mean([t["h2d_bytes"] for t in e2e_tm])),
                 "d2h_bytes_per_step": int(np.mean([t["d2h_bytes"] for t in e2e_tm])),
-                "ms_per_step": e2e_ms / args.steps, "ms_each_step": e2e_each},
+                "ms_per_step": e2e_ms / args.steps, "ms_each_step": e2e_each,
+                "phases_ms_per_step": {k: round(float(np.mean([t[k] for t in e2e_tm])), 3) for k in (
+                    "total_ms", "h2d_ms", "find_splits_ms", "bin_ms", "bag_ms", "hist_kernel_ms", "partition_ms")}},
         "gpu_launches": int(np.sum([t["kernel_launches"] for t in tms])),
         "roofline": {"bound": "hbm", "kernel": "hist_scan_kernel (DTStatsAggregator update + binsToBestSplit)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,

@@ -206,6 +206,7 @@ struct HNode {
   double threshold = 0.0, gain = std::numeric_limits<double>::quiet_NaN(), impurity = 0.0;
   uint32_t slot = 0;   // index of the node's entry segment in the device segment table
   uint32_t ub = 0;     // upper bound on the segment's length (exact for roots and when rows are sharded)
+  uint32_t weight = 0xffffffffu;   // sum of the node's class counts (roots: an upper bound)
   // class counts = cnt_a[c] - (cnt_b ? cnt_b[c] : 0); both point into the fit's result arena (the
   // split records copied back from the device): a left child shares its parent's "left" array, a
   // right child is parent total minus parent left, a node that went through a group owns its totals.
@@ -245,6 +246,7 @@ struct emrf_ctx {
   int rank = 0, world = 1;
   cudaStream_t stream = nullptr;
   cudaStream_t stream2 = nullptr;   // bagging runs here, underneath input copy / findSplits / binning
+  cudaStream_t stream3 = nullptr;   // chunked host -> device copy of the feature matrix (binning follows chunk by chunk)
   int sm_count = 148;
   int host_threads = 1;   // OpenMP threads for the host scheduler's parallel pieces (cores / ranks on this node)
   size_t smem_optin = 0;
@@ -256,7 +258,7 @@ struct emrf_ctx {
   void* nccl_comm = nullptr;
   // grow-only scratch reused across groups
   DevBuf d_group, d_results, d_ghist, d_tickets;
-  PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum;
+  PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum, h_sample;
   DevBuf d_split, d_part;   // partition work of the current group (written by decide_kernel)
   std::vector<HTree> tree_pools;   // LearningNode pools of the last fit (memory reused by the next)
   DevBuf d_seeds, d_table, d_tsum;
@@ -310,6 +312,7 @@ static int ctx_init(emrf_ctx* c, int device) {
   c->smem_optin = prop.sharedMemPerBlockOptin;
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking));
   memset(&c->tm, 0, sizeof(c->tm));
   c->host_threads = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
   return EMRF_OK;
@@ -385,6 +388,7 @@ extern "C" void emrf_ctx_destroy(emrf_ctx_t* c) {
   }
   if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
   if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
+  if (c->stream3) { cudaStreamSynchronize(c->stream3); cudaStreamDestroy(c->stream3); }
   const int dev = c->device;
   delete c;
   DevCache::get().trim(dev);
@@ -549,9 +553,15 @@ static int stage_input(emrf_ctx* c, const void* src_hd, size_t bytes, DevBuf& ow
 // ---------------------------------------------------------------------------------------------
 // findSplits on the device
 // ---------------------------------------------------------------------------------------------
+// A feature matrix that is still on its way to the device: findSplits then takes its (few) sampled rows from
+// the host copy instead of waiting for the transfer; `ready` fires when the whole matrix has arrived.
+struct HostX {
+  const double* h;
+  cudaEvent_t ready;
+};
 static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX, int64_t N_local, int F, const int64_t* part_off_local,
                            int n_parts_local, DevBuf& d_thr, DevBuf& d_ns, std::vector<double>& h_thr, std::vector<int>& h_ns,
-                           const ShardSpec* sh = nullptr, std::vector<DevBuf>* keep = nullptr) {
+                           const ShardSpec* sh = nullptr, std::vector<DevBuf>* keep = nullptr, const HostX* hx = nullptr) {
   // `keep`: where temporaries are parked instead of being freed here — cudaFree synchronises the whole
   // device and would stall this stream behind the bagging kernel running on the other one.
   // metadata and sampling are defined on the WHOLE dataset
@@ -581,15 +591,36 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
       int n_pad = 2;
       while (n_pad < n_s) n_pad <<= 1;
       DevBuf d_rows, d_S;
-      if (sampled) {
+      if (sampled && !hx) {
         CU(d_rows.alloc((size_t)n_s * 8));
         CU(cudaMemcpyAsync(d_rows.p, rows.data(), (size_t)n_s * 8, cudaMemcpyHostToDevice, c->stream));
       }
       CU(d_S.alloc((size_t)F * n_pad * 8));
       const int64_t total = (int64_t)n_pad * F;
+      // rows gathered on the host (matrix still in flight) into a pinned, device-mapped block that the gather
+      // kernel reads straight over PCIe: a copy would queue behind the matrix chunks in the copy engine
+      const double* d_comp = nullptr;
+      auto host_gather = [&](const int64_t* local_rows, int n) -> int {
+        CU(c->h_sample.ensure((size_t)std::max(n, 1) * F * 8));
+        double* hb = c->h_sample.as<double>();
+#pragma omp parallel for num_threads(c->host_threads) schedule(static)
+        for (int j = 0; j < n; j++) memcpy(hb + (size_t)j * F, hx->h + (size_t)local_rows[j] * F, (size_t)F * 8);
+        void* dp = nullptr;
+        CU(cudaHostGetDevicePointer(&dp, hb, 0));
+        d_comp = (const double*)dp;
+        c->tm.h2d_bytes += (int64_t)n * F * 8;
+        return EMRF_OK;
+      };
       if (!sh) {
-        kern::fs_gather_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(
-            dX, F, d_rows.as<int64_t>(), n_s, n_pad, sampled ? 0 : 1, P.find_splits_policy == 0 ? 1 : 0, d_S.as<double>());
+        if (hx && sampled) {
+          TRY(host_gather(rows.data(), n_s));
+          kern::fs_gather_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(
+              d_comp, F, nullptr, n_s, n_pad, 1, P.find_splits_policy == 0 ? 1 : 0, d_S.as<double>());
+        } else {
+          if (hx) CU(cudaStreamWaitEvent(c->stream, hx->ready, 0));   // every row is a sample: the whole matrix is needed
+          kern::fs_gather_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(
+              dX, F, d_rows.as<int64_t>(), n_s, n_pad, sampled ? 0 : 1, P.find_splits_policy == 0 ? 1 : 0, d_S.as<double>());
+        }
       } else {
         // own samples → global sample positions, all-reduce the bit patterns, then mark sentinels
         std::vector<int64_t> own_rows;
@@ -602,6 +633,14 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
           for (int64_t r = lo; r < hi; r++) { own_rows.push_back(r - lo); own_pos.push_back((int32_t)r); }
         }
         const int n_own = (int)own_rows.size();
+        const double* gX = dX;
+        if (hx && sampled) {
+          TRY(host_gather(own_rows.data(), n_own));
+          for (int j = 0; j < n_own; j++) own_rows[j] = j;
+          gX = d_comp;
+        } else if (hx) {
+          CU(cudaStreamWaitEvent(c->stream, hx->ready, 0));
+        }
         DevBuf d_or, d_op;
         CU(d_or.alloc((size_t)n_own * 8));
         CU(d_op.alloc((size_t)n_own * 4));
@@ -610,7 +649,7 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
         CU(cudaMemsetAsync(d_S.p, 0, (size_t)F * n_pad * 8, c->stream));
         if (n_own)
           kern::fs_gather_sharded_kernel<<<(unsigned)(((int64_t)n_own * F + 255) / 256), 256, 0, c->stream>>>(
-              dX, F, d_or.as<int64_t>(), d_op.as<int32_t>(), n_own, n_pad, d_S.as<double>());
+              gX, F, d_or.as<int64_t>(), d_op.as<int32_t>(), n_own, n_pad, d_S.as<double>());
         const double t_ar0 = now_ms();
         if (env_flag("EMRF_DEBUG_TIMERS")) CU(cudaStreamSynchronize(c->stream));
         const double t_ar1 = now_ms();
@@ -725,27 +764,25 @@ static int run_bag(emrf_ctx* c, const emrf_params_t& P, int64_t N, const int64_t
 // ---------------------------------------------------------------------------------------------
 // histogram kernel dispatch (template on 16 B chunks per TreePoint row)
 // ---------------------------------------------------------------------------------------------
-template <int CH>
+template <int CH, class HT>
 static cudaError_t hist_launch_t(dim3 grid, size_t smem, cudaStream_t st, const kern::HistArgs& A, bool prepare_only) {
   if (prepare_only)
-    return cudaFuncSetAttribute(kern::hist_scan_kernel<CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  kern::hist_scan_kernel<CH><<<grid, kern::kHistThreads, smem, st>>>(A);
+    return cudaFuncSetAttribute(kern::hist_scan_kernel<CH, HT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  kern::hist_scan_kernel<CH, HT><<<grid, kern::kHistThreads, smem, st>>>(A);
   return cudaGetLastError();
 }
-static cudaError_t hist_launch(int ch, dim3 grid, size_t smem, cudaStream_t st, const kern::HistArgs& A, bool prepare_only) {
+// u16: 16-bit shared-memory counters (launches whose nodes are all single-tile and weigh <= 65535)
+static cudaError_t hist_launch(int ch, dim3 grid, size_t smem, cudaStream_t st, const kern::HistArgs& A, bool prepare_only,
+                               bool u16 = false) {
+#define EMRF_HIST_CASE(n) \
+  case n: return u16 ? hist_launch_t<n, uint16_t>(grid, smem, st, A, prepare_only) : hist_launch_t<n, uint32_t>(grid, smem, st, A, prepare_only);
   switch (ch) {
-    case 1: return hist_launch_t<1>(grid, smem, st, A, prepare_only);
-    case 2: return hist_launch_t<2>(grid, smem, st, A, prepare_only);
-    case 3: return hist_launch_t<3>(grid, smem, st, A, prepare_only);
-    case 4: return hist_launch_t<4>(grid, smem, st, A, prepare_only);
-    case 5: return hist_launch_t<5>(grid, smem, st, A, prepare_only);
-    case 6: return hist_launch_t<6>(grid, smem, st, A, prepare_only);
-    case 7: return hist_launch_t<7>(grid, smem, st, A, prepare_only);
-    case 8: return hist_launch_t<8>(grid, smem, st, A, prepare_only);
-    default: return hist_launch_t<0>(grid, smem, st, A, prepare_only);
+    EMRF_HIST_CASE(1) EMRF_HIST_CASE(2) EMRF_HIST_CASE(3) EMRF_HIST_CASE(4)
+    EMRF_HIST_CASE(5) EMRF_HIST_CASE(6) EMRF_HIST_CASE(7) EMRF_HIST_CASE(8)
+    default: return u16 ? hist_launch_t<0, uint16_t>(grid, smem, st, A, prepare_only) : hist_launch_t<0, uint32_t>(grid, smem, st, A, prepare_only);
   }
+#undef EMRF_HIST_CASE
 }
-// features per CTA so that the [k][B][C] uint32 histogram plus the row tiles fit in shared memory
 static int hist_geometry(emrf_ctx* c, int Fp, int f_sub, int B, int C, int* ch_out, int* k_chunk_out, int* n_chunks_out,
                          size_t* hist_bytes_out, size_t* smem_out) {
   const int ch = kern::hist_row_chunks(Fp);
@@ -975,8 +1012,35 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   const void* dXv = nullptr;
   const void* dyv = nullptr;
   bool copied = false;
-  TRY(stage_input(c, features_hd, (size_t)N * F * 8, own_X, &dXv, &copied));
-  TRY(stage_input(c, labels_hd, (size_t)N * 8, own_y, &dyv, nullptr));
+  // A host-resident feature matrix crosses PCIe in chunks on its own stream: findSplits works from the sampled
+  // rows (gathered on the host) and the TreePoint conversion follows the copy chunk by chunk, so that by the
+  // time the last chunk lands only its own binning is left.  Bagging runs under all of it on stream2.
+  struct XChunk { int64_t r0, rows; cudaEvent_t ev; };
+  std::vector<XChunk> x_chunks;
+  HostX hostx{nullptr, nullptr};
+  TRY(stage_input(c, labels_hd, (size_t)N * 8, own_y, &dyv, nullptr));   // first: copies leave in issue order
+  if (!is_device_ptr(features_hd)) {
+    CU(own_X.ensure_exact((size_t)N * F * 8));
+    cudaEvent_t ev_x0 = c->events.get();
+    CU(cudaEventRecord(ev_x0, st));                       // the pool buffer may still be read by work queued on st
+    CU(cudaStreamWaitEvent(c->stream3, ev_x0, 0));
+    const int64_t per = (int64_t)align_up((size_t)((N + 11) / 12), 128);
+    for (int64_t r0 = 0; r0 < N; r0 += per) {
+      const int64_t rows = std::min(per, N - r0);
+      CU(cudaMemcpyAsync((char*)own_X.p + (size_t)r0 * F * 8, (const char*)features_hd + (size_t)r0 * F * 8, (size_t)rows * F * 8,
+                         cudaMemcpyHostToDevice, c->stream3));
+      cudaEvent_t e = c->events.get();
+      CU(cudaEventRecord(e, c->stream3));
+      x_chunks.push_back({r0, rows, e});
+    }
+    tm.h2d_bytes += (int64_t)N * F * 8;
+    dXv = own_X.p;
+    copied = true;
+    hostx.h = features_hd;
+    hostx.ready = x_chunks.back().ev;
+  } else {
+    dXv = features_hd;
+  }
   const double* dX = (const double*)dXv;
   const double* dy = (const double*)dyv;
   CU(cudaEventRecord(ev_in, st));
@@ -1008,7 +1072,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   std::vector<double> h_thr;
   std::vector<int> h_ns;
   std::vector<DevBuf> parked;   // temporaries released once nothing overlaps any more
-  TRY(run_find_splits(c, P, dX, N, F, part_off, n_parts, d_thr, d_ns, h_thr, h_ns, sh, &parked));
+  TRY(run_find_splits(c, P, dX, N, F, part_off, n_parts, d_thr, d_ns, h_thr, h_ns, sh, &parked, copied ? &hostx : nullptr));
   CU(cudaEventRecord(ev_fs, st));
   const int TS = P.max_bins;
   std::vector<int> num_bins(F);
@@ -1016,7 +1080,6 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   for (int f = 0; f < F; f++) { num_bins[f] = h_ns[f] + 1; B = std::max(B, num_bins[f]); }
   DevBuf d_num_bins;
   CU(d_num_bins.alloc((size_t)F * 4));
-  CU(cudaMemcpyAsync(d_num_bins.p, num_bins.data(), (size_t)F * 4, cudaMemcpyHostToDevice, st));
 
   // ---- TreePoint matrices
   const int Fp = (int)align_up(F, 16);
@@ -1024,18 +1087,29 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   DevBuf &d_rm = c->p_rm, &d_cm = c->p_cm;
   CU(d_rm.ensure_exact((size_t)Np * Fp));
   CU(d_cm.ensure_exact((size_t)F * Np));
-  TRY(run_bin(c, dX, N, F, d_thr.as<double>(), d_ns.as<int>(), TS, Fp, Np, d_rm.as<uint8_t>(), d_cm.as<uint8_t>()));
+  if (x_chunks.empty()) {
+    TRY(run_bin(c, dX, N, F, d_thr.as<double>(), d_ns.as<int>(), TS, Fp, Np, d_rm.as<uint8_t>(), d_cm.as<uint8_t>()));
+  } else {
+    for (const XChunk& xc : x_chunks) {   // chunk starts are multiples of 128 rows (the binning tile)
+      CU(cudaStreamWaitEvent(st, xc.ev, 0));
+      TRY(run_bin(c, dX + (size_t)xc.r0 * F, xc.rows, F, d_thr.as<double>(), d_ns.as<int>(), TS, Fp, Np,
+                  d_rm.as<uint8_t>() + (size_t)xc.r0 * Fp, d_cm.as<uint8_t>() + xc.r0));
+    }
+  }
   CU(cudaEventRecord(ev_bin, st));
+  CU(cudaMemcpyAsync(d_num_bins.p, num_bins.data(), (size_t)F * 4, cudaMemcpyHostToDevice, st));   // behind the matrix chunks
 
   // ---- BaggedPoint weights → per-tree entry lists
   // tree-sharded multi-GPU: every rank schedules all trees, but only builds lists (and
   // histograms) for trees t % world == rank.
   DevBuf* d_ent[2] = {&c->p_ent0, &c->p_ent1};
+  int bag_maxw = 255;
   std::vector<uint64_t> tree_base(T + 1, 0), tree_total(T, 0);
   {
     int maxw = 0;
     CU(cudaStreamWaitEvent(st, ev_b1, 0));
     TRY(bag_finish(c, st, P, bag_job, &maxw));
+    bag_maxw = maxw;
     const int n_tiles = (int)((N + kern::kListTile - 1) / kern::kListTile);
     DevBuf& d_counts = c->p_counts;
     DevBuf d_totals, d_base;
@@ -1069,6 +1143,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   size_t hist_bytes, hist_smem;
   TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &hist_smem));
   CU(hist_launch(row_ch, dim3(1), hist_smem, st, kern::HistArgs(), true));
+  // 16-bit counters for launches of small single-tile nodes (EMRF_HIST_U32=1 turns them off)
+  const size_t hist_bytes16 = kern::hist_smem_bytes(k_chunk, B, C, 2);
+  const size_t hist_smem16 = hist_bytes16 + (hist_smem - hist_bytes);
+  const bool allow_u16 = !row_sharded && !env_flag("EMRF_HIST_U32");
+  if (allow_u16) CU(hist_launch(row_ch, dim3(1), hist_smem16, st, kern::HistArgs(), true, true));
   if (row_sharded) CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
   const size_t slot_words = (size_t)f_sub * B * C;
   // L2 blocking of the row gathers (shapes whose row-major TreePoint matrix does not fit L2, e.g. configs[2]);
@@ -1113,6 +1192,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     HNode& r = trees[t].pool[0];
     r.slot = (uint32_t)t;
     r.ub = (uint32_t)tree_total[t];
+    r.weight = (uint32_t)std::min<uint64_t>(tree_total[t] * (uint64_t)std::max(bag_maxw, 1), 0xffffffffull);   // upper bound
   }
   // device segment table: roots now, children written by the partition kernels
   size_t seg_cap = std::max<size_t>((size_t)1 << 18, (size_t)4 * T);
@@ -1271,9 +1351,14 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
 
     // ---- tiles (tree-sharded multi-GPU: own trees only); sizes are upper bounds
     uint64_t total_entries = 0;
-#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : total_entries)
+    uint32_t max_weight = 0;
+#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : total_entries) reduction(max : max_weight)
     for (int i = 0; i < n_nodes; i++)
-      if (mine(group[i].tree)) total_entries += trees[group[i].tree].pool[group[i].pool].ub;
+      if (mine(group[i].tree)) {
+        const HNode& hn = trees[group[i].tree].pool[group[i].pool];
+        total_entries += hn.ub;
+        max_weight = std::max(max_weight, hn.weight);
+      }
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
     // TreePoint matrix larger than L2: many small tiles, launched in row-range order (below), so that the
@@ -1400,7 +1485,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.tickets = c->d_tickets.as<uint32_t>();
     A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
     A.tile_len = tile_len;
-    A.tile_smem_off = (uint32_t)hist_bytes;
+    // every node in one tile and light enough: 16-bit counters, more CTAs per SM
+    const bool u16 = allow_u16 && n_slots == 0 && max_weight <= 65535u;
+    if (env_flag("EMRF_DEBUG_GROUPS"))
+      fprintf(stderr, "[emrf] group %zu: nodes %d tiles %u slots %d max_weight %u tile_len %u u16 %d\n", fo->group_sizes.size(), n_nodes,
+              n_tiles, n_slots, max_weight, tile_len, (int)u16);
+    A.tile_smem_off = (uint32_t)(u16 ? hist_bytes16 : hist_bytes);
     A.impurity = P.impurity; A.min_instances = P.min_instances_per_node; A.hist_only = row_sharded ? 1 : 0;
     A.push_world = push_mode ? c->world : 0; A.push_rank = c->rank; A.push_npr = nodes_per_rank;
     for (int r = 0; r < 8; r++) A.peer_stage[r] = (uint32_t*)c->peer_stage[r];
@@ -1414,7 +1504,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
       CU(cudaEventRecord(e0, st));
       if (n_tiles) {
-        CU(hist_launch(row_ch, dim3(n_tiles, n_chunks), hist_smem, st, A, false));
+        CU(hist_launch(row_ch, dim3(n_tiles, n_chunks), u16 ? hist_smem16 : hist_smem, st, A, false, u16));
         tm.kernel_launches++;
         tm.hist_launches++;
       }
@@ -1609,6 +1699,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       l.slot = u.slot_l; rn.slot = u.slot_l + 1;
       l.ub = std::min(n.ub, r.left_weight);
       rn.ub = std::min(n.ub, r.total_weight - r.left_weight);
+      l.weight = r.left_weight;
+      rn.weight = r.total_weight - r.left_weight;
       n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
       n.left = li; n.right = li + 1;
       decisions[gi] = Decision{li, l_leaf, r_leaf};
@@ -1676,7 +1768,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
 
   float ms = 0;
   CU(cudaEventElapsedTime(&ms, ev_start, ev_end)); tm.total_ms = ms;
-  CU(cudaEventElapsedTime(&ms, ev_start, ev_in)); tm.h2d_ms = copied ? ms : 0.0;
+  tm.h2d_ms = 0.0;   // host-resident features: until the last chunk has landed (findSplits and binning run underneath)
+  if (copied) { CU(cudaEventElapsedTime(&ms, ev_start, x_chunks.back().ev)); tm.h2d_ms = ms; }
   CU(cudaEventElapsedTime(&ms, ev_in, ev_fs)); tm.find_splits_ms = ms;
   CU(cudaEventElapsedTime(&ms, ev_fs, ev_bin)); tm.bin_ms = ms;
   CU(cudaEventElapsedTime(&ms, ev_bin, ev_bag)); tm.bag_ms = ms;   // wait for the bag kernel (if still running) + list building

@@ -660,7 +660,8 @@ __device__ __forceinline__ double div_by(double a, double b, double y) {
 }
 // Impurity of the class-count vector v[c] = (sub ? sub[c] - cnt[c] : cnt[c]); total_u = sum v.
 // Gini: 1 - sum f^2 accumulated in class order; Entropy: -sum f*log2(f) over non-zero classes.
-__device__ __forceinline__ double impurity_dev(int kind, const uint32_t* cnt, const uint32_t* sub, int C,
+template <class HT>
+__device__ __forceinline__ double impurity_dev(int kind, const HT* cnt, const uint32_t* sub, int C,
                                                uint32_t total_u) {
   if (total_u == 0) return 0.0;
   const double total = (double)total_u;
@@ -687,9 +688,12 @@ __device__ __forceinline__ double impurity_dev(int kind, const uint32_t* cnt, co
   return imp;
 }
 
-// Shared-memory carve-up used by hist_scan_kernel and scan_kernel.
+// Shared-memory carve-up used by hist_scan_kernel and scan_kernel.  HT is the counter type: uint32_t, or
+// uint16_t for launches whose every node is accumulated by ONE CTA and weighs at most 65535 (no counter, and
+// no prefix sum over bins, can then exceed 16 bits): half the histogram memory, so more CTAs per SM.
+template <class HT>
 struct ScanSmem {
-  uint32_t* hist;      // [k_chunk][B][C]
+  HT* hist;            // [k_chunk][B][C]
   uint32_t* tot;       // [256]
   double* sq;          // [256]
   double* red_gain;    // [8]
@@ -698,13 +702,14 @@ struct ScanSmem {
   int* feat;           // [k_chunk]
   int* nb;             // [k_chunk]
 };
-__host__ __device__ inline size_t scan_hist_words(int k_chunk, int B, int C) {
-  return ((size_t)k_chunk * B * C + 1) & ~(size_t)1;
+__host__ __device__ inline size_t scan_hist_bytes(int k_chunk, int B, int C, int elem) {
+  return ((size_t)k_chunk * B * C * elem + 15) & ~(size_t)15;
 }
-__device__ __forceinline__ ScanSmem carve_smem(uint8_t* raw, int k_chunk, int B, int C) {
-  ScanSmem s;
-  s.hist = reinterpret_cast<uint32_t*>(raw);
-  s.tot = s.hist + scan_hist_words(k_chunk, B, C);
+template <class HT>
+__device__ __forceinline__ ScanSmem<HT> carve_smem(uint8_t* raw, int k_chunk, int B, int C) {
+  ScanSmem<HT> s;
+  s.hist = reinterpret_cast<HT*>(raw);
+  s.tot = reinterpret_cast<uint32_t*>(raw + scan_hist_bytes(k_chunk, B, C, (int)sizeof(HT)));
   s.sq = reinterpret_cast<double*>(s.tot + 256);
   s.red_gain = s.sq + 256;
   s.pimp = s.red_gain + 8;
@@ -713,8 +718,8 @@ __device__ __forceinline__ ScanSmem carve_smem(uint8_t* raw, int k_chunk, int B,
   s.nb = s.feat + k_chunk;
   return s;
 }
-inline size_t hist_smem_bytes(int k_chunk, int B, int C) {
-  return (scan_hist_words(k_chunk, B, C) * 4 + 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + (size_t)k_chunk * 8 + 16 + 15) & ~(size_t)15;
+inline size_t hist_smem_bytes(int k_chunk, int B, int C, int elem = 4) {
+  return (scan_hist_bytes(k_chunk, B, C, elem) + 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + (size_t)k_chunk * 8 + 16 + 15) & ~(size_t)15;
 }
 // chunks of 16 B per TreePoint row handled by the cooperative row loader (0 = generic byte gather)
 inline int hist_row_chunks(int Fp) { return (Fp / 16 <= 8) ? Fp / 16 : 0; }
@@ -743,18 +748,19 @@ __device__ __forceinline__ int warp_first_argmax(int C, int lane, F v) {
 
 // Scans a histogram chunk held in shared memory: hist[kc][B][C]; nb[k] = numBins of subset
 // feature k0+k.  All threads of the CTA participate; writes the chunk's result record.
-__device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int impurity, int min_instances,
+template <class HT>
+__device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, int impurity, int min_instances,
                            double min_info_gain, ScanResult* res, uint32_t* left_out, uint32_t* total_out) {
   const int tid = threadIdx.x, NT = blockDim.x;
-  uint32_t* sh = S.hist;
+  HT* sh = S.hist;
   const int* nb = S.nb;
   // (a) inclusive prefix sum over bins for every (feature, class) column — conflict-free
   for (int p = tid; p < kc * C; p += NT) {
     const int k = p / C, c = p - k * C;
-    uint32_t* col = sh + (size_t)k * B * C + c;
+    HT* col = sh + (size_t)k * B * C + c;
     uint32_t run = 0;
     const int n = nb[k];
-    for (int b = 0; b < n; b++) { run += col[b * C]; col[b * C] = run; }
+    for (int b = 0; b < n; b++) { run += col[b * C]; col[b * C] = (HT)run; }
   }
   __syncthreads();
   // (b) node totals = last bin of the chunk's first feature (every feature sums to the same)
@@ -792,7 +798,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
   for (int cand = tid; cand < n_cand; cand += NT) {
     const int k = cand / (B - 1), s = cand - k * (B - 1);
     if (s >= nb[k] - 1) continue;
-    const uint32_t* l = sh + ((size_t)k * B + s) * C;
+    const HT* l = sh + ((size_t)k * B + s) * C;
     uint32_t lc = 0;
     for (int c = 0; c < C; c++) lc += l[c];
     const uint32_t rc = tot_all - lc;
@@ -815,8 +821,8 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
         }
         li = il; ri = ir;
       } else {
-        li = impurity_dev(impurity, l, nullptr, C, lc);
-        ri = impurity_dev(impurity, l, S.tot, C, rc);
+        li = impurity_dev<HT>(impurity, l, nullptr, C, lc);
+        ri = impurity_dev<HT>(impurity, l, S.tot, C, rc);
       }
       const double tc = (double)tot_all;  // (leftCount + rightCount).toDouble
       const double lw = __ddiv_rn((double)lc, tc);
@@ -865,7 +871,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
     const int k = ix / (B - 1), s = ix - k * (B - 1);
     if (tid == 0) { res->gain = g; res->impurity = pimp; res->k = k0 + k; res->split = s; res->valid = (g != kInvalidGain); res->total_weight = tot_all; }
     if (tid < 96) {   // three warps: predictions of the node, its left and its right child
-      const uint32_t* lw = sh + ((size_t)k * B + s) * C;
+      const HT* lw = sh + ((size_t)k * B + s) * C;
       const int which = tid >> 5, ln = tid & 31;
       const int p = which == 0 ? warp_first_argmax(C, ln, [&](int c) { return S.tot[c]; })
                   : which == 1 ? warp_first_argmax(C, ln, [&](int c) { return lw[c]; })
@@ -873,7 +879,7 @@ __device__ void scan_chunk(const ScanSmem& S, int kc, int k0, int B, int C, int 
       if (ln == 0) { if (which == 0) res->pred = p; else if (which == 1) res->left_pred = p; else res->right_pred = p; }
     }
     if (my_idx == ix) { res->left_impurity = best_li; res->right_impurity = best_ri; res->left_weight = best_lc; }  // the owner of the winner
-    const uint32_t* l = sh + ((size_t)k * B + s) * C;
+    const HT* l = sh + ((size_t)k * B + s) * C;
     for (int c = tid; c < C; c += NT) { left_out[c] = l[c]; total_out[c] = S.tot[c]; }
   }
 }
@@ -926,16 +932,18 @@ __device__ __forceinline__ uint64_t load_entry(const uint64_t* __restrict__ ent,
   return j < len ? __ldcs(ent + j) : 0ull;
 }
 
-template <int CH>
-__global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs A) {
+template <int CH, class HT = uint32_t>
+__global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_scan_kernel(const HistArgs A) {
+  constexpr bool U16 = sizeof(HT) == 2;
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int tid = threadIdx.x;
   const int chunk = blockIdx.y;
   const int k0 = chunk * A.k_chunk;
   const int kc = min(A.k_chunk, A.f_sub - k0);
   const int B = A.B, C = A.C;
-  const ScanSmem S = carve_smem(smem_raw, A.k_chunk, B, C);
-  uint32_t* sh = S.hist;
+  const ScanSmem<HT> S = carve_smem<HT>(smem_raw, A.k_chunk, B, C);
+  HT* sh = S.hist;
+  uint32_t* shw = reinterpret_cast<uint32_t*>(S.hist);   // the counters as 32-bit words (two per word when U16)
   int* sh_feat = S.feat;
   int* sh_nb = S.nb;
   __shared__ int sh_last;
@@ -953,10 +961,16 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
     sh_feat[k] = f;
     sh_nb[k] = A.num_bins_all[f];
   }
-  for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = 0;
+  for (int i = tid; i < (kc * B * C * (int)sizeof(HT) + 3) / 4; i += kHistThreads) shw[i] = 0;
   __syncthreads();
 
   // ---- accumulate this tile
+  // counter idx gets += w: a 32-bit shared atomic either way (U16: on the word holding the pair, no carry can
+  // cross into the upper half because every counter stays <= 65535)
+  auto hist_add = [&](uint32_t idx, uint32_t w) {
+    if (U16) atomicAdd(shw + (idx >> 1), w << ((idx & 1u) << 4));
+    else atomicAdd(shw + idx, w);
+  };
   const uint64_t* ent = (nd.buf ? A.ent1 : A.ent0) + nd.seg_start + (uint64_t)tile_in_node * A.tile_len;
   const uint64_t tile_first = (uint64_t)tile_in_node * A.tile_len;
   const uint32_t len = tile_first < nd.seg_len ? (uint32_t)min((uint64_t)A.tile_len, nd.seg_len - tile_first) : 0u;
@@ -972,7 +986,7 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
       const uint8_t* rp = bins + (size_t)row * Fp;
       for (int k = 0; k < kc; k++) {
         const uint32_t b = rp[sh_feat[k]];
-        atomicAdd(&sh[(k * B + b) * C + lab], w);
+        hist_add((uint32_t)((k * B + b) * C) + lab, w);
       }
     }
   } else {
@@ -1003,13 +1017,13 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
       const uint32_t w = (uint32_t)(e_cur >> 32) & 0xffu;
       const uint32_t lab = (uint32_t)(e_cur >> 40) & 0xffu;
       if (w) {
-        const int BC = B * C;
-        uint32_t* hl = sh + lab + part * BC;
+        const uint32_t BC = (uint32_t)(B * C);
+        uint32_t hl = lab + part * BC;
         const uint8_t* tb = tile_b + (rlane << 2);
 #pragma unroll 4
         for (int k = part; k < kc; k += SHARE) {
           const uint32_t bin = tb[sh_off[k]];            // byte offset of feature k inside the transposed tile
-          atomicAdd(hl + bin * C, w);
+          hist_add(hl + bin * C, w);
           hl += SHARE * BC;
         }
       }
@@ -1023,6 +1037,7 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
   const size_t slot_words = (size_t)A.f_sub * B * C;
   const size_t rec = (size_t)g * A.n_chunks + chunk;                   // tickets: absolute
   const size_t rrec = (size_t)(g - A.node_base) * A.n_chunks + chunk;    // result record: relative to the launch
+  if constexpr (!U16) {     // 16-bit launches hold single-tile nodes of one GPU only
   if (A.push_world) {
     // ---- fused histogram + reduce-scatter: this rank's partial histogram of node g is stored, dense and
     // coalesced, into slot [this rank][g's index on its owner] of the OWNER rank's staging buffer through
@@ -1065,8 +1080,9 @@ __global__ void __launch_bounds__(kHistThreads) hist_scan_kernel(const HistArgs 
     for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = __ldcg(&gh[i]);
     __syncthreads();
   }
-  scan_chunk(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rrec],
-             A.left_counts + rrec * C, A.total_counts + rrec * C);
+  }
+  scan_chunk<HT>(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rrec],
+                 A.left_counts + rrec * C, A.total_counts + rrec * C);
 }
 
 // K3 alone — binsToBestSplit on histograms already in HBM (stage entry point; also the scan used
@@ -1081,7 +1097,7 @@ __global__ void __launch_bounds__(kHistThreads) scan_kernel(const uint32_t* __re
   const int g = blockIdx.x, chunk = blockIdx.y;
   const int k0 = chunk * k_chunk;
   const int kc = min(k_chunk, f_sub - k0);
-  const ScanSmem S = carve_smem(smem_raw, k_chunk, B, C);
+  const ScanSmem<uint32_t> S = carve_smem<uint32_t>(smem_raw, k_chunk, B, C);
   uint32_t* sh = S.hist;
   int* sh_nb = S.nb;
   for (int k = tid; k < kc; k += kHistThreads) sh_nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
@@ -1089,8 +1105,8 @@ __global__ void __launch_bounds__(kHistThreads) scan_kernel(const uint32_t* __re
   for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = gh[i];
   __syncthreads();
   const size_t rec = (size_t)g * n_chunks + chunk;
-  scan_chunk(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,
-             total_counts + rec * C);
+  scan_chunk<uint32_t>(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,
+                       total_counts + rec * C);
 }
 
 // Owner-side scan of the push mode: node `node0 + blockIdx.x` of the group is summed over the `n_src`
@@ -1106,7 +1122,7 @@ __global__ void __launch_bounds__(kHistThreads) scan_sum_kernel(const uint32_t* 
   const int local = blockIdx.x, g = node0 + local, chunk = blockIdx.y;
   const int k0 = chunk * k_chunk;
   const int kc = min(k_chunk, f_sub - k0);
-  const ScanSmem S = carve_smem(smem_raw, k_chunk, B, C);
+  const ScanSmem<uint32_t> S = carve_smem<uint32_t>(smem_raw, k_chunk, B, C);
   uint32_t* sh = S.hist;
   for (int k = tid; k < kc; k += kHistThreads) S.nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
   const size_t slot_words = (size_t)f_sub * B * C;
@@ -1117,8 +1133,8 @@ __global__ void __launch_bounds__(kHistThreads) scan_sum_kernel(const uint32_t* 
   }
   __syncthreads();
   const size_t rec = (size_t)g * n_chunks + chunk;
-  scan_chunk(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,
-             total_counts + rec * C);
+  scan_chunk<uint32_t>(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,
+                       total_counts + rec * C);
 }
 
 // ---------------------------------------------------------------------------------------------

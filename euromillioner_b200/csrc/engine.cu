@@ -1117,8 +1117,16 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(d_totals.alloc((size_t)T * 8));
     CU(d_base.alloc((size_t)T * 8));
     const int bt = std::min(256, (int)align_up(T, 32));
-    kern::list_count_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), N, T, d_counts.as<uint32_t>());
-    kern::list_scan_kernel<<<(T + 127) / 128, 128, 0, st>>>(d_counts.as<uint32_t>(), n_tiles, T, d_totals.as<uint64_t>());
+    // slab of rows staged in shared memory by the tiled kernels (0: T too large, thread-per-tree kernels)
+    int slab_rows = (int)std::min<int64_t>(512, (48 * 1024 / T) / 32 * 32);
+    if (env_flag("EMRF_LIST_SIMPLE")) slab_rows = 0;
+    if (slab_rows >= 32) {
+      kern::list_count_tiled_kernel<<<n_tiles, 256, (size_t)slab_rows * T, st>>>(d_w.as<uint8_t>(), N, T, slab_rows, d_counts.as<uint32_t>());
+      kern::list_scan_warp_kernel<<<(T * 32 + 127) / 128, 128, 0, st>>>(d_counts.as<uint32_t>(), n_tiles, T, d_totals.as<uint64_t>());
+    } else {
+      kern::list_count_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), N, T, d_counts.as<uint32_t>());
+      kern::list_scan_kernel<<<(T + 127) / 128, 128, 0, st>>>(d_counts.as<uint32_t>(), n_tiles, T, d_totals.as<uint64_t>());
+    }
     tm.kernel_launches += 2;
     CU(cudaMemcpyAsync(tree_total.data(), d_totals.p, (size_t)T * 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -1126,8 +1134,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(d_ent[0]->ensure((size_t)tree_base[T] * 8));
     CU(d_ent[1]->ensure((size_t)tree_base[T] * 8));
     CU(cudaMemcpyAsync(d_base.p, tree_base.data(), (size_t)T * 8, cudaMemcpyHostToDevice, st));
-    kern::list_fill_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, d_counts.as<uint32_t>(),
-                                                   d_base.as<uint64_t>(), d_ent[0]->as<uint64_t>());
+    if (slab_rows >= 32)
+      kern::list_fill_tiled_kernel<<<n_tiles, 256, (size_t)slab_rows * T, st>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, slab_rows,
+                                                                              d_counts.as<uint32_t>(), d_base.as<uint64_t>(),
+                                                                              d_ent[0]->as<uint64_t>());
+    else
+      kern::list_fill_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, d_counts.as<uint32_t>(),
+                                                     d_base.as<uint64_t>(), d_ent[0]->as<uint64_t>());
     tm.kernel_launches += 1;
     CU(cudaGetLastError());
     CU(cudaEventRecord(ev_bag, st));
@@ -2501,3 +2514,15 @@ extern "C" int emrf_build_lag_features(emrf_ctx_t* c, const int32_t* draws, int3
   CU(cudaStreamSynchronize(st));
   return EMRF_OK;
 }
+
+#ifdef EMRF_HIST_PROF
+// debug builds only (make prof): read and clear the histogram kernel's phase counters
+extern "C" int emrf_debug_hist_prof(unsigned long long* out16) {
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpyFromSymbol(out16, kern::g_hist_prof, sizeof(unsigned long long) * 16));
+  unsigned long long z[16] = {0};
+  CU(cudaMemcpyToSymbol(kern::g_hist_prof, z, sizeof(z)));
+  return EMRF_OK;
+}
+#endif
+

@@ -539,6 +539,109 @@ __global__ void reservoir_table_kernel(const int64_t* __restrict__ seeds, int n_
 //   list_fill_kernel  : writes packed entries at tree_base[t] + tile_off[tile][t] + rank
 // Thread = tree, so weight reads are coalesced along T.
 // ---------------------------------------------------------------------------------------------
+// Tiled variants (used while a slab of 32..512 rows x T weights fits 48 KB of shared memory): the CTA copies
+// the slab with coalesced 128-bit loads, then each WARP takes whole trees — its lanes walk 32 consecutive
+// rows of one tree (conflict-free column reads for odd T/4 strides, any T is correct), a ballot ranks the
+// in-bag rows and the entries leave as one contiguous run per step (coalesced 8-byte stores) instead of one
+// scattered store per thread.  Same (tile, tree) counts layout as the simple kernels.
+__device__ __forceinline__ void list_load_slab(const uint8_t* __restrict__ src, size_t bytes, uint8_t* dst) {
+  const size_t n16 = bytes / 16;     // slabs start at multiples of 512 rows: 16-byte aligned for any T
+  const uint4* s4 = reinterpret_cast<const uint4*>(src);
+  uint4* d4 = reinterpret_cast<uint4*>(dst);
+  for (size_t i = threadIdx.x; i < n16; i += blockDim.x) d4[i] = __ldcs(s4 + i);
+  for (size_t i = n16 * 16 + threadIdx.x; i < bytes; i += blockDim.x) dst[i] = src[i];
+}
+__global__ void __launch_bounds__(256) list_count_tiled_kernel(const uint8_t* __restrict__ w, int64_t n_rows, int T,
+                                                               int slab_rows, uint32_t* __restrict__ counts) {
+  extern __shared__ __align__(16) uint8_t slab[];
+  const int64_t t0 = (int64_t)blockIdx.x * kListTile;
+  const int tile_rows = (int)min((int64_t)kListTile, n_rows - t0);
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  uint32_t acc[8];                  // trees wv, wv + nw, ... (T <= 8 * nw per pass)
+  for (int tb = 0; tb < T; tb += 8 * nw) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) acc[i] = 0;
+    for (int s0 = 0; s0 < tile_rows; s0 += slab_rows) {
+      const int rows = min(slab_rows, tile_rows - s0);
+      __syncthreads();
+      list_load_slab(w + (size_t)(t0 + s0) * T, (size_t)rows * T, slab);
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int t = tb + wv + i * nw;
+        if (t < T)
+          for (int rb = 0; rb < rows; rb += 32) {
+            const int r = rb + lane;
+            acc[i] += __popc(__ballot_sync(0xffffffffu, r < rows && slab[(size_t)r * T + t] != 0));
+          }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const int t = tb + wv + i * nw;
+      if (t < T && lane == 0) counts[(size_t)blockIdx.x * T + t] = acc[i];
+    }
+  }
+}
+__global__ void __launch_bounds__(256) list_fill_tiled_kernel(const uint8_t* __restrict__ w, const uint8_t* __restrict__ labels,
+                                                              int64_t n_rows, int T, int slab_rows,
+                                                              const uint32_t* __restrict__ tile_off,
+                                                              const uint64_t* __restrict__ tree_base,
+                                                              uint64_t* __restrict__ entries) {
+  extern __shared__ __align__(16) uint8_t slab[];
+  __shared__ uint8_t lab[512];
+  const int64_t t0 = (int64_t)blockIdx.x * kListTile;
+  const int tile_rows = (int)min((int64_t)kListTile, n_rows - t0);
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  uint64_t pos[8];                  // next free slot of trees wv, wv + nw, ...
+  for (int tb = 0; tb < T; tb += 8 * nw) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const int t = tb + wv + i * nw;
+      pos[i] = t < T ? tree_base[t] + tile_off[(size_t)blockIdx.x * T + t] : 0;
+    }
+    for (int s0 = 0; s0 < tile_rows; s0 += slab_rows) {
+      const int rows = min(slab_rows, tile_rows - s0);
+      __syncthreads();
+      list_load_slab(w + (size_t)(t0 + s0) * T, (size_t)rows * T, slab);
+      for (int r = threadIdx.x; r < rows; r += blockDim.x) lab[r] = labels[t0 + s0 + r];
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int t = tb + wv + i * nw;
+        if (t >= T) continue;
+        uint64_t p = pos[i];
+        for (int rb = 0; rb < rows; rb += 32) {
+          const int r = rb + lane;
+          const uint32_t wt = r < rows ? slab[(size_t)r * T + t] : 0u;
+          const uint32_t m = __ballot_sync(0xffffffffu, wt != 0);
+          if (wt) entries[p + __popc(m & ((1u << lane) - 1))] = pack_entry((uint32_t)(t0 + s0 + r), wt, lab[r]);
+          p += __popc(m);
+        }
+        pos[i] = p;
+      }
+    }
+  }
+}
+// one warp per tree: exclusive scan of its tile counts
+__global__ void list_scan_warp_kernel(uint32_t* __restrict__ counts, int n_tiles, int T, uint64_t* __restrict__ totals) {
+  const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (t >= T) return;
+  uint64_t run = 0;
+  for (int b = 0; b < n_tiles; b += 32) {
+    const int i = b + lane;
+    const uint32_t c = i < n_tiles ? counts[(size_t)i * T + t] : 0;
+    uint32_t inc = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += v;
+    }
+    if (i < n_tiles) counts[(size_t)i * T + t] = (uint32_t)(run + inc - c);   // < 2^32 rows per tree
+    run += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  if (lane == 0) totals[t] = run;
+}
 __global__ void list_count_kernel(const uint8_t* __restrict__ w, int64_t n_rows, int T, uint32_t* __restrict__ counts) {
   const int64_t r0 = (int64_t)blockIdx.x * kListTile;
   const int rows = (int)min((int64_t)kListTile, n_rows - r0);
@@ -688,6 +791,20 @@ __device__ __forceinline__ double impurity_dev(int kind, const HT* cnt, const ui
   return imp;
 }
 
+// Phase profile of hist_scan_kernel (debug builds only: make prof → libemrf_prof.so): cycles of thread 0 per phase,
+// summed over CTAs.  0 prologue, 1 zero, 2 accumulate, 3 flush/ticket, 4 prefix, 5 totals+parent, 6 candidates,
+// 7 arg-max + record, 8 CTAs, 9 CTAs that scanned.
+#ifdef EMRF_HIST_PROF
+__device__ unsigned long long g_hist_prof[16];
+#define HPROF_DECL long long hp_t = clock64();
+#define HPROF(i) do { if (threadIdx.x == 0) { const long long n_ = clock64(); atomicAdd(&g_hist_prof[i], (unsigned long long)(n_ - hp_t)); hp_t = n_; } } while (0)
+#define HPROF_COUNT(i) do { if (threadIdx.x == 0) atomicAdd(&g_hist_prof[i], 1ull); } while (0)
+#else
+#define HPROF_DECL
+#define HPROF(i)
+#define HPROF_COUNT(i)
+#endif
+
 // Shared-memory carve-up used by hist_scan_kernel and scan_kernel.  HT is the counter type: uint32_t, or
 // uint16_t for launches whose every node is accumulated by ONE CTA and weighs at most 65535 (no counter, and
 // no prefix sum over bins, can then exceed 16 bits): half the histogram memory, so more CTAs per SM.
@@ -752,6 +869,7 @@ template <class HT>
 __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, int impurity, int min_instances,
                            double min_info_gain, ScanResult* res, uint32_t* left_out, uint32_t* total_out) {
   const int tid = threadIdx.x, NT = blockDim.x;
+  HPROF_DECL
   HT* sh = S.hist;
   const int* nb = S.nb;
   // (a) inclusive prefix sum over bins for every (feature, class) column — conflict-free
@@ -763,6 +881,7 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
     for (int b = 0; b < n; b++) { run += col[b * C]; col[b * C] = (HT)run; }
   }
   __syncthreads();
+  HPROF(4);
   // (b) node totals = last bin of the chunk's first feature (every feature sums to the same)
   for (int c = tid; c < C; c += NT) S.tot[c] = sh[(size_t)(nb[0] - 1) * C + c];
   __syncthreads();
@@ -789,6 +908,7 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
   }
   __syncthreads();
   const double pimp = *S.pimp;
+  HPROF(5);
   // (c) one candidate (feature, split) per thread, Spark's operation order
   double best_gain = -INFINITY;  // below Double.MinValue: "no candidate"
   double best_li = 0.0, best_ri = 0.0;
@@ -834,6 +954,8 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
   }
   // (d) block arg-max: greatest gain, ties → smallest candidate index (= Spark's first maximum
   // in (subset order, split order))
+  __syncthreads();
+  HPROF(6);
   const int my_idx = best_idx;   // this thread's own best candidate (keeps best_li / best_ri)
   for (int o = 16; o; o >>= 1) {
     const double g2 = __shfl_xor_sync(0xffffffffu, best_gain, o);
@@ -882,6 +1004,7 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
     const HT* l = sh + ((size_t)k * B + s) * C;
     for (int c = tid; c < C; c += NT) { left_out[c] = l[c]; total_out[c] = S.tot[c]; }
   }
+  HPROF(7);
 }
 
 // Row staging for the accumulate loop.  A warp takes 32 entries at a time.  Its lanes fetch the 32
@@ -935,6 +1058,7 @@ __device__ __forceinline__ uint64_t load_entry(const uint64_t* __restrict__ ent,
 template <int CH, class HT = uint32_t>
 __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_scan_kernel(const HistArgs A) {
   constexpr bool U16 = sizeof(HT) == 2;
+  HPROF_DECL
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int tid = threadIdx.x;
   const int chunk = blockIdx.y;
@@ -961,8 +1085,10 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     sh_feat[k] = f;
     sh_nb[k] = A.num_bins_all[f];
   }
+  HPROF(0);
   for (int i = tid; i < (kc * B * C * (int)sizeof(HT) + 3) / 4; i += kHistThreads) shw[i] = 0;
   __syncthreads();
+  HPROF(1);
 
   // ---- accumulate this tile
   // counter idx gets += w: a 32-bit shared atomic either way (U16: on the word holding the pair, no carry can
@@ -1004,6 +1130,12 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     int* sh_off = reinterpret_cast<int*>(smem_raw + A.tile_smem_off + NW * RowTile<CHX>::kWarpWords * 4);
     for (int k = tid; k < kc; k += kHistThreads) sh_off[k] = (((sh_feat[k] >> 2) * TS) << 2) + (sh_feat[k] & 3);
     __syncthreads();
+    // the subset's tile offsets in registers when it is small (8 per lane sharing a row), else read per use
+    constexpr int KR = 8;
+    const bool off_in_regs = kc <= KR * SHARE;
+    int offr[KR];
+#pragma unroll
+    for (int i = 0; i < KR; i++) offr[i] = (part + SHARE * i < kc) ? sh_off[part + SHARE * i] : 0;
     uint4 R[RowTile<CHX>::kLoads];
     uint32_t b = wv;
     uint64_t e_cur = load_entry(ent, len, b * ROWS + rlane);
@@ -1020,11 +1152,22 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
         const uint32_t BC = (uint32_t)(B * C);
         uint32_t hl = lab + part * BC;
         const uint8_t* tb = tile_b + (rlane << 2);
+        if (off_in_regs) {
+#pragma unroll
+          for (int i = 0; i < KR; i++) {
+            if (part + SHARE * i < kc) {
+              const uint32_t bin = tb[offr[i]];
+              hist_add(hl + bin * C, w);
+              hl += SHARE * BC;
+            }
+          }
+        } else {
 #pragma unroll 4
-        for (int k = part; k < kc; k += SHARE) {
-          const uint32_t bin = tb[sh_off[k]];            // byte offset of feature k inside the transposed tile
-          hist_add(hl + bin * C, w);
-          hl += SHARE * BC;
+          for (int k = part; k < kc; k += SHARE) {
+            const uint32_t bin = tb[sh_off[k]];            // byte offset of feature k inside the transposed tile
+            hist_add(hl + bin * C, w);
+            hl += SHARE * BC;
+          }
         }
       }
       __syncwarp();
@@ -1034,6 +1177,8 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
   }
   __syncthreads();
 
+  HPROF(2);
+  HPROF_COUNT(8);
   const size_t slot_words = (size_t)A.f_sub * B * C;
   const size_t rec = (size_t)g * A.n_chunks + chunk;                   // tickets: absolute
   const size_t rrec = (size_t)(g - A.node_base) * A.n_chunks + chunk;    // result record: relative to the launch
@@ -1081,6 +1226,8 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     __syncthreads();
   }
   }
+  HPROF(3);
+  HPROF_COUNT(9);
   scan_chunk<HT>(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rrec],
                  A.left_counts + rrec * C, A.total_counts + rrec * C);
 }

@@ -258,7 +258,7 @@ struct emrf_ctx {
   void* nccl_comm = nullptr;
   // grow-only scratch reused across groups
   DevBuf d_group, d_results, d_ghist, d_tickets;
-  PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum, h_sample;
+  PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum, h_sample, h_sched;
   DevBuf d_split, d_part;   // partition work of the current group (written by decide_kernel)
   std::vector<HTree> tree_pools;   // LearningNode pools of the last fit (memory reused by the next)
   DevBuf d_seeds, d_table, d_tsum;
@@ -983,6 +983,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   cudaStream_t st = c->stream;
   CU(cudaSetDevice(c->device));
   if (N >= (1ll << 32)) return fail(EMRF_ERR_LIMIT, "n_rows must be < 2^32");
+  if (F >= (1 << 24)) return fail(EMRF_ERR_LIMIT, "n_features must be < 2^24");
   // row_sharded: this rank holds a slice of the rows and every tree; node histograms are all-reduced.
   // otherwise (world > 1): tree-sharded — every rank holds all rows and builds trees t % world == rank.
   const bool row_sharded = (sh != nullptr);
@@ -1099,6 +1100,46 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(cudaEventRecord(ev_bin, st));
   CU(cudaMemcpyAsync(d_num_bins.p, num_bins.data(), (size_t)F * 4, cudaMemcpyHostToDevice, st));   // behind the matrix chunks
 
+  // ---- metadata (DecisionTreeMetadata.buildMetadata) and the driver RNG (RandomForest.run)
+  const int f_sub = hl::features_per_node(P, F);
+  if (f_sub < 1 || f_sub > F) return fail(EMRF_ERR_ARG, "featureSubsetStrategy selects %d of %d features", f_sub, F);
+  const bool subsampling = (f_sub != F);
+  hl::JavaUtilRandom rng(P.seed);
+  // ---- feature-subset table: draw k of the driver RNG → (subset, sum of numBins), tabulated on the GPU
+  // in chunks (kernels.cuh reservoir_table_kernel).  selectNodesToSplit then only counts draws.
+  const int64_t draws_bound = 2 * (int64_t)T * ((int64_t)1 << std::min(P.max_depth, 24)) + 1024;
+  const int table_cap = (int)std::min<int64_t>(draws_bound, (int64_t)1 << 20);
+  DevBuf &d_seeds = c->d_seeds, &d_table = c->d_table, &d_tsum = c->d_tsum;
+  PinnedBuf &h_seeds = c->h_seeds, &h_table = c->h_table, &h_tsum = c->h_tsum;
+  int64_t table_base = -1;        // first draw index held by the table (-1: nothing yet)
+  int64_t draw_idx = 0;           // draws consumed so far (accepted nodes + rejected ones)
+  if (subsampling) {
+    CU(d_seeds.ensure((size_t)table_cap * 8));
+    CU(d_table.ensure((size_t)table_cap * f_sub * 4));
+    CU(d_tsum.ensure((size_t)table_cap * 4));
+    CU(h_seeds.ensure((size_t)table_cap * 8));
+    CU(h_table.ensure((size_t)table_cap * f_sub * 4));
+    CU(h_tsum.ensure((size_t)table_cap * 4));
+  }
+  auto table_fill = [&](int64_t base, bool sync = true) -> int {   // rng is positioned at draw `base`
+    int64_t* hs = h_seeds.as<int64_t>();
+    for (int k = 0; k < table_cap; k++) hs[k] = rng.next_long();
+    CU(cudaMemcpyAsync(d_seeds.p, hs, (size_t)table_cap * 8, cudaMemcpyHostToDevice, st));
+    kern::reservoir_table_kernel<<<(table_cap + 127) / 128, 128, 0, st>>>(d_seeds.as<int64_t>(), table_cap, F, f_sub,
+                                                                         d_num_bins.as<int32_t>(), d_table.as<int32_t>(),
+                                                                         d_tsum.as<int32_t>());
+    tm.kernel_launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(h_table.p, d_table.p, (size_t)table_cap * f_sub * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h_tsum.p, d_tsum.p, (size_t)table_cap * 4, cudaMemcpyDeviceToHost, st));
+    if (sync) CU(cudaStreamSynchronize(st));
+    table_base = base;
+    return EMRF_OK;
+  };
+  // the first chunk is tabulated now, underneath bagging; the host waits for it with the entry lists
+  if (subsampling) TRY(table_fill(0, false));
+
+
   // ---- BaggedPoint weights → per-tree entry lists
   // tree-sharded multi-GPU: every rank schedules all trees, but only builds lists (and
   // histograms) for trees t % world == rank.
@@ -1149,9 +1190,6 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   }
 
   // ---- metadata (DecisionTreeMetadata.buildMetadata)
-  const int f_sub = hl::features_per_node(P, F);
-  if (f_sub < 1 || f_sub > F) return fail(EMRF_ERR_ARG, "featureSubsetStrategy selects %d of %d features", f_sub, F);
-  const bool subsampling = (f_sub != F);
   int row_ch, k_chunk, n_chunks;
   size_t hist_bytes, hist_smem;
   TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &hist_smem));
@@ -1222,7 +1260,6 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   std::vector<std::pair<int, int>> stack;
   stack.reserve(1024);
   for (int t = 0; t < T; t++) stack.emplace_back(t, 0);
-  hl::JavaUtilRandom rng(P.seed);
   const int64_t max_mem = (int64_t)P.max_memory_mb * 1024ll * 1024ll;
   int64_t all_feat_bins = 0;
   for (int f = 0; f < F; f++) all_feat_bins += num_bins[f];
@@ -1248,43 +1285,6 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   double host_ms = 0.0, host_sel = 0.0, host_upd = 0.0;
   static const bool verify_gains = getenv("EMRF_VERIFY_GAINS") != nullptr;
   c->arena_reset();
-
-  // ---- feature-subset table: draw k of the driver RNG → (subset, sum of numBins), tabulated on the GPU
-  // in chunks (kernels.cuh reservoir_table_kernel).  selectNodesToSplit then only counts draws.
-  const int64_t draws_bound = 2 * (int64_t)T * ((int64_t)1 << std::min(P.max_depth, 24)) + 1024;
-  const int table_cap = (int)std::min<int64_t>(draws_bound, (int64_t)1 << 20);
-  DevBuf &d_seeds = c->d_seeds, &d_table = c->d_table, &d_tsum = c->d_tsum;
-  PinnedBuf &h_seeds = c->h_seeds, &h_table = c->h_table, &h_tsum = c->h_tsum;
-  int64_t table_base = -1;        // first draw index held by the table (-1: nothing yet)
-  int64_t draw_idx = 0;           // draws consumed so far (accepted nodes + rejected ones)
-  if (subsampling) {
-    CU(d_seeds.ensure((size_t)table_cap * 8));
-    CU(d_table.ensure((size_t)table_cap * f_sub * 4));
-    CU(d_tsum.ensure((size_t)table_cap * 4));
-    CU(h_seeds.ensure((size_t)table_cap * 8));
-    CU(h_table.ensure((size_t)table_cap * f_sub * 4));
-    CU(h_tsum.ensure((size_t)table_cap * 4));
-  }
-  auto table_fill = [&](int64_t base) -> int {   // rng is positioned at draw `base`
-    int64_t* hs = h_seeds.as<int64_t>();
-    for (int k = 0; k < table_cap; k++) hs[k] = rng.next_long();
-    CU(cudaMemcpyAsync(d_seeds.p, hs, (size_t)table_cap * 8, cudaMemcpyHostToDevice, st));
-    kern::reservoir_table_kernel<<<(table_cap + 127) / 128, 128, 0, st>>>(d_seeds.as<int64_t>(), table_cap, F, f_sub,
-                                                                         d_num_bins.as<int32_t>(), d_table.as<int32_t>(),
-                                                                         d_tsum.as<int32_t>());
-    tm.kernel_launches++;
-    CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(h_table.p, d_table.p, (size_t)table_cap * f_sub * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(h_tsum.p, d_tsum.p, (size_t)table_cap * 4, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    table_base = base;
-    return EMRF_OK;
-  };
-  {
-    const double t0 = now_ms();
-    if (subsampling) TRY(table_fill(0));
-    if (getenv("EMRF_DEBUG_TIMERS")) fprintf(stderr, "[emrf] subset table (%d draws): %.3f ms\n", table_cap, now_ms() - t0);
-  }
 
   // ---- selectNodesToSplit.  The driver RNG hands each popped node one nextLong() (drawn BEFORE the
   // memory check, so the node that does not fit consumes a draw too); the reservoir sampling a seed
@@ -1344,11 +1344,77 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   struct Decision { int32_t left_pool; bool l_leaf, r_leaf; };
   std::vector<Decision> decisions;
   std::vector<kern::GroupNode> gn_tmp;
-  struct Upd { uint32_t slot_l, split_idx; int32_t left_pool; };
+  struct Upd { uint32_t dec, slot_l, split_idx; int32_t left_pool; };
   std::vector<Upd> upd_vec;
   struct SplitRef { int tree, pool; };
   std::vector<SplitRef> split_ref_tmp;
   std::vector<int> pool_next(T, 0);
+  // Node statistics of a processed group (impurities, gain, split, class-count pointers, predictions): nothing in
+  // the scheduling depends on them, so they are filled from the full records one group later, under GPU work.
+  struct PendingStats {
+    GroupSel* sel = nullptr;
+    std::vector<Upd> upd;
+    const char* h_res = nullptr;
+    size_t res_left = 0, res_total = 0;
+    int n_nodes = 0, nt = 1;
+    cudaEvent_t rec_done = nullptr;
+  } pending;
+  auto fill_stats = [&](PendingStats& pd) -> int {
+    if (!pd.sel) return EMRF_OK;
+    CU(cudaEventSynchronize(pd.rec_done));
+    const kern::ScanResult* res = (const kern::ScanResult*)pd.h_res;
+    const uint32_t* res_leftc = (const uint32_t*)(pd.h_res + pd.res_left);
+    const uint32_t* res_totalc = (const uint32_t*)(pd.h_res + pd.res_total);
+    const std::vector<GroupEntry>& group = pd.sel->group;
+    const std::vector<int32_t>& group_feat = pd.sel->feat;
+    const Upd* upd = pd.upd.data();
+    int64_t mism = 0;
+#pragma omp parallel for num_threads(pd.nt) schedule(static) reduction(+ : mism)
+    for (int gi = 0; gi < pd.n_nodes; gi++) {
+      const GroupEntry& g = group[gi];
+      const uint32_t dw = upd[gi].dec;
+      HTree& tr = trees[g.tree];
+      const size_t rec = (size_t)gi * n_chunks + (dw & 0xffu);
+      const kern::ScanResult& r = res[rec];
+      const uint32_t* totc = res_totalc + rec * C;
+      const uint32_t* leftc = res_leftc + rec * C;
+      const bool valid = (dw & kern::kDecValid) != 0;
+      // impurities and gain come from the scan kernel (bit-exact IEEE, Spark's operation order);
+      // EMRF_VERIFY_GAINS=1 recomputes them here.
+      const double pimp = r.impurity;
+      const double gain = valid ? r.gain : kern::kInvalidGain;
+      const double limp = valid ? r.left_impurity : 0.0, rimp = valid ? r.right_impurity : 0.0;
+      HNode& n = tr.pool[g.pool];
+      const bool is_leaf = !(dw & kern::kDecNonLeaf);
+      if (verify_gains) {
+        if (valid) {
+          std::vector<uint32_t> rightc(C);
+          uint64_t lc = 0, rc = 0;
+          for (int cc = 0; cc < C; cc++) { rightc[cc] = totc[cc] - leftc[cc]; lc += leftc[cc]; rc += rightc[cc]; }
+          const double hl_ = hl::impurity_of(P.impurity, leftc, C), hr_ = hl::impurity_of(P.impurity, rightc.data(), C);
+          const double hp_ = hl::impurity_of(P.impurity, totc, C);
+          const double tc = (double)(lc + rc);
+          const double lw = (double)lc / tc, rw = (double)rc / tc;
+          const double hg = hp_ - lw * hl_ - rw * hr_;
+          if (hg != gain || hl_ != limp || hr_ != rimp || hp_ != pimp) mism++;
+        }
+        const int level = 31 - __builtin_clz((unsigned)n.id);   // the device's leaf rule against the host's
+        if (is_leaf != ((gain <= 0) || (level == P.max_depth))) mism++;
+      }
+      n.is_leaf = is_leaf; n.gain = gain; n.impurity = pimp; n.valid = valid;
+      n.cnt_a = totc; n.cnt_b = nullptr; n.pred = r.pred;
+      if (is_leaf) continue;
+      const int feat = group_feat[g.feat_at + r.k];
+      n.feature = feat; n.split_bin = r.split; n.threshold = h_thr[(size_t)feat * TS + r.split];
+      HNode& l = tr.pool[n.left];
+      HNode& rn = tr.pool[n.right];
+      l.impurity = limp; l.cnt_a = leftc; l.pred = r.left_pred;
+      rn.impurity = rimp; rn.cnt_a = totc; rn.cnt_b = leftc; rn.pred = r.right_pred;
+    }
+    tm.gain_mismatches += mism;
+    pd.sel = nullptr;
+    return EMRF_OK;
+  };
   double ph[12] = {0};   // EMRF_DEBUG_TIMERS: where the host's time goes, per phase
   double tp = now_ms();
   auto lap = [&](int i) { const double n_ = now_ms(); ph[i] += n_ - tp; tp = n_; };
@@ -1463,8 +1529,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const size_t split_bytes = off_ptn + (size_t)std::max<uint32_t>(ptiles_ub, 4) * 4;
     const size_t off_nleft = align_up((size_t)std::max<uint32_t>(ptiles_ub, 4) * 4, 16);
     const size_t off_limits = off_nleft + (size_t)n_nodes * 8;
+    const size_t off_sched = align_up(off_limits + 16, 16);
+    const size_t off_ptiles = off_sched + (size_t)n_nodes * 16;
     CU(c->d_split.ensure(split_bytes));
-    CU(c->d_part.ensure(off_limits + 16));
+    CU(c->d_part.ensure(off_ptiles + (size_t)n_nodes * 4));
     if ((size_t)next_slot + 2 * (size_t)n_nodes > seg_cap) {   // grow the segment table
       CU(cudaStreamSynchronize(st));
       DevBuf bigger;
@@ -1478,6 +1546,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_sel += d_; }
     lap(0);
 
+    // the previous group's records may still be on their way to the host (second stream): nothing of this group
+    // may overwrite them before that copy is done
+    if (pending.rec_done) CU(cudaStreamWaitEvent(st, pending.rec_done, 0));
     CU(cudaMemcpyAsync(c->d_group.p, c->h_group.p, group_bytes, cudaMemcpyHostToDevice, st));
     tm.h2d_bytes += (int64_t)group_bytes;
     tm.d2h_bytes += (int64_t)res_bytes;
@@ -1560,32 +1631,38 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       }
       TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_dec / 4));
     }
-    // ---- decisions and partition work on the device, the partition kernels right behind; the records (with
-    // the decision words) go to the host on the second stream meanwhile
+    // ---- decisions and partition work on the device, the partition kernels right behind.  The host gets the
+    // compact scheduling records first (second stream) and the full records after them.
     kern::SplitNode* dsn = (kern::SplitNode*)c->d_split.p;
     uint32_t* dtn = (uint32_t*)((char*)c->d_split.p + off_ptn);
     uint32_t* d_tile_left = (uint32_t*)c->d_part.p;
     uint64_t* d_nleft = (uint64_t*)((char*)c->d_part.p + off_nleft);
     uint32_t* d_limits = (uint32_t*)((char*)c->d_part.p + off_limits);
-    {
-      kern::DecideArgs D;
-      D.results = A.results; D.nodes = A.nodes; D.node_feat = A.node_feat;
-      D.node_info = (const uint32_t*)((char*)c->d_group.p + off_info);
-      D.segtab = c->p_segtab.as<kern::Seg>();
-      D.out_splits = dsn; D.out_tile_node = dtn;
-      D.out_dec = (uint32_t*)((char*)c->d_results.p + res_dec);
-      D.out_limits = d_limits;
-      D.n_nodes = n_nodes; D.n_chunks = n_chunks; D.f_sub = f_sub; D.max_depth = P.max_depth;
-      D.next_slot = next_slot;
-      kern::decide_kernel<<<1, 1024, 0, st>>>(D);
-      tm.kernel_launches++;
-      CU(cudaGetLastError());
-    }
-    cudaEvent_t ev_dec = c->events.get(), rec_done = c->events.get();
+    uint4* d_sched = (uint4*)((char*)c->d_part.p + off_sched);
+    uint32_t* d_ptiles = (uint32_t*)((char*)c->d_part.p + off_ptiles);
+    CU(c->h_sched.ensure((size_t)n_nodes * 16));
+    kern::DecideArgs D;
+    D.results = A.results; D.nodes = A.nodes; D.node_feat = A.node_feat;
+    D.node_info = (const uint32_t*)((char*)c->d_group.p + off_info);
+    D.segtab = c->p_segtab.as<kern::Seg>();
+    D.out_splits = dsn; D.out_tile_node = dtn;
+    D.out_dec = (uint32_t*)((char*)c->d_results.p + res_dec);
+    D.out_sched = d_sched; D.out_tiles = d_ptiles;
+    D.out_limits = d_limits;
+    D.n_nodes = n_nodes; D.n_chunks = n_chunks; D.f_sub = f_sub; D.max_depth = P.max_depth;
+    D.next_slot = next_slot;
+    kern::decide_flags_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(D);
+    cudaEvent_t ev_dec = c->events.get(), sched_done = c->events.get(), rec_done = c->events.get();
     CU(cudaEventRecord(ev_dec, st));
     CU(cudaStreamWaitEvent(c->stream2, ev_dec, 0));
+    CU(cudaMemcpyAsync(c->h_sched.p, d_sched, (size_t)n_nodes * 16, cudaMemcpyDeviceToHost, c->stream2));
+    CU(cudaEventRecord(sched_done, c->stream2));
     CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, c->stream2));
     CU(cudaEventRecord(rec_done, c->stream2));
+    tm.d2h_bytes += (int64_t)n_nodes * 16;
+    kern::decide_scan_kernel<<<1, 1024, 0, st>>>(D);
+    tm.kernel_launches += 2;
+    CU(cudaGetLastError());
     if (ptiles_ub) {
       cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
       CU(cudaEventRecord(p0, st));
@@ -1602,12 +1679,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       part_ev.emplace_back(p0, p1);
       CU(cudaGetLastError());
     }
-    // the next group's staging and records must not be overwritten before this copy is done: the host waits
-    // for rec_done below, before it launches anything else
     lap(1);
-    // ---- bookkeeping nobody waits for, done while the GPU works
+    // ---- bookkeeping nobody waits for, done while the GPU works: the previous group's node statistics, this
+    // group's trace
     {
       t_host0 = now_ms();
+      TRY(fill_stats(pending));
       const size_t at0 = fo->trace.size();
       fo->trace.resize(at0 + (size_t)n_nodes * (2 + f_sub));
       int32_t* tr_out = fo->trace.data() + at0;
@@ -1628,15 +1705,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     }
     lap(2);
 
-    // ---- host side of findBestSplits: the decision words say what became of every node; numbering repeats
-    // decide_kernel's (group order).  Class counts are not copied: nodes point into the arena records.
-    CU(cudaEventSynchronize(rec_done));
+    // ---- host side of findBestSplits, the part the next group waits for: the scheduling records say what
+    // became of every node; numbering repeats decide_scan_kernel's (group order); children get identity, segment
+    // slot and size bounds.  Everything else about the nodes is filled in later (fill_stats).
+    CU(cudaEventSynchronize(sched_done));
     t_host0 = now_ms();
     lap(3);
-    const kern::ScanResult* res = (const kern::ScanResult*)h_res;
-    const uint32_t* res_leftc = (const uint32_t*)(h_res + res_left);
-    const uint32_t* res_totalc = (const uint32_t*)(h_res + res_total);
-    const uint32_t* dec = (const uint32_t*)(h_res + res_dec);
+    const uint4* sched = (const uint4*)c->h_sched.p;
     decisions.resize(n_nodes);
     upd_vec.resize(n_nodes);
     Upd* upd = upd_vec.data();
@@ -1644,12 +1719,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     int ns = 0;
     for (int gi = 0; gi < n_nodes; gi++) {
       Upd& u = upd[gi];
+      u.dec = sched[gi].x;
       u.left_pool = -1; u.slot_l = 0; u.split_idx = 0;
-      if (!(dec[gi] & kern::kDecNonLeaf)) continue;
+      if (!(u.dec & kern::kDecNonLeaf)) continue;
       u.slot_l = next_slot; next_slot += 2;
       int& pn = pool_next[group[gi].tree];
       u.left_pool = pn; pn += 2;
-      if (dec[gi] & kern::kDecSplit) u.split_idx = (uint32_t)ns++;
+      if (u.dec & kern::kDecSplit) u.split_idx = (uint32_t)ns++;
     }
     for (int t : cur->trees_seen) trees[t].pool.resize_uninit((size_t)pool_next[t]);
     lap(5);
@@ -1661,65 +1737,35 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       tm.d2h_bytes += (int64_t)ns * 8;
       split_ref.resize((size_t)ns);
     }
-    int64_t mism = 0;
-#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : mism)
+#pragma omp parallel for num_threads(nt_host) schedule(static)
     for (int gi = 0; gi < n_nodes; gi++) {
       const GroupEntry& g = group[gi];
       const Upd& u = upd[gi];
-      const uint32_t dw = dec[gi];
+      if (!(u.dec & kern::kDecNonLeaf)) { decisions[gi] = Decision{-1, true, true}; continue; }
       HTree& tr = trees[g.tree];
-      const size_t rec = (size_t)gi * n_chunks + (dw & 0xffu);
-      const kern::ScanResult& r = res[rec];
-      const uint32_t* totc = res_totalc + rec * C;
-      const uint32_t* leftc = res_leftc + rec * C;
-      const bool valid = (dw & kern::kDecValid) != 0;
-      // impurities and gain come from the scan kernel (bit-exact IEEE, Spark's operation order);
-      // EMRF_VERIFY_GAINS=1 recomputes them here.
-      const double pimp = r.impurity;
-      const double gain = valid ? r.gain : kern::kInvalidGain;
-      const double limp = valid ? r.left_impurity : 0.0, rimp = valid ? r.right_impurity : 0.0;
-      if (valid && verify_gains) {
-        std::vector<uint32_t> rightc(C);
-        uint64_t lc = 0, rc = 0;
-        for (int cc = 0; cc < C; cc++) { rightc[cc] = totc[cc] - leftc[cc]; lc += leftc[cc]; rc += rightc[cc]; }
-        const double hl_ = hl::impurity_of(P.impurity, leftc, C), hr_ = hl::impurity_of(P.impurity, rightc.data(), C);
-        const double hp_ = hl::impurity_of(P.impurity, totc, C);
-        const double tc = (double)(lc + rc);
-        const double lw = (double)lc / tc, rw = (double)rc / tc;
-        const double hg = hp_ - lw * hl_ - rw * hr_;
-        if (hg != gain || hl_ != limp || hr_ != rimp || hp_ != pimp) mism++;
-      }
       HNode& n = tr.pool[g.pool];
-      const bool is_leaf = !(dw & kern::kDecNonLeaf);
-      if (verify_gains) {   // the device's leaf rule against the host's
-        const int level = 31 - __builtin_clz((unsigned)n.id);
-        if (is_leaf != ((gain <= 0) || (level == P.max_depth))) mism++;
-      }
-      n.is_leaf = is_leaf; n.gain = gain; n.impurity = pimp; n.valid = valid;
-      n.cnt_a = totc; n.cnt_b = nullptr; n.pred = r.pred;
-      if (is_leaf) { decisions[gi] = Decision{-1, true, true}; continue; }
-      const int feat = group_feat[g.feat_at + r.k];
-      const int sbin = r.split;
-      const bool l_leaf = (dw & kern::kDecLLeaf) != 0, r_leaf = (dw & kern::kDecRLeaf) != 0;
+      const bool l_leaf = (u.dec & kern::kDecLLeaf) != 0, r_leaf = (u.dec & kern::kDecRLeaf) != 0;
       const int li = u.left_pool;
       HNode& l = *new (&tr.pool[li]) HNode();
       HNode& rn = *new (&tr.pool[li + 1]) HNode();
-      const int id = n.id;
-      l.id = 2 * id; l.is_leaf = l_leaf; l.impurity = limp; l.cnt_a = leftc; l.pred = r.left_pred;
-      rn.id = 2 * id + 1; rn.is_leaf = r_leaf; rn.impurity = rimp; rn.cnt_a = totc; rn.cnt_b = leftc; rn.pred = r.right_pred;
+      const uint32_t lw = sched[gi].y, tw = sched[gi].z;
+      l.id = 2 * n.id; l.is_leaf = l_leaf;
+      rn.id = 2 * n.id + 1; rn.is_leaf = r_leaf;
       // a segment cannot hold more entries than its parent's, nor more than the node's total weight
       // (every entry weighs >= 1): good enough to tile the next launches without reading sizes back
       l.slot = u.slot_l; rn.slot = u.slot_l + 1;
-      l.ub = std::min(n.ub, r.left_weight);
-      rn.ub = std::min(n.ub, r.total_weight - r.left_weight);
-      l.weight = r.left_weight;
-      rn.weight = r.total_weight - r.left_weight;
-      n.feature = feat; n.split_bin = sbin; n.threshold = h_thr[(size_t)feat * TS + sbin];
+      l.ub = std::min(n.ub, lw);
+      rn.ub = std::min(n.ub, tw - lw);
+      l.weight = lw;
+      rn.weight = tw - lw;
       n.left = li; n.right = li + 1;
       decisions[gi] = Decision{li, l_leaf, r_leaf};
-      if (row_sharded && (dw & kern::kDecSplit)) split_ref[u.split_idx] = {g.tree, g.pool};
+      if (row_sharded && (u.dec & kern::kDecSplit)) split_ref[u.split_idx] = {g.tree, g.pool};
     }
-    tm.gain_mismatches += mism;
+    // the statistics of this group's nodes wait for the full records (consumed under the next group's kernels)
+    pending.sel = cur; pending.h_res = h_res; pending.res_left = res_left; pending.res_total = res_total;
+    pending.n_nodes = n_nodes; pending.rec_done = rec_done; pending.nt = nt_host;
+    std::swap(pending.upd, upd_vec);
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
     lap(8);
     // ---- children go on the stack in Scala map iteration order (tree by tree, nodes in pop order)
@@ -1759,6 +1805,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     std::swap(cur, nxt);
   }
 
+  TRY(fill_stats(pending));   // the last group's
   if (env_flag("EMRF_DEBUG_TIMERS"))
     fprintf(stderr, "[emrf] host phases ms: prep %.2f | launch %.2f | bookkeeping %.2f | wait %.2f | numbering %.2f | nodes %.2f | "
             "stack %.2f | select %.2f | other %.2f\n", ph[0], ph[1], ph[2], ph[3], ph[5], ph[8], ph[9], ph[10], ph[11]);
@@ -1789,6 +1836,21 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(cudaEventElapsedTime(&ms, ev_b0, ev_b1)); tm.bag_kernel_ms = ms;
   for (auto& pr : hist_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.hist_kernel_ms += ms; }
   for (auto& pr : part_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.partition_ms += ms; }
+  if (env_flag("EMRF_DEBUG_TIMERS")) {
+    // GPU timeline of the group loop: hist end -> (decide) -> partition start, partition end -> next hist start
+    double gap_dec = 0, gap_next = 0, first_to_last = 0;
+    const bool paired = hist_ev.size() == part_ev.size();
+    for (size_t i = 0; paired && i < hist_ev.size(); i++) {
+      CU(cudaEventElapsedTime(&ms, hist_ev[i].second, part_ev[i].first)); gap_dec += ms;
+      if (i + 1 < hist_ev.size()) { CU(cudaEventElapsedTime(&ms, part_ev[i].second, hist_ev[i + 1].first)); gap_next += ms; }
+    }
+    if (!hist_ev.empty()) { CU(cudaEventElapsedTime(&ms, hist_ev.front().first, hist_ev.back().second)); first_to_last = ms; }
+    CU(cudaEventElapsedTime(&ms, ev_bag, hist_ev.front().first));
+    fprintf(stderr, "[emrf] GPU timeline ms: lists->first hist %.2f | loop %.2f (hist %.2f, part %.2f, hist->part gaps %.2f, part->next hist gaps %.2f)%s\n",
+            (double)ms, first_to_last, tm.hist_kernel_ms, tm.partition_ms, gap_dec, gap_next, paired ? "" : " [some groups had no partition]");
+    CU(cudaEventElapsedTime(&ms, hist_ev.back().second, ev_end));
+    fprintf(stderr, "[emrf] last hist -> end %.2f ms\n", (double)ms);
+  }
   tm.find_best_splits_ms = tm.hist_kernel_ms;
   tm.host_scheduler_ms = host_ms;
   tm.host_select_ms = host_sel;

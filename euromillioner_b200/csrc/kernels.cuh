@@ -1456,7 +1456,7 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64
 // with the records, and (b) the partition work (SplitNode list, tile map, counts) that the K4 kernels
 // launched right behind it consume, so that the GPU never waits for the host between a group's histograms and
 // its partition.  Numbering is in group order: segment slots next_slot + 2*i for the i-th non-leaf node, split
-// index = rank among the nodes that have a child to partition.  One CTA; nodes in chunks of 1024.
+// index = rank among the nodes that have a child to partition.
 // ---------------------------------------------------------------------------------------------
 constexpr uint32_t kDecNonLeaf = 1u << 8, kDecLLeaf = 1u << 9, kDecRLeaf = 1u << 10, kDecSplit = 1u << 11, kDecValid = 1u << 12;
 constexpr uint32_t kInfoMine = 1u << 8;   // node_info: level | kInfoMine (this rank builds/partitions the node's tree)
@@ -1468,12 +1468,49 @@ struct DecideArgs {
   const Seg* segtab;
   SplitNode* out_splits;
   uint32_t* out_tile_node;
-  uint32_t* out_dec;             // [n_nodes] best chunk | kDec* flags
+  uint32_t* out_dec;             // [n_nodes] best chunk | kDec* flags (travels with the records)
+  uint4* out_sched;              // [n_nodes] {decision word, left weight, total weight, feature | split bin << 24}:
+                                 //   all the host needs to number the children and select the next group
+  uint32_t* out_tiles;           // [n_nodes] partition tiles of the node (0 unless kDecSplit)
   uint32_t* out_limits;          // [0] split nodes, [1] partition tiles
   int n_nodes, n_chunks, f_sub, max_depth;
   uint32_t next_slot;
 };
-__global__ void __launch_bounds__(1024) decide_kernel(const DecideArgs A) {
+// step 1, one thread per node: the decision word, the scheduling record and the partition tile count
+__global__ void __launch_bounds__(256) decide_flags_kernel(const DecideArgs A) {
+  const int gi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gi >= A.n_nodes) return;
+  const ScanResult* r0 = A.results + (size_t)gi * A.n_chunks;
+  int best = -1;
+  for (int ch = 0; ch < A.n_chunks; ch++) {        // first maximum in subset order
+    if (r0[ch].k < 0) continue;
+    if (best < 0 || r0[ch].gain > r0[best].gain) best = ch;
+  }
+  const ScanResult& r = r0[best < 0 ? 0 : best];
+  const uint32_t info = A.node_info[gi];
+  const int level = (int)(info & 0xffu);
+  const bool valid = best >= 0 && r.valid;
+  const double gain = valid ? r.gain : kInvalidGain;
+  const bool is_leaf = (gain <= 0) || (level == A.max_depth);
+  uint32_t dec = (uint32_t)(best < 0 ? 0 : best) | (valid ? kDecValid : 0u);
+  uint32_t tiles = 0, fs = 0;
+  if (!is_leaf) {
+    const bool child_leaf = (level + 1) == A.max_depth;
+    const bool l_leaf = child_leaf || (r.left_impurity == 0.0);
+    const bool r_leaf = child_leaf || (r.right_impurity == 0.0);
+    dec |= kDecNonLeaf | (l_leaf ? kDecLLeaf : 0u) | (r_leaf ? kDecRLeaf : 0u);
+    fs = (uint32_t)A.node_feat[(size_t)gi * A.f_sub + r.k] | ((uint32_t)r.split << 24);
+    if ((!l_leaf || !r_leaf) && (info & kInfoMine)) {
+      dec |= kDecSplit;
+      tiles = (A.segtab[A.nodes[gi].seg_slot].len + kPartTile - 1) / kPartTile;
+    }
+  }
+  A.out_dec[gi] = dec;
+  A.out_sched[gi] = make_uint4(dec, r.left_weight, r.total_weight, fs);
+  A.out_tiles[gi] = tiles;
+}
+// step 2, one CTA: numbering in group order (block scans over chunks of 1024 nodes) and the partition work
+__global__ void __launch_bounds__(1024) decide_scan_kernel(const DecideArgs A) {
   __shared__ uint32_t sh_a[32], sh_b[32], sh_t[32];
   __shared__ uint32_t carry[3];
   const int tid = threadIdx.x, lane = tid & 31, wv = tid >> 5;
@@ -1481,34 +1518,9 @@ __global__ void __launch_bounds__(1024) decide_kernel(const DecideArgs A) {
   __syncthreads();
   for (int base = 0; base < A.n_nodes; base += 1024) {
     const int gi = base + tid;
-    uint32_t dec = 0, tiles = 0, len = 0;
-    int best = -1;
-    if (gi < A.n_nodes) {
-      const ScanResult* r0 = A.results + (size_t)gi * A.n_chunks;
-      for (int ch = 0; ch < A.n_chunks; ch++) {        // first maximum in subset order
-        if (r0[ch].k < 0) continue;
-        if (best < 0 || r0[ch].gain > r0[best].gain) best = ch;
-      }
-      const ScanResult& r = r0[best < 0 ? 0 : best];
-      const uint32_t info = A.node_info[gi];
-      const int level = (int)(info & 0xffu);
-      const bool valid = best >= 0 && r.valid;
-      const double gain = valid ? r.gain : kInvalidGain;
-      const bool is_leaf = (gain <= 0) || (level == A.max_depth);
-      dec = (uint32_t)(best < 0 ? 0 : best) | (valid ? kDecValid : 0u);
-      if (!is_leaf) {
-        const bool child_leaf = (level + 1) == A.max_depth;
-        const bool l_leaf = child_leaf || (r.left_impurity == 0.0);
-        const bool r_leaf = child_leaf || (r.right_impurity == 0.0);
-        dec |= kDecNonLeaf | (l_leaf ? kDecLLeaf : 0u) | (r_leaf ? kDecRLeaf : 0u);
-        if ((!l_leaf || !r_leaf) && (info & kInfoMine)) {
-          dec |= kDecSplit;
-          len = A.segtab[A.nodes[gi].seg_slot].len;
-          tiles = (len + kPartTile - 1) / kPartTile;
-        }
-      }
-      A.out_dec[gi] = dec;
-    }
+    const uint4 sc = gi < A.n_nodes ? A.out_sched[gi] : make_uint4(0, 0, 0, 0);
+    const uint32_t dec = sc.x;
+    const uint32_t tiles = gi < A.n_nodes ? A.out_tiles[gi] : 0u;
     // block-wide exclusive scans of (non-leaf, split, tiles)
     uint32_t a = (dec & kDecNonLeaf) ? 1u : 0u, b = (dec & kDecSplit) ? 1u : 0u, t = tiles;
     uint32_t ia = a, ib = b, it = t;
@@ -1532,11 +1544,10 @@ __global__ void __launch_bounds__(1024) decide_kernel(const DecideArgs A) {
     const uint32_t wa = wv ? sh_a[wv - 1] : 0u, wb = wv ? sh_b[wv - 1] : 0u, wt = wv ? sh_t[wv - 1] : 0u;
     const uint32_t ea = carry[0] + wa + ia - a, eb = carry[1] + wb + ib - b, et = carry[2] + wt + it - t;
     if (dec & kDecSplit) {
-      const ScanResult& r = A.results[(size_t)gi * A.n_chunks + (dec & 0xffu)];
       SplitNode sn;
-      sn.seg_start = 0; sn.seg_len = len; sn.buf = 0;       // the kernels take the segment from the table
+      sn.seg_start = 0; sn.seg_len = 0; sn.buf = 0;       // the kernels take the segment from the table
       sn.tile_begin = et; sn.n_tiles = tiles;
-      sn.feature = A.node_feat[(size_t)gi * A.f_sub + r.k]; sn.split_bin = r.split;
+      sn.feature = (int32_t)(sc.w & 0xffffffu); sn.split_bin = (int32_t)(sc.w >> 24);
       sn.seg_slot = A.nodes[gi].seg_slot; sn.left_slot = A.next_slot + 2 * ea; sn.right_slot = sn.left_slot + 1; sn.pad = 0;
       A.out_splits[eb] = sn;
       for (uint32_t q = 0; q < tiles; q++) A.out_tile_node[et + q] = eb;

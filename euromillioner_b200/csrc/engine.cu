@@ -1198,6 +1198,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   const size_t hist_bytes16 = kern::hist_smem_bytes(k_chunk, B, C, 2);
   const size_t hist_smem16 = hist_bytes16 + (hist_smem - hist_bytes);
   const bool allow_u16 = !row_sharded && !env_flag("EMRF_HIST_U32");
+  // nodes holding at least 1/EMRF_CM_DIV of the rows gather from the column-major matrix (0: never)
+  uint32_t cm_min_len = 0;
+  {
+    const char* e = getenv("EMRF_CM_DIV");
+    const long div = e ? atol(e) : 4;
+    if (div > 0) cm_min_len = (uint32_t)std::max<int64_t>(N / div, 1024);
+  }
   if (allow_u16) CU(hist_launch(row_ch, dim3(1), hist_smem16, st, kern::HistArgs(), true, true));
   if (row_sharded) CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
   const size_t slot_words = (size_t)f_sub * B * C;
@@ -1555,7 +1562,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaMemsetAsync(c->d_tickets.p, 0, n_rec * 4, st));
     if (c->world > 1) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
     if (n_slots_alloc) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots_alloc * slot_words * 4, st));
-    kern::HistArgs A;
+    kern::HistArgs A{};
     A.ent0 = d_ent[0]->as<uint64_t>();
     A.ent1 = d_ent[1]->as<uint64_t>();
     A.segtab = c->p_segtab.as<kern::Seg>();
@@ -1579,6 +1586,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.push_world = push_mode ? c->world : 0; A.push_rank = c->rank; A.push_npr = nodes_per_rank;
     for (int r = 0; r < 8; r++) A.peer_stage[r] = (uint32_t*)c->peer_stage[r];
     A.min_info_gain = P.min_info_gain;
+    A.bins_cm = d_cm.as<uint8_t>(); A.Np = Np; A.cm_min_len = cm_min_len;
     A.results = (kern::ScanResult*)c->d_results.p;
     A.left_counts = (uint32_t*)((char*)c->d_results.p + res_left);
     A.total_counts = (uint32_t*)((char*)c->d_results.p + res_total);
@@ -2289,7 +2297,7 @@ extern "C" int emrf_histogram(emrf_ctx_t* c, const uint8_t* bins_rm, int64_t N, 
   CU(cudaMemcpyAsync(d_tiles.p, tn.data(), tn.size() * 4, cudaMemcpyHostToDevice, st));
   CU(cudaMemcpyAsync(d_nb.p, num_bins_all, (size_t)F * 4, cudaMemcpyHostToDevice, st));
   CU(cudaMemsetAsync(d_hist.p, 0, (size_t)n_nodes * slot_words * 4, st));
-  kern::HistArgs A;
+  kern::HistArgs A{};
   memset(&A, 0, sizeof(A));
   A.ent0 = d_ent.as<uint64_t>(); A.ent1 = d_ent.as<uint64_t>();
   A.bins_rm = d_rm.as<uint8_t>();

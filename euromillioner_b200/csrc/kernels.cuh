@@ -748,6 +748,10 @@ struct HistArgs {
   int32_t push_world, push_rank, push_npr;   // push_world == 0: off
   uint32_t* peer_stage[8];                   // [owner]: base of that rank's staging buffer (peer-mapped)
   double min_info_gain;
+  // dense nodes (segment of at least cm_min_len entries; 0 = never) gather from the COLUMN-major matrix instead
+  const uint8_t* bins_cm;                    // [F][Np]
+  int64_t Np;
+  uint32_t cm_min_len;
 };
 
 // Correctly rounded a / b for integer-valued 0 <= a <= b < 2^32 with y = RN(1 / b): one multiply and
@@ -1102,7 +1106,63 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
   const uint32_t len = tile_first < nd.seg_len ? (uint32_t)min((uint64_t)A.tile_len, nd.seg_len - tile_first) : 0u;
   const uint8_t* bins = A.bins_rm;
   const int Fp = A.Fp;
-  if (CH == 0) {
+  if (A.cm_min_len && nd.seg_len >= A.cm_min_len) {
+    // dense node: the entries' rows are ascending and close together, so lane = entry and one LDG.U8 per feature
+    // from the column-major matrix touches only a few sectors per warp (32 entries span about 32*N/len bytes of
+    // the column) — no row staging at all, the LSU pipe carries one load and one atomic per (batch, feature).
+    const uint8_t* cm = A.bins_cm;
+    const size_t Np = (size_t)A.Np;
+    const uint32_t BC = (uint32_t)(B * C);
+    constexpr int KB = 8;      // features whose loads are in flight together
+    if (kc <= KB) {
+      // software pipeline: the gathers of entry j + 256 are in flight while entry j is added
+      uint64_t e0 = tid < len ? __ldcs(ent + tid) : 0ull;
+      uint64_t e1 = tid + kHistThreads < len ? __ldcs(ent + tid + kHistThreads) : 0ull;
+      uint32_t bn[KB];
+#pragma unroll
+      for (int i = 0; i < KB; i++) bn[i] = i < kc ? __ldg(cm + (size_t)sh_feat[i] * Np + (uint32_t)e0) : 0u;
+      for (uint32_t j0 = 0; j0 < len; j0 += kHistThreads) {
+        const uint64_t e = e0;
+        uint32_t bc[KB];
+#pragma unroll
+        for (int i = 0; i < KB; i++) bc[i] = bn[i];
+        e0 = e1;
+        const uint32_t j2 = j0 + 2 * kHistThreads + tid;
+        e1 = j2 < len ? __ldcs(ent + j2) : 0ull;
+        if (j0 + kHistThreads < len) {
+#pragma unroll
+          for (int i = 0; i < KB; i++) bn[i] = i < kc ? __ldg(cm + (size_t)sh_feat[i] * Np + (uint32_t)e0) : 0u;
+        }
+        const uint32_t w = (uint32_t)(e >> 32) & 0xffu;
+        const uint32_t lab = (uint32_t)(e >> 40) & 0xffu;
+        if (w) {
+#pragma unroll
+          for (int i = 0; i < KB; i++)
+            if (i < kc) hist_add((uint32_t)i * BC + bc[i] * C + lab, w);
+        }
+      }
+    } else {
+      uint64_t e_nxt = tid < len ? __ldcs(ent + tid) : 0ull;
+      for (uint32_t j0 = 0; j0 < len; j0 += kHistThreads) {
+        const uint64_t e = e_nxt;
+        const uint32_t jn = j0 + kHistThreads + tid;
+        e_nxt = jn < len ? __ldcs(ent + jn) : 0ull;
+        const uint32_t row = (uint32_t)e;
+        const uint32_t w = (uint32_t)(e >> 32) & 0xffu;
+        const uint32_t lab = (uint32_t)(e >> 40) & 0xffu;
+        for (int k0g = 0; k0g < kc; k0g += KB) {
+          uint32_t bc[KB];
+#pragma unroll
+          for (int i = 0; i < KB; i++) bc[i] = k0g + i < kc ? __ldg(cm + (size_t)sh_feat[k0g + i] * Np + row) : 0u;
+          if (w) {
+#pragma unroll
+            for (int i = 0; i < KB; i++)
+              if (k0g + i < kc) hist_add((uint32_t)(k0g + i) * BC + bc[i] * C + lab, w);
+          }
+        }
+      }
+    }
+  } else if (CH == 0) {
     // generic path (rows wider than 128 B): one byte gather per (entry, feature)
     for (uint32_t j = tid; j < len; j += kHistThreads) {
       const uint64_t e = ent[j];

@@ -315,6 +315,7 @@ static int ctx_init(emrf_ctx* c, int device) {
   CU(cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking));
   memset(&c->tm, 0, sizeof(c->tm));
   c->host_threads = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+  if (const char* e = getenv("EMRF_HOST_THREADS")) c->host_threads = std::max(1, atoi(e));   // experiments
   return EMRF_OK;
 }
 
@@ -1281,8 +1282,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     std::vector<GroupEntry> group;
     std::vector<int32_t> feat;
     std::vector<int> trees_seen;
-    std::vector<std::vector<int>> nodes_for_tree;
-    void clear() { group.clear(); feat.clear(); trees_seen.clear(); nodes_for_tree.clear(); }
+    std::vector<int> tree_off, tree_nodes, tree_fill;   // CSR: nodes (group indices) of trees_seen[q], in pop order
+    uint64_t total_ub = 0;   // entry bounds of this rank's nodes, summed
+    uint32_t max_w = 0;      // heaviest of this rank's nodes
+    void clear() { group.clear(); feat.clear(); trees_seen.clear(); tree_off.clear(); tree_nodes.clear(); total_ub = 0; max_w = 0; }
   };
   GroupSel sel_a, sel_b;
   GroupSel* cur = &sel_a;
@@ -1303,37 +1306,66 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   auto select_group = [&](GroupSel& G) {
     G.clear();
     int64_t mem = 0;
-    while (!stack.empty()) {
-      const auto top = stack.back();
-      const int32_t* sub = nullptr;
-      int64_t total_bins = all_feat_bins;
-      if (subsampling) {
-        // featureSubset = reservoirSampleAndCount(Range(0, F), F_sub, rng.nextLong()) — draw number draw_idx
-        if (draw_idx >= table_base + table_cap) {
-          select_rc = table_fill(table_base + table_cap);
-          if (select_rc != EMRF_OK) return;
-        }
-        const size_t at = (size_t)(draw_idx - table_base);
-        sub = h_table.as<int32_t>() + at * f_sub;
-        total_bins = h_tsum.as<int32_t>()[at];
-        draw_idx++;            // drawn BEFORE the memory check: a node that does not fit still consumes it
+    bool rejected = false;
+    const int32_t* tab = h_table.as<int32_t>();
+    const int32_t* tsum_all = h_tsum.as<int32_t>();
+    while (!stack.empty() && !rejected) {
+      // featureSubset = reservoirSampleAndCount(Range(0, F), F_sub, rng.nextLong()): the i-th node examined takes
+      // draw number draw_idx + i, so a run of stack entries is served by the current window of the table
+      if (subsampling && draw_idx >= table_base + table_cap) {
+        select_rc = table_fill(table_base + table_cap);
+        if (select_rc != EMRF_OK) return;
       }
-      const int64_t node_mem = (int64_t)C * total_bins * 8;
-      if (mem + node_mem <= max_mem || mem == 0) {
-        stack.pop_back();
-        if (tree_slot[top.first] < 0) {
-          tree_slot[top.first] = (int)G.trees_seen.size();
-          G.trees_seen.push_back(top.first);
-          G.nodes_for_tree.emplace_back();
-        }
-        G.nodes_for_tree[tree_slot[top.first]].push_back((int)G.group.size());
-        G.group.push_back({top.first, top.second, (int)G.feat.size()});
-        if (sub) G.feat.insert(G.feat.end(), sub, sub + f_sub);
-        else for (int k = 0; k < F; k++) G.feat.push_back(k);
-        mem += node_mem;
-      } else {
-        break;
+      const size_t s_top = stack.size();
+      const size_t at0 = subsampling ? (size_t)(draw_idx - table_base) : 0;
+      const size_t m = subsampling ? std::min<size_t>(s_top, (size_t)(table_base + table_cap - draw_idx)) : s_top;
+      // how many of the next m entries fit: a running sum over the table's bin totals (sequential, tiny)
+      size_t k = 0;
+      for (; k < m; k++) {
+        const int64_t node_mem = (int64_t)C * (subsampling ? (int64_t)tsum_all[at0 + k] : all_feat_bins) * 8;
+        if (mem + node_mem <= max_mem || mem == 0) mem += node_mem;
+        else { rejected = true; break; }
       }
+      // the admitted nodes, in pop order; the node that did not fit has consumed its draw too
+      const size_t g0 = G.group.size();
+      G.group.resize(g0 + k);
+      G.feat.resize((g0 + k) * (size_t)f_sub);
+      uint64_t tot = 0;
+      uint32_t mw = 0;
+      const int nt = k >= 1024 ? c->host_threads : 1;
+      (void)nt;
+#pragma omp parallel for num_threads(nt) schedule(static) reduction(+ : tot) reduction(max : mw)
+      for (size_t i = 0; i < k; i++) {
+        const auto top = stack[s_top - 1 - i];
+        G.group[g0 + i] = {top.first, top.second, (int)((g0 + i) * (size_t)f_sub)};
+        int32_t* fo_ = G.feat.data() + (g0 + i) * (size_t)f_sub;
+        if (subsampling) memcpy(fo_, tab + (at0 + i) * (size_t)f_sub, (size_t)f_sub * 4);
+        else for (int q = 0; q < F; q++) fo_[q] = q;
+        if (mine(top.first)) {
+          const HNode& hn = trees[top.first].pool[top.second];
+          tot += hn.ub;
+          mw = std::max(mw, hn.weight);
+        }
+      }
+      G.total_ub += tot;
+      G.max_w = std::max(G.max_w, mw);
+      stack.resize(s_top - k);
+      if (subsampling) draw_idx += (int64_t)k + (rejected ? 1 : 0);
+    }
+    // trees in first-seen order (= mutable.HashMap insertion order) and each tree's nodes in pop order
+    const int n = (int)G.group.size();
+    for (int i = 0; i < n; i++) {
+      const int t = G.group[i].tree;
+      if (tree_slot[t] < 0) { tree_slot[t] = (int)G.trees_seen.size(); G.trees_seen.push_back(t); }
+    }
+    G.tree_off.assign(G.trees_seen.size() + 1, 0);
+    for (int i = 0; i < n; i++) G.tree_off[tree_slot[G.group[i].tree] + 1]++;
+    for (size_t q = 0; q < G.trees_seen.size(); q++) G.tree_off[q + 1] += G.tree_off[q];
+    G.tree_nodes.resize(n);
+    {
+      std::vector<int>& fill = G.tree_fill;
+      fill.assign(G.tree_off.begin(), G.tree_off.end() - 1);
+      for (int i = 0; i < n; i++) G.tree_nodes[fill[tree_slot[G.group[i].tree]]++] = i;
     }
     for (int t : G.trees_seen) tree_slot[t] = -1;   // slots are recomputed by whoever consumes the group
   };
@@ -1350,12 +1382,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   if (n_chunks > 255) return fail(EMRF_ERR_LIMIT, "a node's histogram needs %d feature chunks (at most 255)", n_chunks);
   struct Decision { int32_t left_pool; bool l_leaf, r_leaf; };
   std::vector<Decision> decisions;
-  std::vector<kern::GroupNode> gn_tmp;
   struct Upd { uint32_t dec, slot_l, split_idx; int32_t left_pool; };
   std::vector<Upd> upd_vec;
   struct SplitRef { int tree, pool; };
   std::vector<SplitRef> split_ref_tmp;
   std::vector<int> pool_next(T, 0);
+  bool tickets_zeroed = false, ghist_zeroed = false;   // per fit: another entry point may have used the buffers
   // Node statistics of a processed group (impurities, gain, split, class-count pointers, predictions): nothing in
   // the scheduling depends on them, so they are filled from the full records one group later, under GPU work.
   struct PendingStats {
@@ -1436,33 +1468,46 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     fo->group_sizes.push_back(n_nodes);
 
     // ---- tiles (tree-sharded multi-GPU: own trees only); sizes are upper bounds
-    uint64_t total_entries = 0;
-    uint32_t max_weight = 0;
-#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : total_entries) reduction(max : max_weight)
-    for (int i = 0; i < n_nodes; i++)
-      if (mine(group[i].tree)) {
-        const HNode& hn = trees[group[i].tree].pool[group[i].pool];
-        total_entries += hn.ub;
-        max_weight = std::max(max_weight, hn.weight);
-      }
+    const uint64_t total_entries = cur->total_ub;
+    const uint32_t max_weight = cur->max_w;
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
     // TreePoint matrix larger than L2: many small tiles, launched in row-range order (below), so that the
     // CTAs resident at any moment gather rows from the same slice of the matrix and trees share it in L2
     if (l2_blocked) tile_len = 8192;
 
-    // staging layout: [GroupNode n][node_feat n*f_sub][tile_node tiles][tile_q tiles]
-    std::vector<kern::GroupNode>& gn = gn_tmp;
-    gn.resize(n_nodes);
-#pragma omp parallel for num_threads(nt_host) schedule(static)
-    for (int i = 0; i < n_nodes; i++) {
-      const HNode& hn = trees[group[i].tree].pool[group[i].pool];
-      kern::GroupNode& d = gn[i];
-      d.seg_start = 0;
-      d.seg_len = 0;
-      d.buf = 0;
-      d.seg_slot = hn.slot;
-      d.n_tiles = mine(group[i].tree) ? std::max<uint32_t>(1, (hn.ub + tile_len - 1) / tile_len) : 0;
+    // staging layout: [GroupNode n][node_feat n*f_sub][node_info n][tile_node tiles][tile_q tiles], written in place
+    // (pinned); node_info = level | "this rank partitions the node" for decide_flags_kernel
+    const size_t off_feat = align_up(sizeof(kern::GroupNode) * (size_t)n_nodes, 16);
+    const size_t off_info = align_up(off_feat + (size_t)n_nodes * f_sub * 4, 16);
+    const size_t off_tiles = align_up(off_info + (size_t)n_nodes * 4, 16);
+    {
+      const size_t tiles_bound = (size_t)n_nodes + (size_t)(total_entries / tile_len) + 1;
+      const size_t bound = align_up(off_tiles + tiles_bound * 4, 16) + tiles_bound * 4;
+      CU(c->h_group.ensure(bound));
+      CU(c->d_group.ensure(bound));
+    }
+    kern::GroupNode* gn = (kern::GroupNode*)c->h_group.p;
+    // the partition grid's upper bound: every node that may still split, tiled by its entry bound
+    uint64_t ptiles_ub64 = 0;
+    {
+      uint32_t* info = (uint32_t*)((char*)c->h_group.p + off_info);
+      int32_t* feat_out = (int32_t*)((char*)c->h_group.p + off_feat);
+#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : ptiles_ub64)
+      for (int i = 0; i < n_nodes; i++) {
+        const HNode& hn = trees[group[i].tree].pool[group[i].pool];
+        const bool m = mine(group[i].tree);
+        kern::GroupNode& d = gn[i];
+        d.seg_start = 0;
+        d.seg_len = 0;
+        d.buf = 0;
+        d.seg_slot = hn.slot;
+        d.n_tiles = m ? std::max<uint32_t>(1, (hn.ub + tile_len - 1) / tile_len) : 0;
+        const int level = 31 - __builtin_clz((unsigned)hn.id);
+        info[i] = (uint32_t)level | (m ? kern::kInfoMine : 0u);
+        if (m && level < P.max_depth) ptiles_ub64 += (hn.ub + kern::kPartTile - 1) / kern::kPartTile;
+        memcpy(feat_out + (size_t)i * f_sub, group_feat.data() + group[i].feat_at, (size_t)f_sub * 4);
+      }
     }
     uint32_t n_tiles = 0;
     int n_slots = 0;
@@ -1473,31 +1518,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       d.slot = ((row_sharded && !push_mode) || d.n_tiles > 1) ? n_slots++ : -1;
       n_tiles += d.n_tiles;
     }
-    const size_t off_feat = align_up(sizeof(kern::GroupNode) * (size_t)n_nodes, 16);
-    const size_t off_info = align_up(off_feat + (size_t)n_nodes * f_sub * 4, 16);
-    const size_t off_tiles = align_up(off_info + (size_t)n_nodes * 4, 16);
     const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
     const size_t group_bytes = l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4;
-    CU(c->h_group.ensure(group_bytes));
-    CU(c->d_group.ensure(group_bytes));
-    memcpy(c->h_group.p, gn.data(), sizeof(kern::GroupNode) * (size_t)n_nodes);
-    memcpy((char*)c->h_group.p + off_feat, group_feat.data(), (size_t)n_nodes * f_sub * 4);
-    // node_info for decide_kernel (level, "this rank partitions the node") and the partition grid's upper
-    // bound: every node that may still split, tiled by its entry bound
-    uint64_t ptiles_ub64 = 0;
-    {
-      uint32_t* info = (uint32_t*)((char*)c->h_group.p + off_info);
-#pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : ptiles_ub64)
-      for (int i = 0; i < n_nodes; i++) {
-        const HNode& hn = trees[group[i].tree].pool[group[i].pool];
-        const int level = 31 - __builtin_clz((unsigned)hn.id);
-        const bool m = mine(group[i].tree);
-        info[i] = (uint32_t)level | (m ? kern::kInfoMine : 0u);
-        if (m && level < P.max_depth) ptiles_ub64 += (hn.ub + kern::kPartTile - 1) / kern::kPartTile;
-      }
-    }
-    if (ptiles_ub64 > 0x7fffffffull) return fail(EMRF_ERR_LIMIT, "too many partition tiles in one group");
-    const uint32_t ptiles_ub = (uint32_t)ptiles_ub64;
     {
       uint32_t* tn = (uint32_t*)((char*)c->h_group.p + off_tiles);
       if (!l2_blocked) {
@@ -1517,6 +1539,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           }
       }
     }
+    if (ptiles_ub64 > 0x7fffffffull) return fail(EMRF_ERR_LIMIT, "too many partition tiles in one group");
+    const uint32_t ptiles_ub = (uint32_t)ptiles_ub64;
     // record block: [ScanResult r][left r*C][total r*C][decision word n]
     const size_t n_rec = (size_t)n_nodes * n_chunks;
     const size_t res_left = align_up(sizeof(kern::ScanResult) * n_rec, 16);
@@ -1526,10 +1550,22 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(c->d_results.ensure(res_bytes));
     char* h_res = (char*)c->arena_alloc(res_bytes);   // kept until the forest is exported
     if (!h_res) return fail(EMRF_ERR_CUDA, "out of pinned host memory for the split-record arena");
-    CU(c->d_tickets.ensure(n_rec * 4));
+    // single GPU: the HBM histogram slots and tickets a group dirtied are cleared right behind its partition
+    // kernels (while the host schedules), not in front of the next histogram launch; zeroed in full once per
+    // fit and whenever they grow
+    const bool self_clean = (c->world == 1);
+    {
+      const void* pt = c->d_tickets.p;
+      CU(c->d_tickets.ensure(n_rec * 4));
+      if (self_clean && (c->d_tickets.p != pt || !tickets_zeroed)) { CU(cudaMemsetAsync(c->d_tickets.p, 0, c->d_tickets.bytes, st)); tickets_zeroed = true; }
+    }
     const int nodes_per_rank = row_sharded ? (n_nodes + c->world - 1) / c->world : 0;
     const int n_slots_alloc = (row_sharded && !push_mode) ? nodes_per_rank * c->world : n_slots;
-    CU(c->d_ghist.ensure((size_t)std::max(n_slots_alloc, 1) * slot_words * 4));
+    {
+      const void* pg = c->d_ghist.p;
+      CU(c->d_ghist.ensure((size_t)std::max(n_slots_alloc, 1) * slot_words * 4));
+      if (self_clean && (c->d_ghist.p != pg || !ghist_zeroed)) { CU(cudaMemsetAsync(c->d_ghist.p, 0, c->d_ghist.bytes, st)); ghist_zeroed = true; }
+    }
     // partition work of this group, written by decide_kernel: [SplitNode n][tile_node ptiles_ub] and
     // [tile_left ptiles_ub][n_left n][limits 2]
     const size_t off_ptn = align_up(sizeof(kern::SplitNode) * (size_t)n_nodes, 16);
@@ -1559,9 +1595,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaMemcpyAsync(c->d_group.p, c->h_group.p, group_bytes, cudaMemcpyHostToDevice, st));
     tm.h2d_bytes += (int64_t)group_bytes;
     tm.d2h_bytes += (int64_t)res_bytes;
-    CU(cudaMemsetAsync(c->d_tickets.p, 0, n_rec * 4, st));
+    if (!self_clean) CU(cudaMemsetAsync(c->d_tickets.p, 0, n_rec * 4, st));
     if (c->world > 1) CU(cudaMemsetAsync(c->d_results.p, 0, res_bytes, st));
-    if (n_slots_alloc) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots_alloc * slot_words * 4, st));
+    if (n_slots_alloc && !self_clean) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots_alloc * slot_words * 4, st));
     kern::HistArgs A{};
     A.ent0 = d_ent[0]->as<uint64_t>();
     A.ent1 = d_ent[1]->as<uint64_t>();
@@ -1687,6 +1723,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       part_ev.emplace_back(p0, p1);
       CU(cudaGetLastError());
     }
+    if (self_clean) {
+      CU(cudaMemsetAsync(c->d_tickets.p, 0, n_rec * 4, st));
+      if (n_slots_alloc) CU(cudaMemsetAsync(c->d_ghist.p, 0, (size_t)n_slots_alloc * slot_words * 4, st));
+    }
     lap(1);
     // ---- bookkeeping nobody waits for, done while the GPU works: the previous group's node statistics, this
     // group's trace
@@ -1781,7 +1821,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     for (size_t q = 0; q < cur->trees_seen.size(); q++) tree_slot[cur->trees_seen[q]] = (int)q;
     const std::vector<int> order = hl::group_tree_visit_order(cur->trees_seen);
     for (int t : order)
-      for (int gi : cur->nodes_for_tree[tree_slot[t]]) {
+      for (int at = cur->tree_off[tree_slot[t]]; at < cur->tree_off[tree_slot[t] + 1]; at++) {
+        const int gi = cur->tree_nodes[at];
         const Decision& dc = decisions[gi];
         if (dc.left_pool < 0) continue;
         if (!dc.l_leaf) stack.emplace_back(t, dc.left_pool);

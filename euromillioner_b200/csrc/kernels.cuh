@@ -1569,41 +1569,44 @@ __global__ void __launch_bounds__(256) decide_flags_kernel(const DecideArgs A) {
   A.out_sched[gi] = make_uint4(dec, r.left_weight, r.total_weight, fs);
   A.out_tiles[gi] = tiles;
 }
-// step 2, one CTA: numbering in group order (block scans over chunks of 1024 nodes) and the partition work
+// step 2, one CTA: numbering in group order and the partition work.  Every thread owns a contiguous run of
+// nodes: it totals its run, one block scan orders the runs, and a second walk over the run writes the work.
 __global__ void __launch_bounds__(1024) decide_scan_kernel(const DecideArgs A) {
   __shared__ uint32_t sh_a[32], sh_b[32], sh_t[32];
-  __shared__ uint32_t carry[3];
   const int tid = threadIdx.x, lane = tid & 31, wv = tid >> 5;
-  if (tid < 3) carry[tid] = 0;
+  const int per = (A.n_nodes + 1023) / 1024;
+  const int lo = min(tid * per, A.n_nodes), hi = min(lo + per, A.n_nodes);
+  uint32_t a = 0, b = 0, t = 0;
+  for (int gi = lo; gi < hi; gi++) {
+    const uint32_t dec = A.out_sched[gi].x;
+    a += (dec & kDecNonLeaf) ? 1u : 0u;
+    b += (dec & kDecSplit) ? 1u : 0u;
+    t += A.out_tiles[gi];
+  }
+  uint32_t ia = a, ib = b, it = t;
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t xa = __shfl_up_sync(0xffffffffu, ia, o), xb = __shfl_up_sync(0xffffffffu, ib, o),
+                   xt = __shfl_up_sync(0xffffffffu, it, o);
+    if (lane >= o) { ia += xa; ib += xb; it += xt; }
+  }
+  if (lane == 31) { sh_a[wv] = ia; sh_b[wv] = ib; sh_t[wv] = it; }
   __syncthreads();
-  for (int base = 0; base < A.n_nodes; base += 1024) {
-    const int gi = base + tid;
-    const uint4 sc = gi < A.n_nodes ? A.out_sched[gi] : make_uint4(0, 0, 0, 0);
-    const uint32_t dec = sc.x;
-    const uint32_t tiles = gi < A.n_nodes ? A.out_tiles[gi] : 0u;
-    // block-wide exclusive scans of (non-leaf, split, tiles)
-    uint32_t a = (dec & kDecNonLeaf) ? 1u : 0u, b = (dec & kDecSplit) ? 1u : 0u, t = tiles;
-    uint32_t ia = a, ib = b, it = t;
+  if (wv == 0) {
+    uint32_t va = sh_a[lane], vb = sh_b[lane], vt = sh_t[lane];
     for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t xa = __shfl_up_sync(0xffffffffu, ia, o), xb = __shfl_up_sync(0xffffffffu, ib, o),
-                     xt = __shfl_up_sync(0xffffffffu, it, o);
-      if (lane >= o) { ia += xa; ib += xb; it += xt; }
+      const uint32_t xa = __shfl_up_sync(0xffffffffu, va, o), xb = __shfl_up_sync(0xffffffffu, vb, o),
+                     xt = __shfl_up_sync(0xffffffffu, vt, o);
+      if (lane >= o) { va += xa; vb += xb; vt += xt; }
     }
-    if (lane == 31) { sh_a[wv] = ia; sh_b[wv] = ib; sh_t[wv] = it; }
-    __syncthreads();
-    if (wv == 0) {
-      uint32_t va = sh_a[lane], vb = sh_b[lane], vt = sh_t[lane];
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t xa = __shfl_up_sync(0xffffffffu, va, o), xb = __shfl_up_sync(0xffffffffu, vb, o),
-                       xt = __shfl_up_sync(0xffffffffu, vt, o);
-        if (lane >= o) { va += xa; vb += xb; vt += xt; }
-      }
-      sh_a[lane] = va; sh_b[lane] = vb; sh_t[lane] = vt;   // inclusive over warps
-    }
-    __syncthreads();
-    const uint32_t wa = wv ? sh_a[wv - 1] : 0u, wb = wv ? sh_b[wv - 1] : 0u, wt = wv ? sh_t[wv - 1] : 0u;
-    const uint32_t ea = carry[0] + wa + ia - a, eb = carry[1] + wb + ib - b, et = carry[2] + wt + it - t;
-    if (dec & kDecSplit) {
+    sh_a[lane] = va; sh_b[lane] = vb; sh_t[lane] = vt;   // inclusive over warps
+  }
+  __syncthreads();
+  uint32_t ea = (wv ? sh_a[wv - 1] : 0u) + ia - a, eb = (wv ? sh_b[wv - 1] : 0u) + ib - b, et = (wv ? sh_t[wv - 1] : 0u) + it - t;
+  if (tid == 1023) { A.out_limits[0] = eb + b; A.out_limits[1] = et + t; }
+  for (int gi = lo; gi < hi; gi++) {
+    const uint4 sc = A.out_sched[gi];
+    if (sc.x & kDecSplit) {
+      const uint32_t tiles = A.out_tiles[gi];
       SplitNode sn;
       sn.seg_start = 0; sn.seg_len = 0; sn.buf = 0;       // the kernels take the segment from the table
       sn.tile_begin = et; sn.n_tiles = tiles;
@@ -1611,12 +1614,10 @@ __global__ void __launch_bounds__(1024) decide_scan_kernel(const DecideArgs A) {
       sn.seg_slot = A.nodes[gi].seg_slot; sn.left_slot = A.next_slot + 2 * ea; sn.right_slot = sn.left_slot + 1; sn.pad = 0;
       A.out_splits[eb] = sn;
       for (uint32_t q = 0; q < tiles; q++) A.out_tile_node[et + q] = eb;
+      eb++; et += tiles;
     }
-    __syncthreads();
-    if (tid == 1023) { carry[0] = ea + a; carry[1] = eb + b; carry[2] = et + t; }
-    __syncthreads();
+    if (sc.x & kDecNonLeaf) ea++;
   }
-  if (tid == 0) { A.out_limits[0] = carry[1]; A.out_limits[1] = carry[2]; }
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -204,9 +204,6 @@ struct HNode {
   int32_t pred = 0;   // first index of the largest class count (from the scan kernel)
   int32_t feature = -1, split_bin = -1;
   double threshold = 0.0, gain = std::numeric_limits<double>::quiet_NaN(), impurity = 0.0;
-  uint32_t slot = 0;   // index of the node's entry segment in the device segment table
-  uint32_t ub = 0;     // upper bound on the segment's length (exact for roots and when rows are sharded)
-  uint32_t weight = 0xffffffffu;   // sum of the node's class counts (roots: an upper bound)
   // class counts = cnt_a[c] - (cnt_b ? cnt_b[c] : 0); both point into the fit's result arena (the
   // split records copied back from the device): a left child shares its parent's "left" array, a
   // right child is parent total minus parent left, a node that went through a group owns its totals.
@@ -970,8 +967,49 @@ static void ensure_double_stats(emrf_forest* f) {
 // ---------------------------------------------------------------------------------------------
 // emrf_fit
 // ---------------------------------------------------------------------------------------------
-struct GroupEntry {
-  int tree, pool;
+// growable array of trivially copyable T that never value-initialises (the scheduler's per-group arrays are
+// overwritten in full every group; zero-filling them first is a measurable part of the host's critical path)
+template <class T>
+class PodVec {
+ public:
+  PodVec() = default;
+  PodVec(const PodVec&) = delete;
+  PodVec& operator=(const PodVec&) = delete;
+  ~PodVec() { free(p_); }
+  size_t size() const { return n_; }
+  bool empty() const { return n_ == 0; }
+  void clear() { n_ = 0; }
+  void resize(size_t n) {
+    if (n > cap_) {
+      const size_t cap = std::max(n, cap_ * 2);
+      T* q = (T*)realloc((void*)p_, cap * sizeof(T));
+      if (!q) throw std::bad_alloc();
+      p_ = q; cap_ = cap;
+    }
+    n_ = n;
+  }
+  T* data() { return p_; }
+  const T* data() const { return p_; }
+  T& operator[](size_t i) { return p_[i]; }
+  const T& operator[](size_t i) const { return p_[i]; }
+  T* begin() { return p_; }
+  T* end() { return p_ + n_; }
+  const T* begin() const { return p_; }
+  const T* end() const { return p_ + n_; }
+ private:
+  T* p_ = nullptr;
+  size_t n_ = 0, cap_ = 0;
+};
+// What the scheduler knows about a node that waits on the stack or sits in a group — everything selection and
+// staging need, so that neither touches the tree pools (their nodes are filled in later, off the critical path).
+struct StackEnt {
+  int32_t tree, pool;   // pool index of the node inside its tree
+  int32_t id, level;    // Spark node id (1 = root) and its depth
+  uint32_t slot;        // index of the node's entry segment in the device segment table
+  uint32_t ub;          // upper bound on the segment's length (exact for roots and when rows are sharded)
+  uint32_t weight;      // sum of the node's class counts (roots: an upper bound)
+};
+struct GroupEntry : StackEnt {
   int feat_at;  // index into the group's feature array
 };
 
@@ -1248,10 +1286,6 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     trees[t].pool.clear();
     trees[t].pool.reserve(pool_reserve);
     trees[t].pool.emplace_back();
-    HNode& r = trees[t].pool[0];
-    r.slot = (uint32_t)t;
-    r.ub = (uint32_t)tree_total[t];
-    r.weight = (uint32_t)std::min<uint64_t>(tree_total[t] * (uint64_t)std::max(bag_maxw, 1), 0xffffffffull);   // upper bound
   }
   // device segment table: roots now, children written by the partition kernels
   size_t seg_cap = std::max<size_t>((size_t)1 << 18, (size_t)4 * T);
@@ -1265,9 +1299,16 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaStreamSynchronize(st));
   }
   std::vector<uint32_t> hist_slots;   // slot of every node this rank built a histogram for (exact stats at the end)
-  std::vector<std::pair<int, int>> stack;
+  std::vector<StackEnt> stack;
   stack.reserve(1024);
-  for (int t = 0; t < T; t++) stack.emplace_back(t, 0);
+  for (int t = 0; t < T; t++) {
+    StackEnt r;
+    r.tree = t; r.pool = 0; r.id = 1; r.level = 0;
+    r.slot = (uint32_t)t;
+    r.ub = (uint32_t)tree_total[t];
+    r.weight = (uint32_t)std::min<uint64_t>(tree_total[t] * (uint64_t)std::max(bag_maxw, 1), 0xffffffffull);   // upper bound
+    stack.push_back(r);
+  }
   const int64_t max_mem = (int64_t)P.max_memory_mb * 1024ll * 1024ll;
   int64_t all_feat_bins = 0;
   for (int f = 0; f < F; f++) all_feat_bins += num_bins[f];
@@ -1279,13 +1320,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   // A group as selectNodesToSplit leaves it: popped nodes in pop order, their feature subsets, the
   // trees in first-seen order (= mutable.HashMap insertion order) and each tree's nodes.
   struct GroupSel {
-    std::vector<GroupEntry> group;
-    std::vector<int32_t> feat;
+    PodVec<GroupEntry> group;
+    PodVec<int32_t> feat;
+    PodVec<int32_t> tree_of;     // group[i].tree, compact (the per-tree lists below are built from it)
     std::vector<int> trees_seen;
     std::vector<int> tree_off, tree_nodes, tree_fill;   // CSR: nodes (group indices) of trees_seen[q], in pop order
-    uint64_t total_ub = 0;   // entry bounds of this rank's nodes, summed
-    uint32_t max_w = 0;      // heaviest of this rank's nodes
-    void clear() { group.clear(); feat.clear(); trees_seen.clear(); tree_off.clear(); tree_nodes.clear(); total_ub = 0; max_w = 0; }
+    void clear() { group.clear(); feat.clear(); tree_of.clear(); trees_seen.clear(); tree_off.clear(); tree_nodes.clear(); }
   };
   GroupSel sel_a, sel_b;
   GroupSel* cur = &sel_a;
@@ -1330,42 +1370,37 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       const size_t g0 = G.group.size();
       G.group.resize(g0 + k);
       G.feat.resize((g0 + k) * (size_t)f_sub);
-      uint64_t tot = 0;
-      uint32_t mw = 0;
+      G.tree_of.resize(g0 + k);
       const int nt = k >= 1024 ? c->host_threads : 1;
       (void)nt;
-#pragma omp parallel for num_threads(nt) schedule(static) reduction(+ : tot) reduction(max : mw)
+#pragma omp parallel for num_threads(nt) schedule(static)
       for (size_t i = 0; i < k; i++) {
-        const auto top = stack[s_top - 1 - i];
-        G.group[g0 + i] = {top.first, top.second, (int)((g0 + i) * (size_t)f_sub)};
+        GroupEntry& ge = G.group[g0 + i];
+        static_cast<StackEnt&>(ge) = stack[s_top - 1 - i];
+        ge.feat_at = (int)((g0 + i) * (size_t)f_sub);
+        G.tree_of[g0 + i] = ge.tree;
         int32_t* fo_ = G.feat.data() + (g0 + i) * (size_t)f_sub;
         if (subsampling) memcpy(fo_, tab + (at0 + i) * (size_t)f_sub, (size_t)f_sub * 4);
         else for (int q = 0; q < F; q++) fo_[q] = q;
-        if (mine(top.first)) {
-          const HNode& hn = trees[top.first].pool[top.second];
-          tot += hn.ub;
-          mw = std::max(mw, hn.weight);
-        }
       }
-      G.total_ub += tot;
-      G.max_w = std::max(G.max_w, mw);
       stack.resize(s_top - k);
       if (subsampling) draw_idx += (int64_t)k + (rejected ? 1 : 0);
     }
     // trees in first-seen order (= mutable.HashMap insertion order) and each tree's nodes in pop order
     const int n = (int)G.group.size();
+    const int32_t* tof = G.tree_of.data();
     for (int i = 0; i < n; i++) {
-      const int t = G.group[i].tree;
+      const int t = tof[i];
       if (tree_slot[t] < 0) { tree_slot[t] = (int)G.trees_seen.size(); G.trees_seen.push_back(t); }
     }
     G.tree_off.assign(G.trees_seen.size() + 1, 0);
-    for (int i = 0; i < n; i++) G.tree_off[tree_slot[G.group[i].tree] + 1]++;
+    for (int i = 0; i < n; i++) G.tree_off[tree_slot[tof[i]] + 1]++;
     for (size_t q = 0; q < G.trees_seen.size(); q++) G.tree_off[q + 1] += G.tree_off[q];
     G.tree_nodes.resize(n);
     {
       std::vector<int>& fill = G.tree_fill;
       fill.assign(G.tree_off.begin(), G.tree_off.end() - 1);
-      for (int i = 0; i < n; i++) G.tree_nodes[fill[tree_slot[G.group[i].tree]]++] = i;
+      for (int i = 0; i < n; i++) G.tree_nodes[fill[tree_slot[tof[i]]]++] = i;
     }
     for (int t : G.trees_seen) tree_slot[t] = -1;   // slots are recomputed by whoever consumes the group
   };
@@ -1380,12 +1415,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   // the records and decision words on the second stream, builds the tree nodes and children under the
   // partition kernels, and must only have the next group's launch ready by the time they end.
   if (n_chunks > 255) return fail(EMRF_ERR_LIMIT, "a node's histogram needs %d feature chunks (at most 255)", n_chunks);
-  struct Decision { int32_t left_pool; bool l_leaf, r_leaf; };
-  std::vector<Decision> decisions;
+  struct ChildPos { int l, r; uint32_t parent_ub; };   // rows sharded: where a split node's children went on the stack
+  std::vector<ChildPos> child_pos;
   struct Upd { uint32_t dec, slot_l, split_idx; int32_t left_pool; };
   std::vector<Upd> upd_vec;
-  struct SplitRef { int tree, pool; };
-  std::vector<SplitRef> split_ref_tmp;
   std::vector<int> pool_next(T, 0);
   bool tickets_zeroed = false, ghist_zeroed = false;   // per fit: another entry point may have used the buffers
   // Node statistics of a processed group (impurities, gain, split, class-count pointers, predictions): nothing in
@@ -1404,8 +1437,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const kern::ScanResult* res = (const kern::ScanResult*)pd.h_res;
     const uint32_t* res_leftc = (const uint32_t*)(pd.h_res + pd.res_left);
     const uint32_t* res_totalc = (const uint32_t*)(pd.h_res + pd.res_total);
-    const std::vector<GroupEntry>& group = pd.sel->group;
-    const std::vector<int32_t>& group_feat = pd.sel->feat;
+    const PodVec<GroupEntry>& group = pd.sel->group;
+    const PodVec<int32_t>& group_feat = pd.sel->feat;
     const Upd* upd = pd.upd.data();
     int64_t mism = 0;
 #pragma omp parallel for num_threads(pd.nt) schedule(static) reduction(+ : mism)
@@ -1445,8 +1478,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       if (is_leaf) continue;
       const int feat = group_feat[g.feat_at + r.k];
       n.feature = feat; n.split_bin = r.split; n.threshold = h_thr[(size_t)feat * TS + r.split];
-      HNode& l = tr.pool[n.left];
-      HNode& rn = tr.pool[n.right];
+      const int li = upd[gi].left_pool;        // the pool was grown when the group was numbered
+      n.left = li; n.right = li + 1;
+      HNode& l = *new (&tr.pool[li]) HNode();
+      HNode& rn = *new (&tr.pool[li + 1]) HNode();
+      l.id = 2 * n.id; l.is_leaf = (dw & kern::kDecLLeaf) != 0;
+      rn.id = 2 * n.id + 1; rn.is_leaf = (dw & kern::kDecRLeaf) != 0;
       l.impurity = limp; l.cnt_a = leftc; l.pred = r.left_pred;
       rn.impurity = rimp; rn.cnt_a = totc; rn.cnt_b = leftc; rn.pred = r.right_pred;
     }
@@ -1460,16 +1497,18 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   while (!cur->group.empty()) {
     double t_host0 = now_ms();
     lap(11);
-    std::vector<GroupEntry>& group = cur->group;
-    std::vector<int32_t>& group_feat = cur->feat;
+    PodVec<GroupEntry>& group = cur->group;
+    PodVec<int32_t>& group_feat = cur->feat;
     const int n_nodes = (int)group.size();
     const int nt_host = n_nodes >= 1024 ? c->host_threads : 1;   // OpenMP only where a group is worth a fork/join
     (void)nt_host;
     fo->group_sizes.push_back(n_nodes);
 
     // ---- tiles (tree-sharded multi-GPU: own trees only); sizes are upper bounds
-    const uint64_t total_entries = cur->total_ub;
-    const uint32_t max_weight = cur->max_w;
+    uint64_t total_entries = 0;     // entry bounds of this rank's nodes, summed; the heaviest of them
+    uint32_t max_weight = 0;
+    for (const GroupEntry& g : group)
+      if (mine(g.tree)) { total_entries += g.ub; max_weight = std::max(max_weight, g.weight); }
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
     // TreePoint matrix larger than L2: many small tiles, launched in row-range order (below), so that the
@@ -1495,15 +1534,15 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       int32_t* feat_out = (int32_t*)((char*)c->h_group.p + off_feat);
 #pragma omp parallel for num_threads(nt_host) schedule(static) reduction(+ : ptiles_ub64)
       for (int i = 0; i < n_nodes; i++) {
-        const HNode& hn = trees[group[i].tree].pool[group[i].pool];
-        const bool m = mine(group[i].tree);
+        const GroupEntry& hn = group[i];
+        const bool m = mine(hn.tree);
         kern::GroupNode& d = gn[i];
         d.seg_start = 0;
         d.seg_len = 0;
         d.buf = 0;
         d.seg_slot = hn.slot;
         d.n_tiles = m ? std::max<uint32_t>(1, (hn.ub + tile_len - 1) / tile_len) : 0;
-        const int level = 31 - __builtin_clz((unsigned)hn.id);
+        const int level = hn.level;
         info[i] = (uint32_t)level | (m ? kern::kInfoMine : 0u);
         if (m && level < P.max_depth) ptiles_ub64 += (hn.ub + kern::kPartTile - 1) / kern::kPartTile;
         memcpy(feat_out + (size_t)i * f_sub, group_feat.data() + group[i].feat_at, (size_t)f_sub * 4);
@@ -1741,7 +1780,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         const GroupEntry& g = group[i];
         int32_t* o = tr_out + (size_t)i * (2 + f_sub);
         o[0] = g.tree;
-        o[1] = trees[g.tree].pool[g.pool].id;
+        o[1] = g.id;
         for (int k = 0; k < f_sub; k++) o[2 + k] = group_feat[g.feat_at + k];
       }
       int64_t built = 0;
@@ -1760,7 +1799,6 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     t_host0 = now_ms();
     lap(3);
     const uint4* sched = (const uint4*)c->h_sched.p;
-    decisions.resize(n_nodes);
     upd_vec.resize(n_nodes);
     Upd* upd = upd_vec.data();
     for (int t : cur->trees_seen) pool_next[t] = (int)trees[t].pool.size();
@@ -1777,58 +1815,47 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     }
     for (int t : cur->trees_seen) trees[t].pool.resize_uninit((size_t)pool_next[t]);
     lap(5);
-    std::vector<SplitRef>& split_ref = split_ref_tmp;
     // rows sharded: the weight bound is global (world times too loose), so read the exact sizes back
     if (row_sharded && ns) {
       CU(c->h_part.ensure((size_t)ns * 8));
       CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
       tm.d2h_bytes += (int64_t)ns * 8;
-      split_ref.resize((size_t)ns);
+      child_pos.assign((size_t)ns, ChildPos{-1, -1, 0});
     }
-#pragma omp parallel for num_threads(nt_host) schedule(static)
-    for (int gi = 0; gi < n_nodes; gi++) {
-      const GroupEntry& g = group[gi];
-      const Upd& u = upd[gi];
-      if (!(u.dec & kern::kDecNonLeaf)) { decisions[gi] = Decision{-1, true, true}; continue; }
-      HTree& tr = trees[g.tree];
-      HNode& n = tr.pool[g.pool];
-      const bool l_leaf = (u.dec & kern::kDecLLeaf) != 0, r_leaf = (u.dec & kern::kDecRLeaf) != 0;
-      const int li = u.left_pool;
-      HNode& l = *new (&tr.pool[li]) HNode();
-      HNode& rn = *new (&tr.pool[li + 1]) HNode();
-      const uint32_t lw = sched[gi].y, tw = sched[gi].z;
-      l.id = 2 * n.id; l.is_leaf = l_leaf;
-      rn.id = 2 * n.id + 1; rn.is_leaf = r_leaf;
-      // a segment cannot hold more entries than its parent's, nor more than the node's total weight
-      // (every entry weighs >= 1): good enough to tile the next launches without reading sizes back
-      l.slot = u.slot_l; rn.slot = u.slot_l + 1;
-      l.ub = std::min(n.ub, lw);
-      rn.ub = std::min(n.ub, tw - lw);
-      l.weight = lw;
-      rn.weight = tw - lw;
-      n.left = li; n.right = li + 1;
-      decisions[gi] = Decision{li, l_leaf, r_leaf};
-      if (row_sharded && (u.dec & kern::kDecSplit)) split_ref[u.split_idx] = {g.tree, g.pool};
-    }
-    // the statistics of this group's nodes wait for the full records (consumed under the next group's kernels)
-    pending.sel = cur; pending.h_res = h_res; pending.res_left = res_left; pending.res_total = res_total;
-    pending.n_nodes = n_nodes; pending.rec_done = rec_done; pending.nt = nt_host;
-    std::swap(pending.upd, upd_vec);
-    { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
     lap(8);
-    // ---- children go on the stack in Scala map iteration order (tree by tree, nodes in pop order)
-    t_host0 = now_ms();
+    // ---- children go on the stack in Scala map iteration order (tree by tree, nodes in pop order), carrying their
+    // identity, segment slot and size bounds: a segment cannot hold more entries than its parent's, nor more than the
+    // node's total weight (every entry weighs >= 1) — good enough to tile the next launches without reading sizes back
     for (size_t q = 0; q < cur->trees_seen.size(); q++) tree_slot[cur->trees_seen[q]] = (int)q;
     const std::vector<int> order = hl::group_tree_visit_order(cur->trees_seen);
     for (int t : order)
       for (int at = cur->tree_off[tree_slot[t]]; at < cur->tree_off[tree_slot[t] + 1]; at++) {
         const int gi = cur->tree_nodes[at];
-        const Decision& dc = decisions[gi];
-        if (dc.left_pool < 0) continue;
-        if (!dc.l_leaf) stack.emplace_back(t, dc.left_pool);
-        if (!dc.r_leaf) stack.emplace_back(t, dc.left_pool + 1);
+        const Upd& u = upd[gi];
+        if (!(u.dec & kern::kDecNonLeaf)) continue;
+        const GroupEntry& par = group[gi];
+        const uint32_t lw = sched[gi].y, tw = sched[gi].z;
+        StackEnt ch;
+        ch.tree = t; ch.level = par.level + 1;
+        int pos_l = -1, pos_r = -1;
+        if (!(u.dec & kern::kDecLLeaf)) {
+          ch.pool = u.left_pool; ch.id = 2 * par.id; ch.slot = u.slot_l; ch.ub = std::min(par.ub, lw); ch.weight = lw;
+          pos_l = (int)stack.size();
+          stack.push_back(ch);
+        }
+        if (!(u.dec & kern::kDecRLeaf)) {
+          ch.pool = u.left_pool + 1; ch.id = 2 * par.id + 1; ch.slot = u.slot_l + 1; ch.ub = std::min(par.ub, tw - lw); ch.weight = tw - lw;
+          pos_r = (int)stack.size();
+          stack.push_back(ch);
+        }
+        if (row_sharded && (u.dec & kern::kDecSplit)) child_pos[u.split_idx] = ChildPos{pos_l, pos_r, par.ub};
       }
     for (int t : cur->trees_seen) tree_slot[t] = -1;
+    const size_t stack_before_select = stack.size();
+    // the tree nodes themselves (children included) are built from the full records one group later (fill_stats)
+    pending.sel = cur; pending.h_res = h_res; pending.res_left = res_left; pending.res_total = res_total;
+    pending.n_nodes = n_nodes; pending.rec_done = rec_done; pending.nt = nt_host;
+    std::swap(pending.upd, upd_vec);
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
     lap(9);
     // ---- the host selects the next group (needs only the stack) while the GPU partitions
@@ -1842,12 +1869,17 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     if (ns && row_sharded) {
       CU(cudaStreamSynchronize(st));
       t_host0 = now_ms();
+      // exact sizes of the children just created: they are either still on the stack or already in the next group
+      // (popped strictly from the top, so group index i holds what was at stack position stack_before_select - 1 - i)
       const uint64_t* nl = (const uint64_t*)c->h_part.p;
+      auto patch = [&](int pos, uint32_t v) {
+        if (pos < 0) return;
+        if ((size_t)pos < stack.size()) stack[pos].ub = v;
+        else nxt->group[stack_before_select - 1 - (size_t)pos].ub = v;
+      };
       for (int i = 0; i < ns; i++) {
-        HTree& tr = trees[split_ref[i].tree];
-        const HNode& n = tr.pool[split_ref[i].pool];
-        tr.pool[n.left].ub = (uint32_t)nl[i];
-        tr.pool[n.right].ub = n.ub - (uint32_t)nl[i];
+        patch(child_pos[i].l, (uint32_t)nl[i]);
+        patch(child_pos[i].r, child_pos[i].parent_ub - (uint32_t)nl[i]);
       }
       { const double d_ = now_ms() - t_host0; host_ms += d_; host_upd += d_; }
     }

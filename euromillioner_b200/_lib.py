@@ -81,6 +81,7 @@ def lib():
     L.emrf_forest_trace.argtypes = [vp, vp, vp]
     L.emrf_forest_feature_importances.argtypes = [vp, vp]
     L.emrf_predict.argtypes = [vp, vp, vp, i64, vp, vp, vp]
+    L.emrf_predict_thresholds.argtypes = [vp, vp, vp, i64, vp, vp, vp, vp]
     L.emrf_find_splits.argtypes = [vp, P(EmrfParams), vp, i64, i32, P(i64), i32, vp, vp]
     L.emrf_find_splits_sample_rows.argtypes = [P(EmrfParams), i64, P(i64), i32, vp, i64]
     L.emrf_find_splits_sample_rows.restype = i64

@@ -193,6 +193,33 @@ class RandomForestClassifier:
     def setCheckpointInterval(self, v):  # accepted; only meaningful with cacheNodeIds in Spark
         self.checkpointInterval = int(v); return self
 
+    def setThresholds(self, v):
+        """ProbabilisticClassifierParams.thresholds: one value per class, all >= 0, at most one 0; the model then
+        predicts the class with the largest probability / threshold."""
+        t = None if v is None else [float(x) for x in v]
+        if t is not None:
+            if any(not (x >= 0.0) for x in t):
+                raise ValueError("thresholds must all be >= 0")
+            if sum(1 for x in t if x == 0.0) > 1:
+                raise ValueError("at most one threshold may be 0")
+        self._thresholds = t
+        return self
+
+    def setFeaturesCol(self, v):       # column names are accepted for source compatibility; a Dataset here has one
+        return self                    # features matrix and one label vector
+
+    def setLabelCol(self, v):
+        return self
+
+    def setPredictionCol(self, v):
+        return self
+
+    def setRawPredictionCol(self, v):
+        return self
+
+    def setProbabilityCol(self, v):
+        return self
+
     def setNumClasses(self, v):        # stands in for label-column NominalAttribute metadata
         self.numClasses = int(v); return self
 
@@ -231,7 +258,14 @@ class RandomForestClassifier:
         else:
             check(L.emrf_fit(ctx.h, C.byref(p), dataset._fptr(), dataset._lptr(), dataset.n_rows, dataset.n_features,
                              po.ctypes.data_as(C.POINTER(C.c_int64)), len(po) - 1, C.byref(h)))
-        return RandomForestClassificationModel(ctx, h)
+        model = RandomForestClassificationModel(ctx, h)
+        thr = getattr(self, "_thresholds", None)
+        if thr is not None:          # copyValues(model): the estimator's thresholds travel to the model
+            if len(thr) != model.numClasses:   # Spark checks this in train(): require(thresholds.length == numClasses)
+                raise ValueError(f"RandomForestClassifier.train() called with non-matching numClasses and thresholds.length. "
+                                 f"numClasses={model.numClasses}, but thresholds has length {len(thr)}")
+            model._thresholds = list(thr)
+        return model
 
 
 class RandomForestClassificationModel:
@@ -245,6 +279,12 @@ class RandomForestClassificationModel:
         self.numTrees, self.numClasses, self.numFeatures, self.totalNumNodes = t.value, c.value, f.value, n.value
         self.treeWeights = [1.0] * self.numTrees
         self._export = None
+        self._thresholds = None
+
+    def setThresholds(self, v):
+        """ProbabilisticClassificationModel.setThresholds (validated like the estimator's)."""
+        RandomForestClassifier.setThresholds(self, v)
+        return self
 
     def __del__(self):
         try:
@@ -408,6 +448,14 @@ class RandomForestClassificationModel:
         rawp = np.zeros((n, Cn)) if raw else None
         prob = np.zeros((n, Cn)) if probability else None
         pred = np.zeros(n)
-        check(_lib.lib().emrf_predict(self._ctx.h, self._h, dataset._fptr(), n, _ptr(rawp), _ptr(prob), _ptr(pred)))
+        thr = getattr(self, "_thresholds", None)
+        if thr is None:
+            check(_lib.lib().emrf_predict(self._ctx.h, self._h, dataset._fptr(), n, _ptr(rawp), _ptr(prob), _ptr(pred)))
+        else:
+            if len(thr) != Cn:       # Spark: require(thresholds.length == numClasses)
+                raise ValueError(f"thresholds has length {len(thr)}, but the model has {Cn} classes")
+            t = np.ascontiguousarray(thr, np.float64)
+            check(_lib.lib().emrf_predict_thresholds(self._ctx.h, self._h, dataset._fptr(), n, _ptr(t), _ptr(rawp), _ptr(prob),
+                                                     _ptr(pred)))
         dataset.columns.update({"rawPrediction": rawp, "probability": prob, "prediction": pred})
         return dataset

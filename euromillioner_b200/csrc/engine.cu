@@ -2180,18 +2180,33 @@ static int forest_to_device(emrf_ctx* c, emrf_forest* f) {
   return EMRF_OK;
 }
 
-extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* features_hd, int64_t N, double* raw_hd,
-                            double* prob_hd, double* pred_hd) {
+static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* features_hd, int64_t N, double* raw_hd,
+                        double* prob_hd, double* pred_hd, const double* thresholds_h) {
   if (!c || !f_in || !features_hd) return fail(EMRF_ERR_ARG, "NULL argument");
   if (N < 0) return fail(EMRF_ERR_ARG, "negative row count");
-  if (N == 0) return EMRF_OK;
   emrf_forest* f = const_cast<emrf_forest*>(f_in);
+  const int C = f->num_classes, F = f->num_features;
+  if (thresholds_h) {   // ProbabilisticClassifierParams.setThresholds: all >= 0, at most one 0
+    int zeros = 0;
+    for (int q = 0; q < C; q++) {
+      if (!(thresholds_h[q] >= 0.0)) return fail(EMRF_ERR_ARG, "thresholds must all be >= 0 (class %d: %g)", q, thresholds_h[q]);
+      zeros += thresholds_h[q] == 0.0;
+    }
+    if (zeros > 1) return fail(EMRF_ERR_ARG, "at most one threshold may be 0 (%d are)", zeros);
+  }
+  if (N == 0) return EMRF_OK;
   CU(cudaSetDevice(c->device));
   TRY(forest_to_device(c, f));
-  const int C = f->num_classes, F = f->num_features;
   cudaStream_t st;
   CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
   struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamDestroy(s); } } sg{st};
+  DevBuf dThr;
+  const double* d_thresholds = nullptr;
+  if (thresholds_h) {
+    CU(dThr.alloc((size_t)C * 8));
+    CU(cudaMemcpyAsync(dThr.p, thresholds_h, (size_t)C * 8, cudaMemcpyHostToDevice, st));
+    d_thresholds = dThr.as<double>();
+  }
   const bool x_dev = is_device_ptr(features_hd);
   const bool raw_dev = raw_hd && is_device_ptr(raw_hd), prob_dev = prob_hd && is_device_ptr(prob_hd),
              pred_dev = pred_hd && is_device_ptr(pred_hd);
@@ -2235,12 +2250,12 @@ extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f_in, const doub
       const unsigned wgrid = (unsigned)((n + kern::kPredWarps * 32 - 1) / (kern::kPredWarps * 32));
       kern::predict_walk_kernel<<<wgrid, kern::kPredWarps * 32, walk_smem, st>>>(
           dBins.as<uint8_t>(), Fp, n, f->d_wnodes.as<kern::WalkNode>(), f->d_wroots.as<int32_t>(), f->num_trees,
-          f->d_leaf_prob.as<double>(), C, raw, prob, pred);
+          f->d_leaf_prob.as<double>(), C, raw, prob, pred, d_thresholds);
     } else {
       const int64_t threads = n * 32;
       kern::predict_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(x, n, F, f->d_nodes.as<kern::DevNode>(),
                                                                            f->d_roots.as<int64_t>(), f->num_trees,
-                                                                           f->d_leaf_prob.as<double>(), C, raw, prob, pred);
+                                                                           f->d_leaf_prob.as<double>(), C, raw, prob, pred, d_thresholds);
     }
     CU(cudaGetLastError());
     if (raw_hd && !raw_dev) CU(cudaMemcpyAsync(raw_hd + r0 * C, raw, (size_t)n * C * 8, cudaMemcpyDeviceToHost, st));
@@ -2249,6 +2264,14 @@ extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f_in, const doub
     CU(cudaStreamSynchronize(st));
   }
   return EMRF_OK;
+}
+extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f, const double* features_hd, int64_t N, double* raw_hd,
+                            double* prob_hd, double* pred_hd) {
+  return predict_impl(c, f, features_hd, N, raw_hd, prob_hd, pred_hd, nullptr);
+}
+extern "C" int emrf_predict_thresholds(emrf_ctx_t* c, const emrf_forest_t* f, const double* features_hd, int64_t N,
+                                       const double* thresholds, double* raw_hd, double* prob_hd, double* pred_hd) {
+  return predict_impl(c, f, features_hd, N, raw_hd, prob_hd, pred_hd, thresholds);
 }
 
 // ---------------------------------------------------------------------------------------------

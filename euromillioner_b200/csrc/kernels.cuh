@@ -1788,7 +1788,8 @@ __global__ void __launch_bounds__(256) predict_kernel(const double* __restrict__
                                                       const int64_t* __restrict__ tree_root, int T,
                                                       const double* __restrict__ leaf_prob, int C,
                                                       double* __restrict__ raw, double* __restrict__ prob,
-                                                      double* __restrict__ pred) {
+                                                      double* __restrict__ pred,
+                                                      const double* __restrict__ thresholds = nullptr) {
   const int lane = threadIdx.x & 31;
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (row >= n_rows) return;
@@ -1831,6 +1832,20 @@ __global__ void __launch_bounds__(256) predict_kernel(const double* __restrict__
     s = __dadd_rn(s, v);
     if (c == 0 || v > best) { best = v; best_c = c; }
   }
+  if (thresholds) {   // probability2prediction: first maximum of probability(c) / thresholds(c), NaN never wins
+    double mx = -INFINITY;
+    best_c = 0;
+    for (int c = 0; c < C; c++) {
+      const int q = c >> 5;
+      double v = 0.0;
+#pragma unroll
+      for (int qq = 0; qq < kMaxClassSlots; qq++) if (qq == q) v = votes[qq];
+      v = __shfl_sync(0xffffffffu, v, c & 31);
+      const double pr = (s != 0.0) ? __ddiv_rn(v, s) : v;
+      const double scaled = __ddiv_rn(pr, thresholds[c]);
+      if (scaled > mx) { mx = scaled; best_c = c; }
+    }
+  }
   if (pred && lane == 0) pred[row] = (double)best_c;
   if (prob) {
 #pragma unroll
@@ -1868,7 +1883,8 @@ __global__ void __launch_bounds__(kPredWarps * 32) predict_walk_kernel(const uin
                                                                        const int32_t* __restrict__ tree_root, int T,
                                                                        const double* __restrict__ leaf_prob, int C,
                                                                        double* __restrict__ raw, double* __restrict__ prob,
-                                                                       double* __restrict__ pred) {
+                                                                       double* __restrict__ pred,
+                                                                       const double* __restrict__ thresholds = nullptr) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
   const int Cp = C | 1;                       // odd stride: "lane = row" accesses are conflict-free
@@ -1956,6 +1972,15 @@ __global__ void __launch_bounds__(kPredWarps * 32) predict_walk_kernel(const uin
       const double v = vr[c];
       s = __dadd_rn(s, v);
       if (c == 0 || v > best) { best = v; best_c = c; }
+    }
+    if (thresholds) {   // probability2prediction: first maximum of probability(c) / thresholds(c), NaN never wins
+      double mx = -INFINITY;
+      best_c = 0;
+      for (int c = 0; c < C; c++) {
+        const double pr = (s != 0.0) ? __ddiv_rn(vr[c], s) : vr[c];
+        const double scaled = __ddiv_rn(pr, thresholds[c]);
+        if (scaled > mx) { mx = scaled; best_c = c; }
+      }
     }
   }
   if (pred && lane < n_here) pred[r0 + lane] = (double)best_c;

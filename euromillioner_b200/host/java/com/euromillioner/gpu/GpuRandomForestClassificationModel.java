@@ -17,6 +17,13 @@ public final class GpuRandomForestClassificationModel implements AutoCloseable {
         numTrees = (int) i[0]; numClasses = (int) i[1]; numFeatures = (int) i[2]; totalNumNodes = i[3];
     }
     public double[] featureImportances() { return Native.featureImportances(forest); }
+    private double[] thresholds;   // ProbabilisticClassificationModel.thresholds (null = unset)
+    public GpuRandomForestClassificationModel setThresholds(double[] t) {
+        if (t != null && t.length != numClasses)
+            throw new IllegalArgumentException("thresholds has length " + t.length + ", but the model has " + numClasses + " classes");
+        thresholds = t == null ? null : t.clone();
+        return this;
+    }
 
     /** Returns {rawPrediction (N*C), probability (N*C), prediction (N)}. */
     public double[][] transform(double[] features) {
@@ -26,7 +33,8 @@ public final class GpuRandomForestClassificationModel implements AutoCloseable {
         ByteBuffer raw = ByteBuffer.allocateDirect((int) (n * numClasses * 8)).order(ByteOrder.nativeOrder());
         ByteBuffer prob = ByteBuffer.allocateDirect((int) (n * numClasses * 8)).order(ByteOrder.nativeOrder());
         ByteBuffer pred = ByteBuffer.allocateDirect((int) (n * 8)).order(ByteOrder.nativeOrder());
-        Native.predict(ctx, forest, fb, n, raw, prob, pred);
+        if (thresholds == null) Native.predict(ctx, forest, fb, n, raw, prob, pred);
+        else Native.predictThresholds(ctx, forest, fb, n, thresholds, raw, prob, pred);
         double[][] out = {new double[(int) (n * numClasses)], new double[(int) (n * numClasses)], new double[(int) n]};
         raw.asDoubleBuffer().get(out[0]); prob.asDoubleBuffer().get(out[1]); pred.asDoubleBuffer().get(out[2]);
         return out;

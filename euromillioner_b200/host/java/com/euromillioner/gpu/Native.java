@@ -27,4 +27,7 @@ final class Native {
     /** raw/prob: N*C doubles or null; pred: N doubles. Safe to call from several executor task threads. */
     static native void predict(long ctx, long forest, ByteBuffer features, long nRows, ByteBuffer raw, ByteBuffer prob,
                                ByteBuffer pred);
+    /** Same with ProbabilisticClassifierParams.thresholds (numClasses values, all >= 0, at most one 0). */
+    static native void predictThresholds(long ctx, long forest, ByteBuffer features, long nRows, double[] thresholds,
+                                         ByteBuffer raw, ByteBuffer prob, ByteBuffer pred);
 }

@@ -64,6 +64,17 @@ JNIEXPORT void JNICALL Java_com_euromillioner_gpu_Native_predict(JNIEnv* env, jc
                      prob ? (double*)env->GetDirectBufferAddress(prob) : nullptr,
                      pred ? (double*)env->GetDirectBufferAddress(pred) : nullptr), );
 }
+JNIEXPORT void JNICALL Java_com_euromillioner_gpu_Native_predictThresholds(JNIEnv* env, jclass, jlong ctx, jlong f, jobject features,
+                                                                           jlong n, jdoubleArray thresholds, jobject raw, jobject prob,
+                                                                           jobject pred) {
+  jdouble* t = env->GetDoubleArrayElements(thresholds, nullptr);
+  const int rc = emrf_predict_thresholds((emrf_ctx_t*)ctx, (emrf_forest_t*)f, (const double*)env->GetDirectBufferAddress(features), n, t,
+                                         raw ? (double*)env->GetDirectBufferAddress(raw) : nullptr,
+                                         prob ? (double*)env->GetDirectBufferAddress(prob) : nullptr,
+                                         pred ? (double*)env->GetDirectBufferAddress(pred) : nullptr);
+  env->ReleaseDoubleArrayElements(thresholds, t, JNI_ABORT);
+  CHECK(rc, );
+}
 // forestExport: ten GetPrimitiveArrayCritical / emrf_forest_export / Release pairs; omitted arrays are an error.
 JNIEXPORT void JNICALL Java_com_euromillioner_gpu_Native_forestExport(JNIEnv* env, jclass, jlong f, jlongArray treeOff, jintArray nodeId,
                                                                       jintArray left, jintArray right, jintArray feature, jdoubleArray thr,

@@ -154,6 +154,14 @@ int emrf_forest_feature_importances(const emrf_forest_t* f, double* out /* F */)
 int emrf_predict(emrf_ctx_t* ctx, const emrf_forest_t* f, const double* features_hd, int64_t n_rows,
                  double* raw_hd, double* prob_hd, double* pred_hd);
 
+/* Same, with ProbabilisticClassifierParams.thresholds set (Spark ML `setThresholds`; `[S]`
+ * ProbabilisticClassificationModel.raw2prediction -> probability2prediction): prediction = first index of the
+ * largest probability(c) / thresholds[c] (a class with threshold 0 and non-zero probability always wins; NaN
+ * never does).  `thresholds` is a HOST array of num_classes doubles, all >= 0 and at most one 0 (EMRF_ERR_ARG
+ * otherwise, as Spark's `require`); NULL = emrf_predict.  raw / probability outputs are unaffected. */
+int emrf_predict_thresholds(emrf_ctx_t* ctx, const emrf_forest_t* f, const double* features_hd, int64_t n_rows,
+                            const double* thresholds, double* raw_hd, double* prob_hd, double* pred_hd);
+
 /* ---- stage-level entry points (each kernel parity-checked alone) ---------------------------- */
 /* RandomForest.findSplits: thresholds_out[F*max_bins] (row f holds n_splits_out[f] values). */
 int emrf_find_splits(emrf_ctx_t* ctx, const emrf_params_t* params, const double* features_hd, int64_t n_rows,

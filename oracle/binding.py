@@ -133,16 +133,19 @@ class OracleForest:
         L.orc_forest_thresholds(C.c_void_p(self.h), C.c_int32(self.max_bins), _p(thr, C.c_double), _p(ns, C.c_int32))
         return thr, ns
 
-    def predict(self, X, want_raw=True, want_prob=True):
+    def predict(self, X, want_raw=True, want_prob=True, thresholds=None):
         L = lib()
         X = np.ascontiguousarray(X, np.float64)
         n = X.shape[0]
         raw = np.zeros((n, self.C)) if want_raw else None
         prob = np.zeros((n, self.C)) if want_prob else None
         pred = np.zeros(n)
-        L.orc_predict(C.c_void_p(self.h), _p(X, C.c_double), C.c_int64(n),
-                      _p(raw, C.c_double) if want_raw else None, _p(prob, C.c_double) if want_prob else None,
-                      _p(pred, C.c_double))
+        outs = (_p(raw, C.c_double) if want_raw else None, _p(prob, C.c_double) if want_prob else None, _p(pred, C.c_double))
+        if thresholds is None:
+            L.orc_predict(C.c_void_p(self.h), _p(X, C.c_double), C.c_int64(n), *outs)
+        else:
+            t = np.ascontiguousarray(thresholds, np.float64)
+            L.orc_predict_thresholds(C.c_void_p(self.h), _p(X, C.c_double), C.c_int64(n), _p(t, C.c_double), *outs)
         return raw, prob, pred
 
 

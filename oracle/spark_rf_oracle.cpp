@@ -864,7 +864,8 @@ static Forest* fit(const Params& p, const double* X, const double* y, int64_t N,
 }
 
 // RandomForestClassificationModel.predictRaw / raw2probabilityInPlace / argmax
-static void predict(const Forest& fo, const double* X, int64_t N, double* raw, double* prob, double* pred) {
+static void predict(const Forest& fo, const double* X, int64_t N, double* raw, double* prob, double* pred,
+                    const double* thresholds = nullptr) {
   const int C = fo.num_classes, F = fo.num_features;
 #pragma omp parallel for schedule(static)
   for (int64_t i = 0; i < N; i++) {
@@ -886,6 +887,16 @@ static void predict(const Forest& fo, const double* X, int64_t N, double* raw, d
       int mi = 0;
       double mv = votes[0];
       for (int c = 1; c < C; c++) if (votes[c] > mv) { mv = votes[c]; mi = c; }
+      if (thresholds) {  // raw2prediction with thresholds = probability2prediction(raw2probability(raw))
+        double s = counts_sum(votes.data(), C);
+        double mx = -std::numeric_limits<double>::infinity();
+        mi = 0;
+        for (int c = 0; c < C; c++) {
+          const double pr = (s != 0) ? votes[c] / s : votes[c];
+          const double scaled = pr / thresholds[c];
+          if (scaled > mx) { mx = scaled; mi = c; }
+        }
+      }
       pred[i] = (double)mi;
     }
     if (prob) {
@@ -1102,6 +1113,10 @@ void orc_forest_export(const void* h, int64_t* tree_off, int32_t* node_id, int32
     threshold[i] = n.threshold; gain[i] = n.gain; impurity[i] = n.impurity; prediction[i] = n.prediction;
   }
   memcpy(stats, f->stats.data(), f->stats.size() * 8);
+}
+void orc_predict_thresholds(const void* h, const double* X, int64_t N, const double* thresholds, double* raw, double* prob,
+                            double* pred) {
+  orc::predict(*(const orc::Forest*)h, X, N, raw, prob, pred, thresholds);
 }
 void orc_predict(const void* h, const double* X, int64_t N, double* raw, double* prob, double* pred) {
   orc::predict(*(const orc::Forest*)h, X, N, raw, prob, pred);

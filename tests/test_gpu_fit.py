@@ -134,6 +134,31 @@ def test_kernel_variants_match_oracle(oracle):
         assert r.returncode == 0 and "VARIANT_OK" in r.stdout, str(env) + r.stdout[-1500:] + r.stderr[-1500:]
 
 
+def test_thresholds_scale_the_prediction_like_spark(ctx, oracle):
+    """setThresholds: prediction = first maximum of probability / threshold (probability2prediction); a zero
+    threshold wins wherever its class has non-zero probability; raw and probability columns do not change."""
+    X, y = synth.flat(5000, 10, 4)
+    rf = RandomForestClassifier(ctx).setNumTrees(7).setMaxDepth(5).setNumClasses(4)
+    model = rf.fit(Dataset(X, y, num_partitions=4))
+    ofo = oracle.fit(oracle.make_params(num_trees=7, max_depth=5, num_classes=4), X, y, oracle.partition_offsets(5000, 4))
+    base = model.transform(Dataset(X)).columns
+    for thr in ([0.1, 0.4, 0.3, 0.2], [1.0, 0.0, 1.0, 1.0], [0.25, 0.25, 0.25, 0.25]):
+        got = model.setThresholds(thr).transform(Dataset(X)).columns
+        _, oprob, opred = ofo.predict(X, thresholds=thr)
+        assert np.array_equal(got["prediction"], opred)
+        assert np.array_equal(got["probability"], oprob) and np.array_equal(got["rawPrediction"], base["rawPrediction"])
+    assert not np.array_equal(model.setThresholds([0.1, 0.4, 0.3, 0.2]).transform(Dataset(X)).columns["prediction"], base["prediction"])
+    assert np.array_equal(model.setThresholds(None).transform(Dataset(X)).columns["prediction"], base["prediction"])
+    with pytest.raises(ValueError):
+        model.setThresholds([0.5, 0.5]).transform(Dataset(X))            # length != numClasses
+    with pytest.raises(ValueError):
+        RandomForestClassifier(ctx).setThresholds([0.0, 0.0, 1.0, 1.0])  # more than one zero
+    with pytest.raises(ValueError):
+        RandomForestClassifier(ctx).setThresholds([-1.0, 1.0, 1.0, 1.0])
+    with pytest.raises(ValueError, match="thresholds"):
+        RandomForestClassifier(ctx).setNumTrees(2).setNumClasses(4).setThresholds([0.5, 0.5]).fit(Dataset(X, y))
+
+
 def test_two_classes_and_empty_partitions(ctx, oracle):
     """Binary labels; a partition layout with empty partitions (their RNG streams are simply unused)."""
     X, y = synth.flat(6000, 12, 2)

@@ -2690,5 +2690,12 @@ extern "C" int emrf_debug_hist_prof(unsigned long long* out16) {
   CU(cudaMemcpyToSymbol(kern::g_hist_prof, z, sizeof(z)));
   return EMRF_OK;
 }
+extern "C" int emrf_debug_bag_prof(unsigned long long* out8) {
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpyFromSymbol(out8, kern::g_bag_prof, sizeof(unsigned long long) * 8));
+  unsigned long long z[8] = {0};
+  CU(cudaMemcpyToSymbol(kern::g_bag_prof, z, sizeof(z)));
+  return EMRF_OK;
+}
 #endif
 

@@ -229,6 +229,16 @@ __global__ void __launch_bounds__(32) bag_poisson_serial_kernel(int64_t seed, co
   atomicMax(max_w, mx);
 }
 
+#ifdef EMRF_HIST_PROF
+__device__ unsigned long long g_bag_prof[8];   // debug builds: 0 producer wait, 1 well_block, 2 consumer wait, 3 poisson_block, 4 emit+flush, 5 blocks
+#define BPROF_DECL long long bp_t = clock64(); unsigned long long bp_acc[6] = {0, 0, 0, 0, 0, 0};
+#define BPROF(i) do { const long long n_ = clock64(); bp_acc[i] += (unsigned long long)(n_ - bp_t); bp_t = n_; } while (0)
+#define BPROF_FLUSH() do { if (lane == 0) for (int i_ = 0; i_ < 6; i_++) if (bp_acc[i_]) atomicAdd(&g_bag_prof[i_], bp_acc[i_]); } while (0)
+#else
+#define BPROF_DECL
+#define BPROF(i)
+#define BPROF_FLUSH()
+#endif
 // ---- one WARP per partition ---------------------------------------------------------------
 // WELL19937c is linear over GF(2).  Writing a_n for the word a step stores (z3) and b_n for the
 // word it hands to the next step (z4 before tempering), every operand of step n except b_{n-1} is
@@ -241,8 +251,9 @@ __global__ void __launch_bounds__(32) bag_poisson_serial_kernel(int64_t seed, co
 // two steps from its carry-in and emits one nextDouble().  The Poisson loop itself (a running
 // product compared with exp(-mean)) stays sequential on lane 0; it reads the 32 uniforms of the
 // block from shared memory.  Bit-identical to the serial stream (tests/test_gpu_stages.py).
-constexpr int kBagPairs = 4;              // partitions per CTA: one producer warp + one consumer warp each
-constexpr int kBagWarps = 2 * kBagPairs;
+constexpr int kBagPairs = 4;              // partitions per CTA: a producer, a walker and an emitter warp each
+constexpr int kBagWarps = 3 * kBagPairs;
+constexpr int kBagStageRing = 4;          // blocks of draws the walker may run ahead of the emitter
 constexpr int kBagObuf = 1024;
 constexpr int kBagRing = 4;               // blocks of 32 uniforms the producer may run ahead
 __device__ __forceinline__ uint32_t well_M(uint32_t x) {
@@ -258,11 +269,15 @@ struct BagSmem {
   uint32_t lut[4][4][256];                 // (M^2)^(2^s) for s = 1..4, one table per input byte
   uint32_t state[kBagPairs][624];
   double ring[kBagPairs][kBagRing][32];    // producer → consumer: blocks of 32 nextDouble() values
-  uint8_t stage[kBagPairs][32][32];        // per lane: the draws of the run it owns in the current block
+  uint8_t stage[kBagPairs][kBagStageRing][32][32];   // walker → emitter: per lane, the draws of the run it owns in a block
+  uint8_t scnt[kBagPairs][kBagStageRing][32];        //   and how many there are
   uint8_t obuf[kBagPairs][kBagObuf];
   volatile uint32_t produced[kBagPairs];   // blocks written by the producer
-  volatile uint32_t consumed[kBagPairs];   // blocks released by the consumer
+  volatile uint32_t consumed[kBagPairs];   // blocks released by the walker
+  volatile uint32_t walked[kBagPairs];     // blocks of draws written by the walker
+  volatile uint32_t emitted[kBagPairs];    // blocks released by the emitter
   volatile uint32_t stop[kBagPairs];
+  volatile uint32_t ovf[kBagPairs];        // a draw above 255 was seen
 };
 __device__ __forceinline__ int well_wrap(int j) { return j >= 624 ? j - 624 : (j < 0 ? j + 624 : j); }
 
@@ -320,7 +335,8 @@ struct PoissonCarry {
   double r = 1.0;
   int n = 0;
 };
-__device__ __forceinline__ int poisson_block(double u, double p_exp, double limit, PoissonCarry& pc, uint8_t* stage, int lane,
+// `nlim` = smallest integer not below 1000*mean: for an integer n, (double)n < limit  <=>  n < nlim.
+__device__ __forceinline__ int poisson_block(double u, double p_exp, int nlim, PoissonCarry& pc, uint8_t* stage, int lane,
                                             int& overflow) {
   const uint32_t tmask = __ballot_sync(0xffffffffu, u < p_exp);
   const bool is_start = (lane == 0) || ((tmask >> (lane - 1)) & 1u);
@@ -336,7 +352,7 @@ __device__ __forceinline__ int poisson_block(double u, double p_exp, double limi
     if (t < len) {
       r = __dmul_rn(r, ut);
       bool emit;
-      if (r >= p_exp) { n++; emit = !((double)n < limit); } else emit = true;
+      if (r >= p_exp) { n++; emit = !(n < nlim); } else emit = true;
       if (emit) {
         if (n > 255) overflow = 1;                     // not representable: reported as an error by the host
         stage[cnt++] = (uint8_t)min(n, 255);
@@ -361,8 +377,8 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
   extern __shared__ __align__(16) uint8_t smem_raw[];
   BagSmem& S = *reinterpret_cast<BagSmem*>(smem_raw);
   const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
-  const int pair = wv >> 1;
-  const bool producer = (wv & 1) == 0;
+  const int pair = wv / 3;
+  const int role = wv - 3 * pair;          // 0 producer, 1 walker, 2 emitter
   for (int e = threadIdx.x; e < 4 * 4 * 256; e += blockDim.x) {
     const int sidx = e >> 10, tb = (e >> 8) & 3, v = e & 255;
     uint32_t x = (uint32_t)v << (8 * tb);
@@ -370,11 +386,14 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
     for (int i = 0; i < reps; i++) x = well_M(x);
     S.lut[sidx][tb][v] = x;
   }
-  if (threadIdx.x < kBagPairs) { S.produced[threadIdx.x] = 0; S.consumed[threadIdx.x] = 0; S.stop[threadIdx.x] = 0; }
+  if (threadIdx.x < kBagPairs) {
+    S.produced[threadIdx.x] = 0; S.consumed[threadIdx.x] = 0; S.walked[threadIdx.x] = 0; S.emitted[threadIdx.x] = 0;
+    S.stop[threadIdx.x] = 0; S.ovf[threadIdx.x] = 0;
+  }
   __syncthreads();
   const int part = blockIdx.x * kBagPairs + pair;
-  if (part >= n_parts) return;              // both warps of the pair leave together
-  if (producer) {
+  if (part >= n_parts) return;              // the three warps of the partition leave together
+  if (role == 0) {
     // ---- producer warp: WELL19937c, 32 uniforms per block into the ring
     uint32_t* A = S.state[pair];
     if (lane == 0) {  // AbstractWell.setSeed(long)
@@ -390,36 +409,63 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
     __syncwarp();
     uint32_t carry = A[0];
     int i0 = 0;
+    BPROF_DECL
     for (uint32_t blk = 0;; blk++) {
       while (blk - S.consumed[pair] >= (uint32_t)kBagRing) {
-        if (S.stop[pair]) return;
+        if (S.stop[pair]) { BPROF_FLUSH(); return; }
         __nanosleep(40);
       }
-      if (S.stop[pair]) return;
+      if (S.stop[pair]) { BPROF_FLUSH(); return; }
+      BPROF(0);
       const double u = well_block(A, S, carry, i0, lane);
       S.ring[pair][blk % kBagRing][lane] = u;
       __threadfence_block();
       __syncwarp();
       if (lane == 0) S.produced[pair] = blk + 1;
+      BPROF(1);
     }
-  } else {
-    // ---- consumer warp: Poisson draws, ordered compaction, coalesced flush
+  } else if (role == 1) {
+    // ---- walker warp: the Poisson product loops, all runs of a block in parallel; draws go to the stage ring
     const double limit = __dmul_rn(1000.0, mean);
-    const int64_t lo = part_off[part], hi = part_off[part + 1];
-    uint8_t* out = weights + (size_t)lo * T;
-    const int64_t total = (hi - lo) * (int64_t)T;
-    int64_t q = 0, flushed = 0;
-    int pos = 0, mx = 0, overflow = 0;
+    const int nlim = limit >= 2147483647.0 ? 2147483647 : (int)ceil(limit);
+    int overflow = 0;
     PoissonCarry pc;
-    uint8_t* stage = S.stage[pair][lane];
-    uint8_t* ob = S.obuf[pair];
-    for (uint32_t blk = 0; q < total; blk++) {
-      while (S.produced[pair] <= blk) __nanosleep(40);
+    BPROF_DECL
+    for (uint32_t blk = 0;; blk++) {
+      while (S.produced[pair] <= blk || blk - S.emitted[pair] >= (uint32_t)kBagStageRing) {
+        if (S.stop[pair]) { BPROF_FLUSH(); return; }
+        __nanosleep(40);
+      }
+      BPROF(2);
       __threadfence_block();
       const double u = S.ring[pair][blk % kBagRing][lane];
       __syncwarp();
       if (lane == 0) S.consumed[pair] = blk + 1;        // the value is in a register: the slot may be refilled
-      const int cnt = poisson_block(u, p_exp, limit, pc, stage, lane, overflow);
+      const int slot = blk % kBagStageRing;
+      const int cnt = poisson_block(u, p_exp, nlim, pc, S.stage[pair][slot][lane], lane, overflow);
+      S.scnt[pair][slot][lane] = (uint8_t)cnt;
+      if (overflow) S.ovf[pair] = 1;
+      __threadfence_block();
+      __syncwarp();
+      if (lane == 0) S.walked[pair] = blk + 1;
+      BPROF(3);
+    }
+  } else {
+    // ---- emitter warp: ordered compaction of the draws, coalesced flush
+    const int64_t lo = part_off[part], hi = part_off[part + 1];
+    uint8_t* out = weights + (size_t)lo * T;
+    const int64_t total = (hi - lo) * (int64_t)T;
+    int64_t q = 0, flushed = 0;
+    int pos = 0, mx = 0;
+    uint8_t* ob = S.obuf[pair];
+    BPROF_DECL
+    for (uint32_t blk = 0; q < total; blk++) {
+      while (S.walked[pair] <= blk) __nanosleep(40);
+      BPROF(0);
+      __threadfence_block();
+      const int slot = blk % kBagStageRing;
+      const uint8_t* stage = S.stage[pair][slot][lane];
+      const int cnt = S.scnt[pair][slot][lane];
       int excl = cnt;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -432,6 +478,8 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
       const int emit_total = (int)(remaining < (int64_t)total_cnt ? remaining : (int64_t)total_cnt);
       for (int k = 0; k < cnt; k++)
         if (excl + k < emit_total) { const uint8_t v = stage[k]; ob[pos + excl + k] = v; mx = max(mx, (int)v); }
+      __syncwarp();
+      if (lane == 0) S.emitted[pair] = blk + 1;         // the slot may be refilled
       pos += emit_total;
       q += emit_total;
       if (pos > kBagObuf - 32 || q >= total) {
@@ -441,11 +489,17 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
         pos = 0;
         __syncwarp();
       }
+      BPROF(4);
+#ifdef EMRF_HIST_PROF
+      bp_acc[5]++;
+#endif
     }
+    BPROF_FLUSH();
     if (lane == 0) S.stop[pair] = 1;
     mx = __reduce_max_sync(0xffffffffu, mx);
-    overflow = __any_sync(0xffffffffu, overflow);
-    if (lane == 0) atomicMax(max_w, overflow ? 256 : mx);
+    // (a draw above 255 in a block past the partition's end cannot set ovf before stop: the walker is at most
+    // kBagStageRing blocks ahead, and an overflow there would also be reported — harmless, it is an error either way)
+    if (lane == 0) atomicMax(max_w, S.ovf[pair] ? 256 : mx);
   }
 }
 // T == 1 without replacement and rate < 1: XORShiftRandom(seed+p+1).nextDouble() < rate

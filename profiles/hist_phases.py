@@ -24,3 +24,9 @@ for it in range(3):
     print(f"fit {it}: CTAs {buf[8]}, scanning CTAs {buf[9]}, cycles/CTA {tot / max(buf[8], 1):.0f}")
     print("  " + " | ".join(f"{n} {100.0 * buf[i] / tot:.1f}% ({buf[i] / max(buf[9] if i >= 4 else buf[8], 1):.0f} cyc)"
                             for i, n in enumerate(names)))
+    bb = (C.c_ulonglong * 8)()
+    L.emrf_debug_bag_prof(bb)
+    nb = max(bb[5], 1)
+    print("  bag kernel, cycles per block of 32 uniforms: producer wait %.0f, well_block %.0f | consumer wait %.0f, poisson_block %.0f, "
+          "emit+flush %.0f  (%d blocks)" % (bb[0] / nb, bb[1] / nb, bb[2] / nb, bb[3] / nb, bb[4] / nb, bb[5]))
+

@@ -1656,6 +1656,12 @@ __global__ void __launch_bounds__(1024) decide_scan_kernel(const DecideArgs A) {
   }
   __syncthreads();
   uint32_t ea = (wv ? sh_a[wv - 1] : 0u) + ia - a, eb = (wv ? sh_b[wv - 1] : 0u) + ib - b, et = (wv ? sh_t[wv - 1] : 0u) + it - t;
+  // nodes with many tiles (top levels) have their tile map entries written by a whole warp afterwards
+  constexpr int kBigMax = 512;
+  __shared__ uint32_t sh_big[kBigMax][3];
+  __shared__ uint32_t sh_nbig;
+  if (tid == 0) sh_nbig = 0;
+  __syncthreads();
   if (tid == 1023) { A.out_limits[0] = eb + b; A.out_limits[1] = et + t; }
   for (int gi = lo; gi < hi; gi++) {
     const uint4 sc = A.out_sched[gi];
@@ -1667,11 +1673,18 @@ __global__ void __launch_bounds__(1024) decide_scan_kernel(const DecideArgs A) {
       sn.feature = (int32_t)(sc.w & 0xffffffu); sn.split_bin = (int32_t)(sc.w >> 24);
       sn.seg_slot = A.nodes[gi].seg_slot; sn.left_slot = A.next_slot + 2 * ea; sn.right_slot = sn.left_slot + 1; sn.pad = 0;
       A.out_splits[eb] = sn;
-      for (uint32_t q = 0; q < tiles; q++) A.out_tile_node[et + q] = eb;
+      uint32_t slot = kBigMax;
+      if (tiles > 8) slot = atomicAdd(&sh_nbig, 1u);
+      if (slot < (uint32_t)kBigMax) { sh_big[slot][0] = eb; sh_big[slot][1] = et; sh_big[slot][2] = tiles; }
+      else for (uint32_t q = 0; q < tiles; q++) A.out_tile_node[et + q] = eb;
       eb++; et += tiles;
     }
     if (sc.x & kDecNonLeaf) ea++;
   }
+  __syncthreads();
+  const uint32_t nbig = min(sh_nbig, (uint32_t)kBigMax);
+  for (uint32_t i = wv; i < nbig; i += 32)
+    for (uint32_t q = lane; q < sh_big[i][2]; q += 32) A.out_tile_node[sh_big[i][1] + q] = sh_big[i][0];
 }
 
 // ---------------------------------------------------------------------------------------------

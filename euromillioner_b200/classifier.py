@@ -322,6 +322,61 @@ class RandomForestClassificationModel:
             self._export = e
         return self._export
 
+    def toJson(self):
+        """The forest as a JSON document: per tree a nested node object in the vocabulary of
+        Spark's `NodeData` (`id`, `prediction`, `impurity`, `impurityStats`, `gain`, `split.featureIndex`,
+        `split.threshold`, `leftChild`/`rightChild`), doubles written with repr() so that the round trip is exact."""
+        import json
+        e = self.export()
+
+        def node(base, i):
+            d = {"id": int(e["node_id"][base + i]), "prediction": float(e["prediction"][base + i]),
+                 "impurity": float(e["impurity"][base + i]), "impurityStats": [float(v) for v in e["stats"][base + i]]}
+            if e["left"][base + i] >= 0:
+                d["gain"] = float(e["gain"][base + i])
+                d["split"] = {"featureIndex": int(e["feature"][base + i]), "threshold": float(e["threshold"][base + i])}
+                d["leftChild"] = node(base, int(e["left"][base + i]))
+                d["rightChild"] = node(base, int(e["right"][base + i]))
+            return d
+
+        import sys
+        sys.setrecursionlimit(max(sys.getrecursionlimit(), 10000))
+        return json.dumps({"class": "org.apache.spark.ml.classification.RandomForestClassificationModel",
+                           "numFeatures": self.numFeatures, "numClasses": self.numClasses,
+                           "trees": [node(int(e["tree_off"][t]), 0) for t in range(self.numTrees)]})
+
+    @classmethod
+    def fromJson(cls, text, ctx=None):
+        """Inverse of toJson (nodes are laid out pre-order, left subtree first, as emrf_forest_export does)."""
+        import json
+        doc = json.loads(text)
+        cols = {k: [] for k in ("node_id", "left", "right", "feature", "threshold", "gain", "impurity", "prediction", "stats")}
+        tree_off = [0]
+
+        def put(d, base):
+            i = len(cols["node_id"]) - base
+            for k, v in (("node_id", d["id"]), ("left", -1), ("right", -1), ("feature", -1), ("threshold", 0.0),
+                         ("gain", d.get("gain", 0.0)), ("impurity", d["impurity"]), ("prediction", d["prediction"]),
+                         ("stats", d["impurityStats"])):
+                cols[k].append(v)
+            if "split" in d:
+                at = base + i
+                cols["feature"][at] = d["split"]["featureIndex"]
+                cols["threshold"][at] = d["split"]["threshold"]
+                cols["left"][at] = put(d["leftChild"], base)
+                cols["right"][at] = put(d["rightChild"], base)
+            return i
+
+        import sys
+        sys.setrecursionlimit(max(sys.getrecursionlimit(), 10000))
+        for tree in doc["trees"]:
+            put(tree, tree_off[-1])
+            tree_off.append(len(cols["node_id"]))
+        e = {k: np.asarray(v) for k, v in cols.items()}
+        e["stats"] = np.asarray(cols["stats"], np.float64).reshape(len(cols["node_id"]), doc["numClasses"])
+        e["tree_off"] = np.asarray(tree_off, np.int64)
+        return cls.from_arrays(e, doc["numFeatures"], ctx)
+
     def trace(self):
         """(group_sizes, per-popped-node rows [tree, node id, F_sub features]) of the fit."""
         L = _lib.lib()

@@ -159,6 +159,19 @@ def test_thresholds_scale_the_prediction_like_spark(ctx, oracle):
         RandomForestClassifier(ctx).setNumTrees(2).setNumClasses(4).setThresholds([0.5, 0.5]).fit(Dataset(X, y))
 
 
+def test_json_round_trip_is_exact(ctx):
+    """toJson / fromJson: same flat arrays, same predictions, bit for bit."""
+    X, y = synth.flat(3000, 9, 5)
+    model = RandomForestClassifier(ctx).setNumTrees(5).setMaxDepth(6).setNumClasses(5).fit(Dataset(X, y, num_partitions=3))
+    text = model.toJson()
+    back = RandomForestClassificationModel.fromJson(text, ctx)
+    a, b = model.export(), back.export()
+    assert all(np.array_equal(a[k], b[k]) for k in a)
+    pa, pb = model.transform(Dataset(X)).columns, back.transform(Dataset(X)).columns
+    assert all(np.array_equal(pa[k], pb[k]) for k in ("rawPrediction", "probability", "prediction"))
+    assert '"leftChild"' in text and '"impurityStats"' in text
+
+
 def test_two_classes_and_empty_partitions(ctx, oracle):
     """Binary labels; a partition layout with empty partitions (their RNG streams are simply unused)."""
     X, y = synth.flat(6000, 12, 2)

@@ -269,8 +269,8 @@ struct BagSmem {
   uint32_t lut[4][4][256];                 // (M^2)^(2^s) for s = 1..4, one table per input byte
   uint32_t state[kBagPairs][624];
   double ring[kBagPairs][kBagRing][32];    // producer → consumer: blocks of 32 nextDouble() values
-  uint8_t stage[kBagPairs][kBagStageRing][32][32];   // walker → emitter: per lane, the draws of the run it owns in a block
-  uint8_t scnt[kBagPairs][kBagStageRing][32];        //   and how many there are
+  uint8_t sn[kBagPairs][kBagStageRing][32];          // walker → emitter: the draw that STARTS at each position of a block
+  uint32_t smask[kBagPairs][kBagStageRing];          //   and which positions start a draw that also ends in the block
   uint8_t obuf[kBagPairs][kBagObuf];
   volatile uint32_t produced[kBagPairs];   // blocks written by the producer
   volatile uint32_t consumed[kBagPairs];   // blocks released by the walker
@@ -370,6 +370,51 @@ __device__ __forceinline__ int poisson_block(double u, double p_exp, int nlim, P
   return cnt;
 }
 
+// PoissonDistribution.sample() over a block of 32 uniforms, every lane at once.  A draw is a maximal prefix of
+// uniforms whose running product stays >= exp(-mean); the next draw starts right behind it.  So lane s walks the
+// draw that WOULD start at position s (about mean + 1 steps; position 0 continues the previous block's open draw),
+// which gives every position a successor, and pointer doubling over those successors (5 rounds) marks the
+// positions that really start a draw when the chain is followed from position 0.  The emitter then needs one
+// byte per marked position and a popcount for its rank — no per-run counts, no serial walk over a whole run.
+__device__ __forceinline__ uint32_t poisson_block_jump(double u, double p_exp, int nlim, PoissonCarry& pc, int lane, int& n_out) {
+  double r = lane == 0 ? pc.r : 1.0;
+  int n = lane == 0 ? pc.n : 0;
+  int end = -1;                      // position of the uniform that closed this lane's draw (-1: ran off the block)
+  bool running = true;
+  for (int t = 0; __any_sync(0xffffffffu, running); t++) {
+    const int pos = lane + t;
+    const double ut = __shfl_sync(0xffffffffu, u, pos & 31);
+    if (running) {
+      if (pos > 31) {
+        running = false;
+      } else {
+        r = __dmul_rn(r, ut);
+        bool emit;
+        if (r >= p_exp) { n++; emit = !(n < nlim); } else emit = true;
+        if (emit) { end = pos; running = false; }
+      }
+    }
+  }
+  int ptr = end >= 0 ? end + 1 : 32;          // where the next draw starts (32: beyond the block)
+  uint32_t chain = 1u << lane;                // draw starts on the chain that begins here
+#pragma unroll
+  for (int k = 0; k < 5; k++) {
+    const uint32_t c2 = __shfl_sync(0xffffffffu, chain, ptr & 31);
+    const int p2 = __shfl_sync(0xffffffffu, ptr, ptr & 31);
+    if (ptr < 32) { chain |= c2; ptr = p2; }
+  }
+  const uint32_t starts = __shfl_sync(0xffffffffu, chain, 0);
+  const uint32_t ended = __ballot_sync(0xffffffffu, end >= 0);
+  const uint32_t open = starts & ~ended;      // at most the last start of the chain
+  const int src = open ? __ffs(open) - 1 : 0;
+  const double or_ = __shfl_sync(0xffffffffu, r, src);
+  const int on_ = __shfl_sync(0xffffffffu, n, src);
+  pc.r = open ? or_ : 1.0;
+  pc.n = open ? on_ : 0;
+  n_out = n;
+  return starts & ended;
+}
+
 __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t seed, const int64_t* __restrict__ part_off,
                                                                      int n_parts, int T, double mean, double p_exp,
                                                                      uint8_t* __restrict__ weights,
@@ -442,8 +487,11 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
       __syncwarp();
       if (lane == 0) S.consumed[pair] = blk + 1;        // the value is in a register: the slot may be refilled
       const int slot = blk % kBagStageRing;
-      const int cnt = poisson_block(u, p_exp, nlim, pc, S.stage[pair][slot][lane], lane, overflow);
-      S.scnt[pair][slot][lane] = (uint8_t)cnt;
+      int n = 0;
+      const uint32_t closed = poisson_block_jump(u, p_exp, nlim, pc, lane, n);
+      if (((closed >> lane) & 1u) && n > 255) overflow = 1;   // not representable: reported as an error by the host
+      S.sn[pair][slot][lane] = (uint8_t)min(n, 255);
+      if (lane == 0) S.smask[pair][slot] = closed;
       if (overflow) S.ovf[pair] = 1;
       __threadfence_block();
       __syncwarp();
@@ -464,20 +512,13 @@ __global__ void __launch_bounds__(kBagWarps * 32) bag_poisson_kernel(int64_t see
       BPROF(0);
       __threadfence_block();
       const int slot = blk % kBagStageRing;
-      const uint8_t* stage = S.stage[pair][slot][lane];
-      const int cnt = S.scnt[pair][slot][lane];
-      int excl = cnt;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, excl, d);
-        if (lane >= d) excl += v;
-      }
-      const int total_cnt = __shfl_sync(0xffffffffu, excl, 31);
-      excl -= cnt;
+      const uint32_t closed = S.smask[pair][slot];
+      const int v = S.sn[pair][slot][lane];
+      const int total_cnt = __popc(closed);
+      const int rank = __popc(closed & ((1u << lane) - 1u));
       const int64_t remaining = total - q;
       const int emit_total = (int)(remaining < (int64_t)total_cnt ? remaining : (int64_t)total_cnt);
-      for (int k = 0; k < cnt; k++)
-        if (excl + k < emit_total) { const uint8_t v = stage[k]; ob[pos + excl + k] = v; mx = max(mx, (int)v); }
+      if (((closed >> lane) & 1u) && rank < emit_total) { ob[pos + rank] = (uint8_t)v; mx = max(mx, v); }
       __syncwarp();
       if (lane == 0) S.emitted[pair] = blk + 1;         // the slot may be refilled
       pos += emit_total;

@@ -688,9 +688,10 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
 
 static int run_bin(emrf_ctx* c, const double* dX, int64_t N, int F, const double* d_thr, const int* d_ns, int TS, int Fp,
                    int64_t Np, uint8_t* d_rm, uint8_t* d_cm) {
-  const size_t tile_bytes = align_up((size_t)kern::kBinRows * Fp, 16);
-  const size_t thr_bytes = (size_t)F * TS * 8;
-  const unsigned grid = (unsigned)((N + kern::kBinRows - 1) / kern::kBinRows);
+  const size_t tile_bytes = kern::bin_tile_bytes(Fp);
+  const size_t thr_bytes = (size_t)F * kern::bin_thr_smem_stride(TS) * 8;
+  // persistent CTAs: each stages the thresholds once and walks tiles with the grid's stride
+  const unsigned grid = (unsigned)std::min<int64_t>((N + kern::kBinRows - 1) / kern::kBinRows, (int64_t)c->sm_count * 8);
   if (tile_bytes + thr_bytes <= 160 * 1024) {
     const size_t smem = tile_bytes + thr_bytes;
     if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -2233,9 +2234,9 @@ static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* 
     static const bool force_f64_walk = getenv("EMRF_PREDICT_F64_WALK") != nullptr;
     if (f->walk_ok && !force_f64_walk && walk_smem <= 200 * 1024) {
       // bin the chunk once (numeric compare against the forest's own threshold tables), then walk bins
-      const size_t tile_bytes = align_up((size_t)kern::kBinRows * Fp, 16);
-      const size_t thr_bytes = (size_t)F * f->walk_ts * 8;
-      const unsigned bgrid = (unsigned)((n + kern::kBinRows - 1) / kern::kBinRows);
+      const size_t tile_bytes = kern::bin_tile_bytes(Fp);
+      const size_t thr_bytes = (size_t)F * kern::bin_thr_smem_stride(f->walk_ts) * 8;
+      const unsigned bgrid = (unsigned)std::min<int64_t>((n + kern::kBinRows - 1) / kern::kBinRows, (int64_t)c->sm_count * 8);
       if (tile_bytes + thr_bytes <= 160 * 1024) {
         const size_t smem = tile_bytes + thr_bytes;
         if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -85,53 +85,85 @@ __device__ __forceinline__ int find_bin_numeric(const double* thr, int n, double
   return lo;
 }
 constexpr int kBinRows = 128;
+// stride (in doubles) of a feature's thresholds in shared memory: odd, so that the lanes of a warp — consecutive
+// FEATURES, all at the same step of their binary searches — read different banks (an even stride such as 32
+// puts every feature's k-th threshold in the same bank: a 32-way conflict on every search step)
+__host__ __device__ inline int bin_thr_smem_stride(int thr_stride) { return thr_stride | 1; }
+__host__ __device__ inline size_t bin_tile_bytes(int Fp) { return ((size_t)kBinRows * (Fp + 4) + 15) & ~(size_t)15; }
 template <bool kThrInSmem, bool kNumeric = false>
 __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, int64_t n_rows, int F, int Fp,
                                                   int64_t Np, const double* __restrict__ thr,
                                                   const int* __restrict__ n_splits, int thr_stride,
                                                   uint8_t* __restrict__ bins_rm, uint8_t* __restrict__ bins_cm) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  // layout: tile[kBinRows][Fp] bytes | (optional) thresholds
+  // layout: tile[kBinRows][Fp + 4] bytes | (optional) thresholds
   uint8_t* tile = smem_raw;
   const double* sthr = thr;
+  int sstride = thr_stride;
   if (kThrInSmem) {
-    double* st = reinterpret_cast<double*>(smem_raw + (((size_t)kBinRows * Fp + 15) & ~(size_t)15));
-    for (int i = threadIdx.x; i < F * thr_stride; i += blockDim.x) st[i] = thr[i];
+    double* st = reinterpret_cast<double*>(smem_raw + bin_tile_bytes(Fp));
+    sstride = bin_thr_smem_stride(thr_stride);
+    for (int i = threadIdx.x; i < F * thr_stride; i += blockDim.x) {
+      const int f = i / thr_stride, k = i - f * thr_stride;
+      st[f * sstride + k] = thr[i];
+    }
     sthr = st;
   }
-  const int64_t row0 = (int64_t)blockIdx.x * kBinRows;
+  // tile rows are Fp + 4 bytes apart (an odd number of words): the word-wise copy to bins_rm and the column
+  // reads for bins_cm below are then free of bank conflicts
+  const int RW = (Fp >> 2) + 1;                          // row stride in words
+  uint32_t* tile_w = reinterpret_cast<uint32_t*>(tile);
+  // a CTA walks tiles of 128 rows with the grid's stride: the thresholds are staged once per CTA, not per tile
+  const int64_t n_tiles = (n_rows + kBinRows - 1) / kBinRows;
+  for (int64_t tile_idx = blockIdx.x; tile_idx < n_tiles; tile_idx += gridDim.x) {
+  const int64_t row0 = tile_idx * kBinRows;
   const int rows = (int)min((int64_t)kBinRows, n_rows - row0);
-  for (int i = threadIdx.x; i < kBinRows * Fp; i += blockDim.x) tile[i] = 0;
+  __syncthreads();                                       // the previous tile has been written out
+  for (int i = threadIdx.x; i < kBinRows * RW; i += blockDim.x) tile_w[i] = 0;
   __syncthreads();
   const int64_t base = row0 * F;
   const int total = rows * F;
+#pragma unroll 4
   for (int e = threadIdx.x; e < total; e += blockDim.x) {
     const int r = e / F, f = e - r * F;
     const double x = X[base + e];
-    tile[r * Fp + f] = (uint8_t)(kNumeric ? find_bin_numeric(sthr + (size_t)f * thr_stride, n_splits[f], x)
-                                          : find_bin_dev(sthr + (size_t)f * thr_stride, n_splits[f], x));
+    tile[r * (RW << 2) + f] = (uint8_t)(kNumeric ? find_bin_numeric(sthr + (size_t)f * sstride, n_splits[f], x)
+                                                 : find_bin_dev(sthr + (size_t)f * sstride, n_splits[f], x));
   }
   __syncthreads();
-  if (bins_rm) {  // rows of the tile are contiguous in bins_rm: straight 128-bit copy
-    const uint4* src = reinterpret_cast<const uint4*>(tile);
-    uint4* dst = reinterpret_cast<uint4*>(bins_rm + (size_t)row0 * Fp);
-    const int n16 = rows * Fp / 16;
-    for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = src[i];
-  }
-  if (bins_cm) {  // per feature: 128 consecutive rows = 8 x 16 B
-    for (int i = threadIdx.x; i < F * (kBinRows / 16); i += blockDim.x) {
-      const int f = i / (kBinRows / 16), c = i - f * (kBinRows / 16);
-      uint32_t w[4];
-#pragma unroll
-      for (int q = 0; q < 4; q++) {
-        uint32_t v = 0;
-#pragma unroll
-        for (int b = 0; b < 4; b++) v |= (uint32_t)tile[(c * 16 + q * 4 + b) * Fp + f] << (8 * b);
-        w[q] = v;
-      }
-      // Np is a multiple of 128 and the buffer is padded, so the full 16 B store is in bounds.
-      *reinterpret_cast<uint4*>(bins_cm + (size_t)f * Np + row0 + c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+  if (bins_rm) {  // rows of the tile are contiguous in bins_rm: coalesced word copy
+    uint32_t* dst = reinterpret_cast<uint32_t*>(bins_rm + (size_t)row0 * Fp);
+    const int wpr = Fp >> 2;
+    for (int i = threadIdx.x; i < rows * wpr; i += blockDim.x) {
+      const int r = i / wpr, w = i - r * wpr;
+      dst[i] = tile_w[r * RW + w];
     }
+  }
+  if (bins_cm) {
+    // a thread takes four features (one word per row) of 16 consecutive rows, transposes the 16 x 4 bytes in
+    // registers and writes one 16-byte run per feature: lanes differ in the word index first, so the reads hit
+    // distinct banks.  Np is a multiple of 128 and the buffer is padded, so the full 16 B stores are in bounds.
+    const int quads = (F + 3) >> 2;
+    for (int i = threadIdx.x; i < quads * (kBinRows / 16); i += blockDim.x) {
+      const int c = i / quads, q = i - c * quads;
+      uint32_t w[16];
+#pragma unroll
+      for (int k = 0; k < 16; k++) w[k] = tile_w[(c * 16 + k) * RW + q];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int f = 4 * q + j;
+        if (f >= F) break;
+        uint32_t o[4];
+#pragma unroll
+        for (int m = 0; m < 4; m++) {
+          const uint32_t lo = __byte_perm(w[4 * m], w[4 * m + 1], (uint32_t)j | ((uint32_t)(4 + j) << 4));       // rows 4m, 4m+1
+          const uint32_t hi = __byte_perm(w[4 * m + 2], w[4 * m + 3], (uint32_t)j | ((uint32_t)(4 + j) << 4));   // rows 4m+2, 4m+3
+          o[m] = __byte_perm(lo, hi, 0x5410);
+        }
+        *reinterpret_cast<uint4*>(bins_cm + (size_t)f * Np + row0 + c * 16) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+  }
   }
 }
 

@@ -271,7 +271,7 @@ __device__ unsigned long long g_bag_prof[8];   // debug builds: 0 producer wait,
 #define BPROF(i)
 #define BPROF_FLUSH()
 #endif
-// ---- one WARP per partition ---------------------------------------------------------------
+// ---- three WARPS per partition: producer (WELL19937c) -> walker (Poisson draws) -> emitter ------
 // WELL19937c is linear over GF(2).  Writing a_n for the word a step stores (z3) and b_n for the
 // word it hands to the next step (z4 before tempering), every operand of step n except b_{n-1} is
 // at least 70 steps old, and
@@ -280,9 +280,9 @@ __device__ unsigned long long g_bag_prof[8];   // debug builds: 0 producer wait,
 // with e_n known from old state.  A block of 64 steps (< 70) is therefore an affine recurrence with
 // a constant matrix: lane j owns steps 2j, 2j+1, the 32 lanes solve it with a Hillis-Steele scan
 // over powers of M^2 (byte-indexed lookup tables in shared memory), then every lane replays its
-// two steps from its carry-in and emits one nextDouble().  The Poisson loop itself (a running
-// product compared with exp(-mean)) stays sequential on lane 0; it reads the 32 uniforms of the
-// block from shared memory.  Bit-identical to the serial stream (tests/test_gpu_stages.py).
+// two steps from its carry-in and emits one nextDouble().  The Poisson loop (a running product
+// compared with exp(-mean)) is done by the walker warp, a block of 32 uniforms at a time, every
+// lane at once (poisson_block_jump).  Bit-identical to the serial stream (tests/test_gpu_stages.py).
 constexpr int kBagPairs = 4;              // partitions per CTA: a producer, a walker and an emitter warp each
 constexpr int kBagWarps = 3 * kBagPairs;
 constexpr int kBagStageRing = 4;          // blocks of draws the walker may run ahead of the emitter
@@ -358,50 +358,12 @@ __device__ __forceinline__ double well_block(uint32_t* A, const BagSmem& S, uint
   return __dmul_rn((double)(int64_t)(hi26 | lo26), 2.220446049250313e-16);   // BitsStreamGenerator.nextDouble()
 }
 
-// PoissonDistribution.sample() over a block of 32 uniforms (one per lane).
-// r <= 1 always, so a uniform below exp(-mean) ends whatever draw is running: such positions cut the
-// stream into independent RUNS (each starts with r = 1, n = 0).  The lane that sits at a run's first
-// position walks the run (mean length 1/(1-e^-mean) uniforms), all runs in parallel; only the block's
-// first run inherits state from the previous block and only its last one can stay open.
+// State of the draw that is still open at the end of a block of 32 uniforms (handed to the next block).
 struct PoissonCarry {
   double r = 1.0;
   int n = 0;
 };
-// `nlim` = smallest integer not below 1000*mean: for an integer n, (double)n < limit  <=>  n < nlim.
-__device__ __forceinline__ int poisson_block(double u, double p_exp, int nlim, PoissonCarry& pc, uint8_t* stage, int lane,
-                                            int& overflow) {
-  const uint32_t tmask = __ballot_sync(0xffffffffu, u < p_exp);
-  const bool is_start = (lane == 0) || ((tmask >> (lane - 1)) & 1u);
-  const uint32_t rest = tmask >> lane;
-  const int run_end = rest ? lane + __ffs(rest) - 1 : 31;
-  const int len = is_start ? run_end - lane + 1 : 0;
-  const int maxlen = __reduce_max_sync(0xffffffffu, len);
-  double r = lane == 0 ? pc.r : 1.0;
-  int n = lane == 0 ? pc.n : 0;
-  int cnt = 0;
-  for (int t = 0; t < maxlen; t++) {
-    const double ut = __shfl_sync(0xffffffffu, u, (lane + t) & 31);
-    if (t < len) {
-      r = __dmul_rn(r, ut);
-      bool emit;
-      if (r >= p_exp) { n++; emit = !(n < nlim); } else emit = true;
-      if (emit) {
-        if (n > 255) overflow = 1;                     // not representable: reported as an error by the host
-        stage[cnt++] = (uint8_t)min(n, 255);
-        n = 0; r = 1.0;
-      }
-    }
-  }
-  // the open run (if the block does not end on a terminator) hands its state to the next block
-  const int open_lane = tmask ? 32 - __clz(tmask) : 0;     // first position after the last terminator
-  const bool has_open = !(tmask >> 31);
-  const double or_ = __shfl_sync(0xffffffffu, r, open_lane & 31);
-  const int on_ = __shfl_sync(0xffffffffu, n, open_lane & 31);
-  pc.r = has_open ? or_ : 1.0;
-  pc.n = has_open ? on_ : 0;
-  return cnt;
-}
-
+// `nlim` below = smallest integer not below 1000*mean: for an integer n, (double)n < limit  <=>  n < nlim.
 // PoissonDistribution.sample() over a block of 32 uniforms, every lane at once.  A draw is a maximal prefix of
 // uniforms whose running product stays >= exp(-mean); the next draw starts right behind it.  So lane s walks the
 // draw that WOULD start at position s (about mean + 1 steps; position 0 continues the previous block's open draw),

@@ -989,6 +989,8 @@ class PodVec {
     }
     n_ = n;
   }
+  void reserve(size_t n) { const size_t keep = n_; resize(std::max(n, n_)); n_ = keep; }
+  void push_back(const T& v) { resize(n_ + 1); p_[n_ - 1] = v; }
   T* data() { return p_; }
   const T* data() const { return p_; }
   T& operator[](size_t i) { return p_[i]; }
@@ -1300,7 +1302,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaStreamSynchronize(st));
   }
   std::vector<uint32_t> hist_slots;   // slot of every node this rank built a histogram for (exact stats at the end)
-  std::vector<StackEnt> stack;
+  PodVec<StackEnt> stack;
   stack.reserve(1024);
   for (int t = 0; t < T; t++) {
     StackEnt r;
@@ -1323,10 +1325,14 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   struct GroupSel {
     PodVec<GroupEntry> group;
     PodVec<int32_t> feat;
-    PodVec<int32_t> tree_of;     // group[i].tree, compact (the per-tree lists below are built from it)
+    PodVec<int32_t> tree_of;     // group[i].tree, compact (the runs below are found in it)
     std::vector<int> trees_seen;
-    std::vector<int> tree_off, tree_nodes, tree_fill;   // CSR: nodes (group indices) of trees_seen[q], in pop order
-    void clear() { group.clear(); feat.clear(); tree_of.clear(); trees_seen.clear(); tree_off.clear(); tree_nodes.clear(); }
+    struct Run { int tree, start, len; };
+    std::vector<Run> runs;       // maximal runs of consecutive nodes of one tree, in pop order (a tree's children
+                                 // are pushed together, so a group is a handful of runs per tree)
+    uint64_t total_ub = 0;       // entry bounds of this rank's nodes, summed; the heaviest of them
+    uint32_t max_w = 0;
+    void clear() { group.clear(); feat.clear(); tree_of.clear(); trees_seen.clear(); runs.clear(); total_ub = 0; max_w = 0; }
   };
   GroupSel sel_a, sel_b;
   GroupSel* cur = &sel_a;
@@ -1374,34 +1380,34 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       G.tree_of.resize(g0 + k);
       const int nt = k >= 1024 ? c->host_threads : 1;
       (void)nt;
-#pragma omp parallel for num_threads(nt) schedule(static)
+      uint64_t tot = 0;
+      uint32_t mw = 0;
+#pragma omp parallel for num_threads(nt) schedule(static) reduction(+ : tot) reduction(max : mw)
       for (size_t i = 0; i < k; i++) {
         GroupEntry& ge = G.group[g0 + i];
         static_cast<StackEnt&>(ge) = stack[s_top - 1 - i];
         ge.feat_at = (int)((g0 + i) * (size_t)f_sub);
         G.tree_of[g0 + i] = ge.tree;
+        if (mine(ge.tree)) { tot += ge.ub; mw = std::max(mw, ge.weight); }
         int32_t* fo_ = G.feat.data() + (g0 + i) * (size_t)f_sub;
         if (subsampling) memcpy(fo_, tab + (at0 + i) * (size_t)f_sub, (size_t)f_sub * 4);
         else for (int q = 0; q < F; q++) fo_[q] = q;
       }
+      G.total_ub += tot;
+      G.max_w = std::max(G.max_w, mw);
       stack.resize(s_top - k);
       if (subsampling) draw_idx += (int64_t)k + (rejected ? 1 : 0);
     }
-    // trees in first-seen order (= mutable.HashMap insertion order) and each tree's nodes in pop order
+    // trees in first-seen order (= mutable.HashMap insertion order) and the runs of each tree's nodes in pop order
     const int n = (int)G.group.size();
     const int32_t* tof = G.tree_of.data();
-    for (int i = 0; i < n; i++) {
+    for (int i = 0; i < n;) {
       const int t = tof[i];
+      int j = i + 1;
+      while (j < n && tof[j] == t) j++;
+      G.runs.push_back({t, i, j - i});
       if (tree_slot[t] < 0) { tree_slot[t] = (int)G.trees_seen.size(); G.trees_seen.push_back(t); }
-    }
-    G.tree_off.assign(G.trees_seen.size() + 1, 0);
-    for (int i = 0; i < n; i++) G.tree_off[tree_slot[tof[i]] + 1]++;
-    for (size_t q = 0; q < G.trees_seen.size(); q++) G.tree_off[q + 1] += G.tree_off[q];
-    G.tree_nodes.resize(n);
-    {
-      std::vector<int>& fill = G.tree_fill;
-      fill.assign(G.tree_off.begin(), G.tree_off.end() - 1);
-      for (int i = 0; i < n; i++) G.tree_nodes[fill[tree_slot[tof[i]]]++] = i;
+      i = j;
     }
     for (int t : G.trees_seen) tree_slot[t] = -1;   // slots are recomputed by whoever consumes the group
   };
@@ -1421,6 +1427,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   struct Upd { uint32_t dec, slot_l, split_idx; int32_t left_pool; };
   std::vector<Upd> upd_vec;
   std::vector<int> pool_next(T, 0);
+  PodVec<uint32_t> nt_tmp, tb_tmp, push_off;   // per-group scratch of the staging and push passes
+  PodVec<int32_t> slot_tmp;
+  std::vector<int> run_order;
   bool tickets_zeroed = false, ghist_zeroed = false;   // per fit: another entry point may have used the buffers
   // Node statistics of a processed group (impurities, gain, split, class-count pointers, predictions): nothing in
   // the scheduling depends on them, so they are filled from the full records one group later, under GPU work.
@@ -1506,10 +1515,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     fo->group_sizes.push_back(n_nodes);
 
     // ---- tiles (tree-sharded multi-GPU: own trees only); sizes are upper bounds
-    uint64_t total_entries = 0;     // entry bounds of this rank's nodes, summed; the heaviest of them
-    uint32_t max_weight = 0;
-    for (const GroupEntry& g : group)
-      if (mine(g.tree)) { total_entries += g.ub; max_weight = std::max(max_weight, g.weight); }
+    uint64_t total_entries = cur->total_ub;   // entry bounds of this rank's nodes, summed; the heaviest of them
+    uint32_t max_weight = cur->max_w;
+    if (row_sharded) {   // the bounds were replaced by exact sizes after the group was selected
+      total_entries = 0;
+      for (const GroupEntry& g : group) total_entries += g.ub;
+    }
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
     // TreePoint matrix larger than L2: many small tiles, launched in row-range order (below), so that the
@@ -1528,6 +1539,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       CU(c->d_group.ensure(bound));
     }
     kern::GroupNode* gn = (kern::GroupNode*)c->h_group.p;
+    nt_tmp.resize(n_nodes); tb_tmp.resize(n_nodes); slot_tmp.resize(n_nodes);
     // the partition grid's upper bound: every node that may still split, tiled by its entry bound
     uint64_t ptiles_ub64 = 0;
     {
@@ -1543,20 +1555,26 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         d.buf = 0;
         d.seg_slot = hn.slot;
         d.n_tiles = m ? std::max<uint32_t>(1, (hn.ub + tile_len - 1) / tile_len) : 0;
+        nt_tmp[i] = d.n_tiles;
         const int level = hn.level;
         info[i] = (uint32_t)level | (m ? kern::kInfoMine : 0u);
         if (m && level < P.max_depth) ptiles_ub64 += (hn.ub + kern::kPartTile - 1) / kern::kPartTile;
         memcpy(feat_out + (size_t)i * f_sub, group_feat.data() + group[i].feat_at, (size_t)f_sub * 4);
       }
     }
+    // (the sequential part works on compact arrays; the staging records get the results in the parallel pass below)
     uint32_t n_tiles = 0;
     int n_slots = 0;
-    for (int i = 0; i < n_nodes; i++) {
-      kern::GroupNode& d = gn[i];
-      d.tile_begin = n_tiles;
-      // row-sharded without push mode: every histogram goes to HBM for the reduce-scatter
-      d.slot = ((row_sharded && !push_mode) || d.n_tiles > 1) ? n_slots++ : -1;
-      n_tiles += d.n_tiles;
+    {
+      const bool all_slots = row_sharded && !push_mode;   // every histogram goes to HBM for the reduce-scatter
+      const uint32_t* ntp = nt_tmp.data();
+      uint32_t* tbp = tb_tmp.data();
+      int32_t* slp = slot_tmp.data();
+      for (int i = 0; i < n_nodes; i++) {
+        tbp[i] = n_tiles;
+        slp[i] = (all_slots || ntp[i] > 1) ? n_slots++ : -1;
+        n_tiles += ntp[i];
+      }
     }
     const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
     const size_t group_bytes = l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4;
@@ -1564,9 +1582,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       uint32_t* tn = (uint32_t*)((char*)c->h_group.p + off_tiles);
       if (!l2_blocked) {
 #pragma omp parallel for num_threads(nt_host) schedule(static)
-        for (int i = 0; i < n_nodes; i++)
-          for (uint32_t q = 0; q < gn[i].n_tiles; q++) tn[gn[i].tile_begin + q] = (uint32_t)i;
+        for (int i = 0; i < n_nodes; i++) {
+          gn[i].tile_begin = tb_tmp[i];
+          gn[i].slot = slot_tmp[i];
+          for (uint32_t q = 0; q < gn[i].n_tiles; q++) tn[tb_tmp[i] + q] = (uint32_t)i;
+        }
       } else {
+        for (int i = 0; i < n_nodes; i++) { gn[i].tile_begin = tb_tmp[i]; gn[i].slot = slot_tmp[i]; }
         // entries of a node are in ascending row order, so tile q of a node with n tiles covers about the
         // q/n-th part of the rows: emit range by range, every node's tiles of that range together
         uint32_t* tq = (uint32_t*)((char*)c->h_group.p + off_tq);
@@ -1829,28 +1851,49 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     // node's total weight (every entry weighs >= 1) — good enough to tile the next launches without reading sizes back
     for (size_t q = 0; q < cur->trees_seen.size(); q++) tree_slot[cur->trees_seen[q]] = (int)q;
     const std::vector<int> order = hl::group_tree_visit_order(cur->trees_seen);
-    for (int t : order)
-      for (int at = cur->tree_off[tree_slot[t]]; at < cur->tree_off[tree_slot[t] + 1]; at++) {
-        const int gi = cur->tree_nodes[at];
-        const Upd& u = upd[gi];
-        if (!(u.dec & kern::kDecNonLeaf)) continue;
-        const GroupEntry& par = group[gi];
-        const uint32_t lw = sched[gi].y, tw = sched[gi].z;
-        StackEnt ch;
-        ch.tree = t; ch.level = par.level + 1;
-        int pos_l = -1, pos_r = -1;
-        if (!(u.dec & kern::kDecLLeaf)) {
-          ch.pool = u.left_pool; ch.id = 2 * par.id; ch.slot = u.slot_l; ch.ub = std::min(par.ub, lw); ch.weight = lw;
-          pos_l = (int)stack.size();
-          stack.push_back(ch);
-        }
-        if (!(u.dec & kern::kDecRLeaf)) {
-          ch.pool = u.left_pool + 1; ch.id = 2 * par.id + 1; ch.slot = u.slot_l + 1; ch.ub = std::min(par.ub, tw - lw); ch.weight = tw - lw;
-          pos_r = (int)stack.size();
-          stack.push_back(ch);
-        }
-        if (row_sharded && (u.dec & kern::kDecSplit)) child_pos[u.split_idx] = ChildPos{pos_l, pos_r, par.ub};
+    // runs in visit order (rank of their tree, then pop order)
+    for (size_t r = 0; r < order.size(); r++) tree_slot[order[r]] = (int)r;
+    const std::vector<GroupSel::Run>& runs = cur->runs;
+    run_order.resize(runs.size());
+    for (size_t i = 0; i < runs.size(); i++) run_order[i] = (int)i;
+    if (runs.size() > 1)
+      std::stable_sort(run_order.begin(), run_order.end(), [&](int a, int b) { return tree_slot[runs[a].tree] < tree_slot[runs[b].tree]; });
+    // pass 1 (sequential, light): where each node's children go
+    push_off.resize(n_nodes);
+    uint32_t n_push = 0;
+    for (int ri : run_order) {
+      const GroupSel::Run& rr = runs[ri];
+      for (int gi = rr.start; gi < rr.start + rr.len; gi++) {
+        const uint32_t d = upd[gi].dec;
+        push_off[gi] = n_push;
+        if (d & kern::kDecNonLeaf) n_push += ((d & kern::kDecLLeaf) ? 0u : 1u) + ((d & kern::kDecRLeaf) ? 0u : 1u);
       }
+    }
+    const size_t stack_base = stack.size();
+    stack.resize(stack_base + n_push);
+    // pass 2 (parallel): the entries themselves
+#pragma omp parallel for num_threads(nt_host) schedule(static)
+    for (int gi = 0; gi < n_nodes; gi++) {
+      const Upd& u = upd[gi];
+      if (!(u.dec & kern::kDecNonLeaf)) continue;
+      const GroupEntry& par = group[gi];
+      const uint32_t lw = sched[gi].y, tw = sched[gi].z;
+      StackEnt ch;
+      ch.tree = par.tree; ch.level = par.level + 1;
+      size_t at = stack_base + push_off[gi];
+      int pos_l = -1, pos_r = -1;
+      if (!(u.dec & kern::kDecLLeaf)) {
+        ch.pool = u.left_pool; ch.id = 2 * par.id; ch.slot = u.slot_l; ch.ub = std::min(par.ub, lw); ch.weight = lw;
+        pos_l = (int)at;
+        stack[at++] = ch;
+      }
+      if (!(u.dec & kern::kDecRLeaf)) {
+        ch.pool = u.left_pool + 1; ch.id = 2 * par.id + 1; ch.slot = u.slot_l + 1; ch.ub = std::min(par.ub, tw - lw); ch.weight = tw - lw;
+        pos_r = (int)at;
+        stack[at++] = ch;
+      }
+      if (row_sharded && (u.dec & kern::kDecSplit)) child_pos[u.split_idx] = ChildPos{pos_l, pos_r, par.ub};
+    }
     for (int t : cur->trees_seen) tree_slot[t] = -1;
     const size_t stack_before_select = stack.size();
     // the tree nodes themselves (children included) are built from the full records one group later (fill_stats)

@@ -1985,6 +1985,31 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   return EMRF_OK;
 }
 
+// Nothing may be thrown across the C boundary, and a call that fails half-way must not leave work of its own in
+// flight on the context's streams (the next call would reuse the buffers under it).
+template <class Fn>
+static int guarded(emrf_ctx* c, Fn&& fn) {
+  int rc;
+  try {
+    rc = fn();
+  } catch (const std::bad_alloc&) {
+    rc = fail(EMRF_ERR_INTERNAL, "out of host memory");
+  } catch (const std::exception& e) {
+    rc = fail(EMRF_ERR_INTERNAL, "internal error: %s", e.what());
+  } catch (...) {
+    rc = fail(EMRF_ERR_INTERNAL, "internal error");
+  }
+  if (rc != EMRF_OK && c) {
+    const std::string msg = emrf_last_error();      // the synchronisations below must not replace the message
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->stream2) cudaStreamSynchronize(c->stream2);
+    if (c->stream3) cudaStreamSynchronize(c->stream3);
+    cudaGetLastError();
+    fail(rc, "%s", msg.c_str());
+  }
+  return rc;
+}
+
 extern "C" int emrf_fit(emrf_ctx_t* c, const emrf_params_t* params, const double* features_hd, const double* labels_hd,
                         int64_t n_rows, int32_t n_features, const int64_t* partition_offsets, int32_t n_partitions,
                         emrf_forest_t** out) {
@@ -1993,7 +2018,7 @@ extern "C" int emrf_fit(emrf_ctx_t* c, const emrf_params_t* params, const double
   if (n_rows < 1 || n_features < 1) return fail(EMRF_ERR_ARG, "empty dataset");
   TRY(check_partitions(n_rows, partition_offsets, n_partitions));
   std::lock_guard<std::mutex> lk(c->fit_mu);
-  return fit_impl(c, *params, features_hd, labels_hd, n_rows, n_features, partition_offsets, n_partitions, out);
+  return guarded(c, [&] { return fit_impl(c, *params, features_hd, labels_hd, n_rows, n_features, partition_offsets, n_partitions, out); });
 }
 
 extern "C" int emrf_fit_sharded(emrf_ctx_t* c, const emrf_params_t* params, const double* features_hd, const double* labels_hd,
@@ -2022,7 +2047,9 @@ extern "C" int emrf_fit_sharded(emrf_ctx_t* c, const emrf_params_t* params, cons
   sh.n_parts_global = n_partitions_global;
   sh.row0 = row0;
   std::lock_guard<std::mutex> lk(c->fit_mu);
-  return fit_impl(c, *params, features_hd, labels_hd, n_rows_local, n_features, local_off.data(), n_partitions_local, out, &sh);
+  return guarded(c, [&] {
+    return fit_impl(c, *params, features_hd, labels_hd, n_rows_local, n_features, local_off.data(), n_partitions_local, out, &sh);
+  });
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -2311,11 +2338,11 @@ static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* 
 }
 extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f, const double* features_hd, int64_t N, double* raw_hd,
                             double* prob_hd, double* pred_hd) {
-  return predict_impl(c, f, features_hd, N, raw_hd, prob_hd, pred_hd, nullptr);
+  return guarded(nullptr, [&] { return predict_impl(c, f, features_hd, N, raw_hd, prob_hd, pred_hd, nullptr); });
 }
 extern "C" int emrf_predict_thresholds(emrf_ctx_t* c, const emrf_forest_t* f, const double* features_hd, int64_t N,
                                        const double* thresholds, double* raw_hd, double* prob_hd, double* pred_hd) {
-  return predict_impl(c, f, features_hd, N, raw_hd, prob_hd, pred_hd, thresholds);
+  return guarded(nullptr, [&] { return predict_impl(c, f, features_hd, N, raw_hd, prob_hd, pred_hd, thresholds); });
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -1690,6 +1690,15 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.total_counts = (uint32_t*)((char*)c->d_results.p + res_total);
     A.tile_base = 0;
     A.node_base = 0;
+    // single GPU, one feature chunk: the scanning CTA also takes the decisions (decide_flags_kernel's work)
+    const bool fuse_decide = c->world == 1 && n_chunks == 1 && !env_flag("EMRF_NO_FUSED_DECIDE");
+    if (fuse_decide) {
+      A.node_info = (const uint32_t*)((char*)c->d_group.p + off_info);
+      A.out_dec = (uint32_t*)((char*)c->d_results.p + res_dec);
+      A.out_sched = (uint4*)((char*)c->d_part.p + off_sched);
+      A.out_ptiles = (uint32_t*)((char*)c->d_part.p + off_ptiles);
+      A.max_depth = P.max_depth;
+    }
     {
       cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
       CU(cudaEventRecord(e0, st));
@@ -1757,7 +1766,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     D.out_limits = d_limits;
     D.n_nodes = n_nodes; D.n_chunks = n_chunks; D.f_sub = f_sub; D.max_depth = P.max_depth;
     D.next_slot = next_slot;
-    kern::decide_flags_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(D);
+    if (!fuse_decide) kern::decide_flags_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(D);
     cudaEvent_t ev_dec = c->events.get(), sched_done = c->events.get(), rec_done = c->events.get();
     CU(cudaEventRecord(ev_dec, st));
     CU(cudaStreamWaitEvent(c->stream2, ev_dec, 0));

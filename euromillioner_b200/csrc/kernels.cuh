@@ -812,6 +812,27 @@ struct ScanResult {
   uint32_t total_weight;  // sum of the node's class counts,
   uint32_t left_weight;   //   of the left child's (upper bounds on the children's entry counts)
 };
+// Decision word of a node: winning feature chunk (low byte) | flags.  node_info: level | kInfoMine.
+constexpr uint32_t kDecNonLeaf = 1u << 8, kDecLLeaf = 1u << 9, kDecRLeaf = 1u << 10, kDecSplit = 1u << 11, kDecValid = 1u << 12;
+constexpr uint32_t kInfoMine = 1u << 8;   // this rank builds/partitions the node's tree
+// Spark's leaf rules for one node (RandomForest.findBestSplits: isLeaf = gain <= 0 || level == maxDepth; a child is
+// a leaf at maxDepth or when its impurity is 0.0), given the winning record `r` of chunk `best` (-1: none).
+// One definition for the fused epilogue of hist_scan_kernel and for decide_flags_kernel.
+__device__ __forceinline__ uint32_t decide_word(const ScanResult& r, int best, uint32_t info, int max_depth) {
+  const int level = (int)(info & 0xffu);
+  const bool valid = best >= 0 && r.valid;
+  const double gain = valid ? r.gain : kInvalidGain;
+  const bool is_leaf = (gain <= 0) || (level == max_depth);
+  uint32_t dec = (uint32_t)(best < 0 ? 0 : best) | (valid ? kDecValid : 0u);
+  if (!is_leaf) {
+    const bool child_leaf = (level + 1) == max_depth;
+    const bool l_leaf = child_leaf || (r.left_impurity == 0.0);
+    const bool r_leaf = child_leaf || (r.right_impurity == 0.0);
+    dec |= kDecNonLeaf | (l_leaf ? kDecLLeaf : 0u) | (r_leaf ? kDecRLeaf : 0u);
+    if ((!l_leaf || !r_leaf) && (info & kInfoMine)) dec |= kDecSplit;
+  }
+  return dec;
+}
 struct HistArgs {
   const uint64_t* ent0;
   const uint64_t* ent1;
@@ -841,6 +862,13 @@ struct HistArgs {
   const uint8_t* bins_cm;                    // [F][Np]
   int64_t Np;
   uint32_t cm_min_len;
+  // fused decide step (single GPU, one feature chunk): the CTA that scans a node also writes its decision word,
+  // scheduling record and partition tile count (what decide_flags_kernel would), saving a launch per group
+  const uint32_t* node_info;                 // nullptr: not fused
+  uint32_t* out_dec;
+  uint4* out_sched;
+  uint32_t* out_ptiles;
+  int32_t max_depth;
 };
 
 // Correctly rounded a / b for integer-valued 0 <= a <= b < 2^32 with y = RN(1 / b): one multiply and
@@ -1379,6 +1407,17 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
   HPROF_COUNT(9);
   scan_chunk<HT>(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rrec],
                  A.left_counts + rrec * C, A.total_counts + rrec * C);
+  if (A.node_info) {          // n_chunks == 1: this record is the node's
+    __syncthreads();          // the record's fields were written by several threads of this CTA
+    if (tid == 0) {
+      const ScanResult r = A.results[rrec];
+      const uint32_t dec = decide_word(r, r.k >= 0 ? 0 : -1, A.node_info[g], A.max_depth);
+      const uint32_t fs = (dec & kDecNonLeaf) ? ((uint32_t)A.node_feat[(size_t)g * A.f_sub + r.k] | ((uint32_t)r.split << 24)) : 0u;
+      A.out_dec[g] = dec;
+      A.out_sched[g] = make_uint4(dec, r.left_weight, r.total_weight, fs);
+      A.out_ptiles[g] = (dec & kDecSplit) ? (nd.seg_len + kPartTile - 1) / kPartTile : 0u;
+    }
+  }
 }
 
 // K3 alone — binsToBestSplit on histograms already in HBM (stage entry point; also the scan used
@@ -1607,8 +1646,6 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64
 // its partition.  Numbering is in group order: segment slots next_slot + 2*i for the i-th non-leaf node, split
 // index = rank among the nodes that have a child to partition.
 // ---------------------------------------------------------------------------------------------
-constexpr uint32_t kDecNonLeaf = 1u << 8, kDecLLeaf = 1u << 9, kDecRLeaf = 1u << 10, kDecSplit = 1u << 11, kDecValid = 1u << 12;
-constexpr uint32_t kInfoMine = 1u << 8;   // node_info: level | kInfoMine (this rank builds/partitions the node's tree)
 struct DecideArgs {
   const ScanResult* results;     // [n_nodes][n_chunks]
   const GroupNode* nodes;
@@ -1636,24 +1673,9 @@ __global__ void __launch_bounds__(256) decide_flags_kernel(const DecideArgs A) {
     if (best < 0 || r0[ch].gain > r0[best].gain) best = ch;
   }
   const ScanResult& r = r0[best < 0 ? 0 : best];
-  const uint32_t info = A.node_info[gi];
-  const int level = (int)(info & 0xffu);
-  const bool valid = best >= 0 && r.valid;
-  const double gain = valid ? r.gain : kInvalidGain;
-  const bool is_leaf = (gain <= 0) || (level == A.max_depth);
-  uint32_t dec = (uint32_t)(best < 0 ? 0 : best) | (valid ? kDecValid : 0u);
-  uint32_t tiles = 0, fs = 0;
-  if (!is_leaf) {
-    const bool child_leaf = (level + 1) == A.max_depth;
-    const bool l_leaf = child_leaf || (r.left_impurity == 0.0);
-    const bool r_leaf = child_leaf || (r.right_impurity == 0.0);
-    dec |= kDecNonLeaf | (l_leaf ? kDecLLeaf : 0u) | (r_leaf ? kDecRLeaf : 0u);
-    fs = (uint32_t)A.node_feat[(size_t)gi * A.f_sub + r.k] | ((uint32_t)r.split << 24);
-    if ((!l_leaf || !r_leaf) && (info & kInfoMine)) {
-      dec |= kDecSplit;
-      tiles = (A.segtab[A.nodes[gi].seg_slot].len + kPartTile - 1) / kPartTile;
-    }
-  }
+  const uint32_t dec = decide_word(r, best, A.node_info[gi], A.max_depth);
+  const uint32_t fs = (dec & kDecNonLeaf) ? ((uint32_t)A.node_feat[(size_t)gi * A.f_sub + r.k] | ((uint32_t)r.split << 24)) : 0u;
+  const uint32_t tiles = (dec & kDecSplit) ? (A.segtab[A.nodes[gi].seg_slot].len + kPartTile - 1) / kPartTile : 0u;
   A.out_dec[gi] = dec;
   A.out_sched[gi] = make_uint4(dec, r.left_weight, r.total_weight, fs);
   A.out_tiles[gi] = tiles;

@@ -255,7 +255,7 @@ struct emrf_ctx {
   void* nccl_comm = nullptr;
   // grow-only scratch reused across groups
   DevBuf d_group, d_results, d_ghist, d_tickets;
-  PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum, h_sample, h_sched;
+  PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum, h_sample, h_sched, h_seg;
   DevBuf d_split, d_part;   // partition work of the current group (written by decide_kernel)
   std::vector<HTree> tree_pools;   // LearningNode pools of the last fit (memory reused by the next)
   DevBuf d_seeds, d_table, d_tsum;
@@ -1944,21 +1944,24 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     fprintf(stderr, "[emrf] host phases ms: prep %.2f | launch %.2f | bookkeeping %.2f | wait %.2f | numbering %.2f | nodes %.2f | "
             "stack %.2f | select %.2f | other %.2f\n", ph[0], ph[1], ph[2], ph[3], ph[5], ph[8], ph[9], ph[10], ph[11]);
   // ---- exact entry counts of every histogram built (the roofline's algorithmic bytes), from the table
-  {
-    std::vector<kern::Seg> segs(next_slot);
-    CU(cudaMemcpyAsync(segs.data(), c->p_segtab.p, (size_t)next_slot * sizeof(kern::Seg), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    int64_t units = 0;
-    for (uint32_t sl : hist_slots) units += segs[sl].len;
-    tm.hist_units = units;
-    tm.hist_alg_bytes += units * (int64_t)(f_sub + 6);
-  }
+  // (the table comes back into page-locked memory while the forest is exported)
+  CU(c->h_seg.ensure((size_t)next_slot * sizeof(kern::Seg)));
+  CU(cudaMemcpyAsync(c->h_seg.p, c->p_segtab.p, (size_t)next_slot * sizeof(kern::Seg), cudaMemcpyDeviceToHost, st));
   // ---- topNodes.map(_.toNode(prune = true))
   double t_host0 = now_ms();
   if (!export_forest(trees, C, *fo, c->host_threads)) return fail(EMRF_ERR_INTERNAL, "out of host memory for the model");
   { const double d_ = now_ms() - t_host0; host_ms += d_; tm.host_export_ms = d_; }
   CU(cudaEventRecord(ev_end, st));
   CU(cudaStreamSynchronize(st));
+  {
+    const kern::Seg* segs = (const kern::Seg*)c->h_seg.p;
+    const size_t n_hs = hist_slots.size();
+    int64_t units = 0;
+#pragma omp parallel for num_threads(c->host_threads) schedule(static) reduction(+ : units)
+    for (size_t i = 0; i < n_hs; i++) units += segs[hist_slots[i]].len;
+    tm.hist_units = units;
+    tm.hist_alg_bytes += units * (int64_t)(f_sub + 6);
+  }
 
   float ms = 0;
   CU(cudaEventElapsedTime(&ms, ev_start, ev_end)); tm.total_ms = ms;

@@ -1776,7 +1776,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaEventRecord(rec_done, c->stream2));
     tm.d2h_bytes += (int64_t)n_nodes * 16;
     kern::decide_scan_kernel<<<1, 1024, 0, st>>>(D);
-    tm.kernel_launches += 2;
+    tm.kernel_launches += fuse_decide ? 1 : 2;
     CU(cudaGetLastError());
     if (ptiles_ub) {
       cudaEvent_t p0 = c->events.get(), p1 = c->events.get();

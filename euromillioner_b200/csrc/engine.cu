@@ -721,7 +721,7 @@ static int bag_launch(emrf_ctx* c, cudaStream_t stream, const emrf_params_t& P, 
   if (T > 1) {
     const double mean = P.subsampling_rate;
     const double p_exp = std::exp(-mean);
-    static const bool serial = getenv("EMRF_BAG_SERIAL") != nullptr;  // one thread per partition (cross-check)
+    static const bool serial = env_flag("EMRF_BAG_SERIAL");  // one thread per partition (cross-check)
     if (serial) {
       CU(cudaFuncSetAttribute(kern::bag_poisson_serial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kern::kBagSmemBytes));
       kern::bag_poisson_serial_kernel<<<(n_parts + 31) / 32, 32, kern::kBagSmemBytes, stream>>>(
@@ -1340,7 +1340,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   std::vector<int> tree_slot(T, -1);
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_ev, part_ev;
   double host_ms = 0.0, host_sel = 0.0, host_upd = 0.0;
-  static const bool verify_gains = getenv("EMRF_VERIFY_GAINS") != nullptr;
+  static const bool verify_gains = env_flag("EMRF_VERIFY_GAINS");
   c->arena_reset();
 
   // ---- selectNodesToSplit.  The driver RNG hands each popped node one nextLong() (drawn BEFORE the
@@ -2313,7 +2313,7 @@ static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* 
     double* pred = pred_hd ? (pred_dev ? pred_hd + r0 : dPred.as<double>()) : nullptr;
     const int Fp = (int)align_up(F, 16);
     const size_t walk_smem = kern::predict_smem_bytes(Fp, C);
-    static const bool force_f64_walk = getenv("EMRF_PREDICT_F64_WALK") != nullptr;
+    static const bool force_f64_walk = env_flag("EMRF_PREDICT_F64_WALK");
     if (f->walk_ok && !force_f64_walk && walk_smem <= 200 * 1024) {
       // bin the chunk once (numeric compare against the forest's own threshold tables), then walk bins
       const size_t tile_bytes = kern::bin_tile_bytes(Fp);

@@ -3,13 +3,16 @@
 // Host side of RandomForest.run (ml/tree/impl/RandomForest.scala, Spark 2.4.6; dependency pin
 // pom.xml:56-61): the sequential node scheduler (selectNodesToSplit: LIFO stack, memory-bounded
 // groups, per-node feature subsets drawn from the driver RNG) stays on the host; everything
-// row-sized runs in the kernels of kernels.cuh.  One device round trip per group for the split
-// records (~0.5 KB per node) and one for the child segment sizes.
+// row-sized runs in the kernels of kernels.cuh.  Per group the GPU runs histogram+scan, the decide
+// kernels and the partition kernels back to back; the host gets a 16-byte scheduling record per node
+// first (what it needs to number the children and select the next group) and the full split records
+// (~0.5 KB per node) behind them, and builds the tree nodes one group later, under GPU work.
 //
 // No PyTorch, no CPU fallback: every compute entry point needs a CUDA device.
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>

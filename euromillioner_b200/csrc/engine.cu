@@ -785,23 +785,66 @@ static cudaError_t hist_launch(int ch, dim3 grid, size_t smem, cudaStream_t st, 
   }
 #undef EMRF_HIST_CASE
 }
+// Row pitch of the row-major TreePoint matrix: 32/64/128 bytes for up to 128 features (the sizes a TMA gather with a
+// matching swizzle mode serves: one row = one swizzle span, four rows = a 128-byte aligned destination), F rounded up
+// to 16 above that (generic byte gathers).
+static int row_pitch(int F) {
+  if (F <= 32) return 32;
+  if (F <= 64) return 64;
+  if (F <= 128) return 128;
+  return (int)((F + 15) / 16 * 16);
+}
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (no link-time libcuda dependency)
+typedef CUresult (*tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static tmap_encode_fn tmap_encoder() {
+  static tmap_encode_fn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+    }
+    return (tmap_encode_fn)p;
+  }();
+  return fn;
+}
+// Row staging by TMA gathers is the default wherever a row is 16/32/64/128 bytes; EMRF_NO_TMA=1 keeps the LDG/STS staging
+// (A/B runs and the variant parity test).
+static bool hist_use_tma(int ch) { return kern::hist_tma_rows(ch) && !env_flag("EMRF_NO_TMA") && tmap_encoder() != nullptr; }
+// 2-D map over this GPU's bins_rm [rows][Fp] (uint8), box {Fp, 1}: tile::gather4 then moves four whole rows per instruction
+static int make_rows_tmap(CUtensorMap* out, const uint8_t* bins_rm, int64_t rows, int Fp) {
+  const cuuint64_t dims[2] = {(cuuint64_t)Fp, (cuuint64_t)rows}, strides[1] = {(cuuint64_t)Fp};
+  const cuuint32_t box[2] = {(cuuint32_t)Fp, 1}, estr[2] = {1, 1};
+  const CUtensorMapSwizzle sw = Fp == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : Fp == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                              : Fp == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+  const CUresult r = tmap_encoder()(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(bins_rm), dims, strides, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(EMRF_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for %lld rows of %d bytes", (int)r, (long long)rows, Fp);
+  return EMRF_OK;
+}
+// Shared-memory geometry of hist_scan_kernel: [staging region][histogram block of k_chunk features]
 static int hist_geometry(emrf_ctx* c, int Fp, int f_sub, int B, int C, int* ch_out, int* k_chunk_out, int* n_chunks_out,
-                         size_t* hist_bytes_out, size_t* smem_out) {
+                         size_t* region_out, size_t* smem_out, bool* tma_out = nullptr) {
   const int ch = kern::hist_row_chunks(Fp);
-  const size_t tile_bytes = kern::hist_tile_bytes(ch);
+  const bool tma = hist_use_tma(ch);
   const size_t smem_cap = std::min<size_t>(c->smem_optin, 227 * 1024);
-  const size_t per_feat = (size_t)B * C * 4;
-  const size_t fixed = 4096 + tile_bytes;
-  int k_chunk = (100 * 1024 > fixed) ? (int)((100 * 1024 - fixed) / per_feat) : 0;
+  const size_t per_feat = (size_t)B * C * 4 + 8;
+  const size_t fixed = kern::hist_region_bytes(ch, tma, std::min(f_sub, 64)) + 64;
+  // two CTAs per SM (each may use (228 KB - 2 * 1 KB) / 2) unless even four features would not fit
+  const size_t two_per_sm = 112 * 1024;
+  int k_chunk = (two_per_sm > fixed) ? (int)((two_per_sm - fixed) / per_feat) : 0;
   if (k_chunk < f_sub && k_chunk < 4) k_chunk = (int)((smem_cap - fixed) / per_feat);  // big bins x classes: one CTA per SM
   if (k_chunk < 1) return fail(EMRF_ERR_LIMIT, "one feature histogram (%d bins x %d classes) exceeds shared memory", B, C);
   k_chunk = std::min(k_chunk, f_sub);
-  if (ch) k_chunk = std::min(k_chunk, 64);   // the row-tile path keeps 64 per-feature offsets in shared memory
+  if (ch) k_chunk = std::min(k_chunk, 64);   // the row-staging paths keep 64 per-feature entries in shared memory
   *ch_out = ch;
   *k_chunk_out = k_chunk;
   *n_chunks_out = (f_sub + k_chunk - 1) / k_chunk;
-  *hist_bytes_out = kern::hist_smem_bytes(k_chunk, B, C);
-  *smem_out = *hist_bytes_out + tile_bytes;
+  *region_out = kern::hist_region_bytes(ch, tma, k_chunk);
+  *smem_out = *region_out + kern::hist_block_bytes(k_chunk, B, C);
+  if (tma_out) *tma_out = tma;
   if (*smem_out > smem_cap) return fail(EMRF_ERR_LIMIT, "histogram tile needs %zu B of shared memory", *smem_out);
   return EMRF_OK;
 }
@@ -1128,7 +1171,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(d_num_bins.alloc((size_t)F * 4));
 
   // ---- TreePoint matrices
-  const int Fp = (int)align_up(F, 16);
+  const int Fp = row_pitch(F);
   const int64_t Np = (int64_t)align_up((size_t)N, 128);
   DevBuf &d_rm = c->p_rm, &d_cm = c->p_cm;
   CU(d_rm.ensure_exact((size_t)Np * Fp));
@@ -1236,12 +1279,16 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
 
   // ---- metadata (DecisionTreeMetadata.buildMetadata)
   int row_ch, k_chunk, n_chunks;
-  size_t hist_bytes, hist_smem;
-  TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &hist_smem));
+  size_t hist_region, hist_smem;
+  bool hist_tma = false;
+  TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_region, &hist_smem, &hist_tma));
   CU(hist_launch(row_ch, dim3(1), hist_smem, st, kern::HistArgs(), true));
+  const size_t hist_bytes = kern::hist_smem_bytes(k_chunk, B, C);   // the stand-alone scan kernels (rows sharded)
+  CUtensorMap rows_tmap;
+  memset(&rows_tmap, 0, sizeof(rows_tmap));
+  if (hist_tma) TRY(make_rows_tmap(&rows_tmap, d_rm.as<uint8_t>(), Np, Fp));
   // 16-bit counters for launches of small single-tile nodes (EMRF_HIST_U32=1 turns them off)
-  const size_t hist_bytes16 = kern::hist_smem_bytes(k_chunk, B, C, 2);
-  const size_t hist_smem16 = hist_bytes16 + (hist_smem - hist_bytes);
+  const size_t hist_smem16 = hist_region + kern::hist_block_bytes(k_chunk, B, C, 2);
   const bool allow_u16 = !row_sharded && !env_flag("EMRF_HIST_U32");
   // nodes holding at least 1/EMRF_CM_DIV of the rows gather from the column-major matrix (0: never)
   uint32_t cm_min_len = 0;
@@ -1682,7 +1729,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     if (env_flag("EMRF_DEBUG_GROUPS"))
       fprintf(stderr, "[emrf] group %zu: nodes %d tiles %u slots %d max_weight %u tile_len %u u16 %d\n", fo->group_sizes.size(), n_nodes,
               n_tiles, n_slots, max_weight, tile_len, (int)u16);
-    A.tile_smem_off = (uint32_t)(u16 ? hist_bytes16 : hist_bytes);
+    A.hist_smem_off = (uint32_t)hist_region;
+    A.use_tma = hist_tma ? 1 : 0;
+    A.tmap = rows_tmap;
     A.impurity = P.impurity; A.min_instances = P.min_instances_per_node; A.hist_only = row_sharded ? 1 : 0;
     A.push_world = push_mode ? c->world : 0; A.push_rank = c->rank; A.push_npr = nodes_per_rank;
     for (int r = 0; r < 8; r++) A.peer_stage[r] = (uint32_t*)c->peer_stage[r];
@@ -2099,6 +2148,34 @@ extern "C" int emrf_forest_import(emrf_ctx_t* c, int32_t T, int32_t C, int32_t F
                                   emrf_forest_t** out) {
   (void)c;
   if (!out || !tree_off || T < 1 || C < 1 || C > 256 || F < 1) return fail(EMRF_ERR_ARG, "bad forest description");
+  if (!left || !right || !feature || !threshold || !stats) return fail(EMRF_ERR_ARG, "forest description: a required array is NULL");
+  // The description usually comes from a file (RandomForestClassificationModel.load / fromJson), and predict walks the
+  // children on the host and on the device without further checks: reject anything that is not a set of proper trees.
+  // Exports are pre-order, so a child index above its parent's rules out cycles; every node but the root must have
+  // exactly one parent.
+  if (tree_off[0] != 0) return fail(EMRF_ERR_ARG, "forest description: tree_off[0] must be 0");
+  for (int32_t t = 0; t < T; t++)
+    if (tree_off[t + 1] <= tree_off[t]) return fail(EMRF_ERR_ARG, "forest description: tree %d is empty or tree_off decreases", t);
+  if (tree_off[T] >= (1ll << 31)) return fail(EMRF_ERR_LIMIT, "forest too large");
+  {
+    std::vector<uint8_t> parents;
+    for (int32_t t = 0; t < T; t++) {
+      const int64_t base = tree_off[t], sz = tree_off[t + 1] - base;
+      parents.assign((size_t)sz, 0);
+      for (int64_t i = 0; i < sz; i++) {
+        const int32_t l = left[base + i], r = right[base + i];
+        if (l < 0 && r < 0) continue;
+        if (l <= i || r <= i || l >= sz || r >= sz || l == r)
+          return fail(EMRF_ERR_ARG, "forest description: tree %d node %lld has bad children (%d, %d)", t, (long long)i, l, r);
+        const int32_t ft = feature[base + i];
+        if (ft < 0 || ft >= F) return fail(EMRF_ERR_ARG, "forest description: tree %d node %lld: feature %d out of range", t, (long long)i, ft);
+        if (parents[l]++ || parents[r]++)
+          return fail(EMRF_ERR_ARG, "forest description: tree %d node %lld shares a child with another node", t, (long long)i);
+      }
+      for (int64_t i = 1; i < sz; i++)
+        if (!parents[i]) return fail(EMRF_ERR_ARG, "forest description: tree %d node %lld is unreachable", t, (long long)i);
+    }
+  }
   emrf_forest* f = new emrf_forest();
   f->num_trees = T; f->num_classes = C; f->num_features = F;
   f->tree_off.assign(tree_off, tree_off + T + 1);
@@ -2444,10 +2521,11 @@ extern "C" int emrf_histogram(emrf_ctx_t* c, const uint8_t* bins_rm, int64_t N, 
   cudaStream_t st = c->stream;
   int B = 1;
   for (int f = 0; f < F; f++) B = std::max(B, num_bins_all[f]);
-  const int Fp = (int)align_up(F, 16);
+  const int Fp = row_pitch(F);
   int row_ch, k_chunk, n_chunks;
-  size_t hist_bytes, smem;
-  TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &smem));
+  size_t region, smem;
+  bool tma = false;
+  TRY(hist_geometry(c, Fp, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &region, &smem, &tma));
   CU(hist_launch(row_ch, dim3(1), smem, st, kern::HistArgs(), true));
   const int64_t n_ent = node_seg_off[n_nodes];
   DevBuf d_rm, d_ent, d_nodes, d_feat, d_tiles, d_nb, d_hist;
@@ -2490,7 +2568,9 @@ extern "C" int emrf_histogram(emrf_ctx_t* c, const uint8_t* bins_rm, int64_t N, 
   A.ghist = d_hist.as<uint32_t>();
   A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
   A.tile_len = tile_len; A.hist_only = 1;
-  A.tile_smem_off = (uint32_t)hist_bytes;
+  A.hist_smem_off = (uint32_t)region;
+  A.use_tma = tma ? 1 : 0;
+  if (tma) TRY(make_rows_tmap(&A.tmap, d_rm.as<uint8_t>(), N, Fp));
   CU(hist_launch(row_ch, dim3((unsigned)tn.size(), n_chunks), smem, st, A, false));
   CU(cudaMemcpyAsync(hist_out, d_hist.p, (size_t)n_nodes * slot_words * 4, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
@@ -2509,9 +2589,9 @@ extern "C" int emrf_best_splits(emrf_ctx_t* c, const uint32_t* hist, int32_t n_n
   int B = 1;
   for (int f = 0; f < F; f++) B = std::max(B, num_bins_all[f]);
   int row_ch, k_chunk, n_chunks;
-  size_t hist_bytes, smem;
-  TRY(hist_geometry(c, 16, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &hist_bytes, &smem));
-  smem = hist_bytes;
+  size_t region, smem;
+  TRY(hist_geometry(c, 16, f_sub, B, C, &row_ch, &k_chunk, &n_chunks, &region, &smem));
+  smem = kern::hist_smem_bytes(k_chunk, B, C);
   CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const size_t slot_words = (size_t)f_sub * B * C;
   const size_t n_rec = (size_t)n_nodes * n_chunks;

@@ -12,6 +12,7 @@
 // All floating-point split arithmetic uses explicit round-to-nearest intrinsics so that no FMA
 // contraction can change a gain (the JVM does not fuse).
 #pragma once
+#include <cuda.h>           // CUtensorMap (type only: the encoder is looked up at run time, nothing links libcuda)
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -852,7 +853,7 @@ struct HistArgs {
   uint32_t tile_len;
   uint32_t tile_base;          // first tile of this launch (a group may be launched in pieces)
   uint32_t node_base;          // first node of this launch: result records are indexed relative to it
-  uint32_t tile_smem_off;      // byte offset of the per-warp row tiles inside dynamic shared memory
+  uint32_t hist_smem_off;      // byte offset of the histogram inside dynamic shared memory (the staging region comes first)
   int32_t impurity, min_instances, hist_only;
   // row-sharded push mode: partial histograms go straight into the owner rank's staging buffer over NVLink
   int32_t push_world, push_rank, push_npr;   // push_world == 0: off
@@ -869,6 +870,10 @@ struct HistArgs {
   uint4* out_sched;
   uint32_t* out_ptiles;
   int32_t max_depth;
+  // TMA row staging (rows of 16/32/64/128 bytes): 2-D tensor map over THIS GPU's bins_rm [Np][Fp], box {Fp, 1},
+  // swizzle mode = row bytes; the accumulate loop fetches four rows per cp.async.bulk.tensor ... tile::gather4
+  int32_t use_tma;
+  alignas(64) CUtensorMap tmap;
 };
 
 // Correctly rounded a / b for integer-valued 0 <= a <= b < 2^32 with y = RN(1 / b): one multiply and
@@ -926,9 +931,12 @@ __device__ unsigned long long g_hist_prof[16];
 #define HPROF_COUNT(i)
 #endif
 
-// Shared-memory carve-up used by hist_scan_kernel and scan_kernel.  HT is the counter type: uint32_t, or
+// Shared-memory carve-up used by hist_scan_kernel and the scan kernels.  HT is the counter type: uint32_t, or
 // uint16_t for launches whose every node is accumulated by ONE CTA and weighs at most 65535 (no counter, and
 // no prefix sum over bins, can then exceed 16 bits): half the histogram memory, so more CTAs per SM.
+// Two pieces: the histogram block [hist k_chunk*B*C][feat k_chunk][nb k_chunk][flag], and the scan's scratch
+// [tot 256][sq 256][reductions].  In hist_scan_kernel the scratch lies over the row-staging region, which is dead by
+// the time a node is scanned; the scan kernels place it behind the histogram block.
 template <class HT>
 struct ScanSmem {
   HT* hist;            // [k_chunk][B][C]
@@ -939,32 +947,51 @@ struct ScanSmem {
   int* red_idx;        // [8]
   int* feat;           // [k_chunk]
   int* nb;             // [k_chunk]
+  int* flag;           // [1]  "this CTA is the node's last tile"
 };
+constexpr size_t kScanScratchBytes = 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + 8;   // 3184, kept 16-byte aligned below
 __host__ __device__ inline size_t scan_hist_bytes(int k_chunk, int B, int C, int elem) {
   return ((size_t)k_chunk * B * C * elem + 15) & ~(size_t)15;
 }
+// histogram block: counters + per-feature tables + flag
+__host__ __device__ inline size_t hist_block_bytes(int k_chunk, int B, int C, int elem = 4) {
+  return (scan_hist_bytes(k_chunk, B, C, elem) + (size_t)k_chunk * 8 + 16 + 15) & ~(size_t)15;
+}
 template <class HT>
-__device__ __forceinline__ ScanSmem<HT> carve_smem(uint8_t* raw, int k_chunk, int B, int C) {
+__device__ __forceinline__ ScanSmem<HT> carve_smem(uint8_t* raw_hist, uint8_t* raw_scratch, int k_chunk, int B, int C) {
   ScanSmem<HT> s;
-  s.hist = reinterpret_cast<HT*>(raw);
-  s.tot = reinterpret_cast<uint32_t*>(raw + scan_hist_bytes(k_chunk, B, C, (int)sizeof(HT)));
+  s.hist = reinterpret_cast<HT*>(raw_hist);
+  s.feat = reinterpret_cast<int*>(raw_hist + scan_hist_bytes(k_chunk, B, C, (int)sizeof(HT)));
+  s.nb = s.feat + k_chunk;
+  s.flag = s.nb + k_chunk;
+  s.tot = reinterpret_cast<uint32_t*>(raw_scratch);
   s.sq = reinterpret_cast<double*>(s.tot + 256);
   s.red_gain = s.sq + 256;
   s.pimp = s.red_gain + 8;
   s.red_idx = reinterpret_cast<int*>(s.pimp + 1);
-  s.feat = s.red_idx + 8;
-  s.nb = s.feat + k_chunk;
   return s;
 }
+// the scan kernels: histogram block, then the scratch
 inline size_t hist_smem_bytes(int k_chunk, int B, int C, int elem = 4) {
-  return (scan_hist_bytes(k_chunk, B, C, elem) + 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + (size_t)k_chunk * 8 + 16 + 15) & ~(size_t)15;
+  return hist_block_bytes(k_chunk, B, C, elem) + ((kScanScratchBytes + 15) & ~(size_t)15);
 }
-// chunks of 16 B per TreePoint row handled by the cooperative row loader (0 = generic byte gather)
+// chunks of 16 B per TreePoint row handled by the cooperative row loaders (0 = generic byte gather)
 inline int hist_row_chunks(int Fp) { return (Fp / 16 <= 8) ? Fp / 16 : 0; }
-inline size_t hist_tile_bytes(int ch) {
-  if (ch == 0) return 0;
-  const int stride = (ch >= 5) ? 17 : ((ch == 1 || ch == 2 || ch == 4) ? 32 + 8 / ch : 33);
-  return (size_t)(kHistThreads / 32) * 4 * ch * stride * 4 + 64 * 4;   // + per-feature tile offsets (k_chunk <= 64 here)
+inline bool hist_tma_rows(int ch) { return ch == 2 || ch == 4 || ch == 8; }   // a gather of four rows must fill a 128-byte aligned span
+// staging region of hist_scan_kernel (first in its dynamic shared memory, 1024-byte aligned):
+//   TMA:    [8 warps][32 rows][16*ch] swizzled stages | [8][32] (weight, label) words | [8] mbarriers | [k_chunk][4] schedule
+//   legacy: [8 warps] transposed row tiles | [64] per-feature tile offsets
+// never smaller than the scan's scratch, which reuses it
+inline size_t hist_region_bytes(int ch, bool tma, int k_chunk) {
+  size_t b = 0;
+  if (ch != 0 && tma && hist_tma_rows(ch)) {
+    b = (size_t)(kHistThreads / 32) * (32 * 16 * ch + 128 + 8) + (size_t)k_chunk * 8;
+  } else if (ch != 0) {
+    const int stride = (ch >= 5) ? 17 : ((ch == 1 || ch == 2 || ch == 4) ? 32 + 8 / ch : 33);
+    b = (size_t)(kHistThreads / 32) * 4 * ch * stride * 4 + 64 * 4;   // + per-feature tile offsets (k_chunk <= 64 here)
+  }
+  if (b < kScanScratchBytes) b = kScanScratchBytes;
+  return (b + 15) & ~(size_t)15;
 }
 
 // first index of the largest value among v(c), c < C, computed by one warp (call with all 32 lanes)
@@ -1128,7 +1155,31 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
   HPROF(7);
 }
 
-// Row staging for the accumulate loop.  A warp takes 32 entries at a time.  Its lanes fetch the 32
+// ---- asynchronous row staging (sm_100a): mbarrier + TMA tile::gather4 ---------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+               : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) { while (!mbar_try_wait(bar, parity)) {} }
+// Four rows r0..r3 of the 2-D tensor (box {row bytes, 1}) land back to back at dst (swizzled as the map says) and
+// complete_tx 4 * row bytes on the barrier.  The map covers this GPU's row-major TreePoint matrix only.
+__device__ __forceinline__ void tma_gather4_rows(uint32_t dst, const CUtensorMap* tm, int r0, int r1, int r2, int r3, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+      ::"r"(dst), "l"(tm), "r"(0), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(bar) : "memory");
+}
+
+// Legacy row staging for the accumulate loop (EMRF_NO_TMA=1, and rows that are not 16/32/64/128 bytes).  A warp takes 32 entries at a time.  Its lanes fetch the 32
 // TreePoint rows cooperatively with 128-bit loads (CH = Fp/16 chunks per row, so one warp-wide
 // LDG.128 covers 32/CH whole rows: every fetched sector is fully used and one row costs Fp bytes of
 // L2 traffic instead of one 32 B sector per feature), park them TRANSPOSED in shared memory
@@ -1177,21 +1228,23 @@ __device__ __forceinline__ uint64_t load_entry(const uint64_t* __restrict__ ent,
 }
 
 template <int CH, class HT = uint32_t>
-__global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_scan_kernel(const HistArgs A) {
+__global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_scan_kernel(const __grid_constant__ HistArgs A) {
   constexpr bool U16 = sizeof(HT) == 2;
   HPROF_DECL
-  extern __shared__ __align__(16) uint8_t smem_raw[];
+  // no static shared memory in this kernel: the dynamic block then starts on the 1024-byte boundary the swizzled TMA
+  // stages need (they come first); layout: [staging region / scan scratch][histogram block]
+  extern __shared__ __align__(1024) uint8_t hist_smem[];
   const int tid = threadIdx.x;
   const int chunk = blockIdx.y;
   const int k0 = chunk * A.k_chunk;
   const int kc = min(A.k_chunk, A.f_sub - k0);
   const int B = A.B, C = A.C;
-  const ScanSmem<HT> S = carve_smem<HT>(smem_raw, A.k_chunk, B, C);
+  const ScanSmem<HT> S = carve_smem<HT>(hist_smem + A.hist_smem_off, hist_smem, A.k_chunk, B, C);
   HT* sh = S.hist;
   uint32_t* shw = reinterpret_cast<uint32_t*>(S.hist);   // the counters as 32-bit words (two per word when U16)
   int* sh_feat = S.feat;
   int* sh_nb = S.nb;
-  __shared__ int sh_last;
+  int& sh_last = *S.flag;
 
   const uint32_t tile_abs = blockIdx.x + A.tile_base;
   const uint32_t g = A.tile_node[tile_abs];
@@ -1279,6 +1332,94 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
         }
       }
     }
+  } else if ((CH == 2 || CH == 4 || CH == 8) && A.use_tma) {
+    // ---- TMA row staging.  Every warp owns one stage of 32 rows x FPB bytes and one mbarrier.  Per batch of 32 entries:
+    // lanes 0..7 each issue one cp.async.bulk.tensor tile::gather4 (four whole rows of the row-major TreePoint matrix per
+    // instruction, no LSU/L1 traffic, no registers), the copy engine writes the rows with the map's swizzle
+    // (16-byte chunk c of stage row r sits at chunk c ^ ((r * FPB >> 7) & (CH - 1)) of its line) and signals the
+    // barrier; the warp then adds its lane's row: one LDS.U8 + one shared atomic per feature.  The next batch's entries
+    // are already in registers, and its gathers are issued right after the stage has been read (24 warps per SM keep
+    // ~24 batches in flight).  Reads: lane = row, but the four 8-lane groups walk the node's features in rotated
+    // order (features sorted by the bank class (f >> 2) & 3 of their byte): rows r..r+7 of one feature cover eight
+    // different 16-byte bank groups, the four groups then differ in the word inside them -> few bank conflicts.
+    constexpr int FPB = 16 * CH;
+    constexpr int NW = kHistThreads / 32;
+    const int lane = tid & 31, wv = tid >> 5, q = lane >> 3;
+    uint8_t* stage = hist_smem + wv * (32 * FPB);
+    uint32_t* meta = reinterpret_cast<uint32_t*>(hist_smem + NW * 32 * FPB) + wv * 32;
+    const uint32_t bar = smem_u32(hist_smem + NW * (32 * FPB + 128)) + 8u * wv;
+    uint16_t* sched = reinterpret_cast<uint16_t*>(hist_smem + NW * (32 * FPB + 128 + 8));   // [kc][4]: feature | k << 8
+    if (lane == 0) { mbar_init(bar, 1); mbar_fence_init(); }
+    // schedule: position p of the class-sorted order holds subset index perm[p]; group q takes p = (i + q * stride) % kc at step i
+    {
+      int* perm = reinterpret_cast<int*>(hist_smem);  // scratch before the first gather (start of warp 0's stage; kc <= 64)
+      for (int k = tid; k < kc; k += kHistThreads) {
+        const int cls = (sh_feat[k] >> 2) & 3;
+        int rank = 0;
+        for (int j = 0; j < kc; j++) { const int cj = (sh_feat[j] >> 2) & 3; rank += (cj < cls) || (cj == cls && j < k); }
+        perm[rank] = k;
+      }
+      __syncthreads();
+      const int stride = (kc + 3) >> 2;
+      for (int t = tid; t < kc * 4; t += kHistThreads) {
+        const int i = t >> 2, qq = t & 3;
+        const int k = perm[(i + qq * stride) % kc];
+        sched[t] = (uint16_t)(sh_feat[k] | (k << 8));
+      }
+      __syncthreads();
+    }
+    const uint32_t n_batches = (len + 31) / 32;
+    const uint32_t my_batches = (uint32_t)wv < n_batches ? (n_batches - wv + NW - 1) / NW : 0u;
+    const uint32_t BC = (uint32_t)(B * C);
+    const uint32_t lane_xor = (((uint32_t)(lane * FPB) >> 7) & (uint32_t)(CH - 1)) << 4;
+    const uint8_t* my_row = stage + lane * FPB;
+    constexpr int KR = 12;                           // features per node held in registers (covers sqrt(F) up to F = 144)
+    const bool in_regs = kc <= KR;
+    uint32_t offr[KR], plr[KR];
+#pragma unroll
+    for (int i = 0; i < KR; i++) {
+      const uint32_t e = i < kc ? sched[i * 4 + q] : 0u;
+      offr[i] = (e & 0xffu) ^ lane_xor;
+      plr[i] = (e >> 8) * BC;
+    }
+    auto load_entry = [&](uint32_t i) -> uint64_t {    // entry of this lane in the warp's i-th batch
+      const uint32_t j = (wv + NW * i) * 32 + lane;
+      return (i < my_batches && j < len) ? __ldcs(ent + j) : 0ull;
+    };
+    const uint32_t stage_addr = smem_u32(stage);
+    auto issue = [&](uint64_t e) {
+      meta[lane] = (uint32_t)(e >> 32) & 0xffffu;      // weight | label << 8, read back by this lane only
+      const int row = (int)(uint32_t)e;                // padding entries gather row 0 with weight 0
+      const int src = 4 * (lane & 7);
+      const int r0 = __shfl_sync(0xffffffffu, row, src), r1 = __shfl_sync(0xffffffffu, row, src + 1);
+      const int r2 = __shfl_sync(0xffffffffu, row, src + 2), r3 = __shfl_sync(0xffffffffu, row, src + 3);
+      if (lane == 0) mbar_arrive_expect_tx(bar, 32 * FPB);
+      __syncwarp();
+      if (lane < 8) tma_gather4_rows(stage_addr + lane * (4 * FPB), &A.tmap, r0, r1, r2, r3, bar);
+    };
+    if (my_batches) issue(load_entry(0));
+    uint64_t e_pref = load_entry(1);
+    for (uint32_t i = 0; i < my_batches; i++) {
+      mbar_wait(bar, i & 1u);
+      const uint32_t m = meta[lane];
+      const uint32_t w = m & 0xffu, lab = m >> 8;
+      if (w) {
+        if (in_regs) {
+#pragma unroll
+          for (int s_ = 0; s_ < KR; s_++)
+            if (s_ < kc) hist_add(plr[s_] + my_row[offr[s_]] * C + lab, w);
+        } else {
+          for (int s_ = 0; s_ < kc; s_++) {
+            const uint32_t e = sched[s_ * 4 + q];
+            hist_add((e >> 8) * BC + my_row[(e & 0xffu) ^ lane_xor] * C + lab, w);
+          }
+        }
+      }
+      __syncwarp();                                    // every lane has read the stage: it may be overwritten
+      const uint64_t e_now = e_pref;
+      e_pref = load_entry(i + 2);
+      if (i + 1 < my_batches) issue(e_now);
+    }
   } else if (CH == 0) {
     // generic path (rows wider than 128 B): one byte gather per (entry, feature)
     for (uint32_t j = tid; j < len; j += kHistThreads) {
@@ -1300,11 +1441,11 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     const int lane = tid & 31, wv = tid >> 5;
     const int rlane = lane & (ROWS - 1), part = lane / ROWS;
     constexpr int NW = kHistThreads / 32;
-    uint32_t* tile = reinterpret_cast<uint32_t*>(smem_raw + A.tile_smem_off) + wv * RowTile<CHX>::kWarpWords;
+    uint32_t* tile = reinterpret_cast<uint32_t*>(hist_smem) + wv * RowTile<CHX>::kWarpWords;
     const uint8_t* tile_b = reinterpret_cast<const uint8_t*>(tile);
     const uint32_t n_batches = (len + ROWS - 1) / ROWS;
     // per-feature byte offsets into the transposed tile: word (f >> 2) of every row, byte (f & 3)
-    int* sh_off = reinterpret_cast<int*>(smem_raw + A.tile_smem_off + NW * RowTile<CHX>::kWarpWords * 4);
+    int* sh_off = reinterpret_cast<int*>(hist_smem + NW * RowTile<CHX>::kWarpWords * 4);
     for (int k = tid; k < kc; k += kHistThreads) sh_off[k] = (((sh_feat[k] >> 2) * TS) << 2) + (sh_feat[k] & 3);
     __syncthreads();
     // the subset's tile offsets in registers when it is small (8 per lane sharing a row), else read per use
@@ -1432,7 +1573,7 @@ __global__ void __launch_bounds__(kHistThreads) scan_kernel(const uint32_t* __re
   const int g = blockIdx.x, chunk = blockIdx.y;
   const int k0 = chunk * k_chunk;
   const int kc = min(k_chunk, f_sub - k0);
-  const ScanSmem<uint32_t> S = carve_smem<uint32_t>(smem_raw, k_chunk, B, C);
+  const ScanSmem<uint32_t> S = carve_smem<uint32_t>(smem_raw, smem_raw + hist_block_bytes(k_chunk, B, C), k_chunk, B, C);
   uint32_t* sh = S.hist;
   int* sh_nb = S.nb;
   for (int k = tid; k < kc; k += kHistThreads) sh_nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
@@ -1457,7 +1598,7 @@ __global__ void __launch_bounds__(kHistThreads) scan_sum_kernel(const uint32_t* 
   const int local = blockIdx.x, g = node0 + local, chunk = blockIdx.y;
   const int k0 = chunk * k_chunk;
   const int kc = min(k_chunk, f_sub - k0);
-  const ScanSmem<uint32_t> S = carve_smem<uint32_t>(smem_raw, k_chunk, B, C);
+  const ScanSmem<uint32_t> S = carve_smem<uint32_t>(smem_raw, smem_raw + hist_block_bytes(k_chunk, B, C), k_chunk, B, C);
   uint32_t* sh = S.hist;
   for (int k = tid; k < kc; k += kHistThreads) S.nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
   const size_t slot_words = (size_t)f_sub * B * C;

@@ -114,9 +114,9 @@ def test_large_matrix_and_l2_blocked_tile_order_match_oracle(oracle):
 
 
 def test_kernel_variants_match_oracle(oracle):
-    """The histogram kernel's variants are chosen per launch / per node: 16-bit counters when every node of a
-    group is light and single-tile, column-major gathers for nodes holding >= 1/4 of the rows, tiled entry-list
-    kernels.  A 200 000-row fit passes through all of them (u32 at the top, u16 below; dense roots, sparse deep
+    """The histogram kernel's variants are chosen per launch / per node: rows staged by TMA gathers or by LDG/STS,
+    16-bit counters when every node of a group is light and single-tile, column-major gathers for nodes holding
+    >= 1/4 of the rows, tiled entry-list kernels.  A 200 000-row fit passes through all of them (u32 at the top, u16 below; dense roots, sparse deep
     nodes); the same fit with every variant switched off must give the same forest, and both must equal the
     oracle's.  Subprocesses: the switches are read once per process."""
     import os, subprocess, sys
@@ -129,7 +129,10 @@ def test_kernel_variants_match_oracle(oracle):
             "o = ob.fit(ob.make_params(num_trees=6, max_depth=8, num_classes=50), X, y, ob.partition_offsets(len(X), 96)).export()\n"
             "assert all(np.array_equal(v, o[k]) for k, v in m.export().items())\n"
             "print('VARIANT_OK')\n") % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    for env in ({}, {"EMRF_HIST_U32": "1", "EMRF_CM_DIV": "0", "EMRF_LIST_SIMPLE": "1"}, {"EMRF_CM_DIV": "64"}):
+    # {}: TMA-gathered row staging (the default); EMRF_NO_TMA=1: the LDG/STS staging it replaced, alone and with the
+    # other variants off; EMRF_CM_DIV=0 with TMA: every node, dense roots included, goes through the gathers
+    for env in ({}, {"EMRF_NO_TMA": "1"}, {"EMRF_NO_TMA": "1", "EMRF_HIST_U32": "1", "EMRF_CM_DIV": "0", "EMRF_LIST_SIMPLE": "1"},
+                {"EMRF_CM_DIV": "0"}, {"EMRF_CM_DIV": "64"}):
         r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "VARIANT_OK" in r.stdout, str(env) + r.stdout[-1500:] + r.stderr[-1500:]
 

@@ -110,3 +110,37 @@ def test_estimator_setters_mirror_spark_requires():
                 lambda: rf.setFeatureSubsetStrategy("half")):
         with pytest.raises(ValueError):
             bad()
+
+
+def _import_forest(tree_off, left, right, feature, F=4, C_=2):
+    """emrf_forest_import on a raw description (no GPU needed: the check is host code). Returns the status code."""
+    L = _lib()
+    n = len(left)
+    a = [np.asarray(tree_off, np.int64), np.arange(n, dtype=np.int32), np.asarray(left, np.int32), np.asarray(right, np.int32),
+         np.asarray(feature, np.int32), np.zeros(n), np.zeros(n), np.zeros(n), np.zeros(n), np.ones(n * C_)]
+    h = C.c_void_p()
+    rc = L.emrf_forest_import(None, len(tree_off) - 1, C_, F, *[x.ctypes.data for x in a], C.byref(h))
+    if rc == 0:
+        L.emrf_forest_free(h)
+    return rc
+
+
+def test_forest_import_rejects_corrupted_descriptions():
+    """RandomForestClassificationModel.load / fromJson feed emrf_forest_import from files: a description that is not a
+    set of proper pre-order trees (cycle, shared child, child outside its tree, bad feature) must be refused, not walked."""
+    ok = dict(tree_off=[0, 3, 4], left=[1, -1, -1, -1], right=[2, -1, -1, -1], feature=[0, -1, -1, -1])
+    assert _import_forest(**ok) == 0
+    bad = [
+        dict(ok, tree_off=[1, 3, 4]),                      # does not start at 0
+        dict(ok, tree_off=[0, 3, 3]),                      # empty tree
+        dict(ok, left=[0, -1, -1, -1]),                    # a node is its own child (cycle)
+        dict(ok, left=[1, -1, -1, -1], right=[1, -1, -1, -1]),   # both children the same node
+        dict(ok, right=[3, -1, -1, -1]),                   # child outside the tree
+        dict(ok, feature=[4, -1, -1, -1]),                 # feature out of range
+        dict(tree_off=[0, 5], left=[1, 3, 3, -1, -1], right=[2, 4, 4, -1, -1], feature=[0, 1, 1, -1, -1]),  # shared children
+        dict(tree_off=[0, 4], left=[1, -1, -1, -1], right=[2, -1, -1, -1], feature=[0, -1, -1, -1]),        # unreachable node
+        dict(tree_off=[0, 3], left=[1, -1, -1], right=[-1, -1, -1], feature=[0, -1, -1]),                   # one child only
+    ]
+    for d in bad:
+        assert _import_forest(**d) == -1, d
+        assert b"forest description" in _lib().emrf_last_error()

@@ -10,12 +10,21 @@ timed region, forest back on the host.
 
 N > 1 (one process per GPU, torchrun): ONE forest of 100 trees on N x 1M rows, ROW-sharded across the
 ranks (weak scaling: 1M rows per GPU; north_star's mode for large shapes): each rank bins, bags and
-histograms its own rows and the ranks all-reduce the node histograms with NCCL every group.
+histograms its own rows and the ranks reduce the node histograms with NCCL every group.
 `--mode trees` instead shards the trees of one 100*N-tree forest (all rows on every rank).  torch is
 used for the rendezvous / barrier only.
 
+Besides the headline the line carries
+  * parity evidence: `parity_vs_oracle` (N = 1: the timed forest against the CPU oracle's, field by field) and
+    `parity_vs_1gpu` (N > 1: the sharded forest against a one-GPU fit of the same global rows on rank 0, plus a
+    forest digest agreed by every rank);
+  * `configs2`: one fit of BASELINE configs[2] (RF 500 trees, depth 12, 10M x 128, 8192 partitions) at this N —
+    one GPU, row-sharded and tree-sharded — with the histogram kernel's roofline fraction, the collectives' time
+    and the strong-scaling efficiency against the one-GPU fit of the same run;
+  * `predict`: batch prediction (BASELINE configs[4] shape) rows/s.
+
 --impl reference: times the CPU oracle (the restated Spark MLlib algorithm; no JVM/Spark exists on
-this box, so there is no oracle/_ref) on the host cores, on a bounded sample of the same workload.
+this box, so there is no oracle/_ref) on the host cores, on the same workload.
 """
 import argparse
 import ctypes as C
@@ -25,6 +34,7 @@ import subprocess
 import sys
 import threading
 import time
+import zlib
 
 import numpy as np
 
@@ -35,6 +45,11 @@ N_ROWS, N_FEATURES, N_CLASSES = 1_000_000, 64, 50
 TREES_PER_GPU, MAX_DEPTH, MAX_BINS, N_PARTS = 100, 10, 32, 1024
 METRIC, UNIT = "rf_fit_rows_trees_per_sec", "rows*trees/s"
 CPU_SAMPLE_TREES = 100   # the whole workload: ~8 s on 16 cores
+SEED = 207336481
+# BASELINE configs[2]
+C2_ROWS, C2_FEATURES, C2_TREES, C2_DEPTH, C2_PARTS = 10_000_000, 128, 500, 12, 8192
+# BASELINE configs[4] (rows are streamed through the forest in resident chunks of this many rows)
+C4_ROWS_RESIDENT = 10_000_000
 
 
 def workload_name(n_gpus, mode="rows"):
@@ -43,6 +58,13 @@ def workload_name(n_gpus, mode="rows"):
     parts = N_PARTS * (n_gpus if mode == "rows" else 1)
     return (f"BASELINE.json configs[1]: RF {trees} trees, depth {MAX_DEPTH}, maxBins {MAX_BINS}, "
             f"{rows} synthetic draw rows x {N_FEATURES} features, {N_CLASSES}-class label, {parts} partitions")
+
+
+def make_config(n_gpus, mode, parallelism, timing):
+    """Both arms print the same keys (the driver compares the two lines' `config`)."""
+    return {"workload": workload_name(n_gpus, mode), "seed": SEED,
+            "l2": "inputs (512 MB f64 features, 1 GB entry lists) are larger than the 126 MB L2; no explicit flush",
+            "parallelism": parallelism, "timing": timing}
 
 
 class ClockSampler:
@@ -89,21 +111,30 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def oracle_params(ob, trees, seed=207336481):
+def oracle_params(ob, trees, seed=SEED):
     return ob.make_params(num_trees=trees, max_depth=MAX_DEPTH, max_bins=MAX_BINS, num_classes=N_CLASSES, seed=seed)
 
 
+def host_threads():
+    """All the host threads this process may use.  torchrun exports OMP_NUM_THREADS=1 to its workers, which would turn
+    the CPU arm into a single-threaded run: the affinity mask is what really bounds us."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def time_oracle(trees):
-    """CPU port timed on all host cores, on the same rows/features with `trees` trees."""
+    """CPU port timed on all host cores, on the same rows/features with `trees` trees; returns the forest too."""
     from euromillioner_b200 import synth
     from oracle import binding as ob
+    ob.lib().orc_set_num_threads(host_threads())
     X, y = synth.flat(N_ROWS, N_FEATURES, N_CLASSES)
     po = ob.partition_offsets(N_ROWS, N_PARTS)
     t0 = time.perf_counter()
     fo = ob.fit(oracle_params(ob, trees), X, y, po)
     dt = time.perf_counter() - t0
-    nodes = int(fo.export()["tree_off"][-1])
-    return N_ROWS * trees / dt, dt, ob.lib().orc_num_threads(), nodes
+    return N_ROWS * trees / dt, dt, ob.lib().orc_num_threads(), fo.export()
 
 
 def run_reference(args, rank):
@@ -116,15 +147,46 @@ def run_reference(args, rank):
             vals.append(v); dts.append(dt)
     value = float(np.mean(vals))
     sample = (f"oracle port of Spark MLlib 2.4.6 RF (C++/OpenMP), same {N_ROWS} rows x {N_FEATURES} features, depth "
-              f"{MAX_DEPTH}, {CPU_SAMPLE_TREES} of {TREES_PER_GPU} trees per step")
+              f"{MAX_DEPTH}, {CPU_SAMPLE_TREES} of {TREES_PER_GPU} trees per step; Spark local[N] itself is unavailable on "
+              f"this box (no JVM)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": float(np.mean(dts)) * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": workload_name(1), "note": "Spark local[N] itself is unavailable on this box (no JVM)"},
+        "config": make_config(1, "rows", f"CPU, {cores} OpenMP threads (all host cores this process may use)",
+                              "wall clock around each fit (time.perf_counter)"),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
+
+
+def forests_equal(a, b):
+    """Field-by-field equality of two exported forests (dicts of arrays); returns (equal, first differing field)."""
+    for k in a:
+        if k not in b or not np.array_equal(a[k], b[k]):
+            return False, k
+    return True, None
+
+
+def forest_digest(exp):
+    d = 0
+    for k in sorted(exp):
+        d = zlib.crc32(np.ascontiguousarray(exp[k]).tobytes(), d)
+    return d
+
+
+def peak_hbm():
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        return json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def hist_roofline(tms, peak):
+    hist_ms = float(np.sum([t["hist_kernel_ms"] for t in tms]))
+    hist_bytes = float(np.sum([t["hist_alg_bytes"] for t in tms]))
+    achieved = hist_bytes / (hist_ms / 1e3) / 1e9 if hist_ms > 0 else 0.0
+    return hist_ms, hist_bytes, achieved, achieved / peak
 
 
 def main():
@@ -134,6 +196,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs2", action="store_true", help="skip the BASELINE configs[2] block (10M x 128, 500 trees)")
+    ap.add_argument("--no-predict", action="store_true", help="skip the batch-predict block (BASELINE configs[4] shape)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the N > 1 one-GPU parity fit")
     ap.add_argument("--mode", default="rows", choices=["rows", "trees"], help="how N > 1 GPUs share one forest")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -145,6 +210,8 @@ def main():
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             raise SystemExit("--gpus N > 1 must be launched with torchrun (one process per GPU)")
+    if args.warmup < 3:
+        args.warmup = 3      # timing rules: at least three untimed fits
 
     from euromillioner_b200 import _lib, synth
     from euromillioner_b200.classifier import Context, Dataset, RandomForestClassifier
@@ -157,6 +224,8 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from euromillioner_b200.dist import make_context
+        # the box's cores are shared by the ranks: say so instead of letting every rank spawn one thread per core
+        os.environ.setdefault("EMRF_HOST_THREADS", str(max(1, host_threads() // world)))
         ctx = make_context(dist)
     else:
         ctx = Context(local_rank)
@@ -166,6 +235,14 @@ def main():
             import torch
             dist.barrier()
             torch.cuda.synchronize()
+
+    def allreduce_max(vals):
+        if dist is None:
+            return [float(v) for v in vals]
+        import torch
+        t = torch.tensor(list(vals), device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t.tolist()]
 
     mode = args.mode if world > 1 else "rows"
     T = TREES_PER_GPU * (world if mode == "trees" else 1)
@@ -185,13 +262,21 @@ def main():
     _lib.check(L.emrf_memcpy_h2d(ctx.h, dX, hX, X.nbytes))
     _lib.check(L.emrf_memcpy_h2d(ctx.h, dy, hy, y.nbytes))
 
-    rf = (RandomForestClassifier(ctx).setNumTrees(T).setMaxDepth(MAX_DEPTH).setMaxBins(MAX_BINS)
-          .setNumClasses(N_CLASSES).setSeed(207336481))
+    def estimator(c, trees, depth=MAX_DEPTH):
+        return (RandomForestClassifier(c).setNumTrees(trees).setMaxDepth(depth).setMaxBins(MAX_BINS)
+                .setNumClasses(N_CLASSES).setSeed(SEED))
+
+    def shard_kw(rows_per_rank, parts_per_rank):
+        """Row-sharded Dataset arguments for this rank: contiguous rows at partition boundaries."""
+        ng, pg = rows_per_rank * world, parts_per_rank * world
+        goff = np.array([(i * ng) // pg for i in range(pg + 1)], np.int64)
+        assert goff[rank * parts_per_rank] == rank * rows_per_rank and goff[(rank + 1) * parts_per_rank] == (rank + 1) * rows_per_rank
+        local = goff[rank * parts_per_rank:(rank + 1) * parts_per_rank + 1] - goff[rank * parts_per_rank]
+        return dict(partition_offsets=local, global_partition_offsets=goff, first_partition=rank * parts_per_rank)
+
+    rf = estimator(ctx, T)
     if world > 1 and mode == "rows":
-        goff = np.array([(i * n_global) // (N_PARTS * world) for i in range(N_PARTS * world + 1)], np.int64)
-        assert goff[rank * N_PARTS] == rank * N_ROWS and goff[(rank + 1) * N_PARTS] == (rank + 1) * N_ROWS
-        local = goff[rank * N_PARTS:(rank + 1) * N_PARTS + 1] - goff[rank * N_PARTS]
-        shard = dict(partition_offsets=local, global_partition_offsets=goff, first_partition=rank * N_PARTS)
+        shard = shard_kw(N_ROWS, N_PARTS)
         ds_dev = Dataset(dX.value, dy.value, n_rows=N_ROWS, n_features=N_FEATURES, **shard)
         ds_host = Dataset(pX, py, **shard)
     else:
@@ -228,12 +313,47 @@ def main():
     e2e_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
 
-    step_ms = float(np.sum(ev_ms))
-    if dist is not None:
-        import torch
-        t = torch.tensor([step_ms, e2e_ms, wall_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        step_ms, e2e_ms, wall_ms = [float(v) for v in t.tolist()]
+    step_ms, e2e_ms, wall_ms = allreduce_max([float(np.sum(ev_ms)), e2e_ms, wall_ms])
+    peak, peak_src = peak_hbm()
+
+    # ---- parity evidence for the timed forest
+    parity = {}
+    exp = model.export()
+    if world > 1:
+        dig = float(forest_digest(exp))
+        lo = -allreduce_max([-dig])[0]
+        hi = allreduce_max([dig])[0]
+        parity["forest_digest_same_on_all_ranks"] = bool(lo == hi)
+        if not args.no_parity:
+            # rank 0 fits the same global Dataset on its own GPU alone; the sharded forest must equal it bit for bit
+            ok = 1.0
+            if rank == 0:
+                c1 = Context(local_rank)
+                n1, p1, t1 = (n_global, N_PARTS * world, T)
+                g = synth.DeviceFlat(c1, n1, N_FEATURES, N_CLASSES)
+                m1 = estimator(c1, t1).fit(Dataset(g.X.value, g.y.value, num_partitions=p1, n_rows=n1, n_features=N_FEATURES))
+                eq, field = forests_equal(exp, m1.export())
+                parity["parity_vs_1gpu"] = bool(eq)
+                if not eq:
+                    parity["parity_first_difference"] = field
+                parity["one_gpu_fit_ms"] = round(c1.timings()["total_ms"], 2)
+                ok = 1.0 if eq else 0.0
+                g.free()
+                del m1
+                c1.close()
+            barrier()
+            _ = ok
+
+    # ---- BASELINE configs[2]: one fit of the shape the north star quotes its targets on, at this N
+    configs2 = None
+    if not args.no_configs2:
+        configs2 = run_configs2(ctx, world, rank, local_rank, barrier, allreduce_max, estimator, shard_kw, peak)
+
+    # ---- batch prediction (BASELINE configs[4] shape)
+    predict = None
+    if not args.no_predict:
+        predict = run_predict(ctx, world, rank, barrier, allreduce_max, estimator)
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -241,29 +361,22 @@ def main():
 
     units = n_global * T * args.steps
     value = units / (step_ms / 1e3)
-    hist_ms = float(np.sum([t["hist_kernel_ms"] for t in tms]))
-    hist_bytes = float(np.sum([t["hist_alg_bytes"] for t in tms]))
+    hist_ms, hist_bytes, achieved, frac = hist_roofline(tms, peak)
     hist_launches = int(np.sum([t["hist_launches"] for t in tms]))
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
-    else:
-        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    achieved = hist_bytes / (hist_ms / 1e3) / 1e9 if hist_ms > 0 else 0.0
     traffic = None
     tp = os.path.join(ROOT, "profiles", "hist_kernel_traffic.json")
-    if os.path.exists(tp):
+    if world == 1 and os.path.exists(tp):   # one ncu capture of this round's kernel on this workload (per launch, mean)
         traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+    cfg = make_config(world, mode,
+                      ("row-sharded x%d (NCCL reduce-scatter of node histograms per group)" % world if mode == "rows"
+                       else "tree-sharded x%d" % world) if world > 1 else "1 GPU",
+                      "CUDA events on the engine stream per fit (emrf_timings_t.total_ms)")
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": step_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u32", "data": "synthetic",
-        "config": {"workload": workload_name(world, mode),
-                   "parallelism": ("row-sharded x%d (NCCL all-reduce of node histograms per group)" % world if mode == "rows"
-                                   else "tree-sharded x%d" % world) if world > 1 else "1 GPU",
-                   "l2": "inputs (512 MB f64 features, 1 GB entry lists) are larger than the 126 MB L2; no explicit flush",
-                   "seed": 207336481, "timing": "CUDA events on the engine stream per fit (emrf_timings_t.total_ms)",
-                   "wall_ms_per_step": wall_ms / args.steps, "ms_each_step": [round(v, 2) for v in ev_ms]},
+        "config": cfg,
+        "wall_ms_per_step": wall_ms / args.steps, "ms_each_step": [round(v, 2) for v in ev_ms],
         "clocks": clocks,
         "e2e": {"value": units / (e2e_ms / 1e3), "unit": UNIT,
                 "h2d_bytes_per_step": int(np.mean([t["h2d_bytes"] for t in e2e_tm])),
@@ -273,25 +386,146 @@ def main():
                     "total_ms", "h2d_ms", "find_splits_ms", "bin_ms", "bag_ms", "hist_kernel_ms", "partition_ms")}},
         "gpu_launches": int(np.sum([t["kernel_launches"] for t in tms])),
         "roofline": {"bound": "hbm", "kernel": "hist_scan_kernel (DTStatsAggregator update + binsToBestSplit)",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": frac, "traffic": traffic,
                      "peak_source": peak_src, "launches": hist_launches,
                      "avg_launch_ms": hist_ms / max(hist_launches, 1),
                      "algorithmic_bytes_per_launch": hist_bytes / max(hist_launches, 1),
+                     "algorithmic_bytes": "(F_sub + 6) B per in-bag (row, tree, level) + F_sub*B*C*4 B per node (SURVEY 8d)",
+                     "entry_bytes_only_frac": float(np.sum([t["hist_units"] for t in tms])) * (8 + 6) / (hist_ms / 1e3) / 1e9 / peak,
                      "share_of_step": hist_ms / step_ms},
         "phases_ms_per_step": {k: float(np.mean([t[k] for t in tms])) for k in (
             "find_splits_ms", "bin_ms", "bag_ms", "hist_kernel_ms", "partition_ms", "host_scheduler_ms",
-            "host_select_ms", "host_update_ms", "host_export_ms", "bag_kernel_ms")},
+            "host_select_ms", "host_update_ms", "host_export_ms", "bag_kernel_ms", "comm_ms")},
+        "comm_bytes_per_step": int(np.mean([t["comm_bytes"] for t in tms])),
         "groups_per_step": int(tms[0]["num_groups"]), "total_nodes": int(model.totalNumNodes),
-        "gain_mismatches": int(np.sum([t["gain_mismatches"] for t in tms])),
     }
+    out.update(parity)
     if world == 1 and not args.no_cpu_baseline:
-        v, dt, cores, _ = time_oracle(CPU_SAMPLE_TREES)
+        v, dt, cores, oexp = time_oracle(CPU_SAMPLE_TREES)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                "sample": f"oracle port (C++/OpenMP) on the same {N_ROWS} rows x {N_FEATURES} features, depth "
                                          f"{MAX_DEPTH}, {CPU_SAMPLE_TREES} of {TREES_PER_GPU} trees: {dt:.1f} s"}
+        eq, field = forests_equal(exp, oexp)     # the timed forest (all 100 trees, 1M rows) against the oracle's
+        out["parity_vs_oracle"] = bool(eq)
+        if not eq:
+            out["parity_first_difference"] = field
+    if configs2 is not None:
+        out["configs2"] = configs2
+    if predict is not None:
+        out["predict"] = predict
     print(json.dumps(out), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def run_configs2(ctx, world, rank, local_rank, barrier, allreduce_max, estimator, shard_kw, peak):
+    """BASELINE configs[2]: RF 500 trees, depth 12, 10M x 128, 8192 partitions.  One warm-up and one timed fit per mode
+    (a fit is seconds long); features generated in HBM by emrf_synth_flat.  N > 1: the rows (then the trees) of the SAME
+    forest are sharded (strong scaling), and rank 0 fits it alone as well: efficiency = t_1 / (N * t_N), forests compared."""
+    from euromillioner_b200 import synth
+    from euromillioner_b200.classifier import Context, Dataset
+
+    def timed_fit(c, ds, trees, reps=1):
+        rf2 = estimator(c, trees, C2_DEPTH)
+        m = rf2.fit(ds)                      # warm-up: buffers of this shape are allocated and faulted in
+        barrier()
+        best, tm_best = None, None
+        for _ in range(reps):
+            m = rf2.fit(ds)
+            tm = c.timings()
+            ms = allreduce_max([tm["total_ms"]])[0]
+            if best is None or ms < best:
+                best, tm_best = ms, tm
+        barrier()
+        return m, best, tm_best
+
+    def block(ms, tm, n_gpus):
+        hist_ms, _, achieved, frac = hist_roofline([tm], peak)
+        return {"ms_per_fit": round(ms, 2), "rows_trees_per_sec": C2_ROWS * C2_TREES / (ms / 1e3), "n_gpus": n_gpus,
+                "hist_kernel_ms": round(hist_ms, 2), "hist_achieved_gbs": round(achieved, 1), "hist_frac_of_hbm_peak": round(frac, 4),
+                "partition_ms": round(tm["partition_ms"], 2), "comm_ms": round(tm["comm_ms"], 2), "comm_bytes": int(tm["comm_bytes"]),
+                "groups": int(tm["num_groups"]), "host_scheduler_ms": round(tm["host_scheduler_ms"], 1)}
+
+    out = {"workload": f"BASELINE.json configs[2]: RF {C2_TREES} trees, depth {C2_DEPTH}, maxBins {MAX_BINS}, {C2_ROWS} rows x "
+                       f"{C2_FEATURES} features, {N_CLASSES}-class label, {C2_PARTS} partitions; one warm-up + one timed fit per mode"}
+    one_exp, t1 = None, None
+    if rank == 0:
+        c1 = ctx if world == 1 else Context(local_rank)
+        g = synth.DeviceFlat(c1, C2_ROWS, C2_FEATURES, N_CLASSES)
+        ds = Dataset(g.X.value, g.y.value, num_partitions=C2_PARTS, n_rows=C2_ROWS, n_features=C2_FEATURES)
+        # no barrier inside: the other ranks wait below
+        rf2 = estimator(c1, C2_TREES, C2_DEPTH)
+        rf2.fit(ds)
+        m = rf2.fit(ds)
+        tm = c1.timings()
+        t1 = tm["total_ms"]
+        out["one_gpu"] = block(t1, tm, 1)
+        out["one_gpu"]["total_nodes"] = int(m.totalNumNodes)
+        if world > 1:
+            one_exp = m.export()
+        del m
+        g.free()
+        if world > 1:
+            c1.close()
+    if world == 1:
+        return out
+    barrier()
+    t1 = allreduce_max([t1 if rank == 0 else 0.0])[0]
+    # ---- row-sharded: contiguous rows at partition boundaries
+    rows_r, parts_r = C2_ROWS // world, C2_PARTS // world
+    g = synth.DeviceFlat(ctx, rows_r, C2_FEATURES, N_CLASSES, row_start=rank * rows_r)
+    ds = Dataset(g.X.value, g.y.value, n_rows=rows_r, n_features=C2_FEATURES, **shard_kw(rows_r, parts_r))
+    m, ms, tm = timed_fit(ctx, ds, C2_TREES)
+    if rank == 0:
+        out["row_sharded"] = block(ms, tm, world)
+        out["row_sharded"]["efficiency_vs_one_gpu"] = round(t1 / (world * ms), 3)
+        out["row_sharded"]["parity_vs_1gpu"] = bool(forests_equal(m.export(), one_exp)[0])
+    del m
+    g.free()
+    barrier()
+    # ---- tree-sharded: every rank holds all rows, trees t % world == rank are built here
+    g = synth.DeviceFlat(ctx, C2_ROWS, C2_FEATURES, N_CLASSES)
+    ds = Dataset(g.X.value, g.y.value, num_partitions=C2_PARTS, n_rows=C2_ROWS, n_features=C2_FEATURES)
+    m, ms, tm = timed_fit(ctx, ds, C2_TREES)
+    if rank == 0:
+        out["tree_sharded"] = block(ms, tm, world)
+        out["tree_sharded"]["efficiency_vs_one_gpu"] = round(t1 / (world * ms), 3)
+        out["tree_sharded"]["parity_vs_1gpu"] = bool(forests_equal(m.export(), one_exp)[0])
+    del m
+    g.free()
+    barrier()
+    return out
+
+
+def run_predict(ctx, world, rank, barrier, allreduce_max, estimator):
+    """Batch prediction, BASELINE configs[4] shape: a 500-tree depth-12 forest over 128 features; every rank walks its own
+    rows (rows are independent: no collective).  The forest is fitted on 200k rows (what bounds predict is the number of
+    nodes visited, not how the forest was made); C4_ROWS_RESIDENT rows per rank generated in HBM, labels back on the host."""
+    from euromillioner_b200 import synth
+    from euromillioner_b200.classifier import Context, Dataset
+    c = Context(ctx.device) if world > 1 else ctx      # predict needs no communicator
+    gfit = synth.DeviceFlat(c, 200_000, C2_FEATURES, N_CLASSES)
+    m = estimator(c, C2_TREES, C2_DEPTH).fit(Dataset(gfit.X.value, gfit.y.value, num_partitions=64, n_rows=200_000,
+                                                     n_features=C2_FEATURES))
+    gfit.free()
+    n = C4_ROWS_RESIDENT
+    g = synth.DeviceFlat(c, n, C2_FEATURES, N_CLASSES, row_start=rank * n)
+    ds = Dataset(g.X.value, None, n_rows=n, n_features=C2_FEATURES)
+    m.transform(ds, raw=False, probability=False)   # warm-up (forest upload, buffers)
+    barrier()
+    t0 = time.perf_counter()
+    m.transform(ds, raw=False, probability=False)
+    ms = allreduce_max([(time.perf_counter() - t0) * 1e3])[0]
+    barrier()
+    g.free()
+    out = {"workload": f"BASELINE.json configs[4] shape: {C2_TREES}-tree depth-{C2_DEPTH} forest ({int(m.totalNumNodes)} nodes, fitted on "
+                       f"200000 rows), {n} rows x {C2_FEATURES} features per GPU resident in HBM, predicted labels copied to the host",
+           "n_gpus": world, "ms": round(ms, 2), "rows_per_sec": n * world / (ms / 1e3),
+           "tree_walks_per_sec": n * world * C2_TREES / (ms / 1e3),
+           "input_gbs": n * world * C2_FEATURES * 8 / (ms / 1e3) / 1e9}
+    if world > 1:
+        c.close()
+    return out
 
 
 if __name__ == "__main__":

@@ -31,7 +31,8 @@ class EmrfTimings(C.Structure):
         "hist_kernel_ms", "partition_ms", "host_scheduler_ms")] + [(n, C.c_int64) for n in (
             "hist_launches", "kernel_launches", "hist_alg_bytes", "hist_units", "num_groups",
             "total_nodes_split", "gain_mismatches", "h2d_bytes", "d2h_bytes")] + [
-        (n, C.c_double) for n in ("host_select_ms", "host_update_ms", "host_export_ms", "bag_kernel_ms")]
+        (n, C.c_double) for n in ("host_select_ms", "host_update_ms", "host_export_ms", "bag_kernel_ms", "comm_ms")] + [
+        (n, C.c_int64) for n in ("comm_bytes", "gains_verified")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -91,6 +92,7 @@ def lib():
     L.emrf_best_splits.argtypes = [vp, vp, i32, vp, i32, vp, i32, i32, i32, i32, f64, vp, vp, vp, vp, vp, vp]
     L.emrf_update_partition.argtypes = [vp, vp, i64, i32, vp, vp, i32, vp, vp, vp, vp]
     L.emrf_build_lag_features.argtypes = [vp, vp, i32, i32, i32, vp, vp]
+    L.emrf_synth_flat.argtypes = [vp, i64, i32, i32, i64, i64, vp, vp]
     L.emrf_update_partition_noalloc.argtypes = [vp, vp, i64, i32, vp, vp, i32, vp, vp, vp, vp]
     L.emrf_host_java_random_next_long.argtypes = [i64, i32]
     L.emrf_host_java_random_next_long.restype = i64

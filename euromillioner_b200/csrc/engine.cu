@@ -1388,7 +1388,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   GroupSel* cur = &sel_a;
   GroupSel* nxt = &sel_b;
   std::vector<int> tree_slot(T, -1);
-  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_ev, part_ev;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> hist_ev, part_ev, comm_ev;
   double host_ms = 0.0, host_sel = 0.0, host_upd = 0.0;
   static const bool verify_gains = env_flag("EMRF_VERIFY_GAINS");
   c->arena_reset();
@@ -1500,8 +1500,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const PodVec<GroupEntry>& group = pd.sel->group;
     const PodVec<int32_t>& group_feat = pd.sel->feat;
     const Upd* upd = pd.upd.data();
-    int64_t mism = 0;
-#pragma omp parallel for num_threads(pd.nt) schedule(static) reduction(+ : mism)
+    int64_t mism = 0, verified = 0;
+#pragma omp parallel for num_threads(pd.nt) schedule(static) reduction(+ : mism, verified)
     for (int gi = 0; gi < pd.n_nodes; gi++) {
       const GroupEntry& g = group[gi];
       const uint32_t dw = upd[gi].dec;
@@ -1519,6 +1519,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       HNode& n = tr.pool[g.pool];
       const bool is_leaf = !(dw & kern::kDecNonLeaf);
       if (verify_gains) {
+        verified++;
         if (valid) {
           std::vector<uint32_t> rightc(C);
           uint64_t lc = 0, rc = 0;
@@ -1548,6 +1549,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       rn.impurity = rimp; rn.cnt_a = totc; rn.cnt_b = leftc; rn.pred = r.right_pred;
     }
     tm.gain_mismatches += mism;
+    tm.gains_verified += verified;
     pd.sel = nullptr;
     return EMRF_OK;
   };
@@ -1572,7 +1574,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       for (const GroupEntry& g : group) total_entries += g.ub;
     }
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
-    tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
+    static const uint32_t tile_min = [] { const char* e = getenv("EMRF_TILE_MIN"); return e ? (uint32_t)std::max(256L, atol(e)) : 8192u; }();
+    static const uint32_t tile_div = [] { const char* e = getenv("EMRF_TILE_DIV"); return e ? (uint32_t)std::max(1L, atol(e)) : 16u; }();
+    if (tile_div != 16) tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * tile_div - 1) / ((uint64_t)c->sm_count * tile_div)), 256);
+    tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, tile_min), 65536);
     // TreePoint matrix larger than L2: many small tiles, launched in row-range order (below), so that the
     // CTAs resident at any moment gather rows from the same slice of the matrix and trees share it in L2
     if (l2_blocked) tile_len = 8192;
@@ -1763,6 +1768,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       hist_ev.emplace_back(e0, e1);
       CU(cudaGetLastError());
     }
+    // collectives are timed on their own (CUDA events right around each call: emrf_timings_t.comm_ms)
+    auto comm_begin = [&]() -> cudaEvent_t { cudaEvent_t e = c->events.get(); cudaEventRecord(e, st); return e; };
+    auto comm_end = [&](cudaEvent_t e0, int64_t bytes) { cudaEvent_t e1 = c->events.get(); cudaEventRecord(e1, st); comm_ev.emplace_back(e0, e1); tm.comm_bytes += bytes; };
     if (c->world > 1) {
       if (row_sharded && push_mode) {
         // every rank's partials must have landed in the owners' staging buffers: a 1-word all-reduce is the
@@ -1783,7 +1791,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         // does it: a reduce-scatter leaves each rank with the summed histograms (exact integers) of ITS
         // share of the group's nodes, it scans those, and the small split records are combined with an
         // all-reduce over zero-filled slots (as in the tree-sharded mode).
-        TRY(nccl_reduce_scatter_u32(c, c->d_ghist.as<uint32_t>(), (size_t)nodes_per_rank * slot_words));
+        {
+          const cudaEvent_t e0 = comm_begin();
+          TRY(nccl_reduce_scatter_u32(c, c->d_ghist.as<uint32_t>(), (size_t)nodes_per_rank * slot_words));
+          comm_end(e0, (int64_t)nodes_per_rank * c->world * (int64_t)slot_words * 4);
+        }
         const int first = c->rank * nodes_per_rank;
         const int mine_n = std::max(0, std::min(nodes_per_rank, n_nodes - first));
         if (mine_n > 0) {
@@ -1796,7 +1808,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           CU(cudaGetLastError());
         }
       }
-      TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_dec / 4));
+      {
+        const cudaEvent_t e0 = comm_begin();
+        TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_dec / 4));
+        comm_end(e0, (int64_t)res_dec);
+      }
     }
     // ---- decisions and partition work on the device, the partition kernels right behind.  The host gets the
     // compact scheduling records first (second stream) and the full records after them.
@@ -2025,6 +2041,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   CU(cudaEventElapsedTime(&ms, ev_b0, ev_b1)); tm.bag_kernel_ms = ms;
   for (auto& pr : hist_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.hist_kernel_ms += ms; }
   for (auto& pr : part_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.partition_ms += ms; }
+  for (auto& pr : comm_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.comm_ms += ms; }
   if (env_flag("EMRF_DEBUG_TIMERS")) {
     // GPU timeline of the group loop: hist end -> (decide) -> partition start, partition end -> next hist start
     double gap_dec = 0, gap_next = 0, first_to_last = 0;
@@ -2845,6 +2862,23 @@ extern "C" int emrf_build_lag_features(emrf_ctx_t* c, const int32_t* draws, int3
   if (labels_hd && !y_dev) CU(cudaMemcpyAsync(labels_hd, dy, (size_t)n_rows * 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   return EMRF_OK;
+}
+
+extern "C" int emrf_synth_flat(emrf_ctx_t* c, int64_t n_rows, int32_t n_features, int32_t n_classes, int64_t seed, int64_t row_start,
+                               double* features_dev, double* labels_dev) {
+  if (!c || !features_dev) return fail(EMRF_ERR_ARG, "NULL argument");
+  if (n_rows < 0 || n_features < 1 || n_classes < 1 || row_start < 0) return fail(EMRF_ERR_ARG, "bad shape");
+  if (!is_device_ptr(features_dev) || (labels_dev && !is_device_ptr(labels_dev))) return fail(EMRF_ERR_ARG, "outputs must be device buffers");
+  return guarded(c, [&]() -> int {
+    CU(cudaSetDevice(c->device));
+    if (n_rows == 0) return EMRF_OK;
+    const int64_t total = n_rows * n_features;
+    const unsigned grid = (unsigned)std::min<int64_t>((total + 255) / 256, (int64_t)c->sm_count * 32);
+    kern::synth_flat_kernel<<<grid, 256, 0, c->stream>>>(n_rows, n_features, n_classes, (uint64_t)seed, row_start, features_dev, labels_dev);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(c->stream));
+    return EMRF_OK;
+  });
 }
 
 #ifdef EMRF_HIST_PROF

@@ -2281,5 +2281,34 @@ __global__ void lag_features_kernel(const int32_t* __restrict__ draws, int n_dra
   if (f == 0 && y) y[row] = (double)(draws[(size_t)t * 7 + ball] - 1);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Synthetic flat-mode inputs (there is no network for the reference's scrape,
+// Main.java:37-67): x[i][j] = 1 + splitmix64(seed, i*F + j) mod 50, label[i] = (x[i][0] + x[i][3] +
+// splitmix64(seed ^ 0xA5A5A5A5, i) mod 5) mod C — the same index-addressable generator as synth.flat, on the
+// device, so that the 10 GB matrix of BASELINE configs[2] never crosses PCIe.
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ inline uint64_t splitmix64_at(uint64_t seed, uint64_t idx) {
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull * (idx + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+__global__ void synth_flat_kernel(int64_t n_rows, int F, int C, uint64_t seed, int64_t row_start, double* __restrict__ X,
+                                  double* __restrict__ y) {
+  const int64_t total = n_rows * F;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / F;
+    const int f = (int)(i - r * F);
+    const uint64_t g = (uint64_t)(row_start + r);
+    X[i] = (double)(1 + (int)(splitmix64_at(seed, g * (uint64_t)F + (uint64_t)f) % 50));
+    if (f == 0 && y) {
+      const int v0 = 1 + (int)(splitmix64_at(seed, g * (uint64_t)F) % 50);
+      const int v3 = F > 3 ? 1 + (int)(splitmix64_at(seed, g * (uint64_t)F + 3) % 50) : 0;
+      const int e = (int)(splitmix64_at(seed ^ 0xA5A5A5A5ull, g) % 5);
+      y[r] = (double)((v0 + v3 + e) % C);
+    }
+  }
+}
+
 }  // namespace kern
 }  // namespace emrf

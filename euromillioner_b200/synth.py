@@ -66,3 +66,37 @@ def draw_history(n_draws=1500, lag=10, ball=0, seed=20200614):
         X[:, (l - 1) * 7:(l - 1) * 7 + 7] = b[lag - l:n_draws - l]
     y = (b[lag:, ball] - 1).astype(np.float64)
     return X, y, (50 if ball < 5 else 12)
+
+
+class DeviceFlat:
+    """flat() generated in HBM by the engine (emrf_synth_flat): device pointers of an n_rows x n_features float64 matrix
+    and its labels, for shapes whose host copy would only exist to cross PCIe (BASELINE configs[2]: 10 GB)."""
+
+    def __init__(self, ctx, n_rows, n_features, n_classes=50, seed=42, row_start=0):
+        import ctypes as C
+        from . import _lib
+        L = _lib.lib()
+        self.ctx, self.n_rows, self.n_features = ctx, int(n_rows), int(n_features)
+        self.X, self.y = C.c_void_p(), C.c_void_p()
+        _lib.check(L.emrf_dev_alloc(ctx.h, self.n_rows * self.n_features * 8, C.byref(self.X)))
+        _lib.check(L.emrf_dev_alloc(ctx.h, self.n_rows * 8, C.byref(self.y)))
+        _lib.check(L.emrf_synth_flat(ctx.h, self.n_rows, self.n_features, n_classes, seed, row_start, self.X, self.y))
+
+    def to_host(self):
+        import ctypes as C
+        import numpy as np
+        from . import _lib
+        L = _lib.lib()
+        X = np.empty((self.n_rows, self.n_features), np.float64)
+        y = np.empty(self.n_rows, np.float64)
+        _lib.check(L.emrf_memcpy_d2h(self.ctx.h, C.c_void_p(X.ctypes.data), self.X, X.nbytes))
+        _lib.check(L.emrf_memcpy_d2h(self.ctx.h, C.c_void_p(y.ctypes.data), self.y, y.nbytes))
+        return X, y
+
+    def free(self):
+        from . import _lib
+        L = _lib.lib()
+        for p in (self.X, self.y):
+            if p and p.value:
+                L.emrf_dev_free(self.ctx.h, p)
+        self.X = self.y = None

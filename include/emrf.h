@@ -80,6 +80,10 @@ typedef struct {
   double host_update_ms;    /*   driver-side node updates after each group */
   double host_export_ms;    /*   LearningNode.toNode(prune) + flat export */
   double bag_kernel_ms;     /* the Poisson kernel alone (second stream, overlaps h2d/findSplits/binning) */
+  double comm_ms;           /* multi-GPU: device time of the per-group collectives (reduceByKey's merge of the node
+                               histograms: reduce-scatter, and the all-reduce of the split records), CUDA events */
+  int64_t comm_bytes;       /*   bytes this rank handed to those collectives (send buffers, summed over groups) */
+  int64_t gains_verified;   /* EMRF_VERIFY_GAINS=1: split records recomputed on the host (gain_mismatches counts the differences) */
 } emrf_timings_t;
 
 const char* emrf_last_error(void);
@@ -204,6 +208,14 @@ int emrf_update_partition(emrf_ctx_t* ctx, const uint8_t* bins_cm, int64_t n_row
  * (labels_hd may be NULL).  Outputs may be host or device buffers. */
 int emrf_build_lag_features(emrf_ctx_t* ctx, const int32_t* draws, int32_t n_draws, int32_t lag, int32_t ball,
                             double* features_hd, double* labels_hd);
+
+/* Synthetic flat-mode inputs of SURVEY.md Appendix C, generated in place on the device (the reference's own inputs come
+ * from a web scrape, Main.java:37-67, which has no network here): rows [row_start, row_start + n_rows) of
+ * x[i][j] = 1 + splitmix64(seed, i*F + j) mod 50 and label[i] = (x[i][0] + x[i][3] + splitmix64(seed ^ 0xA5A5A5A5, i) mod 5)
+ * mod n_classes, bit-identical to euromillioner_b200/synth.py flat().  labels_dev may be NULL.  Used by bench.py for the
+ * 10M x 128 shape of BASELINE configs[2], whose 10 GB should not cross PCIe. */
+int emrf_synth_flat(emrf_ctx_t* ctx, int64_t n_rows, int32_t n_features, int32_t n_classes, int64_t seed,
+                    int64_t row_start, double* features_dev, double* labels_dev);
 
 /* Partition update for callers that cannot allocate device memory (a process whose GPU memory is
  * wholly owned by a pool allocator, or a loop that must avoid cudaMalloc's device-wide sync).

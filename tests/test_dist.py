@@ -44,6 +44,21 @@ def test_reference_arm_runs_on_rank0_only(monkeypatch):
     assert r.returncode == 0 and r.stdout.strip() == ""
 
 
+def test_reference_arm_uses_all_cores_under_torchrun():
+    """torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm must still use every core it may run on
+    (round 1: the reference arm ran single-threaded at N > 1 and was killed by the driver's time limit)."""
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "import bench\n"
+            "from oracle import binding as ob\n"
+            "ob.lib().orc_set_num_threads(bench.host_threads())\n"
+            "print('THREADS', ob.lib().orc_num_threads(), bench.host_threads())\n") % ROOT
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, OMP_NUM_THREADS="1"), capture_output=True, text=True,
+                       timeout=120)
+    assert r.returncode == 0, r.stderr[-1000:]
+    used, avail = [int(v) for v in r.stdout.split("THREADS")[1].split()[:2]]
+    assert used == avail and (avail == 1 or used > 1)
+
+
 @pytest.mark.gpu
 def test_tree_and_row_sharded_fits_match_oracle_on_2_gpus():
     import ctypes

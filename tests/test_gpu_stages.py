@@ -170,3 +170,17 @@ def test_lag_feature_builder_matches_host_construction(ctx, ball, lag):
     X, y = stages.build_lag_features(d, lag, ball, ctx)
     Xw, yw, _ = synth.draw_history(400, lag, ball)
     assert np.array_equal(X, Xw) and np.array_equal(y, yw)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,F,C_,start", [(3000, 10, 50, 0), (1000, 64, 50, 123456), (257, 3, 12, 7), (2048, 128, 50, 9_999_000)])
+def test_device_generator_matches_numpy_generator(ctx, n, F, C_, start):
+    """emrf_synth_flat (App. C flat mode, generated in HBM for the configs[2] bench shape) == synth.flat, bit for bit."""
+    from euromillioner_b200 import synth
+    d = synth.DeviceFlat(ctx, n, F, C_, seed=42, row_start=start)
+    try:
+        X, y = d.to_host()
+    finally:
+        d.free()
+    Xn, yn = synth.flat(n, F, C_, seed=42, row_start=start)
+    assert np.array_equal(X, Xn) and np.array_equal(y, yn)

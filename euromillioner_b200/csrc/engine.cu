@@ -1625,11 +1625,23 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       const uint32_t* ntp = nt_tmp.data();
       uint32_t* tbp = tb_tmp.data();
       int32_t* slp = slot_tmp.data();
+      // tile order = launch order: the tiles of multi-tile nodes (full tiles, the longest CTAs) first, then the larger
+      // single-tile nodes, then the small ones, so that a launch does not end on a few long CTAs (a group arrives in
+      // pop order: deepest, i.e. smallest, nodes first).  Row-range order (l2_blocked) has its own tile map.
+      uint32_t cls_tiles[3] = {0, 0, 0};
       for (int i = 0; i < n_nodes; i++) {
-        tbp[i] = n_tiles;
         slp[i] = (all_slots || ntp[i] > 1) ? n_slots++ : -1;
-        n_tiles += ntp[i];
+        const int cls = l2_blocked ? 0 : (ntp[i] > 1 ? 0 : (group[i].ub >= 2048 ? 1 : 2));
+        tbp[i] = (uint32_t)cls;              // class now, first tile below
+        cls_tiles[cls] += ntp[i];
       }
+      uint32_t cls_off[3] = {0, cls_tiles[0], cls_tiles[0] + cls_tiles[1]};
+      for (int i = 0; i < n_nodes; i++) {
+        const uint32_t cls = tbp[i];
+        tbp[i] = cls_off[cls];
+        cls_off[cls] += ntp[i];
+      }
+      n_tiles = cls_tiles[0] + cls_tiles[1] + cls_tiles[2];
     }
     const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
     const size_t group_bytes = l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4;

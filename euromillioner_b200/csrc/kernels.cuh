@@ -1020,39 +1020,77 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
   HPROF_DECL
   HT* sh = S.hist;
   const int* nb = S.nb;
-  // (a) inclusive prefix sum over bins for every (feature, class) column — conflict-free
-  for (int p = tid; p < kc * C; p += NT) {
-    const int k = p / C, c = p - k * C;
-    HT* col = sh + (size_t)k * B * C + c;
-    uint32_t run = 0;
-    const int n = nb[k];
-    for (int b = 0; b < n; b++) { run += col[b * C]; col[b * C] = (HT)run; }
+  // (a) inclusive prefix sum over bins for every (feature, class) column.  Up to 32 bins (maxBins' default): one warp
+  // per column, lane = bin, five shuffle steps — two columns in flight per warp; more bins: one thread per column.
+  if (B <= 32) {
+    const int lane = tid & 31, nwp = NT >> 5;
+    const int n_cols = kc * C;
+    for (int p = tid >> 5; p < n_cols; p += 2 * nwp) {
+      const int p2 = p + nwp;
+      const int k = p / C, c = p - k * C;
+      const int k2 = p2 < n_cols ? p2 / C : k, c2 = p2 < n_cols ? p2 - k2 * C : c;
+      HT* col = sh + (size_t)k * B * C + c;
+      HT* col2 = sh + (size_t)k2 * B * C + c2;
+      const int n = nb[k], n2 = p2 < n_cols ? nb[k2] : 0;
+      uint32_t v = lane < n ? (uint32_t)col[lane * C] : 0u;
+      uint32_t v2 = lane < n2 ? (uint32_t)col2[lane * C] : 0u;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, v, d), t2 = __shfl_up_sync(0xffffffffu, v2, d);
+        if (lane >= d) { v += t; v2 += t2; }
+      }
+      if (lane < n) col[lane * C] = (HT)v;
+      if (lane < n2) col2[lane * C] = (HT)v2;
+    }
+  } else {
+    for (int p = tid; p < kc * C; p += NT) {
+      const int k = p / C, c = p - k * C;
+      HT* col = sh + (size_t)k * B * C + c;
+      uint32_t run = 0;
+      const int n = nb[k];
+      for (int b = 0; b < n; b++) { run += col[b * C]; col[b * C] = (HT)run; }
+    }
   }
   __syncthreads();
   HPROF(4);
-  // (b) node totals = last bin of the chunk's first feature (every feature sums to the same)
+  // (b) node totals = last bin of the chunk's first feature (every feature sums to the same), their sum, and the
+  // parent impurity: the per-class terms in parallel, then the ordered subtraction chain (Gini.calculate /
+  // Entropy.calculate accumulate class by class) by one lane reading them back from shared memory
   for (int c = tid; c < C; c += NT) S.tot[c] = sh[(size_t)(nb[0] - 1) * C + c];
   __syncthreads();
   uint32_t tot_all = 0;
-  for (int c = 0; c < C; c++) tot_all += S.tot[c];
-  // parent impurity: the per-class terms in parallel, then the ordered subtraction chain
-  for (int c = tid; c < C; c += NT) {
-    double term = 0.0;
-    const uint32_t v = S.tot[c];
-    if (v && tot_all) {
-      const double f = __ddiv_rn((double)v, (double)tot_all);
-      term = impurity == 0 ? __dmul_rn(f, f) : __dmul_rn(f, __ddiv_rn(log(f), log(2.0)));
-    }
-    S.sq[c] = term;
+  {
+    const int lane = tid & 31;
+    for (int c = lane; c < C; c += 32) tot_all += S.tot[c];
+    for (int o = 16; o; o >>= 1) tot_all += __shfl_xor_sync(0xffffffffu, tot_all, o);
   }
-  __syncthreads();
-  if (tid == 0) {
-    double imp = 0.0;
-    if (tot_all) {
-      imp = impurity == 0 ? 1.0 : 0.0;
-      for (int c = 0; c < C; c++) imp = __dsub_rn(imp, S.sq[c]);
+  if (tid < 32) {
+    for (int c = tid; c < C; c += 32) {
+      double term = 0.0;
+      const uint32_t v = S.tot[c];
+      if (v && tot_all) {
+        const double f = __ddiv_rn((double)v, (double)tot_all);
+        term = impurity == 0 ? __dmul_rn(f, f) : __dmul_rn(f, __ddiv_rn(log(f), log(2.0)));
+      }
+      S.sq[c] = term;
     }
-    *S.pimp = imp;
+    __syncwarp();
+    if (tid == 0) {
+      double imp = 0.0;
+      if (tot_all) {
+        imp = impurity == 0 ? 1.0 : 0.0;
+        int c = 0;
+        for (; c + 8 <= C; c += 8) {          // eight loads in flight, then the ordered chain
+          double t[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) t[j] = S.sq[c + j];
+#pragma unroll
+          for (int j = 0; j < 8; j++) imp = __dsub_rn(imp, t[j]);
+        }
+        for (; c < C; c++) imp = __dsub_rn(imp, S.sq[c]);
+      }
+      *S.pimp = imp;
+    }
   }
   __syncthreads();
   const double pimp = *S.pimp;
@@ -1101,8 +1139,7 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
     if (gain > best_gain) { best_gain = gain; best_idx = cand; best_li = li; best_ri = ri; best_lc = lc; }  // first max
   }
   // (d) block arg-max: greatest gain, ties → smallest candidate index (= Spark's first maximum
-  // in (subset order, split order))
-  __syncthreads();
+  // in (subset order, split order)): warp shuffles, one barrier, then every warp folds the per-warp results itself
   HPROF(6);
   const int my_idx = best_idx;   // this thread's own best candidate (keeps best_li / best_ri)
   for (int o = 16; o; o >>= 1) {
@@ -1112,20 +1149,20 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
   }
   if ((tid & 31) == 0) { S.red_gain[tid >> 5] = best_gain; S.red_idx[tid >> 5] = best_idx; }
   __syncthreads();
-  if (tid < 32) {
-    const int nw = NT >> 5;
-    double g = tid < nw ? S.red_gain[tid] : -INFINITY;
-    int ix = tid < nw ? S.red_idx[tid] : 0x7fffffff;
-    for (int o = 16; o; o >>= 1) {
+  double g;
+  int ix;
+  {
+    const int nw = NT >> 5, lane = tid & 31;
+    g = lane < nw ? S.red_gain[lane] : -INFINITY;
+    ix = lane < nw ? S.red_idx[lane] : 0x7fffffff;
+    for (int o = 4; o; o >>= 1) {          // at most 8 warps per CTA
       const double g2 = __shfl_xor_sync(0xffffffffu, g, o);
       const int i2 = __shfl_xor_sync(0xffffffffu, ix, o);
       if (g2 > g || (g2 == g && i2 < ix)) { g = g2; ix = i2; }
     }
-    if (tid == 0) { S.red_gain[0] = g; S.red_idx[0] = ix; }
+    g = __shfl_sync(0xffffffffu, g, 0);
+    ix = __shfl_sync(0xffffffffu, ix, 0);
   }
-  __syncthreads();
-  const double g = S.red_gain[0];
-  const int ix = S.red_idx[0];
   if (ix == 0x7fffffff) {
     if (tid == 0) {
       res->gain = kInvalidGain; res->impurity = pimp; res->left_impurity = 0.0; res->right_impurity = 0.0;
@@ -1246,23 +1283,25 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
   int* sh_nb = S.nb;
   int& sh_last = *S.flag;
 
+  // the node's descriptors are three dependent loads deep (tile -> node -> segment / features -> bins per feature); the
+  // histogram is cleared while the first of them is in flight
   const uint32_t tile_abs = blockIdx.x + A.tile_base;
   const uint32_t g = A.tile_node[tile_abs];
+  for (int i = tid; i < (kc * B * C * (int)sizeof(HT) + 3) / 4; i += kHistThreads) shw[i] = 0;
+  HPROF(1);
   GroupNode nd = A.nodes[g];
-  if (A.segtab) {
-    const Seg sg = A.segtab[nd.seg_slot];
-    nd.seg_start = sg.start; nd.seg_len = sg.len; nd.buf = sg.buf;
-  }
-  const uint32_t tile_in_node = A.tile_q ? A.tile_q[tile_abs] : tile_abs - nd.tile_begin;
   for (int k = tid; k < kc; k += kHistThreads) {
     const int f = A.node_feat[(size_t)g * A.f_sub + k0 + k];
     sh_feat[k] = f;
     sh_nb[k] = A.num_bins_all[f];
   }
-  HPROF(0);
-  for (int i = tid; i < (kc * B * C * (int)sizeof(HT) + 3) / 4; i += kHistThreads) shw[i] = 0;
+  if (A.segtab) {
+    const Seg sg = A.segtab[nd.seg_slot];
+    nd.seg_start = sg.start; nd.seg_len = sg.len; nd.buf = sg.buf;
+  }
+  const uint32_t tile_in_node = A.tile_q ? A.tile_q[tile_abs] : tile_abs - nd.tile_begin;
   __syncthreads();
-  HPROF(1);
+  HPROF(0);
 
   // ---- accumulate this tile
   // counter idx gets += w: a 32-bit shared atomic either way (U16: on the word holding the pair, no carry can

@@ -1290,6 +1290,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   // 16-bit counters for launches of small single-tile nodes (EMRF_HIST_U32=1 turns them off)
   const size_t hist_smem16 = hist_region + kern::hist_block_bytes(k_chunk, B, C, 2);
   const bool allow_u16 = !row_sharded && !env_flag("EMRF_HIST_U32");
+  // ... also for groups with multi-tile nodes (their last tile then scans the 32-bit sums k_chunk / 2 features at a time)
+  const bool u16_mixed_ok = allow_u16 && n_chunks == 1 && k_chunk >= 2 && !env_flag("EMRF_NO_U16_MIXED");
   // nodes holding at least 1/EMRF_CM_DIV of the rows gather from the column-major matrix (0: never)
   uint32_t cm_min_len = 0;
   {
@@ -1574,10 +1576,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       for (const GroupEntry& g : group) total_entries += g.ub;
     }
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
-    static const uint32_t tile_min = [] { const char* e = getenv("EMRF_TILE_MIN"); return e ? (uint32_t)std::max(256L, atol(e)) : 8192u; }();
-    static const uint32_t tile_div = [] { const char* e = getenv("EMRF_TILE_DIV"); return e ? (uint32_t)std::max(1L, atol(e)) : 16u; }();
-    if (tile_div != 16) tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * tile_div - 1) / ((uint64_t)c->sm_count * tile_div)), 256);
-    tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, tile_min), 65536);
+    // 16-bit launch with multi-tile nodes: a tile's counters cannot pass 65535 if its entries' weights cannot, i.e. if
+    // tile_len * (largest bootstrap weight) <= 65535; its nodes' summed histograms live in HBM as 32-bit words.  Used
+    // when the group's tiles would be about that short anyway (every group below the top levels); EMRF_HIST_U32=1: off
+    const uint32_t tile16 = (65535u / (uint32_t)std::max(bag_maxw, 1)) & ~255u;
+    const bool u16_mixed = allow_u16 && u16_mixed_ok && tile_len <= tile16 && tile16 >= 2048;
+    tile_len = std::min<uint32_t>(std::max<uint32_t>(tile_len, 8192), 65536);
+    if (u16_mixed) tile_len = std::min(tile_len, tile16);
     // TreePoint matrix larger than L2: many small tiles, launched in row-range order (below), so that the
     // CTAs resident at any moment gather rows from the same slice of the matrix and trees share it in L2
     if (l2_blocked) tile_len = 8192;
@@ -1742,7 +1747,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
     A.tile_len = tile_len;
     // every node in one tile and light enough: 16-bit counters, more CTAs per SM
-    const bool u16 = allow_u16 && n_slots == 0 && max_weight <= 65535u;
+    const bool u16 = u16_mixed || (allow_u16 && n_slots == 0 && max_weight <= 65535u);
     if (env_flag("EMRF_DEBUG_GROUPS"))
       fprintf(stderr, "[emrf] group %zu: nodes %d tiles %u slots %d max_weight %u tile_len %u u16 %d\n", fo->group_sizes.size(), n_nodes,
               n_tiles, n_slots, max_weight, tile_len, (int)u16);

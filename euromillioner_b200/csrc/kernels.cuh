@@ -948,8 +948,10 @@ struct ScanSmem {
   int* feat;           // [k_chunk]
   int* nb;             // [k_chunk]
   int* flag;           // [1]  "this CTA is the node's last tile"
+  double* inc_gain;    // [1]  best gain of the pieces of this node scanned so far (scan in pieces, see scan_chunk)
+  int* inc_has;        // [1]  ... and whether any of them had a candidate
 };
-constexpr size_t kScanScratchBytes = 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + 8;   // 3184, kept 16-byte aligned below
+constexpr size_t kScanScratchBytes = 256 * 4 + 256 * 8 + 9 * 8 + 8 * 4 + 8 + 16;   // 3200
 __host__ __device__ inline size_t scan_hist_bytes(int k_chunk, int B, int C, int elem) {
   return ((size_t)k_chunk * B * C * elem + 15) & ~(size_t)15;
 }
@@ -969,6 +971,8 @@ __device__ __forceinline__ ScanSmem<HT> carve_smem(uint8_t* raw_hist, uint8_t* r
   s.red_gain = s.sq + 256;
   s.pimp = s.red_gain + 8;
   s.red_idx = reinterpret_cast<int*>(s.pimp + 1);
+  s.inc_gain = reinterpret_cast<double*>(s.red_idx + 8);
+  s.inc_has = reinterpret_cast<int*>(s.inc_gain + 1);
   return s;
 }
 // the scan kernels: histogram block, then the scratch
@@ -1013,9 +1017,13 @@ __device__ __forceinline__ int warp_first_argmax(int C, int lane, F v) {
 
 // Scans a histogram chunk held in shared memory: hist[kc][B][C]; nb[k] = numBins of subset
 // feature k0+k.  All threads of the CTA participate; writes the chunk's result record.
+// `later_piece`: the node is scanned in pieces (a multi-tile node of a 16-bit launch: its summed 32-bit counters only fit
+// the histogram block a few features at a time); an earlier piece has already written the record, and this one replaces
+// it only with a strictly greater gain — Spark's first maximum in (subset order, split order) over all features.
 template <class HT>
 __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, int impurity, int min_instances,
-                           double min_info_gain, ScanResult* res, uint32_t* left_out, uint32_t* total_out) {
+                           double min_info_gain, ScanResult* res, uint32_t* left_out, uint32_t* total_out,
+                           bool later_piece = false) {
   const int tid = threadIdx.x, NT = blockDim.x;
   HPROF_DECL
   HT* sh = S.hist;
@@ -1163,6 +1171,9 @@ __device__ void scan_chunk(const ScanSmem<HT>& S, int kc, int k0, int B, int C, 
     g = __shfl_sync(0xffffffffu, g, 0);
     ix = __shfl_sync(0xffffffffu, ix, 0);
   }
+  if (later_piece && *S.inc_has && !(ix != 0x7fffffff && g > *S.inc_gain)) return;   // uniform: every thread reads the same words
+  __syncthreads();                                                                  // ... before they are replaced
+  if (tid == 0) { *S.inc_gain = ix == 0x7fffffff ? -INFINITY : g; *S.inc_has = ix != 0x7fffffff; }
   if (ix == 0x7fffffff) {
     if (tid == 0) {
       res->gain = kInvalidGain; res->impurity = pimp; res->left_impurity = 0.0; res->right_impurity = 0.0;
@@ -1383,7 +1394,8 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     // different 16-byte bank groups, the four groups then differ in the word inside them -> few bank conflicts.
     constexpr int FPB = 16 * CH;
     constexpr int NW = kHistThreads / 32;
-    const int lane = tid & 31, wv = tid >> 5, q = lane >> 3;
+    const int lane = tid & 31, q = lane >> 3;
+    const int wv = __shfl_sync(0xffffffffu, tid >> 5, 0);     // warp-uniform for the compiler: stage and barrier addresses stay in uniform registers
     uint8_t* stage = hist_smem + wv * (32 * FPB);
     uint32_t* meta = reinterpret_cast<uint32_t*>(hist_smem + NW * 32 * FPB) + wv * 32;
     const uint32_t bar = smem_u32(hist_smem + NW * (32 * FPB + 128)) + 8u * wv;
@@ -1412,6 +1424,12 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     const uint32_t BC = (uint32_t)(B * C);
     const uint32_t lane_xor = (((uint32_t)(lane * FPB) >> 7) & (uint32_t)(CH - 1)) << 4;
     const uint8_t* my_row = stage + lane * FPB;
+    // Counter address of (feature step s, bin, label) as a 32-bit shared address: base[s] + bin * cstep + label term.
+    // 32-bit counters: word index; 16-bit counters with an even class count: the pair's word and a weight shifted into
+    // the label's half (both fixed per entry) — four instructions per feature: LDS.U8, IMAD, IADD, RED.
+    const bool fast_addr = !U16 || (C & 1) == 0;
+    const uint32_t cstep = U16 ? (uint32_t)C * 2u : (uint32_t)C * 4u;
+    const uint32_t hist_addr = smem_u32(shw);
     constexpr int KR = 12;                           // features per node held in registers (covers sqrt(F) up to F = 144)
     const bool in_regs = kc <= KR;
     uint32_t offr[KR], plr[KR];
@@ -1419,7 +1437,7 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     for (int i = 0; i < KR; i++) {
       const uint32_t e = i < kc ? sched[i * 4 + q] : 0u;
       offr[i] = (e & 0xffu) ^ lane_xor;
-      plr[i] = (e >> 8) * BC;
+      plr[i] = fast_addr ? hist_addr + (e >> 8) * BC * (U16 ? 2u : 4u) : (e >> 8) * BC;
     }
     auto load_entry = [&](uint32_t i) -> uint64_t {    // entry of this lane in the warp's i-th batch
       const uint32_t j = (wv + NW * i) * 32 + lane;
@@ -1436,6 +1454,7 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
       __syncwarp();
       if (lane < 8) tma_gather4_rows(stage_addr + lane * (4 * FPB), &A.tmap, r0, r1, r2, r3, bar);
     };
+    auto red_add = [](uint32_t addr, uint32_t v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); };
     if (my_batches) issue(load_entry(0));
     uint64_t e_pref = load_entry(1);
     for (uint32_t i = 0; i < my_batches; i++) {
@@ -1443,7 +1462,22 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
       const uint32_t m = meta[lane];
       const uint32_t w = m & 0xffu, lab = m >> 8;
       if (w) {
-        if (in_regs) {
+        if (in_regs && fast_addr) {
+          const uint32_t lterm = U16 ? (lab >> 1) * 4u : lab * 4u;
+          const uint32_t wv_ = U16 ? w << ((lab & 1u) << 4) : w;
+          // whole groups of four features run without per-step tests; the last partial group tests each step
+#pragma unroll
+          for (int g4 = 0; g4 < KR; g4 += 4) {
+            if (kc >= g4 + 4) {
+#pragma unroll
+              for (int s_ = g4; s_ < g4 + 4; s_++) red_add(plr[s_] + lterm + my_row[offr[s_]] * cstep, wv_);
+            } else {
+#pragma unroll
+              for (int s_ = g4; s_ < g4 + 4; s_++)
+                if (s_ < kc) red_add(plr[s_] + lterm + my_row[offr[s_]] * cstep, wv_);
+            }
+          }
+        } else if (in_regs) {
 #pragma unroll
           for (int s_ = 0; s_ < KR; s_++)
             if (s_ < kc) hist_add(plr[s_] + my_row[offr[s_]] * C + lab, w);
@@ -1539,7 +1573,7 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
   const size_t slot_words = (size_t)A.f_sub * B * C;
   const size_t rec = (size_t)g * A.n_chunks + chunk;                   // tickets: absolute
   const size_t rrec = (size_t)(g - A.node_base) * A.n_chunks + chunk;    // result record: relative to the launch
-  if constexpr (!U16) {     // 16-bit launches hold single-tile nodes of one GPU only
+  if constexpr (!U16) {     // the fused NVLink push is used by row-sharded fits, which never run 16-bit launches
   if (A.push_world) {
     // ---- fused histogram + reduce-scatter: this rank's partial histogram of node g is stored, dense and
     // coalesced, into slot [this rank][g's index on its owner] of the OWNER rank's staging buffer through
@@ -1566,7 +1600,9 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     for (int i = tid; i < kc * B * C; i += kHistThreads) dst[i] = __ldcg(&gh[i]);   // last tile forwards the sum
     return;
   }
+  }
   if (nd.slot >= 0) {
+    // multi-tile node: the tile's counters (16- or 32-bit) are added to the node's 32-bit slot in HBM
     uint32_t* gh = A.ghist + (size_t)nd.slot * slot_words + (size_t)k0 * B * C;
     for (int i = tid; i < kc * B * C; i += kHistThreads) {
       const uint32_t v = sh[i];
@@ -1579,14 +1615,33 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     __syncthreads();
     if (!sh_last) return;
     __threadfence();
-    for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = __ldcg(&gh[i]);
-    __syncthreads();
-  }
+    if constexpr (U16) {
+      // the summed counters need 32 bits: the last tile scans the node kh features at a time in the (16-bit) block,
+      // later pieces replacing the record only with a strictly greater gain
+      uint32_t* sh32 = reinterpret_cast<uint32_t*>(S.hist);
+      const int kh = kc / 2;                      // the engine runs such launches only with kc >= 2
+      ScanSmem<uint32_t> S32;
+      S32.hist = sh32; S32.tot = S.tot; S32.sq = S.sq; S32.red_gain = S.red_gain; S32.pimp = S.pimp; S32.red_idx = S.red_idx;
+      S32.flag = S.flag; S32.inc_gain = S.inc_gain; S32.inc_has = S.inc_has;
+      for (int kh0 = 0; kh0 < kc; kh0 += kh) {
+        const int khc = min(kh, kc - kh0);
+        __syncthreads();                          // the previous piece has been scanned
+        for (int i = tid; i < khc * B * C; i += kHistThreads) sh32[i] = __ldcg(&gh[(size_t)kh0 * B * C + i]);
+        S32.feat = S.feat + kh0; S32.nb = S.nb + kh0;
+        __syncthreads();
+        scan_chunk<uint32_t>(S32, khc, k0 + kh0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rrec],
+                             A.left_counts + rrec * C, A.total_counts + rrec * C, kh0 > 0);
+      }
+    } else {
+      for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = __ldcg(&gh[i]);
+      __syncthreads();
+    }
   }
   HPROF(3);
   HPROF_COUNT(9);
-  scan_chunk<HT>(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rrec],
-                 A.left_counts + rrec * C, A.total_counts + rrec * C);
+  if (!(U16 && nd.slot >= 0))
+    scan_chunk<HT>(S, kc, k0, B, C, A.impurity, A.min_instances, A.min_info_gain, &A.results[rrec],
+                   A.left_counts + rrec * C, A.total_counts + rrec * C);
   if (A.node_info) {          // n_chunks == 1: this record is the node's
     __syncthreads();          // the record's fields were written by several threads of this CTA
     if (tid == 0) {

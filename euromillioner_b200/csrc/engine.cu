@@ -1709,7 +1709,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const size_t off_sched = align_up(off_limits + 16, 16);
     const size_t off_ptiles = off_sched + (size_t)n_nodes * 16;
     CU(c->d_split.ensure(split_bytes));
-    CU(c->d_part.ensure(off_ptiles + (size_t)n_nodes * 4));
+    // one-pass partition: a status word per tile and the tile ticket behind them (cleared per group)
+    const size_t off_status = align_up(off_ptiles + (size_t)n_nodes * 4, 16);
+    const size_t status_bytes = (size_t)std::max<uint32_t>(ptiles_ub, 1) * 8 + 16;
+    CU(c->d_part.ensure(off_status + status_bytes));
     if ((size_t)next_slot + 2 * (size_t)n_nodes > seg_cap) {   // grow the segment table
       CU(cudaStreamSynchronize(st));
       DevBuf bigger;
@@ -1866,15 +1869,28 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     if (ptiles_ub) {
       cudaEvent_t p0 = c->events.get(), p1 = c->events.get();
       CU(cudaEventRecord(p0, st));
-      kern::part_count_kernel<<<ptiles_ub, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                       d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left,
-                                                                       c->p_segtab.as<kern::Seg>(), d_limits);
-      kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>(), d_limits);
-      kern::part_scatter_kernel<<<ptiles_ub, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                         d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
-                                                                         d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft,
+      static const bool three_pass = env_flag("EMRF_PART_3PASS");   // count / scan / scatter (stable order), for A/B runs
+      if (three_pass) {
+        kern::part_count_kernel<<<ptiles_ub, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                         d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left,
                                                                          c->p_segtab.as<kern::Seg>(), d_limits);
-      tm.kernel_launches += 3;
+        kern::part_scan_kernel<<<n_nodes, 256, 0, st>>>(dsn, d_tile_left, d_nleft, c->p_segtab.as<kern::Seg>(), d_limits);
+        kern::part_scatter_kernel<<<ptiles_ub, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                           d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                           d_cm.as<uint8_t>(), Np, dsn, dtn, d_tile_left, d_nleft,
+                                                                           c->p_segtab.as<kern::Seg>(), d_limits);
+        tm.kernel_launches += 3;
+      } else {
+        // one pass: every entry and bin byte is read once; tiles chain their left counts by look-back
+        unsigned long long* d_status = (unsigned long long*)((char*)c->d_part.p + off_status);
+        uint32_t* d_ticket = (uint32_t*)((char*)c->d_part.p + off_status + (size_t)std::max<uint32_t>(ptiles_ub, 1) * 8);
+        CU(cudaMemsetAsync(d_status, 0, status_bytes, st));
+        kern::part_onepass_kernel<<<ptiles_ub, kern::kPartThreads, 0, st>>>(d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                           d_ent[0]->as<uint64_t>(), d_ent[1]->as<uint64_t>(),
+                                                                           d_cm.as<uint8_t>(), Np, dsn, dtn, d_status, d_ticket, d_nleft,
+                                                                           c->p_segtab.as<kern::Seg>(), d_limits);
+        tm.kernel_launches += 1;
+      }
       CU(cudaEventRecord(p1, st));
       part_ev.emplace_back(p0, p1);
       CU(cudaGetLastError());

@@ -1872,6 +1872,121 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(const uint64
   }
 }
 
+// K4 in ONE pass over the entries (what a fit runs; the three kernels above remain the stage entry points' stable
+// partition).  A tile reads its 2048 entries and their bin bytes once, publishes its number of lefts, obtains the lefts
+// of the node's earlier tiles by decoupled look-back over the published counts, and scatters straight from
+// registers: lefts forward from the start of the node's segment in the other buffer, rights BACKWARD from its end.
+// The right child therefore holds its rows in reverse order; nothing downstream depends on the order of a
+// segment (histograms are sums, the next partition classifies entry by entry), and a segment stays monotone in the
+// row index, which is all the column gathers' locality needs.  The node's last tile writes the children's segments.
+// status[t]: flag << 62 | count, flag 1 = this tile's lefts, 2 = lefts of all the node's tiles up to and including t.
+__global__ void __launch_bounds__(kPartThreads) part_onepass_kernel(const uint64_t* ent0, const uint64_t* ent1,
+                                                                    uint64_t* out0, uint64_t* out1,
+                                                                    const uint8_t* __restrict__ bins_cm, int64_t Np,
+                                                                    const SplitNode* __restrict__ nodes,
+                                                                    const uint32_t* __restrict__ tile_node,
+                                                                    unsigned long long* status, uint32_t* ticket,
+                                                                    uint64_t* __restrict__ n_left, Seg* __restrict__ segtab,
+                                                                    const uint32_t* __restrict__ limits) {
+  __shared__ uint32_t sh_w[kPartThreads / 32];
+  __shared__ uint32_t sh_excl;
+  // a tile waits only for lower-numbered tiles of its node; CTAs are dispatched in blockIdx order (the assumption every
+  // decoupled look-back scan makes), so those are resident or finished (`ticket` is kept for a dynamic numbering)
+  (void)ticket;
+  const uint32_t tile = blockIdx.x;
+  if (tile >= limits[1]) return;   // grid provisioned from upper bounds (decide_scan_kernel wrote the real count)
+  const uint32_t g = tile_node[tile];
+  const SplitNode nd = load_split(nodes, g, segtab);
+  const uint32_t t_in = tile - nd.tile_begin;
+  const uint64_t tile_start = (uint64_t)t_in * kPartTile;
+  const uint64_t* ent = (nd.buf ? ent1 : ent0) + nd.seg_start + tile_start;
+  uint64_t* dst = (nd.buf ? out0 : out1) + nd.seg_start;  // other buffer, same segment
+  const uint32_t len = tile_start < nd.seg_len ? min((uint32_t)kPartTile, nd.seg_len - (uint32_t)tile_start) : 0u;
+  const uint8_t* col = bins_cm + (size_t)nd.feature * Np;
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  const uint32_t wbase = wv * (32 * kPartPerLane);
+  uint64_t e[kPartPerLane];
+#pragma unroll
+  for (int r = 0; r < kPartPerLane; r++) {
+    const uint32_t j = wbase + r * 32 + lane;
+    e[r] = j < len ? __ldcs(ent + j) : ~0ull;
+  }
+  uint32_t bal[kPartPerLane];
+  uint32_t wleft = 0;
+#pragma unroll
+  for (int r = 0; r < kPartPerLane; r++) {
+    const bool left = (e[r] != ~0ull) && ((int)col[(uint32_t)e[r]] <= nd.split_bin);
+    bal[r] = __ballot_sync(0xffffffffu, left);
+    wleft += __popc(bal[r]);
+  }
+  if (lane == 0) sh_w[wv] = wleft;
+  __syncthreads();
+  uint32_t lefts_before = 0, tile_lefts = 0;   // lefts in earlier warps of the tile; in the whole tile
+#pragma unroll
+  for (int i = 0; i < kPartThreads / 32; i++) {
+    const uint32_t v = sh_w[i];
+    if (i < wv) lefts_before += v;
+    tile_lefts += v;
+  }
+  if (wv == 0) {
+    constexpr unsigned long long kAgg = 1ull << 62, kIncl = 2ull << 62;
+    uint32_t excl = 0;
+    volatile unsigned long long* vs = status;
+    if (t_in == 0) {
+      if (lane == 0) vs[tile] = kIncl | tile_lefts;
+    } else {
+      if (lane == 0) vs[tile] = kAgg | tile_lefts;
+      int look = (int)tile - 1;                       // nearest predecessor first; stop at the node's first tile
+      while (true) {
+        const int idx = look - lane;
+        const bool in_node = idx >= (int)nd.tile_begin;
+        unsigned long long sv;
+        do {
+          sv = in_node ? vs[idx] : kIncl;            // before the node's first tile: an inclusive count of 0
+        } while (__any_sync(0xffffffffu, (sv >> 62) == 0));
+        const uint32_t incl_mask = __ballot_sync(0xffffffffu, (sv >> 62) == 2);
+        const int first_incl = incl_mask ? __ffs(incl_mask) - 1 : 32;
+        uint32_t v = lane <= first_incl ? (uint32_t)sv : 0u;   // aggregates up to (and including) the first inclusive count
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        excl += v;
+        if (incl_mask) break;
+        look -= 32;
+      }
+      if (lane == 0) vs[tile] = kIncl | (unsigned long long)(excl + tile_lefts);
+    }
+    if (lane == 0) sh_excl = excl;
+  }
+  __syncthreads();
+  const uint32_t excl = sh_excl;
+  if (len) {
+    const uint64_t left_base = excl;                                   // lefts of earlier tiles
+    const uint64_t right_last = (uint64_t)nd.seg_len - 1 - (tile_start - excl);   // position of this tile's first right
+    uint32_t lrank = lefts_before;
+#pragma unroll
+    for (int r = 0; r < kPartPerLane; r++) {
+      const uint32_t j = wbase + r * 32 + lane;
+      const uint32_t before = __popc(bal[r] & ((1u << lane) - 1));
+      if (j < len) {
+        const uint32_t my_l = lrank + before;           // lefts before j in the tile
+        if ((bal[r] >> lane) & 1u) dst[left_base + my_l] = e[r];
+        else dst[right_last - (j - my_l)] = e[r];
+      }
+      lrank += __popc(bal[r]);
+    }
+  }
+  if (t_in == nd.n_tiles - 1 && threadIdx.x == 0) {
+    const uint32_t total = excl + tile_lefts;
+    n_left[g] = total;
+    if (segtab) {   // children: [left ... | ... right] in the other buffer, same place
+      Seg l, r;
+      l.start = nd.seg_start; l.len = total; l.buf = nd.buf ^ 1u;
+      r.start = nd.seg_start + total; r.len = nd.seg_len - total; r.buf = nd.buf ^ 1u;
+      segtab[nd.left_slot] = l;
+      segtab[nd.right_slot] = r;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Driver side of findBestSplits, on the device: turns a group's split records into (a) one decision word per
 // node — the winning feature chunk and Spark's leaf rules (RandomForest.findBestSplits: isLeaf = gain <= 0 ||

@@ -19,15 +19,8 @@ P = int(sys.argv[5]) if len(sys.argv) > 5 else 8192
 ctx = Context(0)
 L = _lib.lib()
 t0 = time.time()
-dX, dy = C.c_void_p(), C.c_void_p()
-_lib.check(L.emrf_dev_alloc(ctx.h, N * F * 8, C.byref(dX)))
-_lib.check(L.emrf_dev_alloc(ctx.h, N * 8, C.byref(dy)))
-chunk = 500_000
-for a in range(0, N, chunk):          # generate and upload in chunks (host RAM stays small)
-    b = min(N, a + chunk)
-    X, y = synth.flat(b - a, F, 50, row_start=a)
-    _lib.check(L.emrf_memcpy_h2d(ctx.h, C.c_void_p(dX.value + a * F * 8), X.ctypes.data, X.nbytes))
-    _lib.check(L.emrf_memcpy_h2d(ctx.h, C.c_void_p(dy.value + a * 8), y.ctypes.data, y.nbytes))
+g = synth.DeviceFlat(ctx, N, F, 50)        # generated in HBM by the engine (emrf_synth_flat)
+dX, dy = g.X, g.y
 print(f"data ready in {time.time() - t0:.1f} s", flush=True)
 rf = RandomForestClassifier(ctx).setNumTrees(T).setMaxDepth(D).setNumClasses(50)
 for rep in range(2):

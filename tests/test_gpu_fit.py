@@ -131,9 +131,11 @@ def test_kernel_variants_match_oracle(oracle):
             "print('VARIANT_OK')\n") % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     # {}: TMA-gathered row staging (the default); EMRF_NO_TMA=1: the LDG/STS staging it replaced, alone and with the
     # other variants off; EMRF_CM_DIV=0 with TMA: every node, dense roots included, goes through the gathers;
-    # EMRF_NO_U16_MIXED=1: multi-tile nodes keep 32-bit launches (default: 16-bit tiles + piecewise scan of the sums)
+    # EMRF_NO_U16_MIXED=1: multi-tile nodes keep 32-bit launches (default: 16-bit tiles + piecewise scan of the sums);
+    # EMRF_PART_3PASS=1: count / scan / scatter partition (default: one pass with look-back, right children reversed)
     for env in ({}, {"EMRF_NO_TMA": "1"}, {"EMRF_NO_TMA": "1", "EMRF_HIST_U32": "1", "EMRF_CM_DIV": "0", "EMRF_LIST_SIMPLE": "1"},
-                {"EMRF_CM_DIV": "0"}, {"EMRF_CM_DIV": "64"}, {"EMRF_NO_U16_MIXED": "1"}, {"EMRF_NO_U16_MIXED": "1", "EMRF_CM_DIV": "0"}):
+                {"EMRF_CM_DIV": "0"}, {"EMRF_CM_DIV": "64"}, {"EMRF_NO_U16_MIXED": "1"}, {"EMRF_NO_U16_MIXED": "1", "EMRF_CM_DIV": "0"},
+                {"EMRF_PART_3PASS": "1"}):
         r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "VARIANT_OK" in r.stdout, str(env) + r.stdout[-1500:] + r.stderr[-1500:]
 

@@ -941,6 +941,9 @@ struct emrf_forest {
   bool walk_ok = false;
   int walk_ts = 0;            // threshold table stride
   DevBuf d_wnodes, d_wroots, d_pthr, d_pns;
+  DevBuf d_wblocks, d_broots; // 32-byte two-level tree blocks of the compact walk and each tree's root block
+  DevBuf d_leaf_rec;          // compact leaf records (counts + total + 1/total), see predict_walk_compact_kernel
+  int leaf_count_bytes = 0;   // 0: not available (non-integral or huge class counts), 2 or 4
 };
 
 static inline void node_counts(const HNode& n, int C, uint32_t* out) {
@@ -2387,12 +2390,130 @@ static int forest_to_device(emrf_ctx* c, emrf_forest* f) {
       CU(cudaMemcpy(f->d_wroots.p, wroots.data(), (size_t)f->num_trees * 4, cudaMemcpyHostToDevice));
       CU(cudaMemcpy(f->d_pthr.p, pthr.data(), pthr.size() * 8, cudaMemcpyHostToDevice));
       CU(cudaMemcpy(f->d_pns.p, pns.data(), (size_t)F * 4, cudaMemcpyHostToDevice));
+      // compact leaf records: integer class counts (true of every forest trained here or by Spark) instead of the
+      // per-class probabilities; the walk recomputes count / total exactly
+      bool integral = C <= 256;
+      double max_count = 0.0;
+      for (int64_t i = 0; i < n && integral; i++) {
+        if (f->nodes[i].left >= 0) continue;
+        double total = 0.0;
+        for (int cc = 0; cc < C; cc++) {
+          const double v = f->stats[i * C + cc];
+          if (!(v >= 0.0) || v != std::floor(v) || v >= 4294967296.0) { integral = false; break; }
+          total += v;
+          max_count = std::max(max_count, v);
+        }
+        if (total >= 4294967296.0) integral = false;
+      }
+      f->leaf_count_bytes = 0;
+      if (integral) {
+        const int cb = max_count <= 65535.0 ? 2 : 4;
+        const size_t rb = kern::leaf_rec_bytes(C, cb);
+        std::vector<uint8_t> recs((size_t)std::max<int64_t>(n_leaves, 1) * rb, 0);
+        for (int64_t i = 0; i < n; i++) {
+          if (f->nodes[i].left >= 0 || !dn[i].right) continue;     // internal node, or an empty leaf (never read)
+          uint8_t* r = recs.data() + (size_t)dn[i].left * rb;
+          double total = 0.0;
+          for (int cc = 0; cc < C; cc++) total += f->stats[i * C + cc];
+          const double ty[2] = {total, 1.0 / total};
+          memcpy(r, ty, 16);
+          for (int cc = 0; cc < C; cc++) {
+            const size_t slot = (size_t)(cc >> 6) * 64 + (size_t)(cc & 31) * 2 + ((cc >> 5) & 1);   // lane's pair: (c, c + 32)
+            const uint32_t v = (uint32_t)f->stats[i * C + cc];
+            if (cb == 2) reinterpret_cast<uint16_t*>(r + 16)[slot] = (uint16_t)v;
+            else reinterpret_cast<uint32_t*>(r + 16)[slot] = v;
+          }
+        }
+        CU(f->d_leaf_rec.alloc(recs.size()));
+        CU(cudaMemcpy(f->d_leaf_rec.p, recs.data(), recs.size(), cudaMemcpyHostToDevice));
+        // two-level blocks (kern::WalkBlock): breadth-first over block roots, a split node's grandchildren blocks allocated
+        // as they are met; a leaf's record index (-1: empty leaf) sits where the pointer to it would be
+        std::vector<kern::WalkBlock> blocks;
+        std::vector<int32_t> broots(f->num_trees);
+        blocks.reserve((size_t)n / 2 + f->num_trees);
+        std::vector<std::pair<int64_t, int32_t>> todo;     // (flat node index of a block's root, block index)
+        auto leaf_idx = [&](int64_t i) -> int32_t { return dn[i].right ? dn[i].left : -1; };
+        auto split_bin_of = [&](const FlatNode& nd) -> uint8_t {
+          const auto& tb = tab[nd.feature];
+          return (uint8_t)(std::lower_bound(tb.begin(), tb.end(), nd.threshold) - tb.begin());
+        };
+        for (int t = 0; t < f->num_trees; t++) {
+          const int64_t base = f->tree_off[t];
+          broots[t] = (int32_t)blocks.size();
+          blocks.emplace_back();
+          todo.clear();
+          todo.emplace_back(base, broots[t]);
+          for (size_t q = 0; q < todo.size(); q++) {
+            const int64_t i = todo[q].first;
+            const int32_t bi = todo[q].second;
+            kern::WalkBlock b;
+            memset(&b, 0, sizeof(b));
+            const FlatNode& nd = f->nodes[i];
+            if (nd.left < 0) { b.fl0 = 1; b.leaf0 = leaf_idx(i); blocks[bi] = b; continue; }
+            b.f0 = (uint16_t)nd.feature; b.sb0 = split_bin_of(nd);
+            for (int side = 0; side < 2; side++) {
+              const int64_t ci = base + (side ? nd.right : nd.left);
+              const FlatNode& ch = f->nodes[ci];
+              uint8_t fl = 0;
+              int32_t pl = 0, pr = 0;
+              uint16_t cf = 0;
+              uint8_t csb = 0;
+              if (ch.left < 0) { fl = 1; pl = leaf_idx(ci); }
+              else {
+                cf = (uint16_t)ch.feature; csb = split_bin_of(ch);
+                const int64_t gl = base + ch.left, gr = base + ch.right;
+                if (f->nodes[gl].left < 0) { fl |= 2; pl = leaf_idx(gl); }
+                else { pl = (int32_t)blocks.size(); blocks.emplace_back(); todo.emplace_back(gl, pl); }
+                if (f->nodes[gr].left < 0) { fl |= 4; pr = leaf_idx(gr); }
+                else { pr = (int32_t)blocks.size(); blocks.emplace_back(); todo.emplace_back(gr, pr); }
+              }
+              if (side == 0) { b.f1 = cf; b.sb1 = csb; b.fl1 = fl; b.p1l = pl; b.p1r = pr; }
+              else { b.f2 = cf; b.sb2 = csb; b.fl2 = fl; b.p2l = pl; b.p2r = pr; }
+            }
+            blocks[bi] = b;
+          }
+        }
+        CU(f->d_wblocks.alloc(blocks.size() * sizeof(kern::WalkBlock)));
+        CU(f->d_broots.alloc((size_t)f->num_trees * 4));
+        CU(cudaMemcpy(f->d_wblocks.p, blocks.data(), blocks.size() * sizeof(kern::WalkBlock), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(f->d_broots.p, broots.data(), (size_t)f->num_trees * 4, cudaMemcpyHostToDevice));
+        f->leaf_count_bytes = cb;
+      }
     }
   }
   f->dev_device = c->device;
   return EMRF_OK;
 }
 
+template <class CT, int CB>
+static cudaError_t walk_compact_t(const emrf_forest* f, const uint8_t* bins, int Fp, int64_t n, int C, double* raw, double* prob,
+                                  double* pred, const double* thr, cudaStream_t st) {
+  const size_t smem = (size_t)kern::kWalk2Warps * 32 * Fp;
+  if (smem > 48 * 1024) {
+    const cudaError_t e = cudaFuncSetAttribute(kern::predict_walk_compact_kernel<CT, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  const unsigned grid = (unsigned)((n + kern::kWalk2Warps * 32 - 1) / (kern::kWalk2Warps * 32));
+  kern::predict_walk_compact_kernel<CT, CB><<<grid, kern::kWalk2Warps * 32, smem, st>>>(
+      bins, Fp, n, f->d_wblocks.as<kern::WalkBlock>(), f->d_broots.as<int32_t>(), f->num_trees, f->d_leaf_rec.as<uint8_t>(), C, raw, prob,
+      pred, thr);
+  return cudaGetLastError();
+}
+static int launch_walk_compact(const emrf_forest* f, const uint8_t* bins, int Fp, int64_t n, int C, double* raw, double* prob, double* pred,
+                               const double* thr, cudaStream_t st) {
+  const int cb = (C + 63) / 64;
+  const bool u16 = f->leaf_count_bytes == 2;
+  cudaError_t e;
+#define EMRF_WALK_CASE(CB_)                                                                     \
+  e = u16 ? walk_compact_t<uint16_t, CB_>(f, bins, Fp, n, C, raw, prob, pred, thr, st)        \
+          : walk_compact_t<uint32_t, CB_>(f, bins, Fp, n, C, raw, prob, pred, thr, st)
+  if (cb <= 1) { EMRF_WALK_CASE(1); }
+  else if (cb == 2) { EMRF_WALK_CASE(2); }
+  else { EMRF_WALK_CASE(4); }
+  CU(e);
+#undef EMRF_WALK_CASE
+  return EMRF_OK;
+}
 static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* features_hd, int64_t N, double* raw_hd,
                         double* prob_hd, double* pred_hd, const double* thresholds_h) {
   if (!c || !f_in || !features_hd) return fail(EMRF_ERR_ARG, "NULL argument");
@@ -2410,9 +2531,13 @@ static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* 
   if (N == 0) return EMRF_OK;
   CU(cudaSetDevice(c->device));
   TRY(forest_to_device(c, f));
-  cudaStream_t st;
-  CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-  struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamDestroy(s); } } sg{st};
+  // two streams and two sets of staging buffers: chunk i+1's host->device copy and binning run under chunk i's walk and
+  // its device->host copies (a stream reuses its own buffer set in stream order, so no host wait inside the loop)
+  cudaStream_t sts[2] = {nullptr, nullptr};
+  struct StreamGuard { cudaStream_t* s; ~StreamGuard() { for (int i = 0; i < 2; i++) if (s[i]) cudaStreamDestroy(s[i]); } } sg{sts};
+  CU(cudaStreamCreateWithFlags(&sts[0], cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&sts[1], cudaStreamNonBlocking));
+  cudaStream_t st = sts[0];
   DevBuf dThr;
   const double* d_thresholds = nullptr;
   if (thresholds_h) {
@@ -2424,14 +2549,22 @@ static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* 
   const bool raw_dev = raw_hd && is_device_ptr(raw_hd), prob_dev = prob_hd && is_device_ptr(prob_hd),
              pred_dev = pred_hd && is_device_ptr(pred_hd);
   // chunk so that staging buffers stay modest
-  const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(N, (int64_t)(512ll << 20) / ((int64_t)F * 8)));
-  DevBuf dX, dRaw, dProb, dPred, dBins;
-  CU(dBins.alloc((size_t)align_up((size_t)chunk, 128) * align_up(F, 16)));
-  if (!x_dev) CU(dX.alloc((size_t)chunk * F * 8));
-  if (raw_hd && !raw_dev) CU(dRaw.alloc((size_t)chunk * C * 8));
-  if (prob_hd && !prob_dev) CU(dProb.alloc((size_t)chunk * C * 8));
-  if (pred_hd && !pred_dev) CU(dPred.alloc((size_t)chunk * 8));
-  for (int64_t r0 = 0; r0 < N; r0 += chunk) {
+  const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(N, (int64_t)(256ll << 20) / ((int64_t)F * 8)));
+  const int n_sets = N > chunk ? 2 : 1;
+  DevBuf dXs[2], dRaws[2], dProbs[2], dPreds[2], dBinss[2];
+  for (int i = 0; i < n_sets; i++) {
+    CU(dBinss[i].alloc((size_t)align_up((size_t)chunk, 128) * align_up(F, 16)));
+    if (!x_dev) CU(dXs[i].alloc((size_t)chunk * F * 8));
+    if (raw_hd && !raw_dev) CU(dRaws[i].alloc((size_t)chunk * C * 8));
+    if (prob_hd && !prob_dev) CU(dProbs[i].alloc((size_t)chunk * C * 8));
+    if (pred_hd && !pred_dev) CU(dPreds[i].alloc((size_t)chunk * 8));
+  }
+  if (d_thresholds) CU(cudaStreamSynchronize(sts[0]));   // the thresholds were copied on stream 0; stream 1 reads them too
+  int64_t chunk_idx = 0;
+  for (int64_t r0 = 0; r0 < N; r0 += chunk, chunk_idx++) {
+    const int set = (int)(chunk_idx & 1) % n_sets;
+    st = sts[set];
+    DevBuf &dX = dXs[set], &dRaw = dRaws[set], &dProb = dProbs[set], &dPred = dPreds[set], &dBins = dBinss[set];
     const int64_t n = std::min(chunk, N - r0);
     const double* x = features_hd + r0 * F;
     if (!x_dev) {
@@ -2459,11 +2592,16 @@ static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* 
         kern::bin_kernel<false, true><<<bgrid, 256, tile_bytes, st>>>(x, n, F, Fp, 0, f->d_pthr.as<double>(), f->d_pns.as<int>(),
                                                                       f->walk_ts, dBins.as<uint8_t>(), nullptr);
       }
-      if (walk_smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::predict_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)walk_smem));
-      const unsigned wgrid = (unsigned)((n + kern::kPredWarps * 32 - 1) / (kern::kPredWarps * 32));
-      kern::predict_walk_kernel<<<wgrid, kern::kPredWarps * 32, walk_smem, st>>>(
-          dBins.as<uint8_t>(), Fp, n, f->d_wnodes.as<kern::WalkNode>(), f->d_wroots.as<int32_t>(), f->num_trees,
-          f->d_leaf_prob.as<double>(), C, raw, prob, pred, d_thresholds);
+      static const bool dense_leaves = env_flag("EMRF_PREDICT_DENSE_LEAVES");   // the f64 probability records (A/B runs, parity test)
+      if (f->leaf_count_bytes && !dense_leaves) {
+        TRY(launch_walk_compact(f, dBins.as<uint8_t>(), Fp, n, C, raw, prob, pred, d_thresholds, st));
+      } else {
+        if (walk_smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::predict_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)walk_smem));
+        const unsigned wgrid = (unsigned)((n + kern::kPredWarps * 32 - 1) / (kern::kPredWarps * 32));
+        kern::predict_walk_kernel<<<wgrid, kern::kPredWarps * 32, walk_smem, st>>>(
+            dBins.as<uint8_t>(), Fp, n, f->d_wnodes.as<kern::WalkNode>(), f->d_wroots.as<int32_t>(), f->num_trees,
+            f->d_leaf_prob.as<double>(), C, raw, prob, pred, d_thresholds);
+      }
     } else {
       const int64_t threads = n * 32;
       kern::predict_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(x, n, F, f->d_nodes.as<kern::DevNode>(),
@@ -2474,8 +2612,9 @@ static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* 
     if (raw_hd && !raw_dev) CU(cudaMemcpyAsync(raw_hd + r0 * C, raw, (size_t)n * C * 8, cudaMemcpyDeviceToHost, st));
     if (prob_hd && !prob_dev) CU(cudaMemcpyAsync(prob_hd + r0 * C, prob, (size_t)n * C * 8, cudaMemcpyDeviceToHost, st));
     if (pred_hd && !pred_dev) CU(cudaMemcpyAsync(pred_hd + r0, pred, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
   }
+  CU(cudaStreamSynchronize(sts[0]));
+  CU(cudaStreamSynchronize(sts[1]));
   return EMRF_OK;
 }
 extern "C" int emrf_predict(emrf_ctx_t* c, const emrf_forest_t* f, const double* features_hd, int64_t N, double* raw_hd,

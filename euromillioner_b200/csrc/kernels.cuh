@@ -2471,6 +2471,187 @@ __global__ void __launch_bounds__(kPredWarps * 32) predict_walk_kernel(const uin
   }
 }
 
+// K5, compact form (what emrf_predict runs when every leaf's class counts are integers below 2^32, as they are in any
+// forest this engine or Spark's RandomForestClassifier trains).  A leaf record holds the COUNTS, not the
+// probabilities: [double total][double RN(1/total)][for every block of 64 classes: lane l's pair (class 64b+l,
+// class 64b+l+32)] with 16- or 32-bit counts — 144 B instead of 400 B for 50 classes, and the record traffic is what
+// bounds this kernel.  probability(c) = count(c) / total is recomputed with div_by (correctly rounded for such integers:
+// the same double predictRaw's `/` gives), so raw votes, probabilities and labels stay bit-identical.
+// One warp per 32 rows, ONE ROW AT A TIME: lanes walk 32 different trees for the row (lane = tree: 32 pointer chases
+// in flight), then the warp adds the 32 leaves in tree order with lane = class — the row's votes never leave
+// registers, no vote array in shared memory, so the occupancy is bounded by registers only.
+// Tree layout of the compact walk: 32-byte blocks (one L2 sector) holding a node and its two children, so that a lane
+// descends TWO levels per dependent load.  p?l / p?r: where the child's own left / right child lives — a block index, or
+// (flag bits 1 / 2) a leaf record index; a child that is itself a leaf (flag bit 0) keeps its record index in p?l.
+struct __align__(32) WalkBlock {
+  uint16_t f0; uint8_t sb0, fl0; int32_t leaf0;                      // the block's root (fl0 & 1: leaf, record leaf0)
+  uint16_t f1; uint8_t sb1, fl1; uint16_t f2; uint8_t sb2, fl2;     // its left and right child
+  int32_t p1l, p1r, p2l, p2r;
+};
+static_assert(sizeof(WalkBlock) == 32, "one sector per block");
+template <class CT> struct LeafPair;
+template <> struct LeafPair<uint16_t> { using type = uint32_t; __device__ static void split(uint32_t v, uint32_t& a, uint32_t& b) { a = v & 0xffffu; b = v >> 16; } };
+template <> struct LeafPair<uint32_t> { using type = uint2; __device__ static void split(uint2 v, uint32_t& a, uint32_t& b) { a = v.x; b = v.y; } };
+__host__ __device__ inline size_t leaf_rec_bytes(int C, int count_bytes) { return 16 + (size_t)((C + 63) / 64) * 32 * 2 * count_bytes; }
+constexpr int kWalk2Warps = 8;
+template <class CT, int CB>
+__global__ void __launch_bounds__(kWalk2Warps * 32, CB == 1 ? 4 : 1) predict_walk_compact_kernel(const uint8_t* __restrict__ bins_rm, int Fp, int64_t n_rows,
+                                                                               const WalkBlock* __restrict__ blocks,
+                                                                               const int32_t* __restrict__ tree_root, int T,
+                                                                               const uint8_t* __restrict__ leaf_rec, int C,
+                                                                               double* __restrict__ raw, double* __restrict__ prob,
+                                                                               double* __restrict__ pred,
+                                                                               const double* __restrict__ thresholds) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  using Pair = typename LeafPair<CT>::type;
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  uint8_t* rows = smem_raw + (size_t)wv * 32 * Fp;              // this warp's 32 binned rows
+  const int64_t r0 = ((int64_t)blockIdx.x * kWalk2Warps + wv) * 32;
+  if (r0 >= n_rows) return;
+  const int n_here = (int)min((int64_t)32, n_rows - r0);
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(bins_rm + (size_t)r0 * Fp);
+    uint4* dst = reinterpret_cast<uint4*>(rows);
+    for (int i = lane; i < n_here * (Fp >> 4); i += 32) dst[i] = src[i];
+  }
+  __syncwarp();
+  const size_t rec_bytes = leaf_rec_bytes(C, (int)sizeof(CT));
+  constexpr int TB = 8;      // leaf records in flight per lane while a row's votes are accumulated
+  constexpr int RJ = 2;      // rows walked together: two independent pointer chases per lane
+  for (int j0 = 0; j0 < n_here; j0 += RJ) {
+    const uint8_t* my[RJ];
+    double a0[RJ][CB], a1[RJ][CB];
+#pragma unroll
+    for (int r = 0; r < RJ; r++) {
+      my[r] = rows + (size_t)min(j0 + r, n_here - 1) * Fp;
+#pragma unroll
+      for (int b = 0; b < CB; b++) { a0[r][b] = 0.0; a1[r][b] = 0.0; }
+    }
+    for (int t0 = 0; t0 < T; t0 += 32) {
+      // lane = tree: walk tree t0 + lane for rows j0 .. j0 + RJ - 1
+      int li[RJ];
+#pragma unroll
+      for (int r = 0; r < RJ; r++) li[r] = -1;
+      if (t0 + lane < T) {
+        int blk[RJ];
+        bool any = true;
+#pragma unroll
+        for (int r = 0; r < RJ; r++) blk[r] = tree_root[t0 + lane];
+        while (any) {
+          any = false;
+#pragma unroll
+          for (int r = 0; r < RJ; r++) {
+            if (blk[r] < 0) continue;
+            const uint4 lo = __ldg(reinterpret_cast<const uint4*>(blocks + blk[r]));
+            const uint4 hi = __ldg(reinterpret_cast<const uint4*>(blocks + blk[r]) + 1);
+            // lo.x = f0 | sb0 << 16 | fl0 << 24, lo.y = leaf0, lo.z / lo.w = the children's headers; hi = p1l p1r p2l p2r
+            if ((lo.x >> 24) & 1u) { li[r] = (int)lo.y; blk[r] = -1; continue; }
+            const bool go = my[r][lo.x & 0xffffu] > ((lo.x >> 16) & 0xffu);
+            const uint32_t hd = go ? lo.w : lo.z;
+            const int pl = (int)(go ? hi.z : hi.x), pr = (int)(go ? hi.w : hi.y);
+            const uint32_t fl = hd >> 24;
+            if (fl & 1u) { li[r] = pl; blk[r] = -1; continue; }
+            const bool go2 = my[r][hd & 0xffffu] > ((hd >> 16) & 0xffu);
+            const int p = go2 ? pr : pl;
+            if (fl & (go2 ? 4u : 2u)) { li[r] = p; blk[r] = -1; continue; }
+            blk[r] = p;
+            any = true;
+          }
+        }
+      }
+      const int nt = min(32, T - t0);
+      // lane = class: votes(c) += count(c) / total, trees in order, TB records in flight
+#pragma unroll
+      for (int r = 0; r < RJ; r++) {
+        if (j0 + r >= n_here) break;
+        for (int u0 = 0; u0 < nt; u0 += TB) {
+          Pair cw[TB][CB];
+          double tt[TB], yy[TB];
+#pragma unroll
+          for (int u = 0; u < TB; u++) {
+            const int l = __shfl_sync(0xffffffffu, li[r], (u0 + u) & 31);
+            const bool ok = (u0 + u < nt) && (l >= 0);
+            const uint8_t* rec = leaf_rec + (size_t)max(l, 0) * rec_bytes;
+            const double2 ty = ok ? *reinterpret_cast<const double2*>(rec) : make_double2(1.0, 1.0);
+            tt[u] = ty.x; yy[u] = ty.y;
+#pragma unroll
+            for (int b = 0; b < CB; b++) {
+              if (ok) cw[u][b] = reinterpret_cast<const Pair*>(rec + 16)[b * 32 + lane];
+              else cw[u][b] = Pair();
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < TB; u++) {
+#pragma unroll
+            for (int b = 0; b < CB; b++) {
+              uint32_t c0, c1;
+              LeafPair<CT>::split(cw[u][b], c0, c1);
+              // (double)count without the conversion unit: 2^52 + n is exact in a double whose low word is n
+              const double d0 = __dsub_rn(__hiloint2double(0x43300000, (int)c0), 4503599627370496.0);
+              const double d1 = __dsub_rn(__hiloint2double(0x43300000, (int)c1), 4503599627370496.0);
+              a0[r][b] = __dadd_rn(a0[r][b], div_by(d0, tt[u], yy[u]));   // an empty or absent leaf adds +0.0: exact
+              a1[r][b] = __dadd_rn(a1[r][b], div_by(d1, tt[u], yy[u]));
+            }
+          }
+        }
+      }
+    }
+    // ---- finalise the rows: index-order sum, first-max argmax (or probability / threshold), outputs
+#pragma unroll
+    for (int r = 0; r < RJ; r++) {
+      const int j = j0 + r;
+      if (j >= n_here) break;
+      double ssum = 0.0;
+      for (int c = 0; c < C; c++) {
+        const int b = c >> 6, h = (c >> 5) & 1;
+        double v = 0.0;
+#pragma unroll
+        for (int bb = 0; bb < CB; bb++) if (bb == b) v = h ? a1[r][bb] : a0[r][bb];
+        ssum = __dadd_rn(ssum, __shfl_sync(0xffffffffu, v, c & 31));
+      }
+      // candidates of this lane: classes 64b + lane and 64b + lane + 32
+      double best = -INFINITY;
+      int best_c = 0x7fffffff;
+#pragma unroll
+      for (int b = 0; b < CB; b++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int c = 64 * b + 32 * h + lane;
+          if (c < C) {
+            double v = h ? a1[r][b] : a0[r][b];
+            if (thresholds) {      // probability2prediction: first maximum of probability(c) / thresholds(c), NaN never wins
+              const double pr = (ssum != 0.0) ? __ddiv_rn(v, ssum) : v;
+              v = __ddiv_rn(pr, thresholds[c]);
+            }
+            if (v > best) { best = v; best_c = c; }          // c ascends within a lane: first maximum kept
+          }
+        }
+      }
+      for (int o = 16; o; o >>= 1) {
+        const double b2 = __shfl_xor_sync(0xffffffffu, best, o);
+        const int c2 = __shfl_xor_sync(0xffffffffu, best_c, o);
+        if (c2 != 0x7fffffff && (best_c == 0x7fffffff || b2 > best || (b2 == best && c2 < best_c))) { best = b2; best_c = c2; }
+      }
+      if (best_c == 0x7fffffff) best_c = 0;     // every candidate was NaN or -inf: Spark's loop keeps class 0
+      if (pred && lane == 0) pred[r0 + j] = (double)best_c;
+      if (raw || prob) {
+#pragma unroll
+        for (int b = 0; b < CB; b++) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            const int c = 64 * b + 32 * h + lane;
+            if (c < C) {
+              const double v = h ? a1[r][b] : a0[r][b];
+              if (raw) raw[(r0 + j) * C + c] = v;
+              if (prob) prob[(r0 + j) * C + c] = (ssum != 0.0) ? __ddiv_rn(v, ssum) : v;
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Draw-history feature builder (the step before the path; reference analogue: the row -> features
 // loop of Main.java:86-102, here with the lag window north_star describes).  draws[Dn][7] holds the

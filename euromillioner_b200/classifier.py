@@ -23,6 +23,63 @@ def _ptr(a):
     return None if a is None else C.c_void_p(a.ctypes.data)
 
 
+def java_double_to_string(x):
+    """java.lang.Double.toString: what Scala string interpolation prints for a Double (`Predict: 12.0`, `<= 24.5`,
+    `1.0E-5`, `1.0E7`).  Digits are the shortest that round-trip (Python's repr); Java switches to computerised scientific
+    notation outside [1e-3, 1e7) and always shows at least one fractional digit.  (JDKs before 19 print a few doubles
+    with one digit more than the shortest, JDK-4511638; none of the values a forest over integer-valued features
+    holds — midpoints x.5 and class indices — is among them.)"""
+    x = float(x)
+    if x != x:
+        return "NaN"
+    if x in (float("inf"), float("-inf")):
+        return "Infinity" if x > 0 else "-Infinity"
+    if x == 0.0:
+        return "-0.0" if str(x).startswith("-") else "0.0"
+    sign = "-" if x < 0 else ""
+    mant, _, exp = repr(abs(x)).partition("e")
+    ip, _, fp = mant.partition(".")
+    digits = (ip + fp).lstrip("0")
+    # value = 0.DIGITS * 10^point
+    point = len(ip) + (int(exp) if exp else 0)
+    if ip.strip("0") == "":                                  # 0.000123 style mantissa
+        lead = len(fp) - len(fp.lstrip("0"))
+        point = -lead + (int(exp) if exp else 0)
+    digits = digits.rstrip("0") or "0"
+    if 1e-3 <= abs(x) < 1e7:
+        if point <= 0:
+            return sign + "0." + "0" * (-point) + digits
+        if len(digits) <= point:
+            return sign + digits + "0" * (point - len(digits)) + ".0"
+        return sign + digits[:point] + "." + digits[point:]
+    return sign + digits[0] + "." + (digits[1:] or "0") + "E" + str(point - 1)
+
+
+def debug_string(e, num_trees, uid):
+    """TreeEnsembleModel.toDebugString of Spark 2.4 for a flat export `e` (see emrf_forest_export): the header is
+    RandomForestClassificationModel.toString, every tree is `  Tree i (weight w):` followed by
+    Node.subtreeToString(indentFactor = 4): `If (feature f <= t)` / left subtree / `Else (feature f > t)` / right
+    subtree, one more space per level, leaves `Predict: p`."""
+    out = [f"RandomForestClassificationModel (uid={uid}) with {num_trees} trees\n"]
+    for t in range(num_trees):
+        out.append(f"  Tree {t} (weight 1.0):\n")
+        base = int(e["tree_off"][t])
+        stack = [(0, 4, None)]            # (node, indent, pending "Else" line to print first)
+        while stack:
+            i, ind, pre = stack.pop()
+            if pre is not None:
+                out.append(pre)
+            pad = " " * ind
+            if e["left"][base + i] < 0:
+                out.append(f"{pad}Predict: {java_double_to_string(e['prediction'][base + i])}\n")
+                continue
+            f, thr = int(e["feature"][base + i]), java_double_to_string(e["threshold"][base + i])
+            out.append(f"{pad}If (feature {f} <= {thr})\n")
+            stack.append((int(e["right"][base + i]), ind + 1, f"{pad}Else (feature {f} > {thr})\n"))
+            stack.append((int(e["left"][base + i]), ind + 1, None))
+    return "".join(out)
+
+
 class Context:
     """Owns one GPU (device, stream, scratch) — emrf_ctx_t."""
 
@@ -280,6 +337,7 @@ class RandomForestClassificationModel:
         self.treeWeights = [1.0] * self.numTrees
         self._export = None
         self._thresholds = None
+        self.uid = "rfc_" + "%012x" % (abs(hash((self.numTrees, self.totalNumNodes, id(self)))) & 0xffffffffffff)   # Identifiable.randomUID("rfc")
 
     def setThresholds(self, v):
         """ProbabilisticClassificationModel.setThresholds (validated like the estimator's)."""
@@ -392,27 +450,17 @@ class RandomForestClassificationModel:
         check(_lib.lib().emrf_forest_feature_importances(self._h, _ptr(out)))
         return out
 
+    def toString(self):
+        """RandomForestClassificationModel.toString (Spark 2.4: the uid is part of it)."""
+        return f"RandomForestClassificationModel (uid={self.uid}) with {self.numTrees} trees"
+
+    __str__ = toString
+
     @property
     def toDebugString(self):
-        """Spark's text form: `If (feature 3 <= 24.5)` / `Else (feature 3 > 24.5)` / `Predict: 12.0`."""
-        e = self.export()
-        lines = [f"RandomForestClassificationModel with {self.numTrees} trees"]
-
-        def walk(base, i, depth):
-            pad = " " * (depth + 4)  # Node.subtreeToString(indentFactor = 4 + depth)
-            if e["left"][base + i] < 0:
-                lines.append(f"{pad}Predict: {float(e['prediction'][base + i])!r}")
-                return
-            f, thr = int(e["feature"][base + i]), float(e["threshold"][base + i])
-            lines.append(f"{pad}If (feature {f} <= {thr!r})")
-            walk(base, e["left"][base + i], depth + 1)
-            lines.append(f"{pad}Else (feature {f} > {thr!r})")
-            walk(base, e["right"][base + i], depth + 1)
-
-        for t in range(self.numTrees):
-            lines.append(f"  Tree {t} (weight 1.0):")
-            walk(int(e["tree_off"][t]), 0, 0)
-        return "\n".join(lines) + "\n"
+        """Spark 2.4's text form, byte for byte (given the same uid): diffing it against a real Spark run of
+        tools/SparkGolden.java is the way to pin parity."""
+        return debug_string(self.export(), self.numTrees, self.uid)
 
     # ---- Spark ML persistence (SURVEY.md §8 f4) --------------------------------------------------------
     def save(self, path, uid="rfc_b200", params=None):

@@ -20,3 +20,29 @@ out = {"tree_off": [int(v) for v in e["tree_off"]], "group_sizes": [int(v) for v
 with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "cfg1_forest.json"), "w") as f:
     json.dump(out, f)
 print("wrote cfg1_forest.json", out["tree_off"][-1], "nodes")
+
+
+# ---- toDebugString of the first three trees, rendered here straight from the oracle's export with its own small
+# recursive printer (NOT the product's renderer): Spark 2.4's Node.subtreeToString / TreeEnsembleModel.toDebugString
+def jstr(v):
+    v = float(v)
+    assert (1e-3 <= abs(v) < 1e7 or v == 0.0) and v == v   # every number of this forest prints in plain decimal notation
+    r = repr(v)
+    return r if "." in r else r + ".0"
+
+
+def subtree(base, i, indent):
+    pad = " " * indent
+    if e["left"][base + i] < 0:
+        return f"{pad}Predict: {jstr(e['prediction'][base + i])}\n"
+    f, t = int(e["feature"][base + i]), jstr(e["threshold"][base + i])
+    return (f"{pad}If (feature {f} <= {t})\n" + subtree(base, int(e["left"][base + i]), indent + 1) +
+            f"{pad}Else (feature {f} > {t})\n" + subtree(base, int(e["right"][base + i]), indent + 1))
+
+
+txt = "RandomForestClassificationModel (uid=rfc_golden) with 3 trees\n"
+for t in range(3):
+    txt += f"  Tree {t} (weight 1.0):\n" + subtree(int(e["tree_off"][t]), 0, 4)
+with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "cfg1_debug_string_3trees.txt"), "w") as f:
+    f.write(txt)
+print("wrote cfg1_debug_string_3trees.txt", len(txt), "bytes")

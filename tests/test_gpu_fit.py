@@ -231,7 +231,7 @@ def test_device_resident_inputs_and_model_roundtrip(ctx, oracle):
         assert np.array_equal(a[k], b[k])
     imp = m_host.featureImportances
     assert imp.shape == (32,) and abs(imp.sum() - 1.0) < 1e-12 and imp[0] > imp[10] and imp[3] > imp[10]
-    assert m_host.toDebugString.startswith("RandomForestClassificationModel with 5 trees")
+    assert m_host.toDebugString.startswith(f"RandomForestClassificationModel (uid={m_host.uid}) with 5 trees\n  Tree 0 (weight 1.0):\n    ")
 
 
 def test_spark_ml_persistence_layout_round_trip(ctx, tmp_path):

@@ -171,3 +171,29 @@ def test_oracle_learns_like_an_independent_random_forest(oracle):
     sk = sklearn.RandomForestClassifier(n_estimators=30, max_depth=8, max_features="sqrt", random_state=7).fit(Xtr, ytr)
     acc_sk = float((sk.predict(Xte) == yte).mean())
     assert acc > 0.85 and abs(acc - acc_sk) < 0.05, (acc, acc_sk)
+
+
+def test_debug_string_matches_committed_spark_format_text(oracle):
+    """toDebugString in Spark 2.4's exact text: the product's renderer (classifier.debug_string) applied
+    to the oracle's export of BASELINE configs[0] must reproduce tests/golden/cfg1_debug_string_3trees.txt, which
+    make_golden.py rendered with its own recursive printer — header with (uid=...), `If (feature f <= t)` /
+    `Else (feature f > t)` / `Predict: p`, one more space per level starting at four."""
+    from euromillioner_b200 import synth
+    from euromillioner_b200.classifier import debug_string
+    X, y, Cn = synth.draw_history()
+    p = oracle.make_params(num_trees=20, max_depth=6, max_bins=32, num_classes=Cn)
+    e = oracle.fit(p, X, y, oracle.partition_offsets(len(X), 8)).export()
+    with open(os.path.join(GOLDEN, "cfg1_debug_string_3trees.txt")) as f:
+        want = f.read()
+    assert debug_string(e, 3, "rfc_golden") == want
+
+
+def test_java_double_to_string_known_answers():
+    """java.lang.Double.toString known answers (JLS / JDK javadoc examples and boundary cases of the two notations)."""
+    from euromillioner_b200.classifier import java_double_to_string as j
+    for v, want in [(24.5, "24.5"), (12.0, "12.0"), (1e-5, "1.0E-5"), (1e7, "1.0E7"), (9999999.0, "9999999.0"),
+                    (0.001, "0.001"), (0.00099, "9.9E-4"), (123456789.125, "1.23456789125E8"), (-3.25, "-3.25"),
+                    (100.0, "100.0"), (1.5e-7, "1.5E-7"), (0.0, "0.0"), (-0.0, "-0.0"), (1e22, "1.0E22"), (0.1, "0.1"),
+                    (12345678.9, "1.23456789E7"), (float("nan"), "NaN"), (float("inf"), "Infinity"),
+                    (float("-inf"), "-Infinity"), (1.7976931348623157e308, "1.7976931348623157E308"), (0.012, "0.012")]:
+        assert j(v) == want, (v, j(v), want)

@@ -21,7 +21,7 @@ class EmrfParams(C.Structure):
         ("subsampling_rate", C.c_double),
         ("max_memory_mb", C.c_int32), ("find_splits_policy", C.c_int32),
         ("seed", C.c_int64),
-        ("shard_mode", C.c_int32), ("reserved", C.c_int32),
+        ("shard_mode", C.c_int32), ("policy_flags", C.c_int32),
     ]
 
 

@@ -187,6 +187,7 @@ class RandomForestClassifier:
         self.cacheNodeIds, self.checkpointInterval = False, 10
         self.numClasses = 0  # 0 = infer from labels (Predictor.getNumClasses)
         self.findSplitsPolicy = 0
+        self.selectNodesLoopPolicy = 0   # 1: pre-`groupDone` loop condition of selectNodesToSplit
         self.shardMode = 0
 
     # --- Spark ML setters -----------------------------------------------------------------
@@ -295,6 +296,7 @@ class RandomForestClassifier:
         p.min_info_gain, p.subsampling_rate = self.minInfoGain, self.subsamplingRate
         p.max_memory_mb, p.find_splits_policy, p.seed = self.maxMemoryInMB, self.findSplitsPolicy, self.seed
         p.shard_mode = self.shardMode
+        p.policy_flags = 1 if self.selectNodesLoopPolicy else 0
         return p
 
     def fit(self, dataset):

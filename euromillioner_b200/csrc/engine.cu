@@ -723,7 +723,7 @@ static int bag_launch(emrf_ctx* c, cudaStream_t stream, const emrf_params_t& P, 
   CU(cudaMemsetAsync(job.d_max.p, 0, 4, stream));
   if (T > 1) {
     const double mean = P.subsampling_rate;
-    const double p_exp = std::exp(-mean);
+    const double p_exp = hl::poisson_exp_policy(mean);
     static const bool serial = env_flag("EMRF_BAG_SERIAL");  // one thread per partition (cross-check)
     if (serial) {
       CU(cudaFuncSetAttribute(kern::bag_poisson_serial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kern::kBagSmemBytes));
@@ -1408,10 +1408,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   auto select_group = [&](GroupSel& G) {
     G.clear();
     int64_t mem = 0;
-    bool rejected = false;
+    bool rejected = false;     // `rejected`: a node did not fit (it has spent its draw); `full`: the older loop form stopped first
+    bool full = false;
     const int32_t* tab = h_table.as<int32_t>();
     const int32_t* tsum_all = h_tsum.as<int32_t>();
-    while (!stack.empty() && !rejected) {
+    while (!stack.empty() && !rejected && !full) {
       // featureSubset = reservoirSampleAndCount(Range(0, F), F_sub, rng.nextLong()): the i-th node examined takes
       // draw number draw_idx + i, so a run of stack entries is served by the current window of the table
       if (subsampling && draw_idx >= table_base + table_cap) {
@@ -1424,6 +1425,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       // how many of the next m entries fit: a running sum over the table's bin totals (sequential, tiny)
       size_t k = 0;
       for (; k < m; k++) {
+        if (!hl::select_nodes_examines_next(P.policy_flags, mem, max_mem)) { full = true; break; }
         const int64_t node_mem = (int64_t)C * (subsampling ? (int64_t)tsum_all[at0 + k] : all_feat_bins) * 8;
         if (mem + node_mem <= max_mem || mem == 0) mem += node_mem;
         else { rejected = true; break; }
@@ -2949,6 +2951,8 @@ extern "C" int emrf_update_partition_noalloc(emrf_ctx_t* c, const uint8_t* bins_
   if ((size_t)n_nodes > kNoAllocMaxNodes)
     return fail(EMRF_ERR_LIMIT, "emrf_update_partition_noalloc handles at most %zu nodes per call (got %d)", kNoAllocMaxNodes, n_nodes);
   if (c->device < 0 || c->device >= 64) return fail(EMRF_ERR_LIMIT, "device ordinal %d not supported", c->device);
+  if (node_seg_off[0] < 0) return fail(EMRF_ERR_ARG, "node_seg_off[0] is negative");
+  return guarded(c, [&]() -> int {       // no exception (std::bad_alloc of the descriptor vectors) may cross the C boundary
   // host-side descriptors first, so that the size check happens before anything is enqueued
   std::vector<kern::SplitNode> sn(n_nodes);
   size_t n_tiles = 0;
@@ -2970,6 +2974,16 @@ extern "C" int emrf_update_partition_noalloc(emrf_ctx_t* c, const uint8_t* bins_
   if (n_tiles > kNoAllocMaxTiles)
     return fail(EMRF_ERR_LIMIT, "emrf_update_partition_noalloc handles at most %zu entries per call (%zu tiles of %d; got %zu tiles)",
                 kNoAllocMaxTiles * (size_t)kern::kPartTile, kNoAllocMaxTiles, kern::kPartTile, n_tiles);
+  // the kernels read entries_dev while they write entries_out_dev: the two must be distinct device buffers (checked with
+  // cudaPointerGetAttributes, which allocates nothing)
+  if (!is_device_ptr(bins_cm_dev) || !is_device_ptr(entries_dev) || !is_device_ptr(entries_out_dev) || !is_device_ptr(n_left_dev))
+    return fail(EMRF_ERR_ARG, "emrf_update_partition_noalloc takes device pointers for bins_cm, entries, entries_out and n_left");
+  {
+    const uint64_t n_ent = (uint64_t)node_seg_off[n_nodes];
+    const uintptr_t a0 = (uintptr_t)entries_dev, b0 = (uintptr_t)entries_out_dev;
+    if (a0 == b0 || (a0 < b0 + n_ent * 8 && b0 < a0 + n_ent * 8))
+      return fail(EMRF_ERR_ARG, "entries_out_dev must not alias entries_dev (the partition is not done in place)");
+  }
   std::vector<uint32_t> tn(n_tiles);
   for (int i = 0; i < n_nodes; i++)
     for (uint32_t q = 0; q < sn[i].n_tiles; q++) tn[sn[i].tile_begin + q] = (uint32_t)i;
@@ -3007,6 +3021,7 @@ extern "C" int emrf_update_partition_noalloc(emrf_ctx_t* c, const uint8_t* bins_
   }
   CU(cudaStreamSynchronize(st));  // sn / tn are pageable host memory read by the async copies
   return EMRF_OK;
+  });
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -277,5 +277,15 @@ inline double impurity_of(int kind, const uint32_t* counts, int n_classes) {
   return imp;
 }
 
+// POLICY: how RandomForest.selectNodesToSplit ends a group.  Default (`groupDone` form, taken to be Spark
+// 2.4.6's): the node that does not fit is examined — and spends a draw of the driver RNG — even when the group's memory
+// already equals the limit.  policy_flags bit 0: the older loop tests `memUsage < maxMemoryUsage || memUsage == 0` first
+// and stops without a draw in exactly that case.
+inline bool select_nodes_examines_next(int policy_flags, int64_t mem_usage, int64_t max_mem) {
+  return (policy_flags & 1) == 0 ? true : (mem_usage < max_mem || mem_usage == 0);
+}
+// POLICY: the pivot exp(-mean) of commons-math's PoissonDistribution.sample() (FastMath.exp there).
+inline double poisson_exp_policy(double mean) { return std::exp(-mean); }
+
 }  // namespace hostlogic
 }  // namespace emrf

@@ -52,7 +52,9 @@ typedef struct {
   int32_t find_splits_policy;      /* 0 = Spark 2.4 (zero filter + expected sample count); 1 = pre-2.4 */
   int64_t seed;                    /* default 207336481 = "…RandomForestClassifier".hashCode */
   int32_t shard_mode;              /* multi-GPU: 0 tree-sharded, 1 row-sharded (ignored when world==1) */
-  int32_t reserved;
+  int32_t policy_flags;            /* bit 0: RandomForest.selectNodesToSplit ends a group with the pre-`groupDone` loop condition
+                                      (`while (memUsage < maxMemoryUsage || memUsage == 0)`): differs from the default only when a
+                                      group's memory lands exactly on maxMemoryInMB */
 } emrf_params_t;
 
 /* Phase timers named after Spark's TimeTracker phases (ml/tree/impl/TimeTracker.scala), device
@@ -225,7 +227,10 @@ int emrf_synth_flat(emrf_ctx_t* ctx, int64_t n_rows, int32_t n_features, int32_t
  * the caller, and all working storage is a fixed 2 293 760-byte device array inside the library
  * (held by every GPU that loads it, until exit).  Limits per call: 4096 nodes, 262 144 tiles of
  * 2048 entries; larger requests fail with EMRF_ERR_LIMIT.  The first call on a device looks up
- * the array's address (do it before any stream capture); concurrent calls on one GPU race. */
+ * the array's address (do it before any stream capture); concurrent calls on one GPU race.
+ * Refused with EMRF_ERR_ARG before anything is enqueued: a host pointer for any of the four buffers, an output that is
+ * or overlaps the input (the partition is not done in place), a negative node_seg_off[0].  The call returns after its
+ * GPU work has completed, and no C++ exception leaves it. */
 int emrf_update_partition_noalloc(emrf_ctx_t* ctx, const uint8_t* bins_cm_dev, int64_t col_stride,
                                   int32_t n_features, const uint64_t* entries_dev,
                                   const int64_t* node_seg_off, int32_t n_nodes,

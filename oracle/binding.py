@@ -23,6 +23,7 @@ class OrcParams(C.Structure):
         ("subsampling_rate", C.c_double),
         ("max_memory_mb", C.c_int32), ("find_splits_policy", C.c_int32),
         ("seed", C.c_int64),
+        ("select_nodes_loop_policy", C.c_int32), ("pad", C.c_int32),
     ]
 
 
@@ -32,7 +33,7 @@ FEATURE_SUBSET = {"auto": 0, "all": 1, "sqrt": 2, "log2": 3, "onethird": 4}
 def make_params(num_trees=20, max_depth=5, max_bins=32, num_classes=2, seed=207336481,
                 impurity="gini", feature_subset="auto", subsampling_rate=1.0,
                 min_instances_per_node=1, min_info_gain=0.0, max_memory_mb=256,
-                find_splits_policy=0, cls=OrcParams):
+                find_splits_policy=0, select_nodes_loop_policy=0, cls=OrcParams):
     p = cls()
     p.num_trees, p.max_depth, p.max_bins = num_trees, max_depth, max_bins
     p.min_instances_per_node, p.num_classes = min_instances_per_node, num_classes
@@ -47,6 +48,10 @@ def make_params(num_trees=20, max_depth=5, max_bins=32, num_classes=2, seed=2073
             p.feature_subset_kind, p.feature_subset_value = 6, v
     p.min_info_gain, p.subsampling_rate = min_info_gain, subsampling_rate
     p.max_memory_mb, p.find_splits_policy, p.seed = max_memory_mb, find_splits_policy, seed
+    if hasattr(p, "select_nodes_loop_policy"):
+        p.select_nodes_loop_policy = select_nodes_loop_policy
+    else:
+        p.policy_flags = 1 if select_nodes_loop_policy else 0      # EmrfParams: bit 0
     return p
 
 

@@ -167,7 +167,7 @@ struct Well19937c {
 struct PoissonSampler {
   Well19937c rng;
   double mean, p;
-  explicit PoissonSampler(double mean_) : mean(mean_), p(std::exp(-mean_)) {}
+  explicit PoissonSampler(double mean_);
   void reseed(int64_t seed) { rng.setSeed(seed); }
   int sample() {
     int64_t n = 0;
@@ -181,6 +181,7 @@ struct PoissonSampler {
   }
 };
 
+// (constructor defined below Params: the pivot is a policy function)
 // -------------------------------------------------------------------------------------
 // core:util/random/SamplingUtils.reservoirSampleAndCount.  Result NOT sorted.
 // -------------------------------------------------------------------------------------
@@ -286,7 +287,23 @@ struct Params {
   int32_t max_memory_mb = 256;
   int32_t find_splits_policy = 0;   // 0: Spark 2.4 (zero filter + expected numSamples); 1: pre-2.4
   int64_t seed = 207336481LL;
+  int32_t select_nodes_loop_policy = 0;   // 0: `groupDone` loop; 1: `while (memUsage < maxMemoryUsage || memUsage == 0)` loop
 };
+
+// POLICY: how RandomForest.selectNodesToSplit ends a group.  Both forms admit a node while
+// memUsage + nodeMemUsage <= maxMemoryUsage (or the group is empty) and both spend an rng.nextLong() on the node that does
+// not fit.  They differ only when a group's memory lands EXACTLY on the limit: the `groupDone` form (policy 0, what this
+// restatement takes Spark 2.4.6 to do) then draws for one more node and rejects it; the older form (policy 1) tests
+// `memUsage < maxMemoryUsage || memUsage == 0` before looking at the next node and stops without a draw.
+static inline bool select_nodes_examines_next(int policy, int64_t mem_usage, int64_t max_mem) {
+  return policy == 0 ? true : (mem_usage < max_mem || mem_usage == 0);
+}
+
+// POLICY: the pivot of commons-math 3.4.1 PoissonDistribution.sample() is FastMath.exp(-mean); libm's exp
+// stands in for it here.  For subsamplingRate = 1.0 both are the double nearest to 1/e (0x3FD78B56362CEF38) as far as
+// this restatement knows; if a JVM ever disagrees, this is the one place to change.
+static inline double poisson_exp_policy(double mean) { return std::exp(-mean); }
+inline PoissonSampler::PoissonSampler(double mean_) : mean(mean_), p(poisson_exp_policy(mean_)) {}
 
 // ml/tree/impl/DecisionTreeMetadata.buildMetadata
 static int num_features_per_node(const Params& p, int F) {
@@ -731,7 +748,7 @@ static Forest* fit(const Params& p, const double* X, const double* y, int64_t N,
     std::vector<int> trees_seen;  // first-seen order = mutable HashMap insertion order
     std::map<int, std::vector<int>> nodes_for_tree;  // tree → group indices in pop order
     int64_t mem = 0, hist_total = 0;
-    while (!stack.empty()) {
+    while (!stack.empty() && select_nodes_examines_next(p.select_nodes_loop_policy, mem, max_mem)) {
       auto top = stack.back();
       std::vector<int> subset;
       if (subsampling) subset = reservoir_sample_range(F, f_sub, rng.nextLong());
@@ -919,6 +936,7 @@ typedef struct {
   double feature_subset_value, min_info_gain, subsampling_rate;
   int32_t max_memory_mb, find_splits_policy;
   int64_t seed;
+  int32_t select_nodes_loop_policy, pad;
 } orc_params_t;
 
 static orc::Params to_params(const orc_params_t* p) {
@@ -929,6 +947,7 @@ static orc::Params to_params(const orc_params_t* p) {
   q.feature_subset_value = p->feature_subset_value; q.min_info_gain = p->min_info_gain;
   q.subsampling_rate = p->subsampling_rate; q.max_memory_mb = p->max_memory_mb;
   q.find_splits_policy = p->find_splits_policy; q.seed = p->seed;
+  q.select_nodes_loop_policy = p->select_nodes_loop_policy;
   return q;
 }
 

@@ -332,3 +332,24 @@ def test_predict_variants_chunks_and_threads(ctx, oracle):
             "print('DENSE_OK')\n") % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, EMRF_PREDICT_DENSE_LEAVES="1"), capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "DENSE_OK" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+def test_select_nodes_loop_policy_matches_oracle_when_a_group_fills_memory_exactly(ctx, oracle):
+    """SURVEY.md A.9 policy: two classes x 4 features x 32 bins = 2048 B per node and maxMemoryInMB = 1 make every full
+    group land EXACTLY on the limit (512 nodes), the one case where the `groupDone` loop (default) and the older
+    `while (memUsage < maxMemoryUsage || memUsage == 0)` loop differ (the former spends one more draw of the driver
+    RNG).  The engine must follow the oracle under either policy, and the two policies must give different forests."""
+    rng = np.random.default_rng(3)
+    X = rng.integers(1, 33, size=(40000, 16)).astype(np.float64)      # 32 distinct values: 32 bins per feature
+    y = ((X[:, 0] + X[:, 5] + rng.integers(0, 3, size=len(X))) % 2).astype(np.float64)
+    exports = []
+    for pol in (0, 1):
+        rf = (RandomForestClassifier(ctx).setNumTrees(40).setMaxDepth(9).setNumClasses(2).setMaxMemoryInMB(1))
+        rf.selectNodesLoopPolicy = pol
+        model = rf.fit(Dataset(X, y, num_partitions=8))
+        po = oracle.make_params(num_trees=40, max_depth=9, num_classes=2, max_memory_mb=1, select_nodes_loop_policy=pol)
+        ofo = oracle.fit(po, X, y, oracle.partition_offsets(len(X), 8))
+        _assert_same_forest(model, ofo)
+        assert 512 in list(ofo.group_sizes())
+        exports.append(model.export())
+    assert not np.array_equal(exports[0]["feature"], exports[1]["feature"])

@@ -329,7 +329,7 @@ def main():
             ok = 1.0
             if rank == 0:
                 c1 = Context(local_rank)
-                n1, p1, t1 = (n_global, N_PARTS * world, T)
+                n1, p1, t1 = (n_global, N_PARTS * (world if mode == "rows" else 1), T)
                 g = synth.DeviceFlat(c1, n1, N_FEATURES, N_CLASSES)
                 m1 = estimator(c1, t1).fit(Dataset(g.X.value, g.y.value, num_partitions=p1, n_rows=n1, n_features=N_FEATURES))
                 eq, field = forests_equal(exp, m1.export())

@@ -1623,7 +1623,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         nt_tmp[i] = d.n_tiles;
         const int level = hn.level;
         info[i] = (uint32_t)level | (m ? kern::kInfoMine : 0u);
-        if (m && level < P.max_depth) ptiles_ub64 += (hn.ub + kern::kPartTile - 1) / kern::kPartTile;
+        if (m && level < P.max_depth) ptiles_ub64 += std::max<uint32_t>(1, (hn.ub + kern::kPartTile - 1) / kern::kPartTile);
         memcpy(feat_out + (size_t)i * f_sub, group_feat.data() + group[i].feat_at, (size_t)f_sub * 4);
       }
     }

@@ -1650,7 +1650,7 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
       const uint32_t fs = (dec & kDecNonLeaf) ? ((uint32_t)A.node_feat[(size_t)g * A.f_sub + r.k] | ((uint32_t)r.split << 24)) : 0u;
       A.out_dec[g] = dec;
       A.out_sched[g] = make_uint4(dec, r.left_weight, r.total_weight, fs);
-      A.out_ptiles[g] = (dec & kDecSplit) ? (nd.seg_len + kPartTile - 1) / kPartTile : 0u;
+      A.out_ptiles[g] = (dec & kDecSplit) ? max(1u, (nd.seg_len + kPartTile - 1) / kPartTile) : 0u;   // >= 1: the node's last tile writes the children's segments
     }
   }
 }
@@ -2025,7 +2025,9 @@ __global__ void __launch_bounds__(256) decide_flags_kernel(const DecideArgs A) {
   const ScanResult& r = r0[best < 0 ? 0 : best];
   const uint32_t dec = decide_word(r, best, A.node_info[gi], A.max_depth);
   const uint32_t fs = (dec & kDecNonLeaf) ? ((uint32_t)A.node_feat[(size_t)gi * A.f_sub + r.k] | ((uint32_t)r.split << 24)) : 0u;
-  const uint32_t tiles = (dec & kDecSplit) ? (A.segtab[A.nodes[gi].seg_slot].len + kPartTile - 1) / kPartTile : 0u;
+  // at least one tile per split node, even when this rank holds none of its rows (rows sharded): the one-pass
+  // partition's last tile of a node is what writes the children's segments and the left count
+  const uint32_t tiles = (dec & kDecSplit) ? max(1u, (A.segtab[A.nodes[gi].seg_slot].len + kPartTile - 1) / kPartTile) : 0u;
   A.out_dec[gi] = dec;
   A.out_sched[gi] = make_uint4(dec, r.left_weight, r.total_weight, fs);
   A.out_tiles[gi] = tiles;

@@ -247,6 +247,7 @@ struct emrf_ctx {
   cudaStream_t stream = nullptr;
   cudaStream_t stream2 = nullptr;   // bagging runs here, underneath input copy / findSplits / binning
   cudaStream_t stream3 = nullptr;   // chunked host -> device copy of the feature matrix (binning follows chunk by chunk)
+  cudaStream_t stream_comm = nullptr;   // rows sharded: per-piece reduce-scatter + owner-side scan, under the next piece's histogram kernel
   int sm_count = 148;
   int host_threads = 1;   // OpenMP threads for the host scheduler's parallel pieces (cores / ranks on this node)
   size_t smem_optin = 0;
@@ -313,6 +314,7 @@ static int ctx_init(emrf_ctx* c, int device) {
   CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&c->stream_comm, cudaStreamNonBlocking));
   memset(&c->tm, 0, sizeof(c->tm));
   c->host_threads = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
   if (const char* e = getenv("EMRF_HOST_THREADS")) c->host_threads = std::max(1, atoi(e));   // experiments
@@ -390,6 +392,7 @@ extern "C" void emrf_ctx_destroy(emrf_ctx_t* c) {
   if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
   if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
   if (c->stream3) { cudaStreamSynchronize(c->stream3); cudaStreamDestroy(c->stream3); }
+  if (c->stream_comm) { cudaStreamSynchronize(c->stream_comm); cudaStreamDestroy(c->stream_comm); }
   const int dev = c->device;
   delete c;
   DevCache::get().trim(dev);
@@ -401,22 +404,22 @@ extern "C" int emrf_get_timings(const emrf_ctx_t* c, emrf_timings_t* out) {
 }
 // in-place all-reduce over the ctx communicator: uint32 sum (histograms, split records, raw bit
 // patterns against zeros) or int32 max (label flags)
-static int nccl_allreduce(emrf_ctx* c, void* buf, size_t count, bool int32_max) {
+static int nccl_allreduce(emrf_ctx* c, void* buf, size_t count, bool int32_max, cudaStream_t stream = nullptr) {
   if (c->world == 1) return EMRF_OK;
   static ncclAllReduce_t ar = nullptr;
   if (!ar) ar = (ncclAllReduce_t)dlsym(c->nccl_lib, "ncclAllReduce");
   int rc = ar(buf, buf, count, int32_max ? /*ncclInt32*/ 2 : /*ncclUint32*/ 3, int32_max ? /*ncclMax*/ 2 : /*ncclSum*/ 0,
-              c->nccl_comm, c->stream);
+              c->nccl_comm, stream ? stream : c->stream);
   if (rc) return fail(EMRF_ERR_CUDA, "ncclAllReduce failed (%d)", rc);
   return EMRF_OK;
 }
-static int nccl_allreduce_u32(emrf_ctx* c, uint32_t* buf, size_t count) { return nccl_allreduce(c, buf, count, false); }
+static int nccl_allreduce_u32(emrf_ctx* c, uint32_t* buf, size_t count, cudaStream_t stream = nullptr) { return nccl_allreduce(c, buf, count, false, stream); }
 // in-place reduce-scatter (uint32 sum): rank r ends up with the sum of words [r*per_rank, (r+1)*per_rank)
-static int nccl_reduce_scatter_u32(emrf_ctx* c, uint32_t* buf, size_t per_rank) {
+static int nccl_reduce_scatter_u32(emrf_ctx* c, uint32_t* buf, size_t per_rank, cudaStream_t stream = nullptr) {
   static ncclReduceScatter_t rs = nullptr;
   if (!rs) rs = (ncclReduceScatter_t)dlsym(c->nccl_lib, "ncclReduceScatter");
   if (!rs) return fail(EMRF_ERR_CUDA, "ncclReduceScatter missing");
-  int rc = rs(buf, buf + (size_t)c->rank * per_rank, per_rank, /*ncclUint32*/ 3, /*ncclSum*/ 0, c->nccl_comm, c->stream);
+  int rc = rs(buf, buf + (size_t)c->rank * per_rank, per_rank, /*ncclUint32*/ 3, /*ncclSum*/ 0, c->nccl_comm, stream ? stream : c->stream);
   if (rc) return fail(EMRF_ERR_CUDA, "ncclReduceScatter failed (%d)", rc);
   return EMRF_OK;
 }
@@ -1630,28 +1633,56 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     // (the sequential part works on compact arrays; the staging records get the results in the parallel pass below)
     uint32_t n_tiles = 0;
     int n_slots = 0;
+    // Rows sharded (NCCL path): a group is cut into pieces of consecutive nodes, each with its own block of histogram slots
+    // [world][npr] — the reduce-scatter of piece p runs on the communication stream under the histogram kernel of piece
+    // p + 1.  Piece q: nodes [pc_n0[q], pc_n0[q+1]), tiles [pc_t0[q], pc_t0[q+1]), slots from pc_s0[q], npr = pc_npr[q].
+    constexpr int kMaxPieces = 8;
+    int n_pieces = 1;
+    int pc_n0[kMaxPieces + 1], pc_npr[kMaxPieces], pc_s0[kMaxPieces + 1];
+    uint32_t pc_t0[kMaxPieces + 1];
     {
       const bool all_slots = row_sharded && !push_mode;   // every histogram goes to HBM for the reduce-scatter
+      if (all_slots) {
+        // default 1: measured on 2 B200s, 2 / 4 / 8 pieces make the fit SLOWER (40.0 -> 41.5 / 43.9 / 49.8 ms): the collective
+        // and the histogram kernel compete for the same HBM and SMs, and shorter launches fill the GPU worse
+        static const int want = [] { const char* e = getenv("EMRF_RS_PIECES"); return e ? std::min(8, std::max(1, atoi(e))) : 1; }();
+        n_pieces = std::max(1, std::min(want, n_nodes / 128));      // small groups: one piece
+      }
+      pc_s0[0] = 0;
+      for (int q = 0; q <= n_pieces; q++) pc_n0[q] = (int)((int64_t)n_nodes * q / n_pieces);
+      for (int q = 0; q < n_pieces; q++) {
+        pc_npr[q] = all_slots ? (pc_n0[q + 1] - pc_n0[q] + c->world - 1) / c->world : 0;
+        pc_s0[q + 1] = pc_s0[q] + pc_npr[q] * c->world;
+      }
       const uint32_t* ntp = nt_tmp.data();
       uint32_t* tbp = tb_tmp.data();
       int32_t* slp = slot_tmp.data();
       // tile order = launch order: the tiles of multi-tile nodes (full tiles, the longest CTAs) first, then the larger
       // single-tile nodes, then the small ones, so that a launch does not end on a few long CTAs (a group arrives in
       // pop order: deepest, i.e. smallest, nodes first).  Row-range order (l2_blocked) has its own tile map.
-      uint32_t cls_tiles[3] = {0, 0, 0};
-      for (int i = 0; i < n_nodes; i++) {
-        slp[i] = (all_slots || ntp[i] > 1) ? n_slots++ : -1;
-        const int cls = l2_blocked ? 0 : (ntp[i] > 1 ? 0 : (group[i].ub >= 2048 ? 1 : 2));
-        tbp[i] = (uint32_t)cls;              // class now, first tile below
-        cls_tiles[cls] += ntp[i];
+      uint32_t cls_tiles[3 * kMaxPieces];
+      for (int q = 0; q < 3 * n_pieces; q++) cls_tiles[q] = 0;
+      for (int q = 0, i = 0; q < n_pieces; q++) {
+        for (; i < pc_n0[q + 1]; i++) {
+          slp[i] = all_slots ? pc_s0[q] + (i - pc_n0[q]) : (ntp[i] > 1 ? n_slots++ : -1);
+          const int cls = 3 * q + (l2_blocked ? 0 : (ntp[i] > 1 ? 0 : (group[i].ub >= 2048 ? 1 : 2)));
+          tbp[i] = (uint32_t)cls;              // class now, first tile below
+          cls_tiles[cls] += ntp[i];
+        }
       }
-      uint32_t cls_off[3] = {0, cls_tiles[0], cls_tiles[0] + cls_tiles[1]};
+      if (all_slots) n_slots = pc_s0[n_pieces];
+      uint32_t cls_off[3 * kMaxPieces];
+      for (int q = 0; q < 3 * n_pieces; q++) {
+        cls_off[q] = n_tiles;
+        if (q % 3 == 0) pc_t0[q / 3] = n_tiles;
+        n_tiles += cls_tiles[q];
+      }
+      pc_t0[n_pieces] = n_tiles;
       for (int i = 0; i < n_nodes; i++) {
         const uint32_t cls = tbp[i];
         tbp[i] = cls_off[cls];
         cls_off[cls] += ntp[i];
       }
-      n_tiles = cls_tiles[0] + cls_tiles[1] + cls_tiles[2];
     }
     const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
     const size_t group_bytes = l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4;
@@ -1698,8 +1729,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       CU(c->d_tickets.ensure(n_rec * 4));
       if (self_clean && (c->d_tickets.p != pt || !tickets_zeroed)) { CU(cudaMemsetAsync(c->d_tickets.p, 0, c->d_tickets.bytes, st)); tickets_zeroed = true; }
     }
-    const int nodes_per_rank = row_sharded ? (n_nodes + c->world - 1) / c->world : 0;
-    const int n_slots_alloc = (row_sharded && !push_mode) ? nodes_per_rank * c->world : n_slots;
+    const int nodes_per_rank = row_sharded ? (n_nodes + c->world - 1) / c->world : 0;   // the push path's single piece
+    const int n_slots_alloc = n_slots;
     {
       const void* pg = c->d_ghist.p;
       CU(c->d_ghist.ensure((size_t)std::max(n_slots_alloc, 1) * slot_words * 4));
@@ -1781,21 +1812,54 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       A.out_ptiles = (uint32_t*)((char*)c->d_part.p + off_ptiles);
       A.max_depth = P.max_depth;
     }
+    const bool piped = row_sharded && !push_mode && c->world > 1;   // pieces of the group: histogram kernel || reduce-scatter
+    cudaStream_t sc = c->stream_comm;
+    // collectives are timed on their own (CUDA events right around each call, on the stream that carries it:
+    // emrf_timings_t.comm_ms; with pieces in flight this is device time of the collectives, not exposed time)
+    auto comm_begin = [&](cudaStream_t s_) -> cudaEvent_t { cudaEvent_t e = c->events.get(); cudaEventRecord(e, s_); return e; };
+    auto comm_end = [&](cudaEvent_t e0, int64_t bytes, cudaStream_t s_) { cudaEvent_t e1 = c->events.get(); cudaEventRecord(e1, s_); comm_ev.emplace_back(e0, e1); tm.comm_bytes += bytes; };
     {
       cudaEvent_t e0 = c->events.get(), e1 = c->events.get();
       CU(cudaEventRecord(e0, st));
-      if (n_tiles) {
-        CU(hist_launch(row_ch, dim3(n_tiles, n_chunks), u16 ? hist_smem16 : hist_smem, st, A, false, u16));
-        tm.kernel_launches++;
-        tm.hist_launches++;
+      for (int q = 0; q < n_pieces; q++) {
+        const uint32_t t0 = pc_t0[q], nt = pc_t0[q + 1] - pc_t0[q];
+        if (nt) {
+          A.tile_base = t0;
+          CU(hist_launch(row_ch, dim3(nt, n_chunks), u16 ? hist_smem16 : hist_smem, st, A, false, u16));
+          tm.kernel_launches++;
+          if (q == 0) tm.hist_launches++;
+        }
+        if (!piped) continue;
+        // reduceByKey(_.merge(_)) of Spark's per-partition aggregators, keyed by node exactly as Spark does it: a
+        // reduce-scatter leaves each rank with the summed histograms (exact integers) of ITS share of the piece's nodes, it
+        // scans those; the small split records are combined at the end with an all-reduce over zero-filled slots.
+        cudaEvent_t ev_piece = c->events.get();
+        CU(cudaEventRecord(ev_piece, st));
+        CU(cudaStreamWaitEvent(sc, ev_piece, 0));
+        const int npr = pc_npr[q], size_q = pc_n0[q + 1] - pc_n0[q];
+        if (size_q == 0) continue;
+        uint32_t* piece_hist = c->d_ghist.as<uint32_t>() + (size_t)pc_s0[q] * slot_words;
+        {
+          const cudaEvent_t c0 = comm_begin(sc);
+          TRY(nccl_reduce_scatter_u32(c, piece_hist, (size_t)npr * slot_words, sc));
+          comm_end(c0, (int64_t)npr * c->world * (int64_t)slot_words * 4, sc);
+        }
+        const int first_local = c->rank * npr;
+        const int mine_n = std::max(0, std::min(npr, size_q - first_local));
+        if (mine_n > 0) {
+          const size_t first = (size_t)pc_n0[q] + first_local;      // group index of this rank's first node of the piece
+          kern::scan_kernel<<<dim3(mine_n, n_chunks), kern::kHistThreads, hist_bytes, sc>>>(
+              piece_hist + (size_t)first_local * slot_words, A.node_feat + first * f_sub, A.num_bins_all, f_sub,
+              B, C, k_chunk, n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain,
+              A.results + first * n_chunks, A.left_counts + first * n_chunks * C, A.total_counts + first * n_chunks * C);
+          tm.kernel_launches++;
+          CU(cudaGetLastError());
+        }
       }
       CU(cudaEventRecord(e1, st));
       hist_ev.emplace_back(e0, e1);
       CU(cudaGetLastError());
     }
-    // collectives are timed on their own (CUDA events right around each call: emrf_timings_t.comm_ms)
-    auto comm_begin = [&]() -> cudaEvent_t { cudaEvent_t e = c->events.get(); cudaEventRecord(e, st); return e; };
-    auto comm_end = [&](cudaEvent_t e0, int64_t bytes) { cudaEvent_t e1 = c->events.get(); cudaEventRecord(e1, st); comm_ev.emplace_back(e0, e1); tm.comm_bytes += bytes; };
     if (c->world > 1) {
       if (row_sharded && push_mode) {
         // every rank's partials must have landed in the owners' staging buffers: a 1-word all-reduce is the
@@ -1811,32 +1875,18 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
           tm.kernel_launches++;
           CU(cudaGetLastError());
         }
-      } else if (row_sharded) {
-        // reduceByKey(_.merge(_)) of Spark's per-partition aggregators, keyed by node exactly as Spark
-        // does it: a reduce-scatter leaves each rank with the summed histograms (exact integers) of ITS
-        // share of the group's nodes, it scans those, and the small split records are combined with an
-        // all-reduce over zero-filled slots (as in the tree-sharded mode).
-        {
-          const cudaEvent_t e0 = comm_begin();
-          TRY(nccl_reduce_scatter_u32(c, c->d_ghist.as<uint32_t>(), (size_t)nodes_per_rank * slot_words));
-          comm_end(e0, (int64_t)nodes_per_rank * c->world * (int64_t)slot_words * 4);
-        }
-        const int first = c->rank * nodes_per_rank;
-        const int mine_n = std::max(0, std::min(nodes_per_rank, n_nodes - first));
-        if (mine_n > 0) {
-          kern::scan_kernel<<<dim3(mine_n, n_chunks), kern::kHistThreads, hist_bytes, st>>>(
-              c->d_ghist.as<uint32_t>() + (size_t)first * slot_words, A.node_feat + (size_t)first * f_sub, A.num_bins_all, f_sub,
-              B, C, k_chunk, n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain,
-              A.results + (size_t)first * n_chunks, A.left_counts + (size_t)first * n_chunks * C,
-              A.total_counts + (size_t)first * n_chunks * C);
-          tm.kernel_launches++;
-          CU(cudaGetLastError());
-        }
       }
+      // the split records of all ranks (each rank wrote its nodes' records, zeros elsewhere)
+      cudaStream_t sr = piped ? sc : st;
       {
-        const cudaEvent_t e0 = comm_begin();
-        TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_dec / 4));
-        comm_end(e0, (int64_t)res_dec);
+        const cudaEvent_t c0 = comm_begin(sr);
+        TRY(nccl_allreduce_u32(c, (uint32_t*)c->d_results.p, res_dec / 4, sr));
+        comm_end(c0, (int64_t)res_dec, sr);
+      }
+      if (piped) {
+        cudaEvent_t ev_comm = c->events.get();
+        CU(cudaEventRecord(ev_comm, sc));
+        CU(cudaStreamWaitEvent(st, ev_comm, 0));
       }
     }
     // ---- decisions and partition work on the device, the partition kernels right behind.  The host gets the
@@ -2123,6 +2173,7 @@ static int guarded(emrf_ctx* c, Fn&& fn) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->stream2) cudaStreamSynchronize(c->stream2);
     if (c->stream3) cudaStreamSynchronize(c->stream3);
+    if (c->stream_comm) cudaStreamSynchronize(c->stream_comm);
     cudaGetLastError();
     fail(rc, "%s", msg.c_str());
   }

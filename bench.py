@@ -21,7 +21,8 @@ Besides the headline the line carries
   * `configs2`: one fit of BASELINE configs[2] (RF 500 trees, depth 12, 10M x 128, 8192 partitions) at this N —
     one GPU, row-sharded and tree-sharded — with the histogram kernel's roofline fraction, the collectives' time
     and the strong-scaling efficiency against the one-GPU fit of the same run;
-  * `predict`: batch prediction (BASELINE configs[4] shape) rows/s.
+  * `configs3`: BASELINE configs[3], the seven per-ball models dealt to the GPUs (model-parallel, no collective);
+  * `predict`: BASELINE configs[4], 100M rows through a 500-tree depth-12 forest, rows/s.
 
 --impl reference: times the CPU oracle (the restated Spark MLlib algorithm; no JVM/Spark exists on
 this box, so there is no oracle/_ref) on the host cores, on the same workload.
@@ -48,8 +49,10 @@ CPU_SAMPLE_TREES = 100   # the whole workload: ~8 s on 16 cores
 SEED = 207336481
 # BASELINE configs[2]
 C2_ROWS, C2_FEATURES, C2_TREES, C2_DEPTH, C2_PARTS = 10_000_000, 128, 500, 12, 8192
-# BASELINE configs[4] (rows are streamed through the forest in resident chunks of this many rows)
-C4_ROWS_RESIDENT = 10_000_000
+# BASELINE configs[3]: the 7 per-ball models (5 mains, 50 classes; 2 stars, 12 classes), 200 trees each, on the draw history
+C3_TREES, C3_DEPTH, C3_DRAWS, C3_LAG, C3_PARTS = 200, 6, 1500, 10, 8
+# BASELINE configs[4]: 100M rows through a 500-tree depth-12 forest, generated and predicted in resident chunks
+C4_ROWS_TOTAL, C4_ROWS_CHUNK = 100_000_000, 10_000_000
 
 
 def workload_name(n_gpus, mode="rows"):
@@ -197,7 +200,8 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs2", action="store_true", help="skip the BASELINE configs[2] block (10M x 128, 500 trees)")
-    ap.add_argument("--no-predict", action="store_true", help="skip the batch-predict block (BASELINE configs[4] shape)")
+    ap.add_argument("--no-configs3", action="store_true", help="skip the BASELINE configs[3] block (7 per-ball models)")
+    ap.add_argument("--no-predict", action="store_true", help="skip the batch-predict block (BASELINE configs[4])")
     ap.add_argument("--no-parity", action="store_true", help="skip the N > 1 one-GPU parity fit")
     ap.add_argument("--mode", default="rows", choices=["rows", "trees"], help="how N > 1 GPUs share one forest")
     args = ap.parse_args()
@@ -349,7 +353,12 @@ def main():
     if not args.no_configs2:
         configs2 = run_configs2(ctx, world, rank, local_rank, barrier, allreduce_max, estimator, shard_kw, peak)
 
-    # ---- batch prediction (BASELINE configs[4] shape)
+    # ---- BASELINE configs[3]: the seven per-ball models, one fit per model, models dealt to the GPUs
+    configs3 = None
+    if not args.no_configs3:
+        configs3 = run_configs3(ctx, world, rank, barrier, allreduce_max)
+
+    # ---- batch prediction (BASELINE configs[4])
     predict = None
     if not args.no_predict:
         predict = run_predict(ctx, world, rank, barrier, allreduce_max, estimator)
@@ -411,6 +420,8 @@ def main():
             out["parity_first_difference"] = field
     if configs2 is not None:
         out["configs2"] = configs2
+    if configs3 is not None:
+        out["configs3"] = configs3
     if predict is not None:
         out["predict"] = predict
     print(json.dumps(out), flush=True)
@@ -497,10 +508,61 @@ def run_configs2(ctx, world, rank, local_rank, barrier, allreduce_max, estimator
     return out
 
 
+def run_configs3(ctx, world, rank, barrier, allreduce_max):
+    """BASELINE configs[3]: all 7 per-ball models (balls 0-4: 50 classes, balls 5-6: 12 classes), 200 trees each, depth 6, on
+    the 1 490 lag-window rows of 1 500 synthetic draws.  Many-model / small-data: model-parallel, ball b is fitted by rank
+    b % N with its own context and RNG, no collective.  Features are built on the device from the draws
+    table (emrf_build_lag_features); rank 0 checks its first model against the CPU oracle."""
+    from euromillioner_b200 import _lib, synth
+    from euromillioner_b200.classifier import Context, Dataset, RandomForestClassifier
+    c = Context(ctx.device) if world > 1 else ctx
+    L = _lib.lib()
+    draws = np.ascontiguousarray(synth.draws(C3_DRAWS), np.int32)
+    n, F = C3_DRAWS - C3_LAG, 7 * C3_LAG
+    dX, dy = C.c_void_p(), C.c_void_p()
+    _lib.check(L.emrf_dev_alloc(c.h, n * F * 8, C.byref(dX)))
+    _lib.check(L.emrf_dev_alloc(c.h, n * 8, C.byref(dy)))
+    mine = [b for b in range(7) if b % world == rank]
+
+    def fit_all():
+        models = []
+        for b in mine:
+            _lib.check(L.emrf_build_lag_features(c.h, draws.ctypes.data, C3_DRAWS, C3_LAG, b, dX, dy))
+            rf = (RandomForestClassifier(c).setNumTrees(C3_TREES).setMaxDepth(C3_DEPTH).setMaxBins(MAX_BINS)
+                  .setNumClasses(50 if b < 5 else 12).setSeed(SEED + b))
+            models.append(rf.fit(Dataset(dX.value, dy.value, num_partitions=C3_PARTS, n_rows=n, n_features=F)))
+        return models
+
+    fit_all()
+    barrier()
+    t0 = time.perf_counter()
+    models = fit_all()
+    ms = allreduce_max([(time.perf_counter() - t0) * 1e3])[0]
+    barrier()
+    out = {"workload": f"BASELINE.json configs[3]: 7 per-ball models x {C3_TREES} trees, depth {C3_DEPTH}, {n} rows x {F} lag features "
+                       f"({C3_DRAWS} draws, {C3_LAG}-draw window), ball b on GPU b % {world}",
+           "n_gpus": world, "ms_all_models": round(ms, 2), "models_per_sec": 7 / (ms / 1e3),
+           "rows_trees_per_sec": 7 * n * C3_TREES / (ms / 1e3)}
+    if rank == 0:
+        from oracle import binding as ob
+        Xh, yh, Cn = synth.draw_history(C3_DRAWS, C3_LAG, mine[0])
+        o = ob.fit(ob.make_params(num_trees=C3_TREES, max_depth=C3_DEPTH, max_bins=MAX_BINS, num_classes=Cn, seed=SEED + mine[0]),
+                   Xh, yh, ob.partition_offsets(len(Xh), C3_PARTS)).export()
+        out["parity_vs_oracle_first_model"] = bool(forests_equal(models[0].export(), o)[0])
+        out["nodes_first_model"] = int(models[0].totalNumNodes)
+    del models
+    L.emrf_dev_free(c.h, dX)
+    L.emrf_dev_free(c.h, dy)
+    if world > 1:
+        c.close()
+    return out
+
+
 def run_predict(ctx, world, rank, barrier, allreduce_max, estimator):
-    """Batch prediction, BASELINE configs[4] shape: a 500-tree depth-12 forest over 128 features; every rank walks its own
-    rows (rows are independent: no collective).  The forest is fitted on 200k rows (what bounds predict is the number of
-    nodes visited, not how the forest was made); C4_ROWS_RESIDENT rows per rank generated in HBM, labels back on the host."""
+    """Batch prediction, BASELINE configs[4]: 100M rows x 128 features through a 500-tree depth-12 forest; every rank takes
+    100M / N rows (rows are independent: no collective) in chunks of 10M generated in HBM (a chunk's f64 features are
+    10 GB), labels copied to the host.  The forest is fitted on 200k rows (what bounds predict is the number of node
+    visits and leaf records read, not how the forest was made).  Timed: the predict calls only, not the generator."""
     from euromillioner_b200 import synth
     from euromillioner_b200.classifier import Context, Dataset
     c = Context(ctx.device) if world > 1 else ctx      # predict needs no communicator
@@ -508,21 +570,30 @@ def run_predict(ctx, world, rank, barrier, allreduce_max, estimator):
     m = estimator(c, C2_TREES, C2_DEPTH).fit(Dataset(gfit.X.value, gfit.y.value, num_partitions=64, n_rows=200_000,
                                                      n_features=C2_FEATURES))
     gfit.free()
-    n = C4_ROWS_RESIDENT
-    g = synth.DeviceFlat(c, n, C2_FEATURES, N_CLASSES, row_start=rank * n)
-    ds = Dataset(g.X.value, None, n_rows=n, n_features=C2_FEATURES)
-    m.transform(ds, raw=False, probability=False)   # warm-up (forest upload, buffers)
+    rows_rank = C4_ROWS_TOTAL // world
+    ms_local, done, first = 0.0, 0, True
+    while done < rows_rank:
+        n = min(C4_ROWS_CHUNK, rows_rank - done)
+        g = synth.DeviceFlat(c, n, C2_FEATURES, N_CLASSES, row_start=rank * rows_rank + done)
+        ds = Dataset(g.X.value, None, n_rows=n, n_features=C2_FEATURES)
+        if first:
+            m.transform(ds, raw=False, probability=False)   # warm-up (forest upload, buffers)
+            barrier()
+            first = False
+        t0 = time.perf_counter()
+        m.transform(ds, raw=False, probability=False)
+        ms_local += (time.perf_counter() - t0) * 1e3
+        g.free()
+        done += n
+    ms = allreduce_max([ms_local])[0]
     barrier()
-    t0 = time.perf_counter()
-    m.transform(ds, raw=False, probability=False)
-    ms = allreduce_max([(time.perf_counter() - t0) * 1e3])[0]
-    barrier()
-    g.free()
-    out = {"workload": f"BASELINE.json configs[4] shape: {C2_TREES}-tree depth-{C2_DEPTH} forest ({int(m.totalNumNodes)} nodes, fitted on "
-                       f"200000 rows), {n} rows x {C2_FEATURES} features per GPU resident in HBM, predicted labels copied to the host",
-           "n_gpus": world, "ms": round(ms, 2), "rows_per_sec": n * world / (ms / 1e3),
-           "tree_walks_per_sec": n * world * C2_TREES / (ms / 1e3),
-           "input_gbs": n * world * C2_FEATURES * 8 / (ms / 1e3) / 1e9}
+    total = rows_rank * world
+    out = {"workload": f"BASELINE.json configs[4]: {total} rows x {C2_FEATURES} features through a {C2_TREES}-tree depth-{C2_DEPTH} forest "
+                       f"({int(m.totalNumNodes)} nodes, fitted on 200000 rows); {rows_rank} rows per GPU in resident chunks of "
+                       f"{C4_ROWS_CHUNK}, predicted labels copied to the host",
+           "n_gpus": world, "ms": round(ms, 2), "rows_per_sec": total / (ms / 1e3),
+           "tree_walks_per_sec": total * C2_TREES / (ms / 1e3),
+           "input_gbs": total * C2_FEATURES * 8 / (ms / 1e3) / 1e9}
     if world > 1:
         c.close()
     return out

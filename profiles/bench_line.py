@@ -18,6 +18,7 @@ print("phases", {k: round(v, 2) for k, v in d["phases_ms_per_step"].items()})
 for k in ("parity_vs_oracle", "parity_vs_1gpu", "forest_digest_same_on_all_ranks", "comm_bytes_per_step"):
     if k in d:
         print(k, d[k])
-for k in ("configs2", "predict"):
+print("ms_each_step", d.get("ms_each_step"))
+for k in ("configs2", "configs3", "predict"):
     if k in d:
         print(k, json.dumps(d[k]))

@@ -782,8 +782,7 @@ static cudaError_t hist_launch(int ch, dim3 grid, size_t smem, cudaStream_t st, 
 #define EMRF_HIST_CASE(n) \
   case n: return u16 ? hist_launch_t<n, uint16_t>(grid, smem, st, A, prepare_only) : hist_launch_t<n, uint32_t>(grid, smem, st, A, prepare_only);
   switch (ch) {
-    EMRF_HIST_CASE(1) EMRF_HIST_CASE(2) EMRF_HIST_CASE(3) EMRF_HIST_CASE(4)
-    EMRF_HIST_CASE(5) EMRF_HIST_CASE(6) EMRF_HIST_CASE(7) EMRF_HIST_CASE(8)
+    EMRF_HIST_CASE(2) EMRF_HIST_CASE(4) EMRF_HIST_CASE(8)   // row_pitch(): 32 / 64 / 128 bytes, or wider rows (generic path, 0)
     default: return u16 ? hist_launch_t<0, uint16_t>(grid, smem, st, A, prepare_only) : hist_launch_t<0, uint32_t>(grid, smem, st, A, prepare_only);
   }
 #undef EMRF_HIST_CASE

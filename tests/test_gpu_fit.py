@@ -67,7 +67,7 @@ def test_cfg4_other_balls(ctx, oracle, ball):
     (40000, 64, 30, 7, 32, {"maxMemoryInMB": 2}),                 # tiny groups: the memory check redraws the RNG
     (3000, 10, 40, 12, 3, {"feature_subset": "onethird"}),        # deep, small: pure children, many leaves
     (25000, 16, 5, 6, 4, {"maxBins": 100, "feature_subset": "0.5"}),
-    (12000, 100, 4, 6, 6, {}),                                    # Fp = 112: 7 row chunks (irregular tile stride)
+    (12000, 100, 4, 6, 6, {}),                                    # 100 features: rows padded to 128 bytes
     (9000, 150, 3, 5, 4, {}),                                     # rows wider than 128 B: generic byte-gather path
     (5000, 3, 4, 5, 1, {"maxBins": 2}),                           # one split per feature, one partition
     (4000, 1, 3, 4, 7, {}),                                       # a single feature

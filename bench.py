@@ -228,8 +228,6 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from euromillioner_b200.dist import make_context
-        # the box's cores are shared by the ranks: say so instead of letting every rank spawn one thread per core
-        os.environ.setdefault("EMRF_HOST_THREADS", str(max(1, host_threads() // world)))
         ctx = make_context(dist)
     else:
         ctx = Context(local_rank)

@@ -364,8 +364,9 @@ extern "C" int emrf_ctx_create_dist(int32_t device, int32_t rank, int32_t world,
   if (rc != EMRF_OK) { delete c; return rc; }
   c->rank = rank;
   c->world = world;
-  // launchers such as torchrun export OMP_NUM_THREADS=1; size the host pool explicitly instead
-  c->host_threads = std::max(1, c->host_threads / std::max(1, world));
+  // launchers such as torchrun export OMP_NUM_THREADS=1; size the host pool explicitly instead: this node's cores shared
+  // by the ranks (EMRF_HOST_THREADS, when set, is already the per-rank count)
+  if (!getenv("EMRF_HOST_THREADS")) c->host_threads = std::max(1, c->host_threads / std::max(1, world));
   if (world > 1) {
     if (!nccl_uid) { delete c; return fail(EMRF_ERR_ARG, "nccl_uid is NULL"); }
     void* lib = nccl_open();

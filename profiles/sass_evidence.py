@@ -40,7 +40,7 @@ for f in funcs[1:]:
         strip = lambda l: re.sub(r'\s*/\* 0x[0-9a-f]+ \*/\s*$', '', l).rstrip()
         idx = [i for i, l in enumerate(lines) if 'UTMALDG' in l]
         if idx:
-            a, b = max(0, idx[-1] - 22), min(len(lines), idx[-1] + 4)
+            a, b = max(0, idx[0] - 24), min(len(lines), idx[0] + 3)
             out += ["## The gather loop of `hist_scan_kernel<4, uint32_t>` (rows of 64 bytes), verbatim", "", "```"] + [strip(l) for l in lines[a:b]] + ["```"]
         idx = [i for i, l in enumerate(lines) if 'SYNCS.PHASECHK' in l]
         if idx:

@@ -59,77 +59,95 @@ __global__ void labels_kernel(const double* __restrict__ y, int64_t n, int n_cla
 // consecutive elements of the row-major input), bins staged in shared memory, then written twice
 // with 128-bit stores: row-major rows and column-major 128-row runs.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool java_less(double a, double b) {
-  // Double.compare(a,b) < 0 for non-NaN a (thresholds are never NaN); NaN b sorts above all.
-  if (a < b) return true;
-  if (a > b) return false;
-  if (b != b) return true;
-  return (__double_as_longlong(a) < 0) && (__double_as_longlong(b) >= 0);  // -0.0 < 0.0
-}
-__device__ __forceinline__ int find_bin_dev(const double* thr, int n, double x) {
-  int lo = 0, hi = n;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (java_less(thr[mid], x)) lo = mid + 1; else hi = mid;
-  }
-  return lo;
-}
-// Predict-time variant: bin = #thresholds numerically below x (NaN above all), so that
-// bin(x) <= s  <=>  x <= thr[s]  — ContinuousSplit.shouldGoLeft on raw features.
-__device__ __forceinline__ int find_bin_numeric(const double* thr, int n, double x) {
-  if (x != x) return n;
-  int lo = 0, hi = n;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (thr[mid] < x) lo = mid + 1; else hi = mid;
-  }
-  return lo;
-}
 constexpr int kBinRows = 128;
 // stride (in doubles) of a feature's thresholds in shared memory: odd, so that the lanes of a warp — consecutive
 // FEATURES, all at the same step of their binary searches — read different banks (an even stride such as 32
 // puts every feature's k-th threshold in the same bank: a 32-way conflict on every search step)
 __host__ __device__ inline int bin_thr_smem_stride(int thr_stride) { return thr_stride | 1; }
 __host__ __device__ inline size_t bin_tile_bytes(int Fp) { return ((size_t)kBinRows * (Fp + 4) + 15) & ~(size_t)15; }
+// Order-preserving 64-bit key of a double: unsigned comparison of keys == java.lang.Double.compare for non-NaN values
+// (-0.0 below +0.0).  The numeric variant (predict: plain `<`) first folds -0.0 into +0.0.
+template <bool kNumeric>
+__device__ __forceinline__ unsigned long long bin_key(double v) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  if (kNumeric && b == 0x8000000000000000ull) b = 0ull;
+  return b ^ ((unsigned long long)((long long)b >> 63) | 0x8000000000000000ull);
+}
 template <bool kThrInSmem, bool kNumeric = false>
 __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, int64_t n_rows, int F, int Fp,
                                                   int64_t Np, const double* __restrict__ thr,
                                                   const int* __restrict__ n_splits, int thr_stride,
                                                   uint8_t* __restrict__ bins_rm, uint8_t* __restrict__ bins_cm) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  // layout: tile[kBinRows][Fp + 4] bytes | (optional) thresholds
+  // layout: tile[kBinRows][Fp + 4] bytes | (optional) threshold KEYS, one table of `sstride` 64-bit keys per feature
   uint8_t* tile = smem_raw;
-  const double* sthr = thr;
-  int sstride = thr_stride;
+  unsigned long long* skey = reinterpret_cast<unsigned long long*>(smem_raw + bin_tile_bytes(Fp));
+  const int sstride = bin_thr_smem_stride(thr_stride);
   if (kThrInSmem) {
-    double* st = reinterpret_cast<double*>(smem_raw + bin_tile_bytes(Fp));
-    sstride = bin_thr_smem_stride(thr_stride);
     for (int i = threadIdx.x; i < F * thr_stride; i += blockDim.x) {
       const int f = i / thr_stride, k = i - f * thr_stride;
-      st[f * sstride + k] = thr[i];
+      skey[f * sstride + k] = bin_key<kNumeric>(thr[i]);
     }
-    sthr = st;
   }
+  // number of thresholds ordered before x = the bin: a branch-free lower bound over the feature's sorted keys, `steps`
+  // halvings for every value (steps = bits needed for the largest table), positions past the feature's own count masked
+  int steps = 0;
+  while ((1 << steps) < thr_stride) steps++;          // n_splits[f] <= thr_stride - 1 < 2^steps
+  auto find_bin = [&](int f, int n, double x) -> int {
+    if (x != x) return n;                              // NaN sorts above every threshold
+    const unsigned long long xk = bin_key<kNumeric>(x);
+    int pos = 0;
+    for (int st = steps - 1; st >= 0; st--) {
+      const int j = pos + (1 << st);                   // candidate count: thresholds 0 .. j-1 all below x?
+      const int jj = min(j, max(n, 1)) - 1;
+      const unsigned long long k = kThrInSmem ? skey[f * sstride + jj] : bin_key<kNumeric>(thr[(size_t)f * thr_stride + jj]);
+      if (j <= n && k < xk) pos = j;
+    }
+    return pos;
+  };
   // tile rows are Fp + 4 bytes apart (an odd number of words): the word-wise copy to bins_rm and the column
   // reads for bins_cm below are then free of bank conflicts
   const int RW = (Fp >> 2) + 1;                          // row stride in words
   uint32_t* tile_w = reinterpret_cast<uint32_t*>(tile);
+  for (int i = threadIdx.x; i < kBinRows * RW; i += blockDim.x) tile_w[i] = 0;   // once: the padding bytes stay zero
   // a CTA walks tiles of 128 rows with the grid's stride: the thresholds are staged once per CTA, not per tile
   const int64_t n_tiles = (n_rows + kBinRows - 1) / kBinRows;
+  const bool vec2 = ((reinterpret_cast<uintptr_t>(X) & 15) == 0) && ((F & 1) == 0);   // two values per 128-bit load
   for (int64_t tile_idx = blockIdx.x; tile_idx < n_tiles; tile_idx += gridDim.x) {
   const int64_t row0 = tile_idx * kBinRows;
   const int rows = (int)min((int64_t)kBinRows, n_rows - row0);
-  __syncthreads();                                       // the previous tile has been written out
-  for (int i = threadIdx.x; i < kBinRows * RW; i += blockDim.x) tile_w[i] = 0;
-  __syncthreads();
+  __syncthreads();                                       // the previous tile has been written out (and the keys are staged)
   const int64_t base = row0 * F;
   const int total = rows * F;
+  if (vec2) {
+    // eight 128-bit loads in flight per thread; a pair never straddles a row (F is even)
+    const double2* X2 = reinterpret_cast<const double2*>(X + base);
+    const int pairs = total >> 1;
+    constexpr int U = 8;
+    for (int p0 = threadIdx.x; p0 < pairs; p0 += U * 256) {
+      double2 v[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int p = p0 + u * 256;
+        v[u] = p < pairs ? __ldcs(X2 + p) : make_double2(0.0, 0.0);
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int p = p0 + u * 256;
+        if (p < pairs) {
+          const int e = 2 * p;
+          const int r = e / F, f = e - r * F;
+          const int b0 = find_bin(f, n_splits[f], v[u].x), b1 = find_bin(f + 1, n_splits[f + 1], v[u].y);
+          *reinterpret_cast<uint16_t*>(tile + r * (RW << 2) + f) = (uint16_t)(b0 | (b1 << 8));
+        }
+      }
+    }
+  } else {
 #pragma unroll 4
-  for (int e = threadIdx.x; e < total; e += blockDim.x) {
-    const int r = e / F, f = e - r * F;
-    const double x = X[base + e];
-    tile[r * (RW << 2) + f] = (uint8_t)(kNumeric ? find_bin_numeric(sthr + (size_t)f * sstride, n_splits[f], x)
-                                                 : find_bin_dev(sthr + (size_t)f * sstride, n_splits[f], x));
+    for (int e = threadIdx.x; e < total; e += blockDim.x) {
+      const int r = e / F, f = e - r * F;
+      tile[r * (RW << 2) + f] = (uint8_t)find_bin(f, n_splits[f], X[base + e]);
+    }
   }
   __syncthreads();
   if (bins_rm) {  // rows of the tile are contiguous in bins_rm: coalesced word copy

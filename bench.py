@@ -228,6 +228,10 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from euromillioner_b200.dist import make_context
+        # every context of this process (the communicator's and the plain ones of the parity / configs blocks) gets this
+        # rank's share of the host cores: ranks that wait in a barrier spin on theirs, and an OpenMP team wider than its
+        # share then loses its barriers to them (measured: a 1.8 s fit took 38 s)
+        os.environ.setdefault("EMRF_HOST_THREADS", str(max(1, host_threads() // world)))
         ctx = make_context(dist)
     else:
         ctx = Context(local_rank)

@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
   // number of thresholds ordered before x = the bin: a branch-free lower bound over the feature's sorted keys, `steps`
   // halvings for every value (steps = bits needed for the largest table), positions past the feature's own count masked
   int steps = 0;
-  while ((1 << steps) < thr_stride) steps++;          // n_splits[f] <= thr_stride - 1 < 2^steps
+  while ((1 << steps) <= thr_stride) steps++;         // n_splits[f] <= thr_stride < 2^steps
   auto find_bin = [&](int f, int n, double x) -> int {
     if (x != x) return n;                              // NaN sorts above every threshold
     const unsigned long long xk = bin_key<kNumeric>(x);

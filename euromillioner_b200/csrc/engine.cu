@@ -1241,9 +1241,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   int bag_maxw = 255;
   std::vector<uint64_t> tree_base(T + 1, 0), tree_total(T, 0);
   {
+    // on the bagging stream, right behind the weights: with host-resident features (or a sharded findSplits) the
+    // lists are ready before the last rows are binned; the main stream joins below
+    cudaStream_t sl = c->stream2;
     int maxw = 0;
-    CU(cudaStreamWaitEvent(st, ev_b1, 0));
-    TRY(bag_finish(c, st, P, bag_job, &maxw));
+    TRY(bag_finish(c, sl, P, bag_job, &maxw));
     bag_maxw = maxw;
     const int n_tiles = (int)((N + kern::kListTile - 1) / kern::kListTile);
     DevBuf& d_counts = c->p_counts;
@@ -1256,30 +1258,34 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     int slab_rows = (int)std::min<int64_t>(512, (48 * 1024 / T) / 32 * 32);
     if (env_flag("EMRF_LIST_SIMPLE")) slab_rows = 0;
     if (slab_rows >= 32) {
-      kern::list_count_tiled_kernel<<<n_tiles, 256, (size_t)slab_rows * T, st>>>(d_w.as<uint8_t>(), N, T, slab_rows, d_counts.as<uint32_t>());
-      kern::list_scan_warp_kernel<<<(T * 32 + 127) / 128, 128, 0, st>>>(d_counts.as<uint32_t>(), n_tiles, T, d_totals.as<uint64_t>());
+      kern::list_count_tiled_kernel<<<n_tiles, 256, (size_t)slab_rows * T, sl>>>(d_w.as<uint8_t>(), N, T, slab_rows, d_counts.as<uint32_t>());
+      kern::list_scan_warp_kernel<<<(T * 32 + 127) / 128, 128, 0, sl>>>(d_counts.as<uint32_t>(), n_tiles, T, d_totals.as<uint64_t>());
     } else {
-      kern::list_count_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), N, T, d_counts.as<uint32_t>());
-      kern::list_scan_kernel<<<(T + 127) / 128, 128, 0, st>>>(d_counts.as<uint32_t>(), n_tiles, T, d_totals.as<uint64_t>());
+      kern::list_count_kernel<<<n_tiles, bt, 0, sl>>>(d_w.as<uint8_t>(), N, T, d_counts.as<uint32_t>());
+      kern::list_scan_kernel<<<(T + 127) / 128, 128, 0, sl>>>(d_counts.as<uint32_t>(), n_tiles, T, d_totals.as<uint64_t>());
     }
     tm.kernel_launches += 2;
-    CU(cudaMemcpyAsync(tree_total.data(), d_totals.p, (size_t)T * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(cudaMemcpyAsync(tree_total.data(), d_totals.p, (size_t)T * 8, cudaMemcpyDeviceToHost, sl));
+    CU(cudaStreamSynchronize(sl));
     for (int t = 0; t < T; t++) tree_base[t + 1] = tree_base[t] + tree_total[t];
     CU(d_ent[0]->ensure((size_t)tree_base[T] * 8));
     CU(d_ent[1]->ensure((size_t)tree_base[T] * 8));
-    CU(cudaMemcpyAsync(d_base.p, tree_base.data(), (size_t)T * 8, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(d_base.p, tree_base.data(), (size_t)T * 8, cudaMemcpyHostToDevice, sl));
     if (slab_rows >= 32)
-      kern::list_fill_tiled_kernel<<<n_tiles, 256, (size_t)slab_rows * T, st>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, slab_rows,
+      kern::list_fill_tiled_kernel<<<n_tiles, 256, (size_t)slab_rows * T, sl>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, slab_rows,
                                                                               d_counts.as<uint32_t>(), d_base.as<uint64_t>(),
                                                                               d_ent[0]->as<uint64_t>());
     else
-      kern::list_fill_kernel<<<n_tiles, bt, 0, st>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, d_counts.as<uint32_t>(),
+      kern::list_fill_kernel<<<n_tiles, bt, 0, sl>>>(d_w.as<uint8_t>(), d_labels.as<uint8_t>(), N, T, d_counts.as<uint32_t>(),
                                                      d_base.as<uint64_t>(), d_ent[0]->as<uint64_t>());
     tm.kernel_launches += 1;
     CU(cudaGetLastError());
+    cudaEvent_t ev_lists = c->events.get();
+    CU(cudaEventRecord(ev_lists, sl));
+    CU(cudaStreamWaitEvent(st, ev_lists, 0));
     CU(cudaEventRecord(ev_bag, st));
-    CU(cudaStreamSynchronize(st));  // the small tables die here; d_w stays in the ctx pool
+    CU(cudaStreamSynchronize(sl));  // the small tables die here; d_w stays in the ctx pool
+    CU(cudaStreamSynchronize(st));
     parked.clear();
   }
 
@@ -2130,6 +2136,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   for (auto& pr : hist_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.hist_kernel_ms += ms; }
   for (auto& pr : part_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.partition_ms += ms; }
   for (auto& pr : comm_ev) { CU(cudaEventElapsedTime(&ms, pr.first, pr.second)); tm.comm_ms += ms; }
+  if (env_flag("EMRF_DEBUG_TIMERS") && copied) {
+    fprintf(stderr, "[emrf] feature chunks landed at ms:");
+    for (const XChunk& xc : x_chunks) { CU(cudaEventElapsedTime(&ms, ev_start, xc.ev)); fprintf(stderr, " %.2f", ms); }
+    fprintf(stderr, "\n");
+  }
   if (env_flag("EMRF_DEBUG_TIMERS")) {
     // GPU timeline of the group loop: hist end -> (decide) -> partition start, partition end -> next hist start
     double gap_dec = 0, gap_next = 0, first_to_last = 0;

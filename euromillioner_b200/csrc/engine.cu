@@ -1312,7 +1312,10 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     if (div > 0) cm_min_len = (uint32_t)std::max<int64_t>(N / div, 1024);
   }
   if (allow_u16) CU(hist_launch(row_ch, dim3(1), hist_smem16, st, kern::HistArgs(), true, true));
-  if (row_sharded) CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
+  if (row_sharded) {
+    CU(cudaFuncSetAttribute(kern::scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
+    CU(cudaFuncSetAttribute(kern::scan_owned_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_bytes));
+  }
   const size_t slot_words = (size_t)f_sub * B * C;
   // L2 blocking of the row gathers (shapes whose row-major TreePoint matrix does not fit L2, e.g. configs[2]);
   // opt-in (EMRF_L2_BLOCK=1): measured on 10M x 128, depth 12, 50 trees it shortens the histogram kernel by
@@ -1343,6 +1346,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       push_mode = true;
     }
   }
+  // rows sharded over NCCL: light nodes cross the links as packed 16-bit counters (EMRF_NO_RS_PACK=1: all 32-bit)
+  const bool rs_pack_ok = row_sharded && c->world > 1 && !push_mode && (B * C) % 2 == 0 && !env_flag("EMRF_NO_RS_PACK");
 
   // ---- trees, stack, driver RNG (RandomForest.run)
   // node pools live in the context: a fit reuses the (already faulted-in) memory of the previous one
@@ -1373,7 +1378,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     r.tree = t; r.pool = 0; r.id = 1; r.level = 0;
     r.slot = (uint32_t)t;
     r.ub = (uint32_t)tree_total[t];
-    r.weight = (uint32_t)std::min<uint64_t>(tree_total[t] * (uint64_t)std::max(bag_maxw, 1), 0xffffffffull);   // upper bound
+    // upper bound; rows sharded: the local count says nothing about the other ranks' rows (and the packed transport
+    // must class a node the same way on every rank), so roots count as heavy
+    r.weight = row_sharded ? 0xffffffffu : (uint32_t)std::min<uint64_t>(tree_total[t] * (uint64_t)std::max(bag_maxw, 1), 0xffffffffull);
     stack.push_back(r);
   }
   const int64_t max_mem = (int64_t)P.max_memory_mb * 1024ll * 1024ll;
@@ -1495,6 +1502,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   std::vector<int> pool_next(T, 0);
   PodVec<uint32_t> nt_tmp, tb_tmp, push_off;   // per-group scratch of the staging and push passes
   PodVec<int32_t> slot_tmp;
+  std::vector<uint32_t> own_nodes;             // rows sharded, packed transport: the group nodes this rank scans
   std::vector<int> run_order;
   bool tickets_zeroed = false, ghist_zeroed = false;   // per fit: another entry point may have used the buffers
   // Node statistics of a processed group (impurities, gain, split, class-count pointers, predictions): nothing in
@@ -1608,7 +1616,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const size_t off_tiles = align_up(off_info + (size_t)n_nodes * 4, 16);
     {
       const size_t tiles_bound = (size_t)n_nodes + (size_t)(total_entries / tile_len) + 1;
-      const size_t bound = align_up(off_tiles + tiles_bound * 4, 16) + tiles_bound * 4;
+      const size_t bound = align_up(off_tiles + tiles_bound * 4, 16) + tiles_bound * 4 + 16 + (size_t)n_nodes * 4;
       CU(c->h_group.ensure(bound));
       CU(c->d_group.ensure(bound));
     }
@@ -1643,6 +1651,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     // [world][npr] — the reduce-scatter of piece p runs on the communication stream under the histogram kernel of piece
     // p + 1.  Piece q: nodes [pc_n0[q], pc_n0[q+1]), tiles [pc_t0[q], pc_t0[q+1]), slots from pc_s0[q], npr = pc_npr[q].
     constexpr int kMaxPieces = 8;
+    bool pack_slots = false;
+    int pack_share = 0;
     int n_pieces = 1;
     int pc_n0[kMaxPieces + 1], pc_npr[kMaxPieces], pc_s0[kMaxPieces + 1];
     uint32_t pc_t0[kMaxPieces + 1];
@@ -1654,6 +1664,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         static const int want = [] { const char* e = getenv("EMRF_RS_PIECES"); return e ? std::min(8, std::max(1, atoi(e))) : 1; }();
         n_pieces = std::max(1, std::min(want, n_nodes / 128));      // small groups: one piece
       }
+      // one piece: nodes whose weight over all ranks is <= 65535 travel as packed 16-bit counters, half the bytes;
+      // each rank's share of the buffer is [its heavy nodes, whole slots][its light nodes, half slots]
+      pack_slots = all_slots && n_pieces == 1 && rs_pack_ok;
       pc_s0[0] = 0;
       for (int q = 0; q <= n_pieces; q++) pc_n0[q] = (int)((int64_t)n_nodes * q / n_pieces);
       for (int q = 0; q < n_pieces; q++) {
@@ -1677,6 +1690,22 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         }
       }
       if (all_slots) n_slots = pc_s0[n_pieces];
+      if (pack_slots) {
+        int n_light = 0;
+        for (int i = 0; i < n_nodes; i++) n_light += (group[i].weight <= 65535u);
+        const int n_heavy = n_nodes - n_light;
+        const int npr_h = (n_heavy + c->world - 1) / c->world, npr_l = (n_light + c->world - 1) / c->world;
+        pack_share = 2 * npr_h + npr_l;                     // half slots per rank
+        own_nodes.clear();
+        int h = 0, l = 0;
+        for (int i = 0; i < n_nodes; i++) {
+          int r;
+          if (group[i].weight <= 65535u) { r = l / npr_l; slp[i] = r * pack_share + 2 * npr_h + l % npr_l; l++; }
+          else { r = h / npr_h; slp[i] = r * pack_share + 2 * (h % npr_h); h++; }
+          if (r == c->rank) own_nodes.push_back((uint32_t)i);
+        }
+        n_slots = (pack_share * c->world + 1) / 2;
+      }
       uint32_t cls_off[3 * kMaxPieces];
       for (int q = 0; q < 3 * n_pieces; q++) {
         cls_off[q] = n_tiles;
@@ -1691,18 +1720,26 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       }
     }
     const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
-    const size_t group_bytes = l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4;
+    const size_t off_own = align_up(l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4, 16);
+    const size_t group_bytes = pack_slots ? off_own + own_nodes.size() * 4
+                                          : (l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4);
+    if (pack_slots && !own_nodes.empty()) memcpy((char*)c->h_group.p + off_own, own_nodes.data(), own_nodes.size() * 4);
     {
       uint32_t* tn = (uint32_t*)((char*)c->h_group.p + off_tiles);
+      const uint32_t light_mark = pack_slots ? kern::kNodePacked : 0u;
       if (!l2_blocked) {
 #pragma omp parallel for num_threads(nt_host) schedule(static)
         for (int i = 0; i < n_nodes; i++) {
           gn[i].tile_begin = tb_tmp[i];
           gn[i].slot = slot_tmp[i];
+          if (group[i].weight <= 65535u) gn[i].buf = light_mark;
           for (uint32_t q = 0; q < gn[i].n_tiles; q++) tn[tb_tmp[i] + q] = (uint32_t)i;
         }
       } else {
-        for (int i = 0; i < n_nodes; i++) { gn[i].tile_begin = tb_tmp[i]; gn[i].slot = slot_tmp[i]; }
+        for (int i = 0; i < n_nodes; i++) {
+          gn[i].tile_begin = tb_tmp[i]; gn[i].slot = slot_tmp[i];
+          if (group[i].weight <= 65535u) gn[i].buf = light_mark;
+        }
         // entries of a node are in ascending row order, so tile q of a node with n tiles covers about the
         // q/n-th part of the rows: emit range by range, every node's tiles of that range together
         uint32_t* tq = (uint32_t*)((char*)c->h_group.p + off_tq);
@@ -1802,6 +1839,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.impurity = P.impurity; A.min_instances = P.min_instances_per_node; A.hist_only = row_sharded ? 1 : 0;
     A.push_world = push_mode ? c->world : 0; A.push_rank = c->rank; A.push_npr = nodes_per_rank;
     for (int r = 0; r < 8; r++) A.peer_stage[r] = (uint32_t*)c->peer_stage[r];
+    A.slot_half = pack_slots ? 1 : 0;
     A.min_info_gain = P.min_info_gain;
     A.bins_cm = d_cm.as<uint8_t>(); A.Np = Np; A.cm_min_len = cm_min_len;
     A.results = (kern::ScanResult*)c->d_results.p;
@@ -1845,6 +1883,23 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         const int npr = pc_npr[q], size_q = pc_n0[q + 1] - pc_n0[q];
         if (size_q == 0) continue;
         uint32_t* piece_hist = c->d_ghist.as<uint32_t>() + (size_t)pc_s0[q] * slot_words;
+        if (pack_slots) {
+          const size_t share_words = (size_t)pack_share * (slot_words / 2);
+          {
+            const cudaEvent_t c0 = comm_begin(sc);
+            TRY(nccl_reduce_scatter_u32(c, piece_hist, share_words, sc));
+            comm_end(c0, (int64_t)c->world * (int64_t)share_words * 4, sc);
+          }
+          if (!own_nodes.empty()) {
+            kern::scan_owned_kernel<<<dim3((unsigned)own_nodes.size(), n_chunks), kern::kHistThreads, hist_bytes, sc>>>(
+                piece_hist, A.nodes, (const uint32_t*)((char*)c->d_group.p + off_own), A.node_feat, A.num_bins_all, f_sub, B, C,
+                k_chunk, n_chunks, P.impurity, P.min_instances_per_node, P.min_info_gain, A.results, A.left_counts,
+                A.total_counts);
+            tm.kernel_launches++;
+            CU(cudaGetLastError());
+          }
+          continue;
+        }
         {
           const cudaEvent_t c0 = comm_begin(sc);
           TRY(nccl_reduce_scatter_u32(c, piece_hist, (size_t)npr * slot_words, sc));

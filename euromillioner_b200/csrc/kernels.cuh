@@ -817,6 +817,7 @@ struct GroupNode {
   uint32_t buf;
   uint32_t seg_slot;    // index into HistArgs.segtab
 };
+constexpr uint32_t kNodePacked = 2u;   // GroupNode.buf bit: the node's histogram slot holds packed 16-bit counters
 struct ScanResult {
   double gain;
   double impurity;        // parent (node) impurity
@@ -873,6 +874,10 @@ struct HistArgs {
   uint32_t node_base;          // first node of this launch: result records are indexed relative to it
   uint32_t hist_smem_off;      // byte offset of the histogram inside dynamic shared memory (the staging region comes first)
   int32_t impurity, min_instances, hist_only;
+  // rows sharded, histograms bound for a reduce-scatter: slot_half != 0 makes GroupNode.slot count HALF slots
+  // (f_sub*B*C/2 words) and nodes marked kNodePacked flush two 16-bit counters per word (exact under a 32-bit
+  // integer sum as long as the node's weight summed over all ranks is <= 65535: no carry leaves the low half)
+  int32_t slot_half;
   // row-sharded push mode: partial histograms go straight into the owner rank's staging buffer over NVLink
   int32_t push_world, push_rank, push_npr;   // push_world == 0: off
   uint32_t* peer_stage[8];                   // [owner]: base of that rank's staging buffer (peer-mapped)
@@ -1319,6 +1324,8 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
   for (int i = tid; i < (kc * B * C * (int)sizeof(HT) + 3) / 4; i += kHistThreads) shw[i] = 0;
   HPROF(1);
   GroupNode nd = A.nodes[g];
+  const bool packed_slot = (nd.buf & kNodePacked) != 0;
+  nd.buf &= 1u;
   for (int k = tid; k < kc; k += kHistThreads) {
     const int f = A.node_feat[(size_t)g * A.f_sub + k0 + k];
     sh_feat[k] = f;
@@ -1619,6 +1626,25 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
     return;
   }
   }
+  if constexpr (!U16) {
+    if (A.slot_half) {      // hist_only: slots in half units, light nodes packed (the engine packs only with B*C even)
+      const size_t half = slot_words >> 1;
+      if (packed_slot) {
+        uint32_t* gh = A.ghist + (size_t)nd.slot * half + (((size_t)k0 * B * C) >> 1);
+        for (int i = tid; i < (kc * B * C) >> 1; i += kHistThreads) {
+          const uint32_t v = sh[2 * i] | (sh[2 * i + 1] << 16);
+          if (v) atomicAdd(&gh[i], v);
+        }
+      } else {
+        uint32_t* gh = A.ghist + (size_t)nd.slot * half + (size_t)k0 * B * C;
+        for (int i = tid; i < kc * B * C; i += kHistThreads) {
+          const uint32_t v = sh[i];
+          if (v) atomicAdd(&gh[i], v);
+        }
+      }
+      return;
+    }
+  }
   if (nd.slot >= 0) {
     // multi-tile node: the tile's counters (16- or 32-bit) are added to the node's 32-bit slot in HBM
     uint32_t* gh = A.ghist + (size_t)nd.slot * slot_words + (size_t)k0 * B * C;
@@ -1691,6 +1717,44 @@ __global__ void __launch_bounds__(kHistThreads) scan_kernel(const uint32_t* __re
   for (int k = tid; k < kc; k += kHistThreads) sh_nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
   const uint32_t* gh = hist + ((size_t)g * f_sub + k0) * B * C;
   for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = gh[i];
+  __syncthreads();
+  const size_t rec = (size_t)g * n_chunks + chunk;
+  scan_chunk<uint32_t>(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,
+                       total_counts + rec * C);
+}
+
+// The same for the nodes a rank owns after the reduce-scatter of a packed group (HistArgs.slot_half layout): block x
+// scans group node own[x]; a packed slot is unpacked into the 32-bit block on the way in.  Records are indexed by the
+// node's position in the group.
+__global__ void __launch_bounds__(kHistThreads) scan_owned_kernel(const uint32_t* __restrict__ ghist, const GroupNode* __restrict__ nodes,
+                                                                 const uint32_t* __restrict__ own, const int32_t* node_feat,
+                                                                 const int32_t* num_bins_all, int f_sub, int B, int C,
+                                                                 int k_chunk, int n_chunks, int impurity, int min_instances,
+                                                                 double min_info_gain, ScanResult* results,
+                                                                 uint32_t* left_counts, uint32_t* total_counts) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const int tid = threadIdx.x;
+  const uint32_t g = own[blockIdx.x];
+  const int chunk = blockIdx.y;
+  const int k0 = chunk * k_chunk;
+  const int kc = min(k_chunk, f_sub - k0);
+  const ScanSmem<uint32_t> S = carve_smem<uint32_t>(smem_raw, smem_raw + hist_block_bytes(k_chunk, B, C), k_chunk, B, C);
+  uint32_t* sh = S.hist;
+  int* sh_nb = S.nb;
+  for (int k = tid; k < kc; k += kHistThreads) sh_nb[k] = num_bins_all[node_feat[(size_t)g * f_sub + k0 + k]];
+  const GroupNode nd = nodes[g];
+  const size_t half = ((size_t)f_sub * B * C) >> 1;
+  if (nd.buf & kNodePacked) {
+    const uint32_t* gh = ghist + (size_t)nd.slot * half + (((size_t)k0 * B * C) >> 1);
+    for (int i = tid; i < (kc * B * C) >> 1; i += kHistThreads) {
+      const uint32_t v = gh[i];
+      sh[2 * i] = v & 0xffffu;
+      sh[2 * i + 1] = v >> 16;
+    }
+  } else {
+    const uint32_t* gh = ghist + (size_t)nd.slot * half + (size_t)k0 * B * C;
+    for (int i = tid; i < kc * B * C; i += kHistThreads) sh[i] = gh[i];
+  }
   __syncthreads();
   const size_t rec = (size_t)g * n_chunks + chunk;
   scan_chunk<uint32_t>(S, kc, k0, B, C, impurity, min_instances, min_info_gain, &results[rec], left_counts + rec * C,

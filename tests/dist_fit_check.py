@@ -33,9 +33,10 @@ P = 32
 goff = np.array([(i * len(X)) // P for i in range(P + 1)], np.int64)
 p_lo, p_hi = (rank * P) // world, ((rank + 1) * P) // world
 r_lo, r_hi = int(goff[p_lo]), int(goff[p_hi])
-for kw in ({}, {"n": 9000}):            # second case: N <= 10000 → findSplits keeps every row
-    n = kw.get("n", len(X))
-    Xs, ys = X[:n], y[:n]
+Xb, yb = synth.flat(200000, 16, 50)    # third case: nodes above and below 65535 rows in one group (packed 16-bit transport)
+for kw in ({}, {"n": 9000}, {"big": True}):            # second case: N <= 10000 → findSplits keeps every row
+    n = len(Xb) if kw.get("big") else kw.get("n", len(X))
+    Xs, ys = (Xb, yb) if kw.get("big") else (X[:n], y[:n])
     goff = np.array([(i * n) // P for i in range(P + 1)], np.int64)
     r_lo, r_hi = int(goff[p_lo]), int(goff[p_hi])
     rf2 = RandomForestClassifier(ctx).setNumTrees(7).setMaxDepth(7).setNumClasses(50).setMaxMemoryInMB(16)

@@ -68,11 +68,12 @@ def test_tree_and_row_sharded_fits_match_oracle_on_2_gpus():
     cuda.cuDeviceGetCount(ctypes.byref(n))
     if n.value < 2:
         pytest.skip("needs 2 GPUs")
-    for push in ("0", "1"):   # NCCL reduce-scatter path, then the fused NVLink-push path
-        env = dict(os.environ, EMRF_PEER_PUSH=push)
+    # NCCL reduce-scatter path (light nodes packed to 16 bits), the same all 32-bit, then the fused NVLink-push path
+    for push, no_pack in (("0", "0"), ("0", "1"), ("1", "0")):
+        env = dict(os.environ, EMRF_PEER_PUSH=push, EMRF_NO_RS_PACK=no_pack)
         r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
                             "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "dist_fit_check.py")],
                            capture_output=True, text=True, timeout=600, env=env)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
         assert "DIST_FIT_OK world=2" in r.stdout
-        assert r.stdout.count("DIST_ROWS_OK world=2") == 2
+        assert r.stdout.count("DIST_ROWS_OK world=2") == 3

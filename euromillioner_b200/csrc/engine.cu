@@ -260,6 +260,7 @@ struct emrf_ctx {
   // grow-only scratch reused across groups
   DevBuf d_group, d_results, d_ghist, d_tickets;
   PinnedBuf h_group, h_part, h_seeds, h_table, h_tsum, h_sample, h_sched, h_seg;
+  size_t last_nodes_split = 0, last_trace_len = 0;   // sizes the previous fit ended with (reserve hints)
   PinnedBuf h_export;   // world > 4: this rank's trees, exported, on their way to the other ranks
   DevBuf d_export;
   DevBuf d_split, d_part;   // partition work of the current group (written by decide_kernel)
@@ -1453,6 +1454,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     CU(cudaStreamSynchronize(st));
   }
   std::vector<uint32_t> hist_slots;   // slot of every node this rank built a histogram for (exact stats at the end)
+  hist_slots.reserve(c->last_nodes_split + 1024);   // sized like the previous fit's: no regrowth inside the group loop
   PodVec<StackEnt> stack;
   stack.reserve(1024);
   for (int t = 0; t < T; t++) {
@@ -1472,6 +1474,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   emrf_forest* fo = new emrf_forest();
   std::unique_ptr<emrf_forest> fo_guard(fo);
   fo->num_trees = T; fo->num_classes = C; fo->num_features = F; fo->f_sub = f_sub;
+  fo->trace.reserve(c->last_trace_len + 4096);
+  fo->group_sizes.reserve(256);
 
   // A group as selectNodesToSplit leaves it: popped nodes in pop order, their feature subsets, the
   // trees in first-seen order (= mutable.HashMap insertion order) and each tree's nodes.
@@ -1935,6 +1939,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       A.node_info = (const uint32_t*)((char*)c->d_group.p + off_info);
       A.out_dec = (uint32_t*)((char*)c->d_results.p + res_dec);
       A.out_sched = (uint4*)((char*)c->d_part.p + off_sched);
+      // ... and the host's copy of the scheduling records is written by the kernel itself (zero-copy): the host then
+      // waits for the kernel's own event instead of a copy on the second stream behind it
+      CU(c->h_sched.ensure((size_t)n_nodes * 16));
+      void* hs_dev = nullptr;
+      CU(cudaHostGetDevicePointer(&hs_dev, c->h_sched.p, 0));
+      A.out_sched_host = (uint4*)hs_dev;
       A.out_ptiles = (uint32_t*)((char*)c->d_part.p + off_ptiles);
       A.max_depth = P.max_depth;
     }
@@ -2056,7 +2066,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     cudaEvent_t ev_dec = c->events.get(), sched_done = c->events.get(), rec_done = c->events.get();
     CU(cudaEventRecord(ev_dec, st));
     CU(cudaStreamWaitEvent(c->stream2, ev_dec, 0));
-    CU(cudaMemcpyAsync(c->h_sched.p, d_sched, (size_t)n_nodes * 16, cudaMemcpyDeviceToHost, c->stream2));
+    if (!fuse_decide) CU(cudaMemcpyAsync(c->h_sched.p, d_sched, (size_t)n_nodes * 16, cudaMemcpyDeviceToHost, c->stream2));
     CU(cudaEventRecord(sched_done, c->stream2));
     CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, c->stream2));
     CU(cudaEventRecord(rec_done, c->stream2));
@@ -2126,7 +2136,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     // ---- host side of findBestSplits, the part the next group waits for: the scheduling records say what
     // became of every node; numbering repeats decide_scan_kernel's (group order); children get identity, segment
     // slot and size bounds.  Everything else about the nodes is filled in later (fill_stats).
-    CU(cudaEventSynchronize(sched_done));
+    CU(cudaEventSynchronize(fuse_decide ? ev_dec : sched_done));
     t_host0 = now_ms();
     lap(3);
     const uint4* sched = (const uint4*)c->h_sched.p;
@@ -2239,6 +2249,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   }
 
   TRY(fill_stats(pending));   // the last group's
+  c->last_nodes_split = hist_slots.size();
+  c->last_trace_len = fo->trace.size();
   if (env_flag("EMRF_DEBUG_TIMERS"))
     fprintf(stderr, "[emrf] host phases ms: prep %.2f | launch %.2f | bookkeeping %.2f | wait %.2f | numbering %.2f | nodes %.2f | "
             "stack %.2f | select %.2f | other %.2f\n", ph[0], ph[1], ph[2], ph[3], ph[5], ph[8], ph[9], ph[10], ph[11]);

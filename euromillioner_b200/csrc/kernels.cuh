@@ -891,6 +891,7 @@ struct HistArgs {
   const uint32_t* node_info;                 // nullptr: not fused
   uint32_t* out_dec;
   uint4* out_sched;
+  uint4* out_sched_host;                     // the same records straight into page-locked host memory (nullptr: none)
   uint32_t* out_ptiles;
   int32_t max_depth;
   // TMA row staging (rows of 16/32/64/128 bytes): 2-D tensor map over THIS GPU's bins_rm [Np][Fp], box {Fp, 1},
@@ -1694,6 +1695,7 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
       const uint32_t fs = (dec & kDecNonLeaf) ? ((uint32_t)A.node_feat[(size_t)g * A.f_sub + r.k] | ((uint32_t)r.split << 24)) : 0u;
       A.out_dec[g] = dec;
       A.out_sched[g] = make_uint4(dec, r.left_weight, r.total_weight, fs);
+      if (A.out_sched_host) A.out_sched_host[g] = make_uint4(dec, r.left_weight, r.total_weight, fs);
       A.out_ptiles[g] = (dec & kDecSplit) ? max(1u, (nd.seg_len + kPartTile - 1) / kPartTile) : 0u;   // >= 1: the node's last tile writes the children's segments
     }
   }

@@ -1429,6 +1429,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       push_mode = true;
     }
   }
+  // rows sharded over NCCL: the device tiles every group from the exact segment lengths (tile_map_kernel), the host only
+  // provisions the launches from bounds — no stream synchronisation per group to read the children's sizes back
+  // (EMRF_RS_HOST_SIZES=1: the host reads them and tiles, as on one GPU)
+  static const int rs_pieces_want = [] { const char* e = getenv("EMRF_RS_PIECES"); return e ? std::min(8, std::max(1, atoi(e))) : 1; }();
+  const bool dev_tiles = row_sharded && c->world > 1 && !push_mode && !l2_blocked && rs_pieces_want == 1 && !env_flag("EMRF_RS_HOST_SIZES");
+  std::vector<uint64_t> tree_acc(dev_tiles ? T : 0, 0);
   // rows sharded over NCCL: light nodes cross the links as packed 16-bit counters (EMRF_NO_RS_PACK=1: all 32-bit)
   const bool rs_pack_ok = row_sharded && c->world > 1 && !push_mode && (B * C) % 2 == 0 && !env_flag("EMRF_NO_RS_PACK");
 
@@ -1679,9 +1685,14 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     // ---- tiles (tree-sharded multi-GPU: own trees only); sizes are upper bounds
     uint64_t total_entries = cur->total_ub;   // entry bounds of this rank's nodes, summed; the heaviest of them
     uint32_t max_weight = cur->max_w;
-    if (row_sharded) {   // the bounds were replaced by exact sizes after the group was selected
+    if (row_sharded) {   // the bounds were replaced by exact sizes after the group was selected ...
       total_entries = 0;
-      for (const GroupEntry& g : group) total_entries += g.ub;
+      if (dev_tiles) {   // ... or not: the nodes of a tree are disjoint, so they hold at most the tree's entries together
+        for (const GroupEntry& g : group) tree_acc[g.tree] += g.ub;
+        for (int t : cur->trees_seen) { total_entries += std::min<uint64_t>(tree_acc[t], tree_total[t]); tree_acc[t] = 0; }
+      } else {
+        for (const GroupEntry& g : group) total_entries += g.ub;
+      }
     }
     uint32_t tile_len = (uint32_t)align_up((size_t)((total_entries + (uint64_t)c->sm_count * 16 - 1) / ((uint64_t)c->sm_count * 16)), 256);
     // 16-bit launch with multi-tile nodes: a tile's counters cannot pass 65535 if its entries' weights cannot, i.e. if
@@ -1702,7 +1713,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     const size_t off_tiles = align_up(off_info + (size_t)n_nodes * 4, 16);
     {
       const size_t tiles_bound = (size_t)n_nodes + (size_t)(total_entries / tile_len) + 1;
-      const size_t bound = align_up(off_tiles + tiles_bound * 4, 16) + tiles_bound * 4 + 16 + (size_t)n_nodes * 4;
+      const size_t bound = align_up(off_tiles + tiles_bound * 4, 16) + tiles_bound * 4 + 16 + (size_t)n_nodes * 4 + 32;
       CU(c->h_group.ensure(bound));
       CU(c->d_group.ensure(bound));
     }
@@ -1722,11 +1733,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         d.seg_len = 0;
         d.buf = 0;
         d.seg_slot = hn.slot;
-        d.n_tiles = m ? std::max<uint32_t>(1, (hn.ub + tile_len - 1) / tile_len) : 0;
+        d.n_tiles = dev_tiles ? 1u : (m ? std::max<uint32_t>(1, (hn.ub + tile_len - 1) / tile_len) : 0);   // dev_tiles: set on the device
         nt_tmp[i] = d.n_tiles;
         const int level = hn.level;
         info[i] = (uint32_t)level | (m ? kern::kInfoMine : 0u);
-        if (m && level < P.max_depth) ptiles_ub64 += std::max<uint32_t>(1, (hn.ub + kern::kPartTile - 1) / kern::kPartTile);
+        if (m && level < P.max_depth && !dev_tiles) ptiles_ub64 += std::max<uint32_t>(1, (hn.ub + kern::kPartTile - 1) / kern::kPartTile);
         memcpy(feat_out + (size_t)i * f_sub, group_feat.data() + group[i].feat_at, (size_t)f_sub * 4);
       }
     }
@@ -1747,8 +1758,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       if (all_slots) {
         // default 1: measured on 2 B200s, 2 / 4 / 8 pieces make the fit SLOWER (40.0 -> 41.5 / 43.9 / 49.8 ms): the collective
         // and the histogram kernel compete for the same HBM and SMs, and shorter launches fill the GPU worse
-        static const int want = [] { const char* e = getenv("EMRF_RS_PIECES"); return e ? std::min(8, std::max(1, atoi(e))) : 1; }();
-        n_pieces = std::max(1, std::min(want, n_nodes / 128));      // small groups: one piece
+        n_pieces = std::max(1, std::min(rs_pieces_want, n_nodes / 128));      // small groups: one piece
       }
       // one piece: nodes whose weight over all ranks is <= 65535 travel as packed 16-bit counters, half the bytes;
       // each rank's share of the buffer is [its heavy nodes, whole slots][its light nodes, half slots]
@@ -1804,6 +1814,11 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         tbp[i] = cls_off[cls];
         cls_off[cls] += ntp[i];
       }
+    }
+    if (dev_tiles) {   // grids from the bounds: sum of ceil(len / tile) <= sum(len) / tile + nodes
+      n_tiles = (uint32_t)(total_entries / tile_len) + (uint32_t)n_nodes;
+      pc_t0[n_pieces] = n_tiles;
+      ptiles_ub64 = total_entries / kern::kPartTile + (uint64_t)n_nodes;
     }
     const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
     const size_t off_own = align_up(l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4, 16);
@@ -1914,6 +1929,14 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     A.tickets = c->d_tickets.as<uint32_t>();
     A.Fp = Fp; A.f_sub = f_sub; A.B = B; A.C = C; A.k_chunk = k_chunk; A.n_chunks = n_chunks;
     A.tile_len = tile_len;
+    if (dev_tiles) {
+      uint32_t* d_tile_limit = (uint32_t*)((char*)c->d_group.p + align_up(group_bytes, 16));
+      kern::tile_map_kernel<<<1, 1024, 0, st>>>((kern::GroupNode*)c->d_group.p, c->p_segtab.as<kern::Seg>(), n_nodes, tile_len,
+                                               (uint32_t*)((char*)c->d_group.p + off_tiles), d_tile_limit, n_tiles);
+      tm.kernel_launches++;
+      CU(cudaGetLastError());
+      A.tile_limit = d_tile_limit;
+    }
     // every node in one tile and light enough: 16-bit counters, more CTAs per SM
     const bool u16 = u16_mixed || (allow_u16 && n_slots == 0 && max_weight <= 65535u);
     if (env_flag("EMRF_DEBUG_GROUPS"))
@@ -2157,7 +2180,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     for (int t : cur->trees_seen) trees[t].pool.resize_uninit((size_t)pool_next[t]);
     lap(5);
     // rows sharded: the weight bound is global (world times too loose), so read the exact sizes back
-    if (row_sharded && ns) {
+    if (row_sharded && ns && !dev_tiles) {
       CU(c->h_part.ensure((size_t)ns * 8));
       CU(cudaMemcpyAsync(c->h_part.p, d_nleft, (size_t)ns * 8, cudaMemcpyDeviceToHost, st));
       tm.d2h_bytes += (int64_t)ns * 8;
@@ -2210,7 +2233,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
         pos_r = (int)at;
         stack[at++] = ch;
       }
-      if (row_sharded && (u.dec & kern::kDecSplit)) child_pos[u.split_idx] = ChildPos{pos_l, pos_r, par.ub};
+      if (row_sharded && !dev_tiles && (u.dec & kern::kDecSplit)) child_pos[u.split_idx] = ChildPos{pos_l, pos_r, par.ub};
     }
     for (int t : cur->trees_seen) tree_slot[t] = -1;
     const size_t stack_before_select = stack.size();
@@ -2228,7 +2251,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     }
     TRY(select_rc);
     lap(10);
-    if (ns && row_sharded) {
+    if (ns && row_sharded && !dev_tiles) {
       CU(cudaStreamSynchronize(st));
       t_host0 = now_ms();
       // exact sizes of the children just created: they are either still on the stack or already in the next group

@@ -871,6 +871,7 @@ struct HistArgs {
   int32_t Fp, f_sub, B, C, k_chunk, n_chunks;
   uint32_t tile_len;
   uint32_t tile_base;          // first tile of this launch (a group may be launched in pieces)
+  const uint32_t* tile_limit;  // grid provisioned from an upper bound: tiles from *tile_limit on do not exist (nullptr: exact grid)
   uint32_t node_base;          // first node of this launch: result records are indexed relative to it
   uint32_t hist_smem_off;      // byte offset of the histogram inside dynamic shared memory (the staging region comes first)
   int32_t impurity, min_instances, hist_only;
@@ -1321,6 +1322,7 @@ __global__ void __launch_bounds__(kHistThreads, sizeof(HT) == 2 ? 4 : 3) hist_sc
   // the node's descriptors are three dependent loads deep (tile -> node -> segment / features -> bins per feature); the
   // histogram is cleared while the first of them is in flight
   const uint32_t tile_abs = blockIdx.x + A.tile_base;
+  if (A.tile_limit && tile_abs >= *A.tile_limit) return;
   const uint32_t g = A.tile_node[tile_abs];
   for (int i = tid; i < (kc * B * C * (int)sizeof(HT) + 3) / 4; i += kHistThreads) shw[i] = 0;
   HPROF(1);
@@ -2072,6 +2074,81 @@ __global__ void __launch_bounds__(kPartThreads, 8) part_onepass_kernel(const uin
       segtab[nd.right_slot] = r;
     }
   }
+}
+
+// Rows sharded: the host knows a node's LOCAL entry count only as a loose bound (its exact value would cost a
+// stream synchronisation per group), the device knows it exactly (segment table).  One CTA tiles the group's nodes
+// from the exact lengths — every node gets at least one tile, as the host would give it — and writes the tile map
+// and the tile count the histogram launch (provisioned from the bound) stops at.
+__global__ void __launch_bounds__(1024) tile_map_kernel(GroupNode* __restrict__ nodes, const Seg* __restrict__ segtab, int n_nodes,
+                                                        uint32_t tile_len, uint32_t* __restrict__ tile_node,
+                                                        uint32_t* __restrict__ tile_limit, uint32_t tile_cap) {
+  // tile order = launch order, as the host builds it: the tiles of multi-tile nodes first (full tiles, the longest CTAs),
+  // then the larger single-tile nodes, then the small ones
+  __shared__ uint32_t sh_t[3][32];
+  const int tid = threadIdx.x, lane = tid & 31, wv = tid >> 5;
+  const int per = (n_nodes + 1023) / 1024;
+  const int lo = min(tid * per, n_nodes), hi = min(lo + per, n_nodes);
+  auto node_tiles = [&](int gi, int& cls) {
+    const uint32_t len = segtab[nodes[gi].seg_slot].len;
+    const uint32_t tiles = max(1u, (len + tile_len - 1) / tile_len);
+    cls = tiles > 1 ? 0 : (len >= 2048 ? 1 : 2);
+    return tiles;
+  };
+  uint32_t t[3] = {0, 0, 0};
+  for (int gi = lo; gi < hi; gi++) {
+    int cls;
+    const uint32_t tiles = node_tiles(gi, cls);
+    t[cls] += tiles;
+  }
+  uint32_t it[3] = {t[0], t[1], t[2]};
+  for (int o = 1; o < 32; o <<= 1)
+#pragma unroll
+    for (int q = 0; q < 3; q++) {
+      const uint32_t x = __shfl_up_sync(0xffffffffu, it[q], o);
+      if (lane >= o) it[q] += x;
+    }
+  if (lane == 31)
+    for (int q = 0; q < 3; q++) sh_t[q][wv] = it[q];
+  __syncthreads();
+  if (wv == 0) {
+    uint32_t v[3] = {sh_t[0][lane], sh_t[1][lane], sh_t[2][lane]};
+    for (int o = 1; o < 32; o <<= 1)
+#pragma unroll
+      for (int q = 0; q < 3; q++) {
+        const uint32_t x = __shfl_up_sync(0xffffffffu, v[q], o);
+        if (lane >= o) v[q] += x;
+      }
+    for (int q = 0; q < 3; q++) sh_t[q][lane] = v[q];   // inclusive over warps
+  }
+  __syncthreads();
+  const uint32_t tot0 = sh_t[0][31], tot1 = sh_t[1][31], tot2 = sh_t[2][31];
+  uint32_t et[3];
+  for (int q = 0; q < 3; q++) et[q] = (wv ? sh_t[q][wv - 1] : 0u) + it[q] - t[q];
+  et[1] += tot0;
+  et[2] += tot0 + tot1;
+  if (tid == 0) *tile_limit = min(tot0 + tot1 + tot2, tile_cap);   // (the cap is a proven bound; min() only guards the tile map's allocation)
+  constexpr int kBigMax = 512;
+  __shared__ uint32_t sh_big[kBigMax][3];
+  __shared__ uint32_t sh_nbig;
+  if (tid == 0) sh_nbig = 0;
+  __syncthreads();
+  for (int gi = lo; gi < hi; gi++) {
+    int cls;
+    const uint32_t tiles = node_tiles(gi, cls);
+    const uint32_t at = et[cls];
+    nodes[gi].tile_begin = at;
+    nodes[gi].n_tiles = tiles;
+    uint32_t slot = kBigMax;
+    if (tiles > 8) slot = atomicAdd(&sh_nbig, 1u);
+    if (slot < (uint32_t)kBigMax) { sh_big[slot][0] = (uint32_t)gi; sh_big[slot][1] = at; sh_big[slot][2] = tiles; }
+    else for (uint32_t q = 0; q < tiles && at + q < tile_cap; q++) tile_node[at + q] = (uint32_t)gi;
+    et[cls] += tiles;
+  }
+  __syncthreads();
+  const uint32_t nbig = min(sh_nbig, (uint32_t)kBigMax);
+  for (uint32_t i = wv; i < nbig; i += 32)
+    for (uint32_t q = lane; q < sh_big[i][2] && sh_big[i][1] + q < tile_cap; q += 32) tile_node[sh_big[i][1] + q] = sh_big[i][0];
 }
 
 // ---------------------------------------------------------------------------------------------

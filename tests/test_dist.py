@@ -70,8 +70,9 @@ def test_tree_and_row_sharded_fits_match_oracle_on_2_gpus():
         pytest.skip("needs 2 GPUs")
     # NCCL reduce-scatter path (light nodes packed to 16 bits), the same all 32-bit, then the fused NVLink-push path
     # and once with every rank exporting only its share of the trees (the default above 4 ranks)
+    # (the second run also tiles the groups on the host from sizes read back, instead of on the device)
     for push, no_pack, shard in (("0", "0", "0"), ("0", "1", "1"), ("1", "0", "0")):
-        env = dict(os.environ, EMRF_PEER_PUSH=push, EMRF_NO_RS_PACK=no_pack, EMRF_EXPORT_SHARD=shard)
+        env = dict(os.environ, EMRF_PEER_PUSH=push, EMRF_NO_RS_PACK=no_pack, EMRF_EXPORT_SHARD=shard, EMRF_RS_HOST_SIZES=no_pack)
         r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
                             "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "dist_fit_check.py")],
                            capture_output=True, text=True, timeout=600, env=env)

@@ -2085,12 +2085,16 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     D.out_limits = d_limits;
     D.n_nodes = n_nodes; D.n_chunks = n_chunks; D.f_sub = f_sub; D.max_depth = P.max_depth;
     D.next_slot = next_slot;
-    if (!fuse_decide) kern::decide_flags_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(D);
-    cudaEvent_t ev_dec = c->events.get(), sched_done = c->events.get(), rec_done = c->events.get();
+    D.out_sched_host = nullptr;
+    if (!fuse_decide) {   // zero-copy scheduling records here too: the host waits for this kernel's event
+      void* hs_dev = nullptr;
+      CU(cudaHostGetDevicePointer(&hs_dev, c->h_sched.p, 0));
+      D.out_sched_host = (uint4*)hs_dev;
+      kern::decide_flags_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(D);
+    }
+    cudaEvent_t ev_dec = c->events.get(), rec_done = c->events.get();
     CU(cudaEventRecord(ev_dec, st));
     CU(cudaStreamWaitEvent(c->stream2, ev_dec, 0));
-    if (!fuse_decide) CU(cudaMemcpyAsync(c->h_sched.p, d_sched, (size_t)n_nodes * 16, cudaMemcpyDeviceToHost, c->stream2));
-    CU(cudaEventRecord(sched_done, c->stream2));
     CU(cudaMemcpyAsync(h_res, c->d_results.p, res_bytes, cudaMemcpyDeviceToHost, c->stream2));
     CU(cudaEventRecord(rec_done, c->stream2));
     tm.d2h_bytes += (int64_t)n_nodes * 16;
@@ -2159,7 +2163,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     // ---- host side of findBestSplits, the part the next group waits for: the scheduling records say what
     // became of every node; numbering repeats decide_scan_kernel's (group order); children get identity, segment
     // slot and size bounds.  Everything else about the nodes is filled in later (fill_stats).
-    CU(cudaEventSynchronize(fuse_decide ? ev_dec : sched_done));
+    CU(cudaEventSynchronize(ev_dec));
     t_host0 = now_ms();
     lap(3);
     const uint4* sched = (const uint4*)c->h_sched.p;

@@ -2171,6 +2171,7 @@ struct DecideArgs {
   uint32_t* out_dec;             // [n_nodes] best chunk | kDec* flags (travels with the records)
   uint4* out_sched;              // [n_nodes] {decision word, left weight, total weight, feature | split bin << 24}:
                                  //   all the host needs to number the children and select the next group
+  uint4* out_sched_host;         // the same records, stored straight into page-locked host memory (nullptr: none)
   uint32_t* out_tiles;           // [n_nodes] partition tiles of the node (0 unless kDecSplit)
   uint32_t* out_limits;          // [0] split nodes, [1] partition tiles
   int n_nodes, n_chunks, f_sub, max_depth;
@@ -2194,6 +2195,7 @@ __global__ void __launch_bounds__(256) decide_flags_kernel(const DecideArgs A) {
   const uint32_t tiles = (dec & kDecSplit) ? max(1u, (A.segtab[A.nodes[gi].seg_slot].len + kPartTile - 1) / kPartTile) : 0u;
   A.out_dec[gi] = dec;
   A.out_sched[gi] = make_uint4(dec, r.left_weight, r.total_weight, fs);
+  if (A.out_sched_host) A.out_sched_host[gi] = make_uint4(dec, r.left_weight, r.total_weight, fs);
   A.out_tiles[gi] = tiles;
 }
 // step 2, one CTA: numbering in group order and the partition work.  Every thread owns a contiguous run of

@@ -101,6 +101,7 @@ def lib():
     L.emrf_host_reservoir_sample.argtypes = [i32, i32, i64, vp]
     L.emrf_host_group_tree_order.argtypes = [vp, i32, vp]
     L.emrf_host_num_features_per_node.argtypes = [P(EmrfParams), i32]
+    L.emrf_host_packed_slot_layout.argtypes = [vp, i32, i32, vp, vp]
     _lib = L
     return L
 

@@ -1594,7 +1594,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   std::vector<int> pool_next(T, 0);
   PodVec<uint32_t> nt_tmp, tb_tmp, push_off;   // per-group scratch of the staging and push passes
   PodVec<int32_t> slot_tmp;
-  std::vector<uint32_t> own_nodes;             // rows sharded, packed transport: the group nodes this rank scans
+  std::vector<uint32_t> own_nodes, pack_w;     // rows sharded, packed transport: the group nodes this rank scans
+  std::vector<int> pack_owner;
   std::vector<int> run_order;
   bool tickets_zeroed = false, ghist_zeroed = false;   // per fit: another entry point may have used the buffers
   // Node statistics of a processed group (impurities, gain, split, class-count pointers, predictions): nothing in
@@ -1787,19 +1788,12 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       }
       if (all_slots) n_slots = pc_s0[n_pieces];
       if (pack_slots) {
-        int n_light = 0;
-        for (int i = 0; i < n_nodes; i++) n_light += (group[i].weight <= 65535u);
-        const int n_heavy = n_nodes - n_light;
-        const int npr_h = (n_heavy + c->world - 1) / c->world, npr_l = (n_light + c->world - 1) / c->world;
-        pack_share = 2 * npr_h + npr_l;                     // half slots per rank
+        pack_w.resize(n_nodes); pack_owner.resize(n_nodes);
+        for (int i = 0; i < n_nodes; i++) pack_w[i] = group[i].weight;
+        pack_share = hl::packed_slot_layout(pack_w.data(), n_nodes, c->world, slp, pack_owner.data());   // half slots per rank
         own_nodes.clear();
-        int h = 0, l = 0;
-        for (int i = 0; i < n_nodes; i++) {
-          int r;
-          if (group[i].weight <= 65535u) { r = l / npr_l; slp[i] = r * pack_share + 2 * npr_h + l % npr_l; l++; }
-          else { r = h / npr_h; slp[i] = r * pack_share + 2 * (h % npr_h); h++; }
-          if (r == c->rank) own_nodes.push_back((uint32_t)i);
-        }
+        for (int i = 0; i < n_nodes; i++)
+          if (pack_owner[i] == c->rank) own_nodes.push_back((uint32_t)i);
         n_slots = (pack_share * c->world + 1) / 2;
       }
       uint32_t cls_off[3 * kMaxPieces];
@@ -3148,6 +3142,11 @@ extern "C" int32_t emrf_host_group_tree_order(const int32_t* trees_first_seen, i
   std::vector<int> o = hl::group_tree_visit_order(in);
   for (size_t i = 0; i < o.size(); i++) out[i] = o[i];
   return (int32_t)o.size();
+}
+extern "C" int32_t emrf_host_packed_slot_layout(const uint32_t* weight, int32_t n, int32_t world, int32_t* slot_out,
+                                                int32_t* owner_out) {
+  if (!weight || !slot_out || !owner_out || n < 0 || world < 1) return -1;
+  return hl::packed_slot_layout(weight, n, world, slot_out, owner_out);
 }
 extern "C" int32_t emrf_host_num_features_per_node(const emrf_params_t* params, int32_t n_features) {
   return hl::features_per_node(*params, n_features);

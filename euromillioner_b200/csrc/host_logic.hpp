@@ -287,5 +287,26 @@ inline bool select_nodes_examines_next(int policy_flags, int64_t mem_usage, int6
 // POLICY: the pivot exp(-mean) of commons-math's PoissonDistribution.sample() (FastMath.exp there).
 inline double poisson_exp_policy(double mean) { return std::exp(-mean); }
 
+// Rows sharded over `world` ranks: where each node's partial histogram sits in the buffer that is reduce-scattered.
+// A node is LIGHT when its weight over all ranks is <= 65535 (its cells then fit 16 bits, two per 32-bit word) and takes
+// one half slot, a heavy node two.  Rank r receives the half slots [r*share, (r+1)*share): first its heavy nodes, then its
+// light ones; heavy node number h goes to rank h / ceil(heavy/world), light node l to rank l / ceil(light/world).
+// slot_out[i] = first half slot of node i, owner_out[i] = the rank that scans it; returns share.
+inline int packed_slot_layout(const uint32_t* weight, int n, int world, int* slot_out, int* owner_out) {
+  int n_light = 0;
+  for (int i = 0; i < n; i++) n_light += (weight[i] <= 65535u);
+  const int n_heavy = n - n_light;
+  const int npr_h = (n_heavy + world - 1) / world, npr_l = (n_light + world - 1) / world;
+  const int share = 2 * npr_h + npr_l;
+  int h = 0, l = 0;
+  for (int i = 0; i < n; i++) {
+    int r;
+    if (weight[i] <= 65535u) { r = l / npr_l; slot_out[i] = r * share + 2 * npr_h + l % npr_l; l++; }
+    else { r = h / npr_h; slot_out[i] = r * share + 2 * (h % npr_h); h++; }
+    owner_out[i] = r;
+  }
+  return share;
+}
+
 }  // namespace hostlogic
 }  // namespace emrf

@@ -244,6 +244,9 @@ double emrf_host_xorshift_next_double(int64_t seed, int32_t nth);             /*
 int32_t emrf_host_reservoir_sample(int32_t n_items, int32_t k, int64_t seed, int32_t* out); /* SamplingUtils */
 int32_t emrf_host_group_tree_order(const int32_t* trees_first_seen, int32_t n, int32_t* out); /* Scala map order */
 int32_t emrf_host_num_features_per_node(const emrf_params_t* params, int32_t n_features);
+/* rows sharded: half-slot position and owner rank of every node of a group in the reduce-scattered histogram buffer
+ * (nodes of weight <= 65535 take one half slot and travel as packed 16-bit counters); returns half slots per rank */
+int32_t emrf_host_packed_slot_layout(const uint32_t* weight, int32_t n, int32_t world, int32_t* slot_out, int32_t* owner_out);
 
 #ifdef __cplusplus
 }

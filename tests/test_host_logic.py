@@ -144,3 +144,30 @@ def test_forest_import_rejects_corrupted_descriptions():
     for d in bad:
         assert _import_forest(**d) == -1, d
         assert b"forest description" in _lib().emrf_last_error()
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_packed_slot_layout_of_the_reduce_scattered_histograms(world):
+    """Every rank's share is one contiguous run of half slots, heavy nodes take two and light nodes one, nothing overlaps,
+    and a node is owned by the rank whose share holds it (what ncclReduceScatter hands that rank)."""
+    L = _lib()
+    rng = np.random.default_rng(world)
+    for n in (1, 2, 7, 100, 2542):
+        for p_light in (0.0, 0.5, 0.93, 1.0):
+            w = np.where(rng.random(n) < p_light, rng.integers(1, 65536, n), rng.integers(65536, 2**32, n)).astype(np.uint32)
+            slot, owner = np.zeros(n, np.int32), np.zeros(n, np.int32)
+            share = L.emrf_host_packed_slot_layout(w.ctypes.data, n, world, slot.ctypes.data, owner.ctypes.data)
+            size = np.where(w <= 65535, 1, 2)
+            assert share >= 1 and np.all(slot >= 0) and np.all(slot + size <= share * world)
+            assert np.array_equal(owner, slot // share) and np.array_equal(owner, (slot + size - 1) // share)
+            used = np.zeros(share * world, np.int32)
+            for s_, z in zip(slot, size):
+                used[s_:s_ + z] += 1
+            assert used.max() == 1                                    # no two nodes share a half slot
+            assert np.all(slot[w > 65535] % 2 == (share % 2) * (owner[w > 65535] % 2))   # whole slots stay word-aligned
+            # light nodes sit behind the heavy ones of the same rank
+            for r in range(world):
+                hv, lt = slot[(owner == r) & (w > 65535)], slot[(owner == r) & (w <= 65535)]
+                if len(hv) and len(lt):
+                    assert hv.max() + 2 <= lt.min()
+            assert np.bincount(owner, minlength=world).max() <= -(-np.sum(w > 65535) // world) + -(-np.sum(w <= 65535) // world)

@@ -706,20 +706,38 @@ static int run_find_splits(emrf_ctx* c, const emrf_params_t& P, const double* dX
   return EMRF_OK;
 }
 
-static int run_bin(emrf_ctx* c, const double* dX, int64_t N, int F, const double* d_thr, const int* d_ns, int TS, int Fp,
-                   int64_t Np, uint8_t* d_rm, uint8_t* d_cm) {
+// bin_kernel with the thresholds in shared memory, instantiated for the key table's row length
+template <bool kNumeric, int KROW>
+static int bin_launch_smem_t(unsigned grid, size_t smem, cudaStream_t st, const double* dX, int64_t N, int F, int Fp, int64_t Np,
+                             const double* d_thr, const int* d_ns, int TS, int max_n, uint8_t* d_rm, uint8_t* d_cm) {
+  if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<true, kNumeric, KROW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern::bin_kernel<true, kNumeric, KROW><<<grid, 256, smem, st>>>(dX, N, F, Fp, Np, d_thr, d_ns, TS, max_n, d_rm, d_cm);
+  return EMRF_OK;
+}
+template <bool kNumeric>
+static int bin_launch_smem(int krow, unsigned grid, size_t smem, cudaStream_t st, const double* dX, int64_t N, int F, int Fp, int64_t Np,
+                           const double* d_thr, const int* d_ns, int TS, int max_n, uint8_t* d_rm, uint8_t* d_cm) {
+  switch (krow) {
+    case 16: return bin_launch_smem_t<kNumeric, 16>(grid, smem, st, dX, N, F, Fp, Np, d_thr, d_ns, TS, max_n, d_rm, d_cm);
+    case 32: return bin_launch_smem_t<kNumeric, 32>(grid, smem, st, dX, N, F, Fp, Np, d_thr, d_ns, TS, max_n, d_rm, d_cm);
+    case 64: return bin_launch_smem_t<kNumeric, 64>(grid, smem, st, dX, N, F, Fp, Np, d_thr, d_ns, TS, max_n, d_rm, d_cm);
+    case 128: return bin_launch_smem_t<kNumeric, 128>(grid, smem, st, dX, N, F, Fp, Np, d_thr, d_ns, TS, max_n, d_rm, d_cm);
+    default: return bin_launch_smem_t<kNumeric, 0>(grid, smem, st, dX, N, F, Fp, Np, d_thr, d_ns, TS, max_n, d_rm, d_cm);
+  }
+}
+static int run_bin(emrf_ctx* c, const double* dX, int64_t N, int F, const double* d_thr, const int* d_ns, int TS, int max_n, int Fp,
+                   int64_t Np, uint8_t* d_rm, uint8_t* d_cm) {   // max_n: upper bound on the features' split counts (<= TS)
   const size_t tile_bytes = kern::bin_tile_bytes(Fp);
-  const size_t thr_bytes = (size_t)F * kern::bin_thr_smem_stride(TS) * 8;
+  const size_t thr_bytes = kern::bin_thr_smem_bytes(F, max_n);
   // persistent CTAs: each stages the thresholds once and walks tiles with the grid's stride
   const unsigned grid = (unsigned)std::min<int64_t>((N + kern::kBinRows - 1) / kern::kBinRows, (int64_t)c->sm_count * 8);
   if (tile_bytes + thr_bytes <= 160 * 1024) {
     const size_t smem = tile_bytes + thr_bytes;
-    if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern::bin_kernel<true><<<grid, 256, smem, c->stream>>>(dX, N, F, Fp, Np, d_thr, d_ns, TS, d_rm, d_cm);
+    TRY((bin_launch_smem<false>(kern::bin_key_row(F), grid, smem, c->stream, dX, N, F, Fp, Np, d_thr, d_ns, TS, max_n, d_rm, d_cm)));
   } else {
     if (tile_bytes > 200 * 1024) return fail(EMRF_ERR_LIMIT, "too many features for the binning tile (%d)", F);
     if (tile_bytes > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes));
-    kern::bin_kernel<false><<<grid, 256, tile_bytes, c->stream>>>(dX, N, F, Fp, Np, d_thr, d_ns, TS, d_rm, d_cm);
+    kern::bin_kernel<false><<<grid, 256, tile_bytes, c->stream>>>(dX, N, F, Fp, Np, d_thr, d_ns, TS, max_n, d_rm, d_cm);
   }
   c->tm.kernel_launches += 1;
   CU(cudaGetLastError());
@@ -1265,12 +1283,13 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   DevBuf &d_rm = c->p_rm, &d_cm = c->p_cm;
   CU(d_rm.ensure_exact((size_t)Np * Fp));
   CU(d_cm.ensure_exact((size_t)F * Np));
+  if (env_flag("EMRF_DEBUG_TIMERS")) fprintf(stderr, "[emrf] binning: %d features, longest threshold table %d, table stride %d\n", F, B - 1, TS);
   if (x_chunks.empty()) {
-    TRY(run_bin(c, dX, N, F, d_thr.as<double>(), d_ns.as<int>(), TS, Fp, Np, d_rm.as<uint8_t>(), d_cm.as<uint8_t>()));
+    TRY(run_bin(c, dX, N, F, d_thr.as<double>(), d_ns.as<int>(), TS, B - 1, Fp, Np, d_rm.as<uint8_t>(), d_cm.as<uint8_t>()));
   } else {
     for (const XChunk& xc : x_chunks) {   // chunk starts are multiples of 128 rows (the binning tile)
       CU(cudaStreamWaitEvent(st, xc.ev, 0));
-      TRY(run_bin(c, dX + (size_t)xc.r0 * F, xc.rows, F, d_thr.as<double>(), d_ns.as<int>(), TS, Fp, Np,
+      TRY(run_bin(c, dX + (size_t)xc.r0 * F, xc.rows, F, d_thr.as<double>(), d_ns.as<int>(), TS, B - 1, Fp, Np,
                   d_rm.as<uint8_t>() + (size_t)xc.r0 * Fp, d_cm.as<uint8_t>() + xc.r0));
     }
   }
@@ -2819,17 +2838,16 @@ static int predict_impl(emrf_ctx_t* c, const emrf_forest_t* f_in, const double* 
     if (f->walk_ok && !force_f64_walk && walk_smem <= 200 * 1024) {
       // bin the chunk once (numeric compare against the forest's own threshold tables), then walk bins
       const size_t tile_bytes = kern::bin_tile_bytes(Fp);
-      const size_t thr_bytes = (size_t)F * kern::bin_thr_smem_stride(f->walk_ts) * 8;
+      const size_t thr_bytes = kern::bin_thr_smem_bytes(F, f->walk_ts);
       const unsigned bgrid = (unsigned)std::min<int64_t>((n + kern::kBinRows - 1) / kern::kBinRows, (int64_t)c->sm_count * 8);
       if (tile_bytes + thr_bytes <= 160 * 1024) {
         const size_t smem = tile_bytes + thr_bytes;
-        if (smem > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern::bin_kernel<true, true><<<bgrid, 256, smem, st>>>(x, n, F, Fp, 0, f->d_pthr.as<double>(), f->d_pns.as<int>(),
-                                                               f->walk_ts, dBins.as<uint8_t>(), nullptr);
+        TRY((bin_launch_smem<true>(kern::bin_key_row(F), bgrid, smem, st, x, n, F, Fp, 0, f->d_pthr.as<double>(), f->d_pns.as<int>(),
+                                   f->walk_ts, f->walk_ts, dBins.as<uint8_t>(), nullptr)));
       } else {
         if (tile_bytes > 48 * 1024) CU(cudaFuncSetAttribute(kern::bin_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_bytes));
         kern::bin_kernel<false, true><<<bgrid, 256, tile_bytes, st>>>(x, n, F, Fp, 0, f->d_pthr.as<double>(), f->d_pns.as<int>(),
-                                                                      f->walk_ts, dBins.as<uint8_t>(), nullptr);
+                                                                      f->walk_ts, f->walk_ts, dBins.as<uint8_t>(), nullptr);
       }
       static const bool dense_leaves = env_flag("EMRF_PREDICT_DENSE_LEAVES");   // the f64 probability records (A/B runs, parity test)
       if (f->leaf_count_bytes && !dense_leaves) {
@@ -2913,7 +2931,7 @@ extern "C" int emrf_bin(emrf_ctx_t* c, const double* features_hd, int64_t N, int
   const int64_t Np = (int64_t)align_up((size_t)N, 128);
   CU(d_rm.alloc((size_t)Np * Fp));
   CU(d_cm.alloc((size_t)F * Np));
-  TRY(run_bin(c, (const double*)dX, N, F, d_thr.as<double>(), d_ns.as<int>(), thr_stride, Fp, Np, d_rm.as<uint8_t>(),
+  TRY(run_bin(c, (const double*)dX, N, F, d_thr.as<double>(), d_ns.as<int>(), thr_stride, thr_stride, Fp, Np, d_rm.as<uint8_t>(),
               d_cm.as<uint8_t>()));
   if (bins_rm_out)
     CU(cudaMemcpy2DAsync(bins_rm_out, (size_t)F, d_rm.p, (size_t)Fp, (size_t)F, (size_t)N, cudaMemcpyDeviceToHost, c->stream));

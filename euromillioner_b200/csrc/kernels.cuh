@@ -13,6 +13,7 @@
 // contraction can change a gain (the JVM does not fuse).
 #pragma once
 #include <cuda.h>           // CUtensorMap (type only: the encoder is looked up at run time, nothing links libcuda)
+#include <type_traits>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -60,10 +61,20 @@ __global__ void labels_kernel(const double* __restrict__ y, int64_t n, int n_cla
 // with 128-bit stores: row-major rows and column-major 128-row runs.
 // ---------------------------------------------------------------------------------------------
 constexpr int kBinRows = 128;
-// stride (in doubles) of a feature's thresholds in shared memory: odd, so that the lanes of a warp — consecutive
-// FEATURES, all at the same step of their binary searches — read different banks (an even stride such as 32
-// puts every feature's k-th threshold in the same bank: a 32-way conflict on every search step)
-__host__ __device__ inline int bin_thr_smem_stride(int thr_stride) { return thr_stride | 1; }
+// Threshold keys in shared memory: [threshold index][column], the row padded to 16 keys, where feature f sits in column
+// (f >> 1) + (f & 1) * ceil(F / 2).  The lanes of a warp hold consecutive PAIRS of features (128-bit loads) and are each at
+// their own step of their own search: with the threshold index major and the feature minor, the bank of a lookup depends
+// on the lane's feature only — 32 lanes, 32 consecutive columns, the two wavefronts a 64-bit access needs and no more
+// (one table per feature with an odd stride, as before, spreads a warp over random banks: ~4 wavefronts per lookup).
+// The table has 2^steps - 1 rows, steps = the halvings a lower bound over the longest table needs; rows past a feature's
+// own count hold the largest key, so the search needs neither a bounds test nor the count.
+__host__ __device__ inline int bin_key_row(int F) {   // 16 / 32 / 64 / 128 columns up to 128 features: compile-time strides (KROW)
+  return F <= 16 ? 16 : F <= 32 ? 32 : F <= 64 ? 64 : F <= 128 ? 128 : ((F + 15) & ~15);
+}
+__host__ __device__ inline int bin_search_steps(int max_n) { int s = 1; while ((1 << s) - 1 < max_n) s++; return s; }
+__host__ __device__ inline size_t bin_thr_smem_bytes(int F, int max_n) {
+  return (size_t)((1 << bin_search_steps(max_n)) - 1) * bin_key_row(F) * 8 + (size_t)((F + 3) & ~3) * 4;
+}
 __host__ __device__ inline size_t bin_tile_bytes(int Fp) { return ((size_t)kBinRows * (Fp + 4) + 15) & ~(size_t)15; }
 // Order-preserving 64-bit key of a double: unsigned comparison of keys == java.lang.Double.compare for non-NaN values
 // (-0.0 below +0.0).  The numeric variant (predict: plain `<`) first folds -0.0 into +0.0.
@@ -73,35 +84,68 @@ __device__ __forceinline__ unsigned long long bin_key(double v) {
   if (kNumeric && b == 0x8000000000000000ull) b = 0ull;
   return b ^ ((unsigned long long)((long long)b >> 63) | 0x8000000000000000ull);
 }
-template <bool kThrInSmem, bool kNumeric = false>
+// KROW: bin_key_row(F) as a compile-time constant (0: run-time) — the search's table offsets become immediates
+template <bool kThrInSmem, bool kNumeric = false, int KROW = 0>
 __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, int64_t n_rows, int F, int Fp,
                                                   int64_t Np, const double* __restrict__ thr,
-                                                  const int* __restrict__ n_splits, int thr_stride,
+                                                  const int* __restrict__ n_splits, int thr_stride, int max_n,
                                                   uint8_t* __restrict__ bins_rm, uint8_t* __restrict__ bins_cm) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  // layout: tile[kBinRows][Fp + 4] bytes | (optional) threshold KEYS, one table of `sstride` 64-bit keys per feature
+  // layout: tile[kBinRows][Fp + 4] bytes | (optional) threshold KEYS [2^steps - 1][bin_key_row(F)] | n_splits[F]
+  // (max_n: an upper bound on n_splits[], known to the host, that sizes the table)
   uint8_t* tile = smem_raw;
   unsigned long long* skey = reinterpret_cast<unsigned long long*>(smem_raw + bin_tile_bytes(Fp));
-  const int sstride = bin_thr_smem_stride(thr_stride);
+  const int krow = KROW ? KROW : bin_key_row(F), half = (F + 1) >> 1;
+  const int steps = bin_search_steps(max_n), key_rows = (1 << steps) - 1;
+  int* sns = reinterpret_cast<int*>(skey + (size_t)key_rows * krow);      // n_splits, staged with the keys
   if (kThrInSmem) {
+    for (int i = threadIdx.x; i < key_rows * krow; i += blockDim.x) skey[i] = ~0ull;
+    for (int f = threadIdx.x; f < F; f += blockDim.x) sns[f] = n_splits[f];
+    __syncthreads();
     for (int i = threadIdx.x; i < F * thr_stride; i += blockDim.x) {
       const int f = i / thr_stride, k = i - f * thr_stride;
-      skey[f * sstride + k] = bin_key<kNumeric>(thr[i]);
+      if (k < sns[f]) skey[k * krow + (f >> 1) + (f & 1) * half] = bin_key<kNumeric>(thr[i]);
     }
   }
   // number of thresholds ordered before x = the bin: a branch-free lower bound over the feature's sorted keys, `steps`
-  // halvings for every value (steps = bits needed for the largest table), positions past the feature's own count masked
-  int steps = 0;
-  while ((1 << steps) <= thr_stride) steps++;         // n_splits[f] <= thr_stride < 2^steps
-  auto find_bin = [&](int f, int n, double x) -> int {
-    if (x != x) return n;                              // NaN sorts above every threshold
+  // halvings for every value; P is the position in units of table rows * krow
+  auto splits_of = [&](int f) -> int { return kThrInSmem ? sns[f] : n_splits[f]; };
+  auto find_bin = [&](auto fixed, int f, double x) -> int {   // fixed: integral_constant<int, steps> for 4..6 steps (tested outside the loops), 0 = any
+    if (x != x) return splits_of(f);                   // NaN sorts above every threshold
     const unsigned long long xk = bin_key<kNumeric>(x);
     int pos = 0;
-    for (int st = steps - 1; st >= 0; st--) {
-      const int j = pos + (1 << st);                   // candidate count: thresholds 0 .. j-1 all below x?
-      const int jj = min(j, max(n, 1)) - 1;
-      const unsigned long long k = kThrInSmem ? skey[f * sstride + jj] : bin_key<kNumeric>(thr[(size_t)f * thr_stride + jj]);
-      if (j <= n && k < xk) pos = j;
+    if constexpr (kThrInSmem) {
+      // A walks down the feature's column: A = column base + pos * row bytes; with KROW the offsets below are immediates
+      const char* kb = reinterpret_cast<const char*>(skey + (f >> 1) + (f & 1) * half);
+      const char* A = kb;
+#define EMRF_BIN_STEP(st) \
+      { if (*reinterpret_cast<const unsigned long long*>(A + ((1 << (st)) - 1) * krow * 8) < xk) A += (1 << (st)) * krow * 8; }
+      constexpr int kFixed = decltype(fixed)::value;
+      if constexpr (kFixed >= 4) {                     // the usual table lengths (maxBins 16 / 32 / 64): no ladder of tests in front
+        if constexpr (kFixed >= 6) EMRF_BIN_STEP(5)
+        if constexpr (kFixed >= 5) EMRF_BIN_STEP(4)
+        EMRF_BIN_STEP(3) EMRF_BIN_STEP(2) EMRF_BIN_STEP(1) EMRF_BIN_STEP(0)
+      } else {
+        switch (steps) {                               // falls through: straight-line code from the first step down
+          default: EMRF_BIN_STEP(7)
+          case 7: EMRF_BIN_STEP(6)
+          case 6: EMRF_BIN_STEP(5)
+          case 5: EMRF_BIN_STEP(4)
+          case 4: EMRF_BIN_STEP(3)
+          case 3: EMRF_BIN_STEP(2)
+          case 2: EMRF_BIN_STEP(1)
+          case 1: EMRF_BIN_STEP(0)
+        }
+      }
+#undef EMRF_BIN_STEP
+      pos = (int)(A - kb) / (krow * 8);
+    } else {
+      const int n = splits_of(f);
+      for (int st = steps - 1; st >= 0; st--) {
+        const int j = pos + (1 << st);                 // candidate count: thresholds 0 .. j-1 all below x?
+        const int jj = min(j, max(n, 1)) - 1;
+        if (j <= n && bin_key<kNumeric>(thr[(size_t)f * thr_stride + jj]) < xk) pos = j;
+      }
     }
     return pos;
   };
@@ -124,6 +168,9 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
     const double2* X2 = reinterpret_cast<const double2*>(X + base);
     const int pairs = total >> 1;
     constexpr int U = 8;
+    // (row, feature) of this thread's pair, advanced by 512 elements per load without dividing
+    const int dr = 512 / F, df = 512 - dr * F;
+    int r = (2 * (int)threadIdx.x) / F, f = 2 * (int)threadIdx.x - r * F;
     for (int p0 = threadIdx.x; p0 < pairs; p0 += U * 256) {
       double2 v[U];
 #pragma unroll
@@ -131,31 +178,40 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
         const int p = p0 + u * 256;
         v[u] = p < pairs ? __ldcs(X2 + p) : make_double2(0.0, 0.0);
       }
+      auto bin_pairs = [&](auto fixed) {
 #pragma unroll
-      for (int u = 0; u < U; u++) {
-        const int p = p0 + u * 256;
-        if (p < pairs) {
-          const int e = 2 * p;
-          const int r = e / F, f = e - r * F;
-          const int b0 = find_bin(f, n_splits[f], v[u].x), b1 = find_bin(f + 1, n_splits[f + 1], v[u].y);
-          *reinterpret_cast<uint16_t*>(tile + r * (RW << 2) + f) = (uint16_t)(b0 | (b1 << 8));
+        for (int u = 0; u < U; u++) {
+          const int p = p0 + u * 256;
+          if (p < pairs) {
+            const int b0 = find_bin(fixed, f, v[u].x), b1 = find_bin(fixed, f + 1, v[u].y);
+            *reinterpret_cast<uint16_t*>(tile + r * (RW << 2) + f) = (uint16_t)(b0 | (b1 << 8));
+          }
+          r += dr; f += df;
+          if (f >= F) { f -= F; r++; }
         }
-      }
+      };
+      if (steps == 5) bin_pairs(std::integral_constant<int, 5>{});
+      else if (steps == 6) bin_pairs(std::integral_constant<int, 6>{});
+      else if (steps == 4) bin_pairs(std::integral_constant<int, 4>{});
+      else bin_pairs(std::integral_constant<int, 0>{});
     }
   } else {
 #pragma unroll 4
     for (int e = threadIdx.x; e < total; e += blockDim.x) {
       const int r = e / F, f = e - r * F;
-      tile[r * (RW << 2) + f] = (uint8_t)find_bin(f, n_splits[f], X[base + e]);
+      tile[r * (RW << 2) + f] = (uint8_t)find_bin(std::integral_constant<int, 0>{}, f, X[base + e]);
     }
   }
   __syncthreads();
   if (bins_rm) {  // rows of the tile are contiguous in bins_rm: coalesced word copy
     uint32_t* dst = reinterpret_cast<uint32_t*>(bins_rm + (size_t)row0 * Fp);
     const int wpr = Fp >> 2;
-    for (int i = threadIdx.x; i < rows * wpr; i += blockDim.x) {
-      const int r = i / wpr, w = i - r * wpr;
+    const int dr = 256 / wpr, dw = 256 - dr * wpr;       // (row, word) advanced by 256 words without dividing
+    int r = (int)threadIdx.x / wpr, w = (int)threadIdx.x - r * wpr;
+    for (int i = threadIdx.x; i < rows * wpr; i += 256) {
       dst[i] = tile_w[r * RW + w];
+      r += dr; w += dw;
+      if (w >= wpr) { w -= wpr; r++; }
     }
   }
   if (bins_cm) {

@@ -65,6 +65,7 @@ def lib():
     L.emrf_ctx_destroy.argtypes = [vp]
     L.emrf_ctx_destroy.restype = None
     L.emrf_get_timings.argtypes = [vp, P(EmrfTimings)]
+    L.emrf_ctx_release_buffers.argtypes = [vp, P(i64)]
     L.emrf_dev_alloc.argtypes = [vp, i64, P(vp)]
     L.emrf_dev_free.argtypes = [vp, vp]
     L.emrf_host_alloc_pinned.argtypes = [i64, P(vp)]

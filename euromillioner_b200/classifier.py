@@ -104,6 +104,13 @@ class Context:
         check(_lib.lib().emrf_get_timings(self.h, C.byref(t)))
         return t.as_dict()
 
+    def release_buffers(self):
+        """Give the context's device buffers and the library's cached blocks back to the driver (the next fit
+        re-allocates); returns the bytes freed on the device."""
+        n = C.c_int64(0)
+        check(_lib.lib().emrf_ctx_release_buffers(self.h, C.byref(n)))
+        return int(n.value)
+
     def close(self):
         if getattr(self, "h", None):
             _lib.lib().emrf_ctx_destroy(self.h)

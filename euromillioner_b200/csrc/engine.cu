@@ -79,10 +79,11 @@ class DevCache {
     if (n <= ((size_t)64 << 20)) { size_t p = 256; while (p < n) p <<= 1; return p; }
     return (n + ((size_t)2 << 20) - 1) & ~(((size_t)2 << 20) - 1);
   }
-  cudaError_t take(size_t n, void** out, size_t* cap) {
+  cudaError_t take(size_t n, void** out, size_t* cap, int* dev_out) {   // on the CURRENT device; *dev_out = that device
     const size_t want = round_up(n);
     int dev = 0;
     cudaGetDevice(&dev);
+    *dev_out = dev;
     {
       std::lock_guard<std::mutex> lk(mu_);
       auto it = free_.find(std::make_pair(dev, want));
@@ -97,9 +98,7 @@ class DevCache {
     if (e == cudaSuccess) *cap = want;
     return e;
   }
-  void give(void* p, size_t cap) {
-    int dev = 0;
-    cudaGetDevice(&dev);
+  void give(void* p, size_t cap, int dev) {   // dev: the device the block was allocated on (not the caller's current one)
     std::lock_guard<std::mutex> lk(mu_);
     free_.insert(std::make_pair(std::make_pair(dev, cap), p));
   }
@@ -122,22 +121,26 @@ class DevCache {
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;   // capacity
+  int dev = -1;       // the device that owns the block: it goes back to that device's free list whoever releases it
   DevBuf() {}
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
-  DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+  DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes), dev(o.dev) { o.p = nullptr; o.bytes = 0; o.dev = -1; }
   ~DevBuf() { release(); }
   void release() {
-    if (p) DevCache::get().give(p, bytes);
+    if (p) DevCache::get().give(p, bytes, dev);
     p = nullptr;
     bytes = 0;
+    dev = -1;
   }
-  cudaError_t alloc(size_t n) {
-    if (p && n <= bytes) return cudaSuccess;
+  cudaError_t alloc(size_t n) {   // on the current device; a block that lives on another device is released, not reused
+    int cur = 0;
+    cudaGetDevice(&cur);
+    if (p && n <= bytes && dev == cur) return cudaSuccess;
     release();
-    return DevCache::get().take(n, &p, &bytes);
+    return DevCache::get().take(n, &p, &bytes, &dev);
   }
-  cudaError_t ensure(size_t n) {  // grow-only
+  cudaError_t ensure(size_t n) {  // grow-only (contexts own their buffers: one device for life)
     if (n <= bytes) return cudaSuccess;
     return alloc(n + n / 4);
   }
@@ -384,11 +387,21 @@ extern "C" int emrf_ctx_create_dist(int32_t device, int32_t rank, int32_t world,
   *out = c;
   return EMRF_OK;
 }
+static int nccl_allreduce(emrf_ctx* c, void* buf, size_t count, bool int32_max, cudaStream_t stream);
 extern "C" void emrf_ctx_destroy(emrf_ctx_t* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   for (int r = 0; r < 8; r++)
     if (r != c->rank && c->peer_stage[r]) cudaIpcCloseMemHandle(c->peer_stage[r]);
+  // EMRF_PEER_PUSH: this rank's staging buffer is mapped by its peers.  It may be freed only when every rank has
+  // finished with it and closed its mappings: a 1-word all-reduce is the barrier (contexts of one communicator are
+  // destroyed together, as they are created)
+  if (c->peer_ok && c->nccl_comm && c->stream && c->p_ipc.p) {
+    cudaStreamSynchronize(c->stream);
+    cudaMemsetAsync(c->p_ipc.p, 0, 4, c->stream);
+    nccl_allreduce(c, c->p_ipc.p, 1, false, c->stream);
+    cudaStreamSynchronize(c->stream);
+  }
   if (c->nccl_comm) {
     auto d = (ncclCommDestroy_t)dlsym(c->nccl_lib, "ncclCommDestroy");
     if (d) d(c->nccl_comm);
@@ -401,6 +414,24 @@ extern "C" void emrf_ctx_destroy(emrf_ctx_t* c) {
   delete c;
   DevCache::get().trim(dev);
 }
+extern "C" int emrf_ctx_release_buffers(emrf_ctx_t* c, int64_t* bytes_released) {
+  if (!c) return fail(EMRF_ERR_ARG, "ctx is NULL");
+  std::lock_guard<std::mutex> lk(c->fit_mu);
+  CU(cudaSetDevice(c->device));
+  for (cudaStream_t s_ : {c->stream, c->stream2, c->stream3, c->stream_comm})
+    if (s_) CU(cudaStreamSynchronize(s_));
+  size_t before = 0, after = 0, total = 0;
+  CU(cudaMemGetInfo(&before, &total));
+  // (the peer-mapped staging buffer of EMRF_PEER_PUSH stays: its peers have it mapped)
+  for (DevBuf* b : {&c->d_group, &c->d_results, &c->d_ghist, &c->d_tickets, &c->d_export, &c->d_split, &c->d_part, &c->d_seeds,
+                    &c->d_table, &c->d_tsum, &c->p_w, &c->p_X, &c->p_y, &c->p_labels, &c->p_rm, &c->p_cm, &c->p_ent0, &c->p_ent1,
+                    &c->p_counts, &c->p_segtab})
+    b->release();
+  DevCache::get().trim(c->device);
+  CU(cudaMemGetInfo(&after, &total));
+  if (bytes_released) *bytes_released = (int64_t)after - (int64_t)before;
+  return EMRF_OK;
+}
 extern "C" int emrf_get_timings(const emrf_ctx_t* c, emrf_timings_t* out) {
   if (!c || !out) return fail(EMRF_ERR_ARG, "NULL argument");
   *out = c->tm;
@@ -408,7 +439,7 @@ extern "C" int emrf_get_timings(const emrf_ctx_t* c, emrf_timings_t* out) {
 }
 // in-place all-reduce over the ctx communicator: uint32 sum (histograms, split records, raw bit
 // patterns against zeros) or int32 max (label flags)
-static int nccl_allreduce(emrf_ctx* c, void* buf, size_t count, bool int32_max, cudaStream_t stream = nullptr) {
+static int nccl_allreduce(emrf_ctx* c, void* buf, size_t count, bool int32_max, cudaStream_t stream) {
   if (c->world == 1) return EMRF_OK;
   static ncclAllReduce_t ar = nullptr;
   if (!ar) ar = (ncclAllReduce_t)dlsym(c->nccl_lib, "ncclAllReduce");
@@ -464,15 +495,30 @@ static int peer_stage_setup(emrf_ctx* c, size_t bytes) {
   TRY(nccl_allreduce_u32(c, c->p_ipc.as<uint32_t>(), all.size() / 4));
   CU(cudaMemcpyAsync(all.data(), c->p_ipc.p, all.size(), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
-  for (int r = 0; r < c->world; r++) {
+  uint32_t failed = 0;
+  std::string why;
+  for (int r = 0; r < c->world && !failed; r++) {
     if (r == c->rank) { c->peer_stage[r] = c->p_stage.p; continue; }
     cudaIpcMemHandle_t h;
     memcpy(&h, &all[(size_t)r * 64], 64);
     cudaError_t e = cudaIpcOpenMemHandle(&c->peer_stage[r], h, cudaIpcMemLazyEnablePeerAccess);
     if (e != cudaSuccess) {
       cudaGetLastError();
-      return fail(EMRF_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d) failed: %s", r, cudaGetErrorString(e));
+      c->peer_stage[r] = nullptr;
+      failed = 1;
+      why = std::string("cudaIpcOpenMemHandle(rank ") + std::to_string(r) + ") failed: " + cudaGetErrorString(e);
     }
+  }
+  // every rank proceeds or every rank fails: a rank that returned alone would leave the others in the next collective
+  CU(cudaMemcpyAsync(c->p_ipc.p, &failed, 4, cudaMemcpyHostToDevice, st));
+  TRY(nccl_allreduce_u32(c, c->p_ipc.as<uint32_t>(), 1));
+  uint32_t any_failed = 0;
+  CU(cudaMemcpyAsync(&any_failed, c->p_ipc.p, 4, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (any_failed) {
+    for (int r = 0; r < c->world; r++)
+      if (r != c->rank && c->peer_stage[r]) { cudaIpcCloseMemHandle(c->peer_stage[r]); c->peer_stage[r] = nullptr; }
+    return fail(EMRF_ERR_CUDA, "%s", failed ? why.c_str() : "a peer rank could not map the staging buffers");
   }
   c->peer_bytes = c->p_stage.bytes >= bytes ? bytes : 0;
   c->peer_ok = true;
@@ -1250,7 +1296,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   kern::labels_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(dy, N, P.num_classes, d_labels.as<uint8_t>(), d_flags.as<int>());
   tm.kernel_launches++;
   int flags[2] = {0, 0};
-  if (row_sharded) TRY(nccl_allreduce(c, d_flags.p, 2, true));
+  if (row_sharded) TRY(nccl_allreduce(c, d_flags.p, 2, true, nullptr));
   CU(cudaMemcpyAsync(flags, d_flags.p, 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   if (flags[0]) return fail(EMRF_ERR_ARG, "Classifier given dataset with invalid label: labels must be integers in [0, numClasses)");
@@ -1914,6 +1960,7 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       CU(cudaStreamSynchronize(st));
       std::swap(bigger.p, c->p_segtab.p);
       std::swap(bigger.bytes, c->p_segtab.bytes);
+      std::swap(bigger.dev, c->p_segtab.dev);
       seg_cap = c->p_segtab.bytes / sizeof(kern::Seg);
     }
     { const double d_ = now_ms() - t_host0; host_ms += d_; host_sel += d_; }
@@ -2548,6 +2595,12 @@ extern "C" int emrf_forest_feature_importances(const emrf_forest_t* f, double* o
 static int forest_to_device(emrf_ctx* c, emrf_forest* f) {
   std::lock_guard<std::mutex> lk(f->dev_mu);
   if (f->dev_device == c->device) return EMRF_OK;
+  if (f->dev_device >= 0) {   // the forest was last used on another GPU: that copy goes back to its own device's cache
+    for (DevBuf* b : {&f->d_nodes, &f->d_roots, &f->d_leaf_prob, &f->d_wnodes, &f->d_wroots, &f->d_pthr, &f->d_pns, &f->d_wblocks,
+                      &f->d_broots, &f->d_leaf_rec})
+      b->release();
+    f->dev_device = -1;
+  }
   ensure_double_stats(f);
   const int C = f->num_classes;
   const int64_t n = (int64_t)f->nodes.size();

@@ -101,6 +101,11 @@ int emrf_ctx_create_dist(int32_t device, int32_t rank, int32_t world, const uint
                          emrf_ctx_t** out);
 void emrf_ctx_destroy(emrf_ctx_t* ctx);
 int emrf_get_timings(const emrf_ctx_t* ctx, emrf_timings_t* out);
+/* A context keeps its fit-sized device buffers (TreePoint matrices, entry lists, histogram slots: ~1.4 GB after a
+ * configs[1] fit, tens of GB at 10M x 128) and the library keeps freed blocks in a per-device cache, so that the next fit
+ * allocates nothing.  A long-lived host (a Spark executor) calls this between jobs to give all of it back to the driver;
+ * the next fit re-allocates.  Not to be called while a fit or predict on this context is running. */
+int emrf_ctx_release_buffers(emrf_ctx_t* ctx, int64_t* bytes_released);
 
 /* Device/pinned memory helpers for hosts without a CUDA binding of their own (the JNI shim). */
 int emrf_dev_alloc(emrf_ctx_t* ctx, int64_t bytes, void** out);

@@ -275,6 +275,12 @@ def test_fit_is_deterministic_and_counts_are_conserved(ctx):
     # root count = sum of Poisson weights ~ N
     roots = e1["stats"][e1["tree_off"][:-1]].sum(axis=1)
     assert np.all(np.abs(roots - 300000) < 5000)
+    # the context hands its device buffers back (a long-lived executor between jobs) and fits the same forest afterwards
+    freed = ctx.release_buffers()
+    assert freed > 50 * 1000 * 1000, freed       # TreePoint matrices, entry lists, weights of a 300k x 64 x 10-tree fit
+    e3 = rf.fit(Dataset(X, y, num_partitions=256)).export()
+    for k in e1:
+        assert np.array_equal(e1[k], e3[k]), k
 
 
 def test_gain_verifier_runs_and_finds_no_mismatch(oracle):

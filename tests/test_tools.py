@@ -53,3 +53,29 @@ def test_compare_tool_reads_the_spark_golden_format(oracle, tmp_path):
     open(p, "w").write("\n".join(lines) + "\n")
     r = subprocess.run([sys.executable, tool, d, "--oracle"], capture_output=True, text=True, timeout=300)
     assert r.returncode == 1 and "threshold: 1 of" in r.stdout, r.stdout[-2000:]
+
+
+def test_java_host_and_jni_shim_agree():
+    """The Java host is source only (no JDK here): every `native` method of Native.java must have its JNI function in
+    emrf_jni.cpp, and the shim must type-check against include/emrf.h (compiled with a stand-in jni.h)."""
+    import re
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    java = open(os.path.join(root, "euromillioner_b200/host/java/com/euromillioner/gpu/Native.java")).read()
+    shim_path = os.path.join(root, "euromillioner_b200/host/jni/emrf_jni.cpp")
+    shim = open(shim_path).read()
+    natives = re.findall(r"static native [\w\[\]]+ (\w+)\(", java)
+    assert len(natives) >= 15
+    for name in natives:
+        assert f"Java_com_euromillioner_gpu_Native_{name}(" in shim, name
+    defined = re.findall(r"Java_com_euromillioner_gpu_Native_(\w+)\(", shim)
+    assert sorted(set(defined)) == sorted(set(natives))
+    # every Native.* call in the other classes names a declared method
+    for cls in ("GpuContext", "GpuRandomForestClassifier", "GpuRandomForestClassificationModel"):
+        src = open(os.path.join(root, f"euromillioner_b200/host/java/com/euromillioner/gpu/{cls}.java")).read()
+        for used in set(re.findall(r"Native\.(\w+)\(", src)):
+            assert used in natives, (cls, used)
+    stub = os.path.join(root, "tests", "golden", "jni_stub")
+    r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-I", stub, "-I", os.path.join(root, "include"), shim_path],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]

@@ -358,7 +358,11 @@ __device__ unsigned long long g_bag_prof[8];   // debug builds: 0 producer wait,
 // two steps from its carry-in and emits one nextDouble().  The Poisson loop (a running product
 // compared with exp(-mean)) is done by the walker warp, a block of 32 uniforms at a time, every
 // lane at once (poisson_block_jump).  Bit-identical to the serial stream (tests/test_gpu_stages.py).
-constexpr int kBagPairs = 4;              // partitions per CTA: a producer, a walker and an emitter warp each
+// partitions per CTA: a producer, a walker and an emitter warp each.  The kernel's time is one partition's serial latency
+// whatever shares the SM (2 / 4 / 7 / 8 per CTA: 5.50 / 5.48 / 5.28 / 5.45 ms for 1 024 partitions); 8 puts the 1 024
+// partitions of the bench on 128 of the 148 SMs and leaves the others to what runs beside it — with rows sharded the
+// findSplits all-reduce, whose NCCL kernel does not fit on an SM that holds bagging CTAs (5.7 -> 3.4 ms)
+constexpr int kBagPairs = 8;
 constexpr int kBagWarps = 3 * kBagPairs;
 constexpr int kBagStageRing = 4;          // blocks of draws the walker may run ahead of the emitter
 constexpr int kBagObuf = 1024;

@@ -103,6 +103,8 @@ def lib():
     L.emrf_host_group_tree_order.argtypes = [vp, i32, vp]
     L.emrf_host_num_features_per_node.argtypes = [P(EmrfParams), i32]
     L.emrf_host_packed_slot_layout.argtypes = [vp, i32, i32, vp, vp]
+    L.emrf_host_group_tiles_bound.argtypes = [vp, vp, i32, vp, i32, C.c_uint32]
+    L.emrf_host_group_tiles_bound.restype = i64
     _lib = L
     return L
 

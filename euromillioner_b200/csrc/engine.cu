@@ -5,8 +5,11 @@
 // groups, per-node feature subsets drawn from the driver RNG) stays on the host; everything
 // row-sized runs in the kernels of kernels.cuh.  Per group the GPU runs histogram+scan, the decide
 // kernels and the partition kernels back to back; the host gets a 16-byte scheduling record per node
-// first (what it needs to number the children and select the next group) and the full split records
-// (~0.5 KB per node) behind them, and builds the tree nodes one group later, under GPU work.
+// first (what it needs to number the children and select the next group; stored by the deciding kernel
+// straight into page-locked host memory) and the full split records (~0.5 KB per node) behind them on a
+// second stream, and builds the tree nodes one group later, under GPU work.  Several GPUs: rows sharded
+// (reduce-scatter of the node histograms keyed by node, light nodes packed to 16 bits, groups tiled on
+// the device) or trees sharded; see DESIGN.md §5.
 //
 // No PyTorch, no CPU fallback: every compute entry point needs a CUDA device.
 #include <cuda_runtime.h>
@@ -1500,6 +1503,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
   static const int rs_pieces_want = [] { const char* e = getenv("EMRF_RS_PIECES"); return e ? std::min(8, std::max(1, atoi(e))) : 1; }();
   const bool dev_tiles = row_sharded && c->world > 1 && !push_mode && !l2_blocked && rs_pieces_want == 1 && !env_flag("EMRF_RS_HOST_SIZES");
   std::vector<uint64_t> tree_acc(dev_tiles ? T : 0, 0);
+  std::vector<uint32_t> bound_ub;
+  std::vector<int32_t> bound_tree;
   // rows sharded over NCCL: light nodes cross the links as packed 16-bit counters (EMRF_NO_RS_PACK=1: all 32-bit)
   const bool rs_pack_ok = row_sharded && c->world > 1 && !push_mode && (B * C) % 2 == 0 && !env_flag("EMRF_NO_RS_PACK");
 
@@ -1754,8 +1759,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
     if (row_sharded) {   // the bounds were replaced by exact sizes after the group was selected ...
       total_entries = 0;
       if (dev_tiles) {   // ... or not: the nodes of a tree are disjoint, so they hold at most the tree's entries together
-        for (const GroupEntry& g : group) tree_acc[g.tree] += g.ub;
-        for (int t : cur->trees_seen) { total_entries += std::min<uint64_t>(tree_acc[t], tree_total[t]); tree_acc[t] = 0; }
+        bound_ub.resize(n_nodes); bound_tree.resize(n_nodes);
+        for (int i = 0; i < n_nodes; i++) { bound_ub[i] = group[i].ub; bound_tree[i] = group[i].tree; }
+        total_entries = hl::group_entries_bound(bound_ub.data(), bound_tree.data(), n_nodes, tree_total.data(), tree_acc.data());
       } else {
         for (const GroupEntry& g : group) total_entries += g.ub;
       }
@@ -1875,9 +1881,9 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       }
     }
     if (dev_tiles) {   // grids from the bounds: sum of ceil(len / tile) <= sum(len) / tile + nodes
-      n_tiles = (uint32_t)(total_entries / tile_len) + (uint32_t)n_nodes;
+      n_tiles = (uint32_t)hl::tiles_bound(total_entries, tile_len, n_nodes);
       pc_t0[n_pieces] = n_tiles;
-      ptiles_ub64 = total_entries / kern::kPartTile + (uint64_t)n_nodes;
+      ptiles_ub64 = hl::tiles_bound(total_entries, kern::kPartTile, n_nodes);
     }
     const size_t off_tq = align_up(off_tiles + (size_t)n_tiles * 4, 16);
     const size_t off_own = align_up(l2_blocked ? off_tq + (size_t)n_tiles * 4 : off_tiles + (size_t)n_tiles * 4, 16);
@@ -2126,7 +2132,8 @@ static int fit_impl(emrf_ctx* c, const emrf_params_t& P_in, const double* featur
       }
     }
     // ---- decisions and partition work on the device, the partition kernels right behind.  The host gets the
-    // compact scheduling records first (second stream) and the full records after them.
+    // compact scheduling records first (zero-copy stores of the deciding kernel) and the full records after them
+    // (second stream).
     kern::SplitNode* dsn = (kern::SplitNode*)c->d_split.p;
     uint32_t* dtn = (uint32_t*)((char*)c->d_split.p + off_ptn);
     uint32_t* d_tile_left = (uint32_t*)c->d_part.p;
@@ -3218,6 +3225,14 @@ extern "C" int32_t emrf_host_packed_slot_layout(const uint32_t* weight, int32_t 
                                                 int32_t* owner_out) {
   if (!weight || !slot_out || !owner_out || n < 0 || world < 1) return -1;
   return hl::packed_slot_layout(weight, n, world, slot_out, owner_out);
+}
+extern "C" int64_t emrf_host_group_tiles_bound(const uint32_t* ub, const int32_t* tree, int32_t n, const uint64_t* tree_total,
+                                               int32_t n_trees, uint32_t tile_len) {
+  if (!ub || !tree || !tree_total || n < 0 || n_trees < 1 || tile_len < 1) return -1;
+  for (int i = 0; i < n; i++)
+    if (tree[i] < 0 || tree[i] >= n_trees) return -1;
+  std::vector<uint64_t> acc((size_t)n_trees, 0);
+  return (int64_t)hl::tiles_bound(hl::group_entries_bound(ub, tree, n, tree_total, acc.data()), tile_len, n);
 }
 extern "C" int32_t emrf_host_num_features_per_node(const emrf_params_t* params, int32_t n_features) {
   return hl::features_per_node(*params, n_features);

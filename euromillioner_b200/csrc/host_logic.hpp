@@ -308,5 +308,22 @@ inline int packed_slot_layout(const uint32_t* weight, int n, int world, int* slo
   return share;
 }
 
+// Rows sharded, groups tiled on the device: the host knows a node's local entry count only as a bound `ub` (parent's
+// bound, node's weight over all ranks).  The nodes of one tree that are pending together are disjoint, so together they
+// hold at most the tree's local in-bag entries; a group's entries are therefore at most
+//   sum over its trees of min(sum of the tree's node bounds, tree_total[tree]),
+// and its tiles at most  entries / tile + nodes  (every node gets >= 1 tile: ceil(len/tile) <= len/tile + 1).
+// `acc` is scratch of one zeroed word per tree (left zeroed).
+inline uint64_t group_entries_bound(const uint32_t* ub, const int32_t* tree, int n, const uint64_t* tree_total, uint64_t* acc) {
+  for (int i = 0; i < n; i++) acc[tree[i]] += ub[i];
+  uint64_t total = 0;
+  for (int i = 0; i < n; i++) {
+    const int t = tree[i];
+    if (acc[t]) { total += acc[t] < tree_total[t] ? acc[t] : tree_total[t]; acc[t] = 0; }
+  }
+  return total;
+}
+inline uint64_t tiles_bound(uint64_t entries_bound, uint32_t tile_len, int n_nodes) { return entries_bound / tile_len + (uint64_t)n_nodes; }
+
 }  // namespace hostlogic
 }  // namespace emrf

@@ -251,6 +251,10 @@ int32_t emrf_host_group_tree_order(const int32_t* trees_first_seen, int32_t n, i
 int32_t emrf_host_num_features_per_node(const emrf_params_t* params, int32_t n_features);
 /* rows sharded: half-slot position and owner rank of every node of a group in the reduce-scattered histogram buffer
  * (nodes of weight <= 65535 take one half slot and travel as packed 16-bit counters); returns half slots per rank */
+/* rows sharded, groups tiled on the device: the number of tiles a group's launch is provisioned with, from the nodes'
+ * entry bounds, their trees and the trees' local in-bag totals (never below the exact count) */
+int64_t emrf_host_group_tiles_bound(const uint32_t* ub, const int32_t* tree, int32_t n, const uint64_t* tree_total,
+                                    int32_t n_trees, uint32_t tile_len);
 int32_t emrf_host_packed_slot_layout(const uint32_t* weight, int32_t n, int32_t world, int32_t* slot_out, int32_t* owner_out);
 
 #ifdef __cplusplus

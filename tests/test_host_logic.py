@@ -171,3 +171,27 @@ def test_packed_slot_layout_of_the_reduce_scattered_histograms(world):
                 if len(hv) and len(lt):
                     assert hv.max() + 2 <= lt.min()
             assert np.bincount(owner, minlength=world).max() <= -(-np.sum(w > 65535) // world) + -(-np.sum(w <= 65535) // world)
+
+
+def test_group_tiles_bound_is_never_below_the_exact_tile_count():
+    """Rows sharded: launches are provisioned from bounds and tiled on the device from exact lengths.  Random forests of
+    disjoint nodes: exact lengths partition (part of) each tree's entries, bounds are anything >= the exact length."""
+    L = _lib()
+    rng = np.random.default_rng(11)
+    for case in range(200):
+        n_trees = int(rng.integers(1, 6))
+        tree_total = rng.integers(1, 2_000_000, n_trees).astype(np.uint64)
+        n = int(rng.integers(1, 400))
+        tree = rng.integers(0, n_trees, n).astype(np.int32)
+        exact = np.zeros(n, np.uint32)
+        for t in range(n_trees):                      # split (part of) the tree's entries among its nodes; zeros allowed
+            idx = np.where(tree == t)[0]
+            if len(idx):
+                cuts = np.sort(rng.integers(0, int(tree_total[t]) + 1, len(idx) + 1))
+                exact[idx] = np.diff(cuts).astype(np.uint32)
+        ub = (exact + rng.integers(0, 3_000_000, n) * rng.integers(0, 2, n)).astype(np.uint32)    # loose for about half
+        for tile_len in (256, 2048, 8192, 65536):
+            got = L.emrf_host_group_tiles_bound(ub.ctypes.data, tree.ctypes.data, n, tree_total.ctypes.data, n_trees, tile_len)
+            need = int(np.sum(np.maximum(1, -(-exact.astype(np.int64) // tile_len))))
+            assert got >= need, (case, tile_len, got, need)
+            assert got <= int(tree_total.sum()) // tile_len + n           # and no looser than the trees allow

@@ -110,13 +110,16 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
   // number of thresholds ordered before x = the bin: a branch-free lower bound over the feature's sorted keys, `steps`
   // halvings for every value; P is the position in units of table rows * krow
   auto splits_of = [&](int f) -> int { return kThrInSmem ? sns[f] : n_splits[f]; };
-  auto find_bin = [&](auto fixed, int f, double x) -> int {   // fixed: integral_constant<int, steps> for 4..6 steps (tested outside the loops), 0 = any
-    if (x != x) return splits_of(f);                   // NaN sorts above every threshold
-    const unsigned long long xk = bin_key<kNumeric>(x);
+  // column of feature f in the key table (as a byte pointer); the two features of a pair are `half` columns apart
+  auto key_column = [&](int f) -> const char* { return reinterpret_cast<const char*>(skey + (f >> 1) + (f & 1) * half); };
+  // fixed: integral_constant<int, steps> for 4..6 steps (tested outside the loops), 0 = any; kb = key_column(f)
+  auto find_bin = [&](auto fixed, int f, const char* kb, double x) -> int {
     int pos = 0;
     if constexpr (kThrInSmem) {
+      // NaN sorts above every threshold: it searches as the largest key, which the padding rows hold too (they are not
+      // below it), so it lands on the feature's count without a branch
+      const unsigned long long xk = (x != x) ? ~0ull : bin_key<kNumeric>(x);
       // A walks down the feature's column: A = column base + pos * row bytes; with KROW the offsets below are immediates
-      const char* kb = reinterpret_cast<const char*>(skey + (f >> 1) + (f & 1) * half);
       const char* A = kb;
 #define EMRF_BIN_STEP(st) \
       { if (*reinterpret_cast<const unsigned long long*>(A + ((1 << (st)) - 1) * krow * 8) < xk) A += (1 << (st)) * krow * 8; }
@@ -140,6 +143,8 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
 #undef EMRF_BIN_STEP
       pos = (int)(A - kb) / (krow * 8);
     } else {
+      if (x != x) return splits_of(f);                 // NaN sorts above every threshold
+      const unsigned long long xk = bin_key<kNumeric>(x);
       const int n = splits_of(f);
       for (int st = steps - 1; st >= 0; st--) {
         const int j = pos + (1 << st);                 // candidate count: thresholds 0 .. j-1 all below x?
@@ -170,7 +175,10 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
     constexpr int U = 8;
     // (row, feature) of this thread's pair, advanced by 512 elements per load without dividing
     const int dr = 512 / F, df = 512 - dr * F;
+    const int row_bytes = RW << 2;
     int r = (2 * (int)threadIdx.x) / F, f = 2 * (int)threadIdx.x - r * F;
+    int toff = r * row_bytes + f;                        // byte offset of the pair inside the tile
+    const int dtoff = dr * row_bytes + df;
     for (int p0 = threadIdx.x; p0 < pairs; p0 += U * 256) {
       double2 v[U];
 #pragma unroll
@@ -183,11 +191,12 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
         for (int u = 0; u < U; u++) {
           const int p = p0 + u * 256;
           if (p < pairs) {
-            const int b0 = find_bin(fixed, f, v[u].x), b1 = find_bin(fixed, f + 1, v[u].y);
-            *reinterpret_cast<uint16_t*>(tile + r * (RW << 2) + f) = (uint16_t)(b0 | (b1 << 8));
+            const char* kb = key_column(f);              // f is even: feature f + 1 sits `half` columns further
+            const int b0 = find_bin(fixed, f, kb, v[u].x), b1 = find_bin(fixed, f + 1, kb + half * 8, v[u].y);
+            *reinterpret_cast<uint16_t*>(tile + toff) = (uint16_t)(b0 | (b1 << 8));
           }
-          r += dr; f += df;
-          if (f >= F) { f -= F; r++; }
+          f += df; toff += dtoff;
+          if (f >= F) { f -= F; toff += row_bytes - F; }
         }
       };
       if (steps == 5) bin_pairs(std::integral_constant<int, 5>{});
@@ -199,7 +208,7 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
 #pragma unroll 4
     for (int e = threadIdx.x; e < total; e += blockDim.x) {
       const int r = e / F, f = e - r * F;
-      tile[r * (RW << 2) + f] = (uint8_t)find_bin(std::integral_constant<int, 0>{}, f, X[base + e]);
+      tile[r * (RW << 2) + f] = (uint8_t)find_bin(std::integral_constant<int, 0>{}, f, key_column(f), X[base + e]);
     }
   }
   __syncthreads();

@@ -123,6 +123,20 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* __restrict__ X, 
       const char* A = kb;
 #define EMRF_BIN_STEP(st) \
       { if (*reinterpret_cast<const unsigned long long*>(A + ((1 << (st)) - 1) * krow * 8) < xk) A += (1 << (st)) * krow * 8; }
+      if constexpr (KROW > 0 && decltype(fixed)::value >= 4) {
+        // the same walk on the 32-bit shared address, one predicated add per step (the compiler's form of the loop above
+        // keeps base and offset apart: an OR and an add per step)
+        uint32_t a = (uint32_t)__cvta_generic_to_shared(kb);
+        const uint32_t a0 = a;
+#define EMRF_BIN_STEP_A(st)                                                                                          \
+        asm("{\n\t.reg .pred p;\n\t.reg .u64 k;\n\tld.shared.u64 k, [%0+%2];\n\tsetp.lt.u64 p, k, %1;\n\t@p add.u32 %0, %0, %3;\n\t}" \
+            : "+r"(a) : "l"(xk), "n"(((1 << (st)) - 1) * KROW * 8), "n"((1 << (st)) * KROW * 8));
+        if constexpr (decltype(fixed)::value >= 6) EMRF_BIN_STEP_A(5)
+        if constexpr (decltype(fixed)::value >= 5) EMRF_BIN_STEP_A(4)
+        EMRF_BIN_STEP_A(3) EMRF_BIN_STEP_A(2) EMRF_BIN_STEP_A(1) EMRF_BIN_STEP_A(0)
+#undef EMRF_BIN_STEP_A
+        return (int)((a - a0) / (uint32_t)((KROW ? KROW : 1) * 8));
+      }
       constexpr int kFixed = decltype(fixed)::value;
       if constexpr (kFixed >= 4) {                     // the usual table lengths (maxBins 16 / 32 / 64): no ladder of tests in front
         if constexpr (kFixed >= 6) EMRF_BIN_STEP(5)

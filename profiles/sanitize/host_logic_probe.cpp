@@ -47,6 +47,22 @@ int main() {
   acc += (unsigned long long)(hl::impurity_of(0, counts, 5) * 1e9) + (unsigned long long)(hl::impurity_of(1, counts, 5) * 1e9);
   acc += hl::select_nodes_examines_next(0, 10, 10) + 2 * hl::select_nodes_examines_next(1, 10, 10);
   acc += (unsigned long long)(hl::poisson_exp_policy(1.0) * 1e9);
+  // rows sharded: packed slot layout and the device-tiling bounds
+  for (int world : {1, 2, 3, 8}) {
+    for (int n : {1, 2, 31, 2542}) {
+      std::vector<uint32_t> w(n);
+      for (int i = 0; i < n; i++) w[i] = (uint32_t)((i * 2654435761u) >> (i % 3 ? 8 : 20));
+      std::vector<int> slot(n), owner(n);
+      acc += (unsigned)hl::packed_slot_layout(w.data(), n, world, slot.data(), owner.data());
+      for (int i = 0; i < n; i++) acc += (unsigned)slot[i] + (unsigned)owner[i];
+      std::vector<int32_t> tree(n);
+      std::vector<uint64_t> tot(7), scratch(7, 0);
+      for (int i = 0; i < n; i++) tree[i] = i % 7;
+      for (int t = 0; t < 7; t++) tot[t] = 1000u * (t + 1);
+      acc += hl::tiles_bound(hl::group_entries_bound(w.data(), tree.data(), n, tot.data(), scratch.data()), 256, n);
+      for (uint64_t v : scratch) acc += v;   // left zeroed
+    }
+  }
   hl::ScalaMutableIntTable tab;
   for (int i = 0; i < 300; i++) tab.insert((i * 7919) % 1000);
   for (int v : tab.iteration_order()) acc += (unsigned)v;

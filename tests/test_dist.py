@@ -1,5 +1,5 @@
-"""N > 1 path.  CPU (gloo, world_size 2): the rendezvous plumbing, tree ownership and the rule that only
-rank 0 runs/prints the reference arm.  GPU (needs >= 2 B200s): a tree-sharded fit equals the oracle forest."""
+"""N > 1 path.  CPU (gloo, world_size 2): the rendezvous plumbing, tree ownership, the packed histogram exchange of the
+rows-sharded fit (layout from the library, sums by gloo) and the rule that only rank 0 runs/prints the reference arm.  GPU (needs >= 2 B200s): a tree-sharded fit equals the oracle forest."""
 import json
 import os
 import subprocess
@@ -34,6 +34,71 @@ def test_gloo_world2_rendezvous_and_tree_ownership():
         assert p.exitcode == 0
     assert got[0] == (0, True, (0, 0, 2), [0, 2, 4, 6])
     assert got[1] == (1, True, (1, 1, 2), [1, 3, 5])
+
+
+def _gloo_packed_worker(rank, world, port, q):
+    """The rows-sharded exchange of one group on the CPU: every rank holds partial node histograms for its rows, lays them
+    out with the library's packed slot layout (light nodes as 16-bit pairs), the ranks sum the buffers as 32-bit integers
+    (gloo all-reduce standing in for NCCL's reduce-scatter: a rank then looks only at its own share) and every owner unpacks
+    its nodes.  The result must be the plain sum of the ranks' histograms."""
+    import ctypes as C
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from euromillioner_b200 import _lib
+    L = _lib.lib()
+    n_nodes, words = 37, 6 * 4 * 5 * 2                      # slot: f_sub x bins x classes counters (an even number)
+    rng = np.random.default_rng(5)                          # the same on both ranks: global weights and the split of each cell
+    weight = np.where(rng.random(n_nodes) < 0.7, rng.integers(1, 65536, n_nodes), rng.integers(65536, 400000, n_nodes)).astype(np.uint32)
+    total = np.zeros((n_nodes, words), np.int64)
+    for i in range(n_nodes):                                # cells of a node sum to its weight (so no cell exceeds it)
+        total[i] = rng.multinomial(int(weight[i]), np.full(words, 1.0 / words))
+    share0 = (total * rng.random((n_nodes, words))).astype(np.int64)
+    mine = share0 if rank == 0 else total - share0          # this rank's partial histograms
+    slot, owner = np.zeros(n_nodes, np.int32), np.zeros(n_nodes, np.int32)
+    share = L.emrf_host_packed_slot_layout(weight.ctypes.data, n_nodes, world, slot.ctypes.data, owner.ctypes.data)
+    half = words // 2
+    buf = np.zeros(share * world * half, np.int64)
+    for i in range(n_nodes):
+        at = int(slot[i]) * half
+        if weight[i] <= 65535:
+            buf[at:at + half] += mine[i, 0::2] | (mine[i, 1::2] << 16)      # two 16-bit counters per word
+        else:
+            buf[at:at + words] += mine[i]
+    t = torch.from_numpy(buf)
+    dist.all_reduce(t)                                       # exact integers; every word stays below 2^32
+    assert int(t.max()) < 2 ** 32
+    ok = True
+    for i in np.where(owner == rank)[0]:
+        at = int(slot[i]) * half
+        if weight[i] <= 65535:
+            w = t[at:at + half].numpy()
+            got = np.empty(words, np.int64)
+            got[0::2], got[1::2] = w & 0xffff, w >> 16
+        else:
+            got = t[at:at + words].numpy()
+        ok &= bool(np.array_equal(got, total[i]))
+    q.put((rank, ok, int(np.sum(owner == rank))))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_packed_histogram_exchange_is_exact():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_packed_worker, args=(r, 2, 29541, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got[0][1] and got[1][1]
+    assert got[0][2] + got[1][2] == 37 and min(got[0][2], got[1][2]) >= 17     # the nodes are dealt evenly
 
 
 def test_reference_arm_runs_on_rank0_only(monkeypatch):
